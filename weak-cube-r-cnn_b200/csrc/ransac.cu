@@ -1,0 +1,191 @@
+// ransac.cu -- RANSAC ground plane + up vector (north_star step 1, second half).
+// Reference: ProposalNetwork/utils/plane.py:79-134 (Plane_torch.fit_parallel),
+// roi_heads.py:508-525 (axis fix-ups).
+//
+// The reference materialises a (1000 x N) distance matrix four times over; here
+// each thread owns one hypothesis (plane + 1/denominator in registers) and every
+// point of the image streams once through shared memory in float4 tiles.
+// Rounding order is the reference's (see oracle/csrc/wcr_oracle.c):
+//   cross  = fma(a1, b2, -(a2*b1))           (torch.cross on CPU)
+//   norm   = sqrt(fma(z,z,fma(y,y,x*x)))     (torch.norm p=2)
+//   k      = -((c0*q0 + c1*q1) + c2*q2)      q = sample point 1 (plane.py:112)
+//   dist   = (((a*x + b*y) + c*z) + d) / sqrt((a*a + b*b) + c*c)
+// The library is built with -fmad=false so none of the separately rounded
+// products above is contracted.
+#include "common.cuh"
+
+namespace wcr {
+
+constexpr int RANSAC_TPB = 128;    // hypotheses per CTA
+constexpr int RANSAC_TILE = 1024;  // points per shared-memory tile (16 KB)
+
+__device__ __forceinline__ float cross_c(float a1, float b2, float a2, float b1)
+{
+    const float t = a2 * b1;
+    return fmaf(a1, b2, -t);
+}
+
+// three distinct indices in [0, n) from one Philox block (partial Fisher-Yates)
+__device__ __forceinline__ void philox_triple(uint64_t seed, uint32_t image, uint32_t iter,
+                                              int n, int &i0, int &i1, int &i2)
+{
+    uint32_t r[4];
+    Philox::gen(seed, iter, image, 0x52414e53u /* "RANS" */, 0u, r);
+    i0 = (int)__umulhi(r[0], (uint32_t)n);
+    i1 = (int)__umulhi(r[1], (uint32_t)(n - 1));
+    i2 = (int)__umulhi(r[2], (uint32_t)(n - 2));
+    if (i1 >= i0) ++i1;
+    const int lo = min(i0, i1), hi = max(i0, i1);
+    if (i2 >= lo) ++i2;
+    if (i2 >= hi) ++i2;
+}
+
+// grid = (ceil(iters / RANSAC_TPB), n_images)
+__global__ void __launch_bounds__(RANSAC_TPB)
+ransac_count_kernel(const float4 *__restrict__ pts, const int *__restrict__ count, int cap,
+                    const int32_t *__restrict__ sample_idx, int iters, float thresh,
+                    uint64_t seed, float4 *__restrict__ eqs, int *__restrict__ out_counts)
+{
+    __shared__ float4 tile[RANSAC_TILE];
+    const int img = blockIdx.y;
+    const int n = count[img];
+    const float4 *P = pts + (size_t)img * cap;
+    const int h = blockIdx.x * RANSAC_TPB + threadIdx.x;
+    const bool live = h < iters;
+
+    float a = 0.f, b = 0.f, c = 0.f, d = 0.f, den = 1.f;
+    if (live && n >= 3) {
+        int i0, i1, i2;
+        if (sample_idx) {
+            const int32_t *s = sample_idx + ((size_t)img * iters + h) * 3;
+            i0 = s[0]; i1 = s[1]; i2 = s[2];
+        } else {
+            philox_triple(seed, (uint32_t)img, (uint32_t)h, n, i0, i1, i2);
+        }
+        const float4 p0 = P[i0], p1 = P[i1], p2 = P[i2];
+        const float ax = p1.x - p0.x, ay = p1.y - p0.y, az = p1.z - p0.z;
+        const float bx = p2.x - p0.x, by = p2.y - p0.y, bz = p2.z - p0.z;
+        float cx = cross_c(ay, bz, az, by);
+        float cy = cross_c(az, bx, ax, bz);
+        float cz = cross_c(ax, by, ay, bx);
+        const float nrm = sqrtf(fmaf(cz, cz, fmaf(cy, cy, cx * cx)));
+        cx = cx / nrm; cy = cy / nrm; cz = cz / nrm;  // collinear triple -> NaN, never an inlier
+        a = cx; b = cy; c = cz;
+        d = -((cx * p1.x + cy * p1.y) + cz * p1.z);
+        den = sqrtf((a * a + b * b) + c * c);
+    } else if (live) {
+        a = b = c = d = nanf_();
+    }
+
+    int cnt = 0;
+    for (int base = 0; base < n; base += RANSAC_TILE) {
+        const int m = min(RANSAC_TILE, n - base);
+        __syncthreads();
+        for (int j = threadIdx.x; j < m; j += RANSAC_TPB) tile[j] = P[base + j];
+        __syncthreads();
+        if (den == 1.0f) {  // x / 1.0f == x exactly: skip the IEEE division
+#pragma unroll 8
+            for (int j = 0; j < m; ++j) {
+                const float4 p = tile[j];
+                const float dist = ((a * p.x + b * p.y) + c * p.z) + d;
+                cnt += (fabsf(dist) <= thresh) ? 1 : 0;
+            }
+        } else {
+#pragma unroll 4
+            for (int j = 0; j < m; ++j) {
+                const float4 p = tile[j];
+                const float dist = (((a * p.x + b * p.y) + c * p.z) + d) / den;
+                cnt += (fabsf(dist) <= thresh) ? 1 : 0;
+            }
+        }
+    }
+    if (live) {
+        out_counts[(size_t)img * iters + h] = cnt;
+        eqs[(size_t)img * iters + h] = make_float4(a, b, c, d);
+    }
+}
+
+// One CTA per image: first arg-max of the counts (torch.argmax returns the first
+// maximal index, plane.py:128), negate (plane.py:134), fix-ups
+// (roi_heads.py:514-525), optional inlier mask of the winner.
+__global__ void __launch_bounds__(256)
+ransac_select_kernel(const float4 *__restrict__ pts, const int *__restrict__ count, int cap,
+                     const float4 *__restrict__ eqs, const int *__restrict__ counts, int iters,
+                     float thresh, float *__restrict__ out_eq, float *__restrict__ out_normal,
+                     int *__restrict__ out_best, uint8_t *__restrict__ out_mask)
+{
+    __shared__ int s_cnt[256];
+    __shared__ int s_idx[256];
+    const int img = blockIdx.x;
+    const int *C = counts + (size_t)img * iters;
+    int best_c = -1, best_i = 0x7fffffff;
+    for (int i = threadIdx.x; i < iters; i += 256) {
+        const int c = C[i];
+        if (c > best_c) { best_c = c; best_i = i; }  // strided ascending: keeps first max
+    }
+    s_cnt[threadIdx.x] = best_c; s_idx[threadIdx.x] = best_i;
+    __syncthreads();
+    for (int o = 128; o > 0; o >>= 1) {
+        if (threadIdx.x < o) {
+            const int c2 = s_cnt[threadIdx.x + o], i2 = s_idx[threadIdx.x + o];
+            const int c1 = s_cnt[threadIdx.x], i1 = s_idx[threadIdx.x];
+            if (c2 > c1 || (c2 == c1 && i2 < i1)) { s_cnt[threadIdx.x] = c2; s_idx[threadIdx.x] = i2; }
+        }
+        __syncthreads();
+    }
+    const int best = s_idx[0];
+    const float4 e = eqs[(size_t)img * iters + best];
+    if (threadIdx.x == 0) {
+        out_best[img] = best;
+        out_eq[img * 4 + 0] = -e.x; out_eq[img * 4 + 1] = -e.y;
+        out_eq[img * 4 + 2] = -e.z; out_eq[img * 4 + 3] = -e.w;
+        float nx = -e.x, ny = -e.y, nz = -e.z;
+        if (fabsf(nz) > fabsf(ny)) {  // back wall: n[[0,2,1]] * [1,1,-1]
+            const float t = ny; ny = nz; nz = -t;
+        }
+        if (fabsf(nx) > fabsf(ny)) {  // side wall: n[[2,0,1]] * [-1,1,1]
+            const float ox = nx, oy = ny, oz = nz;
+            nx = -oz; ny = ox; nz = oy;
+        }
+        if (ny < 0.f) { nx = -nx; ny = -ny; nz = -nz; }
+        out_normal[img * 3 + 0] = nx; out_normal[img * 3 + 1] = ny; out_normal[img * 3 + 2] = nz;
+    }
+    if (out_mask) {
+        const int n = count[img];
+        const float4 *P = pts + (size_t)img * cap;
+        const float den = sqrtf((e.x * e.x + e.y * e.y) + e.z * e.z);
+        for (int j = threadIdx.x; j < n; j += 256) {
+            const float4 p = P[j];
+            const float dist = (((e.x * p.x + e.y * p.y) + e.z * p.z) + e.w) / den;
+            out_mask[(size_t)img * cap + j] = (fabsf(dist) <= thresh) ? 1 : 0;
+        }
+    }
+}
+
+}  // namespace wcr
+
+extern "C" int wcr_ransac_ground(const float *pts, const int *count, int cap, int n_images,
+                                 const int32_t *sample_idx, int iters, float thresh,
+                                 uint64_t seed, float *out_eq, float *out_normal,
+                                 int *out_best, int *out_counts, uint8_t *out_inlier_mask,
+                                 float *ws_eqs, void *stream)
+{
+    WCR_CHECK_DEVICE();
+    WCR_REQUIRE(pts && count && out_eq && out_normal && out_best && out_counts && ws_eqs,
+                "wcr_ransac_ground: null pointer");
+    WCR_REQUIRE(n_images >= 0 && iters >= 1 && cap >= 1, "wcr_ransac_ground: bad sizes");
+    WCR_REQUIRE(n_images <= 65535, "wcr_ransac_ground: too many images for one call");
+    WCR_REQUIRE((((uintptr_t)pts | (uintptr_t)ws_eqs) & 15) == 0,
+                "wcr_ransac_ground: pts/ws_eqs not 16-byte aligned");
+    if (n_images == 0) return WCR_OK;
+    dim3 grid((iters + wcr::RANSAC_TPB - 1) / wcr::RANSAC_TPB, n_images);
+    wcr::ransac_count_kernel<<<grid, wcr::RANSAC_TPB, 0, (cudaStream_t)stream>>>(
+        (const float4 *)pts, count, cap, sample_idx, iters, thresh, seed, (float4 *)ws_eqs,
+        out_counts);
+    WCR_CHECK_LAUNCH("ransac_count_kernel");
+    wcr::ransac_select_kernel<<<n_images, 256, 0, (cudaStream_t)stream>>>(
+        (const float4 *)pts, count, cap, (const float4 *)ws_eqs, out_counts, iters, thresh,
+        out_eq, out_normal, out_best, out_inlier_mask);
+    WCR_CHECK_LAUNCH("ransac_select_kernel");
+    return WCR_OK;
+}

@@ -1,0 +1,86 @@
+"""ctypes binding of include/wcr.h (libwcr_b200.so). Plumbing only.
+
+The product path has NO CPU fallback: if the shared library is missing or the
+device is not sm_100, calls raise. torch is used for device memory and streams;
+every pointer handed to C is ``tensor.data_ptr()``.
+"""
+from __future__ import annotations
+
+import ctypes
+import os
+
+import torch
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "_lib", "libwcr_b200.so")
+
+c_void_p, c_int, c_float, c_i64, c_u64 = (ctypes.c_void_p, ctypes.c_int, ctypes.c_float,
+                                          ctypes.c_int64, ctypes.c_uint64)
+
+# name -> (restype, argtypes); must list every symbol include/wcr.h declares.
+SIGNATURES = {
+    "wcr_abi_version": (c_int, []),
+    "wcr_last_error": (ctypes.c_char_p, []),
+    "wcr_device_check": (c_int, []),
+    "wcr_launch_count": (c_i64, []),
+    "wcr_reset_launch_count": (None, []),
+    "wcr_unproject_ground": (c_int, [c_void_p, c_int, c_int, c_void_p, c_int, c_void_p, c_void_p]),
+    "wcr_unproject_cloud": (c_int, [c_void_p, c_int, c_int, c_int, c_int, c_void_p, c_i64, c_void_p]),
+    "wcr_ransac_ground": (c_int, [c_void_p, c_void_p, c_int, c_int, c_void_p, c_int, c_float, c_u64,
+                                  c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
+                                  c_void_p]),
+}
+
+_lib = None
+
+
+class WcrError(RuntimeError):
+    pass
+
+
+def load():
+    """Load libwcr_b200.so; raise loudly if it is not built."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise WcrError(
+            f"{LIB_PATH} is missing: build it with `python weak-cube-r-cnn_b200/build.py` "
+            "(there is no CPU or eager fallback for this path)")
+    lib = ctypes.CDLL(LIB_PATH)
+    for name, (res, args) in SIGNATURES.items():
+        fn = getattr(lib, name)  # AttributeError if the symbol is not exported
+        fn.restype = res
+        fn.argtypes = args
+    _lib = lib
+    return lib
+
+
+def check(rc: int, what: str):
+    if rc != 0:
+        msg = load().wcr_last_error()
+        raise WcrError(f"{what} failed (code {rc}): {msg.decode() if msg else ''}")
+
+
+def stream_ptr(device=None) -> int:
+    return torch.cuda.current_stream(device).cuda_stream
+
+
+def ptr(t) -> int | None:
+    if t is None:
+        return None
+    return t.data_ptr()
+
+
+def require_cuda(*tensors):
+    for t in tensors:
+        if t is not None and not t.is_cuda:
+            raise WcrError("wcr: CUDA tensors required (there is no CPU fallback on this path)")
+
+
+def launch_count() -> int:
+    return int(load().wcr_launch_count())
+
+
+def reset_launch_count():
+    load().wcr_reset_launch_count()
