@@ -1,0 +1,330 @@
+#!/usr/bin/env python
+"""bench.py -- cube proposals scored/sec on synthetic SUN RGB-D-shaped inputs.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl wcr|reference]
+    python -m torch.distributed.run --nproc-per-node N ... bench.py --gpus N ...
+
+A step = one pass of the hot path over one batch (BASELINE.json configs[1]:
+64 images 640x480, ~20 GT boxes/image, 1000 proposals/box) per GPU:
+ground-plane RANSAC -> pseudo depth -> fused sample+score+top-k (+ the NCCL
+all-gather of the top-k records when N > 1). Prints ONE JSON line on rank 0.
+
+--impl reference times the CPU arm: the reference path's restatement in C
+(oracle/, OpenMP over all host cores) on a bounded sample of the same workload.
+The reference itself is Python/torch and cannot travel to the GPU box
+(/root/reference does not exist there); DESIGN.md "Measurement" says so.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "weak-cube-r-cnn_b200"))
+
+IMAGES_PER_GPU = 64
+H, W, NPROP, TOPK = 480, 640, 1000, 16
+ALG_FLOP_PER_TEST = 18.0      # 3 sub + 9 mul + 6 add per (proposal, point)
+FP32_NOMINAL_TFLOPS = 148 * 128 * 2 * 1.965e9 / 1e12   # 74.4, SURVEY §8d
+METRIC = "cube proposals scored/sec"
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="wcr", choices=["wcr", "reference"])
+    ap.add_argument("--images", type=int, default=IMAGES_PER_GPU, help="images per GPU")
+    ap.add_argument("--cpu-sample-images", type=int, default=2)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    return ap.parse_args()
+
+
+def workload_name(images):
+    return (f"SUN RGB-D val-shaped batch: {images} images {W}x{H} per GPU, ~20 GT boxes/image "
+            f"(Poisson), {NPROP} proposals/box, top-{TOPK}")
+
+
+# ------------------------------------------------------------------ CPU arm --
+def cpu_arm(n_images: int, first: int = 0, repeats: int = 1):
+    """Time the oracle's C restatement (OpenMP, all cores) on `n_images` images of
+    the workload. Returns (proposals/s, cores, sample string, seconds)."""
+    import numpy as np
+    import torch
+    from oracle import clib, cubes as oc, ground as og
+    from wcr import synth
+    import random
+    ims = synth.make_batch(n_images, H, W, first=first)
+    priors = synth.make_priors()
+    rng = np.random.default_rng(0)
+    n_prop = 0
+    t0 = time.perf_counter()
+    for _ in range(repeats):
+        for im in ims:
+            depth = im["depth"].numpy()
+            K = im["K"].numpy()
+            g = None if tuple(im["ground"].shape) == (1, 1) else im["ground"].numpy()
+            pts, _ = og.unproject_ground_frame(depth, g, K, 5)
+            if len(pts) >= 3:
+                ids = og.draw_id_samples(len(pts), 1000, random.Random(1))
+                eq, _, _ = og.fit_parallel(pts, ids, 0.05)
+                normal = og.fix_up_normal(eq[:3])
+            else:
+                normal = np.array([0, 1, 0], dtype=np.float32)
+            for b in range(len(im["boxes"])):
+                box = im["boxes"][b].numpy()
+                z0 = float(oc.box_center_depth(depth, box))
+                pm = priors[int(im["classes"][b])].numpy()
+                a = np.empty((7, NPROP), dtype=np.float32)
+                a[0] = np.clip(rng.normal((box[0] + box[2]) / 2, 0.25 * (box[2] - box[0]), NPROP), box[0], box[2])
+                a[1] = np.clip(rng.normal((box[1] + box[3]) / 2, 0.25 * (box[3] - box[1]), NPROP), box[1], box[3])
+                a[2] = np.clip(rng.normal(z0, 0.15 * z0, NPROP), 0.5 * z0, 1.5 * z0)
+                for d in range(3):
+                    a[3 + d] = np.clip(rng.normal(pm[0, d], pm[1, d], NPROP), 0.05, pm[0, d] + 3 * pm[1, d])
+                a[6] = rng.uniform(0, np.pi, NPROP)
+                cubes = oc.assemble_cubes(K, normal, a)
+                r = oc.score_box(depth, K, box, (H, W), cubes)
+                oc.topk(r["score"], TOPK)
+                n_prop += NPROP
+    dt = time.perf_counter() - t0
+    cores = clib.num_threads()
+    sample = (f"{n_images} images x{repeats} of the same synthetic workload "
+              f"({n_prop // NPROP} boxes, {n_prop} proposals), C restatement with OpenMP")
+    return n_prop / dt, cores, sample, dt
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    from oracle import clib
+    clib.build()
+    n = max(1, args.cpu_sample_images)
+    cpu_arm(1)  # warm
+    vals, secs = [], 0.0
+    for w in range(args.warmup):
+        cpu_arm(1, first=w)
+    for s in range(args.steps):
+        v, cores, sample, dt = cpu_arm(n, first=s * n)
+        vals.append(v); secs += dt
+    value = sum(vals) / len(vals)
+    line = {
+        "impl": "reference", "metric": METRIC, "value": value, "unit": "proposals/s",
+        "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": 1e3 * secs / args.steps, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": workload_name(args.images), "step_sample": sample},
+        "cpu_baseline": {"value": value, "unit": "proposals/s", "cores": cores, "kind": "port",
+                         "sample": sample},
+        "e2e": {"value": value, "unit": "proposals/s", "h2d_bytes_per_step": 0,
+                "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+# ------------------------------------------------------------------ GPU arm --
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons DURING the timed region."""
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index: int):
+        self.rows, self.proc, self.index = [], None, index
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                 "-i", str(self.index), "-lms", "100"],
+                stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except OSError:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(",")])
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        self.t.join(timeout=2)
+        mhz = sorted(int(r[0]) for r in self.rows if r and r[0].isdigit())
+        mx = [int(r[1]) for r in self.rows if len(r) > 1 and r[1].isdigit()]
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = [n for i, n in enumerate(names)
+                   if any(len(r) > 2 + i and r[2 + i] == "Active" for r in self.rows)]
+        return {"sm_mhz": mhz[len(mhz) // 2] if mhz else None, "sm_max_mhz": mx[0] if mx else None,
+                "samples": len(mhz), "reasons": reasons}
+
+
+def run_wcr(args):
+    import torch
+    import torch.distributed as dist
+    from wcr import _abi, synth, dist as wdist
+    from wcr.pipeline import ShardRunner
+    from wcr.proposals import ScoreConfig, score_topk, box_center_depth
+    from wcr.ground import unproject_cloud
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    lib = _abi.load()                      # raises if the CUDA library is not built
+    _abi.check(lib.wcr_device_check(), "wcr_device_check")
+
+    # weak scaling: every rank owns `images` images of the global synthetic set
+    ims = synth.make_batch(args.images, H, W, first=rank * args.images)
+    priors = synth.make_priors()
+    n_local_boxes = sum(len(im["boxes"]) for im in ims)
+    gather = wdist.TopkGather(n_local_boxes, TOPK, dev)
+    runner = ShardRunner(ims, NPROP, dev, priors=priors, score_cfg=ScoreConfig(k=TOPK), seed=1234,
+                         records=gather.send)
+    runner.upload()
+    torch.cuda.synchronize()
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)   # > 126 MB L2
+
+    def one_step(ev=None):
+        runner.step(ev)
+        if world > 1:
+            gather.gather_padded()
+
+    # algorithmic work of one scoring launch: N * sum_b P_b point tests
+    runner.step()
+    z0 = box_center_depth(runner.shard, runner.boxes)
+    full = score_topk(runner.shard, runner.boxes, None, NPROP, runner.score_cfg, priors=runner.priors,
+                      normals=runner.normals, z0=z0, seed=1234, want_all=True)
+    tests_per_launch = float(full["npts"].sum().item()) * NPROP
+    del full
+
+    for _ in range(max(args.warmup, 3)):
+        flush.zero_(); one_step()
+    torch.cuda.synchronize()
+
+    # ---- device-resident timing (value) + scoring-kernel timing (roofline) ----
+    ev = [(torch.cuda.Event(True), torch.cuda.Event(True), torch.cuda.Event(True),
+           torch.cuda.Event(True)) for _ in range(args.steps)]
+    sampler = ClockSampler(local)
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize()
+    if rank == 0:
+        sampler.start()
+    _abi.reset_launch_count()
+    for s in range(args.steps):
+        flush.zero_()                      # L2 flush between timed iterations (untimed)
+        ev[s][0].record()
+        one_step((ev[s][2], ev[s][3]))
+        ev[s][1].record()
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+    launches = _abi.launch_count()
+    step_ms = sum(e[0].elapsed_time(e[1]) for e in ev)
+    score_ms = sum(e[2].elapsed_time(e[3]) for e in ev) / args.steps
+
+    # ---- end-to-end through the public API with host buffers ------------------
+    for _ in range(2):
+        runner.run_host()
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    for s in range(args.steps):
+        runner.run_host()
+        if world > 1:
+            gather.gather_padded()
+            torch.cuda.synchronize()
+    e2e_s = time.perf_counter() - t0
+    clocks = sampler.stop() if rank == 0 else None
+
+    # ---- FP32 probe + HBM-bound unprojection kernel (aux rooflines) -----------
+    probe_out = torch.empty(148 * 8 * 256 * 2, dtype=torch.float32, device=dev)
+    e0, e1 = torch.cuda.Event(True), torch.cuda.Event(True)
+    best = 0.0
+    for _ in range(5):
+        e0.record()
+        flops = lib.wcr_probe_ffma(probe_out.data_ptr(), probe_out.numel(), 4096, _abi.stream_ptr(dev))
+        e1.record(); torch.cuda.synchronize()
+        best = max(best, flops / (e0.elapsed_time(e1) * 1e-3) / 1e12)
+    fp32_probe_tflops = best
+    cloud_ms = []
+    for _ in range(5):
+        flush.zero_(); e0.record(); unproject_cloud(runner.shard, 1); e1.record()
+        torch.cuda.synchronize(); cloud_ms.append(e0.elapsed_time(e1))
+    cloud_bytes = args.images * H * W * (4 + 16)
+    cloud_gbs = cloud_bytes / (min(cloud_ms) * 1e-3) / 1e9
+
+    t = torch.tensor([step_ms, e2e_s, score_ms], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    step_ms, e2e_s, score_ms = (float(x) for x in t.cpu())
+    props = torch.tensor([runner.n_proposals], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(props)
+    total_props = float(props.item())
+
+    if rank == 0:
+        peaks = {}
+        try:
+            peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+        except OSError:
+            pass
+        hbm_peak = peaks.get("hbm_gbs", 6650.0)
+        achieved = ALG_FLOP_PER_TEST * tests_per_launch / (score_ms * 1e-3) / 1e12
+        line = {
+            "metric": METRIC, "value": total_props * args.steps / (step_ms * 1e-3),
+            "unit": "proposals/s", "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
+            "ms_per_step": step_ms / args.steps, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": workload_name(args.images), "l2": "256 MiB flush between timed steps",
+                       "parallelism": f"image-sharded x{world}, all-gather of top-k records",
+                       "boxes_rank0": runner.n_boxes, "rng": "in-kernel Philox4x32-10"},
+            "e2e": {"value": total_props * args.steps / e2e_s, "unit": "proposals/s",
+                    "h2d_bytes_per_step": runner.h2d_bytes, "d2h_bytes_per_step": runner.d2h_bytes},
+            "gpu_launches": int(launches),
+            "clocks": clocks,
+            "roofline": {"bound": "fp32", "kernel": "score_topk_kernel", "achieved": achieved,
+                         "peak": fp32_probe_tflops, "unit": "TFLOP/s",
+                         "frac": achieved / fp32_probe_tflops,
+                         "peak_source": "FFMA probe kernel timed in this run (MEASURED_PEAKS.json has no FP32 figure)",
+                         "frac_of_nominal_74.4": achieved / FP32_NOMINAL_TFLOPS,
+                         "point_tests_per_s": tests_per_launch / (score_ms * 1e-3),
+                         "alg_flop_per_test": ALG_FLOP_PER_TEST, "kernel_ms": score_ms,
+                         "kernel_share_of_step": score_ms * args.steps / step_ms, "traffic": None},
+            "roofline_aux": {"bound": "hbm", "kernel": "unproject_cloud_kernel", "achieved": cloud_gbs,
+                             "peak": hbm_peak, "unit": "GB/s", "frac": cloud_gbs / hbm_peak,
+                             "bytes_per_launch": cloud_bytes},
+        }
+        if not args.no_cpu_baseline and world == 1:
+            from oracle import clib
+            clib.build()
+            cpu_arm(1)
+            v, cores, sample, dt = cpu_arm(args.cpu_sample_images)
+            line["cpu_baseline"] = {"value": v, "unit": "proposals/s", "cores": cores,
+                                    "kind": "port", "sample": sample, "seconds": dt}
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    a = parse()
+    if a.impl == "reference":
+        run_reference(a)
+    else:
+        run_wcr(a)

@@ -52,6 +52,13 @@ int         wcr_device_check(void);
 int64_t     wcr_launch_count(void);
 void        wcr_reset_launch_count(void);
 
+/* FP32-pipe probe (16 independent FFMA chains per thread, 8 CTAs x 256 threads
+ * per SM). Returns the number of FLOPs enqueued (> 0) or a negative error; the
+ * caller times it with CUDA events: the FP32 roofline denominator of this device
+ * under this run's clocks. out must hold sm_count*8*256 floats. Not counted by
+ * wcr_launch_count(). */
+int64_t     wcr_probe_ffma(float *out, int64_t out_elems, int iters, void *stream);
+
 /* ---------------------------------------------------------------- step 1 -- */
 
 /* Strided unprojection in the "ground frame" + ordered compaction of the
@@ -93,6 +100,105 @@ int wcr_ransac_ground(const float *pts /* float4 */, const int *count, int cap,
                       int *out_counts, uint8_t *out_inlier_mask,
                       float *ws_eqs /* float4 [n_images][iters] workspace */,
                       void *stream);
+
+/* ------------------------------------------------------------ steps 2+3 -- */
+
+/* One GT 2D box of the shard. 32 bytes, device memory. */
+typedef struct WcrBox {
+    float   x1, y1, x2, y2;   /* GT 2D box in pixels of its image */
+    int32_t image;            /* index into the WcrImage table */
+    int32_t cls;              /* category id -> priors[cls] */
+    float   clamp0, clamp1;   /* the `clamp` tuple handed to Cubes.get_bube_corners
+                                 (spaces.py:224): x is clamped with clamp0, y with
+                                 clamp1. The ROI head passes [H, W] (roi_heads.py:
+                                 801-806, 950) -- the caller decides, as in the
+                                 reference. */
+} WcrBox;
+
+/* Free parameters of the proposal composite (project spec, the
+ * reference ships only the building blocks). 48 bytes, passed BY VALUE fields
+ * through a host pointer (h_params). */
+typedef struct WcrSampleParams {
+    float sigma_xy;       /* std of the 2D centre as a fraction of box w / h      */
+    float sigma_z;        /* std of z as a fraction of the pseudo depth z0        */
+    float z_lo, z_hi;     /* z truncated to [z0*z_lo, z0*z_hi]                    */
+    float dim_lo;         /* dims truncated to [dim_lo, mean + dim_hi_sigmas*std] */
+    float dim_hi_sigmas;
+    float yaw_lo, yaw_hi; /* yaw ~ U[yaw_lo, yaw_hi)                              */
+    int32_t max_tries;    /* bounded rejection loop of the in-kernel sampler      */
+    int32_t reserved0, reserved1, reserved2;
+} WcrSampleParams;
+
+/* Score weights: score = s_iou^e_iou * s_pts^e_pts * s_seg^e_seg with small
+ * non-negative integer exponents (0 == term skipped), SURVEY A3.12. */
+typedef struct WcrScoreParams {
+    int32_t e_iou, e_pts, e_seg;
+    int32_t point_stride;   /* depth ROI sub-sampling (1 == every pixel)          */
+    int32_t seg_mode;       /* 0 = mask_iou (utils.py:225), 1 = mod_mask_iou (:236) */
+    int32_t reserved0, reserved1, reserved2;
+} WcrScoreParams;
+
+#define WCR_CUBE_FLOATS   15   /* [cx cy cz w h l R(9 row-major)], spaces.py:130-150 */
+#define WCR_RECORD_FLOATS 20   /* idx(i32) score cube[15] s_iou s_pts s_seg           */
+#define WCR_SAMPLE_ATTRS   7   /* u v z w h l yaw                                     */
+#define WCR_MAX_TOPK      32
+
+/* One block of the in-kernel generator (Philox4x32-10, counter (c0..c3), key =
+ * the 64-bit seed, low word first): lets a test pin the device generator to the
+ * published known-answer vectors.  out4 [4] uint32, device. */
+int wcr_philox_block(uint64_t key, uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3,
+                     uint32_t *out4, void *stream);
+
+/* Pseudo depth per box: depth at the box centre with the reference's 10-px clamp
+ * (roi_heads.py:645-652, pseudo_gt_z_point_loss applied to the GT box centre).
+ *   out_z0 [n_boxes] */
+int wcr_box_center_depth(const WcrImage *images, const WcrBox *boxes, int n_boxes,
+                         float *out_z0, void *stream);
+
+/* Per-box cube sampling (north_star step 2; composite A2.7 built from
+ * ProposalNetwork/utils/utils.py:41-59 sample_normal_in_range, :111-145
+ * vec_perp_t / orthobasis_from_normal_t / rotate_vector_t and the lifting of
+ * roi_heads.py:927-928).
+ *   priors   [n_classes][2][3]  (mean w,h,l ; std w,h,l), math_util.py:419
+ *   normals  [n_images][3]      up vectors from wcr_ransac_ground
+ *   z0       [n_boxes]          from wcr_box_center_depth
+ *   replay   [n_boxes][7][N] final samples (u v z w h l yaw) drawn by the
+ *            reference's own sampler (parity mode), or NULL => in-kernel
+ *            Philox4x32-10 keyed by (seed; proposal, box, attribute, try)
+ *   out_cubes [n_boxes][N][15] */
+int wcr_sample_cubes(const WcrImage *images, const WcrBox *boxes, int n_boxes,
+                     const float *priors, const float *normals, const float *z0,
+                     const WcrSampleParams *h_params, int N, const float *replay,
+                     uint64_t seed, float *out_cubes, void *stream);
+
+/* Fused scoring + per-box top-k (north_star step 3; composite A3.12). Per
+ * (box, proposal): 8 corners (math_util.py:198-217), projection + clamp
+ * (spaces.py:224-245), projected box (conversions.py:25-48), 2D IoU vs the GT
+ * box (utils.py:181-187), point-in-oriented-cube count over the depth pixels of
+ * the GT box ROI unprojected through K (A3.11 / A1.4), segmentation-mask
+ * coverage (utils.py:225-245, 490-493), combined score, top-k.
+ *   cubes     [n_boxes][N][15] or NULL => sampled in-kernel (same generator and
+ *             arguments as wcr_sample_cubes; priors/normals/z0/h_sample/seed are
+ *             only read in that case)
+ *   seg_bits  bit-packed per-box masks or NULL (term skipped); seg_off[n_boxes+1]
+ *             word offsets; box b's mask covers its integer ROI, row-major,
+ *             rows padded to 32 bits
+ *   k <= WCR_MAX_TOPK
+ *   out_records [n_boxes][k][20]; slots beyond N hold idx = -1
+ *   optional per-proposal outputs (NULL to skip), all [n_boxes][N]:
+ *     out_scores, out_iou, out_count (int32), out_proj [n_boxes][N][4]
+ *   out_npts  [n_boxes] valid depth points per ROI (P_b), optional
+ *   ws        workspace, wcr_score_workspace_bytes(n_boxes, N, k) bytes */
+int64_t wcr_score_workspace_bytes(int n_boxes, int N, int k);
+int wcr_score_topk(const WcrImage *images, const WcrBox *boxes, int n_boxes,
+                   const float *cubes, int N,
+                   const float *priors, const float *normals, const float *z0,
+                   const WcrSampleParams *h_sample, uint64_t seed,
+                   const uint32_t *seg_bits, const int64_t *seg_off,
+                   const WcrScoreParams *h_score, int k,
+                   float *out_records, float *out_scores, float *out_iou,
+                   int32_t *out_count, float *out_proj, int32_t *out_npts,
+                   void *ws, void *stream);
 
 #ifdef __cplusplus
 }

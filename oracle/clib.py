@@ -24,7 +24,7 @@ def build(force: bool = False) -> str:
             and os.path.getmtime(_OUT) >= os.path.getmtime(_SRC)):
         return _OUT
     cmd = ["gcc", "-O2", "-fPIC", "-shared", "-std=c11", "-ffp-contract=off",
-           "-fno-fast-math", "-fopenmp", "-o", _OUT, _SRC, "-lm"]
+           "-fno-fast-math", "-fopenmp", "-mfma", "-mavx2", "-o", _OUT, _SRC, "-lm"]
     subprocess.check_call(cmd)
     return _OUT
 
@@ -58,3 +58,73 @@ def plane_counts(pts: np.ndarray, eqs: np.ndarray, thresh: float) -> np.ndarray:
                            _p(eqs, ctypes.c_float), ctypes.c_int64(eqs.shape[0]),
                            ctypes.c_float(thresh), _p(counts, ctypes.c_int64))
     return counts
+
+
+# ---- steps 2+3 --------------------------------------------------------------
+c_f, c_i = ctypes.c_float, ctypes.c_int
+
+
+def box_center_depth(depth: np.ndarray, box: np.ndarray) -> np.float32:
+    depth = np.ascontiguousarray(depth, dtype=np.float32)
+    box = np.ascontiguousarray(box, dtype=np.float32)
+    fn = lib().orc_box_center_depth
+    fn.restype = c_f
+    return np.float32(fn(_p(depth, c_f), c_i(depth.shape[0]), c_i(depth.shape[1]),
+                         c_i(depth.shape[1]), _p(box, c_f)))
+
+
+def assemble_cubes(K4: np.ndarray, normal: np.ndarray, attrs: np.ndarray) -> np.ndarray:
+    """attrs (7, N) = u v z w h l yaw -> cubes (N, 15)."""
+    K4 = np.ascontiguousarray(K4, dtype=np.float32)
+    normal = np.ascontiguousarray(normal, dtype=np.float32)
+    attrs = np.ascontiguousarray(attrs, dtype=np.float32)
+    N = attrs.shape[1]
+    out = np.empty((N, 15), dtype=np.float32)
+    lib().orc_assemble_cubes(_p(K4, c_f), _p(normal, c_f), _p(attrs, c_f), c_i(N), _p(out, c_f))
+    return out
+
+
+def project_cube(cube: np.ndarray, K4: np.ndarray, clamp0: float, clamp1: float):
+    cube = np.ascontiguousarray(cube, dtype=np.float32)
+    K4 = np.ascontiguousarray(K4, dtype=np.float32)
+    box = np.empty(4, dtype=np.float32)
+    corners = np.empty((8, 2), dtype=np.float32)
+    lib().orc_project_cube(_p(cube, c_f), _p(K4, c_f), c_f(clamp0), c_f(clamp1), _p(box, c_f),
+                           _p(corners, c_f))
+    return box, corners
+
+
+def score_box(depth: np.ndarray, K4: np.ndarray, gbox: np.ndarray, clamp0: float, clamp1: float,
+              cubes: np.ndarray, stride: int = 1, e_iou: int = 1, e_pts: int = 1):
+    """-> dict(score (N,), iou (N,), count (N,) i32, proj (N,4), npts int)."""
+    depth = np.ascontiguousarray(depth, dtype=np.float32)
+    K4 = np.ascontiguousarray(K4, dtype=np.float32)
+    gbox = np.ascontiguousarray(gbox, dtype=np.float32)
+    cubes = np.ascontiguousarray(cubes, dtype=np.float32)
+    N = cubes.shape[0]
+    score = np.empty(N, dtype=np.float32)
+    iou = np.empty(N, dtype=np.float32)
+    count = np.empty(N, dtype=np.int32)
+    proj = np.empty((N, 4), dtype=np.float32)
+    fn = lib().orc_score_box
+    fn.restype = c_i
+    npts = fn(_p(depth, c_f), c_i(depth.shape[0]), c_i(depth.shape[1]), c_i(depth.shape[1]),
+              _p(K4, c_f), _p(gbox, c_f), c_f(clamp0), c_f(clamp1), _p(cubes, c_f), c_i(N),
+              c_i(stride), c_i(e_iou), c_i(e_pts), _p(score, c_f), _p(iou, c_f),
+              _p(count, ctypes.c_int32), _p(proj, c_f))
+    return {"score": score, "iou": iou, "count": count, "proj": proj, "npts": int(npts)}
+
+
+def philox4x32_10(ctr, key) -> np.ndarray:
+    ctr = np.ascontiguousarray(ctr, dtype=np.uint32)
+    key = np.ascontiguousarray(key, dtype=np.uint32)
+    out = np.empty(4, dtype=np.uint32)
+    lib().orc_philox4x32_10(_p(ctr, ctypes.c_uint32), _p(key, ctypes.c_uint32),
+                            _p(out, ctypes.c_uint32))
+    return out
+
+
+def num_threads() -> int:
+    fn = lib().orc_num_threads
+    fn.restype = c_i
+    return int(fn())

@@ -12,6 +12,9 @@
 #include <math.h>
 #include <stdint.h>
 #include <stddef.h>
+#ifdef _OPENMP
+#include <omp.h>
+#endif
 
 /* ProposalNetwork/utils/plane.py:96-113 -- hypothesis plane through 3 sampled
  * points. torch.cross(A,B) on CPU evaluates a1*b2 - a2*b1 as
@@ -60,4 +63,210 @@ void orc_plane_counts(const float *pts, int64_t n, const float *eqs, int64_t ite
         }
         counts[i] = cnt;
     }
+}
+
+/* ======================================================================== */
+/* steps 2+3: cube assembly, projection, IoU, point-in-cube, top-k           */
+/* ======================================================================== */
+
+typedef struct { float fx, fy, cx, cy; } orc_intr;
+
+static inline float clamp_keep_nan(float x, float lo, float hi)
+{
+    if (x != x) return x;
+    float t = x < lo ? lo : x;
+    return t > hi ? hi : t;
+}
+
+/* roi_heads.py:645-652 applied to the GT box centre (Boxes.get_centers). */
+float orc_box_center_depth(const float *depth, int H, int W, int pitch, const float *box)
+{
+    float x = (box[0] + box[2]) / 2.f, y = (box[1] + box[3]) / 2.f;
+    x = clamp_keep_nan(x, 10.f, (float)(W - 11));
+    y = clamp_keep_nan(y, 10.f, (float)(H - 11));
+    return depth[(size_t)(int)y * pitch + (int)x];
+}
+
+/* utils.py:111-131 vec_perp_t / rotate_vector_t / orthobasis_from_normal_t and the
+ * lifting of roi_heads.py:927-928. attrs = (u v z w h l yaw). cos/sin are passed
+ * in so that a caller can inject the device's values (libm and CUDA differ in the
+ * last ulp); orc_assemble_cube() below uses libm. */
+void orc_assemble_cube_cs(const float *K4, const float *n, const float *attrs, float c, float s,
+                          float *cube)
+{
+    const float n0 = n[0], n1 = n[1], n2 = n[2];
+    float vp[3], kxv[3], nk[3], x[3];
+    if (n0 == 0.f) { vp[0] = 0.f; vp[1] = n2; vp[2] = -n1; }
+    else {
+        float m = sqrtf((n1 * n1 + n0 * n0) + 0.f);
+        if (!(m > 1e-8f)) m = 1e-8f;
+        vp[0] = n1 / m; vp[1] = (-n0) / m; vp[2] = 0.f / m;
+    }
+    kxv[0] = cross_c(n1, vp[2], n2, vp[1]);
+    kxv[1] = cross_c(n2, vp[0], n0, vp[2]);
+    kxv[2] = cross_c(n0, vp[1], n1, vp[0]);
+    const float kv = (n0 * vp[0] + n1 * vp[1]) + n2 * vp[2];
+    nk[0] = n0 * kv; nk[1] = n1 * kv; nk[2] = n2 * kv;
+    const float omc = 1.f - c;
+    for (int r = 0; r < 3; ++r) x[r] = (vp[r] * c + kxv[r] * s) + nk[r] * omc;
+    const float y0 = cross_c(n1, x[2], n2, x[1]);
+    const float y1 = cross_c(n2, x[0], n0, x[2]);
+    const float y2 = cross_c(n0, x[1], n1, x[0]);
+    const float u = attrs[0], v = attrs[1], z = attrs[2];
+    cube[0] = (z * (u - K4[2])) / K4[0];
+    cube[1] = (z * (v - K4[3])) / K4[1];
+    cube[2] = z;
+    cube[3] = attrs[3]; cube[4] = attrs[4]; cube[5] = attrs[5];
+    cube[6] = x[0]; cube[7] = n0; cube[8] = y0;
+    cube[9] = x[1]; cube[10] = n1; cube[11] = y1;
+    cube[12] = x[2]; cube[13] = n2; cube[14] = y2;
+}
+
+void orc_assemble_cubes(const float *K4, const float *n, const float *attrs /* [7][N] */, int N,
+                        float *cubes /* [N][15] */)
+{
+    for (int j = 0; j < N; ++j) {
+        float a[7];
+        for (int t = 0; t < 7; ++t) a[t] = attrs[(size_t)t * N + j];
+        orc_assemble_cube_cs(K4, n, a, cosf(a[6]), sinf(a[6]), cubes + (size_t)j * 15);
+    }
+}
+
+/* math_util.py:198-217 + spaces.py:224-245 + conversions.py:25-48.
+ * out_box = x1 y1 x2 y2 ; corners (optional) 8 x (x, y) clamped. */
+void orc_project_cube(const float *cube, const float *K4, float clamp0, float clamp1,
+                      float *out_box, float *corners)
+{
+    static const int NX[8] = {1, 0, 0, 1, 1, 0, 0, 1};  /* vertices with -l/2 */
+    static const int NY[8] = {1, 1, 0, 0, 1, 1, 0, 0};  /* vertices with -h/2 */
+    const float hx = cube[5] / 2.f, hy = cube[4] / 2.f, hz = cube[3] / 2.f;
+    const float *R = cube + 6;
+    const float lo0 = (float)(int)(-clamp0 / 2.f + 1.f), hi0 = (float)(int)(clamp0 - 1.f + clamp0);
+    const float lo1 = (float)(int)(-clamp1 / 2.f + 1.f), hi1 = (float)(int)(clamp1 - 1.f + clamp1);
+    float mnx = 0, mxx = 0, mny = 0, mxy = 0;
+    int nanx = 0, nany = 0;
+    for (int i = 0; i < 8; ++i) {
+        const float lx = (NX[i] ? -1.f : 1.f) * hx, ly = (NY[i] ? -1.f : 1.f) * hy,
+                    lz = (i < 4 ? -1.f : 1.f) * hz;
+        const float X = fmaf(R[2], lz, fmaf(R[1], ly, R[0] * lx)) + cube[0];
+        const float Y = fmaf(R[5], lz, fmaf(R[4], ly, R[3] * lx)) + cube[1];
+        const float Z = fmaf(R[8], lz, fmaf(R[7], ly, R[6] * lx)) + cube[2];
+        float px = fmaf(K4[2], Z, K4[0] * X) / Z;
+        float py = fmaf(K4[3], Z, K4[1] * Y) / Z;
+        px = clamp_keep_nan(px, lo0, hi0);
+        py = clamp_keep_nan(py, lo1, hi1);
+        if (corners) { corners[2 * i] = px; corners[2 * i + 1] = py; }
+        nanx |= (px != px); nany |= (py != py);
+        if (i == 0) { mnx = mxx = px; mny = mxy = py; }
+        else {
+            mnx = fminf(mnx, px); mxx = fmaxf(mxx, px);
+            mny = fminf(mny, py); mxy = fmaxf(mxy, py);
+        }
+    }
+    out_box[0] = nanx ? NAN : mnx; out_box[2] = nanx ? NAN : mxx;
+    out_box[1] = nany ? NAN : mny; out_box[3] = nany ? NAN : mxy;
+}
+
+/* detectron2 pairwise_iou as called from utils.py:181-187. */
+float orc_iou_2d(const float *g, const float *p)
+{
+    const float a1 = (g[2] - g[0]) * (g[3] - g[1]);
+    const float a2 = (p[2] - p[0]) * (p[3] - p[1]);
+    float iw = fminf(g[2], p[2]) - fmaxf(g[0], p[0]);
+    float ih = fminf(g[3], p[3]) - fmaxf(g[1], p[1]);
+    if (p[0] != p[0] || p[1] != p[1]) return 0.f;
+    if (iw < 0.f) iw = 0.f;
+    if (ih < 0.f) ih = 0.f;
+    const float inter = iw * ih;
+    return inter > 0.f ? inter / ((a1 + a2) - inter) : 0.f;
+}
+
+static inline float ipow_(float x, int e) { float r = 1.f; for (int i = 0; i < e; ++i) r = r * x; return r; }
+
+/* SURVEY A3.11/A3.12 for ONE box: N cubes against the depth pixels of the box's
+ * integer ROI (Boxes.clip + .long(), roi_heads.py:590-597), sub-sampled by
+ * `stride`. Point p = z*(a_u, b_v, 1), a_u = (u-cx)/fx, b_v = (v-cy)/fy;
+ *   q_k = fma(z, fma(R0k, a_u, fma(R1k, b_v, R2k)), -O_k),
+ *   O_k = fma(R2k, cz, fma(R1k, cy, R0k*cx));
+ * inside iff |q_0| <= l/2 and |q_1| <= h/2 and |q_2| <= w/2 (math_util.py:198-207
+ * axis mapping). Returns P_b (valid points). */
+int orc_score_box(const float *depth, int H, int W, int pitch, const float *K4, const float *gbox,
+                  float clamp0, float clamp1, const float *cubes, int N, int stride, int e_iou,
+                  int e_pts, float *out_score, float *out_iou, int *out_count, float *out_proj)
+{
+    float t;
+    t = gbox[0] < 0.f ? 0.f : gbox[0]; const int u0 = (int)(t > W ? (float)W : t);
+    t = gbox[2] < 0.f ? 0.f : gbox[2]; const int u1 = (int)(t > W ? (float)W : t);
+    t = gbox[1] < 0.f ? 0.f : gbox[1]; const int v0 = (int)(t > H ? (float)H : t);
+    t = gbox[3] < 0.f ? 0.f : gbox[3]; const int v1 = (int)(t > H ? (float)H : t);
+    int npts = 0;
+    if (e_pts > 0)
+        for (int v = v0; v < v1; v += stride)
+            for (int u = u0; u < u1; u += stride) {
+                const float d = depth[(size_t)v * pitch + u];
+                npts += (d > 0.f && d <= 3.402823466e38f);
+            }
+#pragma omp parallel for schedule(dynamic, 8)
+    for (int j = 0; j < N; ++j) {
+        const float *cube = cubes + (size_t)j * 15;
+        float A[3], B[3], C[3], NO[3], Hh[3];
+        for (int k = 0; k < 3; ++k) {
+            A[k] = cube[6 + k]; B[k] = cube[9 + k]; C[k] = cube[12 + k];
+            NO[k] = -fmaf(C[k], cube[2], fmaf(B[k], cube[1], A[k] * cube[0]));
+        }
+        Hh[0] = cube[5] / 2.f; Hh[1] = cube[4] / 2.f; Hh[2] = cube[3] / 2.f;
+        int cnt = 0;
+        if (e_pts > 0)
+            for (int v = v0; v < v1; v += stride) {
+                const float bv = ((float)v - K4[3]) / K4[1];
+                const float G0 = fmaf(B[0], bv, C[0]), G1 = fmaf(B[1], bv, C[1]),
+                            G2 = fmaf(B[2], bv, C[2]);
+                for (int u = u0; u < u1; u += stride) {
+                    const float d = depth[(size_t)v * pitch + u];
+                    if (!(d > 0.f && d <= 3.402823466e38f)) continue;
+                    const float au = ((float)u - K4[2]) / K4[0];
+                    const float q0 = fmaf(d, fmaf(A[0], au, G0), NO[0]);
+                    const float q1 = fmaf(d, fmaf(A[1], au, G1), NO[1]);
+                    const float q2 = fmaf(d, fmaf(A[2], au, G2), NO[2]);
+                    cnt += (fabsf(q0) <= Hh[0]) & (fabsf(q1) <= Hh[1]) & (fabsf(q2) <= Hh[2]);
+                }
+            }
+        float pb[4];
+        orc_project_cube(cube, K4, clamp0, clamp1, pb, NULL);
+        const float siou = orc_iou_2d(gbox, pb);
+        const float spts = npts > 0 ? (float)cnt / (float)npts : 0.f;
+        out_score[j] = (ipow_(siou, e_iou) * ipow_(spts, e_pts)) * 1.f;
+        if (out_iou) out_iou[j] = siou;
+        if (out_count) out_count[j] = cnt;
+        if (out_proj) { out_proj[4 * j] = pb[0]; out_proj[4 * j + 1] = pb[1]; out_proj[4 * j + 2] = pb[2]; out_proj[4 * j + 3] = pb[3]; }
+    }
+    return npts;
+}
+
+/* Philox4x32-10 (Salmon et al., SC'11), for the known-answer test of the
+ * in-kernel generator. */
+void orc_philox4x32_10(const uint32_t ctr[4], const uint32_t key[2], uint32_t out[4])
+{
+    uint32_t c0 = ctr[0], c1 = ctr[1], c2 = ctr[2], c3 = ctr[3], k0 = key[0], k1 = key[1];
+    for (int i = 0; i < 10; ++i) {
+        const uint64_t p0 = (uint64_t)0xD2511F53u * c0, p1 = (uint64_t)0xCD9E8D57u * c2;
+        const uint32_t n0 = (uint32_t)(p1 >> 32) ^ c1 ^ k0, n1 = (uint32_t)p1;
+        const uint32_t n2 = (uint32_t)(p0 >> 32) ^ c3 ^ k1, n3 = (uint32_t)p0;
+        c0 = n0; c1 = n1; c2 = n2; c3 = n3;
+        k0 += 0x9E3779B9u; k1 += 0xBB67AE85u;
+    }
+    out[0] = c0; out[1] = c1; out[2] = c2; out[3] = c3;
+}
+
+int orc_num_threads(void)
+{
+    int n = 1;
+#ifdef _OPENMP
+#pragma omp parallel
+    {
+#pragma omp single
+        n = omp_get_num_threads();
+    }
+#endif
+    return n;
 }

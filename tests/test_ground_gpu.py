@@ -64,7 +64,11 @@ def test_ransac_replay_bit_exact(cuda_lib, H, W):
     ids = draw_reference_samples(count.cpu().tolist(), 1000, rng)
     res = ransac_ground(pts, count, ids.cuda(), want_mask=True)
     P = pts.cpu().numpy(); C = count.cpu().numpy()
+    assert (C >= 3).sum() >= 2
     for i in range(len(ims)):
+        if C[i] < 3:
+            assert torch.isnan(res["eq"][i]).all()
+            continue
         p = P[i, :C[i], :3]
         eq, inl, counts = og.fit_parallel(p, ids[i].numpy().astype(np.int64))
         assert np.array_equal(res["counts"][i].cpu().numpy(), counts)

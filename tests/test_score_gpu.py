@@ -1,0 +1,197 @@
+"""Steps 2+3 parity on the GPU, through the C ABI, against oracle/cubes.py.
+
+Bars (north_star): point-in-cube counts and top-k indices bit-exact against the
+oracle's stated rounding order; IoU / scores within 1e-5 relative (here they are
+bit-exact too, the assertion still states the tolerance)."""
+import numpy as np
+import pytest
+import torch
+
+from oracle import clib, cubes as oc
+
+pytestmark = pytest.mark.gpu
+RTOL = 1e-5
+
+
+def _setup(n_images, H=480, W=640, n_boxes=4, first=0):
+    from wcr import synth
+    from wcr.images import ImageShard
+    from wcr.proposals import BoxTable
+    ims = [synth.make_image(first + i, H, W, n_boxes=n_boxes, dummy_ground=False)
+           for i in range(n_images)]
+    shard = ImageShard([im["depth"].cuda() for im in ims], [im["ground"].cuda() for im in ims],
+                       [im["K"] for im in ims])
+    boxes = BoxTable(shard, [im["boxes"] for im in ims], [im["classes"] for im in ims])
+    normals = torch.tensor([[0.01 * i, 1.0, -0.02 * i] for i in range(n_images)])
+    normals = normals / normals.norm(dim=1, keepdim=True)
+    return ims, shard, boxes, synth.make_priors(), normals
+
+
+def test_philox_known_answers(cuda_lib):
+    """Random123 kat_vectors for philox4x32-10 pin the device generator."""
+    from wcr import _abi
+    kat = [((0, 0, 0, 0), (0, 0), (0x6627e8d5, 0xe169c58d, 0xbc57ac4c, 0x9b00dbd8)),
+           ((0xffffffff,) * 4, (0xffffffff,) * 2, (0x408f276d, 0x41c83b0e, 0xa20bc7c6, 0x6d5451fd)),
+           ((0x243f6a88, 0x85a308d3, 0x13198a2e, 0x03707344), (0xa4093822, 0x299f31d0),
+            (0xd16cfe09, 0x94fdcceb, 0x5001e420, 0x24126ea1))]
+    out = torch.zeros(4, dtype=torch.int32, device="cuda")
+    for ctr, key, want in kat:
+        _abi.check(cuda_lib.wcr_philox_block(key[0] | (key[1] << 32), *ctr, out.data_ptr(),
+                                             _abi.stream_ptr()), "wcr_philox_block")
+        got = out.cpu().numpy().view(np.uint32)
+        assert tuple(int(x) for x in got) == want
+        assert tuple(int(x) for x in clib.philox4x32_10(ctr, key)) == want
+
+
+def test_box_center_depth_bit_exact(cuda_lib):
+    from wcr.proposals import box_center_depth
+    ims, shard, boxes, _, _ = _setup(3, n_boxes=6)
+    z0 = box_center_depth(shard, boxes).cpu().numpy()
+    ref = [oc.box_center_depth(im["depth"].numpy(), im["boxes"][b].numpy())
+           for im in ims for b in range(len(im["boxes"]))]
+    assert np.array_equal(z0, np.array(ref, dtype=np.float32))
+
+
+def _replay_attrs(ims, priors, N, seed):
+    """Plausible (u v z w h l yaw) samples per box, host-drawn (stands in for the
+    reference sampler here; tests/test_compose_ref.py uses the real one)."""
+    g = torch.Generator().manual_seed(seed)
+    out = []
+    for im in ims:
+        for b in range(len(im["boxes"])):
+            x1, y1, x2, y2 = im["boxes"][b].tolist()
+            pm = priors[int(im["classes"][b])]
+            z0 = float(oc.box_center_depth(im["depth"].numpy(), im["boxes"][b].numpy()))
+            a = torch.empty(7, N)
+            a[0] = (x1 + x2) / 2 + 0.25 * (x2 - x1) * torch.randn(N, generator=g)
+            a[1] = (y1 + y2) / 2 + 0.25 * (y2 - y1) * torch.randn(N, generator=g)
+            a[2] = z0 * (1 + 0.15 * torch.randn(N, generator=g)).clamp(0.5, 1.5)
+            for d in range(3):
+                a[3 + d] = (pm[0, d] + pm[1, d] * torch.randn(N, generator=g)).clamp(min=0.05)
+            a[6] = np.pi * torch.rand(N, generator=g)
+            out.append(a)
+    return torch.stack(out)
+
+
+def test_sample_replay_matches_oracle(cuda_lib):
+    from wcr.proposals import propose
+    N = 257
+    ims, shard, boxes, priors, normals = _setup(2, n_boxes=3)
+    replay = _replay_attrs(ims, priors, N, 5)
+    cubes = propose(shard, boxes, priors, normals, N, replay=replay.cuda()).cpu().numpy()
+    gb = 0
+    for i, im in enumerate(ims):
+        for b in range(len(im["boxes"])):
+            ref = oc.assemble_cubes(im["K"].numpy(), normals[i].numpy(), replay[gb].numpy())
+            # centres / dims bit-exact; R within 2 ulp of libm's sin/cos
+            assert np.array_equal(cubes[gb][:, :6], ref[:, :6])
+            np.testing.assert_allclose(cubes[gb][:, 6:], ref[:, 6:], rtol=0, atol=3e-7)
+            gb += 1
+
+
+def test_sample_native_deterministic_and_in_range(cuda_lib):
+    from wcr.proposals import propose, ProposalConfig, box_center_depth
+    N = 1000
+    ims, shard, boxes, priors, normals = _setup(2, n_boxes=5)
+    cfg = ProposalConfig()
+    c1 = propose(shard, boxes, priors, normals, N, cfg, seed=11)
+    c2 = propose(shard, boxes, priors, normals, N, cfg, seed=11)
+    c3 = propose(shard, boxes, priors, normals, N, cfg, seed=12)
+    assert torch.equal(c1, c2) and not torch.equal(c1, c3)
+    c = c1.cpu()
+    z0 = box_center_depth(shard, boxes).cpu()
+    gb = 0
+    for i, im in enumerate(ims):
+        for b in range(len(im["boxes"])):
+            z = c[gb, :, 2]
+            assert (z >= z0[gb] * cfg.z_lo - 1e-6).all() and (z <= z0[gb] * cfg.z_hi + 1e-6).all()
+            pm = priors[int(im["classes"][b])]
+            d = c[gb, :, 3:6]
+            assert (d >= cfg.dim_lo).all() and (d <= pm[0] + cfg.dim_hi_sigmas * pm[1] + 1e-6).all()
+            # sample mean of the dims near the prior mean (truncation is mild)
+            assert torch.allclose(d.mean(0), pm[0], rtol=0.08)
+            R = c[gb, :, 6:].reshape(N, 3, 3)
+            eye = torch.eye(3).expand(N, 3, 3)
+            assert torch.allclose(R.transpose(1, 2) @ R, eye, atol=2e-6)       # orthonormal
+            assert torch.allclose(torch.linalg.det(R), -torch.ones(N), atol=1e-5)  # det = -1 (A2.4)
+            assert torch.allclose(R[:, :, 1], normals[i].expand(N, 3), atol=1e-7)  # column 1 = normal
+            gb += 1
+
+
+@pytest.mark.parametrize("N,H,W,stride", [(1000, 480, 640, 1), (333, 375, 1242, 2), (2500, 240, 320, 1)])
+def test_score_topk_bit_exact(cuda_lib, N, H, W, stride):
+    from wcr.proposals import propose, score_topk, ScoreConfig
+    ims, shard, boxes, priors, normals = _setup(2, H, W, n_boxes=3, first=40)
+    cubes = propose(shard, boxes, priors, normals, N, seed=3)
+    cfg = ScoreConfig(point_stride=stride, k=16)
+    res = score_topk(shard, boxes, cubes, cfg=cfg, want_all=True)
+    cubes_h = cubes.cpu().numpy()
+    gb = 0
+    for i, im in enumerate(ims):
+        for b in range(len(im["boxes"])):
+            ref = oc.score_box(im["depth"].numpy(), im["K"].numpy(), im["boxes"][b].numpy(),
+                               (H, W), cubes_h[gb], stride)
+            assert int(res["npts"][gb]) == ref["npts"]
+            assert np.array_equal(res["count"][gb].cpu().numpy(), ref["count"])      # bit-exact
+            np.testing.assert_allclose(res["proj"][gb].cpu().numpy(), ref["proj"], rtol=RTOL)
+            np.testing.assert_allclose(res["iou"][gb].cpu().numpy(), ref["iou"], rtol=RTOL)
+            np.testing.assert_allclose(res["scores"][gb].cpu().numpy(), ref["score"], rtol=RTOL)
+            want = oc.topk(res["scores"][gb].cpu().numpy(), 16)
+            assert np.array_equal(res["idx"][gb].cpu().numpy(), want)                 # bit-exact
+            assert np.array_equal(oc.topk(ref["score"], 16), want)
+            rec = res["records"][gb].cpu().numpy()
+            for r, j in enumerate(want):
+                assert np.array_equal(rec[r, 2:17], cubes_h[gb][j])
+                assert rec[r, 1] == res["scores"][gb, j].item()
+            assert ref["count"].max() > 0   # the test actually exercises the counter
+            gb += 1
+
+
+def test_score_fused_sampling_equals_two_step(cuda_lib):
+    """cubes == NULL (proposals generated and held in registers) must select the
+    same top-k as sampling to HBM first."""
+    from wcr.proposals import propose, score_topk, ScoreConfig
+    N = 1000
+    ims, shard, boxes, priors, normals = _setup(3, n_boxes=4, first=7)
+    cubes = propose(shard, boxes, priors, normals, N, seed=21)
+    a = score_topk(shard, boxes, cubes, cfg=ScoreConfig())
+    b = score_topk(shard, boxes, None, N, cfg=ScoreConfig(), priors=priors, normals=normals, seed=21)
+    assert torch.equal(a["records"], b["records"])
+
+
+def test_score_edge_cases(cuda_lib):
+    from wcr.images import ImageShard
+    from wcr.proposals import BoxTable, score_topk, ScoreConfig
+    from wcr import synth
+    im = synth.make_image(3, 120, 160, n_boxes=1, dummy_ground=False)
+    im["depth"][:60] = 0.0          # invalid depth rows
+    im["depth"][70, 5] = float("nan")
+    boxes_t = torch.tensor([[-20.0, -5.0, 50.0, 90.0],    # partly outside the image
+                            [30.2, 40.7, 31.1, 41.3],     # empty integer ROI
+                            [10.0, 0.0, 150.0, 59.0]])    # only invalid depth -> P_b = 0
+    shard = ImageShard([im["depth"].cuda()], None, [im["K"]])
+    boxes = BoxTable(shard, [boxes_t], [torch.zeros(3, dtype=torch.long)])
+    g = torch.Generator().manual_seed(0)
+    N = 40
+    cubes = torch.zeros(3, N, 15)
+    cubes[:, :, 0:2] = torch.randn(3, N, 2, generator=g) * 0.5
+    cubes[:, :, 2] = 1.0 + torch.rand(3, N, generator=g) * 3
+    cubes[:, :, 3:6] = 0.2 + torch.rand(3, N, 3, generator=g)
+    cubes[:, :, 6:] = torch.eye(3).reshape(9)
+    cubes[0, 0, 2] = 0.0            # centre at z = 0: corners straddle the camera plane
+    cubes[0, 1, 3:6] = 0.0          # zero-size cube -> 0/0 nowhere, but a point box
+    res = score_topk(shard, boxes, cubes.cuda(), cfg=ScoreConfig(k=32), want_all=True)
+    for b in range(3):
+        ref = oc.score_box(im["depth"].numpy(), im["K"].numpy(), boxes_t[b].numpy(), (120, 160),
+                           cubes[b].numpy())
+        assert int(res["npts"][b]) == ref["npts"]
+        assert np.array_equal(res["count"][b].cpu().numpy(), ref["count"])
+        np.testing.assert_allclose(res["scores"][b].cpu().numpy(), ref["score"], rtol=RTOL)
+        np.testing.assert_array_equal(np.isnan(res["proj"][b].cpu().numpy()), np.isnan(ref["proj"]))
+        assert np.array_equal(res["idx"][b].cpu().numpy(), oc.topk(ref["score"], 32))
+    assert int(res["npts"][1]) == 0 and int(res["npts"][2]) == 0
+    # k > N: the tail is padded with idx = -1
+    res2 = score_topk(shard, boxes, cubes[:, :5].contiguous().cuda(), cfg=ScoreConfig(k=8))
+    assert (res2["idx"][:, 5:] == -1).all() and (res2["idx"][:, :5] >= 0).all()
+    with pytest.raises(Exception):
+        score_topk(shard, boxes, cubes, cfg=ScoreConfig())   # CPU tensor: no fallback

@@ -66,3 +66,37 @@ int64_t wcr_launch_count(void) { return wcr::g_launches; }
 void wcr_reset_launch_count(void) { wcr::g_launches = 0; }
 
 }  // extern "C"
+
+// FP32 pipe probe: 16 independent FFMA chains per thread. bench.py times it with
+// CUDA events to get the FP32 peak of THIS device under THIS run's clocks (the
+// roofline denominator of the scoring kernel; MEASURED_PEAKS.json has no FP32 figure).
+namespace wcr {
+__global__ void __launch_bounds__(256) ffma_probe_kernel(float *out, int iters, float s)
+{
+    float a[16];
+#pragma unroll
+    for (int i = 0; i < 16; ++i) a[i] = threadIdx.x * 1e-3f + i;
+    const float m = 1.0f + s * 1e-7f, c = s * 1e-7f;
+    for (int it = 0; it < iters; ++it)
+#pragma unroll
+        for (int i = 0; i < 16; ++i) a[i] = fmaf(a[i], m, c);
+    float sum = 0.f;
+#pragma unroll
+    for (int i = 0; i < 16; ++i) sum += a[i];
+    out[blockIdx.x * blockDim.x + threadIdx.x] = sum;
+}
+}  // namespace wcr
+
+extern "C" int64_t wcr_probe_ffma(float *out, int64_t out_elems, int iters, void *stream)
+{
+    if (wcr::check_device() != WCR_OK) return WCR_EARCH;
+    const int grid = wcr::sm_count() * 8;
+    if (!out || out_elems < (int64_t)grid * 256 || iters < 1) {
+        wcr::set_error("wcr_probe_ffma: out must hold %d floats", grid * 256);
+        return WCR_EINVAL;
+    }
+    wcr::ffma_probe_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(out, iters, 1.f);
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) { wcr::set_error("ffma_probe_kernel: %s", cudaGetErrorString(e)); return WCR_ELAUNCH; }
+    return (int64_t)grid * 256 * (int64_t)iters * 16 * 2;  // FLOPs enqueued
+}

@@ -16,6 +16,7 @@ LIB_PATH = os.path.join(_HERE, "_lib", "libwcr_b200.so")
 
 c_void_p, c_int, c_float, c_i64, c_u64 = (ctypes.c_void_p, ctypes.c_int, ctypes.c_float,
                                           ctypes.c_int64, ctypes.c_uint64)
+c_u32 = ctypes.c_uint32
 
 # name -> (restype, argtypes); must list every symbol include/wcr.h declares.
 SIGNATURES = {
@@ -29,6 +30,16 @@ SIGNATURES = {
     "wcr_ransac_ground": (c_int, [c_void_p, c_void_p, c_int, c_int, c_void_p, c_int, c_float, c_u64,
                                   c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
                                   c_void_p]),
+    "wcr_probe_ffma": (c_i64, [c_void_p, c_i64, c_int, c_void_p]),
+    "wcr_philox_block": (c_int, [c_u64, c_u32, c_u32, c_u32, c_u32, c_void_p, c_void_p]),
+    "wcr_box_center_depth": (c_int, [c_void_p, c_void_p, c_int, c_void_p, c_void_p]),
+    "wcr_sample_cubes": (c_int, [c_void_p, c_void_p, c_int, c_void_p, c_void_p, c_void_p, c_void_p,
+                                 c_int, c_void_p, c_u64, c_void_p, c_void_p]),
+    "wcr_score_workspace_bytes": (c_i64, [c_int, c_int, c_int]),
+    "wcr_score_topk": (c_int, [c_void_p, c_void_p, c_int, c_void_p, c_int, c_void_p, c_void_p,
+                               c_void_p, c_void_p, c_u64, c_void_p, c_void_p, c_void_p, c_int,
+                               c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
+                               c_void_p, c_void_p]),
 }
 
 _lib = None
@@ -84,3 +95,19 @@ def launch_count() -> int:
 
 def reset_launch_count():
     load().wcr_reset_launch_count()
+
+
+class SampleParams(ctypes.Structure):
+    """include/wcr.h WcrSampleParams (host struct, passed by pointer)."""
+    _fields_ = [("sigma_xy", c_float), ("sigma_z", c_float), ("z_lo", c_float), ("z_hi", c_float),
+                ("dim_lo", c_float), ("dim_hi_sigmas", c_float), ("yaw_lo", c_float),
+                ("yaw_hi", c_float), ("max_tries", ctypes.c_int32), ("reserved0", ctypes.c_int32),
+                ("reserved1", ctypes.c_int32), ("reserved2", ctypes.c_int32)]
+
+
+class ScoreParams(ctypes.Structure):
+    """include/wcr.h WcrScoreParams."""
+    _fields_ = [("e_iou", ctypes.c_int32), ("e_pts", ctypes.c_int32), ("e_seg", ctypes.c_int32),
+                ("point_stride", ctypes.c_int32), ("seg_mode", ctypes.c_int32),
+                ("reserved0", ctypes.c_int32), ("reserved1", ctypes.c_int32),
+                ("reserved2", ctypes.c_int32)]

@@ -1,0 +1,65 @@
+"""Image sharding + the one collective of the path.
+
+The hot path is embarrassingly parallel by image: rank r owns a contiguous image
+shard and runs every kernel on it with no data-path communication. The only
+exchange is the final all-gather of the per-box top-k records (fixed stride,
+80 B * k per box), done with ``torch.distributed.all_gather_into_tensor`` (NCCL
+over NVLink 5 / NVSwitch on the GPU box; ``gloo`` in the CPU tests). The scoring
+kernel writes its records directly into the send buffer (``ScoreWorkspace``'s
+``records`` argument), so there is no staging copy.
+"""
+from __future__ import annotations
+
+import torch
+import torch.distributed as dist
+
+RECORD_FLOATS = 20
+
+
+def shard_range(n_images: int, rank: int, world: int):
+    """Contiguous image shard [lo, hi) of rank ``rank``; sizes differ by <= 1."""
+    base, rem = divmod(n_images, world)
+    lo = rank * base + min(rank, rem)
+    return lo, lo + base + (1 if rank < rem else 0)
+
+
+def is_dist() -> bool:
+    return dist.is_available() and dist.is_initialized() and dist.get_world_size() > 1
+
+
+def gather_counts(n_local: int, device) -> list[int]:
+    """Boxes per rank (one tiny all-gather so records can be un-padded)."""
+    if not is_dist():
+        return [n_local]
+    t = torch.tensor([n_local], dtype=torch.int64, device=device)
+    out = torch.empty((dist.get_world_size(),), dtype=torch.int64, device=device)
+    dist.all_gather_into_tensor(out, t)
+    return [int(x) for x in out.cpu()]
+
+
+class TopkGather:
+    """Pre-allocated send/receive buffers for the top-k all-gather.
+
+    ``send`` (max_boxes, k, 20) is handed to ``ScoreWorkspace(records=...)``;
+    ``gather()`` returns the records of every rank, un-padded, in rank order
+    (= global image order because shards are contiguous)."""
+
+    def __init__(self, n_local_boxes: int, k: int, device):
+        self.k = k
+        self.counts = gather_counts(n_local_boxes, device)
+        self.max_boxes = max(max(self.counts), 1)
+        world = len(self.counts)
+        self.send = torch.zeros((self.max_boxes, k, RECORD_FLOATS), dtype=torch.float32, device=device)
+        self.recv = torch.empty((world, self.max_boxes, k, RECORD_FLOATS), dtype=torch.float32,
+                                device=device)
+
+    def gather_padded(self) -> torch.Tensor:
+        if len(self.counts) == 1:
+            self.recv[0].copy_(self.send)
+        else:
+            dist.all_gather_into_tensor(self.recv.view(-1), self.send.view(-1))
+        return self.recv
+
+    def gather(self) -> torch.Tensor:
+        r = self.gather_padded()
+        return torch.cat([r[i, :c] for i, c in enumerate(self.counts)], dim=0)

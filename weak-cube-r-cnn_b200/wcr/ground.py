@@ -75,6 +75,9 @@ def draw_reference_samples(counts_host, iters: int = 1000, rng=_random):
     hence one D2H sync -- used for parity runs, not for throughput runs)."""
     out = torch.empty((len(counts_host), iters, 3), dtype=torch.int32)
     for i, n in enumerate(counts_host):
+        if int(n) < 3:  # the reference's random.sample raises here; the kernel yields NaN
+            out[i] = 0
+            continue
         out[i] = torch.tensor([rng.sample(range(0, int(n)), 3) for _ in range(iters)],
                               dtype=torch.int32)
     return out

@@ -1,0 +1,199 @@
+"""Cube proposal generation and fused scoring (north_star steps 2 and 3).
+
+NEW entry points: the reference snapshot ships only the building blocks of its
+proposal pipeline; ``propose`` / ``score_topk`` are this project's
+composition of them (A2.7 / A3.12) -- ``oracle/compose.py`` is the same composition
+written with the reference's own functions.
+
+Host code here is plumbing: it builds the device box table and hands pointers to
+libwcr_b200.so (include/wcr.h). No CPU fallback.
+"""
+from __future__ import annotations
+
+import ctypes
+import math
+from dataclasses import dataclass
+
+import numpy as np
+import torch
+
+from . import _abi
+from .images import ImageShard
+
+BOX_DTYPE = np.dtype([("x1", np.float32), ("y1", np.float32), ("x2", np.float32), ("y2", np.float32),
+                      ("image", np.int32), ("cls", np.int32),
+                      ("clamp0", np.float32), ("clamp1", np.float32)])
+assert BOX_DTYPE.itemsize == 32
+
+CUBE_FLOATS, RECORD_FLOATS, MAX_TOPK = 15, 20, 32
+
+
+@dataclass
+class ProposalConfig:
+    """Free parameters of the composite (defaults are this project's spec)."""
+    sigma_xy: float = 0.25       # std of the 2D centre / box width (height)
+    sigma_z: float = 0.15        # std of z / pseudo depth z0
+    z_lo: float = 0.5            # z in [z0*z_lo, z0*z_hi]
+    z_hi: float = 1.5
+    dim_lo: float = 0.05         # dims in [dim_lo, mean + dim_hi_sigmas*std]
+    dim_hi_sigmas: float = 3.0
+    yaw_lo: float = 0.0          # yaw ~ U[0, pi)
+    yaw_hi: float = math.pi
+    max_tries: int = 32
+
+    def c_struct(self) -> _abi.SampleParams:
+        return _abi.SampleParams(self.sigma_xy, self.sigma_z, self.z_lo, self.z_hi, self.dim_lo,
+                                 self.dim_hi_sigmas, self.yaw_lo, self.yaw_hi, self.max_tries, 0, 0, 0)
+
+
+@dataclass
+class ScoreConfig:
+    e_iou: int = 1
+    e_pts: int = 1
+    e_seg: int = 0
+    point_stride: int = 1
+    seg_mode: int = 0
+    k: int = 16
+
+    def c_struct(self) -> _abi.ScoreParams:
+        return _abi.ScoreParams(self.e_iou, self.e_pts, self.e_seg, self.point_stride,
+                                self.seg_mode, 0, 0, 0)
+
+
+class BoxTable:
+    """Device table of ``WcrBox`` records for the GT boxes of a shard.
+
+    ``boxes_per_image``: list of (b_i, 4) tensors; ``classes_per_image``: list of
+    (b_i,) integer tensors. ``clamp`` is the tuple handed to
+    ``Cubes.get_bube_corners`` per image: default ``[H, W]`` as the ROI head does
+    (roi_heads.py:801-806, 950 -- the reference's own call-site convention)."""
+
+    def __init__(self, shard: ImageShard, boxes_per_image, classes_per_image, clamp=None):
+        recs = []
+        sizes = shard.sizes()
+        for i, (bx, cl) in enumerate(zip(boxes_per_image, classes_per_image)):
+            bx = torch.as_tensor(bx, dtype=torch.float32).cpu().numpy().reshape(-1, 4)
+            cl = torch.as_tensor(cl).cpu().numpy().reshape(-1)
+            c0, c1 = clamp[i] if clamp is not None else sizes[i]
+            r = np.zeros(len(bx), dtype=BOX_DTYPE)
+            r["x1"], r["y1"], r["x2"], r["y2"] = bx[:, 0], bx[:, 1], bx[:, 2], bx[:, 3]
+            r["image"], r["cls"] = i, cl
+            r["clamp0"], r["clamp1"] = c0, c1
+            recs.append(r)
+        self.host = np.concatenate(recs) if recs else np.zeros(0, dtype=BOX_DTYPE)
+        self.n_boxes = len(self.host)
+        self.device = shard.device
+        self.table = torch.from_numpy(self.host.view(np.uint8).copy()).to(shard.device)
+        self.num_boxes_per_image = [len(r) for r in recs]
+
+    def __len__(self):
+        return self.n_boxes
+
+
+def box_center_depth(shard: ImageShard, boxes: BoxTable) -> torch.Tensor:
+    """Pseudo depth z0 per box (roi_heads.py:645-652 on the GT box centre)."""
+    lib = _abi.load()
+    z0 = torch.empty((len(boxes),), dtype=torch.float32, device=shard.device)
+    _abi.check(lib.wcr_box_center_depth(shard.table.data_ptr(), boxes.table.data_ptr(), len(boxes),
+                                        z0.data_ptr(), _abi.stream_ptr(shard.device)),
+               "wcr_box_center_depth")
+    return z0
+
+
+def _f32(t, device):
+    return t.to(device=device, dtype=torch.float32).contiguous()
+
+
+def propose(shard: ImageShard, boxes: BoxTable, priors: torch.Tensor, normals: torch.Tensor,
+            N: int = 1000, cfg: ProposalConfig | None = None, *, z0=None, replay=None,
+            seed: int = 0) -> torch.Tensor:
+    """N cubes per box -> (n_boxes, N, 15) f32, the ``Cubes.tensor`` layout
+    (spaces.py:130-150). ``replay`` (n_boxes, 7, N): the (u v z w h l yaw) samples
+    drawn by the reference's ``sample_normal_in_range``; None => in-kernel Philox."""
+    lib = _abi.load()
+    cfg = cfg or ProposalConfig()
+    dev = shard.device
+    priors, normals = _f32(priors, dev), _f32(normals, dev)
+    _abi.require_cuda(priors, normals)
+    if z0 is None:
+        z0 = box_center_depth(shard, boxes)
+    if replay is not None:
+        replay = _f32(replay, dev)
+        assert tuple(replay.shape) == (len(boxes), 7, N)
+    out = torch.empty((len(boxes), N, CUBE_FLOATS), dtype=torch.float32, device=dev)
+    sp = cfg.c_struct()
+    _abi.check(lib.wcr_sample_cubes(shard.table.data_ptr(), boxes.table.data_ptr(), len(boxes),
+                                    priors.data_ptr(), normals.data_ptr(), z0.data_ptr(),
+                                    ctypes.byref(sp), N, _abi.ptr(replay), int(seed),
+                                    out.data_ptr(), _abi.stream_ptr(dev)),
+               "wcr_sample_cubes")
+    return out
+
+
+class ScoreWorkspace:
+    """Caller-owned buffers of ``score_topk`` so a steady-state loop allocates
+    nothing (and so the top-k records can be written straight into a registered
+    NCCL send buffer, see wcr.dist)."""
+
+    def __init__(self, n_boxes: int, N: int, k: int, device, records: torch.Tensor | None = None):
+        lib = _abi.load()
+        nbytes = int(lib.wcr_score_workspace_bytes(n_boxes, N, k))
+        self.ws = torch.empty((max(nbytes, 16),), dtype=torch.uint8, device=device)
+        self.records = records if records is not None else torch.empty(
+            (n_boxes, k, RECORD_FLOATS), dtype=torch.float32, device=device)
+        self.n_boxes, self.N, self.k = n_boxes, N, k
+
+
+def score_topk(shard: ImageShard, boxes: BoxTable, cubes: torch.Tensor | None, N: int | None = None,
+               cfg: ScoreConfig | None = None, *, priors=None, normals=None, z0=None,
+               sample_cfg: ProposalConfig | None = None, seed: int = 0, seg=None,
+               workspace: ScoreWorkspace | None = None, want_all: bool = False):
+    """Fused scoring + per-box top-k. ``cubes`` (n_boxes, N, 15) or None to sample
+    in-kernel (then priors/normals are required; same generator as ``propose``).
+
+    -> dict(records (n_boxes,k,20) f32 [idx bits, score, cube15, s_iou, s_pts, s_seg],
+            idx (n_boxes,k) i32 view, score (n_boxes,k);
+            with want_all: scores, iou (n_boxes,N) f32, count (n_boxes,N) i32,
+            proj (n_boxes,N,4), npts (n_boxes,) i32)."""
+    lib = _abi.load()
+    cfg = cfg or ScoreConfig()
+    dev = shard.device
+    nb = len(boxes)
+    if cubes is not None:
+        _abi.require_cuda(cubes)
+        cubes = _f32(cubes, dev)
+        assert cubes.dim() == 3 and cubes.shape[0] == nb and cubes.shape[2] == CUBE_FLOATS
+        N = cubes.shape[1]
+    else:
+        assert N is not None and priors is not None and normals is not None
+        priors, normals = _f32(priors, dev), _f32(normals, dev)
+        if z0 is None:
+            z0 = box_center_depth(shard, boxes)
+    sp = (sample_cfg or ProposalConfig()).c_struct()
+    sc = cfg.c_struct()
+    if workspace is None:
+        workspace = ScoreWorkspace(nb, N, cfg.k, dev)
+    assert workspace.n_boxes >= nb and workspace.N == N and workspace.k == cfg.k
+    rec = workspace.records
+    outs = {}
+    if want_all:
+        outs["scores"] = torch.empty((nb, N), dtype=torch.float32, device=dev)
+        outs["iou"] = torch.empty((nb, N), dtype=torch.float32, device=dev)
+        outs["count"] = torch.empty((nb, N), dtype=torch.int32, device=dev)
+        outs["proj"] = torch.empty((nb, N, 4), dtype=torch.float32, device=dev)
+        outs["npts"] = torch.empty((nb,), dtype=torch.int32, device=dev)
+    seg_bits = seg_off = None
+    if seg is not None:
+        seg_bits, seg_off = seg
+    _abi.check(lib.wcr_score_topk(
+        shard.table.data_ptr(), boxes.table.data_ptr(), nb, _abi.ptr(cubes), N,
+        _abi.ptr(priors), _abi.ptr(normals), _abi.ptr(z0), ctypes.byref(sp), int(seed),
+        _abi.ptr(seg_bits), _abi.ptr(seg_off), ctypes.byref(sc), cfg.k, rec.data_ptr(),
+        _abi.ptr(outs.get("scores")), _abi.ptr(outs.get("iou")), _abi.ptr(outs.get("count")),
+        _abi.ptr(outs.get("proj")), _abi.ptr(outs.get("npts")), workspace.ws.data_ptr(),
+        _abi.stream_ptr(dev)), "wcr_score_topk")
+    rec = rec[:nb]
+    outs["records"] = rec
+    outs["idx"] = rec[:, :, 0].contiguous().view(torch.int32)
+    outs["score"] = rec[:, :, 1]
+    return outs
