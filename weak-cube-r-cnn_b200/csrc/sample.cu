@@ -42,6 +42,20 @@ sample_cubes_kernel(const WcrImage *__restrict__ images, const WcrBox *__restric
 
 }  // namespace wcr
 
+namespace wcr {
+// host-side launcher shared with score.cu (library-side sampling of wcr_score_topk)
+cudaError_t launch_sample_cubes(const WcrImage *images, const WcrBox *boxes, int n_boxes,
+                                const float *priors, const float *normals, const float *z0,
+                                const WcrSampleParams &sp, int N, const float *replay,
+                                uint64_t seed, float *out_cubes, cudaStream_t st)
+{
+    dim3 grid(n_boxes, (N + 255) / 256);
+    sample_cubes_kernel<<<grid, 256, 0, st>>>(images, boxes, priors, normals, z0, sp, N, replay,
+                                              seed, out_cubes);
+    return cudaGetLastError();
+}
+}  // namespace wcr
+
 extern "C" int wcr_box_center_depth(const WcrImage *images, const WcrBox *boxes, int n_boxes,
                                     float *out_z0, void *stream)
 {
@@ -66,9 +80,8 @@ extern "C" int wcr_sample_cubes(const WcrImage *images, const WcrBox *boxes, int
     WCR_REQUIRE(n_boxes >= 0 && N >= 1, "wcr_sample_cubes: bad sizes");
     WCR_REQUIRE((N + 255) / 256 <= 65535, "wcr_sample_cubes: N too large");
     if (n_boxes == 0) return WCR_OK;
-    dim3 grid(n_boxes, (N + 255) / 256);
-    wcr::sample_cubes_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(
-        images, boxes, priors, normals, z0, *h_params, N, replay, seed, out_cubes);
+    wcr::launch_sample_cubes(images, boxes, n_boxes, priors, normals, z0, *h_params, N, replay,
+                             seed, out_cubes, (cudaStream_t)stream);
     WCR_CHECK_LAUNCH("sample_cubes_kernel");
     return WCR_OK;
 }

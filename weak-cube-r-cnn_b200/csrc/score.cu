@@ -1,16 +1,25 @@
 // score.cu -- fused proposal scoring + per-box top-k (north_star step 3, SURVEY
 // A3.2-A3.6, A3.11, A3.12).
 //
-// One CTA owns one (box, chunk of 256*T proposals). Proposal state lives in
-// registers; the depth pixels of the GT-box ROI stream once through shared memory
-// as (a_u, z) pairs, a_u = (u - cx)/fx. Because every tested point is an
-// unprojected pixel p = z * (a_u, b_v, 1), the local-frame coordinate factors per
+// Work decomposition. A box's ROI can hold 1.6 k ... 110 k depth pixels, so one
+// CTA per box leaves a long tail. The ROI is cut into row blocks of ~SC_ITEM_PX
+// pixels; an ITEM is (box, chunk of 256*T proposals, row block). A persistent grid
+// (2 CTAs per SM) pulls items from an atomic queue. Per item: proposal state in
+// registers, the item's depth pixels stream through shared memory as (a_u, z)
+// pairs, per-proposal inside-counts are added to a global counter array. The CTA
+// that retires the last item of a (box, chunk) runs the epilogue for that chunk
+// (corners -> projection -> clamp -> min/max -> IoU -> score -> top-k); the CTA that
+// retires the last chunk of a box merges the chunk candidates. One launch, no
+// host round trip, records written straight into the caller's (NCCL send) buffer.
+//
+// Point test. Every tested point is an unprojected pixel p = z * (a_u, b_v, 1),
+// a_u = (u - cx)/fx, b_v = (v - cy)/fy, so the local-frame coordinate factors per
 // image row:
-//     q_k = R[:,k] . (p - c) = z * (R0k*a_u + (R1k*b_v + R2k)) - R[:,k].c
-//         = fma(z, fma(A_k, a_u, G_k), -O_k),   G_k = fma(B_k, b_v, C_k) per row
-// i.e. 6 FFMA + 3 compares per (proposal, point) instead of 3 FADD + 9 FFMA. The
-// rounding order above IS the definition oracle/csrc/wcr_oracle.c restates; counts
-// are bit-exact against it (DESIGN.md "Point-in-cube test").
+//     q_k = R[:,k] . (p - c) = fma(z, fma(A_k, a_u, G_k), -O_k),
+//     G_k = fma(B_k, b_v, C_k) per row,  O_k = R[:,k] . c per proposal
+// 6 FFMA + 3 compares per (proposal, point) instead of 3 FADD + 9 FFMA. This
+// rounding order IS the definition oracle/csrc/wcr_oracle.c restates; counts are
+// bit-exact against it (DESIGN.md "Point-in-cube test").
 //
 // FP32 CUDA-core kernel by construction: nothing here is a dense contraction.
 #include <string.h>
@@ -19,7 +28,11 @@
 namespace wcr {
 
 constexpr int SC_THREADS = 256;
-constexpr int SC_TILE = 2048;  // (a_u, z) pairs per shared-memory tile = 16 KB
+constexpr int SC_T = 4;                        // proposals per thread
+constexpr int SC_CHUNK = SC_THREADS * SC_T;    // proposals per item
+constexpr int SC_TILE = 2048;                  // (a_u, z) pairs per smem tile = 16 KB
+constexpr int SC_ITEM_PX = 4096;               // target depth pixels per item
+constexpr int SC_MAX_CHUNKS = 64;
 
 __device__ __forceinline__ void count_inside(int &cnt, float q0, float q1, float q2, float h0,
                                              float h1, float h2)
@@ -34,198 +47,110 @@ __device__ __forceinline__ void count_inside(int &cnt, float q0, float q1, float
         : "f"(q0), "f"(q1), "f"(q2), "f"(h0), "f"(h1), "f"(h2));
 }
 
+// Integer ROI of a GT box: Boxes.clip((h, w)) then .long() slicing, as the
+// reference slices depth patches (roi_heads.py:590-597), sub-sampled by `s`.
+struct Roi { int u0, v0, ncols, nrows, rows_per_item, n_rowblocks; };
+
+__device__ __forceinline__ Roi box_roi(const WcrBox &bx, int H, int W, int s, bool use_pts)
+{
+    Roi r;
+    r.u0 = (int)fminf(fmaxf(bx.x1, 0.f), (float)W);
+    const int u1 = (int)fminf(fmaxf(bx.x2, 0.f), (float)W);
+    r.v0 = (int)fminf(fmaxf(bx.y1, 0.f), (float)H);
+    const int v1 = (int)fminf(fmaxf(bx.y2, 0.f), (float)H);
+    r.ncols = max(0, (u1 - r.u0 + s - 1) / s);
+    r.nrows = max(0, (v1 - r.v0 + s - 1) / s);
+    if (!use_pts || r.ncols == 0) r.nrows = 0;
+    r.rows_per_item = max(1, SC_ITEM_PX / max(r.ncols, 1));
+    r.n_rowblocks = max(1, (r.nrows + r.rows_per_item - 1) / r.rows_per_item);
+    return r;
+}
+
+// Device workspace layout (caller-owned, zeroed by cudaMemsetAsync up to `zero_bytes`).
+struct ScoreWs {
+    int *queue;          // [1]   next item
+    int *item_prefix;    // [n_boxes + 1] exclusive prefix of items per box
+    int *done_chunk;     // [n_boxes][n_chunks] retired items per (box, chunk)
+    int *done_box;       // [n_boxes] retired chunks per box
+    int *npts;           // [n_boxes][n_chunks] valid depth points (P_b), one copy per chunk
+    int *count;          // [n_boxes][N] inside-counts
+    float *cand;         // [n_boxes][n_chunks][k][20] chunk candidates (n_chunks > 1)
+    float *cubes;        // [n_boxes][N][15] when sampled by the library
+};
+
 struct ScoreArgs {
     const WcrImage *images;
     const WcrBox *boxes;
+    int n_boxes;
     const float *cubes;
     int N;
-    const float *priors, *normals, *z0;
-    WcrSampleParams sp;
-    uint64_t seed;
-    const uint32_t *seg_bits;
-    const int64_t *seg_off;
     WcrScoreParams sc;
     int k;
     int n_chunks;
-    float *records;  // out_records if n_chunks == 1 else workspace
+    ScoreWs ws;
+    float *records;
     float *out_scores, *out_iou;
     int32_t *out_count;
     float *out_proj;
     int32_t *out_npts;
 };
 
-// Integer ROI of a GT box: Boxes.clip((h, w)) then .long() slicing, as the
-// reference slices depth patches (roi_heads.py:590-597).
-__device__ __forceinline__ void box_roi(const WcrBox &bx, int H, int W, int &u0, int &v0, int &u1,
-                                        int &v1)
+// One CTA: items per box -> exclusive prefix. n_boxes is at most a few 100 k.
+__global__ void __launch_bounds__(1024)
+score_plan_kernel(const WcrImage *__restrict__ images, const WcrBox *__restrict__ boxes,
+                  int n_boxes, int n_chunks, int stride, int use_pts, int *__restrict__ prefix)
 {
-    u0 = (int)fminf(fmaxf(bx.x1, 0.f), (float)W);
-    u1 = (int)fminf(fmaxf(bx.x2, 0.f), (float)W);
-    v0 = (int)fminf(fmaxf(bx.y1, 0.f), (float)H);
-    v1 = (int)fminf(fmaxf(bx.y2, 0.f), (float)H);
+    __shared__ int s_warp[32];
+    __shared__ int s_carry;
+    const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+    if (tid == 0) s_carry = 0;
+    __syncthreads();
+    for (int base = 0; base < n_boxes; base += 1024) {
+        const int b = base + tid;
+        int n = 0;
+        if (b < n_boxes) {
+            const WcrBox bx = boxes[b];
+            const WcrImage im = images[bx.image];
+            n = box_roi(bx, im.H, im.W, stride, use_pts != 0).n_rowblocks * n_chunks;
+        }
+        int incl = n;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const int t = __shfl_up_sync(0xffffffffu, incl, o);
+            if (lane >= o) incl += t;
+        }
+        if (lane == 31) s_warp[wid] = incl;
+        __syncthreads();
+        if (wid == 0) {
+            const int t = s_warp[lane];
+            int w = t;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const int x = __shfl_up_sync(0xffffffffu, w, o);
+                if (lane >= o) w += x;
+            }
+            s_warp[lane] = w - t;  // exclusive over warps
+        }
+        __syncthreads();
+        const int carry = s_carry;
+        if (b < n_boxes) prefix[b] = carry + s_warp[wid] + incl - n;
+        __syncthreads();
+        if (tid == 1023) s_carry = carry + s_warp[wid] + incl;
+        __syncthreads();
+    }
+    if (tid == 0) prefix[n_boxes] = s_carry;
 }
 
-template <int T>
-__global__ void __launch_bounds__(SC_THREADS, 2) score_topk_kernel(const ScoreArgs a)
+// k rounds of (max score, lowest index) over the CTA's SC_CHUNK candidates in smem.
+// Winner r's local index (or -1) lands in s_win[r], its score in s_wsc[r].
+__device__ __forceinline__ void cta_topk(float *s_score, int k, float *s_red_v, int *s_red_i,
+                                         int *s_win, float *s_wsc)
 {
-    constexpr int CHUNK = SC_THREADS * T;
-    __shared__ __align__(16) float2 tile[SC_TILE];
-    __shared__ float s_score[CHUNK];
-    __shared__ float s_iou[CHUNK];
-    __shared__ float s_pts[CHUNK];
-    __shared__ float s_red_v[SC_THREADS / 32];
-    __shared__ int s_red_i[SC_THREADS / 32];
-    __shared__ int s_win[WCR_MAX_TOPK];
-    __shared__ int s_npts;
-
-    const int b = blockIdx.x, chunk = blockIdx.y;
     const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
-    const WcrBox bx = a.boxes[b];
-    const WcrImage im = a.images[bx.image];
-    const Intr K = {im.fx, im.fy, im.cx, im.cy};
-    const bool fused_sampling = (a.cubes == nullptr);
-    BoxCtx ctx;
-    if (fused_sampling) ctx = make_box_ctx(im, bx, a.priors, a.normals, a.z0[b], a.sp);
-    if (tid == 0) s_npts = 0;
-
-    // ---- prologue: proposal state -> registers ---------------------------------
-    float A[T][3], B[T][3], C[T][3], NO[T][3], Hh[T][3];
-    int cnt[T];
-#pragma unroll
-    for (int t = 0; t < T; ++t) {
-        const int j = chunk * CHUNK + t * SC_THREADS + tid;
-        cnt[t] = 0;
-        if (j < a.N) {
-            float cube[15];
-            if (fused_sampling) {
-                sample_cube(ctx, nullptr, a.N, a.seed, (uint32_t)b, (uint32_t)j, cube);
-            } else {
-                const float *src = a.cubes + ((size_t)b * a.N + j) * 15;
-#pragma unroll
-                for (int i = 0; i < 15; ++i) cube[i] = __ldg(src + i);
-            }
-#pragma unroll
-            for (int k = 0; k < 3; ++k) {
-                A[t][k] = cube[6 + k]; B[t][k] = cube[9 + k]; C[t][k] = cube[12 + k];
-                NO[t][k] = -fmaf(C[t][k], cube[2], fmaf(B[t][k], cube[1], A[t][k] * cube[0]));
-            }
-            Hh[t][0] = cube[5] / 2.f; Hh[t][1] = cube[4] / 2.f; Hh[t][2] = cube[3] / 2.f;
-        } else {
-#pragma unroll
-            for (int k = 0; k < 3; ++k) { A[t][k] = B[t][k] = C[t][k] = NO[t][k] = 0.f; Hh[t][k] = -1.f; }
-        }
-    }
-
-    // ---- main loop: depth ROI tiles ---------------------------------------------
-    int u0, v0, u1, v1;
-    box_roi(bx, im.H, im.W, u0, v0, u1, v1);
-    const int s = a.sc.point_stride;
-    const int ncols = (u1 - u0 + s - 1) / s, nrows = (v1 - v0 + s - 1) / s;
-    const bool use_pts = (a.sc.e_pts > 0) && ncols > 0 && nrows > 0;
-    int my_valid = 0;
-    if (use_pts) {
-        const int pieces = (ncols + SC_TILE - 1) / SC_TILE;
-        const int segpad = (min(ncols, SC_TILE) + 1) & ~1;
-        const int spt = SC_TILE / segpad;  // segments per tile, >= 1
-        const int total_segs = nrows * pieces;
-        for (int seg0 = 0; seg0 < total_segs; seg0 += spt) {
-            const int nseg = min(spt, total_segs - seg0);
-            __syncthreads();
-            for (int idx = tid; idx < nseg * segpad; idx += SC_THREADS) {
-                const int ss = idx / segpad, pos = idx - ss * segpad;
-                const int seg = seg0 + ss;
-                const int row = seg / pieces, piece = seg - row * pieces;
-                const int col = piece * SC_TILE + pos;
-                float av = 0.f, z = nanf_();
-                if (col < ncols && pos < SC_TILE) {
-                    const int u = u0 + col * s, v = v0 + row * s;
-                    const float d = __ldg(im.depth + (size_t)v * im.depth_pitch + u);
-                    av = ((float)u - K.cx) / K.fx;
-                    if (d > 0.f && d <= 3.402823466e38f) { z = d; ++my_valid; }
-                }
-                tile[idx] = make_float2(av, z);
-            }
-            __syncthreads();
-            for (int ss = 0; ss < nseg; ++ss) {
-                const int seg = seg0 + ss;
-                const int row = seg / pieces;
-                const float bv = ((float)(v0 + row * s) - K.cy) / K.fy;
-                float G[T][3];
-#pragma unroll
-                for (int t = 0; t < T; ++t)
-#pragma unroll
-                    for (int k = 0; k < 3; ++k) G[t][k] = fmaf(B[t][k], bv, C[t][k]);
-                const float4 *src = reinterpret_cast<const float4 *>(tile + ss * segpad);
-#pragma unroll 2
-                for (int p = 0; p < segpad / 2; ++p) {
-                    const float4 pp = src[p];
-#pragma unroll
-                    for (int t = 0; t < T; ++t) {
-                        const float q0 = fmaf(pp.y, fmaf(A[t][0], pp.x, G[t][0]), NO[t][0]);
-                        const float q1 = fmaf(pp.y, fmaf(A[t][1], pp.x, G[t][1]), NO[t][1]);
-                        const float q2 = fmaf(pp.y, fmaf(A[t][2], pp.x, G[t][2]), NO[t][2]);
-                        count_inside(cnt[t], q0, q1, q2, Hh[t][0], Hh[t][1], Hh[t][2]);
-                    }
-#pragma unroll
-                    for (int t = 0; t < T; ++t) {
-                        const float q0 = fmaf(pp.w, fmaf(A[t][0], pp.z, G[t][0]), NO[t][0]);
-                        const float q1 = fmaf(pp.w, fmaf(A[t][1], pp.z, G[t][1]), NO[t][1]);
-                        const float q2 = fmaf(pp.w, fmaf(A[t][2], pp.z, G[t][2]), NO[t][2]);
-                        count_inside(cnt[t], q0, q1, q2, Hh[t][0], Hh[t][1], Hh[t][2]);
-                    }
-                }
-            }
-        }
-    }
-    // valid-point total P_b
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) my_valid += __shfl_xor_sync(0xffffffffu, my_valid, o);
-    __syncthreads();
-    if (lane == 0 && my_valid) atomicAdd(&s_npts, my_valid);
-    __syncthreads();
-    const int npts = s_npts;
-    if (a.out_npts && chunk == 0 && tid == 0) a.out_npts[b] = npts;
-
-    // ---- epilogue: corners -> projection -> box -> IoU -> score -----------------
-    float lo0, hi0, lo1, hi1;
-    clamp_bounds(bx.clamp0, lo0, hi0);
-    clamp_bounds(bx.clamp1, lo1, hi1);
-#pragma unroll
-    for (int t = 0; t < T; ++t) {
-        const int loc = t * SC_THREADS + tid;
-        const int j = chunk * CHUNK + loc;
-        float score = -INFINITY, siou = 0.f, spts = 0.f;
-        if (j < a.N) {
-            float cube[15];
-            if (fused_sampling) {
-                sample_cube(ctx, nullptr, a.N, a.seed, (uint32_t)b, (uint32_t)j, cube);
-            } else {
-                const float *src = a.cubes + ((size_t)b * a.N + j) * 15;
-#pragma unroll
-                for (int i = 0; i < 15; ++i) cube[i] = __ldg(src + i);
-            }
-            const ProjBox pb = project_cube(cube, K, lo0, hi0, lo1, hi1, nullptr);
-            siou = iou_2d(bx.x1, bx.y1, bx.x2, bx.y2, pb);
-            spts = npts > 0 ? (float)cnt[t] / (float)npts : 0.f;
-            score = (ipow(siou, a.sc.e_iou) * ipow(spts, a.sc.e_pts)) * 1.f;  // s_seg: seg.cuh
-            const size_t o = (size_t)b * a.N + j;
-            if (a.out_scores) a.out_scores[o] = score;
-            if (a.out_iou) a.out_iou[o] = siou;
-            if (a.out_count) a.out_count[o] = cnt[t];
-            if (a.out_proj) {
-                float *d = a.out_proj + o * 4;
-                d[0] = pb.x1; d[1] = pb.y1; d[2] = pb.x2; d[3] = pb.y2;
-            }
-        }
-        s_score[loc] = score; s_iou[loc] = siou; s_pts[loc] = spts;
-    }
-    __syncthreads();
-
-    // ---- top-k of this chunk: k rounds of (max score, lowest index) -------------
-    for (int r = 0; r < a.k; ++r) {
+    for (int r = 0; r < k; ++r) {
         float bv = -INFINITY; int bi = 0x7fffffff;
 #pragma unroll
-        for (int t = 0; t < T; ++t) {
+        for (int t = 0; t < SC_T; ++t) {
             const int loc = t * SC_THREADS + tid;
             const float v = s_score[loc];
             if (v > bv) { bv = v; bi = loc; }  // ascending loc: keeps the lowest index
@@ -242,53 +167,26 @@ __global__ void __launch_bounds__(SC_THREADS, 2) score_topk_kernel(const ScoreAr
             for (int w = 1; w < SC_THREADS / 32; ++w)
                 if (s_red_v[w] > bv || (s_red_v[w] == bv && s_red_i[w] < bi)) { bv = s_red_v[w]; bi = s_red_i[w]; }
             if (bv == -INFINITY) bi = -1;
-            s_win[r] = bi;
-            if (bi >= 0) s_score[bi] = -INFINITY;  // taken; its value is kept in s_red_v[0]
-            s_red_v[0] = bv;
-        }
-        __syncthreads();
-        // winner's record
-        if (tid == 0) {
-            const int loc = s_win[r];
-            float *rec = a.records + (((size_t)b * a.n_chunks + chunk) * a.k + r) * WCR_RECORD_FLOATS;
-            if (loc < 0) {
-                rec[0] = __int_as_float(-1);
-                for (int i = 1; i < WCR_RECORD_FLOATS; ++i) rec[i] = 0.f;
-            } else {
-                const int j = chunk * CHUNK + loc;
-                float cube[15];
-                if (fused_sampling) sample_cube(ctx, nullptr, a.N, a.seed, (uint32_t)b, (uint32_t)j, cube);
-                else {
-                    const float *src = a.cubes + ((size_t)b * a.N + j) * 15;
-                    for (int i = 0; i < 15; ++i) cube[i] = src[i];
-                }
-                rec[0] = __int_as_float(j);
-                rec[1] = s_red_v[0];
-                for (int i = 0; i < 15; ++i) rec[2 + i] = cube[i];
-                rec[17] = s_iou[loc]; rec[18] = s_pts[loc]; rec[19] = 1.f;
-            }
+            s_win[r] = bi; s_wsc[r] = bv;
+            if (bi >= 0) s_score[bi] = -INFINITY;  // taken
         }
         __syncthreads();
     }
 }
 
-// Merge the per-chunk candidates of one box: one warp per box, k rounds.
-__global__ void __launch_bounds__(32)
-topk_merge_kernel(const float *__restrict__ cand, int n_chunks, int k, float *__restrict__ out)
+// Merge n_chunks*k candidate records of one box (warp 0 of the retiring CTA).
+__device__ __forceinline__ void warp_merge(const float *cand, int n, int k, float *out)
 {
-    const int b = blockIdx.x, lane = threadIdx.x;
-    const int n = n_chunks * k;
-    const float *C = cand + (size_t)b * n * WCR_RECORD_FLOATS;
-    // candidates are few (<= 64 chunks * 32): mark taken ones in a per-lane bitmask
-    unsigned long long taken = 0ull;  // candidate lane + 32*i  <->  bit i
+    const int lane = threadIdx.x & 31;
+    unsigned long long taken = 0ull;  // candidate lane + 32*i  <->  bit i (n <= 2048)
     for (int r = 0; r < k; ++r) {
         float bv = -INFINITY; int bj = 0x7fffffff, bc = -1;
         for (int i = 0; lane + 32 * i < n; ++i) {
             if (taken >> i & 1ull) continue;
             const int c = lane + 32 * i;
-            const int j = __float_as_int(C[(size_t)c * WCR_RECORD_FLOATS]);
+            const int j = __float_as_int(__ldcg(cand + (size_t)c * WCR_RECORD_FLOATS));
             if (j < 0) continue;
-            const float v = C[(size_t)c * WCR_RECORD_FLOATS + 1];
+            const float v = __ldcg(cand + (size_t)c * WCR_RECORD_FLOATS + 1);
             if (v > bv || (v == bv && j < bj)) { bv = v; bj = j; bc = c; }
         }
 #pragma unroll
@@ -298,30 +196,266 @@ topk_merge_kernel(const float *__restrict__ cand, int n_chunks, int k, float *__
             const int oc = __shfl_xor_sync(0xffffffffu, bc, o);
             if (ov > bv || (ov == bv && oj < bj)) { bv = ov; bj = oj; bc = oc; }
         }
-        float *dst = out + ((size_t)b * k + r) * WCR_RECORD_FLOATS;
+        float *dst = out + (size_t)r * WCR_RECORD_FLOATS;
         if (bc < 0) {
             if (lane < WCR_RECORD_FLOATS) dst[lane] = lane == 0 ? __int_as_float(-1) : 0.f;
         } else {
-            if (lane < WCR_RECORD_FLOATS) dst[lane] = C[(size_t)bc * WCR_RECORD_FLOATS + lane];
+            if (lane < WCR_RECORD_FLOATS) dst[lane] = __ldcg(cand + (size_t)bc * WCR_RECORD_FLOATS + lane);
             if ((bc & 31) == lane) taken |= 1ull << (bc >> 5);
+        }
+    }
+}
+
+__global__ void __launch_bounds__(SC_THREADS, 2) score_items_kernel(const ScoreArgs a)
+{
+    constexpr int T = SC_T;
+    __shared__ __align__(16) float2 tile[SC_TILE];
+    __shared__ float s_score[SC_CHUNK];
+    __shared__ float s_iou[SC_CHUNK];
+    __shared__ float s_pts[SC_CHUNK];
+    __shared__ float s_red_v[SC_THREADS / 32];
+    __shared__ int s_red_i[SC_THREADS / 32];
+    __shared__ int s_win[WCR_MAX_TOPK];
+    __shared__ float s_wsc[WCR_MAX_TOPK];
+    __shared__ int s_item, s_flag;
+
+    const int tid = threadIdx.x, lane = tid & 31;
+    const int *__restrict__ prefix = a.ws.item_prefix;
+    const int total = prefix[a.n_boxes];
+    const float *__restrict__ cubes = a.cubes ? a.cubes : a.ws.cubes;
+    const bool use_pts = a.sc.e_pts > 0;
+    const int s = a.sc.point_stride;
+
+    for (;;) {
+        __syncthreads();
+        if (tid == 0) s_item = atomicAdd(a.ws.queue, 1);
+        __syncthreads();
+        const int item = s_item;
+        if (item >= total) break;
+        int b = 0, hi = a.n_boxes;  // prefix[b] <= item < prefix[hi]
+        while (hi - b > 1) {
+            const int mid = (b + hi) >> 1;
+            if (prefix[mid] <= item) b = mid; else hi = mid;
+        }
+        const WcrBox bx = a.boxes[b];
+        const WcrImage im = a.images[bx.image];
+        const Intr K = {im.fx, im.fy, im.cx, im.cy};
+        const Roi roi = box_roi(bx, im.H, im.W, s, use_pts);
+        const int local = item - prefix[b];
+        const int chunk = local / roi.n_rowblocks, rb = local - chunk * roi.n_rowblocks;
+        const int row_begin = rb * roi.rows_per_item;
+        const int row_end = min(roi.nrows, row_begin + roi.rows_per_item);
+
+        // ---- prologue: proposal state -> registers ------------------------------
+        float A[T][3], B[T][3], C[T][3], NO[T][3], Hh[T][3];
+        int cnt[T];
+#pragma unroll
+        for (int t = 0; t < T; ++t) {
+            const int j = chunk * SC_CHUNK + t * SC_THREADS + tid;
+            cnt[t] = 0;
+            if (j < a.N && row_end > row_begin) {
+                const float *src = cubes + ((size_t)b * a.N + j) * 15;
+                float cube[15];
+#pragma unroll
+                for (int i = 0; i < 15; ++i) cube[i] = __ldg(src + i);
+#pragma unroll
+                for (int k = 0; k < 3; ++k) {
+                    A[t][k] = cube[6 + k]; B[t][k] = cube[9 + k]; C[t][k] = cube[12 + k];
+                    NO[t][k] = -fmaf(C[t][k], cube[2], fmaf(B[t][k], cube[1], A[t][k] * cube[0]));
+                }
+                Hh[t][0] = cube[5] / 2.f; Hh[t][1] = cube[4] / 2.f; Hh[t][2] = cube[3] / 2.f;
+            } else {
+#pragma unroll
+                for (int k = 0; k < 3; ++k) { A[t][k] = B[t][k] = C[t][k] = NO[t][k] = 0.f; Hh[t][k] = -1.f; }
+            }
+        }
+
+        // ---- main loop: this item's rows, tile by tile --------------------------
+        int my_valid = 0;
+        if (row_end > row_begin) {
+            const int ncols = roi.ncols;
+            const int pieces = (ncols + SC_TILE - 1) / SC_TILE;
+            const int segpad = (min(ncols, SC_TILE) + 1) & ~1;
+            const int spt = SC_TILE / segpad;  // row segments per tile, >= 1
+            const int total_segs = (row_end - row_begin) * pieces;
+            for (int seg0 = 0; seg0 < total_segs; seg0 += spt) {
+                const int nseg = min(spt, total_segs - seg0);
+                if (seg0) __syncthreads();
+                for (int idx = tid; idx < nseg * segpad; idx += SC_THREADS) {
+                    const int ss = idx / segpad, pos = idx - ss * segpad;
+                    const int seg = seg0 + ss;
+                    const int row = seg / pieces, piece = seg - row * pieces;
+                    const int col = piece * SC_TILE + pos;
+                    float av = 0.f, z = nanf_();
+                    if (col < ncols) {
+                        const int u = roi.u0 + col * s, v = roi.v0 + (row_begin + row) * s;
+                        const float d = __ldg(im.depth + (size_t)v * im.depth_pitch + u);
+                        av = ((float)u - K.cx) / K.fx;
+                        if (d > 0.f && d <= 3.402823466e38f) { z = d; ++my_valid; }
+                    }
+                    tile[idx] = make_float2(av, z);
+                }
+                __syncthreads();
+                for (int ss = 0; ss < nseg; ++ss) {
+                    const int row = (seg0 + ss) / pieces;
+                    const float bv = ((float)(roi.v0 + (row_begin + row) * s) - K.cy) / K.fy;
+                    float G[T][3];
+#pragma unroll
+                    for (int t = 0; t < T; ++t)
+#pragma unroll
+                        for (int k = 0; k < 3; ++k) G[t][k] = fmaf(B[t][k], bv, C[t][k]);
+                    const float4 *src = reinterpret_cast<const float4 *>(tile + ss * segpad);
+#pragma unroll 2
+                    for (int p = 0; p < segpad / 2; ++p) {
+                        const float4 pp = src[p];
+#pragma unroll
+                        for (int t = 0; t < T; ++t) {
+                            const float q0 = fmaf(pp.y, fmaf(A[t][0], pp.x, G[t][0]), NO[t][0]);
+                            const float q1 = fmaf(pp.y, fmaf(A[t][1], pp.x, G[t][1]), NO[t][1]);
+                            const float q2 = fmaf(pp.y, fmaf(A[t][2], pp.x, G[t][2]), NO[t][2]);
+                            count_inside(cnt[t], q0, q1, q2, Hh[t][0], Hh[t][1], Hh[t][2]);
+                        }
+#pragma unroll
+                        for (int t = 0; t < T; ++t) {
+                            const float q0 = fmaf(pp.w, fmaf(A[t][0], pp.z, G[t][0]), NO[t][0]);
+                            const float q1 = fmaf(pp.w, fmaf(A[t][1], pp.z, G[t][1]), NO[t][1]);
+                            const float q2 = fmaf(pp.w, fmaf(A[t][2], pp.z, G[t][2]), NO[t][2]);
+                            count_inside(cnt[t], q0, q1, q2, Hh[t][0], Hh[t][1], Hh[t][2]);
+                        }
+                    }
+                }
+            }
+        }
+
+        // ---- retire the item: counts -> global, ticket ---------------------------
+#pragma unroll
+        for (int t = 0; t < T; ++t) {
+            const int j = chunk * SC_CHUNK + t * SC_THREADS + tid;
+            if (cnt[t] > 0) atomicAdd(a.ws.count + (size_t)b * a.N + j, cnt[t]);
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) my_valid += __shfl_xor_sync(0xffffffffu, my_valid, o);
+        if (lane == 0 && my_valid) atomicAdd(a.ws.npts + (size_t)b * a.n_chunks + chunk, my_valid);
+        __threadfence();
+        __syncthreads();
+        if (tid == 0) {
+            const int ticket = atomicAdd(a.ws.done_chunk + (size_t)b * a.n_chunks + chunk, 1);
+            s_flag = (ticket == roi.n_rowblocks - 1);
+        }
+        __syncthreads();
+        if (!s_flag) continue;
+        __threadfence();
+
+        // ---- epilogue of (box, chunk): corners -> projection -> IoU -> score ------
+        const int npts = __ldcg(a.ws.npts + (size_t)b * a.n_chunks + chunk);
+        if (a.out_npts && chunk == 0 && tid == 0) a.out_npts[b] = npts;
+        float lo0, hi0, lo1, hi1;
+        clamp_bounds(bx.clamp0, lo0, hi0);
+        clamp_bounds(bx.clamp1, lo1, hi1);
+#pragma unroll 1
+        for (int t = 0; t < T; ++t) {
+            const int loc = t * SC_THREADS + tid;
+            const int j = chunk * SC_CHUNK + loc;
+            float score = -INFINITY, siou = 0.f, spts = 0.f;
+            if (j < a.N) {
+                const size_t o = (size_t)b * a.N + j;
+                const float *src = cubes + o * 15;
+                float cube[15];
+#pragma unroll
+                for (int i = 0; i < 15; ++i) cube[i] = __ldg(src + i);
+                const int c = __ldcg(a.ws.count + o);
+                const ProjBox pb = project_cube(cube, K, lo0, hi0, lo1, hi1, nullptr);
+                siou = iou_2d(bx.x1, bx.y1, bx.x2, bx.y2, pb);
+                spts = npts > 0 ? (float)c / (float)npts : 0.f;
+                score = (ipow(siou, a.sc.e_iou) * ipow(spts, a.sc.e_pts)) * 1.f;  // s_seg: later
+                if (a.out_scores) a.out_scores[o] = score;
+                if (a.out_iou) a.out_iou[o] = siou;
+                if (a.out_count) a.out_count[o] = c;
+                if (a.out_proj) {
+                    float *d = a.out_proj + o * 4;
+                    d[0] = pb.x1; d[1] = pb.y1; d[2] = pb.x2; d[3] = pb.y2;
+                }
+            }
+            s_score[loc] = score; s_iou[loc] = siou; s_pts[loc] = spts;
+        }
+        __syncthreads();
+        cta_topk(s_score, a.k, s_red_v, s_red_i, s_win, s_wsc);
+        float *rec_base = a.n_chunks == 1
+                              ? a.records + (size_t)b * a.k * WCR_RECORD_FLOATS
+                              : a.ws.cand + ((size_t)b * a.n_chunks + chunk) * a.k * WCR_RECORD_FLOATS;
+        if (tid < a.k) {
+            const int loc = s_win[tid];
+            float *rec = rec_base + (size_t)tid * WCR_RECORD_FLOATS;
+            if (loc < 0) {
+                rec[0] = __int_as_float(-1);
+                for (int i = 1; i < WCR_RECORD_FLOATS; ++i) rec[i] = 0.f;
+            } else {
+                const int j = chunk * SC_CHUNK + loc;
+                const float *src = cubes + ((size_t)b * a.N + j) * 15;
+                rec[0] = __int_as_float(j);
+                rec[1] = s_wsc[tid];
+                for (int i = 0; i < 15; ++i) rec[2 + i] = __ldg(src + i);
+                rec[17] = s_iou[loc]; rec[18] = s_pts[loc]; rec[19] = 1.f;
+            }
+        }
+        if (a.n_chunks > 1) {
+            __threadfence();
+            __syncthreads();
+            if (tid == 0) s_flag = (atomicAdd(a.ws.done_box + b, 1) == a.n_chunks - 1);
+            __syncthreads();
+            if (s_flag && tid < 32) {
+                __threadfence();
+                warp_merge(a.ws.cand + (size_t)b * a.n_chunks * a.k * WCR_RECORD_FLOATS,
+                           a.n_chunks * a.k, a.k, a.records + (size_t)b * a.k * WCR_RECORD_FLOATS);
+            }
         }
     }
 }
 
 }  // namespace wcr
 
+namespace wcr {
+cudaError_t launch_sample_cubes(const WcrImage *images, const WcrBox *boxes, int n_boxes,
+                                const float *priors, const float *normals, const float *z0,
+                                const WcrSampleParams &sp, int N, const float *replay,
+                                uint64_t seed, float *out_cubes, cudaStream_t st);
+}
+
 namespace {
-constexpr int kT = 4;
-constexpr int kChunk = wcr::SC_THREADS * kT;
-inline int n_chunks_for(int N) { return (N + kChunk - 1) / kChunk; }
+inline int n_chunks_for(int N) { return (N + wcr::SC_CHUNK - 1) / wcr::SC_CHUNK; }
+inline size_t align256(size_t x) { return (x + 255) & ~(size_t)255; }
+
+// Carve the caller's workspace. Returns total bytes; *zero_bytes = leading region
+// that must be zero at launch.
+size_t carve(void *base, int n_boxes, int N, int k, bool need_cubes, wcr::ScoreWs *ws,
+             size_t *zero_bytes)
+{
+    const int nc = n_chunks_for(N);
+    char *p = (char *)base;
+    size_t off = 0;
+    auto take = [&](size_t bytes) { char *q = p ? p + off : nullptr; off += align256(bytes); return q; };
+    int *queue = (int *)take(sizeof(int));
+    int *done_chunk = (int *)take((size_t)n_boxes * nc * sizeof(int));
+    int *done_box = (int *)take((size_t)n_boxes * sizeof(int));
+    int *npts = (int *)take((size_t)n_boxes * nc * sizeof(int));
+    int *count = (int *)take((size_t)n_boxes * N * sizeof(int));
+    if (zero_bytes) *zero_bytes = off;
+    int *prefix = (int *)take((size_t)(n_boxes + 1) * sizeof(int));
+    float *cand = (float *)take(nc > 1 ? (size_t)n_boxes * nc * k * WCR_RECORD_FLOATS * sizeof(float) : 0);
+    float *cubes = (float *)take(need_cubes ? (size_t)n_boxes * N * 15 * sizeof(float) : 0);
+    if (ws) {
+        ws->queue = queue; ws->done_chunk = done_chunk; ws->done_box = done_box; ws->npts = npts;
+        ws->count = count; ws->item_prefix = prefix; ws->cand = cand; ws->cubes = cubes;
+    }
+    return off;
+}
 }  // namespace
 
 extern "C" int64_t wcr_score_workspace_bytes(int n_boxes, int N, int k)
 {
     if (n_boxes < 0 || N < 1 || k < 1) return -1;
-    const int nc = n_chunks_for(N);
-    if (nc <= 1) return 16;  // never dereferenced
-    return (int64_t)n_boxes * nc * k * WCR_RECORD_FLOATS * (int64_t)sizeof(float);
+    // sized for the larger case (library-side sampling needs the cube buffer)
+    return (int64_t)carve(nullptr, n_boxes, N, k, true, nullptr, nullptr);
 }
 
 extern "C" int wcr_score_topk(const WcrImage *images, const WcrBox *boxes, int n_boxes,
@@ -334,7 +468,7 @@ extern "C" int wcr_score_topk(const WcrImage *images, const WcrBox *boxes, int n
                               float *out_proj, int32_t *out_npts, void *ws, void *stream)
 {
     WCR_CHECK_DEVICE();
-    WCR_REQUIRE(images && boxes && h_score && out_records, "wcr_score_topk: null pointer");
+    WCR_REQUIRE(images && boxes && h_score && out_records && ws, "wcr_score_topk: null pointer");
     WCR_REQUIRE(n_boxes >= 0 && N >= 1, "wcr_score_topk: bad sizes");
     WCR_REQUIRE(k >= 1 && k <= WCR_MAX_TOPK, "wcr_score_topk: k must be in [1, %d]", WCR_MAX_TOPK);
     WCR_REQUIRE(cubes || (priors && normals && z0 && h_sample),
@@ -344,27 +478,33 @@ extern "C" int wcr_score_topk(const WcrImage *images, const WcrBox *boxes, int n
                 "wcr_score_topk: negative exponent");
     WCR_REQUIRE(h_score->e_seg == 0 || (seg_bits && seg_off),
                 "wcr_score_topk: e_seg > 0 needs seg_bits and seg_off");
+    WCR_REQUIRE(((uintptr_t)ws & 255) == 0, "wcr_score_topk: workspace must be 256-byte aligned");
     const int nc = n_chunks_for(N);
-    WCR_REQUIRE(nc <= 64, "wcr_score_topk: N too large (max %d)", 64 * kChunk);
-    WCR_REQUIRE(nc == 1 || ws, "wcr_score_topk: workspace required when N > %d", kChunk);
+    WCR_REQUIRE(nc <= wcr::SC_MAX_CHUNKS, "wcr_score_topk: N too large (max %d)",
+                wcr::SC_MAX_CHUNKS * wcr::SC_CHUNK);
     if (n_boxes == 0) return WCR_OK;
+    cudaStream_t st = (cudaStream_t)stream;
 
     wcr::ScoreArgs a;
-    a.images = images; a.boxes = boxes; a.cubes = cubes; a.N = N;
-    a.priors = priors; a.normals = normals; a.z0 = z0;
-    if (h_sample) a.sp = *h_sample; else memset(&a.sp, 0, sizeof(a.sp));
-    a.seed = seed; a.seg_bits = seg_bits; a.seg_off = seg_off; a.sc = *h_score; a.k = k;
-    a.n_chunks = nc;
-    a.records = nc == 1 ? out_records : (float *)ws;
+    size_t zero_bytes = 0;
+    carve(ws, n_boxes, N, k, cubes == nullptr, &a.ws, &zero_bytes);
+    cudaError_t e = cudaMemsetAsync(ws, 0, zero_bytes, st);
+    if (e != cudaSuccess) { wcr::set_error("cudaMemsetAsync: %s", cudaGetErrorString(e)); return WCR_ELAUNCH; }
+    wcr::score_plan_kernel<<<1, 1024, 0, st>>>(images, boxes, n_boxes, nc, h_score->point_stride,
+                                               h_score->e_pts > 0, a.ws.item_prefix);
+    WCR_CHECK_LAUNCH("score_plan_kernel");
+    if (!cubes) {
+        WCR_REQUIRE((N + 255) / 256 <= 65535, "wcr_score_topk: N too large");
+        wcr::launch_sample_cubes(images, boxes, n_boxes, priors, normals, z0, *h_sample, N, nullptr,
+                                 seed, a.ws.cubes, st);
+        WCR_CHECK_LAUNCH("sample_cubes_kernel");
+    }
+    a.images = images; a.boxes = boxes; a.n_boxes = n_boxes; a.cubes = cubes; a.N = N;
+    a.sc = *h_score; a.k = k; a.n_chunks = nc; a.records = out_records;
     a.out_scores = out_scores; a.out_iou = out_iou; a.out_count = out_count;
     a.out_proj = out_proj; a.out_npts = out_npts;
-    dim3 grid(n_boxes, nc);
-    wcr::score_topk_kernel<kT><<<grid, wcr::SC_THREADS, 0, (cudaStream_t)stream>>>(a);
-    WCR_CHECK_LAUNCH("score_topk_kernel");
-    if (nc > 1) {
-        wcr::topk_merge_kernel<<<n_boxes, 32, 0, (cudaStream_t)stream>>>((const float *)ws, nc, k,
-                                                                        out_records);
-        WCR_CHECK_LAUNCH("topk_merge_kernel");
-    }
+    (void)seg_bits; (void)seg_off;
+    wcr::score_items_kernel<<<wcr::sm_count() * 2, wcr::SC_THREADS, 0, st>>>(a);
+    WCR_CHECK_LAUNCH("score_items_kernel");
     return WCR_OK;
 }

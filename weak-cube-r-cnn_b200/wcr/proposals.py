@@ -138,7 +138,7 @@ class ScoreWorkspace:
     def __init__(self, n_boxes: int, N: int, k: int, device, records: torch.Tensor | None = None):
         lib = _abi.load()
         nbytes = int(lib.wcr_score_workspace_bytes(n_boxes, N, k))
-        self.ws = torch.empty((max(nbytes, 16),), dtype=torch.uint8, device=device)
+        self.ws = torch.empty((max(nbytes, 256),), dtype=torch.uint8, device=device)  # 256-B aligned by the allocator
         self.records = records if records is not None else torch.empty(
             (n_boxes, k, RECORD_FLOATS), dtype=torch.float32, device=device)
         self.n_boxes, self.N, self.k = n_boxes, N, k

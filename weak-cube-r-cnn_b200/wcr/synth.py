@@ -37,6 +37,7 @@ def make_image(i: int, H: int = 480, W: int = 640, n_boxes: int | None = None,
     for _ in range(n_bumps):
         bw = int(torch.randint(30, max(31, W // 4), (1,), generator=g).item())
         bh = int(torch.randint(30, max(31, H // 3), (1,), generator=g).item())
+        bw, bh = min(bw, W - 1), min(bh, H - H // 4 - 1)
         x0 = int(torch.randint(0, W - bw, (1,), generator=g).item())
         y0 = int(torch.randint(H // 4, H - bh, (1,), generator=g).item())
         zb = depth[min(y0 + bh, H - 1), x0 + bw // 2].item()  # stands on what is below it
