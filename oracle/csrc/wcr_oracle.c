@@ -185,11 +185,14 @@ static inline float ipow_(float x, int e) { float r = 1.f; for (int i = 0; i < e
 
 /* SURVEY A3.11/A3.12 for ONE box: N cubes against the depth pixels of the box's
  * integer ROI (Boxes.clip + .long(), roi_heads.py:590-597), sub-sampled by
- * `stride`. Point p = z*(a_u, b_v, 1), a_u = (u-cx)/fx, b_v = (v-cy)/fy;
- *   q_k = fma(z, fma(R0k, a_u, fma(R1k, b_v, R2k)), -O_k),
- *   O_k = fma(R2k, cz, fma(R1k, cy, R0k*cx));
- * inside iff |q_0| <= l/2 and |q_1| <= h/2 and |q_2| <= w/2 (math_util.py:198-207
- * axis mapping). Returns P_b (valid points). */
+ * `stride`. Point p = z*(a_u, b_v, 1), a_u = (u-cx)/fx, b_v = (v-cy)/fy. The test
+ * "|R[:,k].(p-c)| <= half_k for k = x,y,z" with half = (l/2, h/2, w/2)
+ * (math_util.py:198-207 axis mapping) is evaluated in unit-cube form:
+ *   A'_k = R0k/half_k, B'_k = R1k/half_k, C'_k = R2k/half_k      (IEEE division)
+ *   O'_k = fma(C'_k, cz, fma(B'_k, cy, A'_k*cx))
+ *   q'_k = fma(z, fma(A'_k, a_u, fma(B'_k, b_v, C'_k)), -O'_k)
+ *   inside iff max(|q'_0|, |q'_1|, |q'_2|) <= 1      (max ignores NaN operands)
+ * A cube with a non-positive dimension contains no point. Returns P_b. */
 int orc_score_box(const float *depth, int H, int W, int pitch, const float *K4, const float *gbox,
                   float clamp0, float clamp1, const float *cubes, int N, int stride, int e_iou,
                   int e_pts, float *out_score, float *out_iou, int *out_count, float *out_proj)
@@ -209,14 +212,15 @@ int orc_score_box(const float *depth, int H, int W, int pitch, const float *K4, 
 #pragma omp parallel for schedule(dynamic, 8)
     for (int j = 0; j < N; ++j) {
         const float *cube = cubes + (size_t)j * 15;
-        float A[3], B[3], C[3], NO[3], Hh[3];
+        float A[3], B[3], C[3], NO[3];
+        const float half[3] = {cube[5] / 2.f, cube[4] / 2.f, cube[3] / 2.f};
+        const int live = cube[3] > 0.f && cube[4] > 0.f && cube[5] > 0.f;
         for (int k = 0; k < 3; ++k) {
-            A[k] = cube[6 + k]; B[k] = cube[9 + k]; C[k] = cube[12 + k];
+            A[k] = cube[6 + k] / half[k]; B[k] = cube[9 + k] / half[k]; C[k] = cube[12 + k] / half[k];
             NO[k] = -fmaf(C[k], cube[2], fmaf(B[k], cube[1], A[k] * cube[0]));
         }
-        Hh[0] = cube[5] / 2.f; Hh[1] = cube[4] / 2.f; Hh[2] = cube[3] / 2.f;
         int cnt = 0;
-        if (e_pts > 0)
+        if (e_pts > 0 && live)
             for (int v = v0; v < v1; v += stride) {
                 const float bv = ((float)v - K4[3]) / K4[1];
                 const float G0 = fmaf(B[0], bv, C[0]), G1 = fmaf(B[1], bv, C[1]),
@@ -228,7 +232,7 @@ int orc_score_box(const float *depth, int H, int W, int pitch, const float *K4, 
                     const float q0 = fmaf(d, fmaf(A[0], au, G0), NO[0]);
                     const float q1 = fmaf(d, fmaf(A[1], au, G1), NO[1]);
                     const float q2 = fmaf(d, fmaf(A[2], au, G2), NO[2]);
-                    cnt += (fabsf(q0) <= Hh[0]) & (fabsf(q1) <= Hh[1]) & (fabsf(q2) <= Hh[2]);
+                    cnt += fmaxf(fmaxf(fabsf(q0), fabsf(q1)), fabsf(q2)) <= 1.f;
                 }
             }
         float pb[4];

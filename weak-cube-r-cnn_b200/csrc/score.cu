@@ -15,13 +15,14 @@
 // Point test. Every tested point is an unprojected pixel p = z * (a_u, b_v, 1),
 // a_u = (u - cx)/fx, b_v = (v - cy)/fy, so the local-frame coordinate factors per
 // image row:
-//     q_k = R[:,k] . (p - c) = fma(z, fma(A_k, a_u, G_k), -O_k),
+//     q_k = R[:,k] . (p - c) = fma(z, fma(A_k, a_u, G_k), -O_k),   (rows pre-scaled by 1/half_k)
 //     G_k = fma(B_k, b_v, C_k) per row,  O_k = R[:,k] . c per proposal
 // 6 FFMA + 3 compares per (proposal, point) instead of 3 FADD + 9 FFMA. This
 // rounding order IS the definition oracle/csrc/wcr_oracle.c restates; counts are
 // bit-exact against it (DESIGN.md "Point-in-cube test").
 //
 // FP32 CUDA-core kernel by construction: nothing here is a dense contraction.
+#include <stdlib.h>
 #include <string.h>
 #include "sample.cuh"
 
@@ -30,21 +31,52 @@ namespace wcr {
 constexpr int SC_THREADS = 256;
 constexpr int SC_T = 4;                        // proposals per thread
 constexpr int SC_CHUNK = SC_THREADS * SC_T;    // proposals per item
-constexpr int SC_TILE = 2048;                  // (a_u, z) pairs per smem tile = 16 KB
+constexpr int SC_TILE = 2048;                  // (a,a,z,z) pixels per smem tile = 32 KB
 constexpr int SC_ITEM_PX = 4096;               // target depth pixels per item
 constexpr int SC_MAX_CHUNKS = 64;
 
-__device__ __forceinline__ void count_inside(int &cnt, float q0, float q1, float q2, float h0,
-                                             float h1, float h2)
+typedef unsigned long long u64;
+__device__ __forceinline__ u64 pack2(float lo, float hi)
+{
+    u64 r;
+    asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi));
+    return r;
+}
+__device__ __forceinline__ void unpack2(u64 v, float &lo, float &hi)
+{
+    asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v));
+}
+// Blackwell packed FP32: two independent IEEE fma.rn per instruction (FFMA2).
+__device__ __forceinline__ u64 ffma2(u64 a, u64 b, u64 c)
+{
+    u64 r;
+    asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(a), "l"(b), "l"(c));
+    return r;
+}
+__device__ __forceinline__ u64 fadd2(u64 a, u64 b)
+{
+    u64 r;
+    asm("add.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
+    return r;
+}
+__device__ __forceinline__ void count_inside1(int &cnt, float q0, float q1, float q2)
 {
     asm("{\n\t.reg .pred p;\n\t.reg .f32 a0, a1, a2;\n\t"
         "abs.f32 a0, %1;\n\tabs.f32 a1, %2;\n\tabs.f32 a2, %3;\n\t"
-        "setp.le.f32 p, a0, %4;\n\t"
-        "setp.le.and.f32 p, a1, %5, p;\n\t"
-        "setp.le.and.f32 p, a2, %6, p;\n\t"
+        "setp.le.f32 p, a0, 0f3F800000;\n\t"
+        "setp.le.and.f32 p, a1, 0f3F800000, p;\n\t"
+        "setp.le.and.f32 p, a2, 0f3F800000, p;\n\t"
         "@p add.s32 %0, %0, 1;\n\t}"
         : "+r"(cnt)
-        : "f"(q0), "f"(q1), "f"(q2), "f"(h0), "f"(h1), "f"(h2));
+        : "f"(q0), "f"(q1), "f"(q2));
+}
+// 1.0f if max(|q0|,|q1|,|q2|) <= 1 else 0.0f. One FMNMX3 + one FSET; NaN -> 0.
+__device__ __forceinline__ float inside_unit(float q0, float q1, float q2)
+{
+    float m, r;
+    asm("max.f32 %0, %1, %2, %3;" : "=f"(m) : "f"(fabsf(q0)), "f"(fabsf(q1)), "f"(fabsf(q2)));
+    asm("set.le.f32.f32 %0, %1, 0f3F800000;" : "=f"(r) : "f"(m));
+    return r;
 }
 
 // Integer ROI of a GT box: Boxes.clip((h, w)) then .long() slicing, as the
@@ -206,10 +238,15 @@ __device__ __forceinline__ void warp_merge(const float *cand, int n, int k, floa
     }
 }
 
-__global__ void __launch_bounds__(SC_THREADS, 2) score_items_kernel(const ScoreArgs a)
+// V selects the inner-loop instruction mix (same arithmetic, same results):
+//   0: FFMA2 (two proposals per packed fma) + FMNMX3 + FSET + FADD2
+//   1: scalar FFMA + FMNMX3 + FSET + FADD
+//   2: scalar FFMA + 3 x FSETP(|q| <= 1) + predicated IADD
+template <int V, int MINB>
+__global__ void __launch_bounds__(SC_THREADS, MINB) score_items_kernel(const ScoreArgs a)
 {
     constexpr int T = SC_T;
-    __shared__ __align__(16) float2 tile[SC_TILE];
+    __shared__ __align__(16) float4 tile[SC_TILE];
     __shared__ float s_score[SC_CHUNK];
     __shared__ float s_iou[SC_CHUNK];
     __shared__ float s_pts[SC_CHUNK];
@@ -246,36 +283,56 @@ __global__ void __launch_bounds__(SC_THREADS, 2) score_items_kernel(const ScoreA
         const int row_begin = rb * roi.rows_per_item;
         const int row_end = min(roi.nrows, row_begin + roi.rows_per_item);
 
-        // ---- prologue: proposal state -> registers ------------------------------
-        float A[T][3], B[T][3], C[T][3], NO[T][3], Hh[T][3];
-        int cnt[T];
+        // ---- prologue: proposal state -> registers, two proposals per FFMA2 lane pair
+        // unit-cube form: row k of the test is scaled by 1/half_k so that
+        // inside <=> max_k |q'_k| <= 1 (one FMNMX3 + one FSET instead of 3 FSETP).
+        u64 A2[T / 2][3], B2[T / 2][3], C2[T / 2][3], NO2[T / 2][3], cnt2[T / 2];
 #pragma unroll
-        for (int t = 0; t < T; ++t) {
-            const int j = chunk * SC_CHUNK + t * SC_THREADS + tid;
-            cnt[t] = 0;
-            if (j < a.N && row_end > row_begin) {
-                const float *src = cubes + ((size_t)b * a.N + j) * 15;
+        for (int pr = 0; pr < T / 2; ++pr) {
+            float Af[2][3], Bf[2][3], Cf[2][3], NOf[2][3];
+#pragma unroll
+            for (int e = 0; e < 2; ++e) {
+                const int j = chunk * SC_CHUNK + (2 * pr + e) * SC_THREADS + tid;
+                bool live = j < a.N && row_end > row_begin;
                 float cube[15];
+                if (live) {
+                    const float *src = cubes + ((size_t)b * a.N + j) * 15;
 #pragma unroll
-                for (int i = 0; i < 15; ++i) cube[i] = __ldg(src + i);
-#pragma unroll
-                for (int k = 0; k < 3; ++k) {
-                    A[t][k] = cube[6 + k]; B[t][k] = cube[9 + k]; C[t][k] = cube[12 + k];
-                    NO[t][k] = -fmaf(C[t][k], cube[2], fmaf(B[t][k], cube[1], A[t][k] * cube[0]));
+                    for (int i = 0; i < 15; ++i) cube[i] = __ldg(src + i);
+                    live = cube[3] > 0.f && cube[4] > 0.f && cube[5] > 0.f;  // empty cube holds no point
                 }
-                Hh[t][0] = cube[5] / 2.f; Hh[t][1] = cube[4] / 2.f; Hh[t][2] = cube[3] / 2.f;
-            } else {
+                if (live) {
+                    const float half[3] = {cube[5] / 2.f, cube[4] / 2.f, cube[3] / 2.f};
 #pragma unroll
-                for (int k = 0; k < 3; ++k) { A[t][k] = B[t][k] = C[t][k] = NO[t][k] = 0.f; Hh[t][k] = -1.f; }
+                    for (int k = 0; k < 3; ++k) {
+                        Af[e][k] = cube[6 + k] / half[k];
+                        Bf[e][k] = cube[9 + k] / half[k];
+                        Cf[e][k] = cube[12 + k] / half[k];
+                        NOf[e][k] = -fmaf(Cf[e][k], cube[2], fmaf(Bf[e][k], cube[1], Af[e][k] * cube[0]));
+                    }
+                } else {
+#pragma unroll
+                    for (int k = 0; k < 3; ++k) { Af[e][k] = Bf[e][k] = Cf[e][k] = 0.f; NOf[e][k] = nanf_(); }
+                }
             }
+#pragma unroll
+            for (int k = 0; k < 3; ++k) {
+                A2[pr][k] = pack2(Af[0][k], Af[1][k]); B2[pr][k] = pack2(Bf[0][k], Bf[1][k]);
+                C2[pr][k] = pack2(Cf[0][k], Cf[1][k]); NO2[pr][k] = pack2(NOf[0][k], NOf[1][k]);
+            }
+            cnt2[pr] = pack2(0.f, 0.f);
         }
+        float cntf[T];
+        int cnti[T];
+#pragma unroll
+        for (int t = 0; t < T; ++t) { cntf[t] = 0.f; cnti[t] = 0; }
 
         // ---- main loop: this item's rows, tile by tile --------------------------
         int my_valid = 0;
         if (row_end > row_begin) {
             const int ncols = roi.ncols;
             const int pieces = (ncols + SC_TILE - 1) / SC_TILE;
-            const int segpad = (min(ncols, SC_TILE) + 1) & ~1;
+            const int segpad = min(ncols, SC_TILE);
             const int spt = SC_TILE / segpad;  // row segments per tile, >= 1
             const int total_segs = (row_end - row_begin) * pieces;
             for (int seg0 = 0; seg0 < total_segs; seg0 += spt) {
@@ -293,38 +350,69 @@ __global__ void __launch_bounds__(SC_THREADS, 2) score_items_kernel(const ScoreA
                         av = ((float)u - K.cx) / K.fx;
                         if (d > 0.f && d <= 3.402823466e38f) { z = d; ++my_valid; }
                     }
-                    tile[idx] = make_float2(av, z);
+                    tile[idx] = make_float4(av, av, z, z);
                 }
                 __syncthreads();
                 for (int ss = 0; ss < nseg; ++ss) {
                     const int row = (seg0 + ss) / pieces;
                     const float bv = ((float)(roi.v0 + (row_begin + row) * s) - K.cy) / K.fy;
-                    float G[T][3];
+                    const u64 bvbv = pack2(bv, bv);
+                    u64 G2[T / 2][3];
 #pragma unroll
-                    for (int t = 0; t < T; ++t)
+                    for (int pr = 0; pr < T / 2; ++pr)
 #pragma unroll
-                        for (int k = 0; k < 3; ++k) G[t][k] = fmaf(B[t][k], bv, C[t][k]);
-                    const float4 *src = reinterpret_cast<const float4 *>(tile + ss * segpad);
-#pragma unroll 2
-                    for (int p = 0; p < segpad / 2; ++p) {
-                        const float4 pp = src[p];
+                        for (int k = 0; k < 3; ++k) G2[pr][k] = ffma2(B2[pr][k], bvbv, C2[pr][k]);
+                    if (V == 0) {
+                        const ulonglong2 *src = reinterpret_cast<const ulonglong2 *>(tile + ss * segpad);
+#pragma unroll 4
+                        for (int p = 0; p < segpad; ++p) {
+                            const ulonglong2 pp = src[p];  // (a,a) , (z,z)
 #pragma unroll
-                        for (int t = 0; t < T; ++t) {
-                            const float q0 = fmaf(pp.y, fmaf(A[t][0], pp.x, G[t][0]), NO[t][0]);
-                            const float q1 = fmaf(pp.y, fmaf(A[t][1], pp.x, G[t][1]), NO[t][1]);
-                            const float q2 = fmaf(pp.y, fmaf(A[t][2], pp.x, G[t][2]), NO[t][2]);
-                            count_inside(cnt[t], q0, q1, q2, Hh[t][0], Hh[t][1], Hh[t][2]);
+                            for (int pr = 0; pr < T / 2; ++pr) {
+                                float q[3][2];
+#pragma unroll
+                                for (int k = 0; k < 3; ++k)
+                                    unpack2(ffma2(pp.y, ffma2(A2[pr][k], pp.x, G2[pr][k]), NO2[pr][k]),
+                                            q[k][0], q[k][1]);
+                                const float r0 = inside_unit(q[0][0], q[1][0], q[2][0]);
+                                const float r1 = inside_unit(q[0][1], q[1][1], q[2][1]);
+                                cnt2[pr] = fadd2(cnt2[pr], pack2(r0, r1));
+                            }
                         }
+                    } else {
+                        float Af[T][3], Gf[T][3], NOf[T][3];
 #pragma unroll
-                        for (int t = 0; t < T; ++t) {
-                            const float q0 = fmaf(pp.w, fmaf(A[t][0], pp.z, G[t][0]), NO[t][0]);
-                            const float q1 = fmaf(pp.w, fmaf(A[t][1], pp.z, G[t][1]), NO[t][1]);
-                            const float q2 = fmaf(pp.w, fmaf(A[t][2], pp.z, G[t][2]), NO[t][2]);
-                            count_inside(cnt[t], q0, q1, q2, Hh[t][0], Hh[t][1], Hh[t][2]);
+                        for (int pr = 0; pr < T / 2; ++pr)
+#pragma unroll
+                            for (int k = 0; k < 3; ++k) {
+                                unpack2(A2[pr][k], Af[2 * pr][k], Af[2 * pr + 1][k]);
+                                unpack2(G2[pr][k], Gf[2 * pr][k], Gf[2 * pr + 1][k]);
+                                unpack2(NO2[pr][k], NOf[2 * pr][k], NOf[2 * pr + 1][k]);
+                            }
+                        const float4 *src = tile + ss * segpad;
+#pragma unroll 4
+                        for (int p = 0; p < segpad; ++p) {
+                            const float4 pp = src[p];
+#pragma unroll
+                            for (int t = 0; t < T; ++t) {
+                                const float q0 = fmaf(pp.z, fmaf(Af[t][0], pp.x, Gf[t][0]), NOf[t][0]);
+                                const float q1 = fmaf(pp.z, fmaf(Af[t][1], pp.x, Gf[t][1]), NOf[t][1]);
+                                const float q2 = fmaf(pp.z, fmaf(Af[t][2], pp.x, Gf[t][2]), NOf[t][2]);
+                                if (V == 1) cntf[t] += inside_unit(q0, q1, q2);
+                                else count_inside1(cnti[t], q0, q1, q2);
+                            }
                         }
                     }
                 }
             }
+        }
+        int cnt[T];
+#pragma unroll
+        for (int pr = 0; pr < T / 2; ++pr) {
+            float c0, c1;
+            unpack2(cnt2[pr], c0, c1);
+            cnt[2 * pr] = (int)c0 + (int)cntf[2 * pr] + cnti[2 * pr];
+            cnt[2 * pr + 1] = (int)c1 + (int)cntf[2 * pr + 1] + cnti[2 * pr + 1];
         }
 
         // ---- retire the item: counts -> global, ticket ---------------------------
@@ -504,7 +592,20 @@ extern "C" int wcr_score_topk(const WcrImage *images, const WcrBox *boxes, int n
     a.out_scores = out_scores; a.out_iou = out_iou; a.out_count = out_count;
     a.out_proj = out_proj; a.out_npts = out_npts;
     (void)seg_bits; (void)seg_off;
-    wcr::score_items_kernel<<<wcr::sm_count() * 2, wcr::SC_THREADS, 0, st>>>(a);
+    static int variant = -1;
+    if (variant < 0) {  // development knob; the default is what DESIGN.md measures
+        const char *ev = getenv("WCR_SCORE_VARIANT");
+        variant = ev ? atoi(ev) : 1;
+    }
+    const int sms = wcr::sm_count();
+    switch (variant) {
+    case 2: wcr::score_items_kernel<2, 2><<<sms * 2, wcr::SC_THREADS, 0, st>>>(a); break;
+    case 10: wcr::score_items_kernel<0, 3><<<sms * 3, wcr::SC_THREADS, 0, st>>>(a); break;
+    case 11: wcr::score_items_kernel<1, 3><<<sms * 3, wcr::SC_THREADS, 0, st>>>(a); break;
+    case 12: wcr::score_items_kernel<2, 3><<<sms * 3, wcr::SC_THREADS, 0, st>>>(a); break;
+    case 0: wcr::score_items_kernel<0, 2><<<sms * 2, wcr::SC_THREADS, 0, st>>>(a); break;
+    default: wcr::score_items_kernel<1, 2><<<sms * 2, wcr::SC_THREADS, 0, st>>>(a); break;
+    }
     WCR_CHECK_LAUNCH("score_items_kernel");
     return WCR_OK;
 }
