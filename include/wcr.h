@@ -200,6 +200,72 @@ int wcr_score_topk(const WcrImage *images, const WcrBox *boxes, int n_boxes,
                    int32_t *out_count, float *out_proj, int32_t *out_npts,
                    void *ws, void *stream);
 
+/* ---------------------------------------------------------------- step 4 -- */
+
+/* Weak-loss block of ROIHeads3DScore._forward_cube (roi_heads.py:786-905 decode,
+ * :927-960 cubes + projected boxes, :973-1031 terms, :1075-1144 uncertainty scaling
+ * and safe reductions; helpers :445-464 pose_loss, :612-656 dim_loss /
+ * pseudo_gt_z_point_loss, :1307-1315 safely_reduce_losses; math_util.py:802-830
+ * R_from_allocentric, :1132-1237 so3_relative_angle_batched; torchvision
+ * generalized_box_iou_loss) as a fused forward / backward kernel pair. */
+#define WCR_LOSS_IOU          1   /* 'iou'                 */
+#define WCR_LOSS_POSE_ALIGN   2   /* 'pose_alignment'      */
+#define WCR_LOSS_POSE_GROUND  4   /* 'pose_ground'         */
+#define WCR_LOSS_Z_CENTER     8   /* 'z_pseudo_gt_center'  */
+#define WCR_LOSS_DIMS        16   /* 'dims'                */
+
+/* order of the scalar outputs (keys of the reference's loss dict, prefix 'Cube/') */
+enum { WCR_T_UNCERT = 0, WCR_T_IOU, WCR_T_POSE, WCR_T_NORMAL, WCR_T_PSEUDO_Z,
+       WCR_T_DIMS_W, WCR_T_DIMS_H, WCR_T_DIMS_L, WCR_LOSS_TERMS };
+
+typedef struct WcrLossParams {
+    int32_t loss_flags;       /* WCR_LOSS_* bits (cfg.loss_functions, config.py:186)   */
+    int32_t z_type;           /* 0 direct, 1 sigmoid, 2 log  (roi_heads.py:874-880)    */
+    int32_t dims_func;        /* 0 exp, 1 sigmoid            (roi_heads.py:856-861)    */
+    float   use_confidence;   /* cfg USE_CONFIDENCE; 0 disables uncertainty scaling    */
+    float   w_3d, w_iou, w_pose, w_normal, w_z, w_dims;   /* LOSS_W_* (config.py:119-127) */
+} WcrLossParams;
+
+/* Every per-box array is indexed by foreground box, boxes of one image contiguous
+ * (the reference's torch.cat order); img_off[n_images+1] are the box ranges. */
+typedef struct WcrLossIO {
+    int32_t n, n_images;
+    /* head outputs, gathered per class (require grad in the reference) */
+    const float *deltas;      /* [n][2]  cube_2d_deltas                       */
+    const float *z_raw;       /* [n]     cube_z before z_type / virtual depth */
+    const float *dims_raw;    /* [n][3]  cube_dims (log-scale for 'exp')      */
+    const float *pose;        /* [n][9]  allocentric R_view, row-major        */
+    const float *uncert;      /* [n]     cube_uncert                          */
+    /* constants */
+    const float *src_boxes;   /* [n][4]  proposal boxes the deltas apply to   */
+    const float *K4;          /* [n][4]  fx fy cx cy of Ks_scaled_per_box     */
+    const float *v2r;         /* [n]     virtual_to_real (math_util.py:732)   */
+    const float *prior_mean;  /* [n][3]  gathered dims prior (w h l)          */
+    const float *prior_std;   /* [n][3]                                       */
+    const float *gt_boxes;    /* [n][4]                                       */
+    const float *clamp;       /* [n][2]  im_sizes[i] handed to get_bube_corners */
+    const int32_t *img_off;   /* [n_images+1]                                 */
+    const WcrImage *images;   /* [n_images] depth maps (z_pseudo_gt_center)   */
+    const float *normals;     /* [n_images][3] from wcr_ransac_ground         */
+    const float *ground_conf; /* [n_images] 0.1 for the (1,1) dummy else 1 (roi_heads.py:988) */
+    /* forward outputs / backward inputs */
+    float   *losses;          /* [8] scalars, already times w_term * w_3d     */
+    int32_t *present;         /* [8] 0 where the reference would not emit the key (None) */
+    float   *terms;           /* [7][n] raw per-box terms before uncertainty scaling,
+                                 row t-1 for term t (row WCR_T_POSE-1 holds the broadcast scalar) */
+    float   *R_ego;           /* [n][9] egocentric pose after R_from_allocentric */
+    float   *proj;            /* [n][4] projected boxes                        */
+    float   *stats;           /* [16]  n_valid per term (8), pose scalar, fail count ... */
+    float   *img_pose;        /* [n_images] per-image pose term (workspace)    */
+    /* backward only */
+    const float *grad_losses; /* [8] upstream gradient of each scalar          */
+    float *d_deltas, *d_z_raw, *d_dims_raw, *d_pose, *d_uncert;  /* same shapes as inputs */
+    float *d_R_pose;          /* [n][9] workspace                              */
+} WcrLossIO;
+
+int wcr_weak_loss_fwd(const WcrLossIO *h_io, const WcrLossParams *h_params, void *stream);
+int wcr_weak_loss_bwd(const WcrLossIO *h_io, const WcrLossParams *h_params, void *stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -1,0 +1,116 @@
+"""Generate tests/golden/*.npz by executing the REFERENCE's own code (read-only at
+/root/reference, imported through oracle/refshim.py) on seeded synthetic inputs.
+
+    python tests/golden/make_golden.py
+
+Authoring container only. The fixtures are committed; the GPU box and the CPU test
+suite read them without touching /root/reference. Inputs are stored in the files
+so that the tests feed bit-identical data to the oracle and to the CUDA path.
+"""
+import os
+import random
+import sys
+
+import numpy as np
+import torch
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+ROOT = os.path.dirname(os.path.dirname(HERE))
+for p in (ROOT, os.path.join(ROOT, "weak-cube-r-cnn_b200")):
+    if p not in sys.path:
+        sys.path.insert(0, p)
+
+from oracle import refshim, standins, loss as ol, loss_inputs as li, ref_loss  # noqa: E402
+from tests.golden.golden_io import save_loss_case  # noqa: E402
+
+
+def golden_ground():
+    """normal_vector_from_maps + Plane_torch.fit_parallel (roi_heads.py:466-528,
+    plane.py:79-134) with Python's random seeded: stores the drawn triples too."""
+    from wcr import synth
+    ns = refshim.load()
+    head = refshim.roi_head_instance()
+    for case, (H, W, seeds) in enumerate([(120, 160, (0, 1, 2)), (150, 210, (5, 6))]):
+        ims = [synth.make_image(s, H, W, n_boxes=2, dummy_ground=(i == 1)) for i, s in enumerate(seeds)]
+        for im in ims:
+            im["K"][0, 0] *= 1.013
+            im["K"][1, 1] *= 0.987
+        depth = standins.ImageList.from_tensors([im["depth"] for im in ims])
+        ground = standins.ImageList([None] * len(ims), [tuple(im["ground"].shape) for im in ims])
+        gt = [im["ground"] for im in ims]
+        ground.__class__ = type("IL", (standins.ImageList,), {
+            "__getitem__": lambda self, i: gt[i], "device": property(lambda self: torch.device("cpu"))})
+        Ks = [im["K"] for im in ims]
+        # replay the draws: same seed, same order as plane.py:95
+        random.seed(100 + case)
+        normals = head.normal_vector_from_maps(ground, depth, Ks)
+        random.seed(100 + case)
+        ids, pts_all, eqs, inls = [], [], [], []
+        from oracle import ground as og
+        for im in ims:
+            g = None if tuple(im["ground"].shape) == (1, 1) else im["ground"].numpy()
+            pts, _ = og.unproject_ground_frame(im["depth"].numpy(), g, im["K"].numpy(), 5)
+            state = random.getstate()
+            eq, inl = ns.plane.Plane_torch().fit_parallel(torch.from_numpy(pts), thresh=0.05, maxIteration=1000)
+            random.setstate(state)
+            ids.append(og.draw_id_samples(len(pts), 1000, random))
+            pts_all.append(pts); eqs.append(eq.numpy()); inls.append(inl.numpy())
+        d = {"H": H, "W": W, "normals": normals.numpy()}
+        for i, im in enumerate(ims):
+            d[f"depth{i}"] = im["depth"].numpy(); d[f"ground{i}"] = im["ground"].numpy()
+            d[f"K{i}"] = im["K"].numpy(); d[f"ids{i}"] = ids[i].astype(np.int32)
+            d[f"pts{i}"] = pts_all[i]; d[f"eq{i}"] = eqs[i]; d[f"inl{i}"] = inls[i]
+        d["n"] = len(ims)
+        np.savez_compressed(os.path.join(HERE, f"ground_{case}.npz"), **d)
+        print("ground", case, normals.numpy())
+
+
+def golden_cubes():
+    """Block-level outputs of the reference: orthobasis_from_normal_t, Cubes.get_all_corners,
+    get_bube_corners, cubes_to_box, iou_2d (utils.py:119-187, spaces.py:192-245,
+    conversions.py:25-48)."""
+    ns = refshim.load()
+    g = torch.Generator().manual_seed(11)
+    I, Pn = 3, 40
+    normal = torch.nn.functional.normalize(torch.tensor([0.03, 0.99, -0.05]), dim=0)
+    yaw = torch.rand(Pn, generator=g) * np.pi
+    R = ns.utils.orthobasis_from_normal_t(normal, yaw)
+    R0 = ns.utils.orthobasis_from_normal_t(torch.tensor([0.0, 1.0, 0.0]), yaw)   # a == 0 branch
+    cubes = torch.zeros(I, Pn, 15)
+    cubes[:, :, 0:2] = torch.randn(I, Pn, 2, generator=g) * 0.8
+    cubes[:, :, 2] = 1.0 + 4 * torch.rand(I, Pn, generator=g)
+    cubes[:, :, 3:6] = 0.2 + 1.5 * torch.rand(I, Pn, 3, generator=g)
+    cubes[:, :, 6:] = R.reshape(Pn, 9)
+    cubes[0, 0, 2] = 0.3                       # close to the camera: clamp bounds hit
+    K = torch.tensor([[525.0, 0, 320], [0, 525, 240], [0, 0, 1]])
+    C = ns.spaces.Cubes(cubes)
+    corners3d = C.get_all_corners()
+    bube = C.get_bube_corners(K, [480, 640])
+    boxes = torch.stack([b.tensor for b in ns.conversions.cubes_to_box(C, K, [480, 640])])
+    gt = torch.tensor([[200.0, 150, 420, 380], [10, 10, 100, 90], [300, 200, 640, 480]])
+    ious = torch.stack([ns.utils.iou_2d(standins.Boxes(gt[i:i + 1]), standins.Boxes(boxes[i])) for i in range(I)])
+    np.savez_compressed(os.path.join(HERE, "cubes_0.npz"), normal=normal.numpy(), yaw=yaw.numpy(),
+                        R=R.numpy(), R0=R0.numpy(), cubes=cubes.numpy(), K=K.numpy(),
+                        corners3d=corners3d.numpy(), bube=bube.numpy(), boxes=boxes.numpy(),
+                        gt=gt.numpy(), ious=ious.numpy())
+    print("cubes", boxes.shape, float(ious.max()))
+
+
+def golden_loss():
+    cases = [(0, [3, 1, 5, 2], False, {}),
+             (1, [6, 2, 9], True, {"z_type": "sigmoid", "dims_priors_func": "sigmoid"}),
+             (2, [1, 1], False, {}),
+             (3, [12, 7, 20], False, {"z_type": "log", "use_confidence": 0.0})]
+    for idx, (seed, nb, big, cfg_kw) in enumerate(cases):
+        inp = li.make_loss_inputs(seed, nb, H=120, W=160, big=big)
+        inp["depth_maps"] = [d.half().float() for d in inp["depth_maps"]]   # stored as fp16
+        L, _, grads = li.run_with_grads(ref_loss.reference_weak_loss, ol.LossConfig(**cfg_kw), inp)
+        save_loss_case(os.path.join(HERE, f"loss_{idx}.npz"), cfg_kw, inp, L, grads)
+        print("loss", idx, {k: round(float(v), 5) for k, v in L.items()})
+
+
+if __name__ == "__main__":
+    assert refshim.available(), "needs /root/reference"
+    golden_ground()
+    golden_cubes()
+    golden_loss()

@@ -1,0 +1,126 @@
+"""Step 4 parity on the GPU: fused weak-loss forward/backward through the C ABI vs
+oracle/loss.py (torch fp32 + autograd; pinned to the reference's own functions by
+tests/test_oracle_loss.py) and vs tests/golden/loss_*.npz (values and autograd
+gradients produced by the reference's code, tests/golden/make_golden.py).
+
+Tolerances (north_star): losses 1e-5 relative, gradients 1e-4 relative (relative to
+the largest gradient magnitude of the tensor, plus the same relative bound
+element-wise where the element is not tiny)."""
+import glob
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import loss as ol, loss_inputs as li
+
+pytestmark = pytest.mark.gpu
+LOSS_RTOL, GRAD_RTOL = 1e-5, 1e-4
+GOLDEN = os.path.join(os.path.dirname(__file__), "golden")
+
+
+def _run_gpu(cfg_kw, inp, upstream=None):
+    from wcr.roi_heads import WeakLossConfig, weak_loss
+    cfg = WeakLossConfig(**cfg_kw)
+    leaves = {k: inp[k].cuda().requires_grad_(True) for k in li.GRAD_KEYS}
+    rest = {k: (v.cuda() if isinstance(v, torch.Tensor) else v) for k, v in inp.items()
+            if k not in li.GRAD_KEYS and k != "depth_maps"}
+    rest["depth_maps"] = [d.cuda() for d in inp["depth_maps"]]
+    losses, per_box = weak_loss(cfg, **leaves, **rest, return_per_box=True)
+    if upstream is None:
+        total = sum(losses.values())
+    else:
+        total = sum(v * upstream[k] for k, v in losses.items())
+    total.backward()
+    grads = {k: (v.grad.cpu() if v.grad is not None else torch.zeros_like(inp[k])) for k, v in leaves.items()}
+    return {k: v.detach().cpu() for k, v in losses.items()}, per_box, grads
+
+
+def _check(La, ga, Lb, gb):
+    assert set(La) == set(Lb), (sorted(La), sorted(Lb))
+    for k in Lb:
+        a, b = float(La[k]), float(Lb[k])
+        if np.isnan(b):
+            assert np.isnan(a), k
+        else:
+            assert abs(a - b) <= LOSS_RTOL * max(abs(b), 1e-6), (k, a, b)
+    for k in gb:
+        a, b = ga[k].reshape(-1).double(), gb[k].reshape(-1).double()
+        scale = b.abs().max().item()
+        assert (a - b).abs().max().item() <= GRAD_RTOL * max(scale, 1e-12), (k, (a - b).abs().max().item(), scale)
+
+
+CFGS = [dict(), dict(z_type="sigmoid", dims_priors_func="sigmoid"),
+        dict(z_type="log", use_confidence=0.0),
+        dict(loss_functions=("iou", "dims")), dict(loss_functions=("pose_alignment", "pose_ground"))]
+
+
+@pytest.mark.parametrize("seed,nb,big", [(0, [3, 1, 5, 2], False), (2, [6, 2, 9], True),
+                                         (5, [40, 17, 1, 64, 3], False)])
+@pytest.mark.parametrize("ci", range(len(CFGS)))
+def test_weak_loss_matches_oracle(cuda_lib, seed, nb, big, ci):
+    inp = li.make_loss_inputs(seed, nb, big=big)
+    La, _, ga = _run_gpu(CFGS[ci], inp)
+    Lb, _, gb = li.run_with_grads(ol.weak_loss, ol.LossConfig(**CFGS[ci]), inp)
+    _check(La, ga, Lb, gb)
+
+
+def test_weak_loss_per_box_outputs(cuda_lib):
+    inp = li.make_loss_inputs(3, [4, 7, 2])
+    _, pg, _ = _run_gpu({}, inp)
+    _, po, _ = li.run_with_grads(ol.weak_loss, ol.LossConfig(), inp)
+    np.testing.assert_allclose(pg["proj"].cpu().numpy(), po["proj"].detach().numpy(), rtol=LOSS_RTOL, atol=1e-4)
+    np.testing.assert_allclose(pg["R"].cpu().numpy(), po["R"].detach().numpy(), rtol=0, atol=2e-6)
+    names = ["iou", "pose", "normal_vec", "pseudo_gt_z", "dims_w", "dims_h", "dims_l"]
+    for r, nme in enumerate(names):
+        np.testing.assert_allclose(pg["terms"][r].cpu().numpy(), po["raw_" + nme].numpy(), rtol=LOSS_RTOL, atol=1e-6)
+
+
+def test_weak_loss_weighted_upstream(cuda_lib):
+    """Non-uniform upstream gradients per loss key."""
+    inp = li.make_loss_inputs(7, [5, 3])
+    from wcr.roi_heads import TERM_KEYS
+    up = {k: 0.3 + 0.4 * i for i, k in enumerate(TERM_KEYS)}
+    La, _, ga = _run_gpu({}, inp, upstream=up)
+    leaves = {k: inp[k].clone().requires_grad_(True) for k in li.GRAD_KEYS}
+    rest = {k: v for k, v in inp.items() if k not in li.GRAD_KEYS}
+    Lb, _ = ol.weak_loss(ol.LossConfig(), **leaves, **rest)
+    sum(v * up[k] for k, v in Lb.items()).backward()
+    _check(La, ga, {k: v.detach() for k, v in Lb.items()}, {k: v.grad for k, v in leaves.items()})
+
+
+def test_weak_loss_none_and_degenerate(cuda_lib):
+    # every image has one box -> the reference returns None for the pose term
+    inp = li.make_loss_inputs(1, [1, 1, 1])
+    La, _, ga = _run_gpu({}, inp)
+    Lb, _, gb = li.run_with_grads(ol.weak_loss, ol.LossConfig(), inp)
+    assert "Cube/loss_pose" not in La and "Cube/loss_pose" not in Lb
+    _check(La, ga, Lb, gb)
+    # NaN prior std -> dim_loss returns (None, None, None)
+    inp = li.make_loss_inputs(4, [3, 2])
+    inp["prior_std"][1, 2] = float("nan")
+    La, _, ga = _run_gpu({}, inp)
+    Lb, _, gb = li.run_with_grads(ol.weak_loss, ol.LossConfig(), inp)
+    assert "Cube/loss_dims_w" not in La
+    _check(La, ga, Lb, gb)
+    # a cube behind the camera / huge deltas: projections hit the clamp bounds
+    inp = li.make_loss_inputs(6, [4, 4])
+    inp["deltas"][0] = torch.tensor([30.0, -30.0])
+    inp["z_raw"][1] = 0.05
+    La, _, ga = _run_gpu({}, inp)
+    Lb, _, gb = li.run_with_grads(ol.weak_loss, ol.LossConfig(), inp)
+    _check(La, ga, Lb, gb)
+    # CPU tensors: no fallback
+    from wcr.roi_heads import WeakLossConfig, weak_loss
+    with pytest.raises(Exception):
+        weak_loss(WeakLossConfig(), **{k: v for k, v in inp.items()})
+
+
+@pytest.mark.parametrize("path", sorted(glob.glob(os.path.join(GOLDEN, "loss_*.npz"))))
+def test_weak_loss_matches_reference_golden(cuda_lib, path):
+    """Values and gradients the REFERENCE's own code produced (committed fixtures)."""
+    from tests.golden.golden_io import load_loss_case
+    cfg_kw, inp, L_ref, g_ref = load_loss_case(path)
+    La, _, ga = _run_gpu(cfg_kw, inp)
+    _check(La, ga, L_ref, g_ref)

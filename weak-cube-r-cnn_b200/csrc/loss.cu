@@ -1,0 +1,605 @@
+// loss.cu -- fused weak-loss forward / backward (north_star step 4, SURVEY A4.1-A4.9,
+// A4.11). Reference: cubercnn/modeling/roi_heads/roi_heads.py:786-1144 and the
+// helpers cited in include/wcr.h.
+//
+// The reference issues O(n) tiny kernels from Python loops (one cubes_to_box call per
+// box, an O(n_i^2) CPU pair loop for the pose term); here:
+//   forward : box kernel (decode -> cube -> 8 corners -> projection -> clamp -> min/max
+//             -> GIoU, pseudo-depth L1, ground-normal cosine, dims hinge)
+//             + pair kernel (one CTA per image) + one reduction CTA
+//   backward: pair kernel + box kernel with the hand-derived chain rule, following
+//             autograd's sub-gradient choices (first arg-extremum over corners,
+//             closed-interval clamp, tie-splitting binary min/max, sign(0) = 0).
+// Latency-bound by nature (n <= a few thousand boxes): no roofline claim.
+#include "cube_math.cuh"
+
+namespace wcr {
+
+// decoded state of one box (roi_heads.py:786-905, 927-931)
+struct Decoded {
+    float cube_x, cube_y, sw, sh;
+    float zf;          // z after z_type, before virtual_to_real
+    float z;           // cube_z
+    float dims[3];     // w h l
+    float M[9];        // allocentric -> egocentric rotation (constant in backward)
+    bool  validM;      // angle > 0
+    float R[9];        // egocentric pose
+    float cube[15];
+    Intr K;
+};
+
+// pytorch3d axis_angle_to_matrix (quaternion route), math_util.py:827
+__device__ __forceinline__ void axis_angle_to_matrix(float ax, float ay, float az, float M[9])
+{
+    const float angles = sqrtf((ax * ax + ay * ay) + az * az);
+    const float half = angles * 0.5f;
+    const float s = (fabsf(angles) < 1e-6f) ? 0.5f - (angles * angles) / 48.f : sinf(half) / angles;
+    const float r = cosf(half), i = ax * s, j = ay * s, k = az * s;
+    const float two_s = 2.0f / (((r * r + i * i) + j * j) + k * k);
+    M[0] = 1.f - two_s * (j * j + k * k); M[1] = two_s * (i * j - k * r); M[2] = two_s * (i * k + j * r);
+    M[3] = two_s * (i * j + k * r); M[4] = 1.f - two_s * (i * i + k * k); M[5] = two_s * (j * k - i * r);
+    M[6] = two_s * (i * k - j * r); M[7] = two_s * (j * k + i * r); M[8] = 1.f - two_s * (i * i + j * j);
+}
+
+__device__ __forceinline__ float sigmoidf_(float x) { return 1.f / (1.f + expf(-x)); }
+
+__device__ __forceinline__ Decoded decode_box(const WcrLossIO &io, const WcrLossParams &P, int i)
+{
+    Decoded d;
+    const float *sb = io.src_boxes + 4 * i;
+    const float *k4 = io.K4 + 4 * i;
+    d.K.fx = k4[0]; d.K.fy = k4[1]; d.K.cx = k4[2]; d.K.cy = k4[3];
+    d.sw = sb[2] - sb[0]; d.sh = sb[3] - sb[1];
+    const float scx = sb[0] + 0.5f * d.sw, scy = sb[1] + 0.5f * d.sh;
+    d.cube_x = scx + d.sw * io.deltas[2 * i];        // roi_heads.py:843
+    d.cube_y = scy + d.sh * io.deltas[2 * i + 1];    // :844
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+        const float raw = io.dims_raw[3 * i + k], pm = io.prior_mean[3 * i + k];
+        if (P.dims_func == 1) {                      // scaled_sigmoid, :856-859
+            const float ps = io.prior_std[3 * i + k];
+            const float dmin = fmaxf(pm - 3.f * ps, 0.f), dmax = pm + 3.f * ps;
+            d.dims[k] = dmin + (dmax - dmin) * sigmoidf_(raw);
+        } else {
+            d.dims[k] = expf(fminf(raw, 5.f)) * pm;  // :861
+        }
+    }
+    // R_from_allocentric (math_util.py:802-830)
+    {
+        float ox = (d.cube_x - d.K.cx) / d.K.fx, oy = (d.cube_y - d.K.cy) / d.K.fy, oz = 1.f;
+        const float nrm = sqrtf((ox * ox + oy * oy) + oz * oz);
+        ox /= nrm; oy /= nrm; oz /= nrm;
+        const float angle = acosf(oz);
+        const float axx = 0.f - oy, axy = 0.f + ox;
+        const float norms = sqrtf((axx * axx + axy * axy) + 0.f);
+        d.validM = angle > 0.f;
+        const float *Rv = io.pose + 9 * i;
+        if (d.validM) {
+            axis_angle_to_matrix(angle * axx / norms, angle * axy / norms, angle * 0.f / norms, d.M);
+#pragma unroll
+            for (int r = 0; r < 3; ++r)
+#pragma unroll
+                for (int c = 0; c < 3; ++c)
+                    d.R[3 * r + c] = fmaf(d.M[3 * r + 2], Rv[6 + c],
+                                          fmaf(d.M[3 * r + 1], Rv[3 + c], d.M[3 * r] * Rv[c]));
+        } else {
+#pragma unroll
+            for (int t = 0; t < 9; ++t) { d.R[t] = Rv[t]; d.M[t] = (t % 4 == 0) ? 1.f : 0.f; }
+        }
+    }
+    const float zr = io.z_raw[i];
+    d.zf = P.z_type == 1 ? sigmoidf_(zr) * 100.f : (P.z_type == 2 ? expf(zr) : zr);  // :874-880
+    d.z = d.zf * io.v2r[i];                                                          // :904-905
+    d.cube[0] = d.z * (d.cube_x - d.K.cx) / d.K.fx;   // :927
+    d.cube[1] = d.z * (d.cube_y - d.K.cy) / d.K.fy;   // :928
+    d.cube[2] = d.z;
+    d.cube[3] = d.dims[0]; d.cube[4] = d.dims[1]; d.cube[5] = d.dims[2];
+#pragma unroll
+    for (int t = 0; t < 9; ++t) d.cube[6 + t] = d.R[t];
+    return d;
+}
+
+// torchvision generalized_box_iou_loss(boxes1 = gt, boxes2 = proj); optionally the
+// gradient w.r.t. proj (x1g y1g x2g y2g).
+__device__ __forceinline__ float giou_loss(const float *g, const float *p, float *dp)
+{
+    const float eps = 1e-7f;
+    const float x1 = g[0], y1 = g[1], x2 = g[2], y2 = g[3];
+    const float x1g = p[0], y1g = p[1], x2g = p[2], y2g = p[3];
+    const float xk1 = fmaxf(x1, x1g), yk1 = fmaxf(y1, y1g), xk2 = fminf(x2, x2g), yk2 = fminf(y2, y2g);
+    const bool nanb = (x1g != x1g) || (y1g != y1g) || (x2g != x2g) || (y2g != y2g);
+    const bool mask = !nanb && (yk2 > yk1) && (xk2 > xk1);
+    const float I = mask ? (xk2 - xk1) * (yk2 - yk1) : 0.f;
+    const float A2 = (x2g - x1g) * (y2g - y1g);
+    const float U = ((x2 - x1) * (y2 - y1) + A2) - I;
+    const float iou = I / (U + eps);
+    const float xc1 = fminf(x1, x1g), yc1 = fminf(y1, y1g), xc2 = fmaxf(x2, x2g), yc2 = fmaxf(y2, y2g);
+    const float C = (xc2 - xc1) * (yc2 - yc1);
+    float loss = 1.f - (iou - ((C - U) / (C + eps)));
+    if (nanb) loss = nanf_();
+    if (dp) {
+        const float Ue = U + eps, Ce = C + eps;
+        const float gI = -(1.f / Ue + I / (Ue * Ue)) + 1.f / Ce;
+        const float gA2 = I / (Ue * Ue) - 1.f / Ce;
+        const float gC = Ue / (Ce * Ce);
+        // binary max/min backward: the larger (smaller) operand takes it, ties split in half
+        auto w_max = [](float other, float self) { return self > other ? 1.f : (self == other ? 0.5f : 0.f); };
+        auto w_min = [](float other, float self) { return self < other ? 1.f : (self == other ? 0.5f : 0.f); };
+        const float iw = xk2 - xk1, ih = yk2 - yk1;
+        const float gI_ = mask ? gI : 0.f;
+        dp[0] = gI_ * (-ih) * w_max(x1, x1g) + gA2 * (-(y2g - y1g)) + gC * (-(yc2 - yc1)) * w_min(x1, x1g);
+        dp[1] = gI_ * (-iw) * w_max(y1, y1g) + gA2 * (-(x2g - x1g)) + gC * (-(xc2 - xc1)) * w_min(y1, y1g);
+        dp[2] = gI_ * (ih) * w_min(x2, x2g) + gA2 * (y2g - y1g) + gC * (yc2 - yc1) * w_max(x2, x2g);
+        dp[3] = gI_ * (iw) * w_min(y2, y2g) + gA2 * (x2g - x1g) + gC * (xc2 - xc1) * w_max(y2, y2g);
+    }
+    return loss;
+}
+
+// depth[(long) clamp(y,10,h-11)][(long) clamp(x,10,w-11)]  (roi_heads.py:645-652)
+__device__ __forceinline__ float depth_at(const WcrImage &im, float x, float y)
+{
+    x = clamp_keep_nan(x, 10.f, (float)(im.W - 11));
+    y = clamp_keep_nan(y, 10.f, (float)(im.H - 11));
+    return im.depth[(size_t)(int)y * im.depth_pitch + (int)x];
+}
+
+__device__ __forceinline__ int image_of(const int32_t *off, int n_images, int i)
+{
+    int lo = 0, hi = n_images;  // off[lo] <= i < off[hi]
+    while (hi - lo > 1) {
+        const int mid = (lo + hi) >> 1;
+        if (off[mid] <= i) lo = mid; else hi = mid;
+    }
+    return lo;
+}
+
+__device__ __forceinline__ float sgn(float x) { return x > 0.f ? 1.f : (x < 0.f ? -1.f : 0.f); }
+
+// F.cosine_similarity(n, p): x / max(||x||, eps) each, then dot.
+__device__ __forceinline__ float cos_sim3(const float *a, const float *b, float *an, float *bn,
+                                          float *bnorm)
+{
+    const float na = fmaxf(sqrtf((a[0] * a[0] + a[1] * a[1]) + a[2] * a[2]), 1e-8f);
+    const float nb = fmaxf(sqrtf((b[0] * b[0] + b[1] * b[1]) + b[2] * b[2]), 1e-8f);
+#pragma unroll
+    for (int k = 0; k < 3; ++k) { an[k] = a[k] / na; bn[k] = b[k] / nb; }
+    *bnorm = nb;
+    return (an[0] * bn[0] + an[1] * bn[1]) + an[2] * bn[2];
+}
+
+constexpr int LT = WCR_LOSS_TERMS - 1;  // per-box term rows (uncert is not one)
+
+// ---------------------------------------------------------------- forward --
+__global__ void __launch_bounds__(128)
+loss_box_fwd_kernel(const WcrLossIO io, const WcrLossParams P)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= io.n) return;
+    const Decoded d = decode_box(io, P, i);
+    float lo0, hi0, lo1, hi1;
+    clamp_bounds(io.clamp[2 * i], lo0, hi0);
+    clamp_bounds(io.clamp[2 * i + 1], lo1, hi1);
+    const ProjBox pb = project_cube(d.cube, d.K, lo0, hi0, lo1, hi1, nullptr);
+    const float proj[4] = {pb.x1, pb.y1, pb.x2, pb.y2};
+#pragma unroll
+    for (int t = 0; t < 4; ++t) io.proj[4 * i + t] = proj[t];
+#pragma unroll
+    for (int t = 0; t < 9; ++t) io.R_ego[9 * i + t] = d.R[t];
+    const float q = nanf_();
+    float term[LT];
+#pragma unroll
+    for (int t = 0; t < LT; ++t) term[t] = q;
+    if (P.loss_flags & WCR_LOSS_IOU) term[WCR_T_IOU - 1] = giou_loss(io.gt_boxes + 4 * i, proj, nullptr);
+    const int img = image_of(io.img_off, io.n_images, i);
+    if (P.loss_flags & WCR_LOSS_POSE_GROUND) {
+        float an[3], bn[3], nb;
+        const float c = cos_sim3(io.normals + 3 * img, d.R + 3, an, bn, &nb);   // row 1 of R (:992)
+        term[WCR_T_NORMAL - 1] = (1.f - fabsf(c)) * io.ground_conf[img];
+    }
+    if (P.loss_flags & WCR_LOSS_Z_CENTER)
+        term[WCR_T_PSEUDO_Z - 1] = fabsf(d.z - depth_at(io.images[img], d.cube_x, d.cube_y));
+    if (P.loss_flags & WCR_LOSS_DIMS) {
+#pragma unroll
+        for (int k = 0; k < 3; ++k) {
+            const float s = fabsf(d.dims[k] - io.prior_mean[3 * i + k]) / io.prior_std[3 * i + k];
+            term[WCR_T_DIMS_W - 1 + k] = fmaxf(s - 1.0f, 0.f);
+            if (s != s) term[WCR_T_DIMS_W - 1 + k] = s;  // torch.max propagates NaN
+        }
+    }
+#pragma unroll
+    for (int t = 0; t < LT; ++t) io.terms[(size_t)t * io.n + i] = term[t];
+}
+
+// block-wide sum of (a, b) over 256 threads, result valid in every thread
+__device__ __forceinline__ void block_sum2(float &a, float &b, float *s_a, float *s_b)
+{
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5, nw = blockDim.x >> 5;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        a += __shfl_xor_sync(0xffffffffu, a, o);
+        b += __shfl_xor_sync(0xffffffffu, b, o);
+    }
+    __syncthreads();
+    if (lane == 0) { s_a[wid] = a; s_b[wid] = b; }
+    __syncthreads();
+    a = 0.f; b = 0.f;
+    for (int w = 0; w < nw; ++w) { a += s_a[w]; b += s_b[w]; }
+}
+
+// cos of the relative angle of two poses: (tr(Ri Rj^T) - 1) / 2  (math_util.py:1179, 1222-1226)
+__device__ __forceinline__ float pair_cos(const float *Ri, const float *Rj)
+{
+    const float d0 = fmaf(Ri[2], Rj[2], fmaf(Ri[1], Rj[1], Ri[0] * Rj[0]));
+    const float d1 = fmaf(Ri[5], Rj[5], fmaf(Ri[4], Rj[4], Ri[3] * Rj[3]));
+    const float d2 = fmaf(Ri[8], Rj[8], fmaf(Ri[7], Rj[7], Ri[6] * Rj[6]));
+    return (((d0 + d1) + d2) - 1.0f) * 0.5f;
+}
+
+// One CTA per image: mean over pairs (i > j) of 1 - |cos|  (roi_heads.py:453-460).
+__global__ void __launch_bounds__(256) loss_pose_fwd_kernel(const WcrLossIO io)
+{
+    __shared__ float s_a[8], s_b[8];
+    const int im = blockIdx.x;
+    const int b0 = io.img_off[im], ni = io.img_off[im + 1] - b0;
+    float sum = 0.f, dummy = 0.f;
+    for (int i = 1 + threadIdx.x; i < ni; i += blockDim.x) {
+        float Ri[9];
+#pragma unroll
+        for (int t = 0; t < 9; ++t) Ri[t] = io.R_ego[9 * (size_t)(b0 + i) + t];
+        for (int j = 0; j < i; ++j) sum += 1.f - fabsf(pair_cos(Ri, io.R_ego + 9 * (size_t)(b0 + j)));
+    }
+    block_sum2(sum, dummy, s_a, s_b);
+    if (threadIdx.x == 0) {
+        const float npairs = 0.5f * (float)ni * (float)(ni - 1);
+        io.img_pose[im] = ni == 0 ? nanf_() : (ni == 1 ? 0.f : sum / npairs);
+    }
+}
+
+__device__ __forceinline__ float term_weight(const WcrLossParams &P, int t)
+{
+    switch (t) {
+    case WCR_T_UNCERT: return P.use_confidence;
+    case WCR_T_IOU: return P.w_iou * P.w_3d;
+    case WCR_T_POSE: return P.w_pose * P.w_3d;
+    case WCR_T_NORMAL: return P.w_normal * P.w_3d;
+    case WCR_T_PSEUDO_Z: return P.w_z * P.w_3d;
+    default: return P.w_dims * P.w_3d;
+    }
+}
+
+__device__ __forceinline__ bool term_enabled(const WcrLossParams &P, int t)
+{
+    switch (t) {
+    case WCR_T_UNCERT: return P.use_confidence > 0.f;
+    case WCR_T_IOU: return P.loss_flags & WCR_LOSS_IOU;
+    case WCR_T_POSE: return P.loss_flags & WCR_LOSS_POSE_ALIGN;
+    case WCR_T_NORMAL: return P.loss_flags & WCR_LOSS_POSE_GROUND;
+    case WCR_T_PSEUDO_Z: return P.loss_flags & WCR_LOSS_Z_CENTER;
+    default: return P.loss_flags & WCR_LOSS_DIMS;
+    }
+}
+
+__device__ __forceinline__ bool finitef_(float x) { return fabsf(x) <= 3.402823466e38f; }
+
+// uncertainty scale (roi_heads.py:1077): sqrt(2) * exp(-u), or 1 when confidence is off
+__device__ __forceinline__ float uncert_sf(const WcrLossIO &io, const WcrLossParams &P, int i)
+{
+    return P.use_confidence > 0.f ? 1.41421356f * expf(-io.uncert[i]) : 1.f;
+}
+
+// One CTA: pose scalar, safe means (roi_heads.py:1307-1315), weights.
+__global__ void __launch_bounds__(256)
+loss_reduce_kernel(const WcrLossIO io, const WcrLossParams P)
+{
+    __shared__ float s_a[8], s_b[8];
+    __shared__ float s_pose;
+    const int tid = threadIdx.x;
+    // pose scalar: sum over images with != 1 boxes, / (fail + 1)   (:451-464)
+    float psum = 0.f, fail = 0.f;
+    for (int im = tid; im < io.n_images; im += blockDim.x) {
+        const int ni = io.img_off[im + 1] - io.img_off[im];
+        if (ni == 1) fail += 1.f; else psum += io.img_pose[im];
+    }
+    block_sum2(psum, fail, s_a, s_b);
+    const bool pose_present = (P.loss_flags & WCR_LOSS_POSE_ALIGN) && ((int)fail != io.n_images);
+    if (tid == 0) s_pose = psum * 1.f / (fail + 1.f);
+    __syncthreads();
+    const float pose = s_pose;
+    if (P.loss_flags & WCR_LOSS_POSE_ALIGN)
+        for (int i = tid; i < io.n; i += blockDim.x) io.terms[(size_t)(WCR_T_POSE - 1) * io.n + i] = pose;
+    // dim_loss returns None when any prior std is NaN (:620-623)
+    float nan_std = 0.f, dummy = 0.f;
+    if (P.loss_flags & WCR_LOSS_DIMS)
+        for (int i = tid; i < 3 * io.n; i += blockDim.x) nan_std += (io.prior_std[i] != io.prior_std[i]) ? 1.f : 0.f;
+    block_sum2(nan_std, dummy, s_a, s_b);
+    __syncthreads();
+    for (int t = 0; t < WCR_LOSS_TERMS; ++t) {
+        float sum = 0.f, cnt = 0.f;
+        bool present = term_enabled(P, t);
+        if (t == WCR_T_POSE) present = pose_present;
+        if (t >= WCR_T_DIMS_W) present = present && nan_std == 0.f;
+        if (present) {
+            for (int i = tid; i < io.n; i += blockDim.x) {
+                const float v = t == WCR_T_UNCERT ? io.uncert[i]
+                                                  : io.terms[(size_t)(t - 1) * io.n + i] * uncert_sf(io, P, i);
+                if (finitef_(v)) { sum += v; cnt += 1.f; }
+            }
+        }
+        block_sum2(sum, cnt, s_a, s_b);
+        if (tid == 0) {
+            io.present[t] = present ? 1 : 0;
+            io.stats[t] = cnt;
+            io.losses[t] = !present ? 0.f : (cnt > 0.f ? (sum / cnt) * term_weight(P, t) : nanf_());
+        }
+        __syncthreads();
+    }
+    if (tid == 0) { io.stats[8] = pose; io.stats[9] = fail; }
+}
+
+// --------------------------------------------------------------- backward --
+// upstream coefficient of the per-box scaled loss l_{t,i} = raw_{t,i} * sf_i:
+//   d(total)/d(l_{t,i}) = g_t * w_t * [l finite] / n_valid_t      (safe mean, :1307-1315)
+__device__ __forceinline__ float term_coef(const WcrLossIO &io, const WcrLossParams &P, int t, float l)
+{
+    if (!io.present[t] || !finitef_(l)) return 0.f;
+    const float nv = io.stats[t];
+    return nv > 0.f ? io.grad_losses[t] * term_weight(P, t) / nv : 0.f;
+}
+
+// One CTA per image: d(total)/d(R_ego) from the pose-alignment term.
+//   P = sum_im L_im / (fail+1), L_im = mean_{i>j}(1 - |cos_ij|), cos_ij = (R_i : R_j - 1)/2
+__global__ void __launch_bounds__(128)
+loss_pose_bwd_kernel(const WcrLossIO io, const WcrLossParams P)
+{
+    __shared__ float s_a[8], s_b[8];
+    const int im = blockIdx.x;
+    const int b0 = io.img_off[im], ni = io.img_off[im + 1] - b0;
+    // dP = sum_i coef_i * sf_i  (raw pose term of every box is the same scalar P)
+    const float pose = io.stats[8];
+    float dP = 0.f, dummy = 0.f;
+    for (int i = threadIdx.x; i < io.n; i += blockDim.x) {
+        const float sf = uncert_sf(io, P, i);
+        dP += term_coef(io, P, WCR_T_POSE, pose * sf) * sf;
+    }
+    block_sum2(dP, dummy, s_a, s_b);
+    const float npairs = 0.5f * (float)ni * (float)(ni - 1);
+    const float scale = ni > 1 ? dP / (npairs * (io.stats[9] + 1.f)) : 0.f;
+    for (int i = threadIdx.x; i < ni; i += blockDim.x) {
+        float Ri[9], g[9];
+#pragma unroll
+        for (int t = 0; t < 9; ++t) { Ri[t] = io.R_ego[9 * (size_t)(b0 + i) + t]; g[t] = 0.f; }
+        for (int j = 0; j < ni; ++j) {
+            if (j == i) continue;
+            const float *Rj = io.R_ego + 9 * (size_t)(b0 + j);
+            const float c = pair_cos(Ri, Rj);
+            const float dc = -sgn(c) * scale * 0.5f;   // d(1-|cos|)/dcos * d cos/d(R_i:R_j)
+#pragma unroll
+            for (int t = 0; t < 9; ++t) g[t] += dc * Rj[t];
+        }
+#pragma unroll
+        for (int t = 0; t < 9; ++t) io.d_R_pose[9 * (size_t)(b0 + i) + t] = g[t];
+    }
+}
+
+__global__ void __launch_bounds__(128)
+loss_box_bwd_kernel(const WcrLossIO io, const WcrLossParams P)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= io.n) return;
+    const Decoded d = decode_box(io, P, i);
+    const int img = image_of(io.img_off, io.n_images, i);
+    const float sf = uncert_sf(io, P, i);
+    float du = 0.f;                       // d/d uncert
+    float dz = 0.f, dcx = 0.f, dcy = 0.f; // d/d cube_z, cube_x, cube_y
+    float ddims[3] = {0.f, 0.f, 0.f};     // d/d (w, h, l)
+    float dR[9];
+#pragma unroll
+    for (int t = 0; t < 9; ++t) dR[t] = 0.f;
+    auto coef = [&](int t, float raw) {   // -> d/d raw, and accumulates d/d uncert
+        const float l = raw * sf;
+        const float c = term_coef(io, P, t, l);
+        if (c != 0.f && P.use_confidence > 0.f) du -= c * l;
+        return c * sf;
+    };
+
+    // ---- 'iou': GIoU -> projected box -> arg-extremum corners -> cube ------------
+    if ((P.loss_flags & WCR_LOSS_IOU) && io.present[WCR_T_IOU]) {
+        float lo0, hi0, lo1, hi1;
+        clamp_bounds(io.clamp[2 * i], lo0, hi0);
+        clamp_bounds(io.clamp[2 * i + 1], lo1, hi1);
+        const float hx = d.dims[2] / 2.f, hy = d.dims[1] / 2.f, hz = d.dims[0] / 2.f;
+        float X[8], Y[8], Z[8], px[8], py[8], cxs[8], cys[8];
+        int ix1 = 0, ix2 = 0, iy1 = 0, iy2 = 0;
+#pragma unroll
+        for (int c = 0; c < 8; ++c) {
+            float sx, sy, sz;
+            corner_signs(c, sx, sy, sz);
+            const float lx = sx * hx, ly = sy * hy, lz = sz * hz;
+            X[c] = fmaf(d.R[2], lz, fmaf(d.R[1], ly, d.R[0] * lx)) + d.cube[0];
+            Y[c] = fmaf(d.R[5], lz, fmaf(d.R[4], ly, d.R[3] * lx)) + d.cube[1];
+            Z[c] = fmaf(d.R[8], lz, fmaf(d.R[7], ly, d.R[6] * lx)) + d.cube[2];
+            px[c] = fmaf(d.K.cx, Z[c], d.K.fx * X[c]) / Z[c];
+            py[c] = fmaf(d.K.cy, Z[c], d.K.fy * Y[c]) / Z[c];
+            cxs[c] = clamp_keep_nan(px[c], lo0, hi0);
+            cys[c] = clamp_keep_nan(py[c], lo1, hi1);
+            if (c > 0) {   // strict comparisons keep the FIRST arg-extremum (torch.min/max over dim)
+                if (cxs[c] < cxs[ix1]) ix1 = c;
+                if (cxs[c] > cxs[ix2]) ix2 = c;
+                if (cys[c] < cys[iy1]) iy1 = c;
+                if (cys[c] > cys[iy2]) iy2 = c;
+            }
+        }
+        const float proj[4] = {cxs[ix1], cys[iy1], cxs[ix2], cys[iy2]};
+        float dproj[4];
+        const float raw = giou_loss(io.gt_boxes + 4 * i, proj, dproj);
+        const float g = coef(WCR_T_IOU, raw);
+        if (g != 0.f) {
+            const int sel[4] = {ix1, iy1, ix2, iy2};
+            float dl[3] = {0.f, 0.f, 0.f};   // d/d (lx, ly, lz) magnitudes hx hy hz, signed below
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+                const int c = sel[e];
+                const bool isx = (e == 0 || e == 2);
+                const float pv = isx ? px[c] : py[c];
+                const float lo = isx ? lo0 : lo1, hi = isx ? hi0 : hi1;
+                if (!(pv >= lo && pv <= hi)) continue;          // clamp backward: closed interval
+                const float gp = g * dproj[e];
+                // p = (f*A + c0*Z)/Z : dA = gp*f/Z ; dZ = gp*(c0/Z - num/Z^2)
+                const float f = isx ? d.K.fx : d.K.fy, c0 = isx ? d.K.cx : d.K.cy;
+                const float Av = isx ? X[c] : Y[c];
+                const float num = fmaf(c0, Z[c], f * Av);
+                const float dA = gp * f / Z[c];
+                const float dZ = gp * c0 / Z[c] - gp * num / (Z[c] * Z[c]);
+                float sx, sy, sz;
+                corner_signs(c, sx, sy, sz);
+                const float l[3] = {sx * hx, sy * hy, sz * hz};
+                const int ra = isx ? 0 : 1;                     // row of R feeding A
+                // corner = R l + centre
+                if (isx) dcx += 0.f;                             // (centre grads below)
+#pragma unroll
+                for (int k = 0; k < 3; ++k) {
+                    dR[3 * ra + k] += dA * l[k];
+                    dR[6 + k] += dZ * l[k];
+                    dl[k] += (d.R[3 * ra + k] * dA + d.R[6 + k] * dZ) * (k == 0 ? sx : (k == 1 ? sy : sz));
+                }
+                // centre: cube[0] or cube[1] gets dA, cube[2] gets dZ
+                const float zc = d.z;
+                if (isx) {   // x3d = z*(cube_x-cx)/fx
+                    dcx += dA * zc / d.K.fx;
+                    dz += dA * (d.cube_x - d.K.cx) / d.K.fx;
+                } else {
+                    dcy += dA * zc / d.K.fy;
+                    dz += dA * (d.cube_y - d.K.cy) / d.K.fy;
+                }
+                dz += dZ;
+            }
+            ddims[2] += 0.5f * dl[0];   // hx = l/2
+            ddims[1] += 0.5f * dl[1];   // hy = h/2
+            ddims[0] += 0.5f * dl[2];   // hz = w/2
+        }
+    }
+    // ---- 'pose_alignment' ---------------------------------------------------------
+    if ((P.loss_flags & WCR_LOSS_POSE_ALIGN) && io.present[WCR_T_POSE]) {
+        coef(WCR_T_POSE, io.stats[8]);   // only the uncertainty part; R part comes from the pair kernel
+#pragma unroll
+        for (int t = 0; t < 9; ++t) dR[t] += io.d_R_pose[9 * (size_t)i + t];
+    }
+    // ---- 'pose_ground' --------------------------------------------------------------
+    if ((P.loss_flags & WCR_LOSS_POSE_GROUND) && io.present[WCR_T_NORMAL]) {
+        float an[3], bn[3], nb;
+        const float c = cos_sim3(io.normals + 3 * img, d.R + 3, an, bn, &nb);
+        const float conf = io.ground_conf[img];
+        const float g = coef(WCR_T_NORMAL, (1.f - fabsf(c)) * conf);
+        if (g != 0.f) {
+            const float dc = -sgn(c) * conf * g;
+            // bn = p / ||p||: dp = (dbn - bn (bn . dbn)) / ||p||, dbn = dc * an
+            const float dot = dc * ((an[0] * bn[0] + an[1] * bn[1]) + an[2] * bn[2]);
+#pragma unroll
+            for (int k = 0; k < 3; ++k) dR[3 + k] += (dc * an[k] - bn[k] * dot) / nb;
+        }
+    }
+    // ---- 'z_pseudo_gt_center' ---------------------------------------------------------
+    if ((P.loss_flags & WCR_LOSS_Z_CENTER) && io.present[WCR_T_PSEUDO_Z]) {
+        const float diff = d.z - depth_at(io.images[img], d.cube_x, d.cube_y);
+        const float g = coef(WCR_T_PSEUDO_Z, fabsf(diff));
+        dz += g * sgn(diff);
+    }
+    // ---- 'dims' -------------------------------------------------------------------------
+    if ((P.loss_flags & WCR_LOSS_DIMS) && io.present[WCR_T_DIMS_W]) {
+#pragma unroll
+        for (int k = 0; k < 3; ++k) {
+            const float mu = io.prior_mean[3 * i + k], sd = io.prior_std[3 * i + k];
+            const float s = fabsf(d.dims[k] - mu) / sd - 1.0f;
+            const float g = coef(WCR_T_DIMS_W + k, fmaxf(s, 0.f));
+            const float w = s > 0.f ? 1.f : (s == 0.f ? 0.5f : 0.f);   // torch.max(a, zeros) tie rule
+            ddims[k] += g * w * sgn(d.dims[k] - mu) / sd;
+        }
+    }
+    // ---- 'uncert' term itself: use_confidence * safe_mean(u) -------------------------------
+    if (io.present[WCR_T_UNCERT]) du += term_coef(io, P, WCR_T_UNCERT, io.uncert[i]);
+
+    // ---- back through the decode ----------------------------------------------------------
+    io.d_uncert[i] = du;
+    io.d_deltas[2 * i] = dcx * d.sw;
+    io.d_deltas[2 * i + 1] = dcy * d.sh;
+    const float v2r = io.v2r[i];
+    float dzr = dz * v2r;
+    if (P.z_type == 1) { const float sg = d.zf / 100.f; dzr *= 100.f * sg * (1.f - sg); }
+    else if (P.z_type == 2) dzr *= d.zf;
+    io.d_z_raw[i] = dzr;
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+        const float raw = io.dims_raw[3 * i + k];
+        float g;
+        if (P.dims_func == 1) {
+            const float pm = io.prior_mean[3 * i + k], ps = io.prior_std[3 * i + k];
+            const float dmin = fmaxf(pm - 3.f * ps, 0.f), dmax = pm + 3.f * ps;
+            const float sg = sigmoidf_(raw);
+            g = ddims[k] * (dmax - dmin) * sg * (1.f - sg);
+        } else {
+            g = raw <= 5.f ? ddims[k] * d.dims[k] : 0.f;   // clip(max=5) passes gradient on x <= 5
+        }
+        io.d_dims_raw[3 * i + k] = g;
+    }
+    // R_ego = M R_view (where angle > 0) -> d R_view = M^T dR
+#pragma unroll
+    for (int r = 0; r < 3; ++r)
+#pragma unroll
+        for (int c = 0; c < 3; ++c)
+            io.d_pose[9 * i + 3 * r + c] = d.validM
+                ? (d.M[r] * dR[c] + d.M[3 + r] * dR[3 + c]) + d.M[6 + r] * dR[6 + c]
+                : dR[3 * r + c];
+}
+
+}  // namespace wcr
+
+static int check_io(const WcrLossIO *io, const WcrLossParams *p, bool bwd)
+{
+    WCR_REQUIRE(io && p, "wcr_weak_loss: null pointer");
+    WCR_REQUIRE(io->n >= 0 && io->n_images >= 1, "wcr_weak_loss: bad sizes");
+    WCR_REQUIRE(io->deltas && io->z_raw && io->dims_raw && io->pose && io->uncert && io->src_boxes &&
+                io->K4 && io->v2r && io->prior_mean && io->prior_std && io->gt_boxes && io->clamp &&
+                io->img_off && io->images && io->normals && io->ground_conf,
+                "wcr_weak_loss: null input pointer");
+    WCR_REQUIRE(io->losses && io->present && io->terms && io->R_ego && io->proj && io->stats &&
+                io->img_pose, "wcr_weak_loss: null output / workspace pointer");
+    if (bwd)
+        WCR_REQUIRE(io->grad_losses && io->d_deltas && io->d_z_raw && io->d_dims_raw && io->d_pose &&
+                    io->d_uncert && io->d_R_pose, "wcr_weak_loss_bwd: null gradient pointer");
+    WCR_REQUIRE(p->z_type >= 0 && p->z_type <= 2 && p->dims_func >= 0 && p->dims_func <= 1,
+                "wcr_weak_loss: unsupported z_type / dims_func");
+    return WCR_OK;
+}
+
+extern "C" int wcr_weak_loss_fwd(const WcrLossIO *h_io, const WcrLossParams *h_params, void *stream)
+{
+    WCR_CHECK_DEVICE();
+    int rc = check_io(h_io, h_params, false);
+    if (rc != WCR_OK) return rc;
+    cudaStream_t st = (cudaStream_t)stream;
+    if (h_io->n > 0) {
+        wcr::loss_box_fwd_kernel<<<(h_io->n + 127) / 128, 128, 0, st>>>(*h_io, *h_params);
+        WCR_CHECK_LAUNCH("loss_box_fwd_kernel");
+    }
+    wcr::loss_pose_fwd_kernel<<<h_io->n_images, 256, 0, st>>>(*h_io);
+    WCR_CHECK_LAUNCH("loss_pose_fwd_kernel");
+    wcr::loss_reduce_kernel<<<1, 256, 0, st>>>(*h_io, *h_params);
+    WCR_CHECK_LAUNCH("loss_reduce_kernel");
+    return WCR_OK;
+}
+
+extern "C" int wcr_weak_loss_bwd(const WcrLossIO *h_io, const WcrLossParams *h_params, void *stream)
+{
+    WCR_CHECK_DEVICE();
+    int rc = check_io(h_io, h_params, true);
+    if (rc != WCR_OK) return rc;
+    if (h_io->n == 0) return WCR_OK;
+    cudaStream_t st = (cudaStream_t)stream;
+    if (h_params->loss_flags & WCR_LOSS_POSE_ALIGN) {
+        wcr::loss_pose_bwd_kernel<<<h_io->n_images, 128, 0, st>>>(*h_io, *h_params);
+        WCR_CHECK_LAUNCH("loss_pose_bwd_kernel");
+    }
+    wcr::loss_box_bwd_kernel<<<(h_io->n + 127) / 128, 128, 0, st>>>(*h_io, *h_params);
+    WCR_CHECK_LAUNCH("loss_box_bwd_kernel");
+    return WCR_OK;
+}

@@ -40,6 +40,8 @@ SIGNATURES = {
                                c_void_p, c_void_p, c_u64, c_void_p, c_void_p, c_void_p, c_int,
                                c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
                                c_void_p, c_void_p]),
+    "wcr_weak_loss_fwd": (c_int, [c_void_p, c_void_p, c_void_p]),
+    "wcr_weak_loss_bwd": (c_int, [c_void_p, c_void_p, c_void_p]),
 }
 
 _lib = None
@@ -111,3 +113,23 @@ class ScoreParams(ctypes.Structure):
                 ("point_stride", ctypes.c_int32), ("seg_mode", ctypes.c_int32),
                 ("reserved0", ctypes.c_int32), ("reserved1", ctypes.c_int32),
                 ("reserved2", ctypes.c_int32)]
+
+
+class LossParams(ctypes.Structure):
+    """include/wcr.h WcrLossParams."""
+    _fields_ = [("loss_flags", ctypes.c_int32), ("z_type", ctypes.c_int32),
+                ("dims_func", ctypes.c_int32), ("use_confidence", c_float), ("w_3d", c_float),
+                ("w_iou", c_float), ("w_pose", c_float), ("w_normal", c_float), ("w_z", c_float),
+                ("w_dims", c_float)]
+
+
+_LOSS_IO_PTRS = ["deltas", "z_raw", "dims_raw", "pose", "uncert", "src_boxes", "K4", "v2r",
+                 "prior_mean", "prior_std", "gt_boxes", "clamp", "img_off", "images", "normals",
+                 "ground_conf", "losses", "present", "terms", "R_ego", "proj", "stats", "img_pose",
+                 "grad_losses", "d_deltas", "d_z_raw", "d_dims_raw", "d_pose", "d_uncert", "d_R_pose"]
+
+
+class LossIO(ctypes.Structure):
+    """include/wcr.h WcrLossIO: two sizes then device pointers."""
+    _fields_ = [("n", ctypes.c_int32), ("n_images", ctypes.c_int32)] + \
+               [(name, c_void_p) for name in _LOSS_IO_PTRS]
