@@ -17,6 +17,9 @@ from oracle import loss as ol, loss_inputs as li
 
 pytestmark = pytest.mark.gpu
 LOSS_RTOL, GRAD_RTOL = 1e-5, 1e-4
+# hinge / L1 terms subtract O(1) quantities: 1 ulp(1.0) = 6e-8 of rounding noise in exp()/acos(),
+# times a loss weight of up to 20, is an absolute floor no fp32 implementation can beat
+LOSS_ATOL = 3e-6
 GOLDEN = os.path.join(os.path.dirname(__file__), "golden")
 
 
@@ -44,7 +47,7 @@ def _check(La, ga, Lb, gb):
         if np.isnan(b):
             assert np.isnan(a), k
         else:
-            assert abs(a - b) <= LOSS_RTOL * max(abs(b), 1e-6), (k, a, b)
+            assert abs(a - b) <= LOSS_RTOL * abs(b) + LOSS_ATOL, (k, a, b)
     for k in gb:
         a, b = ga[k].reshape(-1).double(), gb[k].reshape(-1).double()
         scale = b.abs().max().item()
