@@ -181,12 +181,19 @@ int wcr_sample_cubes(const WcrImage *images, const WcrBox *boxes, int n_boxes,
  *             arguments as wcr_sample_cubes; priors/normals/z0/h_sample/seed are
  *             only read in that case)
  *   seg_bits  bit-packed per-box masks or NULL (term skipped); seg_off[n_boxes+1]
- *             word offsets; box b's mask covers its integer ROI, row-major,
- *             rows padded to 32 bits
+ *             word offsets; box b's mask covers its integer ROI
+ *             [int(clip(x1)), int(clip(x2))) x [int(clip(y1)), int(clip(y2)))
+ *             (Boxes.clip + .long(), roi_heads.py:590-597), row-major, bit (c & 31)
+ *             of word r*ceil(ncols/32) + (c >> 5); padding bits must be zero.
+ *             Mask term of a proposal (A3.12): projected corners clamped a second
+ *             time to [0, clamp-1] (roi_heads.py:950-952) -> jarvis_march
+ *             (utils.py:410-454) -> pixels strictly left of every hull edge
+ *             (fill_polygon > 0, utils.py:456-488) -> mask_iou / mod_mask_iou
+ *             (utils.py:225-245) against the box mask
  *   k <= WCR_MAX_TOPK
  *   out_records [n_boxes][k][20]; slots beyond N hold idx = -1
  *   optional per-proposal outputs (NULL to skip), all [n_boxes][N]:
- *     out_scores, out_iou, out_count (int32), out_proj [n_boxes][N][4]
+ *     out_scores, out_iou, out_seg, out_count (int32), out_proj [n_boxes][N][4]
  *   out_npts  [n_boxes] valid depth points per ROI (P_b), optional
  *   ws        workspace, wcr_score_workspace_bytes(n_boxes, N, k) bytes */
 int64_t wcr_score_workspace_bytes(int n_boxes, int N, int k);
@@ -196,7 +203,7 @@ int wcr_score_topk(const WcrImage *images, const WcrBox *boxes, int n_boxes,
                    const WcrSampleParams *h_sample, uint64_t seed,
                    const uint32_t *seg_bits, const int64_t *seg_off,
                    const WcrScoreParams *h_score, int k,
-                   float *out_records, float *out_scores, float *out_iou,
+                   float *out_records, float *out_scores, float *out_iou, float *out_seg,
                    int32_t *out_count, float *out_proj, int32_t *out_npts,
                    void *ws, void *stream);
 

@@ -95,8 +95,10 @@ def project_cube(cube: np.ndarray, K4: np.ndarray, clamp0: float, clamp1: float)
 
 
 def score_box(depth: np.ndarray, K4: np.ndarray, gbox: np.ndarray, clamp0: float, clamp1: float,
-              cubes: np.ndarray, stride: int = 1, e_iou: int = 1, e_pts: int = 1):
-    """-> dict(score (N,), iou (N,), count (N,) i32, proj (N,4), npts int)."""
+              cubes: np.ndarray, stride: int = 1, e_iou: int = 1, e_pts: int = 1, e_seg: int = 0,
+              seg_mode: int = 0, seg: np.ndarray | None = None):
+    """-> dict(score (N,), iou (N,), count (N,) i32, proj (N,4), seg (N,), npts int).
+    ``seg``: full-image (H, W) u8 mask of THIS box (only its integer ROI is read)."""
     depth = np.ascontiguousarray(depth, dtype=np.float32)
     K4 = np.ascontiguousarray(K4, dtype=np.float32)
     gbox = np.ascontiguousarray(gbox, dtype=np.float32)
@@ -106,13 +108,53 @@ def score_box(depth: np.ndarray, K4: np.ndarray, gbox: np.ndarray, clamp0: float
     iou = np.empty(N, dtype=np.float32)
     count = np.empty(N, dtype=np.int32)
     proj = np.empty((N, 4), dtype=np.float32)
-    fn = lib().orc_score_box
+    sseg = np.ones(N, dtype=np.float32)
+    if seg is not None:
+        seg = np.ascontiguousarray(seg, dtype=np.uint8)
+        assert seg.shape == depth.shape
+    fn = lib().orc_score_box_seg
     fn.restype = c_i
     npts = fn(_p(depth, c_f), c_i(depth.shape[0]), c_i(depth.shape[1]), c_i(depth.shape[1]),
               _p(K4, c_f), _p(gbox, c_f), c_f(clamp0), c_f(clamp1), _p(cubes, c_f), c_i(N),
-              c_i(stride), c_i(e_iou), c_i(e_pts), _p(score, c_f), _p(iou, c_f),
-              _p(count, ctypes.c_int32), _p(proj, c_f))
-    return {"score": score, "iou": iou, "count": count, "proj": proj, "npts": int(npts)}
+              c_i(stride), c_i(e_iou), c_i(e_pts), c_i(e_seg if seg is not None else 0),
+              c_i(seg_mode), _p(seg, ctypes.c_uint8) if seg is not None else None,
+              c_i(depth.shape[1]), _p(score, c_f), _p(iou, c_f), _p(count, ctypes.c_int32),
+              _p(proj, c_f), _p(sseg, c_f))
+    return {"score": score, "iou": iou, "count": count, "proj": proj, "seg": sseg,
+            "npts": int(npts)}
+
+
+def jarvis_march(points: np.ndarray):
+    """utils.py:410-454 -> hull (m,2) f32 in the reference's (flipped) order, or None
+    when the march does not close."""
+    pts = np.ascontiguousarray(points, dtype=np.float32).reshape(-1, 2)
+    hull = np.empty((pts.shape[0], 2), dtype=np.float32)
+    fn = lib().orc_jarvis_march
+    fn.restype = c_i
+    m = fn(_p(pts, c_f), c_i(pts.shape[0]), _p(hull, c_f))
+    return None if m < 0 else hull[:m].copy()
+
+
+def fill_polygon(hull: np.ndarray, H: int, W: int) -> np.ndarray:
+    """utils.py:456-488 -> soft mask (H, W) f32."""
+    hull = np.ascontiguousarray(hull, dtype=np.float32).reshape(-1, 2)
+    out = np.empty((H, W), dtype=np.float32)
+    lib().orc_fill_polygon(_p(hull, c_f), c_i(hull.shape[0]), c_i(H), c_i(W), _p(out, c_f))
+    return out
+
+
+def seg_term(corners: np.ndarray, clamp0: float, clamp1: float, seg: np.ndarray, roi, mode: int = 0):
+    """-> (s_seg f32, inter, bube) for ONE cube's 8 projected corners (8,2)."""
+    corners = np.ascontiguousarray(corners, dtype=np.float32).reshape(16)
+    seg = np.ascontiguousarray(seg, dtype=np.uint8)
+    roi = np.ascontiguousarray(roi, dtype=np.int32)
+    inter, bube = ctypes.c_int(0), ctypes.c_int(0)
+    fn = lib().orc_seg_term
+    fn.restype = c_f
+    v = fn(_p(corners, c_f), c_f(clamp0), c_f(clamp1), _p(seg, ctypes.c_uint8), c_i(seg.shape[0]),
+           c_i(seg.shape[1]), c_i(seg.shape[1]), _p(roi, ctypes.c_int32), c_i(-1), c_i(mode),
+           ctypes.byref(inter), ctypes.byref(bube))
+    return np.float32(v), inter.value, bube.value
 
 
 def philox4x32_10(ctr, key) -> np.ndarray:

@@ -181,6 +181,163 @@ float orc_iou_2d(const float *g, const float *p)
     return inter > 0.f ? inter / ((a1 + a2) - inter) : 0.f;
 }
 
+/* ------------------------------------------------------------------------ */
+/* Convex hull of projected corners + polygon fill + mask IoU (A3.7, A3.8)     */
+/* ------------------------------------------------------------------------ */
+
+/* ProposalNetwork/utils/utils.py:373-377. torch 0-d fp32 arithmetic: every
+ * product and difference rounded separately (no fused multiply-add). */
+static inline float hull_direction(const float *p1, const float *p2, const float *p3)
+{
+    const float a = (p2[0] - p1[0]) * (p3[1] - p1[1]);
+    const float b = (p2[1] - p1[1]) * (p3[0] - p1[0]);
+    return a - b;
+}
+static inline float hull_distance_sq(const float *p1, const float *p2)
+{
+    const float dx = p2[0] - p1[0], dy = p2[1] - p1[1];
+    return dx * dx + dy * dy;
+}
+
+/* utils.py:410-454 jarvis_march on n 2-D points (n <= 32).
+ *  - duplicates (utils.py:379-408, 413-420): index i is "duplicated" when some
+ *    j > i holds the same point; the k-th such index in ascending order (the
+ *    iteration order of a Python set of small ints) gets (k+1) added to x and y;
+ *  - start: min x, ties -> first arg-max of y among them (:423-430);
+ *  - march (:437-452): q = (l+1)%n; for i != l: d = direction(p_l, p_i, p_q);
+ *    take i when d > 0, or d == 0 and i is farther from l than q;
+ *  - result flipped (:454).
+ * Returns the number of hull vertices m (hull[m][2], flipped order), or -1 when
+ * the march does not return to its start within n steps (the reference would
+ * loop forever; this project defines the mask as empty then). */
+int orc_jarvis_march(const float *pts_in, int n, float *hull)
+{
+    float p[32][2];
+    int dup[32], ndup = 0;
+    if (n < 1 || n > 32) return -1;
+    for (int i = 0; i < n; ++i) { p[i][0] = pts_in[2 * i]; p[i][1] = pts_in[2 * i + 1]; }
+    for (int i = 0; i < n - 1; ++i) {
+        int is_dup = 0;
+        for (int j = i + 1; j < n; ++j)
+            if (pts_in[2 * i] == pts_in[2 * j] && pts_in[2 * i + 1] == pts_in[2 * j + 1]) is_dup = 1;
+        if (is_dup) dup[ndup++] = i;
+    }
+    for (int k = 0; k < ndup; ++k) {
+        p[dup[k]][0] = p[dup[k]][0] + (float)(k + 1);
+        p[dup[k]][1] = p[dup[k]][1] + (float)(k + 1);
+    }
+    float min_x = p[0][0];
+    for (int i = 1; i < n; ++i) if (p[i][0] < min_x) min_x = p[i][0];   /* torch.min: NaN excluded by the caller */
+    int index = -1;
+    for (int i = 0; i < n; ++i)
+        if (p[i][0] == min_x && (index < 0 || p[i][1] > p[index][1])) index = i;
+    if (index < 0) return -1;
+    float res[32][2];
+    int m = 0;
+    res[m][0] = p[index][0]; res[m][1] = p[index][1]; ++m;
+    int l = index;
+    for (;;) {
+        int q = (l + 1) % n;
+        for (int i = 0; i < n; ++i) {
+            if (i == l) continue;
+            const float d = hull_direction(p[l], p[i], p[q]);
+            if (d > 0.f || (d == 0.f && hull_distance_sq(p[i], p[l]) > hull_distance_sq(p[q], p[l])))
+                q = i;
+        }
+        l = q;
+        if (l == index) break;
+        if (m == n) return -1;
+        res[m][0] = p[q][0]; res[m][1] = p[q][1]; ++m;
+    }
+    for (int i = 0; i < m; ++i) { hull[2 * i] = res[m - 1 - i][0]; hull[2 * i + 1] = res[m - 1 - i][1]; }
+    return m;
+}
+
+/* utils.py:456-488 fill_polygon: soft mask = prod_i clamp(val_i, 0, 1),
+ * val_i = (X - v1x)*e_y - (Y - v1y)*e_x over integer pixel coordinates. */
+void orc_fill_polygon(const float *hull, int m, int H, int W, float *mask)
+{
+#pragma omp parallel for
+    for (int Y = 0; Y < H; ++Y)
+        for (int X = 0; X < W; ++X) {
+            float prod = 1.f;
+            for (int i = 0; i < m; ++i) {
+                const float *v1 = hull + 2 * i, *v2 = hull + 2 * ((i + 1) % m);
+                const float ex = v2[0] - v1[0], ey = v2[1] - v1[1];
+                const float t1 = ((float)X - v1[0]) * ey, t2 = ((float)Y - v1[1]) * ex;
+                float val = t1 - t2;
+                val = val != val ? val : (val < 0.f ? 0.f : val);   /* torch.max(val, 0) keeps NaN */
+                val = val != val ? val : (val > 1.f ? 1.f : val);
+                prod = prod * val;
+            }
+            mask[(size_t)Y * W + X] = prod;
+        }
+}
+
+/* Second clamp of the projected corners before the hull, roi_heads.py:950-952. */
+static inline void seg_clamp_corners(const float *corners, float clamp0, float clamp1, float *out)
+{
+    const float hx = (float)(int)(clamp0 - 1.f), hy = (float)(int)(clamp1 - 1.f);
+    for (int i = 0; i < 8; ++i) {
+        out[2 * i] = clamp_keep_nan(corners[2 * i], 0.f, hx);
+        out[2 * i + 1] = clamp_keep_nan(corners[2 * i + 1], 0.f, hy);
+    }
+}
+
+/* Composite mask term (project spec built from utils.py:225-245,
+ * 410-493 and roi_heads.py:428, 950-952):
+ *   coords = second-clamped projected corners; hull = jarvis_march(coords);
+ *   bube   = pixels (X, Y) of the H x W image with val_i > 0 for every hull edge,
+ *            rows restricted to [floor(min_y) - 1, ceil(max_y) + 1] (identical to
+ *            fill_polygon(...) > 0 for non-degenerate hulls);
+ *   seg    = the box's mask restricted to its integer ROI [u0,u1) x [v0,v1);
+ *   inter  = |seg & bube|, uni = |seg| + |bube| - inter;
+ *   s_seg  = inter == 0 ? 0 : inter / uni   (mode 1: inter^5 / uni, utils.py:236-245)
+ * Non-finite corners or an unclosed march give 0. */
+float orc_seg_term(const float *corners, float clamp0, float clamp1, const uint8_t *seg, int H, int W,
+                   int pitch, const int *roi /* u0 v0 u1 v1 */, int seg_area /* < 0: count here */,
+                   int mode, int *out_inter, int *out_bube)
+{
+    float c2[16], hull[16];
+    if (out_inter) *out_inter = 0;
+    if (out_bube) *out_bube = 0;
+    for (int i = 0; i < 16; ++i) if (!(fabsf(corners[i]) <= 3.402823466e38f)) return 0.f;
+    seg_clamp_corners(corners, clamp0, clamp1, c2);
+    const int m = orc_jarvis_march(c2, 8, hull);
+    if (m < 1) return 0.f;
+    float mny = hull[1], mxy = hull[1];
+    for (int i = 1; i < m; ++i) { mny = fminf(mny, hull[2 * i + 1]); mxy = fmaxf(mxy, hull[2 * i + 1]); }
+    int r0 = (int)floorf(mny) - 1, r1 = (int)ceilf(mxy) + 1;
+    if (r0 < 0) r0 = 0;
+    if (r1 > H - 1) r1 = H - 1;
+    if (seg_area < 0) {
+        seg_area = 0;
+        for (int v = roi[1]; v < roi[3]; ++v)
+            for (int u = roi[0]; u < roi[2]; ++u) seg_area += seg[(size_t)v * pitch + u] > 0;
+    }
+    int inter = 0, bube = 0;
+    for (int Y = r0; Y <= r1; ++Y)
+        for (int X = 0; X < W; ++X) {
+            int in = 1;
+            for (int i = 0; i < m && in; ++i) {
+                const float *v1 = hull + 2 * i, *v2 = hull + 2 * ((i + 1) % m);
+                const float ex = v2[0] - v1[0], ey = v2[1] - v1[1];
+                const float t1 = ((float)X - v1[0]) * ey, t2 = ((float)Y - v1[1]) * ex;
+                in = (t1 - t2) > 0.f;
+            }
+            if (!in) continue;
+            ++bube;
+            if (X >= roi[0] && X < roi[2] && Y >= roi[1] && Y < roi[3] && seg[(size_t)Y * pitch + X] > 0)
+                ++inter;
+        }
+    if (out_inter) *out_inter = inter;
+    if (out_bube) *out_bube = bube;
+    if (inter == 0) return 0.f;
+    const float fi = (float)inter, fu = (float)(seg_area + bube - inter);
+    if (mode == 1) return ((((fi * fi) * fi) * fi) * fi) / fu;
+    return fi / fu;
+}
+
 static inline float ipow_(float x, int e) { float r = 1.f; for (int i = 0; i < e; ++i) r = r * x; return r; }
 
 /* SURVEY A3.11/A3.12 for ONE box: N cubes against the depth pixels of the box's
@@ -193,9 +350,11 @@ static inline float ipow_(float x, int e) { float r = 1.f; for (int i = 0; i < e
  *   q'_k = fma(z, fma(A'_k, a_u, fma(B'_k, b_v, C'_k)), -O'_k)
  *   inside iff max(|q'_0|, |q'_1|, |q'_2|) <= 1      (max ignores NaN operands)
  * A cube with a non-positive dimension contains no point. Returns P_b. */
-int orc_score_box(const float *depth, int H, int W, int pitch, const float *K4, const float *gbox,
-                  float clamp0, float clamp1, const float *cubes, int N, int stride, int e_iou,
-                  int e_pts, float *out_score, float *out_iou, int *out_count, float *out_proj)
+int orc_score_box_seg(const float *depth, int H, int W, int pitch, const float *K4, const float *gbox,
+                      float clamp0, float clamp1, const float *cubes, int N, int stride, int e_iou,
+                      int e_pts, int e_seg, int seg_mode, const uint8_t *seg /* H x W or NULL */,
+                      int seg_pitch, float *out_score, float *out_iou, int *out_count,
+                      float *out_proj, float *out_seg)
 {
     float t;
     t = gbox[0] < 0.f ? 0.f : gbox[0]; const int u0 = (int)(t > W ? (float)W : t);
@@ -203,6 +362,12 @@ int orc_score_box(const float *depth, int H, int W, int pitch, const float *K4, 
     t = gbox[1] < 0.f ? 0.f : gbox[1]; const int v0 = (int)(t > H ? (float)H : t);
     t = gbox[3] < 0.f ? 0.f : gbox[3]; const int v1 = (int)(t > H ? (float)H : t);
     int npts = 0;
+    /* the mask term always uses the stride-1 integer ROI */
+    const int roi[4] = {u0, v0, u1, v1};
+    int seg_area = 0;
+    if (e_seg > 0 && seg)
+        for (int v = v0; v < v1; ++v)
+            for (int u = u0; u < u1; ++u) seg_area += seg[(size_t)v * seg_pitch + u] > 0;
     if (e_pts > 0)
         for (int v = v0; v < v1; v += stride)
             for (int u = u0; u < u1; u += stride) {
@@ -235,16 +400,29 @@ int orc_score_box(const float *depth, int H, int W, int pitch, const float *K4, 
                     cnt += fmaxf(fmaxf(fabsf(q0), fabsf(q1)), fabsf(q2)) <= 1.f;
                 }
             }
-        float pb[4];
-        orc_project_cube(cube, K4, clamp0, clamp1, pb, NULL);
+        float pb[4], corners[16];
+        orc_project_cube(cube, K4, clamp0, clamp1, pb, corners);
         const float siou = orc_iou_2d(gbox, pb);
         const float spts = npts > 0 ? (float)cnt / (float)npts : 0.f;
-        out_score[j] = (ipow_(siou, e_iou) * ipow_(spts, e_pts)) * 1.f;
+        float sseg = 1.f;
+        if (e_seg > 0 && seg)
+            sseg = orc_seg_term(corners, clamp0, clamp1, seg, H, W, seg_pitch, roi, seg_area,
+                                seg_mode, NULL, NULL);
+        out_score[j] = (ipow_(siou, e_iou) * ipow_(spts, e_pts)) * ipow_(sseg, e_seg);
+        if (out_seg) out_seg[j] = sseg;
         if (out_iou) out_iou[j] = siou;
         if (out_count) out_count[j] = cnt;
         if (out_proj) { out_proj[4 * j] = pb[0]; out_proj[4 * j + 1] = pb[1]; out_proj[4 * j + 2] = pb[2]; out_proj[4 * j + 3] = pb[3]; }
     }
     return npts;
+}
+
+int orc_score_box(const float *depth, int H, int W, int pitch, const float *K4, const float *gbox,
+                  float clamp0, float clamp1, const float *cubes, int N, int stride, int e_iou,
+                  int e_pts, float *out_score, float *out_iou, int *out_count, float *out_proj)
+{
+    return orc_score_box_seg(depth, H, W, pitch, K4, gbox, clamp0, clamp1, cubes, N, stride, e_iou,
+                             e_pts, 0, 0, NULL, 0, out_score, out_iou, out_count, out_proj, NULL);
 }
 
 /* Philox4x32-10 (Salmon et al., SC'11), for the known-answer test of the

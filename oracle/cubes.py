@@ -44,9 +44,18 @@ def project_cube(cube, K, clamp):
     return clib.project_cube(cube, K4_of(K), float(clamp[0]), float(clamp[1]))
 
 
-def score_box(depth, K, gbox, clamp, cubes, stride=1, e_iou=1, e_pts=1):
+def score_box(depth, K, gbox, clamp, cubes, stride=1, e_iou=1, e_pts=1, e_seg=0, seg_mode=0,
+              seg=None):
     return clib.score_box(depth, K4_of(K), gbox, float(clamp[0]), float(clamp[1]), cubes, stride,
-                          e_iou, e_pts)
+                          e_iou, e_pts, e_seg, seg_mode, seg)
+
+
+def box_roi(gbox, H, W):
+    """Integer ROI of a GT box: Boxes.clip((H, W)) then .long() (roi_heads.py:590-597)."""
+    g = np.asarray(gbox, dtype=f32)
+    u0, u1 = int(min(max(g[0], 0), W)), int(min(max(g[2], 0), W))
+    v0, v1 = int(min(max(g[1], 0), H)), int(min(max(g[3], 0), H))
+    return u0, v0, u1, v1
 
 
 def topk(scores: np.ndarray, k: int):

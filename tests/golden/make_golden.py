@@ -96,6 +96,59 @@ def golden_cubes():
     print("cubes", boxes.shape, float(ious.max()))
 
 
+def golden_hull():
+    """convex_hull = jarvis_march + fill_polygon, mask_iou, mod_mask_iou
+    (utils.py:225-245, 410-493) on the reference's own five fixture point sets
+    (utils.py:500-544, copied here as INPUT data) and on seeded random clamped
+    corner sets. Stored: hull vertices, the binarised mask (bit-packed), every
+    fractional soft value, and the two IoUs against a seeded random mask."""
+    ns = refshim.load()
+    U = ns.utils
+    fixtures = [
+        [[271.0, 356.0], [25.3744, 356.0], [0.0, 356.0], [0.0, 89.5266], [271.0, 159.3112],
+         [95.5653, 201.7484], [0.0, 0.0], [271.0, 0.0]],
+        [[150.3456, 0.0], [479.0, 0.0], [11.8427, 0.0], [0.0, 0.0], [121.4681, 232.5976],
+         [375.6230, 383.9329], [12.8765, 630.0], [0.0, 344.7250]],
+        [[290.9577, 171.1176], [197.7348, 483.7612], [383.0, 504.0], [383.0, 27.6211],
+         [2.2419, 52.6505], [0.0, 399.6908], [0.0, 504.0], [0.0, 0.0]],
+        [[271.0, 19.5241], [271.0, 356.0], [0.0, 0.0], [271.0, 0.0], [0.0, 0.0], [163.0264, 77.9408],
+         [164.2467, 321.0222], [0.0, 356.0], [0.0, 0.0]],
+        [[272.0, 1.0], [0.0, 173.5156], [74.8860, 141.3913], [253.8221, 0.0], [271.0, 0.0],
+         [271.0, 356.0], [262.5294, 327.9978], [271.0, 120.8048]],
+    ]
+    rng = np.random.default_rng(17)
+
+    def one_file(name, point_sets, H, W):
+        d = {"H": H, "W": W, "n_sets": len(point_sets)}
+        for i, pts in enumerate(point_sets):
+            pts = np.asarray(pts, dtype=np.float32)
+            hull = U.jarvis_march(torch.from_numpy(pts.copy()))
+            soft = U.fill_polygon(torch.zeros(H, W), hull).numpy()
+            seg = rng.uniform(size=(H, W)) < 0.35
+            d[f"pts_{i}"] = pts
+            d[f"hull_{i}"] = hull.numpy()
+            d[f"maskbits_{i}"] = np.packbits((soft > 0).reshape(-1))
+            frac = np.flatnonzero((soft > 0) & (soft < 1))
+            d[f"frac_idx_{i}"] = frac
+            d[f"frac_val_{i}"] = soft.reshape(-1)[frac]
+            d[f"seg_{i}"] = seg
+            d[f"miou_{i}"] = np.float32(U.mask_iou(torch.from_numpy(seg), soft))
+            d[f"modiou_{i}"] = np.float32(U.mod_mask_iou(torch.from_numpy(seg).float(), soft))
+        np.savez_compressed(os.path.join(HERE, name), **d)
+        print(name, [d[f"hull_{i}"].shape[0] for i in range(len(point_sets))])
+
+    one_file("hull_0.npz", fixtures, 640, 500)
+    sets = []
+    for t in range(12):
+        pts = rng.uniform(-40, 200, size=(8, 2)).astype(np.float32)
+        pts[:, 0] = np.clip(pts[:, 0], 0, 159)
+        pts[:, 1] = np.clip(pts[:, 1], 0, 119)
+        if t % 4 == 0:
+            pts[3] = pts[6]
+        sets.append(pts)
+    one_file("hull_1.npz", sets, 120, 160)
+
+
 def golden_loss():
     cases = [(0, [3, 1, 5, 2], False, {}),
              (1, [6, 2, 9], True, {"z_type": "sigmoid", "dims_priors_func": "sigmoid"}),
@@ -113,4 +166,5 @@ if __name__ == "__main__":
     assert refshim.available(), "needs /root/reference"
     golden_ground()
     golden_cubes()
+    golden_hull()
     golden_loss()

@@ -195,3 +195,75 @@ def test_score_edge_cases(cuda_lib):
     assert (res2["idx"][:, 5:] == -1).all() and (res2["idx"][:, :5] >= 0).all()
     with pytest.raises(Exception):
         score_topk(shard, boxes, cubes, cfg=ScoreConfig())   # CPU tensor: no fallback
+
+
+@pytest.mark.parametrize("N,H,W,mode,eseg", [(600, 480, 640, 0, 1), (300, 375, 1242, 1, 1),
+                                             (1500, 240, 320, 0, 2)])
+def test_score_seg_term_bit_exact(cuda_lib, N, H, W, mode, eseg):
+    """Mask coverage (A3.7/A3.8 inside the fused epilogue): hull march + interval
+    fill + mask IoU must equal the oracle's per-pixel half-plane test bit for bit
+    (integer pixel counts), and so must the top-k with the seg factor."""
+    from wcr import synth
+    from wcr.proposals import propose, score_topk, ScoreConfig, SegMasks
+    ims, shard, boxes, priors, normals = _setup(2, H, W, n_boxes=3, first=60)
+    masks = [m for im in ims for m in synth.seg_masks(im["boxes"], H, W)]
+    seg = SegMasks(shard, boxes, masks)
+    cubes = propose(shard, boxes, priors, normals, N, seed=5)
+    # push some cubes far off-centre so that their hulls clamp onto the image border
+    cubes[:, ::7, 0] += 2.5
+    cubes[:, ::11, 1] -= 2.0
+    cfg = ScoreConfig(e_seg=eseg, seg_mode=mode, k=16)
+    res = score_topk(shard, boxes, cubes, cfg=cfg, seg=seg, want_all=True)
+    cubes_h = cubes.cpu().numpy()
+    gb = 0
+    for im in ims:
+        for b in range(len(im["boxes"])):
+            ref = oc.score_box(im["depth"].numpy(), im["K"].numpy(), im["boxes"][b].numpy(), (H, W),
+                               cubes_h[gb], 1, 1, 1, eseg, mode, masks[gb].numpy())
+            assert np.array_equal(res["count"][gb].cpu().numpy(), ref["count"])
+            np.testing.assert_allclose(res["seg"][gb].cpu().numpy(), ref["seg"], rtol=RTOL)
+            assert np.array_equal(res["seg"][gb].cpu().numpy(), ref["seg"])          # integers / integers
+            np.testing.assert_allclose(res["scores"][gb].cpu().numpy(), ref["score"], rtol=RTOL)
+            want = oc.topk(ref["score"], 16)
+            assert np.array_equal(res["idx"][gb].cpu().numpy(), want)
+            rec = res["records"][gb].cpu().numpy()
+            for r, j in enumerate(want):
+                assert rec[r, 19] == ref["seg"][j] and rec[r, 17] == ref["iou"][j]
+            assert (ref["seg"] > 0).any() and (ref["seg"] == 0).any()
+            gb += 1
+
+
+def test_score_seg_degenerate(cuda_lib):
+    """Empty masks, cubes behind the camera (non-finite corners), cubes entirely
+    outside the image (hull collapses onto the border, duplicate corners)."""
+    from wcr.images import ImageShard
+    from wcr.proposals import BoxTable, score_topk, ScoreConfig, SegMasks
+    from wcr import synth
+    H, W = 120, 160
+    im = synth.make_image(5, H, W, n_boxes=1, dummy_ground=False)
+    boxes_t = torch.tensor([[20.0, 30.0, 120.0, 100.0], [0.0, 0.0, 160.0, 120.0],
+                            [30.2, 40.7, 31.1, 41.3]])
+    shard = ImageShard([im["depth"].cuda()], None, [im["K"]])
+    boxes = BoxTable(shard, [boxes_t], [torch.zeros(3, dtype=torch.long)])
+    masks = list(synth.seg_masks(boxes_t, H, W))
+    masks[1] = torch.zeros(H, W, dtype=torch.uint8)           # empty mask
+    seg = SegMasks(shard, boxes, masks)
+    g = torch.Generator().manual_seed(1)
+    N = 64
+    cubes = torch.zeros(3, N, 15)
+    cubes[:, :, 0:2] = torch.randn(3, N, 2, generator=g) * 1.5
+    cubes[:, :, 2] = 0.5 + torch.rand(3, N, generator=g) * 4
+    cubes[:, :, 3:6] = 0.2 + torch.rand(3, N, 3, generator=g)
+    cubes[:, :, 6:] = torch.eye(3).reshape(9)
+    cubes[:, 0, 2] = 0.0            # straddles the camera plane
+    cubes[:, 1, 2] = -2.0           # behind the camera
+    cubes[:, 2, 0] = 50.0           # far right: every corner clamps to the border
+    cubes[:, 3, 0:2] = -50.0        # top-left: all corners clamp to (0, 0) -> 8 duplicates
+    res = score_topk(shard, boxes, cubes.cuda(), cfg=ScoreConfig(e_seg=1, k=8), seg=seg, want_all=True)
+    for b in range(3):
+        ref = oc.score_box(im["depth"].numpy(), im["K"].numpy(), boxes_t[b].numpy(), (H, W),
+                           cubes[b].numpy(), 1, 1, 1, 1, 0, masks[b].numpy())
+        assert np.array_equal(res["seg"][b].cpu().numpy(), ref["seg"])
+        np.testing.assert_allclose(res["scores"][b].cpu().numpy(), ref["score"], rtol=RTOL)
+        assert np.array_equal(res["idx"][b].cpu().numpy(), oc.topk(ref["score"], 8))
+    assert (res["seg"][1] == 0).all()

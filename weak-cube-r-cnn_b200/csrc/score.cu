@@ -25,6 +25,7 @@
 #include <stdlib.h>
 #include <string.h>
 #include "sample.cuh"
+#include "hull.cuh"
 
 namespace wcr {
 
@@ -125,6 +126,9 @@ struct ScoreArgs {
     int32_t *out_count;
     float *out_proj;
     int32_t *out_npts;
+    const uint32_t *seg_bits;   // bit-packed per-box masks (e_seg > 0)
+    const int64_t *seg_off;     // [n_boxes + 1] word offsets
+    float *out_seg;
 };
 
 // One CTA: items per box -> exclusive prefix. n_boxes is at most a few 100 k.
@@ -249,12 +253,12 @@ __global__ void __launch_bounds__(SC_THREADS, MINB) score_items_kernel(const Sco
     __shared__ __align__(16) float4 tile[SC_TILE];
     __shared__ float s_score[SC_CHUNK];
     __shared__ float s_iou[SC_CHUNK];
-    __shared__ float s_pts[SC_CHUNK];
+    __shared__ float s_seg[SC_CHUNK];
     __shared__ float s_red_v[SC_THREADS / 32];
     __shared__ int s_red_i[SC_THREADS / 32];
     __shared__ int s_win[WCR_MAX_TOPK];
     __shared__ float s_wsc[WCR_MAX_TOPK];
-    __shared__ int s_item, s_flag;
+    __shared__ int s_item, s_flag, s_area;
 
     const int tid = threadIdx.x, lane = tid & 31;
     const int *__restrict__ prefix = a.ws.item_prefix;
@@ -440,11 +444,34 @@ __global__ void __launch_bounds__(SC_THREADS, MINB) score_items_kernel(const Sco
         float lo0, hi0, lo1, hi1;
         clamp_bounds(bx.clamp0, lo0, hi0);
         clamp_bounds(bx.clamp1, lo1, hi1);
+        // mask term: the box's bit-packed mask over its stride-1 integer ROI; |seg| by
+        // a CTA-wide popcount. The point tile is free now and serves as per-thread
+        // scratch for the hull march (32 floats per thread, interleaved).
+        const bool use_seg = a.sc.e_seg > 0;
+        SegBox sb = {nullptr, 0, 0, 0, 0, 0, 0};
+        if (use_seg) {
+            const Roi r1 = box_roi(bx, im.H, im.W, 1, true);
+            sb.u0 = r1.u0; sb.v0 = r1.v0; sb.ncols = r1.ncols; sb.nrows = r1.ncols > 0 ? r1.nrows : 0;
+            sb.wpr = (sb.ncols + 31) >> 5;
+            sb.bits = a.seg_bits + a.seg_off[b];
+            if (tid == 0) s_area = 0;
+            __syncthreads();
+            int part = 0;
+            for (int w = tid; w < sb.nrows * sb.wpr; w += SC_THREADS) part += __popc(__ldg(sb.bits + w));
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) part += __shfl_xor_sync(0xffffffffu, part, o);
+            if (lane == 0 && part) atomicAdd(&s_area, part);
+            __syncthreads();
+            sb.area = s_area;
+        }
+        float *scratch = reinterpret_cast<float *>(tile) + tid;
+        const Strided spx = {scratch, SC_THREADS}, spy = {scratch + 8 * SC_THREADS, SC_THREADS};
+        const Strided shx = {scratch + 16 * SC_THREADS, SC_THREADS}, shy = {scratch + 24 * SC_THREADS, SC_THREADS};
 #pragma unroll 1
         for (int t = 0; t < T; ++t) {
             const int loc = t * SC_THREADS + tid;
             const int j = chunk * SC_CHUNK + loc;
-            float score = -INFINITY, siou = 0.f, spts = 0.f;
+            float score = -INFINITY, siou = 0.f, spts = 0.f, sseg = 1.f;
             if (j < a.N) {
                 const size_t o = (size_t)b * a.N + j;
                 const float *src = cubes + o * 15;
@@ -452,19 +479,37 @@ __global__ void __launch_bounds__(SC_THREADS, MINB) score_items_kernel(const Sco
 #pragma unroll
                 for (int i = 0; i < 15; ++i) cube[i] = __ldg(src + i);
                 const int c = __ldcg(a.ws.count + o);
-                const ProjBox pb = project_cube(cube, K, lo0, hi0, lo1, hi1, nullptr);
+                float cxy[16];
+                const ProjBox pb = project_cube(cube, K, lo0, hi0, lo1, hi1, use_seg ? cxy : nullptr);
                 siou = iou_2d(bx.x1, bx.y1, bx.x2, bx.y2, pb);
                 spts = npts > 0 ? (float)c / (float)npts : 0.f;
-                score = (ipow(siou, a.sc.e_iou) * ipow(spts, a.sc.e_pts)) * 1.f;  // s_seg: later
+                if (use_seg) {
+                    // second clamp of the corners (roi_heads.py:950-952), then hull + fill
+                    const float hx2 = (float)(int)(bx.clamp0 - 1.f), hy2 = (float)(int)(bx.clamp1 - 1.f);
+                    bool finite = true;
+#pragma unroll
+                    for (int i = 0; i < 8; ++i) {
+                        finite = finite && fabsf(cxy[2 * i]) <= 3.402823466e38f && fabsf(cxy[2 * i + 1]) <= 3.402823466e38f;
+                        spx(i) = fminf(fmaxf(cxy[2 * i], 0.f), hx2);
+                        spy(i) = fminf(fmaxf(cxy[2 * i + 1], 0.f), hy2);
+                    }
+                    sseg = 0.f;
+                    if (finite) {
+                        const int m = jarvis_march(spx, spy, 8, shx, shy);
+                        sseg = seg_term(shx, shy, m, im.H, im.W, sb, a.sc.seg_mode);
+                    }
+                }
+                score = (ipow(siou, a.sc.e_iou) * ipow(spts, a.sc.e_pts)) * ipow(sseg, a.sc.e_seg);
                 if (a.out_scores) a.out_scores[o] = score;
                 if (a.out_iou) a.out_iou[o] = siou;
+                if (a.out_seg) a.out_seg[o] = sseg;
                 if (a.out_count) a.out_count[o] = c;
                 if (a.out_proj) {
                     float *d = a.out_proj + o * 4;
                     d[0] = pb.x1; d[1] = pb.y1; d[2] = pb.x2; d[3] = pb.y2;
                 }
             }
-            s_score[loc] = score; s_iou[loc] = siou; s_pts[loc] = spts;
+            s_score[loc] = score; s_iou[loc] = siou; s_seg[loc] = sseg;
         }
         __syncthreads();
         cta_topk(s_score, a.k, s_red_v, s_red_i, s_win, s_wsc);
@@ -483,7 +528,9 @@ __global__ void __launch_bounds__(SC_THREADS, MINB) score_items_kernel(const Sco
                 rec[0] = __int_as_float(j);
                 rec[1] = s_wsc[tid];
                 for (int i = 0; i < 15; ++i) rec[2 + i] = __ldg(src + i);
-                rec[17] = s_iou[loc]; rec[18] = s_pts[loc]; rec[19] = 1.f;
+                const int c = __ldcg(a.ws.count + (size_t)b * a.N + j);
+                rec[17] = s_iou[loc]; rec[18] = npts > 0 ? (float)c / (float)npts : 0.f;
+                rec[19] = s_seg[loc];
             }
         }
         if (a.n_chunks > 1) {
@@ -552,8 +599,9 @@ extern "C" int wcr_score_topk(const WcrImage *images, const WcrBox *boxes, int n
                               const WcrSampleParams *h_sample, uint64_t seed,
                               const uint32_t *seg_bits, const int64_t *seg_off,
                               const WcrScoreParams *h_score, int k, float *out_records,
-                              float *out_scores, float *out_iou, int32_t *out_count,
-                              float *out_proj, int32_t *out_npts, void *ws, void *stream)
+                              float *out_scores, float *out_iou, float *out_seg,
+                              int32_t *out_count, float *out_proj, int32_t *out_npts, void *ws,
+                              void *stream)
 {
     WCR_CHECK_DEVICE();
     WCR_REQUIRE(images && boxes && h_score && out_records && ws, "wcr_score_topk: null pointer");
@@ -591,7 +639,7 @@ extern "C" int wcr_score_topk(const WcrImage *images, const WcrBox *boxes, int n
     a.sc = *h_score; a.k = k; a.n_chunks = nc; a.records = out_records;
     a.out_scores = out_scores; a.out_iou = out_iou; a.out_count = out_count;
     a.out_proj = out_proj; a.out_npts = out_npts;
-    (void)seg_bits; (void)seg_off;
+    a.seg_bits = seg_bits; a.seg_off = seg_off; a.out_seg = out_seg;
     static int variant = -1;
     if (variant < 0) {  // development knob; the default is what DESIGN.md measures
         const char *ev = getenv("WCR_SCORE_VARIANT");

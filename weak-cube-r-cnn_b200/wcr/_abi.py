@@ -39,7 +39,7 @@ SIGNATURES = {
     "wcr_score_topk": (c_int, [c_void_p, c_void_p, c_int, c_void_p, c_int, c_void_p, c_void_p,
                                c_void_p, c_void_p, c_u64, c_void_p, c_void_p, c_void_p, c_int,
                                c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
-                               c_void_p, c_void_p]),
+                               c_void_p, c_void_p, c_void_p]),
     "wcr_weak_loss_fwd": (c_int, [c_void_p, c_void_p, c_void_p]),
     "wcr_weak_loss_bwd": (c_int, [c_void_p, c_void_p, c_void_p]),
 }

@@ -130,6 +130,51 @@ def propose(shard: ImageShard, boxes: BoxTable, priors: torch.Tensor, normals: t
     return out
 
 
+def box_rois(boxes: "BoxTable", shard: ImageShard) -> np.ndarray:
+    """(n_boxes, 4) int32 [u0, v0, u1, v1): Boxes.clip((H, W)) then .long(), the way the
+    reference slices depth patches (roi_heads.py:590-597). Same arithmetic as
+    csrc/score.cu box_roi()."""
+    h = boxes.host
+    sizes = np.asarray(shard.sizes(), dtype=np.float32).reshape(-1, 2)
+    Hs, Ws = sizes[h["image"], 0], sizes[h["image"], 1]
+    u0 = np.minimum(np.maximum(h["x1"], 0), Ws).astype(np.int32)
+    u1 = np.minimum(np.maximum(h["x2"], 0), Ws).astype(np.int32)
+    v0 = np.minimum(np.maximum(h["y1"], 0), Hs).astype(np.int32)
+    v1 = np.minimum(np.maximum(h["y2"], 0), Hs).astype(np.int32)
+    return np.stack([u0, v0, u1, v1], axis=1)
+
+
+class SegMasks:
+    """Bit-packed per-box segmentation masks (include/wcr.h ``seg_bits``/``seg_off``).
+
+    ``masks_per_box``: one (H, W) mask per box (bool / u8 / float, non-zero == object,
+    host or device); only the box's integer ROI is kept -- the mask term of the
+    composite is defined on the ROI. Packing is host-side set-up
+    (numpy packbits), done once per shard."""
+
+    def __init__(self, shard: ImageShard, boxes: "BoxTable", masks_per_box):
+        rois = box_rois(boxes, shard)
+        words, off = [], [0]
+        for (u0, v0, u1, v1), m in zip(rois, masks_per_box):
+            m = torch.as_tensor(m).cpu().numpy()
+            sub = (m[v0:v1, u0:u1] != 0) if (u1 > u0 and v1 > v0) else np.zeros((0, 0), dtype=bool)
+            nrows, ncols = (sub.shape if sub.size else (0, 0))
+            wpr = (ncols + 31) // 32
+            if nrows * wpr:
+                padded = np.zeros((nrows, wpr * 32), dtype=np.uint8)
+                padded[:, :ncols] = sub
+                w = np.packbits(padded, axis=1, bitorder="little").view("<u4").reshape(-1)
+                words.append(w)
+            off.append(off[-1] + nrows * wpr)
+        allw = np.concatenate(words) if words else np.zeros(0, dtype=np.uint32)
+        if allw.size == 0:
+            allw = np.zeros(1, dtype=np.uint32)
+        self.host_bits, self.host_off = allw, np.asarray(off, dtype=np.int64)
+        self.bits = torch.from_numpy(allw.view(np.int32).copy()).to(shard.device)
+        self.off = torch.from_numpy(self.host_off.copy()).to(shard.device)
+        self.n_boxes = len(rois)
+
+
 class ScoreWorkspace:
     """Caller-owned buffers of ``score_topk`` so a steady-state loop allocates
     nothing (and so the top-k records can be written straight into a registered
@@ -153,7 +198,7 @@ def score_topk(shard: ImageShard, boxes: BoxTable, cubes: torch.Tensor | None, N
 
     -> dict(records (n_boxes,k,20) f32 [idx bits, score, cube15, s_iou, s_pts, s_seg],
             idx (n_boxes,k) i32 view, score (n_boxes,k);
-            with want_all: scores, iou (n_boxes,N) f32, count (n_boxes,N) i32,
+            with want_all: scores, iou, seg (n_boxes,N) f32, count (n_boxes,N) i32,
             proj (n_boxes,N,4), npts (n_boxes,) i32)."""
     lib = _abi.load()
     cfg = cfg or ScoreConfig()
@@ -179,17 +224,22 @@ def score_topk(shard: ImageShard, boxes: BoxTable, cubes: torch.Tensor | None, N
     if want_all:
         outs["scores"] = torch.empty((nb, N), dtype=torch.float32, device=dev)
         outs["iou"] = torch.empty((nb, N), dtype=torch.float32, device=dev)
+        outs["seg"] = torch.empty((nb, N), dtype=torch.float32, device=dev)
         outs["count"] = torch.empty((nb, N), dtype=torch.int32, device=dev)
         outs["proj"] = torch.empty((nb, N, 4), dtype=torch.float32, device=dev)
         outs["npts"] = torch.empty((nb,), dtype=torch.int32, device=dev)
     seg_bits = seg_off = None
     if seg is not None:
-        seg_bits, seg_off = seg
+        seg_bits, seg_off = seg.bits, seg.off
+        assert seg.n_boxes == nb
+    elif cfg.e_seg > 0:
+        raise _abi.WcrError("score_topk: e_seg > 0 needs seg=SegMasks(...)")
     _abi.check(lib.wcr_score_topk(
         shard.table.data_ptr(), boxes.table.data_ptr(), nb, _abi.ptr(cubes), N,
         _abi.ptr(priors), _abi.ptr(normals), _abi.ptr(z0), ctypes.byref(sp), int(seed),
         _abi.ptr(seg_bits), _abi.ptr(seg_off), ctypes.byref(sc), cfg.k, rec.data_ptr(),
-        _abi.ptr(outs.get("scores")), _abi.ptr(outs.get("iou")), _abi.ptr(outs.get("count")),
+        _abi.ptr(outs.get("scores")), _abi.ptr(outs.get("iou")), _abi.ptr(outs.get("seg")),
+        _abi.ptr(outs.get("count")),
         _abi.ptr(outs.get("proj")), _abi.ptr(outs.get("npts")), workspace.ws.data_ptr(),
         _abi.stream_ptr(dev)), "wcr_score_topk")
     rec = rec[:nb]
