@@ -207,6 +207,59 @@ int wcr_score_topk(const WcrImage *images, const WcrBox *boxes, int n_boxes,
                    int32_t *out_count, float *out_proj, int32_t *out_npts,
                    void *ws, void *stream);
 
+/* ------------------------------------------------- block-level drop-ins -- */
+/* One launch behind each helper the reference exposes by name (SURVEY A2.1-A2.5,
+ * A3.2-A3.8); the fused entry points above use the same device functions. */
+
+/* cubercnn/util/math_util.py:142-217 get_cuboid_verts_faces, as wrapped by
+ * Cubes.get_all_corners (ProposalNetwork/utils/spaces.py:192-204).
+ *   cubes [n][15] -> out_corners [n][8][3] */
+int wcr_cube_corners(const float *cubes, int64_t n, float *out_corners, void *stream);
+
+/* Cubes.get_bube_corners(K, clamp) (spaces.py:224-245) and cubes_to_box
+ * (ProposalNetwork/utils/conversions.py:25-48): K @ corners, divide by z, clamp to
+ * [int(-c/2+1), int(c-1+c)], min/max. Either output may be NULL.
+ *   out_corners [n][8][2], out_boxes [n][4] (x1 y1 x2 y2) */
+int wcr_bube_corners(const float *cubes, int64_t n, float fx, float fy, float cx, float cy,
+                     float clamp0, float clamp1, float *out_corners, float *out_boxes,
+                     void *stream);
+
+/* ProposalNetwork/utils/utils.py:181-187 iou_2d (detectron2 pairwise_iou of ONE
+ * GT box against P boxes).  gt_box [4] device, boxes [P][4] 16-byte aligned. */
+int wcr_iou_2d(const float *gt_box, const float *boxes, int64_t P, float *out_iou, void *stream);
+
+/* utils.py:490-493 convex_hull(mask, coords) = fill_polygon(jarvis_march(coords)):
+ * soft mask in [0,1], product of the clamped half-plane values of every hull edge.
+ *   coords [n_points][2] device (1..32 points), out_mask H x W, row pitch `pitch`.
+ * An unclosed march (the reference would not terminate) gives zeros. */
+int wcr_convex_hull(const float *coords, int n_points, int H, int W, float *out_mask,
+                    int64_t pitch, void *stream);
+
+/* utils.py:225-234 mask_iou (mode 0) / :236-245 mod_mask_iou (mode 1).
+ *   seg: numel u8 (seg_is_float == 0) or f32 values; bube: numel f32;
+ *   out [1]; ws: 32 bytes of device scratch, 8-byte aligned. */
+int wcr_mask_iou(const void *seg, int seg_is_float, const float *bube, int64_t numel, int mode,
+                 float *out, void *ws, void *stream);
+
+/* utils.py:41-59 sample_normal_in_range with the in-kernel Philox4x32-10 generator
+ * (counter = (column, row, tag, block), key = seed): out [M][count]; with
+ * has_thresholds every element is redrawn until it lies in
+ * [threshold_low, threshold_high[m]] (at most max_tries draws, then clamped). */
+int wcr_sample_normal_in_range(const float *means, const float *stds, int M, int count,
+                               int has_thresholds, float threshold_low,
+                               const float *threshold_high, uint64_t seed, int max_tries,
+                               float *out, void *stream);
+
+/* utils.py:119-131 orthobasis_from_normal_t (with :111-117 vec_perp_t and :133-145
+ * rotate_vector_t): normal [3], yaw [T] -> out_R [T][3][3], columns [x, n, y]. */
+int wcr_orthobasis_from_normal(const float *normal, const float *yaw, int T, float *out_R,
+                               void *stream);
+
+/* utils.py:169-176 vectorized_linspace: out [M][steps] =
+ * arange(steps) * ((end - start) / (steps - 1)) + start. */
+int wcr_vectorized_linspace(const float *start, const float *end, int M, int steps, float *out,
+                            void *stream);
+
 /* ---------------------------------------------------------------- step 4 -- */
 
 /* Weak-loss block of ROIHeads3DScore._forward_cube (roi_heads.py:786-905 decode,

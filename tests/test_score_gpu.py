@@ -13,7 +13,7 @@ pytestmark = pytest.mark.gpu
 RTOL = 1e-5
 
 
-def _setup(n_images, H=480, W=640, n_boxes=4, first=0):
+def _setup(n_images, H=480, W=640, n_boxes=4, first=0, clamp=None):
     from wcr import synth
     from wcr.images import ImageShard
     from wcr.proposals import BoxTable
@@ -21,7 +21,8 @@ def _setup(n_images, H=480, W=640, n_boxes=4, first=0):
            for i in range(n_images)]
     shard = ImageShard([im["depth"].cuda() for im in ims], [im["ground"].cuda() for im in ims],
                        [im["K"] for im in ims])
-    boxes = BoxTable(shard, [im["boxes"] for im in ims], [im["classes"] for im in ims])
+    boxes = BoxTable(shard, [im["boxes"] for im in ims], [im["classes"] for im in ims],
+                     clamp=None if clamp is None else [clamp] * n_images)
     normals = torch.tensor([[0.01 * i, 1.0, -0.02 * i] for i in range(n_images)])
     normals = normals / normals.norm(dim=1, keepdim=True)
     return ims, shard, boxes, synth.make_priors(), normals
@@ -205,7 +206,10 @@ def test_score_seg_term_bit_exact(cuda_lib, N, H, W, mode, eseg):
     (integer pixel counts), and so must the top-k with the seg factor."""
     from wcr import synth
     from wcr.proposals import propose, score_topk, ScoreConfig, SegMasks
-    ims, shard, boxes, priors, normals = _setup(2, H, W, n_boxes=3, first=60)
+    # the ROI head hands [H, W] as the clamp tuple (x clamped by H!); on the wide image
+    # use (W, H) so that the hulls are not all squeezed into x < H
+    clamp = (H, W) if W < 2 * H else (W, H)
+    ims, shard, boxes, priors, normals = _setup(2, H, W, n_boxes=3, first=60, clamp=clamp)
     masks = [m for im in ims for m in synth.seg_masks(im["boxes"], H, W)]
     seg = SegMasks(shard, boxes, masks)
     cubes = propose(shard, boxes, priors, normals, N, seed=5)
@@ -218,7 +222,7 @@ def test_score_seg_term_bit_exact(cuda_lib, N, H, W, mode, eseg):
     gb = 0
     for im in ims:
         for b in range(len(im["boxes"])):
-            ref = oc.score_box(im["depth"].numpy(), im["K"].numpy(), im["boxes"][b].numpy(), (H, W),
+            ref = oc.score_box(im["depth"].numpy(), im["K"].numpy(), im["boxes"][b].numpy(), clamp,
                                cubes_h[gb], 1, 1, 1, eseg, mode, masks[gb].numpy())
             assert np.array_equal(res["count"][gb].cpu().numpy(), ref["count"])
             np.testing.assert_allclose(res["seg"][gb].cpu().numpy(), ref["seg"], rtol=RTOL)

@@ -40,6 +40,16 @@ SIGNATURES = {
                                c_void_p, c_void_p, c_u64, c_void_p, c_void_p, c_void_p, c_int,
                                c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
                                c_void_p, c_void_p, c_void_p]),
+    "wcr_cube_corners": (c_int, [c_void_p, c_i64, c_void_p, c_void_p]),
+    "wcr_bube_corners": (c_int, [c_void_p, c_i64, c_float, c_float, c_float, c_float, c_float,
+                                 c_float, c_void_p, c_void_p, c_void_p]),
+    "wcr_iou_2d": (c_int, [c_void_p, c_void_p, c_i64, c_void_p, c_void_p]),
+    "wcr_convex_hull": (c_int, [c_void_p, c_int, c_int, c_int, c_void_p, c_i64, c_void_p]),
+    "wcr_mask_iou": (c_int, [c_void_p, c_int, c_void_p, c_i64, c_int, c_void_p, c_void_p, c_void_p]),
+    "wcr_sample_normal_in_range": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_float,
+                                           c_void_p, c_u64, c_int, c_void_p, c_void_p]),
+    "wcr_orthobasis_from_normal": (c_int, [c_void_p, c_void_p, c_int, c_void_p, c_void_p]),
+    "wcr_vectorized_linspace": (c_int, [c_void_p, c_void_p, c_int, c_int, c_void_p, c_void_p]),
     "wcr_weak_loss_fwd": (c_int, [c_void_p, c_void_p, c_void_p]),
     "wcr_weak_loss_bwd": (c_int, [c_void_p, c_void_p, c_void_p]),
 }
