@@ -31,6 +31,7 @@ sys.path.insert(0, os.path.join(ROOT, "weak-cube-r-cnn_b200"))
 IMAGES_PER_GPU = 64
 H, W, NPROP, TOPK = 480, 640, 1000, 16
 ALG_FLOP_PER_TEST = 18.0      # 3 sub + 9 mul + 6 add per (proposal, point)
+EXEC_FLOP_PER_TEST = 12.0     # what the kernel issues: 6 FFMA
 FP32_NOMINAL_TFLOPS = 148 * 128 * 2 * 1.965e9 / 1e12   # 74.4, SURVEY §8d
 METRIC = "cube proposals scored/sec"
 
@@ -42,18 +43,31 @@ def parse():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="wcr", choices=["wcr", "reference"])
     ap.add_argument("--images", type=int, default=IMAGES_PER_GPU, help="images per GPU")
-    ap.add_argument("--cpu-sample-images", type=int, default=2)
+    ap.add_argument("--cpu-sample-images", type=int, default=None,
+                    help="images of the workload the CPU arm processes (default: 24 for the "
+                         "cpu_baseline leg, 6 per step for --impl reference)")
+    ap.add_argument("--no-seg", action="store_true", help="skip the mask-coverage term")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     return ap.parse_args()
 
 
-def workload_name(images):
+def workload_name(images, seg=True):
     return (f"SUN RGB-D val-shaped batch: {images} images {W}x{H} per GPU, ~20 GT boxes/image "
-            f"(Poisson), {NPROP} proposals/box, top-{TOPK}")
+            f"(Poisson), {NPROP} proposals/box, score = IoU2D x point-in-cube"
+            f"{' x mask coverage' if seg else ''}, top-{TOPK}")
+
+
+def make_images(n, first, seg):
+    from wcr import synth
+    ims = synth.make_batch(n, H, W, first=first)
+    if seg:
+        for im in ims:
+            im["seg"] = synth.seg_masks(im["boxes"], H, W)
+    return ims
 
 
 # ------------------------------------------------------------------ CPU arm --
-def cpu_arm(n_images: int, first: int = 0, repeats: int = 1):
+def cpu_arm(n_images: int, first: int = 0, repeats: int = 1, seg: bool = True):
     """Time the oracle's C restatement (OpenMP, all cores) on `n_images` images of
     the workload. Returns (proposals/s, cores, sample string, seconds)."""
     import numpy as np
@@ -61,7 +75,7 @@ def cpu_arm(n_images: int, first: int = 0, repeats: int = 1):
     from oracle import clib, cubes as oc, ground as og
     from wcr import synth
     import random
-    ims = synth.make_batch(n_images, H, W, first=first)
+    ims = make_images(n_images, first, seg)
     priors = synth.make_priors()
     rng = np.random.default_rng(0)
     n_prop = 0
@@ -90,7 +104,8 @@ def cpu_arm(n_images: int, first: int = 0, repeats: int = 1):
                     a[3 + d] = np.clip(rng.normal(pm[0, d], pm[1, d], NPROP), 0.05, pm[0, d] + 3 * pm[1, d])
                 a[6] = rng.uniform(0, np.pi, NPROP)
                 cubes = oc.assemble_cubes(K, normal, a)
-                r = oc.score_box(depth, K, box, (H, W), cubes)
+                r = oc.score_box(depth, K, box, (H, W), cubes, 1, 1, 1, 1 if seg else 0, 0,
+                                 im["seg"][b].numpy() if seg else None, fast_seg=True)
                 oc.topk(r["score"], TOPK)
                 n_prop += NPROP
     dt = time.perf_counter() - t0
@@ -106,13 +121,14 @@ def run_reference(args):
         return
     from oracle import clib
     clib.build()
-    n = max(1, args.cpu_sample_images)
-    cpu_arm(1)  # warm
+    n = max(1, args.cpu_sample_images or 6)
+    seg = not args.no_seg
+    cpu_arm(1, seg=seg)  # warm
     vals, secs = [], 0.0
     for w in range(args.warmup):
-        cpu_arm(1, first=w)
+        cpu_arm(1, first=w, seg=seg)
     for s in range(args.steps):
-        v, cores, sample, dt = cpu_arm(n, first=s * n)
+        v, cores, sample, dt = cpu_arm(n, first=s * n, seg=seg)
         vals.append(v); secs += dt
     value = sum(vals) / len(vals)
     line = {
@@ -120,7 +136,7 @@ def run_reference(args):
         "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": 1e3 * secs / args.steps, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": workload_name(args.images), "step_sample": sample},
+        "config": {"workload": workload_name(args.images, seg), "step_sample": sample},
         "cpu_baseline": {"value": value, "unit": "proposals/s", "cores": cores, "kind": "port",
                          "sample": sample},
         "e2e": {"value": value, "unit": "proposals/s", "h2d_bytes_per_step": 0,
@@ -128,6 +144,25 @@ def run_reference(args):
         "gpu_launches": 0,
     }
     print(json.dumps(line), flush=True)
+
+
+def ncu_traffic_bytes():
+    """dram__bytes_read.sum + dram__bytes_write.sum of one scoring launch, from the
+    newest committed `ncu --set full` summary (profiles/score_items_r*.txt); None when
+    there is none. A profiler-derived figure, reported beside the event timing."""
+    import glob
+    import re
+    files = sorted(glob.glob(os.path.join(ROOT, "profiles", "score_items_r*.txt")))
+    if not files:
+        return None
+    unit = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
+    total, seen = 0.0, 0
+    for line in open(files[-1]):
+        m = re.match(r"(dram__bytes_(?:read|write)\.sum)\s+([0-9.]+)\s+(\w+)", line)
+        if m and m.group(3) in unit:
+            total += float(m.group(2)) * unit[m.group(3)]
+            seen += 1
+    return total if seen == 2 else None
 
 
 # ------------------------------------------------------------------ GPU arm --
@@ -188,11 +223,13 @@ def run_wcr(args):
     _abi.check(lib.wcr_device_check(), "wcr_device_check")
 
     # weak scaling: every rank owns `images` images of the global synthetic set
-    ims = synth.make_batch(args.images, H, W, first=rank * args.images)
+    use_seg = not args.no_seg
+    ims = make_images(args.images, rank * args.images, use_seg)
     priors = synth.make_priors()
     n_local_boxes = sum(len(im["boxes"]) for im in ims)
     gather = wdist.TopkGather(n_local_boxes, TOPK, dev)
-    runner = ShardRunner(ims, NPROP, dev, priors=priors, score_cfg=ScoreConfig(k=TOPK), seed=1234,
+    runner = ShardRunner(ims, NPROP, dev, priors=priors,
+                         score_cfg=ScoreConfig(k=TOPK, e_seg=1 if use_seg else 0), seed=1234,
                          records=gather.send)
     runner.upload()
     torch.cuda.synchronize()
@@ -207,7 +244,7 @@ def run_wcr(args):
     runner.step()
     z0 = box_center_depth(runner.shard, runner.boxes)
     full = score_topk(runner.shard, runner.boxes, None, NPROP, runner.score_cfg, priors=runner.priors,
-                      normals=runner.normals, z0=z0, seed=1234, want_all=True)
+                      normals=runner.normals, z0=z0, seed=1234, seg=runner.seg, want_all=True)
     tests_per_launch = float(full["npts"].sum().item()) * NPROP
     del full
 
@@ -291,7 +328,7 @@ def run_wcr(args):
             "unit": "proposals/s", "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
             "ms_per_step": step_ms / args.steps, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": workload_name(args.images), "l2": "256 MiB flush between timed steps",
+            "config": {"workload": workload_name(args.images, use_seg), "l2": "256 MiB flush between timed steps",
                        "parallelism": f"image-sharded x{world}, all-gather of top-k records",
                        "boxes_rank0": runner.n_boxes, "rng": "in-kernel Philox4x32-10"},
             "e2e": {"value": total_props * args.steps / e2e_s, "unit": "proposals/s",
@@ -304,8 +341,12 @@ def run_wcr(args):
                          "peak_source": "FFMA probe kernel timed in this run (MEASURED_PEAKS.json has no FP32 figure)",
                          "frac_of_nominal_74.4": achieved / FP32_NOMINAL_TFLOPS,
                          "point_tests_per_s": tests_per_launch / (score_ms * 1e-3),
-                         "alg_flop_per_test": ALG_FLOP_PER_TEST, "kernel_ms": score_ms,
-                         "kernel_share_of_step": score_ms * args.steps / step_ms, "traffic": None},
+                         "alg_flop_per_test": ALG_FLOP_PER_TEST,
+                         "executed_flop_per_test": EXEC_FLOP_PER_TEST,
+                         "frac_executed": achieved * EXEC_FLOP_PER_TEST / ALG_FLOP_PER_TEST / fp32_probe_tflops,
+                         "kernel_ms": score_ms,
+                         "kernel_share_of_step": score_ms * args.steps / step_ms,
+                         "traffic": ncu_traffic_bytes()},
             "roofline_aux": {"bound": "hbm", "kernel": "unproject_cloud_kernel", "achieved": cloud_gbs,
                              "peak": hbm_peak, "unit": "GB/s", "frac": cloud_gbs / hbm_peak,
                              "bytes_per_launch": cloud_bytes},
@@ -313,8 +354,8 @@ def run_wcr(args):
         if not args.no_cpu_baseline and world == 1:
             from oracle import clib
             clib.build()
-            cpu_arm(1)
-            v, cores, sample, dt = cpu_arm(args.cpu_sample_images)
+            cpu_arm(1, seg=use_seg)
+            v, cores, sample, dt = cpu_arm(args.cpu_sample_images or 24, seg=use_seg)
             line["cpu_baseline"] = {"value": v, "unit": "proposals/s", "cores": cores,
                                     "kind": "port", "sample": sample, "seconds": dt}
         print(json.dumps(line), flush=True)

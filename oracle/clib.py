@@ -96,9 +96,11 @@ def project_cube(cube: np.ndarray, K4: np.ndarray, clamp0: float, clamp1: float)
 
 def score_box(depth: np.ndarray, K4: np.ndarray, gbox: np.ndarray, clamp0: float, clamp1: float,
               cubes: np.ndarray, stride: int = 1, e_iou: int = 1, e_pts: int = 1, e_seg: int = 0,
-              seg_mode: int = 0, seg: np.ndarray | None = None):
+              seg_mode: int = 0, seg: np.ndarray | None = None, fast_seg: bool = False):
     """-> dict(score (N,), iou (N,), count (N,) i32, proj (N,4), seg (N,), npts int).
-    ``seg``: full-image (H, W) u8 mask of THIS box (only its integer ROI is read)."""
+    ``seg``: full-image (H, W) u8 mask of THIS box (only its integer ROI is read).
+    ``fast_seg``: evaluate the mask term with orc_seg_term_fast (same result; what the
+    timed CPU baseline uses)."""
     depth = np.ascontiguousarray(depth, dtype=np.float32)
     K4 = np.ascontiguousarray(K4, dtype=np.float32)
     gbox = np.ascontiguousarray(gbox, dtype=np.float32)
@@ -117,7 +119,7 @@ def score_box(depth: np.ndarray, K4: np.ndarray, gbox: np.ndarray, clamp0: float
     npts = fn(_p(depth, c_f), c_i(depth.shape[0]), c_i(depth.shape[1]), c_i(depth.shape[1]),
               _p(K4, c_f), _p(gbox, c_f), c_f(clamp0), c_f(clamp1), _p(cubes, c_f), c_i(N),
               c_i(stride), c_i(e_iou), c_i(e_pts), c_i(e_seg if seg is not None else 0),
-              c_i(seg_mode), _p(seg, ctypes.c_uint8) if seg is not None else None,
+              c_i(seg_mode | (256 if fast_seg else 0)), _p(seg, ctypes.c_uint8) if seg is not None else None,
               c_i(depth.shape[1]), _p(score, c_f), _p(iou, c_f), _p(count, ctypes.c_int32),
               _p(proj, c_f), _p(sseg, c_f))
     return {"score": score, "iou": iou, "count": count, "proj": proj, "seg": sseg,

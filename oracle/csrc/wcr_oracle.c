@@ -12,6 +12,7 @@
 #include <math.h>
 #include <stdint.h>
 #include <stddef.h>
+#include <stdlib.h>
 #ifdef _OPENMP
 #include <omp.h>
 #endif
@@ -288,7 +289,8 @@ static inline void seg_clamp_corners(const float *corners, float clamp0, float c
  * 410-493 and roi_heads.py:428, 950-952):
  *   coords = second-clamped projected corners; hull = jarvis_march(coords);
  *   bube   = pixels (X, Y) of the H x W image with val_i > 0 for every hull edge,
- *            rows restricted to [floor(min_y) - 1, ceil(max_y) + 1] (identical to
+ *            restricted to the hull's bounding box grown by one pixel,
+ *            [floor(min) - 1, ceil(max) + 1] in x and y (identical to
  *            fill_polygon(...) > 0 for non-degenerate hulls);
  *   seg    = the box's mask restricted to its integer ROI [u0,u1) x [v0,v1);
  *   inter  = |seg & bube|, uni = |seg| + |bube| - inter;
@@ -305,11 +307,17 @@ float orc_seg_term(const float *corners, float clamp0, float clamp1, const uint8
     seg_clamp_corners(corners, clamp0, clamp1, c2);
     const int m = orc_jarvis_march(c2, 8, hull);
     if (m < 1) return 0.f;
-    float mny = hull[1], mxy = hull[1];
-    for (int i = 1; i < m; ++i) { mny = fminf(mny, hull[2 * i + 1]); mxy = fmaxf(mxy, hull[2 * i + 1]); }
+    float mny = hull[1], mxy = hull[1], mnx = hull[0], mxx = hull[0];
+    for (int i = 1; i < m; ++i) {
+        mny = fminf(mny, hull[2 * i + 1]); mxy = fmaxf(mxy, hull[2 * i + 1]);
+        mnx = fminf(mnx, hull[2 * i]); mxx = fmaxf(mxx, hull[2 * i]);
+    }
     int r0 = (int)floorf(mny) - 1, r1 = (int)ceilf(mxy) + 1;
+    int c0 = (int)floorf(mnx) - 1, c1 = (int)ceilf(mxx) + 1;
     if (r0 < 0) r0 = 0;
     if (r1 > H - 1) r1 = H - 1;
+    if (c0 < 0) c0 = 0;
+    if (c1 > W - 1) c1 = W - 1;
     if (seg_area < 0) {
         seg_area = 0;
         for (int v = roi[1]; v < roi[3]; ++v)
@@ -317,7 +325,7 @@ float orc_seg_term(const float *corners, float clamp0, float clamp1, const uint8
     }
     int inter = 0, bube = 0;
     for (int Y = r0; Y <= r1; ++Y)
-        for (int X = 0; X < W; ++X) {
+        for (int X = c0; X <= c1; ++X) {
             int in = 1;
             for (int i = 0; i < m && in; ++i) {
                 const float *v1 = hull + 2 * i, *v2 = hull + 2 * ((i + 1) % m);
@@ -332,6 +340,73 @@ float orc_seg_term(const float *corners, float clamp0, float clamp1, const uint8
         }
     if (out_inter) *out_inter = inter;
     if (out_bube) *out_bube = bube;
+    if (inter == 0) return 0.f;
+    const float fi = (float)inter, fu = (float)(seg_area + bube - inter);
+    if (mode == 1) return ((((fi * fi) * fi) * fi) * fi) / fu;
+    return fi / fu;
+}
+
+/* Same composite term, evaluated the way a tuned CPU port would (used by the timed
+ * CPU baseline, checked equal to orc_seg_term in tests/test_oracle_hull.py):
+ * val_i(X) is monotone in X under IEEE rounding, so each hull edge cuts an integer
+ * half-line out of a pixel row; the row's interior is an interval found by one
+ * division plus an exact fix-up, and |seg & row interval| comes from per-row prefix
+ * sums of the box mask (rowpre [nrows][ncols + 1]). */
+float orc_seg_term_fast(const float *corners, float clamp0, float clamp1, int H, int W,
+                        const int *roi, const int *rowpre, int seg_area, int mode)
+{
+    float c2[16], hull[16];
+    for (int i = 0; i < 16; ++i) if (!(fabsf(corners[i]) <= 3.402823466e38f)) return 0.f;
+    seg_clamp_corners(corners, clamp0, clamp1, c2);
+    const int m = orc_jarvis_march(c2, 8, hull);
+    if (m < 1) return 0.f;
+    float mny = hull[1], mxy = hull[1], mnx = hull[0], mxx = hull[0];
+    for (int i = 1; i < m; ++i) {
+        mny = fminf(mny, hull[2 * i + 1]); mxy = fmaxf(mxy, hull[2 * i + 1]);
+        mnx = fminf(mnx, hull[2 * i]); mxx = fmaxf(mxx, hull[2 * i]);
+    }
+    int r0 = (int)floorf(mny) - 1, r1 = (int)ceilf(mxy) + 1;
+    int c0 = (int)floorf(mnx) - 1, c1 = (int)ceilf(mxx) + 1;
+    if (r0 < 0) r0 = 0;
+    if (r1 > H - 1) r1 = H - 1;
+    if (c0 < 0) c0 = 0;
+    if (c1 > W - 1) c1 = W - 1;
+    const int ncols = roi[2] - roi[0], nrows = roi[3] - roi[1];
+    int inter = 0, bube = 0;
+    for (int Yi = r0; Yi <= r1; ++Yi) {
+        const float Y = (float)Yi;
+        int lo = c0, hi = c1;
+        for (int i = 0; i < m && lo <= hi; ++i) {
+            const float *v1 = hull + 2 * i, *v2 = hull + 2 * ((i + 1) % m);
+            const float ex = v2[0] - v1[0], ey = v2[1] - v1[1];
+            const float t2 = (Y - v1[1]) * ex;
+            if (ey == 0.f) {
+                if (!(((float)lo - v1[0]) * ey > t2)) hi = -1;
+            } else if (ey > 0.f) {
+                float xs = floorf(v1[0] + t2 / ey) + 1.f;
+                xs = xs != xs ? (float)lo : xs;
+                int X = (int)fminf(fmaxf(xs, (float)lo), (float)(hi + 1));
+                while (X > lo && ((float)(X - 1) - v1[0]) * ey > t2) --X;
+                while (X <= hi && !(((float)X - v1[0]) * ey > t2)) ++X;
+                lo = X;
+            } else {
+                float xs = ceilf(v1[0] + t2 / ey) - 1.f;
+                xs = xs != xs ? (float)hi : xs;
+                int X = (int)fminf(fmaxf(xs, (float)(lo - 1)), (float)hi);
+                while (X < hi && ((float)(X + 1) - v1[0]) * ey > t2) ++X;
+                while (X >= lo && !(((float)X - v1[0]) * ey > t2)) --X;
+                hi = X;
+            }
+        }
+        if (lo > hi) continue;
+        bube += hi - lo + 1;
+        const int row = Yi - roi[1];
+        if (row >= 0 && row < nrows) {
+            const int a = (lo > roi[0] ? lo : roi[0]) - roi[0];
+            const int b = (hi < roi[2] - 1 ? hi : roi[2] - 1) - roi[0];
+            if (a <= b) inter += rowpre[(size_t)row * (ncols + 1) + b + 1] - rowpre[(size_t)row * (ncols + 1) + a];
+        }
+    }
     if (inter == 0) return 0.f;
     const float fi = (float)inter, fu = (float)(seg_area + bube - inter);
     if (mode == 1) return ((((fi * fi) * fi) * fi) * fi) / fu;
@@ -365,9 +440,23 @@ int orc_score_box_seg(const float *depth, int H, int W, int pitch, const float *
     /* the mask term always uses the stride-1 integer ROI */
     const int roi[4] = {u0, v0, u1, v1};
     int seg_area = 0;
-    if (e_seg > 0 && seg)
+    /* seg_mode bit 8: use orc_seg_term_fast (timed CPU baseline) instead of the
+     * per-pixel definition */
+    const int fast = (seg_mode >> 8) & 1;
+    seg_mode &= 0xff;
+    int *rowpre = NULL;
+    if (e_seg > 0 && seg) {
         for (int v = v0; v < v1; ++v)
             for (int u = u0; u < u1; ++u) seg_area += seg[(size_t)v * seg_pitch + u] > 0;
+        if (fast && u1 > u0 && v1 > v0) {
+            rowpre = (int *)malloc(sizeof(int) * (size_t)(v1 - v0) * (u1 - u0 + 1));
+            for (int v = v0; v < v1; ++v) {
+                int *rp = rowpre + (size_t)(v - v0) * (u1 - u0 + 1);
+                rp[0] = 0;
+                for (int u = u0; u < u1; ++u) rp[u - u0 + 1] = rp[u - u0] + (seg[(size_t)v * seg_pitch + u] > 0);
+            }
+        }
+    }
     if (e_pts > 0)
         for (int v = v0; v < v1; v += stride)
             for (int u = u0; u < u1; u += stride) {
@@ -406,14 +495,17 @@ int orc_score_box_seg(const float *depth, int H, int W, int pitch, const float *
         const float spts = npts > 0 ? (float)cnt / (float)npts : 0.f;
         float sseg = 1.f;
         if (e_seg > 0 && seg)
-            sseg = orc_seg_term(corners, clamp0, clamp1, seg, H, W, seg_pitch, roi, seg_area,
-                                seg_mode, NULL, NULL);
+            sseg = rowpre ? orc_seg_term_fast(corners, clamp0, clamp1, H, W, roi, rowpre, seg_area, seg_mode)
+                 : (fast ? 0.f
+                         : orc_seg_term(corners, clamp0, clamp1, seg, H, W, seg_pitch, roi, seg_area,
+                                        seg_mode, NULL, NULL));
         out_score[j] = (ipow_(siou, e_iou) * ipow_(spts, e_pts)) * ipow_(sseg, e_seg);
         if (out_seg) out_seg[j] = sseg;
         if (out_iou) out_iou[j] = siou;
         if (out_count) out_count[j] = cnt;
         if (out_proj) { out_proj[4 * j] = pb[0]; out_proj[4 * j + 1] = pb[1]; out_proj[4 * j + 2] = pb[2]; out_proj[4 * j + 3] = pb[3]; }
     }
+    free(rowpre);
     return npts;
 }
 

@@ -45,9 +45,9 @@ def project_cube(cube, K, clamp):
 
 
 def score_box(depth, K, gbox, clamp, cubes, stride=1, e_iou=1, e_pts=1, e_seg=0, seg_mode=0,
-              seg=None):
+              seg=None, fast_seg=False):
     return clib.score_box(depth, K4_of(K), gbox, float(clamp[0]), float(clamp[1]), cubes, stride,
-                          e_iou, e_pts, e_seg, seg_mode, seg)
+                          e_iou, e_pts, e_seg, seg_mode, seg, fast_seg)
 
 
 def box_roi(gbox, H, W):

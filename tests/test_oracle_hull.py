@@ -85,3 +85,31 @@ def test_seg_term_equals_full_image_fill():
         assert inter == int((full & (seg > 0)).sum())
         want = oh.mask_iou(seg, full)
         assert s == want
+
+
+def test_fast_seg_term_equals_definition():
+    """orc_seg_term_fast (row intervals + prefix sums; the timed CPU baseline) ==
+    orc_seg_term (per-pixel definition) through score_box, bit for bit."""
+    import torch
+    from oracle import cubes as oc
+    g = torch.Generator().manual_seed(9)
+    H, W = 96, 128
+    depth = (1.0 + 3.0 * torch.rand(H, W, generator=g)).numpy()
+    K = np.array([[110.0, 0, 64], [0, 110, 48], [0, 0, 1]], np.float32)
+    N = 300
+    attrs = np.zeros((7, N), np.float32)
+    attrs[0] = 64 + 40 * torch.randn(N, generator=g).numpy()
+    attrs[1] = 48 + 30 * torch.randn(N, generator=g).numpy()
+    attrs[2] = 1.0 + 3 * torch.rand(N, generator=g).numpy()
+    attrs[3:6] = 0.2 + 1.5 * torch.rand(3, N, generator=g).numpy()
+    attrs[6] = np.pi * torch.rand(N, generator=g).numpy()
+    cubes = oc.assemble_cubes(K, np.array([0.0, 1.0, 0.0], np.float32), attrs)
+    gbox = np.array([20.3, 10.1, 100.9, 80.2], np.float32)
+    seg = np.zeros((H, W), np.uint8)
+    seg[15:70, 30:90] = (torch.rand(55, 60, generator=g) < 0.6).numpy()
+    for mode in (0, 1):
+        for clamp in ((H, W), (W, H)):
+            a = oc.score_box(depth, K, gbox, clamp, cubes, 1, 1, 1, 1, mode, seg)
+            b = oc.score_box(depth, K, gbox, clamp, cubes, 1, 1, 1, 1, mode, seg, fast_seg=True)
+            assert np.array_equal(a["seg"], b["seg"]) and np.array_equal(a["score"], b["score"])
+            assert (a["seg"] > 0).any()

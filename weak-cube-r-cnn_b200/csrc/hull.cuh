@@ -131,8 +131,8 @@ __device__ __forceinline__ int seg_popc_range(const SegBox &sb, int row, int a, 
 }
 
 // Composite mask term of one cube (project spec, see orc_seg_term): pixels (X, Y)
-// of the H x W image with val_i > 0 for every hull edge, rows restricted to
-// [floor(min_y) - 1, ceil(max_y) + 1]. val_i(X) is monotone in X under IEEE
+// of the H x W image with val_i > 0 for every hull edge, restricted to the hull's
+// bounding box grown by one pixel. val_i(X) is monotone in X under IEEE
 // rounding, so every edge cuts an integer half-line out of the row: the row's
 // interior is an interval [lo, hi] found by one division + an exact fix-up
 // instead of a per-pixel test. inter = |seg & bube|, uni = |seg| + |bube| - inter.
@@ -140,13 +140,18 @@ template <class A>
 __device__ float seg_term(A hx, A hy, int m, int H, int W, const SegBox &sb, int mode)
 {
     if (m < 1) return 0.f;
-    float mny = hy(0), mxy = mny;
-    for (int i = 1; i < m; ++i) { const float y = hy(i); mny = fminf(mny, y); mxy = fmaxf(mxy, y); }
+    float mny = hy(0), mxy = mny, mnx = hx(0), mxx = mnx;
+    for (int i = 1; i < m; ++i) {
+        const float y = hy(i), x = hx(i);
+        mny = fminf(mny, y); mxy = fmaxf(mxy, y);
+        mnx = fminf(mnx, x); mxx = fmaxf(mxx, x);
+    }
     const int r0 = max((int)floorf(mny) - 1, 0), r1 = min((int)ceilf(mxy) + 1, H - 1);
+    const int c0 = max((int)floorf(mnx) - 1, 0), c1 = min((int)ceilf(mxx) + 1, W - 1);
     int inter = 0, bube = 0;
     for (int Yi = r0; Yi <= r1; ++Yi) {
         const float Y = (float)Yi;
-        int lo = 0, hi = W - 1;
+        int lo = c0, hi = c1;
         for (int i = 0; i < m && lo <= hi; ++i) {
             const int i2 = (i + 1 == m) ? 0 : i + 1;
             const float v1x = hx(i), v1y = hy(i);

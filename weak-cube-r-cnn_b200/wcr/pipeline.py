@@ -13,8 +13,8 @@ import torch
 
 from . import _abi, ground
 from .images import ImageShard
-from .proposals import (BoxTable, ProposalConfig, ScoreConfig, ScoreWorkspace, box_center_depth,
-                        score_topk, RECORD_FLOATS)
+from .proposals import (BoxTable, ProposalConfig, ScoreConfig, ScoreWorkspace, SegMasks,
+                        box_center_depth, score_topk, RECORD_FLOATS)
 
 
 class ShardRunner:
@@ -22,8 +22,9 @@ class ShardRunner:
                  sample_cfg: ProposalConfig | None = None, score_cfg: ScoreConfig | None = None,
                  priors: torch.Tensor, seed: int = 0, records: torch.Tensor | None = None):
         """``images``: host dicts with depth (H,W) f32, ground (H,W) u8 or (1,1),
-        K (3,3), boxes (b,4), classes (b,). All images are uploaded into two
-        padded device planes so a step's H2D is two large copies."""
+        K (3,3), boxes (b,4), classes (b,) and -- when ``score_cfg.e_seg > 0`` -- seg
+        (b,H,W) per-box masks. All images are uploaded into two padded device planes
+        so a step's H2D is a handful of large copies."""
         self.device = torch.device(device)
         if self.device.type != "cuda":
             raise _abi.WcrError("wcr: CUDA device required (there is no CPU fallback on this path)")
@@ -55,6 +56,11 @@ class ShardRunner:
         self.boxes = BoxTable(self.shard, [im["boxes"] for im in images],
                               [im["classes"] for im in images])
         self.h_boxes = torch.from_numpy(self.boxes.host.view("uint8").copy()).pin_memory()
+        self.seg = self.h_seg = None
+        if self.score_cfg.e_seg > 0:
+            masks = [m for im in images for m in im["seg"]]
+            self.seg = SegMasks(self.shard, self.boxes, masks)
+            self.h_seg = torch.from_numpy(self.seg.host_bits.view("int32").copy()).pin_memory()
         self.priors = priors.to(self.device, torch.float32).contiguous()
         nb = len(self.boxes)
         self.ws = ScoreWorkspace(nb, N, self.score_cfg.k, self.device, records=records)
@@ -67,7 +73,8 @@ class ShardRunner:
     # bytes a step moves over PCIe in run_host()
     @property
     def h2d_bytes(self) -> int:
-        return self.h_depth.numel() * 4 + self.h_ground.numel() + self.h_boxes.numel()
+        seg = self.h_seg.numel() * 4 if self.h_seg is not None else 0
+        return self.h_depth.numel() * 4 + self.h_ground.numel() + self.h_boxes.numel() + seg
 
     @property
     def d2h_bytes(self) -> int:
@@ -77,6 +84,8 @@ class ShardRunner:
         self.d_depth.copy_(self.h_depth, non_blocking=True)
         self.d_ground.copy_(self.h_ground, non_blocking=True)
         self.boxes.table.copy_(self.h_boxes, non_blocking=True)
+        if self.h_seg is not None:
+            self.seg.bits.copy_(self.h_seg, non_blocking=True)
 
     def step(self, score_events=None):
         """Device-resident pass: 5 kernel launches, no host sync, no D2H.
@@ -95,7 +104,8 @@ class ShardRunner:
     def _score(self, z0):
         return score_topk(self.shard, self.boxes, None, self.N, self.score_cfg,
                           priors=self.priors, normals=self.normals, z0=z0,
-                          sample_cfg=self.sample_cfg, seed=self.seed, workspace=self.ws)
+                          sample_cfg=self.sample_cfg, seed=self.seed, seg=self.seg,
+                          workspace=self.ws)
 
     def download(self):
         self.h_records.copy_(self.ws.records[:self.n_boxes], non_blocking=True)
