@@ -132,60 +132,151 @@ __device__ __forceinline__ int seg_popc_range(const SegBox &sb, int row, int a, 
 
 // Composite mask term of one cube (project spec, see orc_seg_term): pixels (X, Y)
 // of the H x W image with val_i > 0 for every hull edge, restricted to the hull's
-// bounding box grown by one pixel. val_i(X) is monotone in X under IEEE
-// rounding, so every edge cuts an integer half-line out of the row: the row's
-// interior is an interval [lo, hi] found by one division + an exact fix-up
-// instead of a per-pixel test. inter = |seg & bube|, uni = |seg| + |bube| - inter.
-template <class A>
-__device__ float seg_term(A hx, A hy, int m, int H, int W, const SegBox &sb, int mode)
+// bounding box grown by one pixel. val_i(X) is monotone in X under IEEE rounding,
+// so every edge cuts an integer half-line out of a pixel row: the row's interior is
+// an interval [lo, hi] found by one (approximate) division + an exact fix-up instead
+// of a per-pixel test. inter = |seg & bube|, uni = |seg| + |bube| - inter.
+//
+// Smallest X in [c0, c1 + 1] with g(X) > t2 (ey > 0, g non-decreasing), resp. largest
+// X in [c0 - 1, c1] (ey < 0, g non-increasing), g(X) = fl(fl(X - v1x) * ey).
+// Slow, always-right version (walks from the candidate).
+static __device__ __noinline__ int edge_cut_walk(float v1x, float ey, float t2, int c0, int c1, int X)
 {
-    if (m < 1) return 0.f;
+    if (ey > 0.f) {
+        X = min(max(X, c0), c1 + 1);
+        while (X > c0 && ((float)(X - 1) - v1x) * ey > t2) --X;
+        while (X <= c1 && !(((float)X - v1x) * ey > t2)) ++X;
+        return X;
+    }
+    X = min(max(X, c0 - 1), c1);
+    while (X < c1 && ((float)(X + 1) - v1x) * ey > t2) ++X;
+    while (X >= c0 && !(((float)X - v1x) * ey > t2)) --X;
+    return X;
+}
+
+// Edge vectors of a closed hull, e_i = v_{i+1} - v_i (utils.py:465-467), written once
+// per hull so that the per-row loop reads them instead of recomputing.
+template <class A>
+__device__ __forceinline__ void hull_edges(A hx, A hy, int m, A ex, A ey)
+{
+    for (int i = 0; i < m; ++i) {
+        const int i2 = (i + 1 == m) ? 0 : i + 1;
+        ex(i) = hx(i2) - hx(i);
+        ey(i) = hy(i2) - hy(i);
+    }
+}
+
+// One pixel row: interval [lo, hi] of columns strictly left of every hull edge.
+// Per edge: inside <=> g(X) = fl(fl(X - v1x) * ey) > t2, t2 = fl(fl(Y - v1y) * ex)
+// (a - b > 0 <=> a > b). Fast path: candidate column from an approximate division,
+// g evaluated at the candidate and its left neighbour -- the candidate is right, or
+// off by one, or the edge does not cut the row inside [c0, c1] at all; anything else
+// falls back to edge_cut_walk. The edges are independent until the final max/min, so
+// their latencies overlap.
+template <class A>
+__device__ __forceinline__ void row_interval(A hx, A hy, A ex, A ey, int m, float Y, int c0, int c1,
+                                             int &lo, int &hi)
+{
+    lo = c0; hi = c1;
+    const float fc0 = (float)c0, fc1 = (float)c1;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+        if (i < m) {  // m is uniform across the callers' lanes
+            const float v1x = hx(i), eyi = ey(i);
+            const float t2 = (Y - hy(i)) * ex(i);
+            if (eyi == 0.f) {
+                if (!((fc0 - v1x) * eyi > t2)) hi = -1;  // +-0 > t2: the same for every X
+            } else if (eyi > 0.f) {
+                // g non-decreasing (0..0 1..1): smallest X in [c0, c1 + 1] with g(X)
+                float xf = floorf(v1x + __fdividef(t2, eyi)) + 1.f;
+                xf = fminf(fmaxf(xf, fc0), fc1 + 1.f);  // NaN -> c0
+                const bool gm = ((xf - 1.f) - v1x) * eyi > t2;
+                const bool g0 = (xf - v1x) * eyi > t2;
+                int X = (int)xf;
+                const bool left_ok = !gm || xf == fc0;
+                if (left_ok && (g0 || xf > fc1)) {
+                } else if (left_ok && (xf == fc1 || ((xf + 1.f) - v1x) * eyi > t2)) {
+                    X += 1;
+                } else {
+                    X = edge_cut_walk(v1x, eyi, t2, c0, c1, X);
+                }
+                lo = max(lo, X);
+            } else {
+                // g non-increasing (1..1 0..0): largest X in [c0 - 1, c1] with g(X)
+                float xf = ceilf(v1x + __fdividef(t2, eyi)) - 1.f;
+                xf = fmaxf(fminf(xf, fc1), fc0 - 1.f);  // NaN -> c1
+                const bool gp = ((xf + 1.f) - v1x) * eyi > t2;
+                const bool g0 = (xf - v1x) * eyi > t2;
+                int X = (int)xf;
+                const bool right_ok = !gp || xf == fc1;
+                if (right_ok && (g0 || xf < fc0)) {
+                } else if (right_ok && (xf == fc0 || ((xf - 1.f) - v1x) * eyi > t2)) {
+                    X -= 1;
+                } else {
+                    X = edge_cut_walk(v1x, eyi, t2, c0, c1, X);
+                }
+                hi = min(hi, X);
+            }
+        }
+    }
+}
+
+struct HullBox { int r0, r1, c0, c1; };
+template <class A>
+__device__ __forceinline__ HullBox hull_bbox(A hx, A hy, int m, int H, int W)
+{
     float mny = hy(0), mxy = mny, mnx = hx(0), mxx = mnx;
     for (int i = 1; i < m; ++i) {
         const float y = hy(i), x = hx(i);
         mny = fminf(mny, y); mxy = fmaxf(mxy, y);
         mnx = fminf(mnx, x); mxx = fmaxf(mxx, x);
     }
-    const int r0 = max((int)floorf(mny) - 1, 0), r1 = min((int)ceilf(mxy) + 1, H - 1);
-    const int c0 = max((int)floorf(mnx) - 1, 0), c1 = min((int)ceilf(mxx) + 1, W - 1);
-    int inter = 0, bube = 0;
-    for (int Yi = r0; Yi <= r1; ++Yi) {
-        const float Y = (float)Yi;
-        int lo = c0, hi = c1;
-        for (int i = 0; i < m && lo <= hi; ++i) {
-            const int i2 = (i + 1 == m) ? 0 : i + 1;
-            const float v1x = hx(i), v1y = hy(i);
-            const float ex = hx(i2) - v1x, ey = hy(i2) - v1y;
-            const float t2 = (Y - v1y) * ex;
-            // inside this edge  <=>  g(X) = fl(fl(X - v1x) * ey) > t2   (a - b > 0 <=> a > b)
-            if (ey == 0.f) {
-                if (!(((float)lo - v1x) * ey > t2)) hi = -1;  // +-0 > t2, same for every X
-            } else if (ey > 0.f) {  // g non-decreasing: smallest X with g(X) > t2
-                float xs = floorf(v1x + t2 / ey) + 1.f;
-                int X = (int)fminf(fmaxf(xs, (float)lo), (float)(hi + 1));
-                while (X > lo && ((float)(X - 1) - v1x) * ey > t2) --X;
-                while (X <= hi && !(((float)X - v1x) * ey > t2)) ++X;
-                lo = X;
-            } else {  // g non-increasing: largest X with g(X) > t2
-                float xs = ceilf(v1x + t2 / ey) - 1.f;
-                int X = (int)fminf(fmaxf(xs, (float)(lo - 1)), (float)hi);
-                while (X < hi && ((float)(X + 1) - v1x) * ey > t2) ++X;
-                while (X >= lo && !(((float)X - v1x) * ey > t2)) --X;
-                hi = X;
-            }
-        }
-        if (lo > hi) continue;
-        bube += hi - lo + 1;
-        const int row = Yi - sb.v0;
-        if (row >= 0 && row < sb.nrows) {
-            const int a = max(lo, sb.u0) - sb.u0, b = min(hi, sb.u0 + sb.ncols - 1) - sb.u0;
-            if (a <= b) inter += seg_popc_range(sb, row, a, b);
-        }
-    }
+    HullBox b;
+    b.r0 = max((int)floorf(mny) - 1, 0); b.r1 = min((int)ceilf(mxy) + 1, H - 1);
+    b.c0 = max((int)floorf(mnx) - 1, 0); b.c1 = min((int)ceilf(mxx) + 1, W - 1);
+    return b;
+}
+
+__device__ __forceinline__ float seg_ratio(int inter, int bube, int area, int mode)
+{
     if (inter == 0) return 0.f;
-    const float fi = (float)inter, fu = (float)(sb.area + bube - inter);
+    const float fi = (float)inter, fu = (float)(area + bube - inter);
     if (mode == 1) return ((((fi * fi) * fi) * fi) * fi) / fu;  // utils.py:245
     return fi / fu;
+}
+
+// Warp-cooperative pixel counts of ONE hull (1 <= m <= 8, hull and m uniform across
+// the warp): lane l takes rows r0 + l, r0 + 32 + l, ...; every lane returns the
+// totals. Hull vertices are read with broadcast loads; nothing diverges but the
+// one-step fix-up loops.
+template <class A>
+__device__ __forceinline__ void seg_counts_warp(A hx, A hy, A ex, A ey, int m, int H, int W,
+                                                const SegBox &sb, int &inter, int &bube)
+{
+    const int lane = threadIdx.x & 31;
+    const HullBox hb = hull_bbox(hx, hy, m, H, W);
+    int it = 0, bu = 0;
+    for (int Y0 = hb.r0; Y0 <= hb.r1; Y0 += 32) {
+        const int Yi = Y0 + lane;
+        if (Yi <= hb.r1) {
+            int lo, hi;
+            row_interval(hx, hy, ex, ey, m, (float)Yi, hb.c0, hb.c1, lo, hi);
+            if (lo <= hi) {
+                bu += hi - lo + 1;
+                const int row = Yi - sb.v0;
+                if (row >= 0 && row < sb.nrows) {
+                    const int a = max(lo, sb.u0) - sb.u0, b = min(hi, sb.u0 + sb.ncols - 1) - sb.u0;
+                    if (a <= b) it += seg_popc_range(sb, row, a, b);
+                }
+            }
+        }
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        it += __shfl_xor_sync(0xffffffffu, it, o);
+        bu += __shfl_xor_sync(0xffffffffu, bu, o);
+    }
+    inter = it; bube = bu;
 }
 
 }  // namespace wcr

@@ -109,6 +109,7 @@ struct ScoreWs {
     int *count;          // [n_boxes][N] inside-counts
     float *cand;         // [n_boxes][n_chunks][k][20] chunk candidates (n_chunks > 1)
     float *cubes;        // [n_boxes][N][15] when sampled by the library
+    int2 *segcnt;        // [n_boxes][N] (|seg & hull|, |hull|) pixel counts of the mask term
 };
 
 struct ScoreArgs {
@@ -419,6 +420,73 @@ __global__ void __launch_bounds__(SC_THREADS, MINB) score_items_kernel(const Sco
             cnt[2 * pr + 1] = (int)c1 + (int)cntf[2 * pr + 1] + cnti[2 * pr + 1];
         }
 
+        // ---- mask term of this item's share of the chunk's proposals ---------------
+        // The hull rasterisation does not depend on the points, so the chunk's proposals
+        // are dealt out over the box's row-block items (no serial epilogue, no tail):
+        // item rb takes proposals [rb*per, rb*per + per) of the chunk. Thread = proposal
+        // for projection + Jarvis march (hull left in the thread's scratch column of the
+        // now idle point tile), then each warp walks its 32 hulls with lanes = pixel rows.
+        const bool use_seg = a.sc.e_seg > 0;
+        SegBox sb = {nullptr, 0, 0, 0, 0, 0, 0};
+        float lo0, hi0, lo1, hi1;
+        clamp_bounds(bx.clamp0, lo0, hi0);
+        clamp_bounds(bx.clamp1, lo1, hi1);
+        if (use_seg) {
+            const Roi r1 = box_roi(bx, im.H, im.W, 1, true);
+            sb.u0 = r1.u0; sb.v0 = r1.v0; sb.ncols = r1.ncols; sb.nrows = r1.ncols > 0 ? r1.nrows : 0;
+            sb.wpr = (sb.ncols + 31) >> 5;
+            sb.bits = a.seg_bits + a.seg_off[b];
+            const int chunk_n = min(SC_CHUNK, a.N - chunk * SC_CHUNK);
+            const int per = (chunk_n + roi.n_rowblocks - 1) / roi.n_rowblocks;
+            const int q0 = rb * per, q1 = min(q0 + per, chunk_n);
+            float *scratch = reinterpret_cast<float *>(tile) + tid;
+            const Strided spx = {scratch, SC_THREADS}, spy = {scratch + 8 * SC_THREADS, SC_THREADS};
+            const Strided shx = {scratch + 16 * SC_THREADS, SC_THREADS}, shy = {scratch + 24 * SC_THREADS, SC_THREADS};
+            float *wbase = reinterpret_cast<float *>(tile) + (tid & ~31);
+            const float hx2 = (float)(int)(bx.clamp0 - 1.f), hy2 = (float)(int)(bx.clamp1 - 1.f);
+            __syncthreads();  // every thread is done reading the point tile
+#pragma unroll 1
+            for (int base = q0; base < q1; base += SC_THREADS) {
+                // hull h of this round -> (lane h / 8, warp h % 8): spreads a short round over all warps
+                const int q = base + lane * (SC_THREADS / 32) + (tid >> 5);
+                int m_own = -1;
+                if (q < q1) {
+                    const float *src = cubes + ((size_t)b * a.N + chunk * SC_CHUNK + q) * 15;
+                    float cube[15], cxy[16];
+#pragma unroll
+                    for (int i = 0; i < 15; ++i) cube[i] = __ldg(src + i);
+                    project_cube(cube, K, lo0, hi0, lo1, hi1, cxy);
+                    // second clamp of the corners (roi_heads.py:950-952)
+                    bool finite = true;
+#pragma unroll
+                    for (int i = 0; i < 8; ++i) {
+                        finite = finite && fabsf(cxy[2 * i]) <= 3.402823466e38f && fabsf(cxy[2 * i + 1]) <= 3.402823466e38f;
+                        spx(i) = fminf(fmaxf(cxy[2 * i], 0.f), hx2);
+                        spy(i) = fminf(fmaxf(cxy[2 * i + 1], 0.f), hy2);
+                    }
+                    if (finite) {
+                        m_own = jarvis_march(spx, spy, 8, shx, shy);
+                        if (m_own > 0) hull_edges(shx, shy, m_own, spx, spy);  // corners are dead: reuse
+                    }
+                }
+                __syncwarp();
+                int my_inter = 0, my_bube = 0;
+#pragma unroll 1
+                for (int p = 0; p < 32; ++p) {
+                    const int mp = __shfl_sync(0xffffffffu, m_own, p);
+                    if (mp < 1) continue;
+                    const Strided exp_ = {wbase + p, SC_THREADS}, eyp = {wbase + p + 8 * SC_THREADS, SC_THREADS};
+                    const Strided hxp = {wbase + p + 16 * SC_THREADS, SC_THREADS};
+                    const Strided hyp = {wbase + p + 24 * SC_THREADS, SC_THREADS};
+                    int it, bu;
+                    seg_counts_warp(hxp, hyp, exp_, eyp, mp, im.H, im.W, sb, it, bu);
+                    if (lane == p) { my_inter = it; my_bube = bu; }
+                }
+                __syncwarp();
+                if (q < q1) a.ws.segcnt[(size_t)b * a.N + chunk * SC_CHUNK + q] = make_int2(my_inter, my_bube);
+            }
+        }
+
         // ---- retire the item: counts -> global, ticket ---------------------------
 #pragma unroll
         for (int t = 0; t < T; ++t) {
@@ -441,19 +509,9 @@ __global__ void __launch_bounds__(SC_THREADS, MINB) score_items_kernel(const Sco
         // ---- epilogue of (box, chunk): corners -> projection -> IoU -> score ------
         const int npts = __ldcg(a.ws.npts + (size_t)b * a.n_chunks + chunk);
         if (a.out_npts && chunk == 0 && tid == 0) a.out_npts[b] = npts;
-        float lo0, hi0, lo1, hi1;
-        clamp_bounds(bx.clamp0, lo0, hi0);
-        clamp_bounds(bx.clamp1, lo1, hi1);
-        // mask term: the box's bit-packed mask over its stride-1 integer ROI; |seg| by
-        // a CTA-wide popcount. The point tile is free now and serves as per-thread
-        // scratch for the hull march (32 floats per thread, interleaved).
-        const bool use_seg = a.sc.e_seg > 0;
-        SegBox sb = {nullptr, 0, 0, 0, 0, 0, 0};
+        // |seg| of the box mask: CTA-wide popcount (the per-proposal pixel counts were
+        // written by the items)
         if (use_seg) {
-            const Roi r1 = box_roi(bx, im.H, im.W, 1, true);
-            sb.u0 = r1.u0; sb.v0 = r1.v0; sb.ncols = r1.ncols; sb.nrows = r1.ncols > 0 ? r1.nrows : 0;
-            sb.wpr = (sb.ncols + 31) >> 5;
-            sb.bits = a.seg_bits + a.seg_off[b];
             if (tid == 0) s_area = 0;
             __syncthreads();
             int part = 0;
@@ -464,41 +522,29 @@ __global__ void __launch_bounds__(SC_THREADS, MINB) score_items_kernel(const Sco
             __syncthreads();
             sb.area = s_area;
         }
-        float *scratch = reinterpret_cast<float *>(tile) + tid;
-        const Strided spx = {scratch, SC_THREADS}, spy = {scratch + 8 * SC_THREADS, SC_THREADS};
-        const Strided shx = {scratch + 16 * SC_THREADS, SC_THREADS}, shy = {scratch + 24 * SC_THREADS, SC_THREADS};
 #pragma unroll 1
         for (int t = 0; t < T; ++t) {
             const int loc = t * SC_THREADS + tid;
             const int j = chunk * SC_CHUNK + loc;
+            const size_t o = (size_t)b * a.N + j;
             float score = -INFINITY, siou = 0.f, spts = 0.f, sseg = 1.f;
+            int c = 0;
+            ProjBox pb = {0.f, 0.f, 0.f, 0.f};
             if (j < a.N) {
-                const size_t o = (size_t)b * a.N + j;
                 const float *src = cubes + o * 15;
                 float cube[15];
 #pragma unroll
                 for (int i = 0; i < 15; ++i) cube[i] = __ldg(src + i);
-                const int c = __ldcg(a.ws.count + o);
-                float cxy[16];
-                const ProjBox pb = project_cube(cube, K, lo0, hi0, lo1, hi1, use_seg ? cxy : nullptr);
+                c = __ldcg(a.ws.count + o);
+                pb = project_cube(cube, K, lo0, hi0, lo1, hi1, nullptr);
                 siou = iou_2d(bx.x1, bx.y1, bx.x2, bx.y2, pb);
                 spts = npts > 0 ? (float)c / (float)npts : 0.f;
                 if (use_seg) {
-                    // second clamp of the corners (roi_heads.py:950-952), then hull + fill
-                    const float hx2 = (float)(int)(bx.clamp0 - 1.f), hy2 = (float)(int)(bx.clamp1 - 1.f);
-                    bool finite = true;
-#pragma unroll
-                    for (int i = 0; i < 8; ++i) {
-                        finite = finite && fabsf(cxy[2 * i]) <= 3.402823466e38f && fabsf(cxy[2 * i + 1]) <= 3.402823466e38f;
-                        spx(i) = fminf(fmaxf(cxy[2 * i], 0.f), hx2);
-                        spy(i) = fminf(fmaxf(cxy[2 * i + 1], 0.f), hy2);
-                    }
-                    sseg = 0.f;
-                    if (finite) {
-                        const int m = jarvis_march(spx, spy, 8, shx, shy);
-                        sseg = seg_term(shx, shy, m, im.H, im.W, sb, a.sc.seg_mode);
-                    }
+                    const int2 sc2 = __ldcg(a.ws.segcnt + o);
+                    sseg = seg_ratio(sc2.x, sc2.y, sb.area, a.sc.seg_mode);
                 }
+            }
+            if (j < a.N) {
                 score = (ipow(siou, a.sc.e_iou) * ipow(spts, a.sc.e_pts)) * ipow(sseg, a.sc.e_seg);
                 if (a.out_scores) a.out_scores[o] = score;
                 if (a.out_iou) a.out_iou[o] = siou;
@@ -562,8 +608,8 @@ inline size_t align256(size_t x) { return (x + 255) & ~(size_t)255; }
 
 // Carve the caller's workspace. Returns total bytes; *zero_bytes = leading region
 // that must be zero at launch.
-size_t carve(void *base, int n_boxes, int N, int k, bool need_cubes, wcr::ScoreWs *ws,
-             size_t *zero_bytes)
+size_t carve(void *base, int n_boxes, int N, int k, bool need_cubes, bool need_seg,
+             wcr::ScoreWs *ws, size_t *zero_bytes)
 {
     const int nc = n_chunks_for(N);
     char *p = (char *)base;
@@ -578,7 +624,9 @@ size_t carve(void *base, int n_boxes, int N, int k, bool need_cubes, wcr::ScoreW
     int *prefix = (int *)take((size_t)(n_boxes + 1) * sizeof(int));
     float *cand = (float *)take(nc > 1 ? (size_t)n_boxes * nc * k * WCR_RECORD_FLOATS * sizeof(float) : 0);
     float *cubes = (float *)take(need_cubes ? (size_t)n_boxes * N * 15 * sizeof(float) : 0);
+    int2 *segcnt = (int2 *)take(need_seg ? (size_t)n_boxes * N * sizeof(int2) : 0);
     if (ws) {
+        ws->segcnt = segcnt;
         ws->queue = queue; ws->done_chunk = done_chunk; ws->done_box = done_box; ws->npts = npts;
         ws->count = count; ws->item_prefix = prefix; ws->cand = cand; ws->cubes = cubes;
     }
@@ -590,7 +638,7 @@ extern "C" int64_t wcr_score_workspace_bytes(int n_boxes, int N, int k)
 {
     if (n_boxes < 0 || N < 1 || k < 1) return -1;
     // sized for the larger case (library-side sampling needs the cube buffer)
-    return (int64_t)carve(nullptr, n_boxes, N, k, true, nullptr, nullptr);
+    return (int64_t)carve(nullptr, n_boxes, N, k, true, true, nullptr, nullptr);
 }
 
 extern "C" int wcr_score_topk(const WcrImage *images, const WcrBox *boxes, int n_boxes,
@@ -623,7 +671,7 @@ extern "C" int wcr_score_topk(const WcrImage *images, const WcrBox *boxes, int n
 
     wcr::ScoreArgs a;
     size_t zero_bytes = 0;
-    carve(ws, n_boxes, N, k, cubes == nullptr, &a.ws, &zero_bytes);
+    carve(ws, n_boxes, N, k, cubes == nullptr, h_score->e_seg > 0, &a.ws, &zero_bytes);
     cudaError_t e = cudaMemsetAsync(ws, 0, zero_bytes, st);
     if (e != cudaSuccess) { wcr::set_error("cudaMemsetAsync: %s", cudaGetErrorString(e)); return WCR_ELAUNCH; }
     wcr::score_plan_kernel<<<1, 1024, 0, st>>>(images, boxes, n_boxes, nc, h_score->point_stride,
