@@ -140,7 +140,7 @@ __device__ __forceinline__ int seg_popc_range(const SegBox &sb, int row, int a, 
 // Smallest X in [c0, c1 + 1] with g(X) > t2 (ey > 0, g non-decreasing), resp. largest
 // X in [c0 - 1, c1] (ey < 0, g non-increasing), g(X) = fl(fl(X - v1x) * ey).
 // Slow, always-right version (walks from the candidate).
-static __device__ __noinline__ int edge_cut_walk(float v1x, float ey, float t2, int c0, int c1, int X)
+static __device__ __forceinline__ int edge_cut_walk(float v1x, float ey, float t2, int c0, int c1, int X)
 {
     if (ey > 0.f) {
         X = min(max(X, c0), c1 + 1);
@@ -166,59 +166,29 @@ __device__ __forceinline__ void hull_edges(A hx, A hy, int m, A ex, A ey)
     }
 }
 
-// One pixel row: interval [lo, hi] of columns strictly left of every hull edge.
-// Per edge: inside <=> g(X) = fl(fl(X - v1x) * ey) > t2, t2 = fl(fl(Y - v1y) * ex)
-// (a - b > 0 <=> a > b). Fast path: candidate column from an approximate division,
-// g evaluated at the candidate and its left neighbour -- the candidate is right, or
-// off by one, or the edge does not cut the row inside [c0, c1] at all; anything else
-// falls back to edge_cut_walk. The edges are independent until the final max/min, so
-// their latencies overlap.
-template <class A>
-__device__ __forceinline__ void row_interval(A hx, A hy, A ex, A ey, int m, float Y, int c0, int c1,
-                                             int &lo, int &hi)
+// One hull edge held in registers for the row loop.
+struct EdgeRegs { float v1x, v1y, ex, ey, rcp; };
+
+// Exact row interval, one edge at a time (always right, slow): every edge cuts an
+// integer half-line out of the row; walk from an approximate cut to the exact one.
+static __device__ __noinline__ void row_interval_walk(const float *hx, const float *hy, const float *ex,
+                                               const float *ey, int stride, int m, float Y, int c0,
+                                               int c1, int *lo_out, int *hi_out)
 {
-    lo = c0; hi = c1;
-    const float fc0 = (float)c0, fc1 = (float)c1;
-#pragma unroll
-    for (int i = 0; i < 8; ++i) {
-        if (i < m) {  // m is uniform across the callers' lanes
-            const float v1x = hx(i), eyi = ey(i);
-            const float t2 = (Y - hy(i)) * ex(i);
-            if (eyi == 0.f) {
-                if (!((fc0 - v1x) * eyi > t2)) hi = -1;  // +-0 > t2: the same for every X
-            } else if (eyi > 0.f) {
-                // g non-decreasing (0..0 1..1): smallest X in [c0, c1 + 1] with g(X)
-                float xf = floorf(v1x + __fdividef(t2, eyi)) + 1.f;
-                xf = fminf(fmaxf(xf, fc0), fc1 + 1.f);  // NaN -> c0
-                const bool gm = ((xf - 1.f) - v1x) * eyi > t2;
-                const bool g0 = (xf - v1x) * eyi > t2;
-                int X = (int)xf;
-                const bool left_ok = !gm || xf == fc0;
-                if (left_ok && (g0 || xf > fc1)) {
-                } else if (left_ok && (xf == fc1 || ((xf + 1.f) - v1x) * eyi > t2)) {
-                    X += 1;
-                } else {
-                    X = edge_cut_walk(v1x, eyi, t2, c0, c1, X);
-                }
-                lo = max(lo, X);
-            } else {
-                // g non-increasing (1..1 0..0): largest X in [c0 - 1, c1] with g(X)
-                float xf = ceilf(v1x + __fdividef(t2, eyi)) - 1.f;
-                xf = fmaxf(fminf(xf, fc1), fc0 - 1.f);  // NaN -> c1
-                const bool gp = ((xf + 1.f) - v1x) * eyi > t2;
-                const bool g0 = (xf - v1x) * eyi > t2;
-                int X = (int)xf;
-                const bool right_ok = !gp || xf == fc1;
-                if (right_ok && (g0 || xf < fc0)) {
-                } else if (right_ok && (xf == fc0 || ((xf - 1.f) - v1x) * eyi > t2)) {
-                    X -= 1;
-                } else {
-                    X = edge_cut_walk(v1x, eyi, t2, c0, c1, X);
-                }
-                hi = min(hi, X);
-            }
+    int lo = c0, hi = c1;
+    for (int i = 0; i < m && lo <= hi; ++i) {
+        const float v1x = hx[i * stride], eyi = ey[i * stride];
+        const float t2 = (Y - hy[i * stride]) * ex[i * stride];
+        if (eyi == 0.f) {
+            if (!(((float)c0 - v1x) * eyi > t2)) hi = -1;
+        } else {
+            const float xc = v1x + __fdividef(t2, eyi);
+            const float g = fminf(fmaxf(floorf(xc), (float)(c0 - 1)), (float)(c1 + 1));  // NaN -> c0 - 1
+            const int X = edge_cut_walk(v1x, eyi, t2, c0, c1, (int)g);
+            if (eyi > 0.f) lo = max(lo, X); else hi = min(hi, X);
         }
     }
+    *lo_out = lo; *hi_out = hi;
 }
 
 struct HullBox { int r0, r1, c0, c1; };
@@ -245,22 +215,108 @@ __device__ __forceinline__ float seg_ratio(int inter, int bube, int area, int mo
     return fi / fu;
 }
 
+// Rows r0 + lane, r0 + 32 + lane, ... of one hull with M edges (compile-time, so the
+// edge loops are straight-line code with no per-edge branches).
+//
+// Per row, the reference's test for pixel (X, Y) and edge i is
+//     g_i(X) = fl(fl(X - v1x) * ey) > t2_i,   t2_i = fl(fl(Y - v1y) * ex)      (a - b > 0 <=> a > b)
+// g_i is a monotone step in X (IEEE rounding is monotone): 0..0 1..1 for a rising edge
+// (ey > 0), 1..1 0..0 for a falling one, constant for a horizontal one. The row's
+// interior is therefore [L, R], L = first column where ALL rising edges pass, R = last
+// column where ALL falling edges pass. L and R are guessed from approximate cuts
+// (one FFMA per edge) and then PROVED with the exact expression: all rising pass at L
+// and not all at L - 1, all falling pass at R and not all at R + 1 (two exact
+// evaluations per edge). A row whose guess cannot be proved (cut within rounding of a
+// pixel centre, ill-conditioned edge) is redone by row_interval_walk.
+template <int M, class A>
+__device__ __forceinline__ void hull_rows(const EdgeRegs (&e)[8], A hx, A hy, A ex, A ey, int r0, int r1,
+                                          int c0, int c1, const SegBox &sb, int &it, int &bu)
+{
+    const int lane = threadIdx.x & 31;
+    const float fc0 = (float)c0, fc1 = (float)c1;
+    for (int Y0 = r0; Y0 <= r1; Y0 += 32) {
+        const int Yi = Y0 + lane;
+        if (Yi <= r1) {
+            const float Y = (float)Yi;
+            // ---- guess: approximate cuts
+            float t2[M];
+            float lo_c = -INFINITY, hi_c = INFINITY, dacc = -1.f;
+#pragma unroll
+            for (int i = 0; i < M; ++i) {
+                t2[i] = (Y - e[i].v1y) * e[i].ex;
+                const float xc = __fmaf_rn(t2[i], e[i].rcp, e[i].v1x);
+                lo_c = fmaxf(lo_c, e[i].ey > 0.f ? xc : -INFINITY);
+                hi_c = fminf(hi_c, e[i].ey < 0.f ? xc : INFINITY);
+                dacc = fmaxf(dacc, e[i].ey == 0.f ? t2[i] : -1.f);  // horizontal: passes iff (+-0) > t2
+            }
+            const float fL = fminf(fmaxf(floorf(lo_c) + 1.f, fc0), fc1 + 1.f);   // in [c0, c1 + 1]
+            const float fR = fmaxf(fminf(ceilf(hi_c) - 1.f, fc1), fc0 - 1.f);    // in [c0 - 1, c1]
+            // ---- proof: exact evaluations at L, L - 1 (rising edges) and R, R + 1 (falling)
+            unsigned pL = 1u, pLm = 1u, pR = 1u, pRp = 1u;
+#pragma unroll
+            for (int i = 0; i < M; ++i) {
+                const unsigned up = e[i].ey > 0.f, dn = e[i].ey < 0.f;
+                const float xa = up ? fL : fR, xb = up ? fL - 1.f : fR + 1.f;
+                const unsigned ga = (xa - e[i].v1x) * e[i].ey > t2[i];
+                const unsigned gb = (xb - e[i].v1x) * e[i].ey > t2[i];
+                pL &= ga | (up ^ 1u); pLm &= gb | (up ^ 1u);
+                pR &= ga | (dn ^ 1u); pRp &= gb | (dn ^ 1u);
+            }
+            const bool left_ok = (fL == fc0 || !pLm) && (fL > fc1 || pL);
+            const bool right_ok = (fR == fc1 || !pRp) && (fR < fc0 || pR);
+            int lo = (int)fL, hi = (int)fR;
+            if (!(left_ok && right_ok))
+                row_interval_walk(&hx(0), &hy(0), &ex(0), &ey(0), hx.stride, M, Y, c0, c1, &lo, &hi);
+            else if (!(dacc < 0.f))
+                hi = -1;
+            if (lo <= hi) {
+                bu += hi - lo + 1;
+                const int row = Yi - sb.v0;
+                if (row >= 0 && row < sb.nrows) {
+                    const int a = max(lo, sb.u0) - sb.u0, b = min(hi, sb.u0 + sb.ncols - 1) - sb.u0;
+                    if (a <= b) it += seg_popc_range(sb, row, a, b);
+                }
+            }
+        }
+    }
+}
+
 // Warp-cooperative pixel counts of ONE hull (1 <= m <= 8, hull and m uniform across
-// the warp): lane l takes rows r0 + l, r0 + 32 + l, ...; every lane returns the
-// totals. Hull vertices are read with broadcast loads; nothing diverges but the
-// one-step fix-up loops.
+// the warp); every lane returns the totals. The hull's edges are read once (broadcast
+// loads) into registers.
 template <class A>
 __device__ __forceinline__ void seg_counts_warp(A hx, A hy, A ex, A ey, int m, int H, int W,
                                                 const SegBox &sb, int &inter, int &bube)
 {
     const int lane = threadIdx.x & 31;
-    const HullBox hb = hull_bbox(hx, hy, m, H, W);
+    EdgeRegs e[8];
+    float mny = 0.f, mxy = 0.f, mnx = 0.f, mxx = 0.f;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+        if (i < m) {
+            e[i].v1x = hx(i); e[i].v1y = hy(i); e[i].ex = ex(i); e[i].ey = ey(i);
+            e[i].rcp = __frcp_rn(e[i].ey);
+            if (i == 0) { mnx = mxx = e[i].v1x; mny = mxy = e[i].v1y; }
+            else {
+                mnx = fminf(mnx, e[i].v1x); mxx = fmaxf(mxx, e[i].v1x);
+                mny = fminf(mny, e[i].v1y); mxy = fmaxf(mxy, e[i].v1y);
+            }
+        }
+    }
+    const int r0 = max((int)floorf(mny) - 1, 0), r1 = min((int)ceilf(mxy) + 1, H - 1);
+    const int c0 = max((int)floorf(mnx) - 1, 0), c1 = min((int)ceilf(mxx) + 1, W - 1);
     int it = 0, bu = 0;
-    for (int Y0 = hb.r0; Y0 <= hb.r1; Y0 += 32) {
-        const int Yi = Y0 + lane;
-        if (Yi <= hb.r1) {
+    switch (m) {
+    case 3: hull_rows<3>(e, hx, hy, ex, ey, r0, r1, c0, c1, sb, it, bu); break;
+    case 4: hull_rows<4>(e, hx, hy, ex, ey, r0, r1, c0, c1, sb, it, bu); break;
+    case 5: hull_rows<5>(e, hx, hy, ex, ey, r0, r1, c0, c1, sb, it, bu); break;
+    case 6: hull_rows<6>(e, hx, hy, ex, ey, r0, r1, c0, c1, sb, it, bu); break;
+    case 7: hull_rows<7>(e, hx, hy, ex, ey, r0, r1, c0, c1, sb, it, bu); break;
+    case 8: hull_rows<8>(e, hx, hy, ex, ey, r0, r1, c0, c1, sb, it, bu); break;
+    default:  // m = 1, 2: no interior in exact arithmetic; evaluated the slow, literal way
+        for (int Yi = r0 + lane; Yi <= r1; Yi += 32) {
             int lo, hi;
-            row_interval(hx, hy, ex, ey, m, (float)Yi, hb.c0, hb.c1, lo, hi);
+            row_interval_walk(&hx(0), &hy(0), &ex(0), &ey(0), hx.stride, m, (float)Yi, c0, c1, &lo, &hi);
             if (lo <= hi) {
                 bu += hi - lo + 1;
                 const int row = Yi - sb.v0;

@@ -71,6 +71,14 @@ __device__ __forceinline__ void count_inside1(int &cnt, float q0, float q1, floa
         : "+r"(cnt)
         : "f"(q0), "f"(q1), "f"(q2));
 }
+// Read-once global data (depth pixels, cube parameters): keep it out of L1 so that the
+// box mask the hull fill re-reads stays resident.
+__device__ __forceinline__ float ld_stream(const float *p)
+{
+    float v;
+    asm volatile("ld.global.nc.L1::no_allocate.f32 %0, [%1];" : "=f"(v) : "l"(p));
+    return v;
+}
 // 1.0f if max(|q0|,|q1|,|q2|) <= 1 else 0.0f. One FMNMX3 + one FSET; NaN -> 0.
 __device__ __forceinline__ float inside_unit(float q0, float q1, float q2)
 {
@@ -247,6 +255,8 @@ __device__ __forceinline__ void warp_merge(const float *cand, int n, int k, floa
 //   0: FFMA2 (two proposals per packed fma) + FMNMX3 + FSET + FADD2
 //   1: scalar FFMA + FMNMX3 + FSET + FADD
 //   2: scalar FFMA + 3 x FSETP(|q| <= 1) + predicated IADD
+// (an integer-mask FSET + IADD3 pairing was tried too: ptxas lowers it to the
+//  quarter-rate FSETP + predicated IADD, 9 % slower -- profiles/variants_r1.txt)
 template <int V, int MINB>
 __global__ void __launch_bounds__(SC_THREADS, MINB) score_items_kernel(const ScoreArgs a)
 {
@@ -303,7 +313,7 @@ __global__ void __launch_bounds__(SC_THREADS, MINB) score_items_kernel(const Sco
                 if (live) {
                     const float *src = cubes + ((size_t)b * a.N + j) * 15;
 #pragma unroll
-                    for (int i = 0; i < 15; ++i) cube[i] = __ldg(src + i);
+                    for (int i = 0; i < 15; ++i) cube[i] = ld_stream(src + i);
                     live = cube[3] > 0.f && cube[4] > 0.f && cube[5] > 0.f;  // empty cube holds no point
                 }
                 if (live) {
@@ -351,7 +361,7 @@ __global__ void __launch_bounds__(SC_THREADS, MINB) score_items_kernel(const Sco
                     float av = 0.f, z = nanf_();
                     if (col < ncols) {
                         const int u = roi.u0 + col * s, v = roi.v0 + (row_begin + row) * s;
-                        const float d = __ldg(im.depth + (size_t)v * im.depth_pitch + u);
+                        const float d = ld_stream(im.depth + (size_t)v * im.depth_pitch + u);
                         av = ((float)u - K.cx) / K.fx;
                         if (d > 0.f && d <= 3.402823466e38f) { z = d; ++my_valid; }
                     }
@@ -454,7 +464,7 @@ __global__ void __launch_bounds__(SC_THREADS, MINB) score_items_kernel(const Sco
                     const float *src = cubes + ((size_t)b * a.N + chunk * SC_CHUNK + q) * 15;
                     float cube[15], cxy[16];
 #pragma unroll
-                    for (int i = 0; i < 15; ++i) cube[i] = __ldg(src + i);
+                    for (int i = 0; i < 15; ++i) cube[i] = ld_stream(src + i);
                     project_cube(cube, K, lo0, hi0, lo1, hi1, cxy);
                     // second clamp of the corners (roi_heads.py:950-952)
                     bool finite = true;
@@ -534,7 +544,7 @@ __global__ void __launch_bounds__(SC_THREADS, MINB) score_items_kernel(const Sco
                 const float *src = cubes + o * 15;
                 float cube[15];
 #pragma unroll
-                for (int i = 0; i < 15; ++i) cube[i] = __ldg(src + i);
+                for (int i = 0; i < 15; ++i) cube[i] = ld_stream(src + i);
                 c = __ldcg(a.ws.count + o);
                 pb = project_cube(cube, K, lo0, hi0, lo1, hi1, nullptr);
                 siou = iou_2d(bx.x1, bx.y1, bx.x2, bx.y2, pb);
@@ -684,7 +694,8 @@ extern "C" int wcr_score_topk(const WcrImage *images, const WcrBox *boxes, int n
         WCR_CHECK_LAUNCH("sample_cubes_kernel");
     }
     a.images = images; a.boxes = boxes; a.n_boxes = n_boxes; a.cubes = cubes; a.N = N;
-    a.sc = *h_score; a.k = k; a.n_chunks = nc; a.records = out_records;
+    a.sc = *h_score; a.k = k;
+    a.n_chunks = nc; a.records = out_records;
     a.out_scores = out_scores; a.out_iou = out_iou; a.out_count = out_count;
     a.out_proj = out_proj; a.out_npts = out_npts;
     a.seg_bits = seg_bits; a.seg_off = seg_off; a.out_seg = out_seg;
