@@ -75,6 +75,7 @@ def cpu_arm(n_images: int, first: int = 0, repeats: int = 1, seg: bool = True):
     from oracle import clib, cubes as oc, ground as og
     from wcr import synth
     import random
+    clib.set_num_threads()          # torchrun exports OMP_NUM_THREADS=1: ask for every core
     ims = make_images(n_images, first, seg)
     priors = synth.make_priors()
     rng = np.random.default_rng(0)

@@ -326,6 +326,48 @@ typedef struct WcrLossIO {
 int wcr_weak_loss_fwd(const WcrLossIO *h_io, const WcrLossParams *h_params, void *stream);
 int wcr_weak_loss_bwd(const WcrLossIO *h_io, const WcrLossParams *h_params, void *stream);
 
+/* ---- stand-alone loss helpers (one forward + one backward launch each) ---------- */
+
+/* ROIHeads3DScore.pose_loss (roi_heads.py:445-464) with so3_relative_angle_batched
+ * (math_util.py:1132-1181, cos_angle=True): per image with n_i > 1 boxes the mean over
+ * pairs i > j of 1 - |(tr(R_i R_j^T) - 1)/2|; summed and divided by (fail + 1), fail =
+ * images with exactly one box.
+ *   R [n][9], img_off [n_images+1]; img_pose [n_images] scratch;
+ *   out3 = {loss, fail, n_images} (the caller returns None when fail == n_images). */
+int wcr_pose_loss_fwd(const float *R, const int32_t *img_off, int n_images, float *img_pose,
+                      float *out3, void *stream);
+/* grad1 [1]: upstream gradient of the scalar; d_R [n][9]. */
+int wcr_pose_loss_bwd(const float *R, const int32_t *img_off, int n_images, const float *fwd_out3,
+                      const float *grad1, float *d_R, void *stream);
+
+/* ROIHeads3DScore.pseudo_gt_z_point_loss (roi_heads.py:635-656): |pred_z - depth[y, x]|
+ * at the 10-px-clamped, truncated predicted centre.  pred_xy [n][2], pred_z [n];
+ * out_loss [n]; out_sign [n] = sign(pred_z - gt) for wcr_l1_loss_bwd. */
+int wcr_pseudo_z_point_loss(const WcrImage *images, const int32_t *img_off, int n_images, int n,
+                            const float *pred_xy, const float *pred_z, float *out_loss,
+                            float *out_sign, void *stream);
+
+/* ROIHeads3DScore.pseudo_gt_z_box_loss (roi_heads.py:575-610): pseudo depth = LOWER
+ * median (torch.median) of the depth patch under each box after Boxes.clip and .long();
+ * boxes with zero area after clipping fall back to the centre lookup AND are appended
+ * after the in-image boxes of their image, so the pairing with pred_z is by position in
+ * that re-ordered list (reference behaviour, kept).
+ *   boxes [n][4]; ws_gt [n], ws_inside [n] scratch (per-box pseudo depth / in-image flag). */
+int wcr_pseudo_z_box_loss(const WcrImage *images, const int32_t *img_off, int n_images, int n,
+                          const float *boxes, const float *pred_z, float *out_loss, float *out_sign,
+                          float *ws_gt, int32_t *ws_inside, void *stream);
+
+/* backward of smooth_l1(beta = 0) (roi_heads.py:352-353): d_pred[i] = grad[i] * sign[i]. */
+int wcr_l1_loss_bwd(const float *sign, const float *grad, int n, float *d_pred, void *stream);
+
+/* ROIHeads3DScore.dim_loss (roi_heads.py:612-633): max(|d - mean| / std - 1, 0) per axis.
+ *   prior_mean, prior_std, dims [n][3]; out3n [3][n]; nan_flag [1] = number of NaN stds
+ *   (the reference returns (None, None, None) when any is NaN). */
+int wcr_dim_loss_fwd(const float *prior_mean, const float *prior_std, const float *dims, int n,
+                     float *out3n, int32_t *nan_flag, void *stream);
+int wcr_dim_loss_bwd(const float *prior_mean, const float *prior_std, const float *dims,
+                     const float *grad3n, int n, float *d_dims, void *stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -168,6 +168,14 @@ def philox4x32_10(ctr, key) -> np.ndarray:
     return out
 
 
+def set_num_threads(n: int | None = None) -> int:
+    """Use ``n`` OpenMP threads (default: every core this process may run on)."""
+    if n is None:
+        n = len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1)
+    lib().orc_set_num_threads(c_i(int(n)))
+    return num_threads()
+
+
 def num_threads() -> int:
     fn = lib().orc_num_threads
     fn.restype = c_i

@@ -191,6 +191,30 @@ def pseudo_gt_z_point_loss(depth_maps, pred_xy, pred_z, num_boxes_per_image):
     return F.smooth_l1_loss(pred_z, torch.cat(gt), reduction="none", beta=0.0)
 
 
+def pseudo_gt_z_box_loss(depth_maps, proposal_boxes, pred_z):
+    """roi_heads.py:575-610 ('z_pseudo_gt_patch'). depth_maps: list of un-padded (h,w)
+    tensors; proposal_boxes: list of (b_i,4) tensors. Per image: clip to the image
+    (Boxes.clip), boxes with positive clipped area -> torch.median (LOWER median) of the
+    patch sliced with .long() bounds, appended first; the others -> centre lookup with
+    the 10-px clamp, appended after them. The list is paired with pred_z by position."""
+    gt = []
+    for d, b in zip(depth_maps, proposal_boxes):
+        h, w = d.shape
+        b = torch.stack((b[:, 0].clamp(0, w), b[:, 1].clamp(0, h), b[:, 2].clamp(0, w), b[:, 3].clamp(0, h)), 1)
+        area = (b[:, 2] - b[:, 0]) * (b[:, 3] - b[:, 1])
+        m = area > 0
+        for box in b[m]:
+            gt.append(torch.median(d[box[1].long():box[3].long(), box[0].long():box[2].long()]).unsqueeze(0))
+        out = b[~m]
+        if len(out) == 0:
+            continue
+        c = (out[:, :2] + out[:, 2:]) / 2
+        x = torch.clamp(c[:, 0], 10, w - 11)
+        y = torch.clamp(c[:, 1], 10, h - 11)
+        gt.append(d[y.long(), x.long()])
+    return F.smooth_l1_loss(pred_z, torch.cat(gt), reduction="none", beta=0.0)
+
+
 def dim_loss(prior_mean, prior_std, dims):
     """roi_heads.py:612-633."""
     if torch.isnan(prior_std).any():

@@ -149,6 +149,35 @@ def golden_hull():
     one_file("hull_1.npz", sets, 120, 160)
 
 
+def golden_zbox():
+    """ROIHeads3DScore.pseudo_gt_z_box_loss (roi_heads.py:575-610) run as is: boxes partly
+    and fully outside the image, even/odd patch sizes (lower median), 1-pixel patches."""
+    head = refshim.roi_head_instance()
+    g = torch.Generator().manual_seed(31)
+    H, W = 90, 120
+    depth = [(0.5 + 6 * torch.rand(H, W, generator=g)) for _ in range(3)]
+    depth[1][::2] = depth[1][1::2]                          # repeated values
+    boxes = []
+    for i, nb in enumerate((6, 1, 9)):
+        x1 = torch.rand(nb, generator=g) * W * 1.2 - 0.1 * W
+        y1 = torch.rand(nb, generator=g) * H * 1.2 - 0.1 * H
+        bw = 1.0 + torch.rand(nb, generator=g) * 50
+        bh = 1.0 + torch.rand(nb, generator=g) * 40
+        b = torch.stack((x1, y1, x1 + bw, y1 + bh), 1)
+        boxes.append(b)
+    boxes[0][1] = torch.tensor([-30.0, 10.0, -5.0, 40.0])   # fully outside: fallback + re-ordering
+    boxes[2][4] = torch.tensor([50.0, 200.0, 80.0, 230.0])
+    boxes[2][0] = torch.tensor([10.2, 10.3, 12.9, 11.8])    # 2 x 1 patch
+    pred_z = (1 + 5 * torch.rand(16, generator=g)).requires_grad_(True)
+    il = standins.ImageList.from_tensors(depth)
+    loss = head.pseudo_gt_z_box_loss(il, tuple(boxes), pred_z)
+    loss.sum().backward()
+    np.savez_compressed(os.path.join(HERE, "zbox_0.npz"), depth=torch.stack(depth).numpy(),
+                        boxes=torch.cat(boxes).numpy(), nb=np.array([6, 1, 9]), pred_z=pred_z.detach().numpy(),
+                        loss=loss.detach().numpy(), grad=pred_z.grad.numpy())
+    print("zbox", loss.detach().numpy().round(3))
+
+
 def golden_loss():
     cases = [(0, [3, 1, 5, 2], False, {}),
              (1, [6, 2, 9], True, {"z_type": "sigmoid", "dims_priors_func": "sigmoid"}),
@@ -167,4 +196,5 @@ if __name__ == "__main__":
     golden_ground()
     golden_cubes()
     golden_hull()
+    golden_zbox()
     golden_loss()

@@ -47,3 +47,17 @@ def test_giou_matches_torchvision():
     a = torch.rand(50, 4, generator=g) * 100; a[:, 2:] += a[:, :2] + 1
     b = torch.rand(50, 4, generator=g) * 100; b[:, 2:] += b[:, :2] + 1
     assert torch.equal(ol.giou_loss(a, b), generalized_box_iou_loss(a, b, reduction="none"))
+
+
+def test_zbox_oracle_matches_reference_golden():
+    """oracle.pseudo_gt_z_box_loss vs ROIHeads3DScore.pseudo_gt_z_box_loss run as is
+    (tests/golden/zbox_0.npz): values and the gradient w.r.t. pred_z."""
+    import torch
+    z = np.load(os.path.join(os.path.dirname(__file__), "golden", "zbox_0.npz"))
+    depth = [torch.from_numpy(d) for d in z["depth"]]
+    boxes = list(torch.from_numpy(z["boxes"]).split([int(x) for x in z["nb"]]))
+    pz = torch.from_numpy(z["pred_z"]).requires_grad_(True)
+    loss = ol.pseudo_gt_z_box_loss(depth, boxes, pz)
+    loss.sum().backward()
+    assert np.array_equal(loss.detach().numpy(), z["loss"])
+    assert np.array_equal(pz.grad.numpy(), z["grad"])

@@ -11,6 +11,7 @@
 //             autograd's sub-gradient choices (first arg-extremum over corners,
 //             closed-interval clamp, tie-splitting binary min/max, sign(0) = 0).
 // Latency-bound by nature (n <= a few thousand boxes): no roofline claim.
+#include <string.h>
 #include "cube_math.cuh"
 
 namespace wcr {
@@ -601,5 +602,303 @@ extern "C" int wcr_weak_loss_bwd(const WcrLossIO *h_io, const WcrLossParams *h_p
     }
     wcr::loss_box_bwd_kernel<<<(h_io->n + 127) / 128, 128, 0, st>>>(*h_io, *h_params);
     WCR_CHECK_LAUNCH("loss_box_bwd_kernel");
+    return WCR_OK;
+}
+
+// ============================================================================
+// Stand-alone loss helpers behind the reference's method names (roi_heads.py:445
+// pose_loss, :575 pseudo_gt_z_box_loss, :612 dim_loss, :635 pseudo_gt_z_point_loss):
+// one forward and one backward launch each, for callers that do not use the fused
+// block above. Same device functions, same rounding order.
+// ============================================================================
+namespace wcr {
+
+// out[0] = sum_images L_im / (fail + 1), out[1] = fail, out[2] = n_images  (:451-464)
+__global__ void __launch_bounds__(256)
+pose_reduce_kernel(const int32_t *__restrict__ img_off, int n_images, const float *__restrict__ img_pose,
+                   float *__restrict__ out)
+{
+    __shared__ float s_a[8], s_b[8];
+    float psum = 0.f, fail = 0.f;
+    for (int im = threadIdx.x; im < n_images; im += blockDim.x) {
+        const int ni = img_off[im + 1] - img_off[im];
+        if (ni == 1) fail += 1.f; else psum += img_pose[im];
+    }
+    block_sum2(psum, fail, s_a, s_b);
+    if (threadIdx.x == 0) { out[0] = psum * 1.f / (fail + 1.f); out[1] = fail; out[2] = (float)n_images; }
+}
+
+// d loss / d R_i = grad / (npairs_im * (fail + 1)) * sum_{j != i} -sign(cos_ij) / 2 * R_j
+__global__ void __launch_bounds__(128)
+pose_bwd_kernel(const float *__restrict__ R, const int32_t *__restrict__ img_off,
+                const float *__restrict__ fwd_out, const float *__restrict__ grad, float *__restrict__ d_R)
+{
+    const int im = blockIdx.x;
+    const int b0 = img_off[im], ni = img_off[im + 1] - b0;
+    const float npairs = 0.5f * (float)ni * (float)(ni - 1);
+    const float scale = ni > 1 ? grad[0] / (npairs * (fwd_out[1] + 1.f)) : 0.f;
+    for (int i = threadIdx.x; i < ni; i += blockDim.x) {
+        float Ri[9], g[9];
+#pragma unroll
+        for (int t = 0; t < 9; ++t) { Ri[t] = R[9 * (size_t)(b0 + i) + t]; g[t] = 0.f; }
+        for (int j = 0; j < ni; ++j) {
+            if (j == i) continue;
+            const float *Rj = R + 9 * (size_t)(b0 + j);
+            const float dc = -sgn(pair_cos(Ri, Rj)) * scale * 0.5f;
+#pragma unroll
+            for (int t = 0; t < 9; ++t) g[t] += dc * Rj[t];
+        }
+#pragma unroll
+        for (int t = 0; t < 9; ++t) d_R[9 * (size_t)(b0 + i) + t] = g[t];
+    }
+}
+
+// |pred_z - depth[clamp(y), clamp(x)]| per box (:635-656); sign kept for the backward.
+__global__ void __launch_bounds__(128)
+pseudo_z_point_kernel(const WcrImage *__restrict__ images, const int32_t *__restrict__ img_off,
+                      int n_images, int n, const float *__restrict__ pred_xy,
+                      const float *__restrict__ pred_z, float *__restrict__ out_loss,
+                      float *__restrict__ out_sign)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const WcrImage im = images[image_of(img_off, n_images, i)];
+    const float gt = depth_at(im, pred_xy[2 * i], pred_xy[2 * i + 1]);
+    const float d = pred_z[i] - gt;
+    out_loss[i] = fabsf(d);       // smooth_l1(beta = 0) == |x| (:352-353)
+    out_sign[i] = sgn(d);         // nan -> 0, like torch's sign in the L1 backward
+}
+
+__global__ void __launch_bounds__(256)
+l1_bwd_kernel(const float *__restrict__ sign, const float *__restrict__ grad, int n, float *__restrict__ d)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) d[i] = grad[i] * sign[i];
+}
+
+// dim_loss (:612-633): max(|d - mu| / sigma - 1, 0) per axis; nan_flag counts NaN stds.
+__global__ void __launch_bounds__(256)
+dim_loss_kernel(const float *__restrict__ mean, const float *__restrict__ std_, const float *__restrict__ dims,
+                int n, float *__restrict__ out /* [3][n] */, int *__restrict__ nan_flag)
+{
+    const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= 3 * n) return;
+    const int i = idx / 3, k = idx - 3 * i;
+    const float s = std_[idx];
+    if (s != s) atomicAdd(nan_flag, 1);
+    const float a = fabsf(dims[idx] - mean[idx]) / s - 1.0f;
+    out[(size_t)k * n + i] = (a != a) ? a : fmaxf(a, 0.f);   // torch.max(a, 0) keeps NaN
+}
+
+// backward of the above: binary max splits a tie evenly, |.| has gradient sign(.)
+__global__ void __launch_bounds__(256)
+dim_loss_bwd_kernel(const float *__restrict__ mean, const float *__restrict__ std_,
+                    const float *__restrict__ dims, const float *__restrict__ grad /* [3][n] */, int n,
+                    float *__restrict__ d_dims)
+{
+    const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= 3 * n) return;
+    const int i = idx / 3, k = idx - 3 * i;
+    const float diff = dims[idx] - mean[idx];
+    const float a = fabsf(diff) / std_[idx] - 1.0f;
+    const float w = a > 0.f ? 1.f : (a == 0.f ? 0.5f : 0.f);
+    d_dims[idx] = grad[(size_t)k * n + i] * w * sgn(diff) / std_[idx];
+}
+
+// ---- pseudo_gt_z_box_loss (:575-610): lower median of the depth patch under each
+// predicted 2D box. One CTA per box: 4-pass radix select (8 bits per pass, shared
+// histogram) over the order-preserving integer image of the floats; the patch is
+// re-read from L2 each pass. torch.median returns the LOWER median (element
+// (cnt-1)/2 of the sorted patch) and NaN when the patch holds a NaN.
+__device__ __forceinline__ uint32_t float_key(float f)
+{
+    const uint32_t u = __float_as_uint(f);
+    return (u & 0x80000000u) ? ~u : (u | 0x80000000u);
+}
+__device__ __forceinline__ float key_float(uint32_t k)
+{
+    return __uint_as_float((k & 0x80000000u) ? (k & 0x7fffffffu) : ~k);
+}
+
+__global__ void __launch_bounds__(256)
+box_median_kernel(const WcrImage *__restrict__ images, const int32_t *__restrict__ img_off, int n_images,
+                  const float *__restrict__ boxes /* [n][4] */, float *__restrict__ out_gt,
+                  int *__restrict__ out_inside)
+{
+    __shared__ unsigned hist[256];
+    __shared__ unsigned s_prefix, s_rank;
+    __shared__ int s_nan;
+    const int b = blockIdx.x;
+    const WcrImage im = images[image_of(img_off, n_images, b)];
+    // Boxes.clip((h, w)), area() > 0 on the clipped float box, then .long() slicing
+    const float x1 = fminf(fmaxf(boxes[4 * b + 0], 0.f), (float)im.W), y1 = fminf(fmaxf(boxes[4 * b + 1], 0.f), (float)im.H);
+    const float x2 = fminf(fmaxf(boxes[4 * b + 2], 0.f), (float)im.W), y2 = fminf(fmaxf(boxes[4 * b + 3], 0.f), (float)im.H);
+    const bool inside = (x2 - x1) * (y2 - y1) > 0.f;
+    if (!inside) {
+        // fallback of :600-606: centre lookup of the CLIPPED box with the 10-px clamp
+        if (threadIdx.x == 0) {
+            out_gt[b] = depth_at(im, (x1 + x2) / 2.f, (y1 + y2) / 2.f);
+            out_inside[b] = 0;
+        }
+        return;
+    }
+    const int u0 = (int)x1, u1 = (int)x2, v0 = (int)y1, v1 = (int)y2;
+    const int ncols = u1 - u0, cnt = ncols * (v1 - v0);
+    if (cnt <= 0) {  // torch.median of an empty slice raises in the reference; NaN here
+        if (threadIdx.x == 0) { out_gt[b] = nanf_(); out_inside[b] = 1; }
+        return;
+    }
+    if (threadIdx.x == 0) { s_prefix = 0u; s_rank = (unsigned)((cnt - 1) / 2); s_nan = 0; }
+    for (int pass = 0; pass < 4; ++pass) {
+        const int shift = 24 - 8 * pass;
+        hist[threadIdx.x] = 0u;
+        __syncthreads();
+        const unsigned prefix = s_prefix;
+        const unsigned himask = pass == 0 ? 0u : (0xffffffffu << (shift + 8));
+        for (int idx = threadIdx.x; idx < cnt; idx += 256) {
+            const int r = idx / ncols, c = idx - r * ncols;
+            const float f = im.depth[(size_t)(v0 + r) * im.depth_pitch + u0 + c];
+            if (pass == 0 && f != f) s_nan = 1;
+            const uint32_t k = float_key(f);
+            if ((k & himask) == prefix) atomicAdd(&hist[(k >> shift) & 255u], 1u);
+        }
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            unsigned rank = s_rank, acc = 0u;
+            int bin = 0;
+            for (; bin < 255; ++bin) {
+                if (acc + hist[bin] > rank) break;
+                acc += hist[bin];
+            }
+            s_rank = rank - acc;
+            s_prefix = prefix | ((unsigned)bin << shift);
+        }
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) {
+        out_gt[b] = s_nan ? nanf_() : key_float(s_prefix);
+        out_inside[b] = 1;
+    }
+}
+
+// Per image: the reference appends the in-image boxes' medians first and the
+// out-of-image fallbacks after them (:595-606), then pairs that list with pred_z BY
+// POSITION -- reproduced here. One thread per image (boxes per image are few).
+__global__ void __launch_bounds__(128)
+box_z_loss_kernel(const int32_t *__restrict__ img_off, int n_images, const float *__restrict__ gt,
+                  const int *__restrict__ inside, const float *__restrict__ pred_z,
+                  float *__restrict__ out_loss, float *__restrict__ out_sign)
+{
+    const int im = blockIdx.x * blockDim.x + threadIdx.x;
+    if (im >= n_images) return;
+    const int b0 = img_off[im], b1 = img_off[im + 1];
+    int pos = b0;
+    for (int phase = 1; phase >= 0; --phase)
+        for (int b = b0; b < b1; ++b)
+            if (inside[b] == phase) {
+                const float d = pred_z[pos] - gt[b];
+                out_loss[pos] = fabsf(d);
+                out_sign[pos] = sgn(d);
+                ++pos;
+            }
+}
+
+}  // namespace wcr
+
+extern "C" int wcr_pose_loss_fwd(const float *R, const int32_t *img_off, int n_images, float *img_pose,
+                                 float *out3, void *stream)
+{
+    WCR_CHECK_DEVICE();
+    WCR_REQUIRE(R && img_off && img_pose && out3, "wcr_pose_loss_fwd: null pointer");
+    WCR_REQUIRE(n_images >= 1, "wcr_pose_loss_fwd: needs at least one image");
+    WcrLossIO io;
+    memset(&io, 0, sizeof(io));
+    io.n_images = n_images; io.R_ego = const_cast<float *>(R); io.img_off = img_off; io.img_pose = img_pose;
+    wcr::loss_pose_fwd_kernel<<<n_images, 256, 0, (cudaStream_t)stream>>>(io);
+    WCR_CHECK_LAUNCH("loss_pose_fwd_kernel");
+    wcr::pose_reduce_kernel<<<1, 256, 0, (cudaStream_t)stream>>>(img_off, n_images, img_pose, out3);
+    WCR_CHECK_LAUNCH("pose_reduce_kernel");
+    return WCR_OK;
+}
+
+extern "C" int wcr_pose_loss_bwd(const float *R, const int32_t *img_off, int n_images,
+                                 const float *fwd_out3, const float *grad1, float *d_R, void *stream)
+{
+    WCR_CHECK_DEVICE();
+    WCR_REQUIRE(R && img_off && fwd_out3 && grad1 && d_R, "wcr_pose_loss_bwd: null pointer");
+    WCR_REQUIRE(n_images >= 1, "wcr_pose_loss_bwd: needs at least one image");
+    wcr::pose_bwd_kernel<<<n_images, 128, 0, (cudaStream_t)stream>>>(R, img_off, fwd_out3, grad1, d_R);
+    WCR_CHECK_LAUNCH("pose_bwd_kernel");
+    return WCR_OK;
+}
+
+extern "C" int wcr_pseudo_z_point_loss(const WcrImage *images, const int32_t *img_off, int n_images, int n,
+                                       const float *pred_xy, const float *pred_z, float *out_loss,
+                                       float *out_sign, void *stream)
+{
+    WCR_CHECK_DEVICE();
+    WCR_REQUIRE(images && img_off && pred_xy && pred_z && out_loss && out_sign,
+                "wcr_pseudo_z_point_loss: null pointer");
+    WCR_REQUIRE(n_images >= 1 && n >= 0, "wcr_pseudo_z_point_loss: bad sizes");
+    if (n == 0) return WCR_OK;
+    wcr::pseudo_z_point_kernel<<<(n + 127) / 128, 128, 0, (cudaStream_t)stream>>>(
+        images, img_off, n_images, n, pred_xy, pred_z, out_loss, out_sign);
+    WCR_CHECK_LAUNCH("pseudo_z_point_kernel");
+    return WCR_OK;
+}
+
+extern "C" int wcr_pseudo_z_box_loss(const WcrImage *images, const int32_t *img_off, int n_images, int n,
+                                     const float *boxes, const float *pred_z, float *out_loss,
+                                     float *out_sign, float *ws_gt, int32_t *ws_inside, void *stream)
+{
+    WCR_CHECK_DEVICE();
+    WCR_REQUIRE(images && img_off && boxes && pred_z && out_loss && out_sign && ws_gt && ws_inside,
+                "wcr_pseudo_z_box_loss: null pointer");
+    WCR_REQUIRE(n_images >= 1 && n >= 0, "wcr_pseudo_z_box_loss: bad sizes");
+    if (n == 0) return WCR_OK;
+    wcr::box_median_kernel<<<n, 256, 0, (cudaStream_t)stream>>>(images, img_off, n_images, boxes, ws_gt, ws_inside);
+    WCR_CHECK_LAUNCH("box_median_kernel");
+    wcr::box_z_loss_kernel<<<(n_images + 127) / 128, 128, 0, (cudaStream_t)stream>>>(
+        img_off, n_images, ws_gt, ws_inside, pred_z, out_loss, out_sign);
+    WCR_CHECK_LAUNCH("box_z_loss_kernel");
+    return WCR_OK;
+}
+
+extern "C" int wcr_l1_loss_bwd(const float *sign, const float *grad, int n, float *d_pred, void *stream)
+{
+    WCR_CHECK_DEVICE();
+    WCR_REQUIRE(sign && grad && d_pred, "wcr_l1_loss_bwd: null pointer");
+    WCR_REQUIRE(n >= 0, "wcr_l1_loss_bwd: bad size");
+    if (n == 0) return WCR_OK;
+    wcr::l1_bwd_kernel<<<(n + 255) / 256, 256, 0, (cudaStream_t)stream>>>(sign, grad, n, d_pred);
+    WCR_CHECK_LAUNCH("l1_bwd_kernel");
+    return WCR_OK;
+}
+
+extern "C" int wcr_dim_loss_fwd(const float *prior_mean, const float *prior_std, const float *dims, int n,
+                                float *out3n, int32_t *nan_flag, void *stream)
+{
+    WCR_CHECK_DEVICE();
+    WCR_REQUIRE(prior_mean && prior_std && dims && out3n && nan_flag, "wcr_dim_loss_fwd: null pointer");
+    WCR_REQUIRE(n >= 0, "wcr_dim_loss_fwd: bad size");
+    cudaError_t e = cudaMemsetAsync(nan_flag, 0, sizeof(int32_t), (cudaStream_t)stream);
+    if (e != cudaSuccess) { wcr::set_error("cudaMemsetAsync: %s", cudaGetErrorString(e)); return WCR_ELAUNCH; }
+    if (n == 0) return WCR_OK;
+    wcr::dim_loss_kernel<<<(3 * n + 255) / 256, 256, 0, (cudaStream_t)stream>>>(prior_mean, prior_std, dims, n,
+                                                                              out3n, nan_flag);
+    WCR_CHECK_LAUNCH("dim_loss_kernel");
+    return WCR_OK;
+}
+
+extern "C" int wcr_dim_loss_bwd(const float *prior_mean, const float *prior_std, const float *dims,
+                                const float *grad3n, int n, float *d_dims, void *stream)
+{
+    WCR_CHECK_DEVICE();
+    WCR_REQUIRE(prior_mean && prior_std && dims && grad3n && d_dims, "wcr_dim_loss_bwd: null pointer");
+    WCR_REQUIRE(n >= 0, "wcr_dim_loss_bwd: bad size");
+    if (n == 0) return WCR_OK;
+    wcr::dim_loss_bwd_kernel<<<(3 * n + 255) / 256, 256, 0, (cudaStream_t)stream>>>(prior_mean, prior_std, dims,
+                                                                                  grad3n, n, d_dims);
+    WCR_CHECK_LAUNCH("dim_loss_bwd_kernel");
     return WCR_OK;
 }

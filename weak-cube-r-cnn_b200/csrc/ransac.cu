@@ -3,8 +3,8 @@
 // roi_heads.py:508-525 (axis fix-ups).
 //
 // The reference materialises a (1000 x N) distance matrix four times over; here
-// each thread owns one hypothesis (plane + 1/denominator in registers) and every
-// point of the image streams once through shared memory in float4 tiles.
+// each thread owns two hypotheses (planes in registers); a CTA tests them against one
+// 1024-point shared-memory tile of the image and adds the inlier counts atomically.
 // Rounding order is the reference's (see oracle/csrc/wcr_oracle.c):
 //   cross  = fma(a1, b2, -(a2*b1))           (torch.cross on CPU)
 //   norm   = sqrt(fma(z,z,fma(y,y,x*x)))     (torch.norm p=2)
@@ -16,8 +16,10 @@
 
 namespace wcr {
 
-constexpr int RANSAC_TPB = 128;    // hypotheses per CTA
-constexpr int RANSAC_TILE = 1024;  // points per shared-memory tile (16 KB)
+constexpr int RANSAC_TPB = 128;    // threads per CTA
+constexpr int RANSAC_HPT = 2;      // hypotheses per thread (registers)
+constexpr int RANSAC_HPB = RANSAC_TPB * RANSAC_HPT;
+constexpr int RANSAC_TILE = 1024;  // points per CTA (one 16 KB shared-memory tile)
 
 __device__ __forceinline__ float cross_c(float a1, float b2, float a2, float b1)
 {
@@ -40,7 +42,11 @@ __device__ __forceinline__ void philox_triple(uint64_t seed, uint32_t image, uin
     if (i2 >= hi) ++i2;
 }
 
-// grid = (ceil(iters / RANSAC_TPB), n_images)
+// grid = (ceil(iters / RANSAC_HPB), n_images, ceil(cap / RANSAC_TILE)): a CTA counts
+// the inliers of 256 hypotheses (2 per thread, planes in registers) among one tile of
+// 1024 points of one image and adds them to out_counts (zeroed by the caller). Cutting
+// the points as well as the hypotheses keeps every SM busy although images hold
+// between a few hundred and cap ground points; CTAs past the image's point count exit.
 __global__ void __launch_bounds__(RANSAC_TPB)
 ransac_count_kernel(const float4 *__restrict__ pts, const int *__restrict__ count, int cap,
                     const int32_t *__restrict__ sample_idx, int iters, float thresh,
@@ -49,59 +55,76 @@ ransac_count_kernel(const float4 *__restrict__ pts, const int *__restrict__ coun
     __shared__ float4 tile[RANSAC_TILE];
     const int img = blockIdx.y;
     const int n = count[img];
+    const int base = blockIdx.z * RANSAC_TILE;
+    if (base >= n && !(blockIdx.z == 0)) return;  // tile 0 always runs: it publishes the planes
     const float4 *P = pts + (size_t)img * cap;
-    const int h = blockIdx.x * RANSAC_TPB + threadIdx.x;
-    const bool live = h < iters;
+    const int m = max(0, min(RANSAC_TILE, n - base));
+    for (int j = threadIdx.x; j < m; j += RANSAC_TPB) tile[j] = P[base + j];
 
-    float a = 0.f, b = 0.f, c = 0.f, d = 0.f, den = 1.f;
-    if (live && n >= 3) {
-        int i0, i1, i2;
-        if (sample_idx) {
-            const int32_t *s = sample_idx + ((size_t)img * iters + h) * 3;
-            i0 = s[0]; i1 = s[1]; i2 = s[2];
-        } else {
-            philox_triple(seed, (uint32_t)img, (uint32_t)h, n, i0, i1, i2);
+    float a[RANSAC_HPT], b[RANSAC_HPT], c[RANSAC_HPT], d[RANSAC_HPT], den[RANSAC_HPT];
+    bool live[RANSAC_HPT];
+#pragma unroll
+    for (int t = 0; t < RANSAC_HPT; ++t) {
+        const int h = blockIdx.x * RANSAC_HPB + t * RANSAC_TPB + threadIdx.x;
+        live[t] = h < iters;
+        a[t] = b[t] = c[t] = d[t] = nanf_(); den[t] = 1.f;
+        if (live[t] && n >= 3) {
+            int i0, i1, i2;
+            if (sample_idx) {
+                const int32_t *s = sample_idx + ((size_t)img * iters + h) * 3;
+                i0 = s[0]; i1 = s[1]; i2 = s[2];
+            } else {
+                philox_triple(seed, (uint32_t)img, (uint32_t)h, n, i0, i1, i2);
+            }
+            const float4 p0 = P[i0], p1 = P[i1], p2 = P[i2];
+            const float ax = p1.x - p0.x, ay = p1.y - p0.y, az = p1.z - p0.z;
+            const float bx = p2.x - p0.x, by = p2.y - p0.y, bz = p2.z - p0.z;
+            float cx = cross_c(ay, bz, az, by);
+            float cy = cross_c(az, bx, ax, bz);
+            float cz = cross_c(ax, by, ay, bx);
+            const float nrm = sqrtf(fmaf(cz, cz, fmaf(cy, cy, cx * cx)));
+            cx = cx / nrm; cy = cy / nrm; cz = cz / nrm;  // collinear triple -> NaN, never an inlier
+            a[t] = cx; b[t] = cy; c[t] = cz;
+            d[t] = -((cx * p1.x + cy * p1.y) + cz * p1.z);
+            den[t] = sqrtf((cx * cx + cy * cy) + cz * cz);
         }
-        const float4 p0 = P[i0], p1 = P[i1], p2 = P[i2];
-        const float ax = p1.x - p0.x, ay = p1.y - p0.y, az = p1.z - p0.z;
-        const float bx = p2.x - p0.x, by = p2.y - p0.y, bz = p2.z - p0.z;
-        float cx = cross_c(ay, bz, az, by);
-        float cy = cross_c(az, bx, ax, bz);
-        float cz = cross_c(ax, by, ay, bx);
-        const float nrm = sqrtf(fmaf(cz, cz, fmaf(cy, cy, cx * cx)));
-        cx = cx / nrm; cy = cy / nrm; cz = cz / nrm;  // collinear triple -> NaN, never an inlier
-        a = cx; b = cy; c = cz;
-        d = -((cx * p1.x + cy * p1.y) + cz * p1.z);
-        den = sqrtf((a * a + b * b) + c * c);
-    } else if (live) {
-        a = b = c = d = nanf_();
+        if (live[t] && blockIdx.z == 0) eqs[(size_t)img * iters + h] = make_float4(a[t], b[t], c[t], d[t]);
     }
+    __syncthreads();
 
-    int cnt = 0;
-    for (int base = 0; base < n; base += RANSAC_TILE) {
-        const int m = min(RANSAC_TILE, n - base);
-        __syncthreads();
-        for (int j = threadIdx.x; j < m; j += RANSAC_TPB) tile[j] = P[base + j];
-        __syncthreads();
-        if (den == 1.0f) {  // x / 1.0f == x exactly: skip the IEEE division
+    int cnt[RANSAC_HPT];
+#pragma unroll
+    for (int t = 0; t < RANSAC_HPT; ++t) cnt[t] = 0;
+    // x / 1.0f == x exactly: the IEEE division is skipped when the denominator is 1
+    // (it nearly always is, the normal was just normalised)
+    bool unit = true;
+#pragma unroll
+    for (int t = 0; t < RANSAC_HPT; ++t) unit = unit && den[t] == 1.0f;
+    if (unit) {
 #pragma unroll 8
-            for (int j = 0; j < m; ++j) {
-                const float4 p = tile[j];
-                const float dist = ((a * p.x + b * p.y) + c * p.z) + d;
-                cnt += (fabsf(dist) <= thresh) ? 1 : 0;
+        for (int j = 0; j < m; ++j) {
+            const float4 p = tile[j];
+#pragma unroll
+            for (int t = 0; t < RANSAC_HPT; ++t) {
+                const float dist = ((a[t] * p.x + b[t] * p.y) + c[t] * p.z) + d[t];
+                cnt[t] += (fabsf(dist) <= thresh) ? 1 : 0;
             }
-        } else {
+        }
+    } else {
 #pragma unroll 4
-            for (int j = 0; j < m; ++j) {
-                const float4 p = tile[j];
-                const float dist = (((a * p.x + b * p.y) + c * p.z) + d) / den;
-                cnt += (fabsf(dist) <= thresh) ? 1 : 0;
+        for (int j = 0; j < m; ++j) {
+            const float4 p = tile[j];
+#pragma unroll
+            for (int t = 0; t < RANSAC_HPT; ++t) {
+                const float dist = (((a[t] * p.x + b[t] * p.y) + c[t] * p.z) + d[t]) / den[t];
+                cnt[t] += (fabsf(dist) <= thresh) ? 1 : 0;
             }
         }
     }
-    if (live) {
-        out_counts[(size_t)img * iters + h] = cnt;
-        eqs[(size_t)img * iters + h] = make_float4(a, b, c, d);
+#pragma unroll
+    for (int t = 0; t < RANSAC_HPT; ++t) {
+        const int h = blockIdx.x * RANSAC_HPB + t * RANSAC_TPB + threadIdx.x;
+        if (live[t] && cnt[t]) atomicAdd(out_counts + (size_t)img * iters + h, cnt[t]);
     }
 }
 
@@ -178,7 +201,11 @@ extern "C" int wcr_ransac_ground(const float *pts, const int *count, int cap, in
     WCR_REQUIRE((((uintptr_t)pts | (uintptr_t)ws_eqs) & 15) == 0,
                 "wcr_ransac_ground: pts/ws_eqs not 16-byte aligned");
     if (n_images == 0) return WCR_OK;
-    dim3 grid((iters + wcr::RANSAC_TPB - 1) / wcr::RANSAC_TPB, n_images);
+    WCR_REQUIRE((cap + wcr::RANSAC_TILE - 1) / wcr::RANSAC_TILE <= 65535, "wcr_ransac_ground: cap too large");
+    cudaError_t me = cudaMemsetAsync(out_counts, 0, (size_t)n_images * iters * sizeof(int), (cudaStream_t)stream);
+    if (me != cudaSuccess) { wcr::set_error("cudaMemsetAsync: %s", cudaGetErrorString(me)); return WCR_ELAUNCH; }
+    dim3 grid((iters + wcr::RANSAC_HPB - 1) / wcr::RANSAC_HPB, n_images,
+              (cap + wcr::RANSAC_TILE - 1) / wcr::RANSAC_TILE);
     wcr::ransac_count_kernel<<<grid, wcr::RANSAC_TPB, 0, (cudaStream_t)stream>>>(
         (const float4 *)pts, count, cap, sample_idx, iters, thresh, seed, (float4 *)ws_eqs,
         out_counts);

@@ -3,7 +3,7 @@
 //  * unproject_ground_kernel : strided, image-centre frame, ordered compaction of
 //    ground-mask pixels.  Reference: roi_heads.py:474-502.
 //  * unproject_cloud_kernel  : dense, K-principal-point frame,
-//    HBM-bound elementwise: 4 B read + 16 B written per pixel.
+//    HBM-bound elementwise: 4 B read + 16 B written per pixel, 4 pixels per thread.
 #include "common.cuh"
 
 namespace wcr {
@@ -67,31 +67,49 @@ unproject_ground_kernel(const WcrImage *__restrict__ images, int use_nth,
     if (threadIdx.x == 0) out_count[blockIdx.x] = base < cap ? base : cap;
 }
 
-// Dense cloud. grid = (ceil(Ws/256), Hs, n_images). One float read, one float4
-// (STG.128) written per thread: fully coalesced both ways.
-__global__ void __launch_bounds__(256)
-unproject_cloud_kernel(const WcrImage *__restrict__ images, int stride,
-                       float4 *__restrict__ out_xyz, int64_t plane_elems)
+// Dense cloud, HBM bound: 4 B read + 16 B written per pixel. Each thread takes 4
+// consecutive pixels of a row -- one LDG.128 when the row is 16-byte aligned and the
+// stride is 1, four STG.128 -- so a warp reads 512 B and writes 2 KB contiguous and
+// every thread keeps 80 B in flight. grid = (ceil(Hs * ceil(Ws/4) / 256), n_images).
+__device__ __forceinline__ float4 lift_pixel(float z, int u, int v, const WcrImage &im)
 {
-    const WcrImage im = images[blockIdx.z];
-    const int Hs = (im.H + stride - 1) / stride;
-    const int Ws = (im.W + stride - 1) / stride;
-    const int vs = blockIdx.y;
-    const int us = blockIdx.x * blockDim.x + threadIdx.x;
-    if (vs >= Hs || us >= Ws) return;
-    const int v = vs * stride, u = us * stride;
-    const float z = __ldg(im.depth + (size_t)v * im.depth_pitch + u);
-    float4 p;
     if (z > 0.f && z <= 3.402823466e38f) {  // finite and positive
+        float4 p;
         p.x = (z * ((float)u - im.cx)) / im.fx;  // roi_heads.py:927
         p.y = (z * ((float)v - im.cy)) / im.fy;  // roi_heads.py:928
         p.z = z;
         p.w = 0.f;
-    } else {
-        const float q = nanf_();
-        p = make_float4(q, q, q, 0.f);
+        return p;
     }
-    out_xyz[(size_t)blockIdx.z * plane_elems + (size_t)vs * Ws + us] = p;
+    const float q = nanf_();
+    return make_float4(q, q, q, 0.f);
+}
+
+__global__ void __launch_bounds__(256)
+unproject_cloud_kernel(const WcrImage *__restrict__ images, int stride,
+                       float4 *__restrict__ out_xyz, int64_t plane_elems)
+{
+    const WcrImage im = images[blockIdx.y];
+    const int Hs = (im.H + stride - 1) / stride;
+    const int Ws = (im.W + stride - 1) / stride;
+    const int wq = (Ws + 3) >> 2;
+    const int q = blockIdx.x * blockDim.x + threadIdx.x;
+    if (q >= Hs * wq) return;
+    const int vs = q / wq, us0 = (q - vs * wq) << 2;
+    const int v = vs * stride;
+    const float *row = im.depth + (size_t)v * im.depth_pitch;
+    float4 *dst = out_xyz + (size_t)blockIdx.y * plane_elems + (size_t)vs * Ws + us0;
+    float z[4];
+    if (stride == 1 && us0 + 3 < Ws && (((uintptr_t)(row + us0)) & 15) == 0) {
+        const float4 zz = __ldcs(reinterpret_cast<const float4 *>(row + us0));
+        z[0] = zz.x; z[1] = zz.y; z[2] = zz.z; z[3] = zz.w;
+    } else {
+#pragma unroll
+        for (int k = 0; k < 4; ++k) z[k] = (us0 + k < Ws) ? __ldcs(row + (size_t)(us0 + k) * stride) : 0.f;
+    }
+#pragma unroll
+    for (int k = 0; k < 4; ++k)
+        if (us0 + k < Ws) __stcs(dst + k, lift_pixel(z[k], (us0 + k) * stride, v, im));
 }
 
 }  // namespace wcr
@@ -123,7 +141,9 @@ extern "C" int wcr_unproject_cloud(const WcrImage *images, int n_images, int str
     WCR_REQUIRE(((uintptr_t)out_xyz & 15) == 0, "wcr_unproject_cloud: out_xyz not 16-byte aligned");
     WCR_REQUIRE(Hs <= 65535 && n_images <= 65535, "wcr_unproject_cloud: grid too large");
     if (n_images == 0) return WCR_OK;
-    dim3 grid((Ws + 255) / 256, Hs, n_images);
+    const int64_t quads = (int64_t)Hs * ((Ws + 3) / 4);
+    WCR_REQUIRE((quads + 255) / 256 < ((int64_t)1 << 31), "wcr_unproject_cloud: image too large");
+    dim3 grid((unsigned)((quads + 255) / 256), n_images);
     wcr::unproject_cloud_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(
         images, stride, (float4 *)out_xyz, plane_elems);
     WCR_CHECK_LAUNCH("unproject_cloud_kernel");

@@ -52,8 +52,16 @@ SIGNATURES = {
     "wcr_vectorized_linspace": (c_int, [c_void_p, c_void_p, c_int, c_int, c_void_p, c_void_p]),
     "wcr_weak_loss_fwd": (c_int, [c_void_p, c_void_p, c_void_p]),
     "wcr_weak_loss_bwd": (c_int, [c_void_p, c_void_p, c_void_p]),
+    "wcr_pose_loss_fwd": (c_int, [c_void_p, c_void_p, c_int, c_void_p, c_void_p, c_void_p]),
+    "wcr_pose_loss_bwd": (c_int, [c_void_p, c_void_p, c_int, c_void_p, c_void_p, c_void_p, c_void_p]),
+    "wcr_pseudo_z_point_loss": (c_int, [c_void_p, c_void_p, c_int, c_int, c_void_p, c_void_p, c_void_p,
+                                        c_void_p, c_void_p]),
+    "wcr_pseudo_z_box_loss": (c_int, [c_void_p, c_void_p, c_int, c_int, c_void_p, c_void_p, c_void_p,
+                                      c_void_p, c_void_p, c_void_p, c_void_p]),
+    "wcr_l1_loss_bwd": (c_int, [c_void_p, c_void_p, c_int, c_void_p, c_void_p]),
+    "wcr_dim_loss_fwd": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_void_p, c_void_p, c_void_p]),
+    "wcr_dim_loss_bwd": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_void_p, c_void_p]),
 }
-
 _lib = None
 
 

@@ -165,3 +165,165 @@ def safely_reduce_losses(loss: torch.Tensor) -> torch.Tensor:
     if valid.any():
         return loss[valid].mean()
     return loss.mean() * 0.0
+
+
+def _img_off(num_boxes_per_image, dev):
+    off = torch.zeros(len(num_boxes_per_image) + 1, dtype=torch.int32)
+    off[1:] = torch.cumsum(torch.as_tensor(list(num_boxes_per_image), dtype=torch.int32), 0)
+    return off.to(dev), int(off[-1])
+
+
+def _as_shard(depth_maps, dev) -> ImageShard:
+    if isinstance(depth_maps, ImageShard):
+        return depth_maps
+    n = len(depth_maps.image_sizes) if hasattr(depth_maps, "image_sizes") else len(depth_maps)
+    return ImageShard(depth_maps, None, [torch.eye(3)] * n, device=dev)
+
+
+class _PoseLossFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, cube_pose, off, n_images):
+        lib = _abi.load()
+        dev = cube_pose.device
+        R = cube_pose.detach().to(torch.float32).contiguous().view(-1, 9)
+        img_pose = torch.empty((n_images,), dtype=torch.float32, device=dev)
+        out3 = torch.empty((3,), dtype=torch.float32, device=dev)
+        _abi.check(lib.wcr_pose_loss_fwd(R.data_ptr(), off.data_ptr(), n_images, img_pose.data_ptr(),
+                                         out3.data_ptr(), _abi.stream_ptr(dev)), "wcr_pose_loss_fwd")
+        ctx.save_for_backward(R, off, out3)
+        ctx.n_images, ctx.shape = n_images, cube_pose.shape
+        return out3[:1].clone(), out3
+
+    @staticmethod
+    def backward(ctx, grad, _grad_aux):
+        lib = _abi.load()
+        R, off, out3 = ctx.saved_tensors
+        d_R = torch.zeros_like(R)
+        g = grad.to(torch.float32).contiguous()
+        _abi.check(lib.wcr_pose_loss_bwd(R.data_ptr(), off.data_ptr(), ctx.n_images, out3.data_ptr(),
+                                         g.data_ptr(), d_R.data_ptr(), _abi.stream_ptr(R.device)),
+                   "wcr_pose_loss_bwd")
+        return d_R.view(ctx.shape), None, None
+
+
+def pose_loss(cube_pose: torch.Tensor, num_boxes_per_image):
+    """roi_heads.py:445-464. (n,3,3) egocentric poses -> (1,) tensor, or ``None`` when
+    every image holds exactly one box. Differentiable (fused backward kernel). The
+    ``None`` decision needs no device sync: it depends on ``num_boxes_per_image`` only."""
+    _abi.require_cuda(cube_pose)
+    nb = list(num_boxes_per_image)
+    if all(b == 1 for b in nb):
+        return None
+    off, n = _img_off(nb, cube_pose.device)
+    assert n == cube_pose.shape[0]
+    loss, _ = _PoseLossFn.apply(cube_pose, off, len(nb))
+    return loss
+
+
+class _L1GatherFn(torch.autograd.Function):
+    """|pred_z - pseudo depth| with the pseudo depth looked up by a kernel."""
+
+    @staticmethod
+    def forward(ctx, pred_z, launch):
+        dev = pred_z.device
+        pz = pred_z.detach().to(torch.float32).contiguous().view(-1)
+        loss = torch.empty_like(pz)
+        sign = torch.empty_like(pz)
+        launch(pz, loss, sign)
+        ctx.save_for_backward(sign)
+        ctx.shape = pred_z.shape
+        return loss.view(pred_z.shape)
+
+    @staticmethod
+    def backward(ctx, grad):
+        lib = _abi.load()
+        (sign,) = ctx.saved_tensors
+        g = grad.to(torch.float32).contiguous().view(-1)
+        d = torch.empty_like(sign)
+        _abi.check(lib.wcr_l1_loss_bwd(sign.data_ptr(), g.data_ptr(), sign.numel(), d.data_ptr(),
+                                       _abi.stream_ptr(sign.device)), "wcr_l1_loss_bwd")
+        return d.view(ctx.shape), None
+
+
+def pseudo_gt_z_point_loss(depth_maps, pred_xy, pred_z, num_boxes_per_image):
+    """roi_heads.py:635-656: L1 between ``pred_z`` and the depth at the predicted centre
+    (clamped 10 px into the image, truncated). Gradient flows to ``pred_z`` only."""
+    _abi.require_cuda(pred_xy, pred_z)
+    lib = _abi.load()
+    dev = pred_z.device
+    shard = _as_shard(depth_maps, dev)
+    off, n = _img_off(num_boxes_per_image, dev)
+    xy = pred_xy.detach().to(torch.float32).contiguous().view(-1, 2)
+    assert n == xy.shape[0]
+
+    def launch(pz, loss, sign):
+        _abi.check(lib.wcr_pseudo_z_point_loss(shard.table.data_ptr(), off.data_ptr(), len(shard), n,
+                                               xy.data_ptr(), pz.data_ptr(), loss.data_ptr(),
+                                               sign.data_ptr(), _abi.stream_ptr(dev)),
+                   "wcr_pseudo_z_point_loss")
+    return _L1GatherFn.apply(pred_z, launch)
+
+
+def pseudo_gt_z_box_loss(depth_maps, proposal_boxes, pred_z):
+    """roi_heads.py:575-610 ('z_pseudo_gt_patch'): L1 between ``pred_z`` and the lower
+    median of the depth patch under each predicted 2D box. ``proposal_boxes``: one (b_i,4)
+    tensor per image. Reference quirk kept: within an image, boxes with zero area after
+    clipping are moved behind the others before pairing with ``pred_z`` by position."""
+    _abi.require_cuda(pred_z)
+    lib = _abi.load()
+    dev = pred_z.device
+    shard = _as_shard(depth_maps, dev)
+    boxes = [torch.as_tensor(b.tensor if hasattr(b, "tensor") else b) for b in proposal_boxes]
+    off, n = _img_off([b.shape[0] for b in boxes], dev)
+    bx = torch.cat([b.detach().to(device=dev, dtype=torch.float32).view(-1, 4) for b in boxes]).contiguous()
+    gt = torch.empty((max(n, 1),), dtype=torch.float32, device=dev)
+    inside = torch.empty((max(n, 1),), dtype=torch.int32, device=dev)
+
+    def launch(pz, loss, sign):
+        assert pz.numel() == n
+        _abi.check(lib.wcr_pseudo_z_box_loss(shard.table.data_ptr(), off.data_ptr(), len(shard), n,
+                                             bx.data_ptr(), pz.data_ptr(), loss.data_ptr(),
+                                             sign.data_ptr(), gt.data_ptr(), inside.data_ptr(),
+                                             _abi.stream_ptr(dev)), "wcr_pseudo_z_box_loss")
+    return _L1GatherFn.apply(pred_z, launch)
+
+
+class _DimLossFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, dims, mean, std):
+        lib = _abi.load()
+        dev = dims.device
+        d = dims.detach().to(torch.float32).contiguous().view(-1, 3)
+        n = d.shape[0]
+        out = torch.empty((3, max(n, 1)), dtype=torch.float32, device=dev)
+        flag = torch.zeros((1,), dtype=torch.int32, device=dev)
+        _abi.check(lib.wcr_dim_loss_fwd(mean.data_ptr(), std.data_ptr(), d.data_ptr(), n, out.data_ptr(),
+                                        flag.data_ptr(), _abi.stream_ptr(dev)), "wcr_dim_loss_fwd")
+        ctx.save_for_backward(d, mean, std)
+        ctx.shape = dims.shape
+        return out[:, :n], flag
+
+    @staticmethod
+    def backward(ctx, grad, _gflag):
+        lib = _abi.load()
+        d, mean, std = ctx.saved_tensors
+        n = d.shape[0]
+        g = grad.to(torch.float32).contiguous()
+        dd = torch.zeros_like(d)
+        _abi.check(lib.wcr_dim_loss_bwd(mean.data_ptr(), std.data_ptr(), d.data_ptr(), g.data_ptr(), n,
+                                        dd.data_ptr(), _abi.stream_ptr(d.device)), "wcr_dim_loss_bwd")
+        return dd.view(ctx.shape), None, None
+
+
+def dim_loss(priors, dimensions):
+    """roi_heads.py:612-633: ``priors = (prior_mean, prior_std)`` (n,3) each ->
+    three (n,) hinge losses ``max(|d - mean|/std - 1, 0)``, or ``(None, None, None)``
+    when a prior std is NaN (one 4-byte host read, the reference's ``mask.all()``)."""
+    prior_mean, prior_std = priors
+    _abi.require_cuda(dimensions, prior_mean, prior_std)
+    dev = dimensions.device
+    mean, std = _c(prior_mean, dev).view(-1, 3), _c(prior_std, dev).view(-1, 3)
+    out, flag = _DimLossFn.apply(dimensions, mean, std)
+    if int(flag.item()) != 0:
+        return None, None, None
+    return out[0], out[1], out[2]
