@@ -273,6 +273,8 @@ int wcr_vectorized_linspace(const float *start, const float *end, int M, int ste
 #define WCR_LOSS_POSE_GROUND  4   /* 'pose_ground'         */
 #define WCR_LOSS_Z_CENTER     8   /* 'z_pseudo_gt_center'  */
 #define WCR_LOSS_DIMS        16   /* 'dims'                */
+#define WCR_LOSS_Z_PATCH     32   /* 'z_pseudo_gt_patch' (takes precedence over the centre lookup,
+                                     roi_heads.py:1010-1013; same output slot WCR_T_PSEUDO_Z) */
 
 /* order of the scalar outputs (keys of the reference's loss dict, prefix 'Cube/') */
 enum { WCR_T_UNCERT = 0, WCR_T_IOU, WCR_T_POSE, WCR_T_NORMAL, WCR_T_PSEUDO_Z,
@@ -321,6 +323,11 @@ typedef struct WcrLossIO {
     const float *grad_losses; /* [8] upstream gradient of each scalar          */
     float *d_deltas, *d_z_raw, *d_dims_raw, *d_pose, *d_uncert;  /* same shapes as inputs */
     float *d_R_pose;          /* [n][9] workspace                              */
+    /* 'z_pseudo_gt_patch' only (NULL otherwise) */
+    float   *z_dec;           /* [n] decoded cube_z                            */
+    float   *z_gt;            /* [n] per-box pseudo depth (median / fallback)  */
+    int32_t *z_inside;        /* [n] 1 = box has area inside the image         */
+    float   *z_sign;          /* [n] sign(cube_z - pseudo depth), by position  */
 } WcrLossIO;
 
 int wcr_weak_loss_fwd(const WcrLossIO *h_io, const WcrLossParams *h_params, void *stream);

@@ -286,7 +286,9 @@ def weak_loss(cfg: LossConfig, deltas, z_raw, dims_raw, pose, uncert, *, src_box
         conf = ground_conf.repeat_interleave(nb, 0)
         pred_normal = R[:, 1, :]
         terms["normal_vec"] = (1 - F.cosine_similarity(nv, pred_normal, dim=1).abs()) * conf
-    if "z_pseudo_gt_center" in lf:
+    if "z_pseudo_gt_patch" in lf:    # if / elif of roi_heads.py:1010-1013
+        terms["pseudo_gt_z"] = pseudo_gt_z_box_loss(depth_maps, proj.split(list(num_boxes_per_image)), cube_z)
+    elif "z_pseudo_gt_center" in lf:
         cube_xy = torch.cat((cube_x.unsqueeze(1), cube_y.unsqueeze(1)), dim=1)
         terms["pseudo_gt_z"] = pseudo_gt_z_point_loss(depth_maps, cube_xy, cube_z, num_boxes_per_image)
     if "dims" in lf:

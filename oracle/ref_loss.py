@@ -77,7 +77,10 @@ def reference_weak_loss(cfg, deltas, z_raw, dims_raw, pose, uncert, *, src_boxes
         conf = ground_conf.repeat_interleave(nb, 0)
         pred_normal = cube_pose[:, 1, :]
         terms["normal_vec"] = (1 - F.cosine_similarity(nv, pred_normal, dim=1).abs()) * conf
-    if "z_pseudo_gt_center" in lf:   # :1012-1013
+    if "z_pseudo_gt_patch" in lf:   # :1010-1011
+        dm = standins.ImageList.from_tensors(list(depth_maps))
+        terms["pseudo_gt_z"] = head.pseudo_gt_z_box_loss(dm, proj.split(list(num_boxes_per_image)), cube_z)
+    elif "z_pseudo_gt_center" in lf:   # :1012-1013
         dm = standins.ImageList.from_tensors(list(depth_maps))
         terms["pseudo_gt_z"] = head.pseudo_gt_z_point_loss(dm, cube_xy, cube_z, list(num_boxes_per_image))
     if "dims" in lf:   # :1024-1025

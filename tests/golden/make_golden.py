@@ -182,7 +182,9 @@ def golden_loss():
     cases = [(0, [3, 1, 5, 2], False, {}),
              (1, [6, 2, 9], True, {"z_type": "sigmoid", "dims_priors_func": "sigmoid"}),
              (2, [1, 1], False, {}),
-             (3, [12, 7, 20], False, {"z_type": "log", "use_confidence": 0.0})]
+             (3, [12, 7, 20], False, {"z_type": "log", "use_confidence": 0.0}),
+             (4, [5, 1, 8], False, {"loss_functions": ["iou", "z_pseudo_gt_patch", "pose_alignment",
+                                                       "pose_ground", "dims"]})]
     for idx, (seed, nb, big, cfg_kw) in enumerate(cases):
         inp = li.make_loss_inputs(seed, nb, H=120, W=160, big=big)
         inp["depth_maps"] = [d.half().float() for d in inp["depth_maps"]]   # stored as fp16

@@ -56,7 +56,9 @@ def _check(La, ga, Lb, gb):
 
 CFGS = [dict(), dict(z_type="sigmoid", dims_priors_func="sigmoid"),
         dict(z_type="log", use_confidence=0.0),
-        dict(loss_functions=("iou", "dims")), dict(loss_functions=("pose_alignment", "pose_ground"))]
+        dict(loss_functions=("iou", "dims")), dict(loss_functions=("pose_alignment", "pose_ground")),
+        dict(loss_functions=("iou", "z_pseudo_gt_patch", "pose_alignment", "pose_ground", "dims")),
+        dict(loss_functions=("z_pseudo_gt_patch", "z_pseudo_gt_center"), z_type="sigmoid")]
 
 
 @pytest.mark.parametrize("seed,nb,big", [(0, [3, 1, 5, 2], False), (2, [6, 2, 9], True),

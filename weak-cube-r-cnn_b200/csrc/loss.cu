@@ -186,6 +186,7 @@ loss_box_fwd_kernel(const WcrLossIO io, const WcrLossParams P)
     for (int t = 0; t < 4; ++t) io.proj[4 * i + t] = proj[t];
 #pragma unroll
     for (int t = 0; t < 9; ++t) io.R_ego[9 * i + t] = d.R[t];
+    if (io.z_dec) io.z_dec[i] = d.z;
     const float q = nanf_();
     float term[LT];
 #pragma unroll
@@ -197,7 +198,7 @@ loss_box_fwd_kernel(const WcrLossIO io, const WcrLossParams P)
         const float c = cos_sim3(io.normals + 3 * img, d.R + 3, an, bn, &nb);   // row 1 of R (:992)
         term[WCR_T_NORMAL - 1] = (1.f - fabsf(c)) * io.ground_conf[img];
     }
-    if (P.loss_flags & WCR_LOSS_Z_CENTER)
+    if ((P.loss_flags & WCR_LOSS_Z_CENTER) && !(P.loss_flags & WCR_LOSS_Z_PATCH))
         term[WCR_T_PSEUDO_Z - 1] = fabsf(d.z - depth_at(io.images[img], d.cube_x, d.cube_y));
     if (P.loss_flags & WCR_LOSS_DIMS) {
 #pragma unroll
@@ -210,6 +211,14 @@ loss_box_fwd_kernel(const WcrLossIO io, const WcrLossParams P)
 #pragma unroll
     for (int t = 0; t < LT; ++t) io.terms[(size_t)t * io.n + i] = term[t];
 }
+
+__global__ void box_median_kernel(const WcrImage *__restrict__ images, const int32_t *__restrict__ img_off,
+                                  int n_images, const float *__restrict__ boxes, float *__restrict__ out_gt,
+                                  int *__restrict__ out_inside);
+__global__ void box_z_loss_kernel(const int32_t *__restrict__ img_off, int n_images,
+                                  const float *__restrict__ gt, const int *__restrict__ inside,
+                                  const float *__restrict__ pred_z, float *__restrict__ out_loss,
+                                  float *__restrict__ out_sign);
 
 // block-wide sum of (a, b) over 256 threads, result valid in every thread
 __device__ __forceinline__ void block_sum2(float &a, float &b, float *s_a, float *s_b)
@@ -275,7 +284,7 @@ __device__ __forceinline__ bool term_enabled(const WcrLossParams &P, int t)
     case WCR_T_IOU: return P.loss_flags & WCR_LOSS_IOU;
     case WCR_T_POSE: return P.loss_flags & WCR_LOSS_POSE_ALIGN;
     case WCR_T_NORMAL: return P.loss_flags & WCR_LOSS_POSE_GROUND;
-    case WCR_T_PSEUDO_Z: return P.loss_flags & WCR_LOSS_Z_CENTER;
+    case WCR_T_PSEUDO_Z: return P.loss_flags & (WCR_LOSS_Z_CENTER | WCR_LOSS_Z_PATCH);
     default: return P.loss_flags & WCR_LOSS_DIMS;
     }
 }
@@ -499,6 +508,11 @@ loss_box_bwd_kernel(const WcrLossIO io, const WcrLossParams P)
             for (int k = 0; k < 3; ++k) dR[3 + k] += (dc * an[k] - bn[k] * dot) / nb;
         }
     }
+    // ---- 'z_pseudo_gt_patch' (median of the depth patch; sign saved by position) --------
+    if ((P.loss_flags & WCR_LOSS_Z_PATCH) && io.present[WCR_T_PSEUDO_Z]) {
+        const float g = coef(WCR_T_PSEUDO_Z, io.terms[(size_t)(WCR_T_PSEUDO_Z - 1) * io.n + i]);
+        dz += g * io.z_sign[i];
+    } else
     // ---- 'z_pseudo_gt_center' ---------------------------------------------------------
     if ((P.loss_flags & WCR_LOSS_Z_CENTER) && io.present[WCR_T_PSEUDO_Z]) {
         const float diff = d.z - depth_at(io.images[img], d.cube_x, d.cube_y);
@@ -569,6 +583,9 @@ static int check_io(const WcrLossIO *io, const WcrLossParams *p, bool bwd)
                     io->d_uncert && io->d_R_pose, "wcr_weak_loss_bwd: null gradient pointer");
     WCR_REQUIRE(p->z_type >= 0 && p->z_type <= 2 && p->dims_func >= 0 && p->dims_func <= 1,
                 "wcr_weak_loss: unsupported z_type / dims_func");
+    if (p->loss_flags & WCR_LOSS_Z_PATCH)
+        WCR_REQUIRE(io->z_dec && io->z_gt && io->z_inside && io->z_sign,
+                    "wcr_weak_loss: 'z_pseudo_gt_patch' needs the z_dec / z_gt / z_inside / z_sign buffers");
     return WCR_OK;
 }
 
@@ -581,6 +598,16 @@ extern "C" int wcr_weak_loss_fwd(const WcrLossIO *h_io, const WcrLossParams *h_p
     if (h_io->n > 0) {
         wcr::loss_box_fwd_kernel<<<(h_io->n + 127) / 128, 128, 0, st>>>(*h_io, *h_params);
         WCR_CHECK_LAUNCH("loss_box_fwd_kernel");
+    }
+    if (h_io->n > 0 && (h_params->loss_flags & WCR_LOSS_Z_PATCH)) {
+        // roi_heads.py:1010-1011: pseudo depth = median of the depth patch under the PROJECTED box
+        wcr::box_median_kernel<<<h_io->n, 256, 0, st>>>(h_io->images, h_io->img_off, h_io->n_images,
+                                                        h_io->proj, h_io->z_gt, h_io->z_inside);
+        WCR_CHECK_LAUNCH("box_median_kernel");
+        wcr::box_z_loss_kernel<<<(h_io->n_images + 127) / 128, 128, 0, st>>>(
+            h_io->img_off, h_io->n_images, h_io->z_gt, h_io->z_inside, h_io->z_dec,
+            h_io->terms + (size_t)(WCR_T_PSEUDO_Z - 1) * h_io->n, h_io->z_sign);
+        WCR_CHECK_LAUNCH("box_z_loss_kernel");
     }
     wcr::loss_pose_fwd_kernel<<<h_io->n_images, 256, 0, st>>>(*h_io);
     WCR_CHECK_LAUNCH("loss_pose_fwd_kernel");
@@ -731,9 +758,15 @@ box_median_kernel(const WcrImage *__restrict__ images, const int32_t *__restrict
     const int b = blockIdx.x;
     const WcrImage im = images[image_of(img_off, n_images, b)];
     // Boxes.clip((h, w)), area() > 0 on the clipped float box, then .long() slicing
-    const float x1 = fminf(fmaxf(boxes[4 * b + 0], 0.f), (float)im.W), y1 = fminf(fmaxf(boxes[4 * b + 1], 0.f), (float)im.H);
-    const float x2 = fminf(fmaxf(boxes[4 * b + 2], 0.f), (float)im.W), y2 = fminf(fmaxf(boxes[4 * b + 3], 0.f), (float)im.H);
+    const float x1 = clamp_keep_nan(boxes[4 * b + 0], 0.f, (float)im.W), y1 = clamp_keep_nan(boxes[4 * b + 1], 0.f, (float)im.H);
+    const float x2 = clamp_keep_nan(boxes[4 * b + 2], 0.f, (float)im.W), y2 = clamp_keep_nan(boxes[4 * b + 3], 0.f, (float)im.H);
     const bool inside = (x2 - x1) * (y2 - y1) > 0.f;
+    if (x1 != x1 || y1 != y1 || x2 != x2 || y2 != y2) {
+        // a NaN box (cube behind the camera): the reference indexes with an undefined
+        // .long() here; defined as "no pseudo depth" (NaN, masked by the safe mean)
+        if (threadIdx.x == 0) { out_gt[b] = nanf_(); out_inside[b] = 0; }
+        return;
+    }
     if (!inside) {
         // fallback of :600-606: centre lookup of the CLIPPED box with the 10-px clamp
         if (threadIdx.x == 0) {

@@ -144,7 +144,8 @@ class LossParams(ctypes.Structure):
 _LOSS_IO_PTRS = ["deltas", "z_raw", "dims_raw", "pose", "uncert", "src_boxes", "K4", "v2r",
                  "prior_mean", "prior_std", "gt_boxes", "clamp", "img_off", "images", "normals",
                  "ground_conf", "losses", "present", "terms", "R_ego", "proj", "stats", "img_pose",
-                 "grad_losses", "d_deltas", "d_z_raw", "d_dims_raw", "d_pose", "d_uncert", "d_R_pose"]
+                 "grad_losses", "d_deltas", "d_z_raw", "d_dims_raw", "d_pose", "d_uncert", "d_R_pose",
+                 "z_dec", "z_gt", "z_inside", "z_sign"]
 
 
 class LossIO(ctypes.Structure):

@@ -21,7 +21,8 @@ from .images import ImageShard
 
 TERM_KEYS = ("Cube/uncert", "Cube/loss_iou", "Cube/loss_pose", "Cube/loss_normal_vec",
              "Cube/loss_pseudo_gt_z", "Cube/loss_dims_w", "Cube/loss_dims_h", "Cube/loss_dims_l")
-_FLAG = {"iou": 1, "pose_alignment": 2, "pose_ground": 4, "z_pseudo_gt_center": 8, "dims": 16}
+_FLAG = {"iou": 1, "pose_alignment": 2, "pose_ground": 4, "z_pseudo_gt_center": 8, "dims": 16,
+         "z_pseudo_gt_patch": 32}
 _ZTYPE = {"direct": 0, "sigmoid": 1, "log": 2}
 _DIMS = {"exp": 0, "sigmoid": 1}
 
@@ -87,6 +88,10 @@ class _Ctx:
             "proj": torch.empty((max(n, 1), 4), device=dev), "stats": torch.zeros(16, device=dev),
             "img_pose": torch.zeros(B, device=dev),
         }
+        if "z_pseudo_gt_patch" in cfg.loss_functions:
+            t.update({"z_dec": torch.empty(max(n, 1), device=dev), "z_gt": torch.empty(max(n, 1), device=dev),
+                      "z_inside": torch.empty(max(n, 1), dtype=torch.int32, device=dev),
+                      "z_sign": torch.zeros(max(n, 1), device=dev)})
         self.t = t
         self.n_images = B
 
