@@ -47,7 +47,7 @@ int         wcr_abi_version(void);
 const char *wcr_last_error(void);
 /* 0 if the current device is sm_100, else WCR_EARCH. */
 int         wcr_device_check(void);
-/* number of kernel launches enqueued by this library on the calling thread
+/* number of kernel launches enqueued by this library (all threads of the process)
  * since the last wcr_reset_launch_count() (bench.py's gpu_launches). */
 int64_t     wcr_launch_count(void);
 void        wcr_reset_launch_count(void);

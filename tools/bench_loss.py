@@ -1,0 +1,94 @@
+#!/usr/bin/env python
+"""BASELINE.json configs[2]: weak-loss forward + backward at ResNet34-FPN-shaped proposal
+counts (batch 16, n_i ~ U{1..128} foreground boxes per image, random-init head outputs).
+
+    python tools/bench_loss.py [--steps 50] [--warmup 5] [--cpu-repeats 3]
+
+Prints one JSON line: GPU time per fwd+bwd (CUDA events, median), kernel launches per
+step, and the CPU time of the same block through the oracle's torch + autograd
+restatement (`cpu_baseline`, kind "port": the reference's loss block needs detectron2
+objects and /root/reference, neither of which exists on the GPU box). Latency-bound by
+construction (a few hundred KB of data): no roofline claim.
+"""
+import argparse
+import json
+import os
+import statistics
+import sys
+import time
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "weak-cube-r-cnn_b200"))
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--steps", type=int, default=50)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--cpu-repeats", type=int, default=3)
+    ap.add_argument("--patch", action="store_true", help="use 'z_pseudo_gt_patch' (box median) instead of the centre lookup")
+    a = ap.parse_args()
+    import torch
+    from oracle import loss as ol, loss_inputs as li
+    from wcr import _abi
+    from wcr.images import ImageShard
+    from wcr.roi_heads import WeakLossConfig, weak_loss
+
+    g = torch.Generator().manual_seed(0)
+    nb = [int(x) for x in torch.randint(1, 129, (16,), generator=g)]
+    inp = li.make_loss_inputs(7, nb, H=480, W=640)
+    lf = ("iou", "z_pseudo_gt_patch" if a.patch else "z_pseudo_gt_center", "pose_alignment", "pose_ground", "dims")
+    # published weights: IOU 4, NORMAL_VEC 40, Z 100, DIMS 0.1, POSE 4 (README.md:185-191)
+    kw = dict(loss_functions=lf, loss_w_iou=4.0, loss_w_normal_vec=40.0, loss_w_z=100.0, loss_w_dims=0.1, loss_w_pose=4.0)
+    dev = torch.device("cuda", 0)
+    _abi.check(_abi.load().wcr_device_check(), "wcr_device_check")
+    shard = ImageShard([d.to(dev) for d in inp["depth_maps"]], None, [torch.eye(3)] * len(nb), device=dev)
+    leaves = {k: inp[k].to(dev).requires_grad_(True) for k in li.GRAD_KEYS}
+    rest = {k: (v.to(dev) if isinstance(v, torch.Tensor) else v) for k, v in inp.items()
+            if k not in li.GRAD_KEYS and k != "depth_maps"}
+    cfg = WeakLossConfig(**kw)
+
+    def step():
+        for v in leaves.values():
+            v.grad = None
+        losses = weak_loss(cfg, **leaves, **rest, depth_maps=shard)
+        sum(losses.values()).backward()
+        return losses
+
+    for _ in range(a.warmup):
+        step()
+    torch.cuda.synchronize()
+    ms = []
+    _abi.reset_launch_count()
+    for _ in range(a.steps):
+        e0, e1 = torch.cuda.Event(True), torch.cuda.Event(True)
+        e0.record(); step(); e1.record()
+        torch.cuda.synchronize()
+        ms.append(e0.elapsed_time(e1))
+    launches = _abi.launch_count() / a.steps
+    gpu_losses = {k: float(v) for k, v in step().items()}
+
+    torch.set_num_threads(os.cpu_count() or 1)
+    ocfg = ol.LossConfig(**kw)
+    cpu = []
+    for _ in range(a.cpu_repeats):
+        t0 = time.perf_counter()
+        Lc, _, _ = li.run_with_grads(ol.weak_loss, ocfg, inp)
+        cpu.append((time.perf_counter() - t0) * 1e3)
+    worst = max(abs(gpu_losses[k] - float(Lc[k])) / max(abs(float(Lc[k])), 1e-6) for k in Lc)
+    print(json.dumps({
+        "metric": "weak-loss fwd+bwd latency", "value": statistics.median(ms), "unit": "ms",
+        "higher_is_better": False, "n_gpus": 1, "steps": a.steps, "warmup": a.warmup, "dtype": "f32",
+        "data": "synthetic", "config": {"workload": f"weak-loss fwd/bwd, batch 16, {sum(nb)} foreground boxes "
+                                                    f"(n_i~U{{1..128}}), 480x640 depth, loss_functions={list(lf)}"},
+        "gpu_launches_per_step": launches, "ms_min": min(ms), "ms_max": max(ms),
+        "includes": "Python wrapper, one 32-byte D2H read of the 'present' flags, autograd bookkeeping",
+        "cpu_baseline": {"value": statistics.median(cpu), "unit": "ms", "cores": torch.get_num_threads(),
+                         "kind": "port", "sample": "the same inputs, oracle/loss.py (torch fp32 + autograd) on the host"},
+        "max_rel_diff_vs_cpu": worst,
+    }), flush=True)
+
+
+if __name__ == "__main__":
+    main()

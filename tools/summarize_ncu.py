@@ -89,5 +89,25 @@ def kernel(path):
             print(f"{k:12s} {v[0]:14d} {v[0] / tot:7.3f}  stall samples {v[1]}")
 
 
+def multi(path):
+    """One line per captured launch: duration, DRAM bytes and throughput, occupancy."""
+    raw = subprocess.run(["ncu", "-i", path, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
+    rows = list(csv.reader(io.StringIO(raw)))
+    h = rows[0]
+    ix = {n: i for i, n in enumerate(h)}
+    cols = ["gpu__time_duration.sum", "dram__bytes_read.sum", "dram__bytes_write.sum",
+            "dram__bytes.sum.per_second", "FBSP.TriageCompute.dram__throughput.avg.pct_of_peak_sustained_elapsed",
+            "sm__throughput.avg.pct_of_peak_sustained_elapsed",
+            "sm__warps_active.avg.pct_of_peak_sustained_active", "launch__registers_per_thread",
+            "launch__grid_size", "launch__block_size"]
+    cols = [c for c in cols if c in ix]
+    print(f"# {path}: ncu --set full, one row per captured launch (units: {', '.join(rows[1][ix[c]] or '-' for c in cols)})")
+    print("# kernel | " + " | ".join(cols))
+    for r in rows[2:]:
+        if len(r) < len(h):
+            continue
+        print(r[ix["Kernel Name"]].split("(")[0][:40] + " | " + " | ".join(r[ix[c]] for c in cols))
+
+
 if __name__ == "__main__":
-    {"launches": launches, "kernel": kernel}[sys.argv[1]](sys.argv[2])
+    {"launches": launches, "kernel": kernel, "multi": multi}[sys.argv[1]](sys.argv[2])

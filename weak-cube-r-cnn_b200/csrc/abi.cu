@@ -1,12 +1,13 @@
 // abi.cu -- error state, device check, launch bookkeeping for libwcr_b200.
 #include <stdarg.h>
 #include <string.h>
+#include <atomic>
 #include "common.cuh"
 
 namespace wcr {
 
 static thread_local char g_err[512] = "";
-static thread_local int64_t g_launches = 0;
+static std::atomic<int64_t> g_launches{0};  // process-wide: autograd runs backward on its own thread
 
 void set_error(const char *fmt, ...)
 {
@@ -16,7 +17,7 @@ void set_error(const char *fmt, ...)
     va_end(ap);
 }
 
-void count_launch(int n) { g_launches += n; }
+void count_launch(int n) { g_launches.fetch_add(n, std::memory_order_relaxed); }
 
 static int g_checked_dev = -1;
 static int g_checked_rc = WCR_OK;
@@ -62,8 +63,8 @@ extern "C" {
 int wcr_abi_version(void) { return WCR_ABI_VERSION; }
 const char *wcr_last_error(void) { return wcr::g_err; }
 int wcr_device_check(void) { return wcr::check_device(); }
-int64_t wcr_launch_count(void) { return wcr::g_launches; }
-void wcr_reset_launch_count(void) { wcr::g_launches = 0; }
+int64_t wcr_launch_count(void) { return wcr::g_launches.load(std::memory_order_relaxed); }
+void wcr_reset_launch_count(void) { wcr::g_launches.store(0, std::memory_order_relaxed); }
 
 }  // extern "C"
 

@@ -782,19 +782,41 @@ box_median_kernel(const WcrImage *__restrict__ images, const int32_t *__restrict
         return;
     }
     if (threadIdx.x == 0) { s_prefix = 0u; s_rank = (unsigned)((cnt - 1) / 2); s_nan = 0; }
+    const float inv_ncols = 1.0f / (float)ncols;
     for (int pass = 0; pass < 4; ++pass) {
         const int shift = 24 - 8 * pass;
         hist[threadIdx.x] = 0u;
         __syncthreads();
         const unsigned prefix = s_prefix;
         const unsigned himask = pass == 0 ? 0u : (0xffffffffu << (shift + 8));
-        for (int idx = threadIdx.x; idx < cnt; idx += 256) {
-            const int r = idx / ncols, c = idx - r * ncols;
-            const float f = im.depth[(size_t)(v0 + r) * im.depth_pitch + u0 + c];
-            if (pass == 0 && f != f) s_nan = 1;
-            const uint32_t k = float_key(f);
-            if ((k & himask) == prefix) atomicAdd(&hist[(k >> shift) & 255u], 1u);
+        // Depth values of a patch share their leading digits, so a plain shared-memory
+        // histogram serialises on one or two bins (2.5 ms for 1156 boxes, measured). Each
+        // thread run-length encodes its own stream instead: one atomic per change of bin.
+        unsigned last = 0xffffffffu, run = 0u;
+        // 4 independent loads in flight per thread (a clipped projected box can cover the
+        // whole image: one CTA then streams 307 k pixels per pass and is latency bound)
+        for (int i0 = threadIdx.x; i0 < cnt; i0 += 1024) {
+            float f[4];
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+                const int idx = i0 + 256 * q;
+                int r = __float2int_rz(((float)idx + 0.5f) * inv_ncols), c = idx - r * ncols;
+                if (c < 0) { --r; c += ncols; } else if (c >= ncols) { ++r; c -= ncols; }
+                f[q] = idx < cnt ? __ldg(im.depth + (size_t)(v0 + r) * im.depth_pitch + u0 + c) : 0.f;
+            }
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+                if (i0 + 256 * q >= cnt) break;
+                if (pass == 0 && f[q] != f[q]) s_nan = 1;
+                const uint32_t k = float_key(f[q]);
+                if ((k & himask) != prefix) continue;
+                const unsigned bin = (k >> shift) & 255u;
+                if (bin == last) { ++run; continue; }
+                if (run) atomicAdd(&hist[last], run);
+                last = bin; run = 1u;
+            }
         }
+        if (run) atomicAdd(&hist[last], run);
         __syncthreads();
         if (threadIdx.x == 0) {
             unsigned rank = s_rank, acc = 0u;

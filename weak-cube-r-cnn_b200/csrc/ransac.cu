@@ -17,7 +17,7 @@
 namespace wcr {
 
 constexpr int RANSAC_TPB = 128;    // threads per CTA
-constexpr int RANSAC_HPT = 2;      // hypotheses per thread (registers)
+constexpr int RANSAC_HPT = 4;      // hypotheses per thread (registers)
 constexpr int RANSAC_HPB = RANSAC_TPB * RANSAC_HPT;
 constexpr int RANSAC_TILE = 1024;  // points per CTA (one 16 KB shared-memory tile)
 
@@ -43,7 +43,7 @@ __device__ __forceinline__ void philox_triple(uint64_t seed, uint32_t image, uin
 }
 
 // grid = (ceil(iters / RANSAC_HPB), n_images, ceil(cap / RANSAC_TILE)): a CTA counts
-// the inliers of 256 hypotheses (2 per thread, planes in registers) among one tile of
+// the inliers of 512 hypotheses (4 per thread, planes in registers) among one tile of
 // 1024 points of one image and adds them to out_counts (zeroed by the caller). Cutting
 // the points as well as the hypotheses keeps every SM busy although images hold
 // between a few hundred and cap ground points; CTAs past the image's point count exit.
@@ -92,9 +92,11 @@ ransac_count_kernel(const float4 *__restrict__ pts, const int *__restrict__ coun
     }
     __syncthreads();
 
-    int cnt[RANSAC_HPT];
+    // float counters (exact: a tile holds 1024 points): FSET.BF + FADD run at full rate,
+    // FSETP + predicated IADD at a quarter of it on sm_100 (profiles/fp32_micro_r1.jsonl)
+    float cnt[RANSAC_HPT];
 #pragma unroll
-    for (int t = 0; t < RANSAC_HPT; ++t) cnt[t] = 0;
+    for (int t = 0; t < RANSAC_HPT; ++t) cnt[t] = 0.f;
     // x / 1.0f == x exactly: the IEEE division is skipped when the denominator is 1
     // (it nearly always is, the normal was just normalised)
     bool unit = true;
@@ -107,7 +109,7 @@ ransac_count_kernel(const float4 *__restrict__ pts, const int *__restrict__ coun
 #pragma unroll
             for (int t = 0; t < RANSAC_HPT; ++t) {
                 const float dist = ((a[t] * p.x + b[t] * p.y) + c[t] * p.z) + d[t];
-                cnt[t] += (fabsf(dist) <= thresh) ? 1 : 0;
+                cnt[t] += (fabsf(dist) <= thresh) ? 1.f : 0.f;
             }
         }
     } else {
@@ -117,14 +119,14 @@ ransac_count_kernel(const float4 *__restrict__ pts, const int *__restrict__ coun
 #pragma unroll
             for (int t = 0; t < RANSAC_HPT; ++t) {
                 const float dist = (((a[t] * p.x + b[t] * p.y) + c[t] * p.z) + d[t]) / den[t];
-                cnt[t] += (fabsf(dist) <= thresh) ? 1 : 0;
+                cnt[t] += (fabsf(dist) <= thresh) ? 1.f : 0.f;
             }
         }
     }
 #pragma unroll
     for (int t = 0; t < RANSAC_HPT; ++t) {
         const int h = blockIdx.x * RANSAC_HPB + t * RANSAC_TPB + threadIdx.x;
-        if (live[t] && cnt[t]) atomicAdd(out_counts + (size_t)img * iters + h, cnt[t]);
+        if (live[t] && cnt[t] > 0.f) atomicAdd(out_counts + (size_t)img * iters + h, (int)cnt[t]);
     }
 }
 
