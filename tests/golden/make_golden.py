@@ -178,6 +178,30 @@ def golden_zbox():
     print("zbox", loss.detach().numpy().round(3))
 
 
+def golden_replay():
+    """Proposal attributes (u v z w h l yaw) drawn by the REFERENCE's sampler
+    (sample_normal_in_range, utils.py:41-59, torch's global generator under manual_seed)
+    for a few boxes of one small synthetic image: the replay stream of the parity tests
+    (tests/test_oracle_compose.py on the CPU, tests/test_score_gpu.py on the GPU)."""
+    from oracle import compose, cubes as oc
+    from wcr import synth
+    H, W, N = 120, 160, 192
+    im = synth.make_image(77, H, W, n_boxes=4, dummy_ground=False)
+    priors_all = synth.make_priors()
+    depth, K = im["depth"].numpy(), im["K"].numpy()
+    boxes = im["boxes"].numpy()
+    normal = np.array([0.02, 0.999, -0.03], np.float32); normal /= np.linalg.norm(normal)
+    z0 = np.array([oc.box_center_depth(depth, b) for b in boxes], np.float32)
+    priors = priors_all[im["classes"]].numpy()
+    seeds = np.arange(4) + 900
+    attrs = np.stack([compose.draw_attributes(boxes[b], z0[b], priors[b], N, generator_seed=int(seeds[b]))
+                      for b in range(4)])
+    seg = synth.seg_masks(im["boxes"], H, W).numpy()
+    np.savez_compressed(os.path.join(HERE, "replay_0.npz"), depth=depth, K=K, boxes=boxes, normal=normal,
+                        z0=z0, priors=priors, classes=im["classes"].numpy(), seeds=seeds, attrs=attrs, seg=seg)
+    print("replay", attrs.shape, attrs[:, :, 0])
+
+
 def golden_loss():
     cases = [(0, [3, 1, 5, 2], False, {}),
              (1, [6, 2, 9], True, {"z_type": "sigmoid", "dims_priors_func": "sigmoid"}),
@@ -199,4 +223,5 @@ if __name__ == "__main__":
     golden_cubes()
     golden_hull()
     golden_zbox()
+    golden_replay()
     golden_loss()
