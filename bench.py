@@ -43,6 +43,7 @@ def parse():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="wcr", choices=["wcr", "reference"])
     ap.add_argument("--images", type=int, default=IMAGES_PER_GPU, help="images per GPU")
+    ap.add_argument("--boxes", type=int, default=None, help="GT boxes per image (default: Poisson(20))")
     ap.add_argument("--cpu-sample-images", type=int, default=None,
                     help="images of the workload the CPU arm processes (default: 24 for the "
                          "cpu_baseline leg, 6 per step for --impl reference)")
@@ -51,23 +52,39 @@ def parse():
     return ap.parse_args()
 
 
-def workload_name(images, seg=True):
-    return (f"SUN RGB-D val-shaped batch: {images} images {W}x{H} per GPU, ~20 GT boxes/image "
-            f"(Poisson), {NPROP} proposals/box, score = IoU2D x point-in-cube"
+def workload_name(images, seg=True, boxes=None):
+    return (f"SUN RGB-D val-shaped batch: {images} images {W}x{H} per GPU, "
+            f"{'~20 GT boxes/image (Poisson)' if boxes is None else str(boxes) + ' GT boxes/image'}, "
+            f"{NPROP} proposals/box, score = IoU2D x point-in-cube"
             f"{' x mask coverage' if seg else ''}, top-{TOPK}")
 
 
-def make_images(n, first, seg):
+def make_images(n, first, seg, n_boxes=None, dense=True):
+    """Synthetic images first..first+n-1. With ``dense=False`` the per-box masks are
+    bit-packed per image right away (a 1024-image shard would hold 6 GB of dense masks)."""
+    import numpy as np
     from wcr import synth
-    ims = synth.make_batch(n, H, W, first=first)
-    if seg:
-        for im in ims:
-            im["seg"] = synth.seg_masks(im["boxes"], H, W)
+    from wcr.proposals import pack_box_masks
+    ims = []
+    for i in range(n):
+        im = synth.make_image(first + i, H, W, n_boxes)
+        if seg:
+            m = synth.seg_masks(im["boxes"], H, W)
+            if dense:
+                im["seg"] = m
+            else:
+                b = im["boxes"].numpy()
+                rois = np.stack([np.minimum(np.maximum(b[:, 0], 0), W).astype(np.int32),
+                                 np.minimum(np.maximum(b[:, 1], 0), H).astype(np.int32),
+                                 np.minimum(np.maximum(b[:, 2], 0), W).astype(np.int32),
+                                 np.minimum(np.maximum(b[:, 3], 0), H).astype(np.int32)], 1)
+                im["seg_packed"] = pack_box_masks(rois, list(m))
+        ims.append(im)
     return ims
 
 
 # ------------------------------------------------------------------ CPU arm --
-def cpu_arm(n_images: int, first: int = 0, repeats: int = 1, seg: bool = True):
+def cpu_arm(n_images: int, first: int = 0, repeats: int = 1, seg: bool = True, n_boxes=None):
     """Time the oracle's C restatement (OpenMP, all cores) on `n_images` images of
     the workload. Returns (proposals/s, cores, sample string, seconds)."""
     import numpy as np
@@ -76,7 +93,7 @@ def cpu_arm(n_images: int, first: int = 0, repeats: int = 1, seg: bool = True):
     from wcr import synth
     import random
     clib.set_num_threads()          # torchrun exports OMP_NUM_THREADS=1: ask for every core
-    ims = make_images(n_images, first, seg)
+    ims = make_images(n_images, first, seg, n_boxes)
     priors = synth.make_priors()
     rng = np.random.default_rng(0)
     n_prop = 0
@@ -127,9 +144,9 @@ def run_reference(args):
     cpu_arm(1, seg=seg)  # warm
     vals, secs = [], 0.0
     for w in range(args.warmup):
-        cpu_arm(1, first=w, seg=seg)
+        cpu_arm(1, first=w, seg=seg, n_boxes=args.boxes)
     for s in range(args.steps):
-        v, cores, sample, dt = cpu_arm(n, first=s * n, seg=seg)
+        v, cores, sample, dt = cpu_arm(n, first=s * n, seg=seg, n_boxes=args.boxes)
         vals.append(v); secs += dt
     value = sum(vals) / len(vals)
     line = {
@@ -137,7 +154,7 @@ def run_reference(args):
         "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": 1e3 * secs / args.steps, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": workload_name(args.images, seg), "step_sample": sample},
+        "config": {"workload": workload_name(args.images, seg, args.boxes), "step_sample": sample},
         "cpu_baseline": {"value": value, "unit": "proposals/s", "cores": cores, "kind": "port",
                          "sample": sample},
         "e2e": {"value": value, "unit": "proposals/s", "h2d_bytes_per_step": 0,
@@ -225,7 +242,7 @@ def run_wcr(args):
 
     # weak scaling: every rank owns `images` images of the global synthetic set
     use_seg = not args.no_seg
-    ims = make_images(args.images, rank * args.images, use_seg)
+    ims = make_images(args.images, rank * args.images, use_seg, args.boxes, dense=False)
     priors = synth.make_priors()
     n_local_boxes = sum(len(im["boxes"]) for im in ims)
     gather = wdist.TopkGather(n_local_boxes, TOPK, dev)
@@ -329,7 +346,7 @@ def run_wcr(args):
             "unit": "proposals/s", "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
             "ms_per_step": step_ms / args.steps, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": workload_name(args.images, use_seg), "l2": "256 MiB flush between timed steps",
+            "config": {"workload": workload_name(args.images, use_seg, args.boxes), "l2": "256 MiB flush between timed steps",
                        "parallelism": f"image-sharded x{world}, all-gather of top-k records",
                        "boxes_rank0": runner.n_boxes, "rng": "in-kernel Philox4x32-10"},
             "e2e": {"value": total_props * args.steps / e2e_s, "unit": "proposals/s",
@@ -355,8 +372,9 @@ def run_wcr(args):
         if not args.no_cpu_baseline and world == 1:
             from oracle import clib
             clib.build()
-            cpu_arm(1, seg=use_seg)
-            v, cores, sample, dt = cpu_arm(args.cpu_sample_images or 24, seg=use_seg)
+            cpu_arm(1, seg=use_seg, n_boxes=args.boxes)
+            v, cores, sample, dt = cpu_arm(min(args.cpu_sample_images or 24, max(args.images, 1)), seg=use_seg,
+                                           n_boxes=args.boxes)
             line["cpu_baseline"] = {"value": v, "unit": "proposals/s", "cores": cores,
                                     "kind": "port", "sample": sample, "seconds": dt}
         print(json.dumps(line), flush=True)

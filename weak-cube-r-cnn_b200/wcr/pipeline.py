@@ -23,7 +23,7 @@ class ShardRunner:
                  priors: torch.Tensor, seed: int = 0, records: torch.Tensor | None = None):
         """``images``: host dicts with depth (H,W) f32, ground (H,W) u8 or (1,1),
         K (3,3), boxes (b,4), classes (b,) and -- when ``score_cfg.e_seg > 0`` -- seg
-        (b,H,W) per-box masks. All images are uploaded into two padded device planes
+        (b,H,W) per-box masks or seg_packed (``pack_box_masks`` output). All images are uploaded into two padded device planes
         so a step's H2D is a handful of large copies."""
         self.device = torch.device(device)
         if self.device.type != "cuda":
@@ -58,8 +58,10 @@ class ShardRunner:
         self.h_boxes = torch.from_numpy(self.boxes.host.view("uint8").copy()).pin_memory()
         self.seg = self.h_seg = None
         if self.score_cfg.e_seg > 0:
-            masks = [m for im in images for m in im["seg"]]
-            self.seg = SegMasks(self.shard, self.boxes, masks)
+            if all("seg_packed" in im for im in images):
+                self.seg = SegMasks(self.shard, self.boxes, packed=[w for im in images for w in im["seg_packed"]])
+            else:
+                self.seg = SegMasks(self.shard, self.boxes, [m for im in images for m in im["seg"]])
             self.h_seg = torch.from_numpy(self.seg.host_bits.view("int32").copy()).pin_memory()
         self.priors = priors.to(self.device, torch.float32).contiguous()
         nb = len(self.boxes)

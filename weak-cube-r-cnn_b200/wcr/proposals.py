@@ -144,33 +144,46 @@ def box_rois(boxes: "BoxTable", shard: ImageShard) -> np.ndarray:
     return np.stack([u0, v0, u1, v1], axis=1)
 
 
+def pack_box_masks(rois: np.ndarray, masks_per_box) -> list:
+    """Bit-pack one (H, W) mask per box over the box's integer ROI (rows padded to 32
+    bits, bit c & 31 of word c >> 5). -> list of uint32 arrays (nrows * wpr words each).
+    Host-side set-up (numpy packbits)."""
+    out = []
+    for (u0, v0, u1, v1), m in zip(rois, masks_per_box):
+        m = torch.as_tensor(m).cpu().numpy()
+        if u1 <= u0 or v1 <= v0:
+            out.append(np.zeros(0, dtype=np.uint32))
+            continue
+        sub = m[v0:v1, u0:u1] != 0
+        nrows, ncols = sub.shape
+        wpr = (ncols + 31) // 32
+        padded = np.zeros((nrows, wpr * 32), dtype=np.uint8)
+        padded[:, :ncols] = sub
+        out.append(np.packbits(padded, axis=1, bitorder="little").view("<u4").reshape(-1).copy())
+    return out
+
+
 class SegMasks:
     """Bit-packed per-box segmentation masks (include/wcr.h ``seg_bits``/``seg_off``).
 
     ``masks_per_box``: one (H, W) mask per box (bool / u8 / float, non-zero == object,
     host or device); only the box's integer ROI is kept -- the mask term of the
-    composite is defined on the ROI. Packing is host-side set-up
-    (numpy packbits), done once per shard."""
+    composite is defined on the ROI. ``packed``: the same already
+    packed by ``pack_box_masks`` (lets a caller stream images without holding every
+    dense mask). Packing is host-side set-up, done once per shard."""
 
-    def __init__(self, shard: ImageShard, boxes: "BoxTable", masks_per_box):
+    def __init__(self, shard: ImageShard, boxes: "BoxTable", masks_per_box=None, *, packed=None):
         rois = box_rois(boxes, shard)
-        words, off = [], [0]
-        for (u0, v0, u1, v1), m in zip(rois, masks_per_box):
-            m = torch.as_tensor(m).cpu().numpy()
-            sub = (m[v0:v1, u0:u1] != 0) if (u1 > u0 and v1 > v0) else np.zeros((0, 0), dtype=bool)
-            nrows, ncols = (sub.shape if sub.size else (0, 0))
-            wpr = (ncols + 31) // 32
-            if nrows * wpr:
-                padded = np.zeros((nrows, wpr * 32), dtype=np.uint8)
-                padded[:, :ncols] = sub
-                w = np.packbits(padded, axis=1, bitorder="little").view("<u4").reshape(-1)
-                words.append(w)
-            off.append(off[-1] + nrows * wpr)
-        allw = np.concatenate(words) if words else np.zeros(0, dtype=np.uint32)
-        if allw.size == 0:
-            allw = np.zeros(1, dtype=np.uint32)
-        self.host_bits, self.host_off = allw, np.asarray(off, dtype=np.int64)
-        self.bits = torch.from_numpy(allw.view(np.int32).copy()).to(shard.device)
+        words = packed if packed is not None else pack_box_masks(rois, masks_per_box)
+        assert len(words) == len(rois)
+        off = [0]
+        for (u0, v0, u1, v1), w in zip(rois, words):
+            expect = max(v1 - v0, 0) * ((max(u1 - u0, 0) + 31) // 32)
+            assert len(w) == expect, "packed mask does not match the box ROI"
+            off.append(off[-1] + len(w))
+        allw = np.concatenate(words) if len(words) and off[-1] else np.zeros(1, dtype=np.uint32)
+        self.host_bits, self.host_off = allw.astype(np.uint32), np.asarray(off, dtype=np.int64)
+        self.bits = torch.from_numpy(self.host_bits.view(np.int32).copy()).to(shard.device)
         self.off = torch.from_numpy(self.host_off.copy()).to(shard.device)
         self.n_boxes = len(rois)
 
