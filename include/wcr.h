@@ -275,10 +275,28 @@ int wcr_vectorized_linspace(const float *start, const float *end, int M, int ste
 #define WCR_LOSS_DIMS        16   /* 'dims'                */
 #define WCR_LOSS_Z_PATCH     32   /* 'z_pseudo_gt_patch' (takes precedence over the centre lookup,
                                      roi_heads.py:1010-1013; same output slot WCR_T_PSEUDO_Z) */
+/* tier-2 terms */
+#define WCR_LOSS_Z_SEARCH    64   /* 'z': z_loss, roi_heads.py:530-573 (50 offsets of 0.1 m, arg-min of
+                                     the projected-area mismatch; value only, zero gradient) */
+#define WCR_LOSS_DEPTH      128   /* 'depth': depth_range_loss, :658-684 (q90 - q10 of the depth under
+                                     the object's mask vs the depth extent of the cube corners) */
+#define WCR_LOSS_POSE_GROUND2 256 /* 'pose_ground2': normal_to_rotation + so3_relative_angle, :686-696,
+                                     :997-1007; overrides 'pose_ground' in slot WCR_T_NORMAL */
 
 /* order of the scalar outputs (keys of the reference's loss dict, prefix 'Cube/') */
 enum { WCR_T_UNCERT = 0, WCR_T_IOU, WCR_T_POSE, WCR_T_NORMAL, WCR_T_PSEUDO_Z,
-       WCR_T_DIMS_W, WCR_T_DIMS_H, WCR_T_DIMS_L, WCR_LOSS_TERMS };
+       WCR_T_DIMS_W, WCR_T_DIMS_H, WCR_T_DIMS_L, WCR_T_Z, WCR_T_DEPTH, WCR_LOSS_TERMS };
+/* slots of WcrLossIO.stats beyond the per-term valid counts */
+enum { WCR_STAT_POSE = 16, WCR_STAT_FAIL = 17,
+       WCR_STAT_TRACE_ERR = 18,  /* != 0: a relative rotation of 'pose_ground2' has its trace outside
+                                    [-1-1e-4, 3+1e-4] (pytorch3d raises ValueError there)          */
+       WCR_STAT_SHAPE_ERR = 19,  /* != 0: 'depth' with a mask whose shape differs from its depth map */
+       WCR_LOSS_STATS = 32 };
+#define WCR_Z_LOSS_STEPS 50      /* max_count of z_loss (roi_heads.py:531) */
+
+/* torch.linspace(0, 4.9, 50) as z_loss builds it (roi_heads.py:547): host function, no GPU
+ * needed; the fused kernel uses exactly this table. */
+void wcr_z_loss_steps(float out[WCR_Z_LOSS_STEPS]);
 
 typedef struct WcrLossParams {
     int32_t loss_flags;       /* WCR_LOSS_* bits (cfg.loss_functions, config.py:186)   */
@@ -286,6 +304,7 @@ typedef struct WcrLossParams {
     int32_t dims_func;        /* 0 exp, 1 sigmoid            (roi_heads.py:856-861)    */
     float   use_confidence;   /* cfg USE_CONFIDENCE; 0 disables uncertainty scaling    */
     float   w_3d, w_iou, w_pose, w_normal, w_z, w_dims;   /* LOSS_W_* (config.py:119-127) */
+    float   w_depth;          /* LOSS_W_DEPTH (config.py:127)                          */
 } WcrLossParams;
 
 /* Every per-box array is indexed by foreground box, boxes of one image contiguous
@@ -311,16 +330,18 @@ typedef struct WcrLossIO {
     const float *normals;     /* [n_images][3] from wcr_ransac_ground         */
     const float *ground_conf; /* [n_images] 0.1 for the (1,1) dummy else 1 (roi_heads.py:988) */
     /* forward outputs / backward inputs */
-    float   *losses;          /* [8] scalars, already times w_term * w_3d     */
-    int32_t *present;         /* [8] 0 where the reference would not emit the key (None) */
-    float   *terms;           /* [7][n] raw per-box terms before uncertainty scaling,
+    float   *losses;          /* [WCR_LOSS_TERMS] scalars, already times w_term * w_3d */
+    int32_t *present;         /* [WCR_LOSS_TERMS + 2] 0 where the reference would not emit the key (None);
+                                 then copies of the WCR_STAT_TRACE_ERR / WCR_STAT_SHAPE_ERR flags so one
+                                 small D2H read tells the caller everything */
+    float   *terms;           /* [WCR_LOSS_TERMS-1][n] raw per-box terms before uncertainty scaling,
                                  row t-1 for term t (row WCR_T_POSE-1 holds the broadcast scalar) */
     float   *R_ego;           /* [n][9] egocentric pose after R_from_allocentric */
     float   *proj;            /* [n][4] projected boxes                        */
-    float   *stats;           /* [16]  n_valid per term (8), pose scalar, fail count ... */
+    float   *stats;           /* [WCR_LOSS_STATS] n_valid per term, then the WCR_STAT_* slots */
     float   *img_pose;        /* [n_images] per-image pose term (workspace)    */
     /* backward only */
-    const float *grad_losses; /* [8] upstream gradient of each scalar          */
+    const float *grad_losses; /* [WCR_LOSS_TERMS] upstream gradient of each scalar */
     float *d_deltas, *d_z_raw, *d_dims_raw, *d_pose, *d_uncert;  /* same shapes as inputs */
     float *d_R_pose;          /* [n][9] workspace                              */
     /* 'z_pseudo_gt_patch' only (NULL otherwise) */
@@ -328,7 +349,22 @@ typedef struct WcrLossIO {
     float   *z_gt;            /* [n] per-box pseudo depth (median / fallback)  */
     int32_t *z_inside;        /* [n] 1 = box has area inside the image         */
     float   *z_sign;          /* [n] sign(cube_z - pseudo depth), by position  */
+    /* 'depth' only (NULL otherwise): per-object masks as the reference's masks_all_images
+     * (roi_heads.py:273), dense, non-zero == object. Every mask must have the shape of the
+     * depth map of the image its boxes belong to (the reference's align_corners bilinear
+     * resize, :672, is the identity then); a mismatch sets stats[WCR_STAT_SHAPE_ERR]. */
+    const uint8_t *masks;     /* [n_masks][mask_h][mask_w]                     */
+    int32_t  mask_h, mask_w;
+    const int32_t *mask_idx;  /* [n] at_which_mask_idx (:723-726)              */
+    float   *depth_gt;        /* [n] out: q90 - q10 of the masked depth (GT box patch when the mask is empty) */
+    /* 'pose_ground2' only (NULL otherwise) */
+    float   *gt_rot;          /* [n_images][9] workspace: normal_to_rotation per image */
 } WcrLossIO;
+
+/* sizeof() of the ABI structs as the library was compiled, so a binding can verify its
+ * mirror: 0 WcrImage, 1 WcrBox, 2 WcrSampleParams, 3 WcrScoreParams, 4 WcrLossParams,
+ * 5 WcrLossIO; anything else -> 0. Host function, no GPU needed. */
+int64_t wcr_sizeof(int which);
 
 int wcr_weak_loss_fwd(const WcrLossIO *h_io, const WcrLossParams *h_params, void *stream);
 int wcr_weak_loss_bwd(const WcrLossIO *h_io, const WcrLossParams *h_params, void *stream);

@@ -53,6 +53,8 @@ class LossConfig:
     loss_w_normal_vec: float = 20.0
     loss_w_z: float = 1.0
     loss_w_dims: float = 20.0
+    loss_w_seg: float = 2.5             # config.py:124
+    loss_w_depth: float = 1.0           # config.py:127
 
 
 def axis_angle_to_matrix(aa: torch.Tensor) -> torch.Tensor:
@@ -105,9 +107,8 @@ def cuboid_corners(box6, R):
     return verts.transpose(1, 2)
 
 
-def projected_boxes(box6, R, K4, clamp):
-    """spaces.py:224-245 + conversions.py:25-48 with one K and one clamp per box
-    (roi_heads.py:957-960 loops box by box). clamp (n,2) integers."""
+def bube_corners(box6, R, K4, clamp):
+    """spaces.py:224-245 with one K and one clamp per box: (n,8,2) clamped projected corners."""
     corners = cuboid_corners(box6, R)                         # (n,8,3)
     fx, fy, cx, cy = (K4[:, i:i + 1] for i in range(4))
     X, Y, Z = corners[..., 0], corners[..., 1], corners[..., 2]
@@ -118,6 +119,14 @@ def projected_boxes(box6, R, K4, clamp):
     lo1, hi1 = torch.trunc(-c1 / 2 + 1), torch.trunc(c1 - 1 + c1)
     x = _clamp_closed(px, lo0, hi0)      # torch.clamp(x, int, int) forward and backward rule
     y = _clamp_closed(py, lo1, hi1)
+    return torch.stack((x, y), -1)
+
+
+def projected_boxes(box6, R, K4, clamp):
+    """conversions.py:25-48 over bube_corners (roi_heads.py:957-960 loops box by box).
+    clamp (n,2) integers."""
+    b = bube_corners(box6, R, K4, clamp)
+    x, y = b[..., 0], b[..., 1]
     return torch.stack((x.min(1).values, y.min(1).values, x.max(1).values, y.max(1).values), 1)
 
 
@@ -263,7 +272,7 @@ def decode(cfg: LossConfig, deltas, z_raw, dims_raw, pose, src_boxes, K4, virtua
 
 def weak_loss(cfg: LossConfig, deltas, z_raw, dims_raw, pose, uncert, *, src_boxes, K4,
               virtual_to_real, prior_mean, prior_std, gt_boxes, clamp, num_boxes_per_image,
-              depth_maps, normals, ground_conf):
+              depth_maps, normals, ground_conf, gt_masks=None, at_which_mask_idx=None):
     """The loss block. Per-box tensors are (n, ...); normals (B,3) and ground_conf
     (B,) are per image (0.1 where the ground map is the (1,1) dummy, roi_heads.py:988).
     -> (dict of scalar losses keyed like the reference, dict of per-box raw terms)."""
@@ -286,15 +295,31 @@ def weak_loss(cfg: LossConfig, deltas, z_raw, dims_raw, pose, uncert, *, src_box
         conf = ground_conf.repeat_interleave(nb, 0)
         pred_normal = R[:, 1, :]
         terms["normal_vec"] = (1 - F.cosine_similarity(nv, pred_normal, dim=1).abs()) * conf
+    if "pose_ground2" in lf:         # roi_heads.py:997-1007, overrides 'pose_ground'
+        from . import loss_tier2 as t2
+        terms["normal_vec"] = t2.pose_ground2(R, normals, ground_conf, num_boxes_per_image)
     if "z_pseudo_gt_patch" in lf:    # if / elif of roi_heads.py:1010-1013
         terms["pseudo_gt_z"] = pseudo_gt_z_box_loss(depth_maps, proj.split(list(num_boxes_per_image)), cube_z)
     elif "z_pseudo_gt_center" in lf:
         cube_xy = torch.cat((cube_x.unsqueeze(1), cube_y.unsqueeze(1)), dim=1)
         terms["pseudo_gt_z"] = pseudo_gt_z_point_loss(depth_maps, cube_xy, cube_z, num_boxes_per_image)
+    if "segmentation" in lf:         # roi_heads.py:948-954, 1016-1017
+        from . import loss_tier2 as t2
+        bube = torch.stack([t2.clamp_bube_corners(bube_corners(box6[i:i + 1], R[i:i + 1], K4[i:i + 1],
+                                                               clamp[i:i + 1])[0], clamp[i]) for i in range(n)])
+        terms["seg"] = t2.segment_loss(gt_masks, bube.detach(), at_which_mask_idx)
+    if "z" in lf:                    # :1019-1021
+        from . import loss_tier2 as t2
+        terms["z"] = t2.z_loss(gt_boxes, box6, R, K4, clamp.float(), proj)
     if "dims" in lf:
         lw, lh, ll = dim_loss(prior_mean, prior_std, dims)
         if lw is not None:
             terms["dims_w"], terms["dims_h"], terms["dims_l"] = lw, lh, ll
+    if "depth" in lf:                # :1027-1029
+        from . import loss_tier2 as t2
+        terms["depth"], gts = t2.depth_range_loss(gt_masks, at_which_mask_idx, depth_maps, box6, R, gt_boxes,
+                                                  num_boxes_per_image)
+        per_box["depth_gt"] = gts
     per_box.update({"raw_" + k: v.detach().clone() for k, v in terms.items()})
     losses = {}
     if cfg.use_confidence > 0:
@@ -303,7 +328,7 @@ def weak_loss(cfg: LossConfig, deltas, z_raw, dims_raw, pose, uncert, *, src_box
         losses["Cube/uncert"] = cfg.use_confidence * safely_reduce_losses(uncert.clone())
     w = {"iou": cfg.loss_w_iou, "pose": cfg.loss_w_pose, "normal_vec": cfg.loss_w_normal_vec,
          "pseudo_gt_z": cfg.loss_w_z, "dims_w": cfg.loss_w_dims, "dims_h": cfg.loss_w_dims,
-         "dims_l": cfg.loss_w_dims}
+         "dims_l": cfg.loss_w_dims, "seg": cfg.loss_w_seg, "z": cfg.loss_w_z, "depth": cfg.loss_w_depth}
     for k, v in terms.items():
         losses["Cube/loss_" + k] = safely_reduce_losses(v) * w[k] * cfg.loss_w_3d
     return losses, per_box

@@ -57,3 +57,34 @@ def run_with_grads(fn, cfg, inp):
     total.backward()
     return ({k: v.detach() for k, v in losses.items()}, per_box,
             {k: (v.grad if v.grad is not None else torch.zeros_like(v)) for k, v in leaves.items()})
+
+
+def add_masks(inp: dict, seed: int, H=480, W=640, share_every=4, empty_every=7) -> dict:
+    """Per-object GT masks for the tier-2 terms ('segmentation', 'depth'): one filled ellipse
+    inside each GT box as a (1, H, W) bool tensor; every ``share_every``-th box re-uses
+    the previous box's mask (several proposals matched to one object,
+    roi_heads.py:262-270) and every ``empty_every``-th mask is empty (segmentation failed:
+    depth_range_loss falls back to the GT box, roi_heads.py:674-675)."""
+    g = torch.Generator().manual_seed(seed + 991)
+    gt = inp["gt_boxes"]
+    n = gt.shape[0]
+    ys = torch.arange(H, dtype=torch.float32)[:, None]
+    xs = torch.arange(W, dtype=torch.float32)[None, :]
+    masks, idx = [], []
+    for i in range(n):
+        if i % share_every == share_every - 1 and masks:
+            idx.append(len(masks) - 1)
+            continue
+        x1, y1, x2, y2 = gt[i].tolist()
+        cx, cy = 0.5 * (x1 + x2), 0.5 * (y1 + y2)
+        rx = 0.5 * (x2 - x1) * (0.5 + 0.5 * torch.rand((), generator=g).item())
+        ry = 0.5 * (y2 - y1) * (0.5 + 0.5 * torch.rand((), generator=g).item())
+        m = ((xs - cx) / rx) ** 2 + ((ys - cy) / ry) ** 2 <= 1.0
+        if len(masks) % empty_every == empty_every - 1:
+            m = torch.zeros_like(m)
+        masks.append(m[None])
+        idx.append(len(masks) - 1)
+    out = dict(inp)
+    out["gt_masks"] = masks
+    out["at_which_mask_idx"] = idx
+    return out

@@ -19,7 +19,8 @@ from . import refshim, standins
 
 def reference_weak_loss(cfg, deltas, z_raw, dims_raw, pose, uncert, *, src_boxes, K4,
                         virtual_to_real, prior_mean, prior_std, gt_boxes, clamp,
-                        num_boxes_per_image, depth_maps, normals, ground_conf):
+                        num_boxes_per_image, depth_maps, normals, ground_conf, gt_masks=None,
+                        at_which_mask_idx=None):
     from torchvision.ops import generalized_box_iou_loss
     ns = refshim.load()
     head = refshim.roi_head_instance()
@@ -77,16 +78,36 @@ def reference_weak_loss(cfg, deltas, z_raw, dims_raw, pose, uncert, *, src_boxes
         conf = ground_conf.repeat_interleave(nb, 0)
         pred_normal = cube_pose[:, 1, :]
         terms["normal_vec"] = (1 - F.cosine_similarity(nv, pred_normal, dim=1).abs()) * conf
+    if "pose_ground2" in lf:   # :997-1007
+        nb = torch.tensor(list(num_boxes_per_image))
+        nv = normals.repeat_interleave(nb, 0)
+        conf = ground_conf.repeat_interleave(nb, 0)
+        gt_R = head.normal_to_rotation(nv)
+        terms["normal_vec"] = (1 - ns.roi_heads.so3_relative_angle(cube_pose, gt_R, cos_angle=True)) * conf
     if "z_pseudo_gt_patch" in lf:   # :1010-1011
         dm = standins.ImageList.from_tensors(list(depth_maps))
         terms["pseudo_gt_z"] = head.pseudo_gt_z_box_loss(dm, proj.split(list(num_boxes_per_image)), cube_z)
     elif "z_pseudo_gt_center" in lf:   # :1012-1013
         dm = standins.ImageList.from_tensors(list(depth_maps))
         terms["pseudo_gt_z"] = head.pseudo_gt_z_point_loss(dm, cube_xy, cube_z, list(num_boxes_per_image))
+    if "segmentation" in lf:   # :948-954, 1016-1017
+        bube = torch.zeros((n, 8, 2))
+        for i in range(n):
+            bc = cubes[i].get_bube_corners(Ks[i], im_sizes[i])
+            x = torch.clamp(bc[..., 0], 0, int(im_sizes[i][0] - 1))
+            y = torch.clamp(bc[..., 1], 0, int(im_sizes[i][1] - 1))
+            bube[i] = torch.stack((x, y), dim=-1)
+        terms["seg"] = head.segment_loss(gt_masks, bube, at_which_mask_idx)
+    if "z" in lf:   # :1019-1021
+        terms["z"] = head.z_loss(standins.Boxes(gt_boxes), cubes, Ks, im_sizes, standins.Boxes(proj))
     if "dims" in lf:   # :1024-1025
         lw, lh, ll = head.dim_loss((prior_mean, prior_std), cubes.dimensions.squeeze(1))
         if lw is not None:
             terms["dims_w"], terms["dims_h"], terms["dims_l"] = lw, lh, ll
+    if "depth" in lf:   # :1027-1029
+        dm = standins.ImageList.from_tensors(list(depth_maps))
+        terms["depth"] = head.depth_range_loss(gt_masks, at_which_mask_idx, dm, cubes, standins.Boxes(gt_boxes),
+                                               list(num_boxes_per_image))
     per_box = {"proj": proj.detach(), "cube_z": cube_z.detach(), "dims": cube_dims.detach(),
                "R": cube_pose.detach()}
     per_box.update({"raw_" + k: v.detach().clone() for k, v in terms.items()})
@@ -97,7 +118,7 @@ def reference_weak_loss(cfg, deltas, z_raw, dims_raw, pose, uncert, *, src_boxes
         losses["Cube/uncert"] = cfg.use_confidence * head.safely_reduce_losses(uncert.clone())
     w = {"iou": cfg.loss_w_iou, "pose": cfg.loss_w_pose, "normal_vec": cfg.loss_w_normal_vec,
          "pseudo_gt_z": cfg.loss_w_z, "dims_w": cfg.loss_w_dims, "dims_h": cfg.loss_w_dims,
-         "dims_l": cfg.loss_w_dims}
+         "dims_l": cfg.loss_w_dims, "seg": cfg.loss_w_seg, "z": cfg.loss_w_z, "depth": cfg.loss_w_depth}
     for k, v in terms.items():   # :1107-1144
         losses["Cube/loss_" + k] = head.safely_reduce_losses(v) * w[k] * cfg.loss_w_3d
     return losses, per_box

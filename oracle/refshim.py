@@ -116,6 +116,10 @@ def _install():
     p3t = importlib.import_module("pytorch3d.transforms")
     p3t.axis_angle_to_matrix = standins.axis_angle_to_matrix
     p3t.rotation_6d_to_matrix = standins.rotation_6d_to_matrix
+    p3so3 = importlib.import_module("pytorch3d.transforms.so3")
+    p3so3.so3_relative_angle = standins.so3_relative_angle
+    tvo = importlib.import_module("torchvision.ops")   # real torchvision: keep its focal / GIoU losses
+    assert hasattr(tvo, "sigmoid_focal_loss")
     _installed = True
 
 

@@ -165,6 +165,19 @@ def rotation_6d_to_matrix(d6: torch.Tensor) -> torch.Tensor:
     return torch.stack((b1, b2, b3), dim=-2)
 
 
+def so3_relative_angle(R1, R2, cos_angle: bool = False, cos_bound: float = 1e-4, eps: float = 1e-4):
+    """pytorch3d.transforms.so3.so3_relative_angle, cos_angle=True branch (the only one the
+    hot path uses, roi_heads.py:1006): cos = (tr(R1 R2^T) - 1) / 2 with the trace-range check."""
+    R12 = torch.bmm(R1, R2.permute(0, 2, 1))
+    tr = R12[:, 0, 0] + R12[:, 1, 1] + R12[:, 2, 2]
+    if ((tr < -1.0 - eps) + (tr > 3.0 + eps)).any():
+        raise ValueError("A matrix has trace outside valid range [-1-eps,3+eps].")
+    phi_cos = (tr - 1.0) * 0.5
+    if cos_angle:
+        return phi_cos
+    raise NotImplementedError("stand-in covers cos_angle=True only")
+
+
 class _EventSink:
     iter = 1
 

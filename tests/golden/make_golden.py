@@ -217,6 +217,24 @@ def golden_loss():
         print("loss", idx, {k: round(float(v), 5) for k, v in L.items()})
 
 
+def golden_tier2():
+    """Tier-2 terms ('z', 'depth', 'pose_ground2' on top of 'iou', 'dims') through the
+    reference's own z_loss / depth_range_loss / normal_to_rotation. Inputs are re-derived
+    from the seed by the tests (oracle/loss_inputs.py), only outputs are stored."""
+    T2 = ("iou", "z", "depth", "pose_ground2", "dims")
+    for idx, (seed, nb, conf) in enumerate([(0, [3, 1, 5, 2], 1.0), (4, [7, 12, 2], 0.0)]):
+        H, W = 96, 128
+        inp = li.add_masks(li.make_loss_inputs(seed, nb, H=H, W=W), seed, H=H, W=W)
+        cfg = ol.LossConfig(loss_functions=T2, use_confidence=conf)
+        L, pb, grads = li.run_with_grads(ref_loss.reference_weak_loss, cfg, inp)
+        out = {"seed": seed, "nb": np.asarray(nb), "H": H, "W": W, "use_confidence": conf}
+        out.update({"loss:" + k: v.numpy() for k, v in L.items()})
+        out.update({"grad:" + k: v.numpy() for k, v in grads.items()})
+        out.update({"box:" + k: pb[k].numpy() for k in ("raw_z", "raw_depth", "raw_normal_vec")})
+        np.savez_compressed(os.path.join(HERE, f"tier2_{idx}.npz"), **out)
+        print("tier2", idx, {k: round(float(v), 5) for k, v in L.items()})
+
+
 if __name__ == "__main__":
     assert refshim.available(), "needs /root/reference"
     golden_ground()
@@ -225,3 +243,4 @@ if __name__ == "__main__":
     golden_zbox()
     golden_replay()
     golden_loss()
+    golden_tier2()

@@ -36,8 +36,24 @@ def test_struct_sizes_match_header():
     assert IMAGE_DTYPE.itemsize == 48 and BOX_DTYPE.itemsize == 32
     assert ctypes.sizeof(_abi.SampleParams) == 48
     assert ctypes.sizeof(_abi.ScoreParams) == 32
-    assert ctypes.sizeof(_abi.LossParams) == 40
-    assert ctypes.sizeof(_abi.LossIO) == 8 + 8 * len(_abi._LOSS_IO_PTRS)
+    lib = _abi.load()
+    # sizeof() as compiled into the library vs the ctypes / numpy mirrors
+    assert lib.wcr_sizeof(0) == IMAGE_DTYPE.itemsize and lib.wcr_sizeof(1) == BOX_DTYPE.itemsize
+    assert lib.wcr_sizeof(2) == ctypes.sizeof(_abi.SampleParams)
+    assert lib.wcr_sizeof(3) == ctypes.sizeof(_abi.ScoreParams)
+    assert lib.wcr_sizeof(4) == ctypes.sizeof(_abi.LossParams) == 44
+    assert lib.wcr_sizeof(5) == ctypes.sizeof(_abi.LossIO)
+    assert lib.wcr_sizeof(99) == 0
+
+
+def test_z_loss_steps_equal_torch_linspace():
+    """The table the fused 'z' term uses == values_tensor of z_loss (roi_heads.py:547)."""
+    import numpy as np
+    import torch
+    from wcr import _abi
+    out = np.zeros(50, dtype=np.float32)
+    _abi.load().wcr_z_loss_steps(out.ctypes.data)
+    assert np.array_equal(out, torch.linspace(0.0, (50 - 1) / 10, 50).numpy())
 
 
 def test_no_cpu_fallback():

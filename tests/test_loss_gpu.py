@@ -129,3 +129,59 @@ def test_weak_loss_matches_reference_golden(cuda_lib, path):
     cfg_kw, inp, L_ref, g_ref = load_loss_case(path)
     La, _, ga = _run_gpu(cfg_kw, inp)
     _check(La, ga, L_ref, g_ref)
+
+
+# ---- tier-2 terms: 'z' (area search), 'depth' (masked quantile range), 'pose_ground2' ----------
+DEFAULT_CFG = ("dims", "pose_alignment", "pose_ground", "iou", "z", "z_pseudo_gt_patch", "depth")  # config.py:186
+T2CFGS = [dict(loss_functions=("iou", "z", "depth", "pose_ground2", "dims")),
+          dict(loss_functions=("z", "depth"), use_confidence=0.0, z_type="sigmoid"),
+          dict(loss_functions=DEFAULT_CFG),
+          dict(loss_functions=("pose_ground", "pose_ground2"), dims_priors_func="sigmoid")]
+
+
+@pytest.mark.parametrize("seed,nb,hw", [(0, [3, 1, 5, 2], (96, 128)), (3, [6, 9], (96, 128)),
+                                        (7, [4, 2], (480, 640)), (11, [33, 1, 20], (120, 160))])
+@pytest.mark.parametrize("ci", range(len(T2CFGS)))
+def test_weak_loss_tier2_matches_oracle(cuda_lib, seed, nb, hw, ci):
+    H, W = hw
+    inp = li.add_masks(li.make_loss_inputs(seed, nb, H=H, W=W), seed, H=H, W=W)
+    cfg = ol.LossConfig(**T2CFGS[ci])
+    Lb, pb, gb = li.run_with_grads(ol.weak_loss, cfg, inp)
+    La, pa, ga = _run_gpu(T2CFGS[ci], inp)
+    if "depth" in cfg.loss_functions:
+        got = pa["terms"][9 - 1].cpu()      # WCR_T_DEPTH row
+        assert torch.allclose(got, pb["raw_depth"], rtol=1e-5, atol=1e-6)
+    if "z" in cfg.loss_functions:
+        assert torch.equal(pa["terms"][8 - 1].cpu(), pb["raw_z"])      # WCR_T_Z row: exact
+    _check(La, ga, Lb, gb)
+
+
+@pytest.mark.parametrize("path", sorted(glob.glob(os.path.join(GOLDEN, "tier2_*.npz"))))
+def test_weak_loss_tier2_matches_reference_golden(cuda_lib, path):
+    z = np.load(path, allow_pickle=False)
+    nb = [int(v) for v in z["nb"]]
+    H, W, seed = int(z["H"]), int(z["W"]), int(z["seed"])
+    inp = li.add_masks(li.make_loss_inputs(seed, nb, H=H, W=W), seed, H=H, W=W)
+    cfg_kw = dict(loss_functions=("iou", "z", "depth", "pose_ground2", "dims"),
+                  use_confidence=float(z["use_confidence"]))
+    La, pa, ga = _run_gpu(cfg_kw, inp)
+    Lb = {k[5:]: torch.tensor(z[k]) for k in z.files if k.startswith("loss:")}
+    gb = {k[5:]: torch.tensor(z[k]) for k in z.files if k.startswith("grad:")}
+    assert np.array_equal(pa["terms"][8 - 1].cpu().numpy(), z["box:raw_z"])
+    assert np.allclose(pa["terms"][9 - 1].cpu().numpy(), z["box:raw_depth"], rtol=1e-5, atol=1e-6)
+    assert np.allclose(pa["terms"][3 - 1].cpu().numpy(), z["box:raw_normal_vec"], rtol=1e-5, atol=1e-6)
+    _check(La, ga, Lb, gb)
+
+
+def test_depth_term_empty_mask_and_shape_mismatch(cuda_lib):
+    from wcr import _abi
+    H, W = 96, 128
+    inp = li.add_masks(li.make_loss_inputs(2, [5, 4], H=H, W=W), 2, H=H, W=W, empty_every=2)
+    cfg_kw = dict(loss_functions=("depth",))
+    Lb, pb, gb = li.run_with_grads(ol.weak_loss, ol.LossConfig(**cfg_kw), inp)
+    La, pa, ga = _run_gpu(cfg_kw, inp)
+    _check(La, ga, Lb, gb)
+    bad = dict(inp)
+    bad["gt_masks"] = [m[:, :-2] for m in inp["gt_masks"]]
+    with pytest.raises(_abi.WcrError):
+        _run_gpu(cfg_kw, bad)

@@ -101,3 +101,16 @@ extern "C" int64_t wcr_probe_ffma(float *out, int64_t out_elems, int iters, void
     if (e != cudaSuccess) { wcr::set_error("ffma_probe_kernel: %s", cudaGetErrorString(e)); return WCR_ELAUNCH; }
     return (int64_t)grid * 256 * (int64_t)iters * 16 * 2;  // FLOPs enqueued
 }
+
+extern "C" int64_t wcr_sizeof(int which)
+{
+    switch (which) {
+    case 0: return (int64_t)sizeof(WcrImage);
+    case 1: return (int64_t)sizeof(WcrBox);
+    case 2: return (int64_t)sizeof(WcrSampleParams);
+    case 3: return (int64_t)sizeof(WcrScoreParams);
+    case 4: return (int64_t)sizeof(WcrLossParams);
+    case 5: return (int64_t)sizeof(WcrLossIO);
+    default: return 0;
+    }
+}

@@ -11,6 +11,7 @@
 //             autograd's sub-gradient choices (first arg-extremum over corners,
 //             closed-interval clamp, tie-splitting binary min/max, sign(0) = 0).
 // Latency-bound by nature (n <= a few thousand boxes): no roofline claim.
+#include <math.h>
 #include <string.h>
 #include "cube_math.cuh"
 
@@ -171,8 +172,43 @@ __device__ __forceinline__ float cos_sim3(const float *a, const float *b, float 
 constexpr int LT = WCR_LOSS_TERMS - 1;  // per-box term rows (uncert is not one)
 
 // ---------------------------------------------------------------- forward --
+struct ZSteps { float v[WCR_Z_LOSS_STEPS]; };
+
+// depth extent of the 8 cube corners (get_all_corners()[..., 2], roi_heads.py:665-667) with
+// the FIRST arg-max / arg-min corner (torch.max / torch.min over a dim)
+__device__ __forceinline__ float corner_depth_range(const Decoded &d, int &cmax, int &cmin)
+{
+    const float hx = d.dims[2] / 2.f, hy = d.dims[1] / 2.f, hz = d.dims[0] / 2.f;
+    float zmax = 0.f, zmin = 0.f;
+    cmax = 0; cmin = 0;
+#pragma unroll
+    for (int c = 0; c < 8; ++c) {
+        float sx, sy, sz;
+        corner_signs(c, sx, sy, sz);
+        const float Z = fmaf(d.R[8], sz * hz, fmaf(d.R[7], sy * hy, d.R[6] * (sx * hx))) + d.cube[2];
+        if (c == 0) { zmax = Z; zmin = Z; }
+        else {
+            if (Z > zmax || (Z != Z && zmax == zmax)) { zmax = Z; cmax = c; }
+            if (Z < zmin || (Z != Z && zmin == zmin)) { zmin = Z; cmin = c; }
+        }
+    }
+    return zmax - zmin;
+}
+
+// 1 - cos of the relative angle between the predicted pose and the pseudo-GT rotation built
+// from the ground normal (roi_heads.py:1003-1007); also reports pytorch3d's trace check
+__device__ __forceinline__ float ground2_term(const float *R, const float *G, float conf, bool *bad)
+{
+    const float d0 = fmaf(R[2], G[2], fmaf(R[1], G[1], R[0] * G[0]));
+    const float d1 = fmaf(R[5], G[5], fmaf(R[4], G[4], R[3] * G[3]));
+    const float d2 = fmaf(R[8], G[8], fmaf(R[7], G[7], R[6] * G[6]));
+    const float tr = (d0 + d1) + d2;
+    if (bad) *bad = (tr < -1.0f - 1e-4f) || (tr > 3.0f + 1e-4f);
+    return (1.f - (tr - 1.0f) * 0.5f) * conf;
+}
+
 __global__ void __launch_bounds__(128)
-loss_box_fwd_kernel(const WcrLossIO io, const WcrLossParams P)
+loss_box_fwd_kernel(const WcrLossIO io, const WcrLossParams P, const ZSteps zs)
 {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= io.n) return;
@@ -198,8 +234,46 @@ loss_box_fwd_kernel(const WcrLossIO io, const WcrLossParams P)
         const float c = cos_sim3(io.normals + 3 * img, d.R + 3, an, bn, &nb);   // row 1 of R (:992)
         term[WCR_T_NORMAL - 1] = (1.f - fabsf(c)) * io.ground_conf[img];
     }
+    if (P.loss_flags & WCR_LOSS_POSE_GROUND2) {      // overrides 'pose_ground' (:997-1007)
+        bool bad;
+        term[WCR_T_NORMAL - 1] = ground2_term(d.R, io.gt_rot + 9 * img, io.ground_conf[img], &bad);
+        if (bad) io.stats[WCR_STAT_TRACE_ERR] = 1.f;
+    }
     if ((P.loss_flags & WCR_LOSS_Z_CENTER) && !(P.loss_flags & WCR_LOSS_Z_PATCH))
         term[WCR_T_PSEUDO_Z - 1] = fabsf(d.z - depth_at(io.images[img], d.cube_x, d.cube_y));
+    if (P.loss_flags & WCR_LOSS_Z_SEARCH) {           // z_loss, roi_heads.py:530-573
+        const float *g = io.gt_boxes + 4 * i;
+        const float gt_area = (g[2] - g[0]) * (g[3] - g[1]);
+        const float pcx = (proj[0] + proj[2]) / 2.f, pcy = (proj[1] + proj[3]) / 2.f;
+        const float pred_area = (proj[2] - proj[0]) * (proj[3] - proj[1]);
+        // :545-546 compares the BOOL (lower <= centre) with the upper bound
+        const float bx = (g[0] - 50.f <= pcx) ? 1.f : 0.f, by = (g[1] - 50.f <= pcy) ? 1.f : 0.f;
+        const bool within = (bx <= g[2] + 50.f) && (by <= g[3] + 50.f);
+        float score = 5.0f;                           // 0.1 * max_count
+        if (within) {
+            const bool smaller = gt_area < pred_area;
+            float cube[15];
+#pragma unroll
+            for (int t = 0; t < 15; ++t) cube[t] = d.cube[t];
+            float best = 0.f, best_z = d.z;
+            for (int k = 0; k < WCR_Z_LOSS_STEPS; ++k) {
+                const float zk = smaller ? d.z + zs.v[k] : d.z - zs.v[k];
+                cube[2] = zk;
+                const ProjBox mb = project_cube(cube, d.K, lo0, hi0, lo1, hi1, nullptr);
+                float area = (mb.x2 - mb.x1) * (mb.y2 - mb.y1);
+                area = area + (area == 0.f ? 10000000.f : 0.f);
+                const float diff = fabsf(gt_area - area);
+                // torch.argmin: first minimum, a NaN counts as the minimum
+                if (k == 0 || (best == best && (diff != diff || diff < best))) { best = diff; best_z = zk; }
+            }
+            score = fabsf(d.z - best_z);
+        }
+        term[WCR_T_Z - 1] = score / 2.f;
+    }
+    if (P.loss_flags & WCR_LOSS_DEPTH) {              // depth_range_loss, :658-684
+        int cmax, cmin;
+        term[WCR_T_DEPTH - 1] = fabsf(io.depth_gt[i] - corner_depth_range(d, cmax, cmin));
+    }
     if (P.loss_flags & WCR_LOSS_DIMS) {
 #pragma unroll
         for (int k = 0; k < 3; ++k) {
@@ -273,6 +347,8 @@ __device__ __forceinline__ float term_weight(const WcrLossParams &P, int t)
     case WCR_T_POSE: return P.w_pose * P.w_3d;
     case WCR_T_NORMAL: return P.w_normal * P.w_3d;
     case WCR_T_PSEUDO_Z: return P.w_z * P.w_3d;
+    case WCR_T_Z: return P.w_z * P.w_3d;              // roi_heads.py:1125
+    case WCR_T_DEPTH: return P.w_depth * P.w_3d;      // :1143
     default: return P.w_dims * P.w_3d;
     }
 }
@@ -283,8 +359,10 @@ __device__ __forceinline__ bool term_enabled(const WcrLossParams &P, int t)
     case WCR_T_UNCERT: return P.use_confidence > 0.f;
     case WCR_T_IOU: return P.loss_flags & WCR_LOSS_IOU;
     case WCR_T_POSE: return P.loss_flags & WCR_LOSS_POSE_ALIGN;
-    case WCR_T_NORMAL: return P.loss_flags & WCR_LOSS_POSE_GROUND;
+    case WCR_T_NORMAL: return P.loss_flags & (WCR_LOSS_POSE_GROUND | WCR_LOSS_POSE_GROUND2);
     case WCR_T_PSEUDO_Z: return P.loss_flags & (WCR_LOSS_Z_CENTER | WCR_LOSS_Z_PATCH);
+    case WCR_T_Z: return P.loss_flags & WCR_LOSS_Z_SEARCH;
+    case WCR_T_DEPTH: return P.loss_flags & WCR_LOSS_DEPTH;
     default: return P.loss_flags & WCR_LOSS_DIMS;
     }
 }
@@ -327,7 +405,7 @@ loss_reduce_kernel(const WcrLossIO io, const WcrLossParams P)
         float sum = 0.f, cnt = 0.f;
         bool present = term_enabled(P, t);
         if (t == WCR_T_POSE) present = pose_present;
-        if (t >= WCR_T_DIMS_W) present = present && nan_std == 0.f;
+        if (t >= WCR_T_DIMS_W && t <= WCR_T_DIMS_L) present = present && nan_std == 0.f;
         if (present) {
             for (int i = tid; i < io.n; i += blockDim.x) {
                 const float v = t == WCR_T_UNCERT ? io.uncert[i]
@@ -343,7 +421,221 @@ loss_reduce_kernel(const WcrLossIO io, const WcrLossParams P)
         }
         __syncthreads();
     }
-    if (tid == 0) { io.stats[8] = pose; io.stats[9] = fail; }
+    if (tid == 0) {
+        io.stats[WCR_STAT_POSE] = pose; io.stats[WCR_STAT_FAIL] = fail;
+        io.present[WCR_LOSS_TERMS] = io.stats[WCR_STAT_TRACE_ERR] != 0.f;
+        io.present[WCR_LOSS_TERMS + 1] = io.stats[WCR_STAT_SHAPE_ERR] != 0.f;
+    }
+}
+
+
+// ---- 'pose_ground2': normal_to_rotation (roi_heads.py:686-696) -------------------------------
+// The reference repeats the per-image normal once per box and normalises t0 and t1 by the
+// FROBENIUS norm of the whole (n, 3) matrix (torch.norm without dim), so the rows are not unit
+// length when n > 1 -- reproduced. `.any() < 0.001` is evaluated on a bool: the y-axis
+// branch is taken only when every t0 is exactly zero. One CTA; images are few.
+__global__ void __launch_bounds__(256)
+ground_rot_kernel(const float *__restrict__ normals, const int32_t *__restrict__ img_off, int n_images,
+                  float *__restrict__ gt_rot)
+{
+    __shared__ float s_a[8], s_b[8];
+    const int tid = threadIdx.x;
+    float ss = 0.f, any = 0.f;
+    for (int im = tid; im < n_images; im += blockDim.x) {
+        const float ni = (float)(img_off[im + 1] - img_off[im]);
+        const float ny = normals[3 * im + 1], nz = normals[3 * im + 2];
+        const float dot = (0.f * 0.f + nz * nz) + ny * ny;     // t0 = n x (1,0,0) = (0, nz, -ny)
+        ss += ni * dot;
+        if (ni > 0.f && dot != 0.f) any = 1.f;
+    }
+    block_sum2(ss, any, s_a, s_b);
+    const bool ybranch = !(any > 0.f);
+    if (ybranch) {
+        ss = 0.f;
+        float dummy = 0.f;
+        for (int im = tid; im < n_images; im += blockDim.x) {
+            const float ni = (float)(img_off[im + 1] - img_off[im]);
+            const float nx = normals[3 * im], nz = normals[3 * im + 2];
+            ss += ni * ((nz * nz + 0.f) + nx * nx);            // t0 = n x (0,1,0) = (-nz, 0, nx)
+        }
+        block_sum2(ss, dummy, s_a, s_b);
+    }
+    const float norm0 = sqrtf(ss);
+    float s1 = 0.f, dummy = 0.f;
+    for (int im = tid; im < n_images; im += blockDim.x) {
+        const float ni = (float)(img_off[im + 1] - img_off[im]);
+        const float nx = normals[3 * im], ny = normals[3 * im + 1], nz = normals[3 * im + 2];
+        float t0[3];
+        if (ybranch) { t0[0] = (0.f - nz) / norm0; t0[1] = 0.f / norm0; t0[2] = nx / norm0; }
+        else         { t0[0] = 0.f / norm0; t0[1] = nz / norm0; t0[2] = (0.f - ny) / norm0; }
+        // torch.cross(n, t0)
+        const float c0 = fmaf(ny, t0[2], -(nz * t0[1]));
+        const float c1 = fmaf(nz, t0[0], -(nx * t0[2]));
+        const float c2 = fmaf(nx, t0[1], -(ny * t0[0]));
+        float *G = gt_rot + 9 * im;
+        G[0] = t0[0]; G[1] = t0[1]; G[2] = t0[2];
+        G[3] = c0; G[4] = c1; G[5] = c2;                       // normalised below
+        G[6] = nx; G[7] = ny; G[8] = nz;
+        s1 += ni * ((c0 * c0 + c1 * c1) + c2 * c2);
+    }
+    block_sum2(s1, dummy, s_a, s_b);
+    const float norm1 = sqrtf(s1);
+    for (int im = tid; im < n_images; im += blockDim.x)
+#pragma unroll
+        for (int k = 3; k < 6; ++k) gt_rot[9 * im + k] /= norm1;
+}
+
+// ---- 'depth': q90 - q10 of the depth under the object's mask (roi_heads.py:669-679) ----------
+__device__ __forceinline__ uint32_t float_key(float f);
+__device__ __forceinline__ float key_float(uint32_t k);
+
+// a[i0:i1] as Python slices it: negative indices wrap once, then clamp to [0, n]
+__device__ __forceinline__ int py_slice_index(long long i, int n)
+{
+    if (i < 0) i += n;
+    return (int)(i < 0 ? 0 : (i > n ? n : i));
+}
+
+// torch lerp (the interpolation of torch.quantile's default 'linear' mode)
+__device__ __forceinline__ float torch_lerp(float a, float b, float w)
+{
+    const float diff = b - a;
+    return fabsf(w) < 0.5f ? a + w * diff : b - diff * (1.f - w);
+}
+
+// One CTA per box: the four order statistics torch.quantile(x, 0.9) and torch.quantile(x, 0.1)
+// interpolate between, found by ONE 4-pass 8-bit radix select that follows up to four key
+// prefixes at once (a histogram per distinct prefix), over either the masked pixels of the
+// box's image or -- when the mask is empty -- the GT box patch. No sort, no compaction buffer:
+// the reference sorts every masked depth vector twice per box.
+__global__ void __launch_bounds__(256)
+mask_quantile_kernel(const WcrImage *__restrict__ images, const int32_t *__restrict__ img_off, int n_images,
+                     const uint8_t *__restrict__ masks, int mh, int mw, const int32_t *__restrict__ mask_idx,
+                     const float *__restrict__ gt_boxes, float *__restrict__ out_range, float *__restrict__ stats)
+{
+    __shared__ unsigned hist[4][256];
+    __shared__ unsigned s_prefix[4], s_rank[4], s_gprefix[4];
+    __shared__ int s_group[4], s_ngroups, s_cnt, s_rmin, s_rmax, s_nan;
+    const int b = blockIdx.x, tid = threadIdx.x;
+    const WcrImage im = images[image_of(img_off, n_images, b)];
+    if (im.H != mh || im.W != mw) {
+        if (tid == 0) { out_range[b] = nanf_(); stats[WCR_STAT_SHAPE_ERR] = 1.f; }
+        return;
+    }
+    const uint8_t *m = masks + (size_t)mask_idx[b] * mh * mw;
+    if (tid == 0) { s_cnt = 0; s_rmin = mh; s_rmax = -1; s_nan = 0; }
+    __syncthreads();
+    // -- pass A: how many pixels, which rows ----------------------------------------------
+    {
+        int cnt = 0, rmin = mh, rmax = -1;
+        const int total = mh * mw;
+        const int head = min(total, (int)((16 - ((uintptr_t)m & 15)) & 15));
+        const int nvec = (total - head) / 16;
+        auto visit = [&](int idx) { ++cnt; const int r = idx / mw; rmin = min(rmin, r); rmax = max(rmax, r); };
+        for (int i = tid; i < head; i += blockDim.x) if (m[i]) visit(i);
+        for (int i = head + 16 * nvec + tid; i < total; i += blockDim.x) if (m[i]) visit(i);
+        const uint4 *mv = reinterpret_cast<const uint4 *>(m + head);
+        for (int v = tid; v < nvec; v += blockDim.x) {
+            const uint4 w = __ldg(mv + v);
+            if ((w.x | w.y | w.z | w.w) == 0u) continue;
+            const unsigned ww[4] = {w.x, w.y, w.z, w.w};
+#pragma unroll
+            for (int q = 0; q < 4; ++q)
+#pragma unroll
+                for (int e = 0; e < 4; ++e)
+                    if ((ww[q] >> (8 * e)) & 255u) visit(head + 16 * v + 4 * q + e);
+        }
+        if (cnt) { atomicAdd(&s_cnt, cnt); atomicMin(&s_rmin, rmin); atomicMax(&s_rmax, rmax); }
+    }
+    __syncthreads();
+    int cnt = s_cnt;
+    const bool use_mask = cnt > 0;
+    // source region: rows [r0, r1) x cols [c0, c1) of the depth map, masked or not
+    int r0 = s_rmin, r1 = s_rmax + 1, c0 = 0, c1 = mw;
+    if (!use_mask) {   // segmentation failed: depth_map[y1.long():y2.long(), x1.long():x2.long()] (:674-675)
+        const float *g = gt_boxes + 4 * b;
+        c0 = py_slice_index((long long)g[0], mw); c1 = py_slice_index((long long)g[2], mw);
+        r0 = py_slice_index((long long)g[1], mh); r1 = py_slice_index((long long)g[3], mh);
+        cnt = max(r1 - r0, 0) * max(c1 - c0, 0);
+    }
+    if (cnt <= 0) {    // torch.quantile of an empty tensor raises in the reference; NaN here
+        if (tid == 0) out_range[b] = nanf_();
+        return;
+    }
+    float w9, w1;
+    {
+        const float r9 = 0.9f * (float)(cnt - 1), r1f = 0.1f * (float)(cnt - 1);
+        const float b9 = floorf(r9), b1 = floorf(r1f);
+        w9 = r9 - b9; w1 = r1f - b1;
+        if (tid == 0) {
+            s_rank[0] = (unsigned)b9; s_rank[1] = (unsigned)ceilf(r9);
+            s_rank[2] = (unsigned)b1; s_rank[3] = (unsigned)ceilf(r1f);
+#pragma unroll
+            for (int t = 0; t < 4; ++t) { s_prefix[t] = 0u; s_group[t] = 0; }
+            s_gprefix[0] = 0u; s_ngroups = 1;
+        }
+    }
+    const int ncols = c1 - c0, region = (r1 - r0) * ncols;
+    for (int pass = 0; pass < 4; ++pass) {
+        const int shift = 24 - 8 * pass;
+        for (int i = tid; i < 4 * 256; i += blockDim.x) (&hist[0][0])[i] = 0u;
+        __syncthreads();
+        const int ng = s_ngroups;
+        const unsigned gp0 = s_gprefix[0], gp1 = s_gprefix[1], gp2 = s_gprefix[2], gp3 = s_gprefix[3];
+        const unsigned himask = pass == 0 ? 0u : (0xffffffffu << (shift + 8));
+        // per-thread run-length encoding per group: depths under one mask share their leading
+        // bytes, plain shared atomics would serialise on one or two bins
+        unsigned last[4] = {~0u, ~0u, ~0u, ~0u}, run[4] = {0u, 0u, 0u, 0u};
+        auto feed = [&](float f) {
+            if (pass == 0 && f != f) s_nan = 1;
+            const uint32_t k = float_key(f);
+            const unsigned hi = k & himask, bin = (k >> shift) & 255u;
+            const unsigned gp[4] = {gp0, gp1, gp2, gp3};
+#pragma unroll
+            for (int g = 0; g < 4; ++g) {
+                if (g >= ng || hi != gp[g]) continue;
+                if (bin == last[g]) { ++run[g]; continue; }
+                if (run[g]) atomicAdd(&hist[g][last[g]], run[g]);
+                last[g] = bin; run[g] = 1u;
+            }
+        };
+        for (int i = tid; i < region; i += blockDim.x) {
+            const int r = i / ncols, c = i - r * ncols;
+            const int rr = r0 + r, cc = c0 + c;
+            if (use_mask && !m[(size_t)rr * mw + cc]) continue;
+            feed(__ldg(im.depth + (size_t)rr * im.depth_pitch + cc));
+        }
+#pragma unroll
+        for (int g = 0; g < 4; ++g) if (run[g]) atomicAdd(&hist[g][last[g]], run[g]);
+        __syncthreads();
+        if (tid == 0) {
+            for (int t = 0; t < 4; ++t) {
+                const unsigned *h = hist[s_group[t]];
+                unsigned rank = s_rank[t], acc = 0u;
+                int bin = 0;
+                for (; bin < 255; ++bin) {
+                    if (acc + h[bin] > rank) break;
+                    acc += h[bin];
+                }
+                s_rank[t] = rank - acc;
+                s_prefix[t] |= (unsigned)bin << shift;
+            }
+            int g_n = 0;
+            for (int t = 0; t < 4; ++t) {
+                int g = 0;
+                for (; g < g_n; ++g) if (s_gprefix[g] == s_prefix[t]) break;
+                if (g == g_n) s_gprefix[g_n++] = s_prefix[t];
+                s_group[t] = g;
+            }
+            s_ngroups = g_n;
+        }
+        __syncthreads();
+    }
+    if (tid == 0) {
+        const float q9 = torch_lerp(key_float(s_prefix[0]), key_float(s_prefix[1]), w9);
+        const float q1 = torch_lerp(key_float(s_prefix[2]), key_float(s_prefix[3]), w1);
+        out_range[b] = s_nan ? nanf_() : q9 - q1;
+    }
 }
 
 // --------------------------------------------------------------- backward --
@@ -365,7 +657,7 @@ loss_pose_bwd_kernel(const WcrLossIO io, const WcrLossParams P)
     const int im = blockIdx.x;
     const int b0 = io.img_off[im], ni = io.img_off[im + 1] - b0;
     // dP = sum_i coef_i * sf_i  (raw pose term of every box is the same scalar P)
-    const float pose = io.stats[8];
+    const float pose = io.stats[WCR_STAT_POSE];
     float dP = 0.f, dummy = 0.f;
     for (int i = threadIdx.x; i < io.n; i += blockDim.x) {
         const float sf = uncert_sf(io, P, i);
@@ -373,7 +665,7 @@ loss_pose_bwd_kernel(const WcrLossIO io, const WcrLossParams P)
     }
     block_sum2(dP, dummy, s_a, s_b);
     const float npairs = 0.5f * (float)ni * (float)(ni - 1);
-    const float scale = ni > 1 ? dP / (npairs * (io.stats[9] + 1.f)) : 0.f;
+    const float scale = ni > 1 ? dP / (npairs * (io.stats[WCR_STAT_FAIL] + 1.f)) : 0.f;
     for (int i = threadIdx.x; i < ni; i += blockDim.x) {
         float Ri[9], g[9];
 #pragma unroll
@@ -490,12 +782,13 @@ loss_box_bwd_kernel(const WcrLossIO io, const WcrLossParams P)
     }
     // ---- 'pose_alignment' ---------------------------------------------------------
     if ((P.loss_flags & WCR_LOSS_POSE_ALIGN) && io.present[WCR_T_POSE]) {
-        coef(WCR_T_POSE, io.stats[8]);   // only the uncertainty part; R part comes from the pair kernel
+        coef(WCR_T_POSE, io.stats[WCR_STAT_POSE]);   // only the uncertainty part; R part comes from the pair kernel
 #pragma unroll
         for (int t = 0; t < 9; ++t) dR[t] += io.d_R_pose[9 * (size_t)i + t];
     }
     // ---- 'pose_ground' --------------------------------------------------------------
-    if ((P.loss_flags & WCR_LOSS_POSE_GROUND) && io.present[WCR_T_NORMAL]) {
+    if ((P.loss_flags & WCR_LOSS_POSE_GROUND) && !(P.loss_flags & WCR_LOSS_POSE_GROUND2) &&
+        io.present[WCR_T_NORMAL]) {
         float an[3], bn[3], nb;
         const float c = cos_sim3(io.normals + 3 * img, d.R + 3, an, bn, &nb);
         const float conf = io.ground_conf[img];
@@ -518,6 +811,37 @@ loss_box_bwd_kernel(const WcrLossIO io, const WcrLossParams P)
         const float diff = d.z - depth_at(io.images[img], d.cube_x, d.cube_y);
         const float g = coef(WCR_T_PSEUDO_Z, fabsf(diff));
         dz += g * sgn(diff);
+    }
+    // ---- 'pose_ground2' (replaces the cosine term in the same slot) -----------------------
+    if ((P.loss_flags & WCR_LOSS_POSE_GROUND2) && io.present[WCR_T_NORMAL]) {
+        const float *G = io.gt_rot + 9 * img;
+        const float conf = io.ground_conf[img];
+        const float g = coef(WCR_T_NORMAL, ground2_term(d.R, G, conf, nullptr));
+#pragma unroll
+        for (int t = 0; t < 9; ++t) dR[t] += g * conf * -0.5f * G[t];
+    }
+    // ---- 'z' (arg-min over constant offsets: no gradient to the cube, only to uncert) -------
+    if ((P.loss_flags & WCR_LOSS_Z_SEARCH) && io.present[WCR_T_Z])
+        coef(WCR_T_Z, io.terms[(size_t)(WCR_T_Z - 1) * io.n + i]);
+    // ---- 'depth' ------------------------------------------------------------------------------
+    if ((P.loss_flags & WCR_LOSS_DEPTH) && io.present[WCR_T_DEPTH]) {
+        int cmax, cmin;
+        const float pred = corner_depth_range(d, cmax, cmin);
+        const float diff = io.depth_gt[i] - pred;
+        const float g = coef(WCR_T_DEPTH, fabsf(diff)) * -sgn(diff);   // d|gt - pred| / d pred
+        if (g != 0.f) {
+            const float h[3] = {d.dims[2] / 2.f, d.dims[1] / 2.f, d.dims[0] / 2.f};
+            float sa[3], sb[3];
+            corner_signs(cmax, sa[0], sa[1], sa[2]);
+            corner_signs(cmin, sb[0], sb[1], sb[2]);
+            // Z_c = R[2,:] . (s_c * h) + z : the centre's z cancels in max - min
+#pragma unroll
+            for (int k = 0; k < 3; ++k) {
+                dR[6 + k] += g * (sa[k] - sb[k]) * h[k];
+                const float dh = g * d.R[6 + k] * (sa[k] - sb[k]);
+                ddims[2 - k] += 0.5f * dh;                             // hx = l/2, hy = h/2, hz = w/2
+            }
+        }
     }
     // ---- 'dims' -------------------------------------------------------------------------
     if ((P.loss_flags & WCR_LOSS_DIMS) && io.present[WCR_T_DIMS_W]) {
@@ -586,7 +910,26 @@ static int check_io(const WcrLossIO *io, const WcrLossParams *p, bool bwd)
     if (p->loss_flags & WCR_LOSS_Z_PATCH)
         WCR_REQUIRE(io->z_dec && io->z_gt && io->z_inside && io->z_sign,
                     "wcr_weak_loss: 'z_pseudo_gt_patch' needs the z_dec / z_gt / z_inside / z_sign buffers");
+    if (p->loss_flags & WCR_LOSS_DEPTH)
+        WCR_REQUIRE(io->masks && io->mask_idx && io->depth_gt && io->mask_h > 0 && io->mask_w > 0,
+                    "wcr_weak_loss: 'depth' needs masks, mask_idx, depth_gt and the mask shape");
+    if (p->loss_flags & WCR_LOSS_POSE_GROUND2)
+        WCR_REQUIRE(io->gt_rot, "wcr_weak_loss: 'pose_ground2' needs the gt_rot workspace");
     return WCR_OK;
+}
+
+// torch.linspace(0.0, 4.9, 50) in fp32 (roi_heads.py:547): step = (end - start) / (steps - 1);
+// the lower half counts up from start, the upper half counts down from end (ATen's
+// symmetric formulation), each as ONE fused multiply-add -- both ATen's vectorised CPU
+// kernel and its CUDA kernel contract it. tests/test_abi_cpu.py compares this table with
+// torch.linspace bit for bit.
+extern "C" void wcr_z_loss_steps(float out[WCR_Z_LOSS_STEPS])
+{
+    const int steps = WCR_Z_LOSS_STEPS;
+    const float start = 0.0f, end = (float)((steps - 1) / 10.0);
+    const float step = (end - start) / (float)(steps - 1);
+    for (int i = 0; i < steps; ++i)
+        out[i] = i < steps / 2 ? fmaf(step, (float)i, start) : fmaf(-step, (float)(steps - i - 1), end);
 }
 
 extern "C" int wcr_weak_loss_fwd(const WcrLossIO *h_io, const WcrLossParams *h_params, void *stream)
@@ -595,8 +938,23 @@ extern "C" int wcr_weak_loss_fwd(const WcrLossIO *h_io, const WcrLossParams *h_p
     int rc = check_io(h_io, h_params, false);
     if (rc != WCR_OK) return rc;
     cudaStream_t st = (cudaStream_t)stream;
+    cudaError_t e = cudaMemsetAsync(h_io->stats, 0, WCR_LOSS_STATS * sizeof(float), st);
+    if (e != cudaSuccess) { wcr::set_error("cudaMemsetAsync: %s", cudaGetErrorString(e)); return WCR_ELAUNCH; }
+    if (h_params->loss_flags & WCR_LOSS_POSE_GROUND2) {
+        wcr::ground_rot_kernel<<<1, 256, 0, st>>>(h_io->normals, h_io->img_off, h_io->n_images, h_io->gt_rot);
+        WCR_CHECK_LAUNCH("ground_rot_kernel");
+    }
+    if (h_io->n > 0 && (h_params->loss_flags & WCR_LOSS_DEPTH)) {
+        wcr::mask_quantile_kernel<<<h_io->n, 256, 0, st>>>(h_io->images, h_io->img_off, h_io->n_images,
+                                                           h_io->masks, h_io->mask_h, h_io->mask_w,
+                                                           h_io->mask_idx, h_io->gt_boxes, h_io->depth_gt,
+                                                           h_io->stats);
+        WCR_CHECK_LAUNCH("mask_quantile_kernel");
+    }
     if (h_io->n > 0) {
-        wcr::loss_box_fwd_kernel<<<(h_io->n + 127) / 128, 128, 0, st>>>(*h_io, *h_params);
+        wcr::ZSteps zs;
+        wcr_z_loss_steps(zs.v);
+        wcr::loss_box_fwd_kernel<<<(h_io->n + 127) / 128, 128, 0, st>>>(*h_io, *h_params, zs);
         WCR_CHECK_LAUNCH("loss_box_fwd_kernel");
     }
     if (h_io->n > 0 && (h_params->loss_flags & WCR_LOSS_Z_PATCH)) {

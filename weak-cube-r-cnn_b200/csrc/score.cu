@@ -33,7 +33,8 @@ constexpr int SC_THREADS = 256;
 constexpr int SC_T = 4;                        // proposals per thread
 constexpr int SC_CHUNK = SC_THREADS * SC_T;    // proposals per item
 constexpr int SC_TILE = 2048;                  // (a,a,z,z) pixels per smem tile = 32 KB
-constexpr int SC_ITEM_PX = 4096;               // target depth pixels per item
+constexpr int SC_ITEM_PX = 4096;               // target depth pixels per item (large shards)
+constexpr int SC_ITEM_PX_MIN = 512;            // ... shrunk for small shards so every SM gets items
 constexpr int SC_MAX_CHUNKS = 64;
 
 typedef unsigned long long u64;
@@ -92,7 +93,8 @@ __device__ __forceinline__ float inside_unit(float q0, float q1, float q2)
 // reference slices depth patches (roi_heads.py:590-597), sub-sampled by `s`.
 struct Roi { int u0, v0, ncols, nrows, rows_per_item, n_rowblocks; };
 
-__device__ __forceinline__ Roi box_roi(const WcrBox &bx, int H, int W, int s, bool use_pts)
+__device__ __forceinline__ Roi box_roi(const WcrBox &bx, int H, int W, int s, bool use_pts,
+                                       int item_px = SC_ITEM_PX)
 {
     Roi r;
     r.u0 = (int)fminf(fmaxf(bx.x1, 0.f), (float)W);
@@ -102,7 +104,7 @@ __device__ __forceinline__ Roi box_roi(const WcrBox &bx, int H, int W, int s, bo
     r.ncols = max(0, (u1 - r.u0 + s - 1) / s);
     r.nrows = max(0, (v1 - r.v0 + s - 1) / s);
     if (!use_pts || r.ncols == 0) r.nrows = 0;
-    r.rows_per_item = max(1, SC_ITEM_PX / max(r.ncols, 1));
+    r.rows_per_item = max(1, item_px / max(r.ncols, 1));
     r.n_rowblocks = max(1, (r.nrows + r.rows_per_item - 1) / r.rows_per_item);
     return r;
 }
@@ -129,6 +131,7 @@ struct ScoreArgs {
     WcrScoreParams sc;
     int k;
     int n_chunks;
+    int item_px;         // depth pixels per item (plan and item kernel must agree)
     ScoreWs ws;
     float *records;
     float *out_scores, *out_iou;
@@ -143,7 +146,8 @@ struct ScoreArgs {
 // One CTA: items per box -> exclusive prefix. n_boxes is at most a few 100 k.
 __global__ void __launch_bounds__(1024)
 score_plan_kernel(const WcrImage *__restrict__ images, const WcrBox *__restrict__ boxes,
-                  int n_boxes, int n_chunks, int stride, int use_pts, int *__restrict__ prefix)
+                  int n_boxes, int n_chunks, int stride, int use_pts, int item_px,
+                  int *__restrict__ prefix)
 {
     __shared__ int s_warp[32];
     __shared__ int s_carry;
@@ -156,7 +160,7 @@ score_plan_kernel(const WcrImage *__restrict__ images, const WcrBox *__restrict_
         if (b < n_boxes) {
             const WcrBox bx = boxes[b];
             const WcrImage im = images[bx.image];
-            n = box_roi(bx, im.H, im.W, stride, use_pts != 0).n_rowblocks * n_chunks;
+            n = box_roi(bx, im.H, im.W, stride, use_pts != 0, item_px).n_rowblocks * n_chunks;
         }
         int incl = n;
 #pragma unroll
@@ -292,7 +296,7 @@ __global__ void __launch_bounds__(SC_THREADS, MINB) score_items_kernel(const Sco
         const WcrBox bx = a.boxes[b];
         const WcrImage im = a.images[bx.image];
         const Intr K = {im.fx, im.fy, im.cx, im.cy};
-        const Roi roi = box_roi(bx, im.H, im.W, s, use_pts);
+        const Roi roi = box_roi(bx, im.H, im.W, s, use_pts, a.item_px);
         const int local = item - prefix[b];
         const int chunk = local / roi.n_rowblocks, rb = local - chunk * roi.n_rowblocks;
         const int row_begin = rb * roi.rows_per_item;
@@ -684,8 +688,17 @@ extern "C" int wcr_score_topk(const WcrImage *images, const WcrBox *boxes, int n
     carve(ws, n_boxes, N, k, cubes == nullptr, h_score->e_seg > 0, &a.ws, &zero_bytes);
     cudaError_t e = cudaMemsetAsync(ws, 0, zero_bytes, st);
     if (e != cudaSuccess) { wcr::set_error("cudaMemsetAsync: %s", cudaGetErrorString(e)); return WCR_ELAUNCH; }
+    // A 64-image shard has ~10^4 items of 4096 px; a single image with a handful of boxes
+    // would leave most of the 296 resident CTAs idle, so its items are cut finer.
+    {
+        const long long bc = (long long)n_boxes * nc;
+        long long px = wcr::SC_ITEM_PX * bc / 296;
+        int item_px = wcr::SC_ITEM_PX_MIN;
+        while (item_px < wcr::SC_ITEM_PX && item_px < px) item_px <<= 1;
+        a.item_px = item_px;
+    }
     wcr::score_plan_kernel<<<1, 1024, 0, st>>>(images, boxes, n_boxes, nc, h_score->point_stride,
-                                               h_score->e_pts > 0, a.ws.item_prefix);
+                                               h_score->e_pts > 0, a.item_px, a.ws.item_prefix);
     WCR_CHECK_LAUNCH("score_plan_kernel");
     if (!cubes) {
         WCR_REQUIRE((N + 255) / 256 <= 65535, "wcr_score_topk: N too large");

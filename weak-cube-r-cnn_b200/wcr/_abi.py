@@ -61,6 +61,8 @@ SIGNATURES = {
     "wcr_l1_loss_bwd": (c_int, [c_void_p, c_void_p, c_int, c_void_p, c_void_p]),
     "wcr_dim_loss_fwd": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_void_p, c_void_p, c_void_p]),
     "wcr_dim_loss_bwd": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_void_p, c_void_p]),
+    "wcr_z_loss_steps": (None, [c_void_p]),
+    "wcr_sizeof": (c_i64, [c_int]),
 }
 _lib = None
 
@@ -138,7 +140,7 @@ class LossParams(ctypes.Structure):
     _fields_ = [("loss_flags", ctypes.c_int32), ("z_type", ctypes.c_int32),
                 ("dims_func", ctypes.c_int32), ("use_confidence", c_float), ("w_3d", c_float),
                 ("w_iou", c_float), ("w_pose", c_float), ("w_normal", c_float), ("w_z", c_float),
-                ("w_dims", c_float)]
+                ("w_dims", c_float), ("w_depth", c_float)]
 
 
 _LOSS_IO_PTRS = ["deltas", "z_raw", "dims_raw", "pose", "uncert", "src_boxes", "K4", "v2r",
@@ -148,7 +150,12 @@ _LOSS_IO_PTRS = ["deltas", "z_raw", "dims_raw", "pose", "uncert", "src_boxes", "
                  "z_dec", "z_gt", "z_inside", "z_sign"]
 
 
+_LOSS_IO_PTRS2 = ["mask_idx", "depth_gt", "gt_rot"]   # after the mask shape (tier-2 terms)
+
+
 class LossIO(ctypes.Structure):
-    """include/wcr.h WcrLossIO: two sizes then device pointers."""
+    """include/wcr.h WcrLossIO: two sizes, device pointers, then the tier-2 block."""
     _fields_ = [("n", ctypes.c_int32), ("n_images", ctypes.c_int32)] + \
-               [(name, c_void_p) for name in _LOSS_IO_PTRS]
+               [(name, c_void_p) for name in _LOSS_IO_PTRS] + \
+               [("masks", c_void_p), ("mask_h", ctypes.c_int32), ("mask_w", ctypes.c_int32)] + \
+               [(name, c_void_p) for name in _LOSS_IO_PTRS2]

@@ -20,9 +20,12 @@ from . import _abi
 from .images import ImageShard
 
 TERM_KEYS = ("Cube/uncert", "Cube/loss_iou", "Cube/loss_pose", "Cube/loss_normal_vec",
-             "Cube/loss_pseudo_gt_z", "Cube/loss_dims_w", "Cube/loss_dims_h", "Cube/loss_dims_l")
+             "Cube/loss_pseudo_gt_z", "Cube/loss_dims_w", "Cube/loss_dims_h", "Cube/loss_dims_l",
+             "Cube/loss_z", "Cube/loss_depth")
+N_TERMS, N_STATS = len(TERM_KEYS), 32          # WCR_LOSS_TERMS, WCR_LOSS_STATS
+STAT_TRACE_ERR, STAT_SHAPE_ERR = 18, 19
 _FLAG = {"iou": 1, "pose_alignment": 2, "pose_ground": 4, "z_pseudo_gt_center": 8, "dims": 16,
-         "z_pseudo_gt_patch": 32}
+         "z_pseudo_gt_patch": 32, "z": 64, "depth": 128, "pose_ground2": 256}
 _ZTYPE = {"direct": 0, "sigmoid": 1, "log": 2}
 _DIMS = {"exp": 0, "sigmoid": 1}
 
@@ -40,18 +43,19 @@ class WeakLossConfig:
     loss_w_normal_vec: float = 20.0
     loss_w_z: float = 1.0
     loss_w_dims: float = 20.0
+    loss_w_depth: float = 1.0
 
     def c_struct(self) -> _abi.LossParams:
         unknown = [f for f in self.loss_functions if f not in _FLAG]
         if unknown:
             raise _abi.WcrError(f"wcr.weak_loss: loss functions {unknown} are not on the fused path "
-                                "(tier-2 terms, SURVEY.md §8f)")
+                                "('segmentation', SURVEY.md §8f)")
         flags = 0
         for f in self.loss_functions:
             flags |= _FLAG[f]
         return _abi.LossParams(flags, _ZTYPE[self.z_type], _DIMS[self.dims_priors_func],
                                self.use_confidence, self.loss_w_3d, self.loss_w_iou, self.loss_w_pose,
-                               self.loss_w_normal_vec, self.loss_w_z, self.loss_w_dims)
+                               self.loss_w_normal_vec, self.loss_w_z, self.loss_w_dims, self.loss_w_depth)
 
 
 def _c(t, dev, dtype=torch.float32):
@@ -63,7 +67,7 @@ class _Ctx:
 
     def __init__(self, cfg, deltas, z_raw, dims_raw, pose, uncert, src_boxes, K4, virtual_to_real,
                  prior_mean, prior_std, gt_boxes, clamp, num_boxes_per_image, shard, normals,
-                 ground_conf):
+                 ground_conf, gt_masks=None, at_which_mask_idx=None):
         _abi.require_cuda(deltas, z_raw, dims_raw, pose, uncert)
         dev = deltas.device
         n = deltas.shape[0]
@@ -83,15 +87,33 @@ class _Ctx:
             "prior_std": _c(prior_std, dev), "gt_boxes": _c(gt_boxes, dev), "clamp": _c(clamp, dev),
             "img_off": off.to(dev), "images": shard.table, "normals": _c(normals, dev),
             "ground_conf": _c(ground_conf, dev),
-            "losses": torch.zeros(8, device=dev), "present": torch.zeros(8, dtype=torch.int32, device=dev),
-            "terms": torch.empty((7, max(n, 1)), device=dev), "R_ego": torch.empty((max(n, 1), 9), device=dev),
-            "proj": torch.empty((max(n, 1), 4), device=dev), "stats": torch.zeros(16, device=dev),
+            "losses": torch.zeros(N_TERMS, device=dev),
+            "present": torch.zeros(N_TERMS + 2, dtype=torch.int32, device=dev),
+            "terms": torch.empty((N_TERMS - 1, max(n, 1)), device=dev),
+            "R_ego": torch.empty((max(n, 1), 9), device=dev),
+            "proj": torch.empty((max(n, 1), 4), device=dev), "stats": torch.zeros(N_STATS, device=dev),
             "img_pose": torch.zeros(B, device=dev),
         }
         if "z_pseudo_gt_patch" in cfg.loss_functions:
             t.update({"z_dec": torch.empty(max(n, 1), device=dev), "z_gt": torch.empty(max(n, 1), device=dev),
                       "z_inside": torch.empty(max(n, 1), dtype=torch.int32, device=dev),
                       "z_sign": torch.zeros(max(n, 1), device=dev)})
+        self.mask_hw = (0, 0)
+        if "depth" in cfg.loss_functions:
+            if gt_masks is None or at_which_mask_idx is None:
+                raise _abi.WcrError("wcr.weak_loss: 'depth' needs gt_masks and at_which_mask_idx")
+            # masks_all_images (roi_heads.py:273): list of (1, H, W) bool, or one (M, H, W) tensor
+            m = gt_masks if isinstance(gt_masks, torch.Tensor) else torch.stack(
+                [torch.as_tensor(x).reshape(x.shape[-2], x.shape[-1]) for x in gt_masks])
+            m = m.reshape(-1, m.shape[-2], m.shape[-1]).to(device=dev)
+            m = (m != 0).to(torch.uint8).contiguous() if m.dtype not in (torch.uint8, torch.bool) else m.contiguous()
+            t.update({"masks": m.view(torch.uint8) if m.dtype == torch.bool else m,
+                      "mask_idx": torch.as_tensor(list(at_which_mask_idx), dtype=torch.int32).to(dev),
+                      "depth_gt": torch.empty(max(n, 1), device=dev)})
+            assert t["mask_idx"].numel() == n
+            self.mask_hw = (int(m.shape[-2]), int(m.shape[-1]))
+        if "pose_ground2" in cfg.loss_functions:
+            t["gt_rot"] = torch.empty((B, 9), device=dev)
         self.t = t
         self.n_images = B
 
@@ -101,9 +123,10 @@ class _Ctx:
         tt = dict(self.t)
         if extra:
             tt.update(extra)
-        for name in _abi._LOSS_IO_PTRS:
+        for name in _abi._LOSS_IO_PTRS + _abi._LOSS_IO_PTRS2 + ["masks"]:
             v = tt.get(name)
             setattr(io, name, None if v is None else v.data_ptr())
+        io.mask_h, io.mask_w = self.mask_hw
         self._keep = tt
         return io
 
@@ -138,7 +161,8 @@ class _WeakLossFn(torch.autograd.Function):
 
 def weak_loss(cfg: WeakLossConfig, deltas, z_raw, dims_raw, pose, uncert, *, src_boxes, K4,
               virtual_to_real, prior_mean, prior_std, gt_boxes, clamp, num_boxes_per_image,
-              depth_maps, normals, ground_conf, return_per_box: bool = False):
+              depth_maps, normals, ground_conf, gt_masks=None, at_which_mask_idx=None,
+              return_per_box: bool = False):
     """Fused weak-loss block. Per-box tensors follow the reference's torch.cat order
     (boxes of one image contiguous). ``depth_maps``: an ``ImageShard`` or anything
     ``ImageShard`` accepts (ImageList-like / list of (h,w) CUDA tensors); ``normals``
@@ -152,9 +176,14 @@ def weak_loss(cfg: WeakLossConfig, deltas, z_raw, dims_raw, pose, uncert, *, src
     shard = depth_maps if isinstance(depth_maps, ImageShard) else ImageShard(
         depth_maps, None, [torch.eye(3)] * len(num_boxes_per_image), device=deltas.device)
     c = _Ctx(cfg, deltas, z_raw, dims_raw, pose, uncert, src_boxes, K4, virtual_to_real, prior_mean,
-             prior_std, gt_boxes, clamp, num_boxes_per_image, shard, normals, ground_conf)
+             prior_std, gt_boxes, clamp, num_boxes_per_image, shard, normals, ground_conf, gt_masks,
+             at_which_mask_idx)
     out = _WeakLossFn.apply(c, deltas, z_raw, dims_raw, pose, uncert)
-    present = c.t["present"].cpu().tolist()
+    present = c.t["present"].cpu().tolist()     # the one host sync: term flags + two error flags
+    if present[N_TERMS]:
+        raise ValueError("A matrix has trace outside valid range [-1-eps,3+eps].")   # pytorch3d so3_rotation_angle
+    if present[N_TERMS + 1]:
+        raise _abi.WcrError("wcr.weak_loss: 'depth' needs masks of the same shape as their depth maps")
     losses = {k: out[i] for i, k in enumerate(TERM_KEYS) if present[i]}
     if return_per_box:
         t = c.t
