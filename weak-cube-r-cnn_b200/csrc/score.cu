@@ -89,6 +89,27 @@ __device__ __forceinline__ float inside_unit(float q0, float q1, float q2)
     return r;
 }
 
+// Same decision on coordinates pre-scaled by 2^11 (exact), with the compare moved from the
+// half-rate ALU pipe (FSET) to the FMA pipe: C - m^2 with C = 2^22 + 1 is >= 1 exactly when
+// m <= 2^11 and <= 0 otherwise (m^2 - 2^22 is a multiple of 2^-24 * 2^22 away from 0, never
+// in (0, 1)), one rounding, so .sat yields exactly 1.0f / 0.0f; NaN saturates to 0.
+__device__ __forceinline__ float inside_sat(float q0, float q1, float q2)
+{
+    float m, r;
+    asm("max.f32 %0, %1, %2, %3;" : "=f"(m) : "f"(fabsf(q0)), "f"(fabsf(q1)), "f"(fabsf(q2)));
+    asm("fma.rn.sat.f32 %0, %1, %2, 0f4A800002;" : "=f"(r) : "f"(-m), "f"(m));
+    return r;
+}
+
+// FMA-pipe-only form: one saturated indicator per axis, multiplied into the counter
+// (3 FFMA.SAT + FMUL + FFMA; no ALU-pipe instruction at all).
+__device__ __forceinline__ float sat_axis(float q)
+{
+    float r;
+    asm("fma.rn.sat.f32 %0, %1, %2, 0f4A800002;" : "=f"(r) : "f"(-q), "f"(q));
+    return r;
+}
+
 // Integer ROI of a GT box: Boxes.clip((h, w)) then .long() slicing, as the
 // reference slices depth patches (roi_heads.py:590-597), sub-sampled by `s`.
 struct Roi { int u0, v0, ncols, nrows, rows_per_item, n_rowblocks; };
@@ -328,6 +349,9 @@ __global__ void __launch_bounds__(SC_THREADS, MINB) score_items_kernel(const Sco
                         Bf[e][k] = cube[9 + k] / half[k];
                         Cf[e][k] = cube[12 + k] / half[k];
                         NOf[e][k] = -fmaf(Cf[e][k], cube[2], fmaf(Bf[e][k], cube[1], Af[e][k] * cube[0]));
+                        if (V == 4 || V == 5) {   // exact power-of-two scaling for inside_sat
+                            Af[e][k] *= 2048.f; Bf[e][k] *= 2048.f; Cf[e][k] *= 2048.f; NOf[e][k] *= 2048.f;
+                        }
                     }
                 } else {
 #pragma unroll
@@ -369,7 +393,7 @@ __global__ void __launch_bounds__(SC_THREADS, MINB) score_items_kernel(const Sco
                         av = ((float)u - K.cx) / K.fx;
                         if (d > 0.f && d <= 3.402823466e38f) { z = d; ++my_valid; }
                     }
-                    tile[idx] = make_float4(av, av, z, z);
+                    tile[idx] = V == 0 ? make_float4(av, av, z, z) : make_float4(av, z, av, z);
                 }
                 __syncthreads();
                 for (int ss = 0; ss < nseg; ++ss) {
@@ -411,13 +435,15 @@ __global__ void __launch_bounds__(SC_THREADS, MINB) score_items_kernel(const Sco
                         const float4 *src = tile + ss * segpad;
 #pragma unroll 4
                         for (int p = 0; p < segpad; ++p) {
-                            const float4 pp = src[p];
+                            const float2 pp = *reinterpret_cast<const float2 *>(src + p);   // (a_u, z): one LDS.64
 #pragma unroll
                             for (int t = 0; t < T; ++t) {
-                                const float q0 = fmaf(pp.z, fmaf(Af[t][0], pp.x, Gf[t][0]), NOf[t][0]);
-                                const float q1 = fmaf(pp.z, fmaf(Af[t][1], pp.x, Gf[t][1]), NOf[t][1]);
-                                const float q2 = fmaf(pp.z, fmaf(Af[t][2], pp.x, Gf[t][2]), NOf[t][2]);
+                                const float q0 = fmaf(pp.y, fmaf(Af[t][0], pp.x, Gf[t][0]), NOf[t][0]);
+                                const float q1 = fmaf(pp.y, fmaf(Af[t][1], pp.x, Gf[t][1]), NOf[t][1]);
+                                const float q2 = fmaf(pp.y, fmaf(Af[t][2], pp.x, Gf[t][2]), NOf[t][2]);
                                 if (V == 1) cntf[t] += inside_unit(q0, q1, q2);
+                                else if (V == 4) cntf[t] += inside_sat(q0, q1, q2);
+                                else if (V == 5) cntf[t] = fmaf(sat_axis(q0) * sat_axis(q1), sat_axis(q2), cntf[t]);
                                 else count_inside1(cnti[t], q0, q1, q2);
                             }
                         }
@@ -715,7 +741,7 @@ extern "C" int wcr_score_topk(const WcrImage *images, const WcrBox *boxes, int n
     static int variant = -1;
     if (variant < 0) {  // development knob; the default is what DESIGN.md measures
         const char *ev = getenv("WCR_SCORE_VARIANT");
-        variant = ev ? atoi(ev) : 1;
+        variant = ev ? atoi(ev) : 4;
     }
     const int sms = wcr::sm_count();
     switch (variant) {
@@ -724,7 +750,10 @@ extern "C" int wcr_score_topk(const WcrImage *images, const WcrBox *boxes, int n
     case 11: wcr::score_items_kernel<1, 3><<<sms * 3, wcr::SC_THREADS, 0, st>>>(a); break;
     case 12: wcr::score_items_kernel<2, 3><<<sms * 3, wcr::SC_THREADS, 0, st>>>(a); break;
     case 0: wcr::score_items_kernel<0, 2><<<sms * 2, wcr::SC_THREADS, 0, st>>>(a); break;
-    default: wcr::score_items_kernel<1, 2><<<sms * 2, wcr::SC_THREADS, 0, st>>>(a); break;
+    case 5: wcr::score_items_kernel<5, 2><<<sms * 2, wcr::SC_THREADS, 0, st>>>(a); break;
+    case 14: wcr::score_items_kernel<4, 3><<<sms * 3, wcr::SC_THREADS, 0, st>>>(a); break;
+    case 1: wcr::score_items_kernel<1, 2><<<sms * 2, wcr::SC_THREADS, 0, st>>>(a); break;
+    default: wcr::score_items_kernel<4, 2><<<sms * 2, wcr::SC_THREADS, 0, st>>>(a); break;
     }
     WCR_CHECK_LAUNCH("score_items_kernel");
     return WCR_OK;
