@@ -359,7 +359,14 @@ typedef struct WcrLossIO {
     float   *depth_gt;        /* [n] out: q90 - q10 of the masked depth (GT box patch when the mask is empty) */
     /* 'pose_ground2' only (NULL otherwise) */
     float   *gt_rot;          /* [n_images][9] workspace: normal_to_rotation per image */
+    /* 'z_pseudo_gt_patch' and 'depth' (NULL otherwise): wcr_select_ws_bytes(n) bytes, 256-byte aligned */
+    void    *select_ws;
 } WcrLossIO;
+
+/* Workspace of the per-box order-statistic kernels (median of a depth patch, quantiles of
+ * the depth under a mask): per box a 128-byte state and a 4 x 256-bin histogram, plus the
+ * work-item prefix. Host function, no GPU needed. */
+int64_t wcr_select_ws_bytes(int n);
 
 /* sizeof() of the ABI structs as the library was compiled, so a binding can verify its
  * mirror: 0 WcrImage, 1 WcrBox, 2 WcrSampleParams, 3 WcrScoreParams, 4 WcrLossParams,
@@ -395,10 +402,11 @@ int wcr_pseudo_z_point_loss(const WcrImage *images, const int32_t *img_off, int 
  * boxes with zero area after clipping fall back to the centre lookup AND are appended
  * after the in-image boxes of their image, so the pairing with pred_z is by position in
  * that re-ordered list (reference behaviour, kept).
- *   boxes [n][4]; ws_gt [n], ws_inside [n] scratch (per-box pseudo depth / in-image flag). */
+ *   boxes [n][4]; ws_gt [n], ws_inside [n] scratch (per-box pseudo depth / in-image flag);
+ *   select_ws: wcr_select_ws_bytes(n) bytes. */
 int wcr_pseudo_z_box_loss(const WcrImage *images, const int32_t *img_off, int n_images, int n,
                           const float *boxes, const float *pred_z, float *out_loss, float *out_sign,
-                          float *ws_gt, int32_t *ws_inside, void *stream);
+                          float *ws_gt, int32_t *ws_inside, void *select_ws, void *stream);
 
 /* backward of smooth_l1(beta = 0) (roi_heads.py:352-353): d_pred[i] = grad[i] * sign[i]. */
 int wcr_l1_loss_bwd(const float *sign, const float *grad, int n, float *d_pred, void *stream);

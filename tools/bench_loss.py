@@ -28,6 +28,9 @@ def main():
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--cpu-repeats", type=int, default=3)
     ap.add_argument("--patch", action="store_true", help="use 'z_pseudo_gt_patch' (box median) instead of the centre lookup")
+    ap.add_argument("--noise-depth", action="store_true",
+                    help="white-noise depth maps (the parity tests' worst case) instead of the synthetic "
+                         "floor + wall + objects scenes of bench.py")
     ap.add_argument("--default", action="store_true",
                     help="cfg.loss_functions of config.py:186: dims, pose_alignment, pose_ground, iou, z, "
                          "z_pseudo_gt_patch, depth (per-object masks)")
@@ -41,6 +44,10 @@ def main():
     g = torch.Generator().manual_seed(0)
     nb = [int(x) for x in torch.randint(1, 129, (16,), generator=g)]
     inp = li.make_loss_inputs(7, nb, H=480, W=640)
+    if not a.noise_depth:      # scene-like depth (smooth surfaces + 1 % noise), as in bench.py's workload
+        from wcr import synth
+        inp["depth_maps"] = [synth.make_image(1000 + i, 480, 640, n_boxes=8)["depth"].contiguous()
+                             for i in range(len(nb))]
     lf = ("iou", "z_pseudo_gt_patch" if a.patch else "z_pseudo_gt_center", "pose_alignment", "pose_ground", "dims")
     if a.default:
         lf = ("dims", "pose_alignment", "pose_ground", "iou", "z", "z_pseudo_gt_patch", "depth")
@@ -89,7 +96,8 @@ def main():
         "metric": "weak-loss fwd+bwd latency", "value": statistics.median(ms), "unit": "ms",
         "higher_is_better": False, "n_gpus": 1, "steps": a.steps, "warmup": a.warmup, "dtype": "f32",
         "data": "synthetic", "config": {"workload": f"weak-loss fwd/bwd, batch 16, {sum(nb)} foreground boxes "
-                                                    f"(n_i~U{{1..128}}), 480x640 depth, loss_functions={list(lf)}"},
+                                                    f"(n_i~U{{1..128}}), 480x640 {'white-noise' if a.noise_depth else 'scene-like'} depth, "
+                                                    f"loss_functions={list(lf)}"},
         "gpu_launches_per_step": launches, "ms_min": min(ms), "ms_max": max(ms),
         "includes": "Python wrapper, one 32-byte D2H read of the 'present' flags, autograd bookkeeping",
         "cpu_baseline": {"value": statistics.median(cpu) if cpu else None, "unit": "ms", "cores": torch.get_num_threads(),

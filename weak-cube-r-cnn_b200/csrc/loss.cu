@@ -286,9 +286,6 @@ loss_box_fwd_kernel(const WcrLossIO io, const WcrLossParams P, const ZSteps zs)
     for (int t = 0; t < LT; ++t) io.terms[(size_t)t * io.n + i] = term[t];
 }
 
-__global__ void box_median_kernel(const WcrImage *__restrict__ images, const int32_t *__restrict__ img_off,
-                                  int n_images, const float *__restrict__ boxes, float *__restrict__ out_gt,
-                                  int *__restrict__ out_inside);
 __global__ void box_z_loss_kernel(const int32_t *__restrict__ img_off, int n_images,
                                   const float *__restrict__ gt, const int *__restrict__ inside,
                                   const float *__restrict__ pred_z, float *__restrict__ out_loss,
@@ -485,7 +482,34 @@ ground_rot_kernel(const float *__restrict__ normals, const int32_t *__restrict__
         for (int k = 3; k < 6; ++k) gt_rot[9 * im + k] /= norm1;
 }
 
-// ---- 'depth': q90 - q10 of the depth under the object's mask (roi_heads.py:669-679) ----------
+// ---- sliced multi-target radix select ---------------------------------------------------------
+// torch.median of a depth patch (pseudo_gt_z_box_loss, roi_heads.py:598) and the two
+// torch.quantile calls of depth_range_loss (:676) are order statistics of up to 307 k depth
+// values per box. One CTA per box (the first version) is bound by its longest box: a
+// clipped projected box can cover the whole image while most cover a few thousand pixels.
+// Here a box's source region is cut into slices of SEL_SLICE elements; a persistent grid
+// strides over the (box, slice) items of all boxes, each item histograms one 8-bit digit of
+// the order-preserving key into shared memory and adds its non-empty bins to the box's
+// global histogram; the CTA that retires a box's last slice narrows the key prefix of every
+// target rank and clears the histogram. Four launches = four digits. Up to four target
+// ranks are followed at once, one histogram per distinct prefix.
+constexpr int SEL_SLICE = 16384;
+constexpr int SEL_THREADS = 256;
+
+struct SelState {            // 32 words
+    int r0, r1, c0, c1;      // source region of the depth map: rows [r0, r1) x cols [c0, c1)
+    int image;               // index into the image table
+    int mask;                // mask index, or -1: every pixel of the region takes part
+    int slices;              // work items of this box; 0 = nothing to select
+    int T;                   // targets: 1 (median) or 4 (two interpolated quantiles)
+    int arrivals, nan, ngroups, cnt;
+    unsigned prefix[4], rank[4], gprefix[4];
+    int group[4];
+    float w_hi, w_lo;        // lerp weights of the two quantiles
+    int rlo, rhi;            // mask row range gathered by the count pass: mh - min_row, max_row + 1
+};
+static_assert(sizeof(SelState) == 128, "SelState layout");
+
 __device__ __forceinline__ uint32_t float_key(float f);
 __device__ __forceinline__ float key_float(uint32_t k);
 
@@ -503,38 +527,103 @@ __device__ __forceinline__ float torch_lerp(float a, float b, float w)
     return fabsf(w) < 0.5f ? a + w * diff : b - diff * (1.f - w);
 }
 
-// One CTA per box: the four order statistics torch.quantile(x, 0.9) and torch.quantile(x, 0.1)
-// interpolate between, found by ONE 4-pass 8-bit radix select that follows up to four key
-// prefixes at once (a histogram per distinct prefix), over either the masked pixels of the
-// box's image or -- when the mask is empty -- the GT box patch. No sort, no compaction buffer:
-// the reference sorts every masked depth vector twice per box.
-__global__ void __launch_bounds__(256)
-mask_quantile_kernel(const WcrImage *__restrict__ images, const int32_t *__restrict__ img_off, int n_images,
-                     const uint8_t *__restrict__ masks, int mh, int mw, const int32_t *__restrict__ mask_idx,
-                     const float *__restrict__ gt_boxes, float *__restrict__ out_range, float *__restrict__ stats)
+// exclusive prefix of states[b].slices over all boxes -> item_prefix[n + 1]; one CTA of 1024
+__device__ void sel_plan(const SelState *states, int n, int *item_prefix)
 {
-    __shared__ unsigned hist[4][256];
-    __shared__ unsigned s_prefix[4], s_rank[4], s_gprefix[4];
-    __shared__ int s_group[4], s_ngroups, s_cnt, s_rmin, s_rmax, s_nan;
-    const int b = blockIdx.x, tid = threadIdx.x;
-    const WcrImage im = images[image_of(img_off, n_images, b)];
-    if (im.H != mh || im.W != mw) {
-        if (tid == 0) { out_range[b] = nanf_(); stats[WCR_STAT_SHAPE_ERR] = 1.f; }
-        return;
-    }
-    const uint8_t *m = masks + (size_t)mask_idx[b] * mh * mw;
-    if (tid == 0) { s_cnt = 0; s_rmin = mh; s_rmax = -1; s_nan = 0; }
+    __shared__ int s_warp[32];
+    __shared__ int s_carry;
+    const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+    if (tid == 0) s_carry = 0;
     __syncthreads();
-    // -- pass A: how many pixels, which rows ----------------------------------------------
-    {
-        int cnt = 0, rmin = mh, rmax = -1;
-        const int total = mh * mw;
-        const int head = min(total, (int)((16 - ((uintptr_t)m & 15)) & 15));
-        const int nvec = (total - head) / 16;
-        auto visit = [&](int idx) { ++cnt; const int r = idx / mw; rmin = min(rmin, r); rmax = max(rmax, r); };
-        for (int i = tid; i < head; i += blockDim.x) if (m[i]) visit(i);
-        for (int i = head + 16 * nvec + tid; i < total; i += blockDim.x) if (m[i]) visit(i);
-        const uint4 *mv = reinterpret_cast<const uint4 *>(m + head);
+    for (int base = 0; base < n; base += 1024) {
+        const int b = base + tid;
+        const int v = b < n ? states[b].slices : 0;
+        int incl = v;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const int t = __shfl_up_sync(0xffffffffu, incl, o);
+            if (lane >= o) incl += t;
+        }
+        if (lane == 31) s_warp[wid] = incl;
+        __syncthreads();
+        if (wid == 0) {
+            int w = s_warp[lane];
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const int x = __shfl_up_sync(0xffffffffu, w, o);
+                if (lane >= o) w += x;
+            }
+            s_warp[lane] = w;
+        }
+        __syncthreads();
+        const int before = s_carry + (wid ? s_warp[wid - 1] : 0) + incl - v;
+        if (b < n) item_prefix[b] = before;
+        __syncthreads();
+        if (tid == 1023) s_carry = before + v;
+        __syncthreads();
+    }
+    if (tid == 0) item_prefix[n] = s_carry;
+}
+
+__device__ __forceinline__ void sel_arm(SelState &st, int elements)
+{
+    st.slices = (elements + SEL_SLICE - 1) / SEL_SLICE;
+    st.arrivals = 0; st.nan = 0; st.ngroups = 1;
+#pragma unroll
+    for (int t = 0; t < 4; ++t) { st.prefix[t] = 0u; st.gprefix[t] = 0u; st.group[t] = 0; }
+}
+
+// pseudo_gt_z_box_loss (:585-606): region + rank of the lower median of every in-image box;
+// the out-of-image fallback and the degenerate cases are answered here directly.
+__global__ void __launch_bounds__(1024)
+sel_init_median_kernel(const WcrImage *__restrict__ images, const int32_t *__restrict__ img_off, int n_images,
+                       int n, const float *__restrict__ boxes, float *__restrict__ out_gt,
+                       int *__restrict__ out_inside, SelState *__restrict__ states, int *__restrict__ item_prefix)
+{
+    for (int b = threadIdx.x; b < n; b += blockDim.x) {
+        SelState st;
+        memset(&st, 0, sizeof(st));
+        st.image = image_of(img_off, n_images, b);
+        st.mask = -1; st.T = 1;
+        const WcrImage im = images[st.image];
+        // Boxes.clip((h, w)), area() > 0 on the clipped float box, then .long() slicing
+        const float x1 = clamp_keep_nan(boxes[4 * b + 0], 0.f, (float)im.W), y1 = clamp_keep_nan(boxes[4 * b + 1], 0.f, (float)im.H);
+        const float x2 = clamp_keep_nan(boxes[4 * b + 2], 0.f, (float)im.W), y2 = clamp_keep_nan(boxes[4 * b + 3], 0.f, (float)im.H);
+        if (x1 != x1 || y1 != y1 || x2 != x2 || y2 != y2) {
+            // a NaN box (cube behind the camera): the reference indexes with an undefined
+            // .long() here; defined as "no pseudo depth" (NaN, masked by the safe mean)
+            out_gt[b] = nanf_(); out_inside[b] = 0;
+        } else if (!((x2 - x1) * (y2 - y1) > 0.f)) {
+            // fallback of :600-606: centre lookup of the CLIPPED box with the 10-px clamp
+            out_gt[b] = depth_at(im, (x1 + x2) / 2.f, (y1 + y2) / 2.f); out_inside[b] = 0;
+        } else {
+            st.c0 = (int)x1; st.c1 = (int)x2; st.r0 = (int)y1; st.r1 = (int)y2;
+            st.cnt = (st.c1 - st.c0) * (st.r1 - st.r0);
+            out_inside[b] = 1;
+            if (st.cnt <= 0) out_gt[b] = nanf_();   // torch.median of an empty slice raises in the reference
+            else { sel_arm(st, st.cnt); st.rank[0] = (unsigned)((st.cnt - 1) / 2); }
+        }
+        states[b] = st;
+    }
+    __syncthreads();
+    sel_plan(states, n, item_prefix);
+}
+
+// depth_range_loss: masked pixel count and row range of every box's mask; grid (chunks, n)
+constexpr int SEL_COUNT_CHUNK = 16384;
+__global__ void __launch_bounds__(256)
+mask_count_kernel(const uint8_t *__restrict__ masks, int mh, int mw, const int32_t *__restrict__ mask_idx,
+                  SelState *__restrict__ states)
+{
+    const int b = blockIdx.y, tid = threadIdx.x;
+    const int total = mh * mw;
+    const int lo = blockIdx.x * SEL_COUNT_CHUNK, hi = min(total, lo + SEL_COUNT_CHUNK);
+    const uint8_t *m = masks + (size_t)mask_idx[b] * total;
+    int cnt = 0, rmin = mh, rmax = -1;
+    auto visit = [&](int idx) { ++cnt; const int r = idx / mw; rmin = min(rmin, r); rmax = max(rmax, r); };
+    if ((((uintptr_t)(m + lo)) & 15) == 0) {
+        const int nvec = (hi - lo) / 16;
+        const uint4 *mv = reinterpret_cast<const uint4 *>(m + lo);
         for (int v = tid; v < nvec; v += blockDim.x) {
             const uint4 w = __ldg(mv + v);
             if ((w.x | w.y | w.z | w.w) == 0u) continue;
@@ -543,98 +632,254 @@ mask_quantile_kernel(const WcrImage *__restrict__ images, const int32_t *__restr
             for (int q = 0; q < 4; ++q)
 #pragma unroll
                 for (int e = 0; e < 4; ++e)
-                    if ((ww[q] >> (8 * e)) & 255u) visit(head + 16 * v + 4 * q + e);
+                    if ((ww[q] >> (8 * e)) & 255u) visit(lo + 16 * v + 4 * q + e);
         }
-        if (cnt) { atomicAdd(&s_cnt, cnt); atomicMin(&s_rmin, rmin); atomicMax(&s_rmax, rmax); }
+        for (int i = lo + 16 * nvec + tid; i < hi; i += blockDim.x) if (m[i]) visit(i);
+    } else {
+        for (int i = lo + tid; i < hi; i += blockDim.x) if (m[i]) visit(i);
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        cnt += __shfl_xor_sync(0xffffffffu, cnt, o);
+        rmin = min(rmin, __shfl_xor_sync(0xffffffffu, rmin, o));
+        rmax = max(rmax, __shfl_xor_sync(0xffffffffu, rmax, o));
+    }
+    if ((tid & 31) == 0 && cnt) {
+        atomicAdd(&states[b].cnt, cnt);
+        atomicMax(&states[b].rlo, mh - rmin);
+        atomicMax(&states[b].rhi, rmax + 1);
+    }
+}
+
+__global__ void __launch_bounds__(1024)
+sel_init_quantile_kernel(const WcrImage *__restrict__ images, const int32_t *__restrict__ img_off, int n_images,
+                         int n, int mh, int mw, const int32_t *__restrict__ mask_idx,
+                         const float *__restrict__ gt_boxes, float *__restrict__ out_range,
+                         float *__restrict__ stats, SelState *__restrict__ states, int *__restrict__ item_prefix)
+{
+    for (int b = threadIdx.x; b < n; b += blockDim.x) {
+        SelState st = states[b];            // zeroed, then cnt / rlo / rhi from mask_count_kernel
+        st.image = image_of(img_off, n_images, b);
+        st.T = 4; st.slices = 0;
+        const WcrImage im = images[st.image];
+        int elements = 0;
+        if (im.H != mh || im.W != mw) {
+            out_range[b] = nanf_(); stats[WCR_STAT_SHAPE_ERR] = 1.f;
+        } else {
+            if (st.cnt > 0) {               // depth_map[segmentation_mask]
+                st.mask = mask_idx[b];
+                st.r0 = mh - st.rlo; st.r1 = st.rhi; st.c0 = 0; st.c1 = mw;
+                elements = (st.r1 - st.r0) * mw;
+            } else {                        // segmentation failed: the GT box patch (:674-675)
+                const float *g = gt_boxes + 4 * b;
+                st.mask = -1;
+                st.c0 = py_slice_index((long long)g[0], mw); st.c1 = py_slice_index((long long)g[2], mw);
+                st.r0 = py_slice_index((long long)g[1], mh); st.r1 = py_slice_index((long long)g[3], mh);
+                st.cnt = max(st.r1 - st.r0, 0) * max(st.c1 - st.c0, 0);
+                elements = st.cnt;
+            }
+            if (st.cnt <= 0) out_range[b] = nanf_();   // torch.quantile of an empty tensor raises; NaN here
+            else {
+                sel_arm(st, elements);
+                const float r9 = 0.9f * (float)(st.cnt - 1), r1 = 0.1f * (float)(st.cnt - 1);
+                const float b9 = floorf(r9), b1 = floorf(r1);
+                st.w_hi = r9 - b9; st.w_lo = r1 - b1;
+                st.rank[0] = (unsigned)b9; st.rank[1] = (unsigned)ceilf(r9);
+                st.rank[2] = (unsigned)b1; st.rank[3] = (unsigned)ceilf(r1);
+            }
+        }
+        states[b] = st;
     }
     __syncthreads();
-    int cnt = s_cnt;
-    const bool use_mask = cnt > 0;
-    // source region: rows [r0, r1) x cols [c0, c1) of the depth map, masked or not
-    int r0 = s_rmin, r1 = s_rmax + 1, c0 = 0, c1 = mw;
-    if (!use_mask) {   // segmentation failed: depth_map[y1.long():y2.long(), x1.long():x2.long()] (:674-675)
-        const float *g = gt_boxes + 4 * b;
-        c0 = py_slice_index((long long)g[0], mw); c1 = py_slice_index((long long)g[2], mw);
-        r0 = py_slice_index((long long)g[1], mh); r1 = py_slice_index((long long)g[3], mh);
-        cnt = max(r1 - r0, 0) * max(c1 - c0, 0);
-    }
-    if (cnt <= 0) {    // torch.quantile of an empty tensor raises in the reference; NaN here
-        if (tid == 0) out_range[b] = nanf_();
-        return;
-    }
-    float w9, w1;
-    {
-        const float r9 = 0.9f * (float)(cnt - 1), r1f = 0.1f * (float)(cnt - 1);
-        const float b9 = floorf(r9), b1 = floorf(r1f);
-        w9 = r9 - b9; w1 = r1f - b1;
-        if (tid == 0) {
-            s_rank[0] = (unsigned)b9; s_rank[1] = (unsigned)ceilf(r9);
-            s_rank[2] = (unsigned)b1; s_rank[3] = (unsigned)ceilf(r1f);
-#pragma unroll
-            for (int t = 0; t < 4; ++t) { s_prefix[t] = 0u; s_group[t] = 0; }
-            s_gprefix[0] = 0u; s_ngroups = 1;
+    sel_plan(states, n, item_prefix);
+}
+
+// One digit of every box's select. mode 0: out[b] = the selected value (median);
+// mode 1: out[b] = lerp(hi pair) - lerp(lo pair) (q90 - q10). NG = how many distinct key
+// prefixes a box may follow in this launch (1: median, and digit 0 of anything; 4 otherwise).
+template <int NG>
+__global__ void __launch_bounds__(SEL_THREADS)
+sel_pass_kernel(SelState *__restrict__ states, const int *__restrict__ item_prefix, int n,
+                unsigned *__restrict__ hist /* [n][4][256] */, const WcrImage *__restrict__ images,
+                const uint8_t *__restrict__ masks, int mh, int mw, int pass, int mode, float *__restrict__ out)
+{
+    __shared__ unsigned sh[NG][256];
+    __shared__ int s_last;
+    const int tid = threadIdx.x;
+    const int total = item_prefix[n];
+    const int shift = 24 - 8 * pass;
+    const unsigned himask = pass == 0 ? 0u : (0xffffffffu << (shift + 8));
+    for (int item = blockIdx.x; item < total; item += gridDim.x) {
+        int b = 0;
+        {
+            int hi = n;   // item_prefix[b] <= item < item_prefix[hi]
+            while (hi - b > 1) {
+                const int mid = (b + hi) >> 1;
+                if (item_prefix[mid] <= item) b = mid; else hi = mid;
+            }
         }
-    }
-    const int ncols = c1 - c0, region = (r1 - r0) * ncols;
-    for (int pass = 0; pass < 4; ++pass) {
-        const int shift = 24 - 8 * pass;
-        for (int i = tid; i < 4 * 256; i += blockDim.x) (&hist[0][0])[i] = 0u;
-        __syncthreads();
-        const int ng = s_ngroups;
-        const unsigned gp0 = s_gprefix[0], gp1 = s_gprefix[1], gp2 = s_gprefix[2], gp3 = s_gprefix[3];
-        const unsigned himask = pass == 0 ? 0u : (0xffffffffu << (shift + 8));
-        // per-thread run-length encoding per group: depths under one mask share their leading
-        // bytes, plain shared atomics would serialise on one or two bins
-        unsigned last[4] = {~0u, ~0u, ~0u, ~0u}, run[4] = {0u, 0u, 0u, 0u};
-        auto feed = [&](float f) {
-            if (pass == 0 && f != f) s_nan = 1;
-            const uint32_t k = float_key(f);
-            const unsigned hi = k & himask, bin = (k >> shift) & 255u;
-            const unsigned gp[4] = {gp0, gp1, gp2, gp3};
+        const int s = item - item_prefix[b];
+        SelState *sp = states + b;
+        const int r0 = sp->r0, c0 = sp->c0, ncols = sp->c1 - sp->c0, elements = (sp->r1 - sp->r0) * ncols;
+        const int ng = NG == 1 ? 1 : sp->ngroups, slices = sp->slices, mk = sp->mask;
+        unsigned gp[NG];
 #pragma unroll
-            for (int g = 0; g < 4; ++g) {
-                if (g >= ng || hi != gp[g]) continue;
-                if (bin == last[g]) { ++run[g]; continue; }
-                if (run[g]) atomicAdd(&hist[g][last[g]], run[g]);
-                last[g] = bin; run[g] = 1u;
+        for (int g = 0; g < NG; ++g) gp[g] = sp->gprefix[g];
+        const WcrImage im = images[sp->image];
+        const uint8_t *m = mk >= 0 ? masks + (size_t)mk * mh * mw : nullptr;
+        for (int i = tid; i < ng * 256; i += SEL_THREADS) (&sh[0][0])[i] = 0u;
+        __syncthreads();
+        // per-thread run-length encoding per group: neighbouring depths share their leading
+        // bytes, plain shared atomics would serialise on one or two bins
+        unsigned last[NG], run[NG];
+#pragma unroll
+        for (int g = 0; g < NG; ++g) { last[g] = ~0u; run[g] = 0u; }
+        bool saw_nan = false;
+        // branch-free: a predicated shared atomic only when the thread's run of equal bins ends
+        auto feed = [&](float f) {
+            saw_nan |= f != f;
+            const uint32_t u = __float_as_uint(f);
+            const uint32_t k = u ^ ((uint32_t)((int32_t)u >> 31) | 0x80000000u);   // float_key
+            const unsigned hi = k & himask, bin = (k >> shift) & 255u;
+#pragma unroll
+            for (int g = 0; g < NG; ++g) {
+                const bool match = (NG == 1 || g < ng) && hi == gp[g];
+                const bool same = match && bin == last[g];
+                if (match && !same && run[g]) atomicAdd(&sh[g][last[g]], run[g]);
+                run[g] = same ? run[g] + 1u : (match ? 1u : run[g]);
+                last[g] = match ? bin : last[g];
             }
         };
-        for (int i = tid; i < region; i += blockDim.x) {
-            const int r = i / ncols, c = i - r * ncols;
-            const int rr = r0 + r, cc = c0 + c;
-            if (use_mask && !m[(size_t)rr * mw + cc]) continue;
-            feed(__ldg(im.depth + (size_t)rr * im.depth_pitch + cc));
+        const int lo = s * SEL_SLICE, hi = min(elements, lo + SEL_SLICE);
+        const float *dbase = im.depth + (size_t)r0 * im.depth_pitch + c0;
+        const bool vec_mask = m && c0 == 0 && ncols == mw && (mw & 3) == 0 && (((uintptr_t)m) & 3) == 0;
+        if (vec_mask) {
+            // masked rows of full width: 4 pixels per 32-bit mask word, most words are empty
+            const uint32_t *mw32 = reinterpret_cast<const uint32_t *>(m + (size_t)r0 * mw);
+            const int wpr = mw >> 2;                       // words per row
+            const int w_lo = lo >> 2, w_hi = (hi + 3) >> 2;  // lo is a multiple of SEL_SLICE
+            for (int w0 = w_lo + tid; w0 < w_hi; w0 += 2 * SEL_THREADS) {
+                uint32_t bits[2];
+#pragma unroll
+                for (int q = 0; q < 2; ++q) {
+                    const int w = w0 + SEL_THREADS * q;
+                    bits[q] = w < w_hi ? __ldg(mw32 + w) : 0u;
+                }
+#pragma unroll
+                for (int q = 0; q < 2; ++q) {
+                    if (!bits[q]) continue;
+                    const int w = w0 + SEL_THREADS * q;
+                    const int r = w / wpr, c = (w - r * wpr) << 2;
+                    const float *row = dbase + (size_t)r * im.depth_pitch + c;
+                    float f[4];
+#pragma unroll
+                    for (int e = 0; e < 4; ++e) f[e] = (bits[q] >> (8 * e)) & 255u ? __ldg(row + e) : 0.f;
+#pragma unroll
+                    for (int e = 0; e < 4; ++e) if ((bits[q] >> (8 * e)) & 255u) feed(f[e]);
+                }
+            }
+        } else {
+            // 4 CONSECUTIVE elements per thread per round (the run-length encoder then sees
+            // neighbouring pixels; a warp still covers 128 contiguous floats), loads issued
+            // before use; (row, col) advance incrementally by the CTA stride
+            const int stride = 4 * SEL_THREADS;
+            const int dq = stride / ncols, dc = stride - dq * ncols;
+            int i0 = lo + 4 * tid;
+            int r = i0 / ncols, c = i0 - r * ncols;
+            for (; i0 < hi; i0 += stride) {
+                const float *p = dbase + (size_t)r * im.depth_pitch + c;
+                if (!m && c + 3 < ncols && i0 + 3 < hi) {      // 4 pixels of one row: one address
+                    const float f0 = __ldg(p), f1 = __ldg(p + 1), f2 = __ldg(p + 2), f3 = __ldg(p + 3);
+                    feed(f0); feed(f1); feed(f2); feed(f3);
+                } else {
+                    float f[4];
+                    bool take[4];
+                    int rr = r, cc = c;
+#pragma unroll
+                    for (int q = 0; q < 4; ++q) {
+                        take[q] = i0 + q < hi;
+                        if (take[q] && m) take[q] = m[(size_t)(r0 + rr) * mw + c0 + cc] != 0;
+                        f[q] = take[q] ? __ldg(dbase + (size_t)rr * im.depth_pitch + cc) : 0.f;
+                        if (++cc == ncols) { cc = 0; ++rr; }
+                    }
+#pragma unroll
+                    for (int q = 0; q < 4; ++q) if (take[q]) feed(f[q]);
+                }
+                r += dq; c += dc;
+                if (c >= ncols) { c -= ncols; ++r; }
+            }
         }
 #pragma unroll
-        for (int g = 0; g < 4; ++g) if (run[g]) atomicAdd(&hist[g][last[g]], run[g]);
+        for (int g = 0; g < NG; ++g) if (run[g]) atomicAdd(&sh[g][last[g]], run[g]);
+        if (pass == 0 && saw_nan) sp->nan = 1;
         __syncthreads();
-        if (tid == 0) {
-            for (int t = 0; t < 4; ++t) {
-                const unsigned *h = hist[s_group[t]];
-                unsigned rank = s_rank[t], acc = 0u;
-                int bin = 0;
-                for (; bin < 255; ++bin) {
-                    if (acc + h[bin] > rank) break;
-                    acc += h[bin];
+        unsigned *gh = hist + (size_t)b * 1024;
+        for (int i = tid; i < ng * 256; i += SEL_THREADS) {
+            const unsigned v = (&sh[0][0])[i];
+            if (v) atomicAdd(gh + i, v);
+        }
+        __threadfence();
+        __syncthreads();
+        if (tid == 0) s_last = atomicAdd(&sp->arrivals, 1) == slices - 1;
+        __syncthreads();
+        if (s_last) {   // this CTA retired the box's last slice: narrow every target by one digit
+            __threadfence();
+            const int T = sp->T;
+            // stage the box's histograms in shared memory (one coalesced L2 read), then one
+            // warp per target: 8 bins per lane, warp prefix, the lane that holds the rank
+            for (int i = tid; i < ng * 256; i += SEL_THREADS) (&sh[0][0])[i] = __ldcg(gh + i);
+            __syncthreads();
+            const int wid = tid >> 5, lane = tid & 31;
+            if (wid < T) {
+                const unsigned *h = sh[NG == 1 ? 0 : sp->group[wid]] + 8 * lane;
+                unsigned c[8], sum = 0u;
+#pragma unroll
+                for (int q = 0; q < 8; ++q) { c[q] = h[q]; sum += c[q]; }
+                unsigned incl = sum;
+#pragma unroll
+                for (int o = 1; o < 32; o <<= 1) {
+                    const unsigned t = __shfl_up_sync(0xffffffffu, incl, o);
+                    if (lane >= o) incl += t;
                 }
-                s_rank[t] = rank - acc;
-                s_prefix[t] |= (unsigned)bin << shift;
+                const unsigned rank = sp->rank[wid];
+                const unsigned before = incl - sum;
+                // first lane whose inclusive count exceeds the rank (the last lane if none does:
+                // cannot happen while rank < number of elements under the prefix)
+                const unsigned hit = __ballot_sync(0xffffffffu, incl > rank);
+                const int owner = hit ? __ffs(hit) - 1 : 31;
+                if (lane == owner) {
+                    unsigned acc = before;
+                    int q = 0;
+                    for (; q < 7; ++q) {
+                        if (acc + c[q] > rank) break;
+                        acc += c[q];
+                    }
+                    sp->rank[wid] = rank - acc;
+                    sp->prefix[wid] |= (unsigned)(8 * lane + q) << shift;
+                }
             }
-            int g_n = 0;
-            for (int t = 0; t < 4; ++t) {
-                int g = 0;
-                for (; g < g_n; ++g) if (s_gprefix[g] == s_prefix[t]) break;
-                if (g == g_n) s_gprefix[g_n++] = s_prefix[t];
-                s_group[t] = g;
+            __syncthreads();
+            for (int i = tid; i < ng * 256; i += SEL_THREADS) gh[i] = 0u;
+            if (tid == 0) {
+                int g_n = 0;
+                for (int t = 0; t < T; ++t) {
+                    int g = 0;
+                    for (; g < g_n; ++g) if (sp->gprefix[g] == sp->prefix[t]) break;
+                    if (g == g_n) sp->gprefix[g_n++] = sp->prefix[t];
+                    sp->group[t] = g;
+                }
+                sp->ngroups = g_n;
+                sp->arrivals = 0;
+                if (pass == 3) {
+                    float v;
+                    if (mode == 0) v = key_float(sp->prefix[0]);
+                    else v = torch_lerp(key_float(sp->prefix[0]), key_float(sp->prefix[1]), sp->w_hi) -
+                             torch_lerp(key_float(sp->prefix[2]), key_float(sp->prefix[3]), sp->w_lo);
+                    out[b] = sp->nan ? nanf_() : v;
+                }
             }
-            s_ngroups = g_n;
         }
         __syncthreads();
-    }
-    if (tid == 0) {
-        const float q9 = torch_lerp(key_float(s_prefix[0]), key_float(s_prefix[1]), w9);
-        const float q1 = torch_lerp(key_float(s_prefix[2]), key_float(s_prefix[3]), w1);
-        out_range[b] = s_nan ? nanf_() : q9 - q1;
     }
 }
 
@@ -913,6 +1158,9 @@ static int check_io(const WcrLossIO *io, const WcrLossParams *p, bool bwd)
     if (p->loss_flags & WCR_LOSS_DEPTH)
         WCR_REQUIRE(io->masks && io->mask_idx && io->depth_gt && io->mask_h > 0 && io->mask_w > 0,
                     "wcr_weak_loss: 'depth' needs masks, mask_idx, depth_gt and the mask shape");
+    if (p->loss_flags & (WCR_LOSS_DEPTH | WCR_LOSS_Z_PATCH))
+        WCR_REQUIRE(io->select_ws, "wcr_weak_loss: 'depth' / 'z_pseudo_gt_patch' need select_ws "
+                                   "(wcr_select_ws_bytes(n) bytes)");
     if (p->loss_flags & WCR_LOSS_POSE_GROUND2)
         WCR_REQUIRE(io->gt_rot, "wcr_weak_loss: 'pose_ground2' needs the gt_rot workspace");
     return WCR_OK;
@@ -932,6 +1180,68 @@ extern "C" void wcr_z_loss_steps(float out[WCR_Z_LOSS_STEPS])
         out[i] = i < steps / 2 ? fmaf(step, (float)i, start) : fmaf(-step, (float)(steps - i - 1), end);
 }
 
+namespace wcr {
+struct SelWs { SelState *states; unsigned *hist; int *item_prefix; };
+static SelWs carve_select(void *ws, int n)
+{
+    char *p = (char *)ws;
+    SelWs w;
+    w.states = (SelState *)p; p += (size_t)n * sizeof(SelState);
+    w.hist = (unsigned *)p;   p += (size_t)n * 4096;
+    w.item_prefix = (int *)p;
+    return w;
+}
+static int run_select_passes(const SelWs &w, int n, const WcrImage *images, const uint8_t *masks, int mh,
+                             int mw, int mode, float *out, cudaStream_t st)
+{
+    const int grid = sm_count() * 8;
+    for (int pass = 0; pass < 4; ++pass) {
+        // the median follows one rank; two quantiles follow up to four once their prefixes part
+        if (mode == 0 || pass == 0)
+            sel_pass_kernel<1><<<grid, SEL_THREADS, 0, st>>>(w.states, w.item_prefix, n, w.hist, images, masks,
+                                                            mh, mw, pass, mode, out);
+        else
+            sel_pass_kernel<4><<<grid, SEL_THREADS, 0, st>>>(w.states, w.item_prefix, n, w.hist, images, masks,
+                                                            mh, mw, pass, mode, out);
+        WCR_CHECK_LAUNCH("sel_pass_kernel");
+    }
+    return WCR_OK;
+}
+// lower median of the depth patch under every box -> out_gt / out_inside
+static int launch_box_median(const WcrImage *images, const int32_t *img_off, int n_images, int n,
+                             const float *boxes, float *out_gt, int *out_inside, void *ws, cudaStream_t st)
+{
+    const SelWs w = carve_select(ws, n);
+    cudaError_t e = cudaMemsetAsync(w.hist, 0, (size_t)n * 4096, st);
+    if (e != cudaSuccess) { set_error("cudaMemsetAsync: %s", cudaGetErrorString(e)); return WCR_ELAUNCH; }
+    sel_init_median_kernel<<<1, 1024, 0, st>>>(images, img_off, n_images, n, boxes, out_gt, out_inside,
+                                              w.states, w.item_prefix);
+    WCR_CHECK_LAUNCH("sel_init_median_kernel");
+    return run_select_passes(w, n, images, nullptr, 0, 0, 0, out_gt, st);
+}
+// q90 - q10 of the depth under every box's mask -> out_range
+static int launch_mask_quantile(const WcrImage *images, const int32_t *img_off, int n_images, int n,
+                                const uint8_t *masks, int mh, int mw, const int32_t *mask_idx,
+                                const float *gt_boxes, float *out_range, float *stats, void *ws, cudaStream_t st)
+{
+    const SelWs w = carve_select(ws, n);
+    cudaError_t e = cudaMemsetAsync(ws, 0, (size_t)n * (sizeof(SelState) + 4096), st);
+    if (e != cudaSuccess) { set_error("cudaMemsetAsync: %s", cudaGetErrorString(e)); return WCR_ELAUNCH; }
+    const dim3 grid((mh * mw + SEL_COUNT_CHUNK - 1) / SEL_COUNT_CHUNK, n);
+    mask_count_kernel<<<grid, 256, 0, st>>>(masks, mh, mw, mask_idx, w.states);
+    WCR_CHECK_LAUNCH("mask_count_kernel");
+    sel_init_quantile_kernel<<<1, 1024, 0, st>>>(images, img_off, n_images, n, mh, mw, mask_idx, gt_boxes,
+                                                out_range, stats, w.states, w.item_prefix);
+    WCR_CHECK_LAUNCH("sel_init_quantile_kernel");
+    return run_select_passes(w, n, images, masks, mh, mw, 1, out_range, st);
+}
+}  // namespace wcr
+
+extern "C" int64_t wcr_select_ws_bytes(int n)
+{
+    return n < 0 ? 0 : (int64_t)n * (int64_t)(sizeof(wcr::SelState) + 4096) + (int64_t)(n + 1) * 4 + 256;
+}
+
 extern "C" int wcr_weak_loss_fwd(const WcrLossIO *h_io, const WcrLossParams *h_params, void *stream)
 {
     WCR_CHECK_DEVICE();
@@ -945,11 +1255,10 @@ extern "C" int wcr_weak_loss_fwd(const WcrLossIO *h_io, const WcrLossParams *h_p
         WCR_CHECK_LAUNCH("ground_rot_kernel");
     }
     if (h_io->n > 0 && (h_params->loss_flags & WCR_LOSS_DEPTH)) {
-        wcr::mask_quantile_kernel<<<h_io->n, 256, 0, st>>>(h_io->images, h_io->img_off, h_io->n_images,
-                                                           h_io->masks, h_io->mask_h, h_io->mask_w,
-                                                           h_io->mask_idx, h_io->gt_boxes, h_io->depth_gt,
-                                                           h_io->stats);
-        WCR_CHECK_LAUNCH("mask_quantile_kernel");
+        rc = wcr::launch_mask_quantile(h_io->images, h_io->img_off, h_io->n_images, h_io->n, h_io->masks,
+                                       h_io->mask_h, h_io->mask_w, h_io->mask_idx, h_io->gt_boxes,
+                                       h_io->depth_gt, h_io->stats, h_io->select_ws, st);
+        if (rc != WCR_OK) return rc;
     }
     if (h_io->n > 0) {
         wcr::ZSteps zs;
@@ -959,9 +1268,9 @@ extern "C" int wcr_weak_loss_fwd(const WcrLossIO *h_io, const WcrLossParams *h_p
     }
     if (h_io->n > 0 && (h_params->loss_flags & WCR_LOSS_Z_PATCH)) {
         // roi_heads.py:1010-1011: pseudo depth = median of the depth patch under the PROJECTED box
-        wcr::box_median_kernel<<<h_io->n, 256, 0, st>>>(h_io->images, h_io->img_off, h_io->n_images,
-                                                        h_io->proj, h_io->z_gt, h_io->z_inside);
-        WCR_CHECK_LAUNCH("box_median_kernel");
+        rc = wcr::launch_box_median(h_io->images, h_io->img_off, h_io->n_images, h_io->n, h_io->proj,
+                                    h_io->z_gt, h_io->z_inside, h_io->select_ws, st);
+        if (rc != WCR_OK) return rc;
         wcr::box_z_loss_kernel<<<(h_io->n_images + 127) / 128, 128, 0, st>>>(
             h_io->img_off, h_io->n_images, h_io->z_gt, h_io->z_inside, h_io->z_dec,
             h_io->terms + (size_t)(WCR_T_PSEUDO_Z - 1) * h_io->n, h_io->z_sign);
@@ -1090,11 +1399,9 @@ dim_loss_bwd_kernel(const float *__restrict__ mean, const float *__restrict__ st
     d_dims[idx] = grad[(size_t)k * n + i] * w * sgn(diff) / std_[idx];
 }
 
-// ---- pseudo_gt_z_box_loss (:575-610): lower median of the depth patch under each
-// predicted 2D box. One CTA per box: 4-pass radix select (8 bits per pass, shared
-// histogram) over the order-preserving integer image of the floats; the patch is
-// re-read from L2 each pass. torch.median returns the LOWER median (element
-// (cnt-1)/2 of the sorted patch) and NaN when the patch holds a NaN.
+// ---- order-preserving integer image of a float (the key of the radix select above).
+// pseudo_gt_z_box_loss (:575-610) takes the LOWER median (torch.median: element (cnt-1)/2
+// of the sorted patch) and NaN when the patch holds a NaN.
 __device__ __forceinline__ uint32_t float_key(float f)
 {
     const uint32_t u = __float_as_uint(f);
@@ -1103,95 +1410,6 @@ __device__ __forceinline__ uint32_t float_key(float f)
 __device__ __forceinline__ float key_float(uint32_t k)
 {
     return __uint_as_float((k & 0x80000000u) ? (k & 0x7fffffffu) : ~k);
-}
-
-__global__ void __launch_bounds__(256)
-box_median_kernel(const WcrImage *__restrict__ images, const int32_t *__restrict__ img_off, int n_images,
-                  const float *__restrict__ boxes /* [n][4] */, float *__restrict__ out_gt,
-                  int *__restrict__ out_inside)
-{
-    __shared__ unsigned hist[256];
-    __shared__ unsigned s_prefix, s_rank;
-    __shared__ int s_nan;
-    const int b = blockIdx.x;
-    const WcrImage im = images[image_of(img_off, n_images, b)];
-    // Boxes.clip((h, w)), area() > 0 on the clipped float box, then .long() slicing
-    const float x1 = clamp_keep_nan(boxes[4 * b + 0], 0.f, (float)im.W), y1 = clamp_keep_nan(boxes[4 * b + 1], 0.f, (float)im.H);
-    const float x2 = clamp_keep_nan(boxes[4 * b + 2], 0.f, (float)im.W), y2 = clamp_keep_nan(boxes[4 * b + 3], 0.f, (float)im.H);
-    const bool inside = (x2 - x1) * (y2 - y1) > 0.f;
-    if (x1 != x1 || y1 != y1 || x2 != x2 || y2 != y2) {
-        // a NaN box (cube behind the camera): the reference indexes with an undefined
-        // .long() here; defined as "no pseudo depth" (NaN, masked by the safe mean)
-        if (threadIdx.x == 0) { out_gt[b] = nanf_(); out_inside[b] = 0; }
-        return;
-    }
-    if (!inside) {
-        // fallback of :600-606: centre lookup of the CLIPPED box with the 10-px clamp
-        if (threadIdx.x == 0) {
-            out_gt[b] = depth_at(im, (x1 + x2) / 2.f, (y1 + y2) / 2.f);
-            out_inside[b] = 0;
-        }
-        return;
-    }
-    const int u0 = (int)x1, u1 = (int)x2, v0 = (int)y1, v1 = (int)y2;
-    const int ncols = u1 - u0, cnt = ncols * (v1 - v0);
-    if (cnt <= 0) {  // torch.median of an empty slice raises in the reference; NaN here
-        if (threadIdx.x == 0) { out_gt[b] = nanf_(); out_inside[b] = 1; }
-        return;
-    }
-    if (threadIdx.x == 0) { s_prefix = 0u; s_rank = (unsigned)((cnt - 1) / 2); s_nan = 0; }
-    const float inv_ncols = 1.0f / (float)ncols;
-    for (int pass = 0; pass < 4; ++pass) {
-        const int shift = 24 - 8 * pass;
-        hist[threadIdx.x] = 0u;
-        __syncthreads();
-        const unsigned prefix = s_prefix;
-        const unsigned himask = pass == 0 ? 0u : (0xffffffffu << (shift + 8));
-        // Depth values of a patch share their leading digits, so a plain shared-memory
-        // histogram serialises on one or two bins (2.5 ms for 1156 boxes, measured). Each
-        // thread run-length encodes its own stream instead: one atomic per change of bin.
-        unsigned last = 0xffffffffu, run = 0u;
-        // 4 independent loads in flight per thread (a clipped projected box can cover the
-        // whole image: one CTA then streams 307 k pixels per pass and is latency bound)
-        for (int i0 = threadIdx.x; i0 < cnt; i0 += 1024) {
-            float f[4];
-#pragma unroll
-            for (int q = 0; q < 4; ++q) {
-                const int idx = i0 + 256 * q;
-                int r = __float2int_rz(((float)idx + 0.5f) * inv_ncols), c = idx - r * ncols;
-                if (c < 0) { --r; c += ncols; } else if (c >= ncols) { ++r; c -= ncols; }
-                f[q] = idx < cnt ? __ldg(im.depth + (size_t)(v0 + r) * im.depth_pitch + u0 + c) : 0.f;
-            }
-#pragma unroll
-            for (int q = 0; q < 4; ++q) {
-                if (i0 + 256 * q >= cnt) break;
-                if (pass == 0 && f[q] != f[q]) s_nan = 1;
-                const uint32_t k = float_key(f[q]);
-                if ((k & himask) != prefix) continue;
-                const unsigned bin = (k >> shift) & 255u;
-                if (bin == last) { ++run; continue; }
-                if (run) atomicAdd(&hist[last], run);
-                last = bin; run = 1u;
-            }
-        }
-        if (run) atomicAdd(&hist[last], run);
-        __syncthreads();
-        if (threadIdx.x == 0) {
-            unsigned rank = s_rank, acc = 0u;
-            int bin = 0;
-            for (; bin < 255; ++bin) {
-                if (acc + hist[bin] > rank) break;
-                acc += hist[bin];
-            }
-            s_rank = rank - acc;
-            s_prefix = prefix | ((unsigned)bin << shift);
-        }
-        __syncthreads();
-    }
-    if (threadIdx.x == 0) {
-        out_gt[b] = s_nan ? nanf_() : key_float(s_prefix);
-        out_inside[b] = 1;
-    }
 }
 
 // Per image: the reference appends the in-image boxes' medians first and the
@@ -1262,15 +1480,17 @@ extern "C" int wcr_pseudo_z_point_loss(const WcrImage *images, const int32_t *im
 
 extern "C" int wcr_pseudo_z_box_loss(const WcrImage *images, const int32_t *img_off, int n_images, int n,
                                      const float *boxes, const float *pred_z, float *out_loss,
-                                     float *out_sign, float *ws_gt, int32_t *ws_inside, void *stream)
+                                     float *out_sign, float *ws_gt, int32_t *ws_inside, void *select_ws,
+                                     void *stream)
 {
     WCR_CHECK_DEVICE();
-    WCR_REQUIRE(images && img_off && boxes && pred_z && out_loss && out_sign && ws_gt && ws_inside,
+    WCR_REQUIRE(images && img_off && boxes && pred_z && out_loss && out_sign && ws_gt && ws_inside && select_ws,
                 "wcr_pseudo_z_box_loss: null pointer");
     WCR_REQUIRE(n_images >= 1 && n >= 0, "wcr_pseudo_z_box_loss: bad sizes");
     if (n == 0) return WCR_OK;
-    wcr::box_median_kernel<<<n, 256, 0, (cudaStream_t)stream>>>(images, img_off, n_images, boxes, ws_gt, ws_inside);
-    WCR_CHECK_LAUNCH("box_median_kernel");
+    int rc = wcr::launch_box_median(images, img_off, n_images, n, boxes, ws_gt, ws_inside, select_ws,
+                                    (cudaStream_t)stream);
+    if (rc != WCR_OK) return rc;
     wcr::box_z_loss_kernel<<<(n_images + 127) / 128, 128, 0, (cudaStream_t)stream>>>(
         img_off, n_images, ws_gt, ws_inside, pred_z, out_loss, out_sign);
     WCR_CHECK_LAUNCH("box_z_loss_kernel");

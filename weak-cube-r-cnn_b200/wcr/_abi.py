@@ -57,7 +57,8 @@ SIGNATURES = {
     "wcr_pseudo_z_point_loss": (c_int, [c_void_p, c_void_p, c_int, c_int, c_void_p, c_void_p, c_void_p,
                                         c_void_p, c_void_p]),
     "wcr_pseudo_z_box_loss": (c_int, [c_void_p, c_void_p, c_int, c_int, c_void_p, c_void_p, c_void_p,
-                                      c_void_p, c_void_p, c_void_p, c_void_p]),
+                                      c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
+    "wcr_select_ws_bytes": (c_i64, [c_int]),
     "wcr_l1_loss_bwd": (c_int, [c_void_p, c_void_p, c_int, c_void_p, c_void_p]),
     "wcr_dim_loss_fwd": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_void_p, c_void_p, c_void_p]),
     "wcr_dim_loss_bwd": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_void_p, c_void_p]),
@@ -150,7 +151,7 @@ _LOSS_IO_PTRS = ["deltas", "z_raw", "dims_raw", "pose", "uncert", "src_boxes", "
                  "z_dec", "z_gt", "z_inside", "z_sign"]
 
 
-_LOSS_IO_PTRS2 = ["mask_idx", "depth_gt", "gt_rot"]   # after the mask shape (tier-2 terms)
+_LOSS_IO_PTRS2 = ["mask_idx", "depth_gt", "gt_rot", "select_ws"]   # after the mask shape (tier-2 terms)
 
 
 class LossIO(ctypes.Structure):

@@ -114,6 +114,9 @@ class _Ctx:
             self.mask_hw = (int(m.shape[-2]), int(m.shape[-1]))
         if "pose_ground2" in cfg.loss_functions:
             t["gt_rot"] = torch.empty((B, 9), device=dev)
+        if "depth" in cfg.loss_functions or "z_pseudo_gt_patch" in cfg.loss_functions:
+            t["select_ws"] = torch.empty(int(_abi.load().wcr_select_ws_bytes(max(n, 1))), dtype=torch.uint8,
+                                         device=dev)
         self.t = t
         self.n_images = B
 
@@ -313,12 +316,14 @@ def pseudo_gt_z_box_loss(depth_maps, proposal_boxes, pred_z):
     gt = torch.empty((max(n, 1),), dtype=torch.float32, device=dev)
     inside = torch.empty((max(n, 1),), dtype=torch.int32, device=dev)
 
+    sel_ws = torch.empty(int(lib.wcr_select_ws_bytes(n)), dtype=torch.uint8, device=dev)
+
     def launch(pz, loss, sign):
         assert pz.numel() == n
         _abi.check(lib.wcr_pseudo_z_box_loss(shard.table.data_ptr(), off.data_ptr(), len(shard), n,
                                              bx.data_ptr(), pz.data_ptr(), loss.data_ptr(),
                                              sign.data_ptr(), gt.data_ptr(), inside.data_ptr(),
-                                             _abi.stream_ptr(dev)), "wcr_pseudo_z_box_loss")
+                                             sel_ws.data_ptr(), _abi.stream_ptr(dev)), "wcr_pseudo_z_box_loss")
     return _L1GatherFn.apply(pred_z, launch)
 
 
