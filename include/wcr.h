@@ -368,6 +368,49 @@ typedef struct WcrLossIO {
  * work-item prefix. Host function, no GPU needed. */
 int64_t wcr_select_ws_bytes(int n);
 
+/* ---- callers and data formats either side of the path ------------ */
+
+/* pytorch3d.transforms.rotation_6d_to_matrix as cube_head.py:174-176 calls it: Gram-Schmidt of
+ * two 3-vectors, rows b1, b2, b1 x b2. d6 [n][6] -> out_R [n][9]; backward: grad_R [n][9] -> d_d6. */
+int wcr_rotation_6d_fwd(const float *d6, int n, float *out_R, void *stream);
+int wcr_rotation_6d_bwd(const float *d6, const float *grad_R, int n, float *d_d6, void *stream);
+
+/* x[fg_inds, box_classes, ...] of roi_heads.py:823-840: src [n][C][k], classes [n] int64 ->
+ * out [n][k]; backward scatters grad_out into the zero-filled d_src [n][C][k]. */
+int wcr_class_gather_fwd(const float *src, int n, int C, int k, const int64_t *classes, float *out,
+                         void *stream);
+int wcr_class_gather_bwd(const float *grad_out, int n, int C, int k, const int64_t *classes,
+                         float *d_src, void *stream);
+
+/* Per-box constants of roi_heads.py:748-781, 810-814: Ks [B][9], im_scales_ratio [B],
+ * im_current_dims [B][2] -> K4 [n][4] = (fx fy cx cy) / ratio, virtual_to_real [n]
+ * (math_util.py:732-743; 1 when virtual_depth == 0), clamp [n][2] = im_current_dims. */
+int wcr_box_constants(const float *Ks, const float *im_scales_ratio, const float *im_current_dims,
+                      const int32_t *img_off, int n_images, int n, float virtual_focal,
+                      int virtual_depth, float *out_K4, float *out_v2r, float *out_clamp, void *stream);
+
+/* dataset_mapper.py:126-145: PIL Image.resize(size, Image.NEAREST) of the depth map (f32) and
+ * the ground mask (bool). wcr_pil_nearest_table reproduces PIL's source-index table for one axis
+ * (host function, no GPU needed: ImagingScaleAffine accumulates the coordinate in double);
+ * wcr_resize_nearest gathers through the two tables on the device. elem_size 4 or 1;
+ * pitches in elements. */
+void wcr_pil_nearest_table(int in_size, int out_size, int32_t *table);
+int wcr_resize_nearest(const void *src, int elem_size, int in_h, int in_w, int64_t src_pitch,
+                       const int32_t *xtab, const int32_t *ytab, void *dst, int out_h, int out_w,
+                       int64_t dst_pitch, void *stream);
+
+/* ---- 3D IoU ------------------------------------------------------------ */
+
+/* pytorch3d.ops.box3d_overlap as iou_3d (ProposalNetwork/utils/utils.py:189-205), roi_heads.py:942
+ * and omni3d_evaluation.py:106-166 call it: exact intersection volume and IoU of every pair of
+ * oriented boxes. boxes1 [N][8][3], boxes2 [M][8][3] corner lists in pytorch3d's corner order
+ * (what Cubes.get_all_corners returns); out_vol, out_iou [N][M]. */
+int wcr_box3d_overlap(const float *boxes1, int N, const float *boxes2, int M, float *out_vol,
+                      float *out_iou, void *stream);
+/* volume of each box [n][8][3] -> out_vol [n] (pytorch3d raises on boxes of ~zero volume; the
+ * Python shim uses this for the same check). */
+int wcr_box3d_volume(const float *boxes, int n, float *out_vol, void *stream);
+
 /* sizeof() of the ABI structs as the library was compiled, so a binding can verify its
  * mirror: 0 WcrImage, 1 WcrBox, 2 WcrSampleParams, 3 WcrScoreParams, 4 WcrLossParams,
  * 5 WcrLossIO; anything else -> 0. Host function, no GPU needed. */

@@ -63,6 +63,17 @@ SIGNATURES = {
     "wcr_dim_loss_fwd": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_void_p, c_void_p, c_void_p]),
     "wcr_dim_loss_bwd": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_void_p, c_void_p]),
     "wcr_z_loss_steps": (None, [c_void_p]),
+    "wcr_box3d_overlap": (c_int, [c_void_p, c_int, c_void_p, c_int, c_void_p, c_void_p, c_void_p]),
+    "wcr_box3d_volume": (c_int, [c_void_p, c_int, c_void_p, c_void_p]),
+    "wcr_rotation_6d_fwd": (c_int, [c_void_p, c_int, c_void_p, c_void_p]),
+    "wcr_rotation_6d_bwd": (c_int, [c_void_p, c_void_p, c_int, c_void_p, c_void_p]),
+    "wcr_class_gather_fwd": (c_int, [c_void_p, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p]),
+    "wcr_class_gather_bwd": (c_int, [c_void_p, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p]),
+    "wcr_box_constants": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_float, c_int,
+                                  c_void_p, c_void_p, c_void_p, c_void_p]),
+    "wcr_pil_nearest_table": (None, [c_int, c_int, c_void_p]),
+    "wcr_resize_nearest": (c_int, [c_void_p, c_int, c_int, c_int, c_i64, c_void_p, c_void_p, c_void_p,
+                                   c_int, c_int, c_i64, c_void_p]),
     "wcr_sizeof": (c_i64, [c_int]),
 }
 _lib = None

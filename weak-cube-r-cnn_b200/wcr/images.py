@@ -34,6 +34,9 @@ def _iter_images(maps):
             yield t[:h, :w]
         return
     for t in maps:
+        if t is None:          # no ground map for this image (no_ground_idx.csv): same as the (1,1) dummy
+            yield None
+            continue
         while t.dim() > 2:
             t = t[0]
         yield t

@@ -134,3 +134,33 @@ def mask_iou(segmentation_mask, bube_mask):
 def mod_mask_iou(segmentation_mask, bube_mask):
     """intersection**5 / union (utils.py:236-245)."""
     return _mask_iou(segmentation_mask, bube_mask, 1)
+
+
+def box3d_overlap(boxes1: torch.Tensor, boxes2: torch.Tensor, eps: float = 1e-4):
+    """pytorch3d.ops.box3d_overlap: (N,8,3), (M,8,3) corner lists in pytorch3d's corner order
+    -> (vol (N,M), iou (N,M)). Exact clipping on the device (csrc/iou3d.cu). Like pytorch3d it
+    raises ``ValueError`` for a box of ~zero volume (one small host read)."""
+    _abi.require_cuda(boxes1, boxes2)
+    lib = _abi.load()
+    dev = boxes1.device
+    b1, b2 = _f32c(boxes1, dev).reshape(-1, 8, 3), _f32c(boxes2, dev).reshape(-1, 8, 3)
+    N, M = b1.shape[0], b2.shape[0]
+    both = torch.cat((b1, b2))
+    vols = torch.empty((N + M,), dtype=torch.float32, device=dev)
+    _abi.check(lib.wcr_box3d_volume(both.data_ptr(), N + M, vols.data_ptr(), _abi.stream_ptr(dev)),
+               "wcr_box3d_volume")
+    if N + M and bool((vols < eps).any()):
+        raise ValueError("Planes have zero areas")          # pytorch3d _check_nonzero's message
+    vol = torch.empty((N, M), dtype=torch.float32, device=dev)
+    iou = torch.empty((N, M), dtype=torch.float32, device=dev)
+    _abi.check(lib.wcr_box3d_overlap(b1.data_ptr(), N, b2.data_ptr(), M, vol.data_ptr(), iou.data_ptr(),
+                                     _abi.stream_ptr(dev)), "wcr_box3d_overlap")
+    return vol, iou
+
+
+def iou_3d(gt_cube, proposal_cubes):
+    """utils.py:189-205: IoU of ONE GT cube with every proposal cube -> (P,)."""
+    gt_corners = gt_cube.get_all_corners()[0]
+    proposal_corners = proposal_cubes.get_all_corners()[0]
+    vol, iou = box3d_overlap(gt_corners, proposal_corners)
+    return iou[0]
