@@ -282,10 +282,13 @@ int wcr_vectorized_linspace(const float *start, const float *end, int M, int ste
                                      the object's mask vs the depth extent of the cube corners) */
 #define WCR_LOSS_POSE_GROUND2 256 /* 'pose_ground2': normal_to_rotation + so3_relative_angle, :686-696,
                                      :997-1007; overrides 'pose_ground' in slot WCR_T_NORMAL */
+#define WCR_LOSS_SEG        512   /* 'segmentation': segment_loss, :420-443 (soft convex-hull raster of the
+                                     clamped projected corners vs the object mask, focal loss; the raster
+                                     is differentiable in the hull vertices, utils.py:479-483) */
 
 /* order of the scalar outputs (keys of the reference's loss dict, prefix 'Cube/') */
 enum { WCR_T_UNCERT = 0, WCR_T_IOU, WCR_T_POSE, WCR_T_NORMAL, WCR_T_PSEUDO_Z,
-       WCR_T_DIMS_W, WCR_T_DIMS_H, WCR_T_DIMS_L, WCR_T_Z, WCR_T_DEPTH, WCR_LOSS_TERMS };
+       WCR_T_DIMS_W, WCR_T_DIMS_H, WCR_T_DIMS_L, WCR_T_Z, WCR_T_DEPTH, WCR_T_SEG, WCR_LOSS_TERMS };
 /* slots of WcrLossIO.stats beyond the per-term valid counts */
 enum { WCR_STAT_POSE = 16, WCR_STAT_FAIL = 17,
        WCR_STAT_TRACE_ERR = 18,  /* != 0: a relative rotation of 'pose_ground2' has its trace outside
@@ -305,6 +308,7 @@ typedef struct WcrLossParams {
     float   use_confidence;   /* cfg USE_CONFIDENCE; 0 disables uncertainty scaling    */
     float   w_3d, w_iou, w_pose, w_normal, w_z, w_dims;   /* LOSS_W_* (config.py:119-127) */
     float   w_depth;          /* LOSS_W_DEPTH (config.py:127)                          */
+    float   w_seg;            /* LOSS_W_SEG (config.py:124)                            */
 } WcrLossParams;
 
 /* Every per-box array is indexed by foreground box, boxes of one image contiguous
@@ -349,7 +353,7 @@ typedef struct WcrLossIO {
     float   *z_gt;            /* [n] per-box pseudo depth (median / fallback)  */
     int32_t *z_inside;        /* [n] 1 = box has area inside the image         */
     float   *z_sign;          /* [n] sign(cube_z - pseudo depth), by position  */
-    /* 'depth' only (NULL otherwise): per-object masks as the reference's masks_all_images
+    /* 'depth' and 'segmentation' (NULL otherwise): per-object masks as the reference's masks_all_images
      * (roi_heads.py:273), dense, non-zero == object. Every mask must have the shape of the
      * depth map of the image its boxes belong to (the reference's align_corners bilinear
      * resize, :672, is the identity then); a mismatch sets stats[WCR_STAT_SHAPE_ERR]. */
@@ -361,12 +365,25 @@ typedef struct WcrLossIO {
     float   *gt_rot;          /* [n_images][9] workspace: normal_to_rotation per image */
     /* 'z_pseudo_gt_patch' and 'depth' (NULL otherwise): wcr_select_ws_bytes(n) bytes, 256-byte aligned */
     void    *select_ws;
+    /* 'segmentation', backward only: [n][16] d raw_seg / d (clamped projected corners) */
+    float   *seg_dcorner;
 } WcrLossIO;
 
 /* Workspace of the per-box order-statistic kernels (median of a depth patch, quantiles of
  * the depth under a mask): per box a 128-byte state and a 4 x 256-bin histogram, plus the
  * work-item prefix. Host function, no GPU needed. */
 int64_t wcr_select_ws_bytes(int n);
+
+/* ROIHeads3DScore.segment_loss (roi_heads.py:420-443), loss='focal': per box the mean over the
+ * mask's pixels of sigmoid_focal_loss(inputs = object mask as 0/1, targets = convex_hull raster of
+ * the 8 given corners (utils.py:410-493)). masks [n_masks][mask_h][mask_w] u8, mask_idx [n],
+ * corners [n][8][2] (already clamped as roi_heads.py:950-953 does) -> out_loss [n].
+ * Backward: d_corners [n][8][2] = d out_loss[i] / d corners[i] (the soft raster is differentiable
+ * in the hull vertices; ties at val == 0 / val == 1 split in half like torch.max / torch.min). */
+int wcr_segment_loss_fwd(const uint8_t *masks, int mask_h, int mask_w, const int32_t *mask_idx,
+                         const float *corners, int n, float *out_loss, void *stream);
+int wcr_segment_loss_bwd(const uint8_t *masks, int mask_h, int mask_w, const int32_t *mask_idx,
+                         const float *corners, int n, float *d_corners, void *stream);
 
 /* ---- callers and data formats either side of the path ------------ */
 

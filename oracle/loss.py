@@ -307,7 +307,7 @@ def weak_loss(cfg: LossConfig, deltas, z_raw, dims_raw, pose, uncert, *, src_box
         from . import loss_tier2 as t2
         bube = torch.stack([t2.clamp_bube_corners(bube_corners(box6[i:i + 1], R[i:i + 1], K4[i:i + 1],
                                                                clamp[i:i + 1])[0], clamp[i]) for i in range(n)])
-        terms["seg"] = t2.segment_loss(gt_masks, bube.detach(), at_which_mask_idx)
+        terms["seg"] = t2.segment_loss(gt_masks, bube, at_which_mask_idx)
     if "z" in lf:                    # :1019-1021
         from . import loss_tier2 as t2
         terms["z"] = t2.z_loss(gt_boxes, box6, R, K4, clamp.float(), proj)

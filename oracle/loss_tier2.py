@@ -57,16 +57,76 @@ def clamp_bube_corners(bube, clamp):
     return torch.stack((x, y), dim=-1)
 
 
+def hull_indices(points):
+    """jarvis_march (utils.py:410-454) on float32 values, returning WHICH points form the hull
+    (in the reference's flipped order) and the duplicate bump added to them, so that the hull can
+    be rebuilt differentiably as (points + bump)[idx]. None when the march does not close within
+    len(points) steps (the reference would loop forever)."""
+    f = np.float32
+    pts = np.asarray(points, dtype=f).copy()
+    n = len(pts)
+    dup = sorted({i for i in range(n - 1) for j in range(i + 1, n) if np.all(pts[i] == pts[j])})
+    bump = np.zeros_like(pts)
+    for k, d in enumerate(dup):
+        bump[d] += f(k + 1)
+    pts = (pts + bump).astype(f)
+    min_x = pts[:, 0].min()
+    cand = np.nonzero(pts[:, 0] == min_x)[0]
+    index = int(cand[np.argmax(pts[cand][:, 1])]) if len(cand) > 1 else int(cand[0])
+
+    def direction(p1, p2, p3):
+        return f(f(f(p2[0] - p1[0]) * f(p3[1] - p1[1])) - f(f(p2[1] - p1[1]) * f(p3[0] - p1[0])))
+
+    def dist(p1, p2):
+        return f(f(f(p2[0] - p1[0]) ** 2) + f(f(p2[1] - p1[1]) ** 2))
+
+    l, result = index, [index]
+    for _ in range(n + 1):
+        q = (l + 1) % n
+        for i in range(n):
+            if i == l:
+                continue
+            d = direction(pts[l], pts[i], pts[q])
+            if d > 0 or (d == 0 and dist(pts[i], pts[l]) > dist(pts[q], pts[l])):
+                q = i
+        l = q
+        if l == index:
+            return result[::-1], bump
+        result.append(q)
+    return None, bump
+
+
+def fill_polygon_torch(H, W, hull):
+    """utils.py:456-488, differentiable in the hull vertices exactly like the reference."""
+    Y, X = torch.meshgrid(torch.arange(H), torch.arange(W), indexing="ij")
+    gx, gy = X.flatten().float(), Y.flatten().float()
+    new_mask = torch.ones(H, W)
+    zeros, ones = torch.zeros(H, W), torch.ones(H, W)
+    for i in range(len(hull)):
+        v1, v2 = hull[i], hull[(i + 1) % len(hull)]
+        e = v2 - v1
+        points = (gx - v1[0]) * e[1] - (gy - v1[1]) * e[0]
+        new_mask = new_mask * torch.min(torch.max(points.view(H, W), zeros), ones)
+    return new_mask
+
+
+def convex_hull_torch(H, W, coords):
+    idx, bump = hull_indices(coords.detach().numpy())
+    if idx is None:
+        return torch.zeros(H, W)
+    return fill_polygon_torch(H, W, (coords + torch.from_numpy(bump))[idx])
+
+
 def segment_loss(gt_mask, bube_corners, at_which_mask_idx, loss="focal"):
-    """gt_mask: list of (1, H, W) bool; bube_corners (n, 8, 2) already clamped."""
+    """gt_mask: list of (1, H, W) bool; bube_corners (n, 8, 2) already clamped (roi_heads.py
+    :948-954); differentiable w.r.t. the corners through the soft raster, as in the reference."""
     n = len(bube_corners)
     y_hat, y = [], []
     H, W = gt_mask[0].squeeze().shape
     for i in range(n):
         gt_i = gt_mask[at_which_mask_idx[i]][0]
-        raster = ohull.convex_hull((H, W), np.asarray(bube_corners[i], dtype=np.float32))
         y.append((gt_i * 1.0).float())
-        y_hat.append(torch.from_numpy(np.asarray(raster, dtype=np.float32)))
+        y_hat.append(convex_hull_torch(H, W, bube_corners[i]))
     y, y_hat = torch.stack(y), torch.stack(y_hat)
     if loss == "bce":
         return F.binary_cross_entropy_with_logits(y, y_hat, reduction="none").mean((1, 2))

@@ -235,6 +235,22 @@ def golden_tier2():
         print("tier2", idx, {k: round(float(v), 5) for k, v in L.items()})
 
 
+def golden_tier2_seg():
+    """'segmentation' (segment_loss through the reference's convex_hull raster, values and the
+    autograd gradients that flow through the soft raster)."""
+    for idx, (seed, nb) in enumerate([(0, [3, 1, 5, 2]), (6, [4, 7])]):
+        H, W = 96, 128
+        inp = li.add_masks(li.make_loss_inputs(seed, nb, H=H, W=W), seed, H=H, W=W)
+        cfg = ol.LossConfig(loss_functions=("segmentation", "iou"), use_confidence=1.0)
+        L, pb, grads = li.run_with_grads(ref_loss.reference_weak_loss, cfg, inp)
+        out = {"seed": seed, "nb": np.asarray(nb), "H": H, "W": W, "use_confidence": 1.0}
+        out.update({"loss:" + k: v.numpy() for k, v in L.items()})
+        out.update({"grad:" + k: v.numpy() for k, v in grads.items()})
+        out["box:raw_seg"] = pb["raw_seg"].numpy()
+        np.savez_compressed(os.path.join(HERE, f"tier2seg_{idx}.npz"), **out)
+        print("tier2seg", idx, {k: round(float(v), 6) for k, v in L.items()})
+
+
 if __name__ == "__main__":
     assert refshim.available(), "needs /root/reference"
     golden_ground()
@@ -244,3 +260,4 @@ if __name__ == "__main__":
     golden_replay()
     golden_loss()
     golden_tier2()
+    golden_tier2_seg()

@@ -41,7 +41,7 @@ def test_struct_sizes_match_header():
     assert lib.wcr_sizeof(0) == IMAGE_DTYPE.itemsize and lib.wcr_sizeof(1) == BOX_DTYPE.itemsize
     assert lib.wcr_sizeof(2) == ctypes.sizeof(_abi.SampleParams)
     assert lib.wcr_sizeof(3) == ctypes.sizeof(_abi.ScoreParams)
-    assert lib.wcr_sizeof(4) == ctypes.sizeof(_abi.LossParams) == 44
+    assert lib.wcr_sizeof(4) == ctypes.sizeof(_abi.LossParams) == 48
     assert lib.wcr_sizeof(5) == ctypes.sizeof(_abi.LossIO)
     assert lib.wcr_sizeof(99) == 0
 

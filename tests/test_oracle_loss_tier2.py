@@ -44,6 +44,21 @@ def test_tier2_oracle_matches_reference_live(seed, nb, conf):
 
 
 @pytest.mark.skipif(not refshim.available(), reason="needs /root/reference")
+@pytest.mark.parametrize("seed,nb", [(0, [3, 1, 5, 2]), (6, [4, 7])])
+def test_segment_loss_oracle_matches_reference_live(seed, nb):
+    """The soft raster is differentiable in the reference (utils.py:479-483): values AND gradients."""
+    from oracle import ref_loss
+    H, W = 96, 128
+    inp = _inputs(seed, nb, H, W)
+    cfg = ol.LossConfig(loss_functions=("segmentation",), use_confidence=1.0)
+    La, pa, ga = li.run_with_grads(ol.weak_loss, cfg, inp)
+    Lb, pb, gb = li.run_with_grads(ref_loss.reference_weak_loss, cfg, inp)
+    assert torch.allclose(pa["raw_seg"], pb["raw_seg"], rtol=1e-6, atol=1e-8)
+    assert any(float(g.abs().max()) > 0 for g in gb.values())
+    _close(La, ga, Lb, gb)
+
+
+@pytest.mark.skipif(not refshim.available(), reason="needs /root/reference")
 def test_normal_to_rotation_and_linspace_quirks():
     head = refshim.roi_head_instance()
     g = torch.Generator().manual_seed(1)
@@ -64,4 +79,17 @@ def test_tier2_oracle_matches_reference_golden(path):
     gb = {k[5:]: torch.tensor(z[k]) for k in z.files if k.startswith("grad:")}
     for k in ("raw_z", "raw_depth", "raw_normal_vec"):
         assert np.allclose(pa[k].numpy(), z["box:" + k], rtol=1e-6, atol=1e-7), k
+    _close(La, ga, Lb, gb)
+
+
+@pytest.mark.parametrize("path", sorted(glob.glob(os.path.join(GOLDEN, "tier2seg_*.npz"))))
+def test_segment_loss_oracle_matches_reference_golden(path):
+    z = np.load(path, allow_pickle=False)
+    nb = [int(v) for v in z["nb"]]
+    inp = _inputs(int(z["seed"]), nb, int(z["H"]), int(z["W"]))
+    cfg = ol.LossConfig(loss_functions=("segmentation", "iou"), use_confidence=float(z["use_confidence"]))
+    La, pa, ga = li.run_with_grads(ol.weak_loss, cfg, inp)
+    Lb = {k[5:]: torch.tensor(z[k]) for k in z.files if k.startswith("loss:")}
+    gb = {k[5:]: torch.tensor(z[k]) for k in z.files if k.startswith("grad:")}
+    assert np.allclose(pa["raw_seg"].numpy(), z["box:raw_seg"], rtol=1e-6, atol=1e-8)
     _close(La, ga, Lb, gb)

@@ -14,6 +14,7 @@
 #include <math.h>
 #include <string.h>
 #include "cube_math.cuh"
+#include "hull.cuh"
 
 namespace wcr {
 
@@ -346,6 +347,7 @@ __device__ __forceinline__ float term_weight(const WcrLossParams &P, int t)
     case WCR_T_PSEUDO_Z: return P.w_z * P.w_3d;
     case WCR_T_Z: return P.w_z * P.w_3d;              // roi_heads.py:1125
     case WCR_T_DEPTH: return P.w_depth * P.w_3d;      // :1143
+    case WCR_T_SEG: return P.w_seg * P.w_3d;          // :1121
     default: return P.w_dims * P.w_3d;
     }
 }
@@ -360,6 +362,7 @@ __device__ __forceinline__ bool term_enabled(const WcrLossParams &P, int t)
     case WCR_T_PSEUDO_Z: return P.loss_flags & (WCR_LOSS_Z_CENTER | WCR_LOSS_Z_PATCH);
     case WCR_T_Z: return P.loss_flags & WCR_LOSS_Z_SEARCH;
     case WCR_T_DEPTH: return P.loss_flags & WCR_LOSS_DEPTH;
+    case WCR_T_SEG: return P.loss_flags & WCR_LOSS_SEG;
     default: return P.loss_flags & WCR_LOSS_DIMS;
     }
 }
@@ -883,6 +886,174 @@ sel_pass_kernel(SelState *__restrict__ states, const int *__restrict__ item_pref
     }
 }
 
+// ---- 'segmentation': segment_loss (roi_heads.py:420-443) ------------------------------------------
+// y_hat = convex_hull(mask shape, clamped projected corners): Jarvis march, then the SOFT raster
+// prod_e min(max(val_e, 0), 1) (utils.py:456-488), which is differentiable in the hull vertices;
+// loss_i = mean over pixels of sigmoid_focal_loss(inputs = GT mask as 0/1 "logits", targets =
+// raster) -- the argument order of the reference, kept. The reference builds an (n, H, W) raster
+// with ~8 full-image torch ops per edge per box; here one CTA per box evaluates every pixel once
+// (early exit at the first edge with val < 0), forward and backward share the code. Gradient
+// conventions of autograd: binary max/min split ties (val == 0 or val == 1 exactly -- common,
+// the clamped corners and the pixel centres are integers) in half.
+struct FocalConst { float p[2], c[2]; };   // sigmoid(x), log(1 + exp(-x)) for x = 0, 1
+
+__device__ __forceinline__ FocalConst focal_const()
+{
+    FocalConst k;
+    k.p[0] = 0.5f; k.p[1] = 1.f / (1.f + expf(-1.f));
+    k.c[0] = logf(2.f); k.c[1] = logf(1.f + expf(-1.f));
+    return k;
+}
+// torchvision sigmoid_focal_loss(inputs = x in {0, 1}, targets = t), alpha 0.25, gamma 2; optionally d/dt
+__device__ __forceinline__ float focal_xt(const FocalConst &k, int x, float t, float *ddt)
+{
+    const float p = k.p[x], xf = (float)x;
+    const float ce = (1.f - t) * xf + k.c[x];                  // BCE-with-logits, max_val = 0 for x >= 0
+    const float p_t = p * t + (1.f - p) * (1.f - t);
+    const float m = 1.f - p_t;
+    const float loss = ce * (m * m);
+    const float alpha_t = 0.25f * t + (1.f - 0.25f) * (1.f - t);
+    if (ddt) *ddt = -0.5f * loss + alpha_t * (-xf * (m * m) + ce * (2.f * m) * (1.f - 2.f * p));
+    return alpha_t * loss;
+}
+
+template <bool BWD>
+__global__ void __launch_bounds__(256)
+seg_loss_kernel(const WcrLossIO io, const WcrLossParams P, const float *__restrict__ corners_in /* [n][16] or NULL */,
+                float *__restrict__ out_raw /* [n] */, float *__restrict__ out_dcorner /* [n][16] */)
+{
+    __shared__ float s_hx[8], s_hy[8];
+    __shared__ int s_ci[8], s_m;
+    __shared__ double s_red[8];
+    __shared__ float s_g[8][16];
+    const int i = blockIdx.x, tid = threadIdx.x;
+    const int H = io.mask_h, W = io.mask_w;
+    if (tid == 0) {
+        float px[8], py[8], hx[8], hy[8];
+        bool bad = false;
+        if (corners_in) {           // stand-alone segment_loss: the caller's (already clamped) corners
+#pragma unroll
+            for (int c = 0; c < 8; ++c) { px[c] = corners_in[16 * (size_t)i + 2 * c]; py[c] = corners_in[16 * (size_t)i + 2 * c + 1]; }
+        } else {
+            const Decoded d = decode_box(io, P, i);
+            float lo0, hi0, lo1, hi1, cxy[16];
+            clamp_bounds(io.clamp[2 * i], lo0, hi0);
+            clamp_bounds(io.clamp[2 * i + 1], lo1, hi1);
+            project_cube(d.cube, d.K, lo0, hi0, lo1, hi1, cxy);
+            // second clamp, roi_heads.py:951-952: x into [0, int(c0 - 1)], y into [0, int(c1 - 1)]
+            const float mx = (float)(int)(io.clamp[2 * i] - 1.f), my = (float)(int)(io.clamp[2 * i + 1] - 1.f);
+#pragma unroll
+            for (int c = 0; c < 8; ++c) {
+                px[c] = clamp_keep_nan(cxy[2 * c], 0.f, mx);
+                py[c] = clamp_keep_nan(cxy[2 * c + 1], 0.f, my);
+            }
+        }
+#pragma unroll
+        for (int c = 0; c < 8; ++c) bad |= px[c] != px[c] || py[c] != py[c];
+        int m = -1;
+        if (!bad) m = jarvis_march(Strided{px, 1}, Strided{py, 1}, 8, Strided{hx, 1}, Strided{hy, 1});
+        s_m = m;
+        for (int v = 0; v < max(m, 0); ++v) {
+            s_hx[v] = hx[v]; s_hy[v] = hy[v];
+            int ci = 0;
+            for (int c = 7; c >= 0; --c) if (px[c] == hx[v] && py[c] == hy[v]) ci = c;   // px/py carry the bump
+            s_ci[v] = ci;
+        }
+    }
+    __syncthreads();
+    const int m = s_m;
+    const FocalConst fk = focal_const();
+    const uint8_t *mask = io.masks + (size_t)io.mask_idx[i] * H * W;
+    const int N = H * W;
+    float v1x[8], v1y[8], ex[8], ey[8];
+#pragma unroll
+    for (int e = 0; e < 8; ++e) {
+        const int e2 = e + 1 < m ? e + 1 : 0;
+        v1x[e] = e < m ? s_hx[e] : 0.f; v1y[e] = e < m ? s_hy[e] : 0.f;
+        ex[e] = e < m ? s_hx[e2] - s_hx[e] : 0.f; ey[e] = e < m ? s_hy[e2] - s_hy[e] : 0.f;
+    }
+    double acc = 0.0;
+    float g[16];
+#pragma unroll
+    for (int k = 0; k < 16; ++k) g[k] = 0.f;
+    for (int idx = tid; idx < N; idx += blockDim.x) {
+        const int y = idx / W, x = idx - y * W;
+        const int xm = mask[idx] != 0;
+        const float X = (float)x, Y = (float)y;
+        float t = m > 0 ? 1.f : 0.f, il[8];
+        bool dead = m <= 0;
+        int zeros = 0, e0 = 0;
+        float vmin = 3.0e38f;
+#pragma unroll
+        for (int e = 0; e < 8; ++e) {
+            if (e >= m || dead) { il[e] = 1.f; continue; }
+            const float val = (X - v1x[e]) * ey[e] - (Y - v1y[e]) * ex[e];
+            if (!(val >= 0.f)) { dead = true; t = 0.f; il[e] = 0.f; continue; }    // val < 0 (or NaN): outside
+            if (val == 0.f) { ++zeros; e0 = e; }
+            vmin = fminf(vmin, val);
+            il[e] = fminf(val, 1.f);
+            t = t * il[e];
+        }
+        if (!BWD) {
+            acc += (double)focal_xt(fk, xm, t, nullptr);
+        } else if (!dead && zeros <= 1 && vmin <= 1.f) {
+            float ddt;
+            focal_xt(fk, xm, t, &ddt);
+            const float up = ddt / (float)N;
+#pragma unroll
+            for (int e = 0; e < 8; ++e) {
+                if (e >= m) continue;
+                const float val = (X - v1x[e]) * ey[e] - (Y - v1y[e]) * ex[e];
+                float w;                                   // d clamp(val, 0, 1) / d val with torch's tie split
+                if (zeros == 1) w = e == e0 ? 0.5f : 0.f;  // every other factor multiplies a zero
+                else w = val < 1.f ? 1.f : (val == 1.f ? 0.5f : 0.f);
+                if (w == 0.f) continue;
+                float others = 1.f;
+#pragma unroll
+                for (int o = 0; o < 8; ++o) if (o < m && o != e) others *= il[o];
+                const float ge = up * w * others;
+                const int e2 = e + 1 < m ? e + 1 : 0;
+                const float v2x = v1x[e] + ex[e], v2y = v1y[e] + ey[e];
+                // val = (X - v1x)(v2y - v1y) - (Y - v1y)(v2x - v1x)
+                g[2 * e] += ge * (Y - v2y);      g[2 * e + 1] += ge * (v2x - X);
+                g[2 * e2] += ge * -(Y - v1y[e]); g[2 * e2 + 1] += ge * (X - v1x[e]);
+            }
+        }
+    }
+    const int lane = tid & 31, wid = tid >> 5;
+    if (!BWD) {
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+        if (lane == 0) s_red[wid] = acc;
+        __syncthreads();
+        if (tid == 0) {
+            double s = 0.0;
+            for (int w = 0; w < 8; ++w) s += s_red[w];
+            out_raw[i] = (float)(s / (double)N);
+        }
+    } else {
+#pragma unroll
+        for (int k = 0; k < 16; ++k) {
+            float v = g[k];
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+            if (lane == 0) s_g[wid][k] = v;
+        }
+        __syncthreads();
+        if (tid < 16) {
+            float out = 0.f;
+            const int c = tid >> 1, ax = tid & 1;           // gradient of corner c, axis ax
+            for (int v = 0; v < m; ++v)
+                if (s_ci[v] == c) {
+                    float s = 0.f;
+                    for (int w = 0; w < 8; ++w) s += s_g[w][2 * v + ax];
+                    out += s;
+                }
+            out_dcorner[16 * (size_t)i + tid] = out;
+        }
+    }
+}
+
 // --------------------------------------------------------------- backward --
 // upstream coefficient of the per-box scaled loss l_{t,i} = raw_{t,i} * sf_i:
 //   d(total)/d(l_{t,i}) = g_t * w_t * [l finite] / n_valid_t      (safe mean, :1307-1315)
@@ -926,6 +1097,39 @@ loss_pose_bwd_kernel(const WcrLossIO io, const WcrLossParams P)
 #pragma unroll
         for (int t = 0; t < 9; ++t) io.d_R_pose[9 * (size_t)(b0 + i) + t] = g[t];
     }
+}
+
+// Gradient gp of a loss w.r.t. ONE projected coordinate (x if isx else y) of corner c, pushed back
+// through p = (f * A + c0 * Z) / Z, corner = R (s * h) + centre, centre = z * ((cube_xy - c0) / f, 1).
+__device__ __forceinline__ void corner_backprop(const Decoded &d, int c, bool isx, float gp, float Xc, float Yc,
+                                                float Zc, float hx, float hy, float hz, float *dR, float *dl,
+                                                float &dcx, float &dcy, float &dz)
+{
+    // p = (f*A + c0*Z)/Z : dA = gp*f/Z ; dZ = gp*(c0/Z - num/Z^2)
+    const float f = isx ? d.K.fx : d.K.fy, c0 = isx ? d.K.cx : d.K.cy;
+    const float Av = isx ? Xc : Yc;
+    const float num = fmaf(c0, Zc, f * Av);
+    const float dA = gp * f / Zc;
+    const float dZ = gp * c0 / Zc - gp * num / (Zc * Zc);
+    float sx, sy, sz;
+    corner_signs(c, sx, sy, sz);
+    const float l[3] = {sx * hx, sy * hy, sz * hz};
+    const int ra = isx ? 0 : 1;                     // row of R feeding A
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+        dR[3 * ra + k] += dA * l[k];
+        dR[6 + k] += dZ * l[k];
+        dl[k] += (d.R[3 * ra + k] * dA + d.R[6 + k] * dZ) * (k == 0 ? sx : (k == 1 ? sy : sz));
+    }
+    // centre: cube[0] or cube[1] gets dA, cube[2] gets dZ
+    if (isx) {   // x3d = z*(cube_x-cx)/fx
+        dcx += dA * d.z / d.K.fx;
+        dz += dA * (d.cube_x - d.K.cx) / d.K.fx;
+    } else {
+        dcy += dA * d.z / d.K.fy;
+        dz += dA * (d.cube_y - d.K.cy) / d.K.fy;
+    }
+    dz += dZ;
 }
 
 __global__ void __launch_bounds__(128)
@@ -990,39 +1194,43 @@ loss_box_bwd_kernel(const WcrLossIO io, const WcrLossParams P)
                 const float pv = isx ? px[c] : py[c];
                 const float lo = isx ? lo0 : lo1, hi = isx ? hi0 : hi1;
                 if (!(pv >= lo && pv <= hi)) continue;          // clamp backward: closed interval
-                const float gp = g * dproj[e];
-                // p = (f*A + c0*Z)/Z : dA = gp*f/Z ; dZ = gp*(c0/Z - num/Z^2)
-                const float f = isx ? d.K.fx : d.K.fy, c0 = isx ? d.K.cx : d.K.cy;
-                const float Av = isx ? X[c] : Y[c];
-                const float num = fmaf(c0, Z[c], f * Av);
-                const float dA = gp * f / Z[c];
-                const float dZ = gp * c0 / Z[c] - gp * num / (Z[c] * Z[c]);
-                float sx, sy, sz;
-                corner_signs(c, sx, sy, sz);
-                const float l[3] = {sx * hx, sy * hy, sz * hz};
-                const int ra = isx ? 0 : 1;                     // row of R feeding A
-                // corner = R l + centre
-                if (isx) dcx += 0.f;                             // (centre grads below)
-#pragma unroll
-                for (int k = 0; k < 3; ++k) {
-                    dR[3 * ra + k] += dA * l[k];
-                    dR[6 + k] += dZ * l[k];
-                    dl[k] += (d.R[3 * ra + k] * dA + d.R[6 + k] * dZ) * (k == 0 ? sx : (k == 1 ? sy : sz));
-                }
-                // centre: cube[0] or cube[1] gets dA, cube[2] gets dZ
-                const float zc = d.z;
-                if (isx) {   // x3d = z*(cube_x-cx)/fx
-                    dcx += dA * zc / d.K.fx;
-                    dz += dA * (d.cube_x - d.K.cx) / d.K.fx;
-                } else {
-                    dcy += dA * zc / d.K.fy;
-                    dz += dA * (d.cube_y - d.K.cy) / d.K.fy;
-                }
-                dz += dZ;
+                corner_backprop(d, c, isx, g * dproj[e], X[c], Y[c], Z[c], hx, hy, hz, dR, dl, dcx, dcy, dz);
             }
             ddims[2] += 0.5f * dl[0];   // hx = l/2
             ddims[1] += 0.5f * dl[1];   // hy = h/2
             ddims[0] += 0.5f * dl[2];   // hz = w/2
+        }
+    }
+    // ---- 'segmentation': d raw / d (second-clamped corners) comes from seg_loss_kernel<true> ----
+    if ((P.loss_flags & WCR_LOSS_SEG) && io.present[WCR_T_SEG]) {
+        const float g = coef(WCR_T_SEG, io.terms[(size_t)(WCR_T_SEG - 1) * io.n + i]);
+        if (g != 0.f) {
+            float lo0, hi0, lo1, hi1;
+            clamp_bounds(io.clamp[2 * i], lo0, hi0);
+            clamp_bounds(io.clamp[2 * i + 1], lo1, hi1);
+            const float mx = (float)(int)(io.clamp[2 * i] - 1.f), my = (float)(int)(io.clamp[2 * i + 1] - 1.f);
+            const float hx = d.dims[2] / 2.f, hy = d.dims[1] / 2.f, hz = d.dims[0] / 2.f;
+            float dl[3] = {0.f, 0.f, 0.f};
+#pragma unroll
+            for (int c = 0; c < 8; ++c) {
+                float sx, sy, sz;
+                corner_signs(c, sx, sy, sz);
+                const float lx = sx * hx, ly = sy * hy, lz = sz * hz;
+                const float Xc = fmaf(d.R[2], lz, fmaf(d.R[1], ly, d.R[0] * lx)) + d.cube[0];
+                const float Yc = fmaf(d.R[5], lz, fmaf(d.R[4], ly, d.R[3] * lx)) + d.cube[1];
+                const float Zc = fmaf(d.R[8], lz, fmaf(d.R[7], ly, d.R[6] * lx)) + d.cube[2];
+                const float pxy[2] = {fmaf(d.K.cx, Zc, d.K.fx * Xc) / Zc, fmaf(d.K.cy, Zc, d.K.fy * Yc) / Zc};
+#pragma unroll
+                for (int ax = 0; ax < 2; ++ax) {
+                    const float gp = g * io.seg_dcorner[16 * (size_t)i + 2 * c + ax];
+                    const float lo = ax ? lo1 : lo0, hi = ax ? hi1 : hi0, m2 = ax ? my : mx;
+                    const float pv = pxy[ax];
+                    if (gp == 0.f || !(pv >= lo && pv <= hi)) continue;   // first clamp (spaces.py:241-242), closed
+                    if (!(pv >= 0.f && pv <= m2)) continue;               // second clamp (roi_heads.py:951-952)
+                    corner_backprop(d, c, ax == 0, gp, Xc, Yc, Zc, hx, hy, hz, dR, dl, dcx, dcy, dz);
+                }
+            }
+            ddims[2] += 0.5f * dl[0]; ddims[1] += 0.5f * dl[1]; ddims[0] += 0.5f * dl[2];
         }
     }
     // ---- 'pose_alignment' ---------------------------------------------------------
@@ -1158,6 +1366,11 @@ static int check_io(const WcrLossIO *io, const WcrLossParams *p, bool bwd)
     if (p->loss_flags & WCR_LOSS_DEPTH)
         WCR_REQUIRE(io->masks && io->mask_idx && io->depth_gt && io->mask_h > 0 && io->mask_w > 0,
                     "wcr_weak_loss: 'depth' needs masks, mask_idx, depth_gt and the mask shape");
+    if (p->loss_flags & WCR_LOSS_SEG) {
+        WCR_REQUIRE(io->masks && io->mask_idx && io->mask_h > 0 && io->mask_w > 0,
+                    "wcr_weak_loss: 'segmentation' needs masks, mask_idx and the mask shape");
+        if (bwd) WCR_REQUIRE(io->seg_dcorner, "wcr_weak_loss_bwd: 'segmentation' needs seg_dcorner");
+    }
     if (p->loss_flags & (WCR_LOSS_DEPTH | WCR_LOSS_Z_PATCH))
         WCR_REQUIRE(io->select_ws, "wcr_weak_loss: 'depth' / 'z_pseudo_gt_patch' need select_ws "
                                    "(wcr_select_ws_bytes(n) bytes)");
@@ -1276,6 +1489,11 @@ extern "C" int wcr_weak_loss_fwd(const WcrLossIO *h_io, const WcrLossParams *h_p
             h_io->terms + (size_t)(WCR_T_PSEUDO_Z - 1) * h_io->n, h_io->z_sign);
         WCR_CHECK_LAUNCH("box_z_loss_kernel");
     }
+    if (h_io->n > 0 && (h_params->loss_flags & WCR_LOSS_SEG)) {
+        wcr::seg_loss_kernel<false><<<h_io->n, 256, 0, st>>>(
+            *h_io, *h_params, nullptr, h_io->terms + (size_t)(WCR_T_SEG - 1) * h_io->n, nullptr);
+        WCR_CHECK_LAUNCH("seg_loss_kernel");
+    }
     wcr::loss_pose_fwd_kernel<<<h_io->n_images, 256, 0, st>>>(*h_io);
     WCR_CHECK_LAUNCH("loss_pose_fwd_kernel");
     wcr::loss_reduce_kernel<<<1, 256, 0, st>>>(*h_io, *h_params);
@@ -1293,6 +1511,10 @@ extern "C" int wcr_weak_loss_bwd(const WcrLossIO *h_io, const WcrLossParams *h_p
     if (h_params->loss_flags & WCR_LOSS_POSE_ALIGN) {
         wcr::loss_pose_bwd_kernel<<<h_io->n_images, 128, 0, st>>>(*h_io, *h_params);
         WCR_CHECK_LAUNCH("loss_pose_bwd_kernel");
+    }
+    if (h_params->loss_flags & WCR_LOSS_SEG) {
+        wcr::seg_loss_kernel<true><<<h_io->n, 256, 0, st>>>(*h_io, *h_params, nullptr, nullptr, h_io->seg_dcorner);
+        WCR_CHECK_LAUNCH("seg_loss_kernel");
     }
     wcr::loss_box_bwd_kernel<<<(h_io->n + 127) / 128, 128, 0, st>>>(*h_io, *h_params);
     WCR_CHECK_LAUNCH("loss_box_bwd_kernel");
@@ -1533,5 +1755,39 @@ extern "C" int wcr_dim_loss_bwd(const float *prior_mean, const float *prior_std,
     wcr::dim_loss_bwd_kernel<<<(3 * n + 255) / 256, 256, 0, (cudaStream_t)stream>>>(prior_mean, prior_std, dims,
                                                                                   grad3n, n, d_dims);
     WCR_CHECK_LAUNCH("dim_loss_bwd_kernel");
+    return WCR_OK;
+}
+
+extern "C" int wcr_segment_loss_fwd(const uint8_t *masks, int mask_h, int mask_w, const int32_t *mask_idx,
+                                    const float *corners, int n, float *out_loss, void *stream)
+{
+    WCR_CHECK_DEVICE();
+    WCR_REQUIRE(masks && mask_idx && corners && out_loss, "wcr_segment_loss_fwd: null pointer");
+    WCR_REQUIRE(n >= 0 && mask_h > 0 && mask_w > 0, "wcr_segment_loss_fwd: bad sizes");
+    if (n == 0) return WCR_OK;
+    WcrLossIO io;
+    WcrLossParams P;
+    memset(&io, 0, sizeof(io));
+    memset(&P, 0, sizeof(P));
+    io.n = n; io.masks = masks; io.mask_h = mask_h; io.mask_w = mask_w; io.mask_idx = mask_idx;
+    wcr::seg_loss_kernel<false><<<n, 256, 0, (cudaStream_t)stream>>>(io, P, corners, out_loss, nullptr);
+    WCR_CHECK_LAUNCH("seg_loss_kernel");
+    return WCR_OK;
+}
+
+extern "C" int wcr_segment_loss_bwd(const uint8_t *masks, int mask_h, int mask_w, const int32_t *mask_idx,
+                                    const float *corners, int n, float *d_corners, void *stream)
+{
+    WCR_CHECK_DEVICE();
+    WCR_REQUIRE(masks && mask_idx && corners && d_corners, "wcr_segment_loss_bwd: null pointer");
+    WCR_REQUIRE(n >= 0 && mask_h > 0 && mask_w > 0, "wcr_segment_loss_bwd: bad sizes");
+    if (n == 0) return WCR_OK;
+    WcrLossIO io;
+    WcrLossParams P;
+    memset(&io, 0, sizeof(io));
+    memset(&P, 0, sizeof(P));
+    io.n = n; io.masks = masks; io.mask_h = mask_h; io.mask_w = mask_w; io.mask_idx = mask_idx;
+    wcr::seg_loss_kernel<true><<<n, 256, 0, (cudaStream_t)stream>>>(io, P, corners, nullptr, d_corners);
+    WCR_CHECK_LAUNCH("seg_loss_kernel");
     return WCR_OK;
 }

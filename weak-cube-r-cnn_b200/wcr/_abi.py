@@ -63,6 +63,8 @@ SIGNATURES = {
     "wcr_dim_loss_fwd": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_void_p, c_void_p, c_void_p]),
     "wcr_dim_loss_bwd": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_void_p, c_void_p]),
     "wcr_z_loss_steps": (None, [c_void_p]),
+    "wcr_segment_loss_fwd": (c_int, [c_void_p, c_int, c_int, c_void_p, c_void_p, c_int, c_void_p, c_void_p]),
+    "wcr_segment_loss_bwd": (c_int, [c_void_p, c_int, c_int, c_void_p, c_void_p, c_int, c_void_p, c_void_p]),
     "wcr_box3d_overlap": (c_int, [c_void_p, c_int, c_void_p, c_int, c_void_p, c_void_p, c_void_p]),
     "wcr_box3d_volume": (c_int, [c_void_p, c_int, c_void_p, c_void_p]),
     "wcr_rotation_6d_fwd": (c_int, [c_void_p, c_int, c_void_p, c_void_p]),
@@ -152,7 +154,7 @@ class LossParams(ctypes.Structure):
     _fields_ = [("loss_flags", ctypes.c_int32), ("z_type", ctypes.c_int32),
                 ("dims_func", ctypes.c_int32), ("use_confidence", c_float), ("w_3d", c_float),
                 ("w_iou", c_float), ("w_pose", c_float), ("w_normal", c_float), ("w_z", c_float),
-                ("w_dims", c_float), ("w_depth", c_float)]
+                ("w_dims", c_float), ("w_depth", c_float), ("w_seg", c_float)]
 
 
 _LOSS_IO_PTRS = ["deltas", "z_raw", "dims_raw", "pose", "uncert", "src_boxes", "K4", "v2r",
@@ -162,7 +164,7 @@ _LOSS_IO_PTRS = ["deltas", "z_raw", "dims_raw", "pose", "uncert", "src_boxes", "
                  "z_dec", "z_gt", "z_inside", "z_sign"]
 
 
-_LOSS_IO_PTRS2 = ["mask_idx", "depth_gt", "gt_rot", "select_ws"]   # after the mask shape (tier-2 terms)
+_LOSS_IO_PTRS2 = ["mask_idx", "depth_gt", "gt_rot", "select_ws", "seg_dcorner"]   # after the mask shape (tier-2 terms)
 
 
 class LossIO(ctypes.Structure):

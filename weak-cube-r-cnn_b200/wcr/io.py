@@ -28,6 +28,16 @@ def pil_nearest_table(in_size: int, out_size: int) -> np.ndarray:
     return tab
 
 
+_TABLES: dict = {}
+
+
+def _device_table(n_in: int, n_out: int, dev) -> torch.Tensor:
+    key = (n_in, n_out, str(dev))
+    if key not in _TABLES:            # a data loader sees a handful of (stored, augmented) size pairs
+        _TABLES[key] = torch.from_numpy(pil_nearest_table(n_in, n_out)).to(dev)
+    return _TABLES[key]
+
+
 def resize_nearest(t: torch.Tensor, size) -> torch.Tensor:
     """``np.array(Image.fromarray(a).resize((w, h), Image.NEAREST))`` for a (H, W) float32 / bool /
     uint8 CUDA tensor; ``size`` = (h, w) of the augmented image (``image.shape[:2]``)."""
@@ -46,8 +56,7 @@ def resize_nearest(t: torch.Tensor, size) -> torch.Tensor:
     if (ih, iw) == (oh, ow):
         return src.clone()          # PIL copies when the size is unchanged
     dev = src.device
-    xt = torch.from_numpy(pil_nearest_table(iw, ow)).to(dev)
-    yt = torch.from_numpy(pil_nearest_table(ih, oh)).to(dev)
+    xt, yt = _device_table(iw, ow, dev), _device_table(ih, oh, dev)
     out = torch.empty((oh, ow), dtype=view.dtype, device=dev)
     _abi.check(lib.wcr_resize_nearest(view.data_ptr(), view.element_size(), ih, iw, iw, xt.data_ptr(),
                                       yt.data_ptr(), out.data_ptr(), oh, ow, ow, _abi.stream_ptr(dev)),

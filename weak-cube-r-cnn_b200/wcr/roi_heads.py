@@ -21,11 +21,11 @@ from .images import ImageShard
 
 TERM_KEYS = ("Cube/uncert", "Cube/loss_iou", "Cube/loss_pose", "Cube/loss_normal_vec",
              "Cube/loss_pseudo_gt_z", "Cube/loss_dims_w", "Cube/loss_dims_h", "Cube/loss_dims_l",
-             "Cube/loss_z", "Cube/loss_depth")
+             "Cube/loss_z", "Cube/loss_depth", "Cube/loss_seg")
 N_TERMS, N_STATS = len(TERM_KEYS), 32          # WCR_LOSS_TERMS, WCR_LOSS_STATS
 STAT_TRACE_ERR, STAT_SHAPE_ERR = 18, 19
 _FLAG = {"iou": 1, "pose_alignment": 2, "pose_ground": 4, "z_pseudo_gt_center": 8, "dims": 16,
-         "z_pseudo_gt_patch": 32, "z": 64, "depth": 128, "pose_ground2": 256}
+         "z_pseudo_gt_patch": 32, "z": 64, "depth": 128, "pose_ground2": 256, "segmentation": 512}
 _ZTYPE = {"direct": 0, "sigmoid": 1, "log": 2}
 _DIMS = {"exp": 0, "sigmoid": 1}
 
@@ -44,18 +44,20 @@ class WeakLossConfig:
     loss_w_z: float = 1.0
     loss_w_dims: float = 20.0
     loss_w_depth: float = 1.0
+    loss_w_seg: float = 2.5
 
     def c_struct(self) -> _abi.LossParams:
         unknown = [f for f in self.loss_functions if f not in _FLAG]
         if unknown:
             raise _abi.WcrError(f"wcr.weak_loss: loss functions {unknown} are not on the fused path "
-                                "('segmentation', SURVEY.md §8f)")
+                                "(SURVEY.md §8f)")
         flags = 0
         for f in self.loss_functions:
             flags |= _FLAG[f]
         return _abi.LossParams(flags, _ZTYPE[self.z_type], _DIMS[self.dims_priors_func],
                                self.use_confidence, self.loss_w_3d, self.loss_w_iou, self.loss_w_pose,
-                               self.loss_w_normal_vec, self.loss_w_z, self.loss_w_dims, self.loss_w_depth)
+                               self.loss_w_normal_vec, self.loss_w_z, self.loss_w_dims, self.loss_w_depth,
+                               self.loss_w_seg)
 
 
 def _c(t, dev, dtype=torch.float32):
@@ -99,9 +101,9 @@ class _Ctx:
                       "z_inside": torch.empty(max(n, 1), dtype=torch.int32, device=dev),
                       "z_sign": torch.zeros(max(n, 1), device=dev)})
         self.mask_hw = (0, 0)
-        if "depth" in cfg.loss_functions:
+        if "depth" in cfg.loss_functions or "segmentation" in cfg.loss_functions:
             if gt_masks is None or at_which_mask_idx is None:
-                raise _abi.WcrError("wcr.weak_loss: 'depth' needs gt_masks and at_which_mask_idx")
+                raise _abi.WcrError("wcr.weak_loss: 'depth' / 'segmentation' need gt_masks and at_which_mask_idx")
             # masks_all_images (roi_heads.py:273): list of (1, H, W) bool, or one (M, H, W) tensor
             m = gt_masks if isinstance(gt_masks, torch.Tensor) else torch.stack(
                 [torch.as_tensor(x).reshape(x.shape[-2], x.shape[-1]) for x in gt_masks])
@@ -154,6 +156,8 @@ class _WeakLossFn(torch.autograd.Function):
              "d_deltas": torch.zeros((n, 2), device=dev), "d_z_raw": torch.zeros((n,), device=dev),
              "d_dims_raw": torch.zeros((n, 3), device=dev), "d_pose": torch.zeros((n, 9), device=dev),
              "d_uncert": torch.zeros((n,), device=dev), "d_R_pose": torch.zeros((max(n, 1), 9), device=dev)}
+        if "segmentation" in c.cfg.loss_functions:
+            g["seg_dcorner"] = torch.zeros((max(n, 1), 16), device=dev)
         io = c.io(g)
         _abi.check(lib.wcr_weak_loss_bwd(ctypes.byref(io), ctypes.byref(c.params),
                                          _abi.stream_ptr(dev)), "wcr_weak_loss_bwd")
@@ -366,3 +370,52 @@ def dim_loss(priors, dimensions):
     if int(flag.item()) != 0:
         return None, None, None
     return out[0], out[1], out[2]
+
+
+def _stack_masks(gt_mask, dev):
+    m = gt_mask if isinstance(gt_mask, torch.Tensor) else torch.stack(
+        [torch.as_tensor(x).reshape(x.shape[-2], x.shape[-1]) for x in gt_mask])
+    m = m.reshape(-1, m.shape[-2], m.shape[-1]).to(device=dev)
+    if m.dtype == torch.bool:
+        return m.contiguous().view(torch.uint8)
+    return (m != 0).to(torch.uint8).contiguous() if m.dtype != torch.uint8 else m.contiguous()
+
+
+class _SegmentLossFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, corners, masks, idx):
+        lib = _abi.load()
+        c = corners.detach().to(torch.float32).contiguous().view(-1, 16)
+        n = c.shape[0]
+        out = torch.empty((n,), dtype=torch.float32, device=c.device)
+        _abi.check(lib.wcr_segment_loss_fwd(masks.data_ptr(), masks.shape[1], masks.shape[2], idx.data_ptr(),
+                                            c.data_ptr(), n, out.data_ptr(), _abi.stream_ptr(c.device)),
+                   "wcr_segment_loss_fwd")
+        ctx.save_for_backward(c, masks, idx)
+        ctx.shape = corners.shape
+        return out
+
+    @staticmethod
+    def backward(ctx, g):
+        lib = _abi.load()
+        c, masks, idx = ctx.saved_tensors
+        n = c.shape[0]
+        d = torch.empty_like(c)
+        _abi.check(lib.wcr_segment_loss_bwd(masks.data_ptr(), masks.shape[1], masks.shape[2], idx.data_ptr(),
+                                            c.data_ptr(), n, d.data_ptr(), _abi.stream_ptr(c.device)),
+                   "wcr_segment_loss_bwd")
+        return (d * g.to(torch.float32).view(n, 1)).view(ctx.shape), None, None
+
+
+def segment_loss(gt_mask, bube_corners, at_which_mask_idx, loss: str = "focal"):
+    """roi_heads.py:420-443 (``loss='focal'``, the only mode the reference calls, :1017):
+    ``gt_mask`` list of (1,H,W) masks (or one (M,H,W) tensor), ``bube_corners`` (n,8,2) clamped
+    projected corners, ``at_which_mask_idx`` (n,) -> (n,) losses, differentiable in the corners."""
+    if loss != "focal":
+        raise _abi.WcrError("wcr.segment_loss: only loss='focal' is on the device path")
+    _abi.require_cuda(bube_corners)
+    dev = bube_corners.device
+    masks = _stack_masks(gt_mask, dev)
+    idx = torch.as_tensor(list(at_which_mask_idx) if not isinstance(at_which_mask_idx, torch.Tensor)
+                          else at_which_mask_idx, dtype=torch.int32).to(dev)
+    return _SegmentLossFn.apply(bube_corners, masks, idx)
