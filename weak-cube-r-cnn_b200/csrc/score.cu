@@ -29,9 +29,7 @@
 
 namespace wcr {
 
-constexpr int SC_THREADS = 256;
-constexpr int SC_T = 4;                        // proposals per thread
-constexpr int SC_CHUNK = SC_THREADS * SC_T;    // proposals per item
+constexpr int SC_CHUNK = 1024;                 // proposals per item = threads x proposals per thread
 constexpr int SC_TILE = 2048;                  // (a,a,z,z) pixels per smem tile = 32 KB
 constexpr int SC_ITEM_PX = 4096;               // target depth pixels per item (large shards)
 constexpr int SC_ITEM_PX_MIN = 512;            // ... shrunk for small shards so every SM gets items
@@ -130,6 +128,8 @@ __device__ __forceinline__ Roi box_roi(const WcrBox &bx, int H, int W, int s, bo
     return r;
 }
 
+struct PParam;   // score_tiles.cuh
+
 // Device workspace layout (caller-owned, zeroed by cudaMemsetAsync up to `zero_bytes`).
 struct ScoreWs {
     int *queue;          // [1]   next item
@@ -141,6 +141,8 @@ struct ScoreWs {
     float *cand;         // [n_boxes][n_chunks][k][20] chunk candidates (n_chunks > 1)
     float *cubes;        // [n_boxes][N][15] when sampled by the library
     int2 *segcnt;        // [n_boxes][N] (|seg & hull|, |hull|) pixel counts of the mask term
+    PParam *params;      // [n_boxes][N] point-test constants (tile path)
+    int4 *cullbox;       // [n_boxes][N] cull boxes (tile path)
 };
 
 struct ScoreArgs {
@@ -153,6 +155,7 @@ struct ScoreArgs {
     int k;
     int n_chunks;
     int item_px;         // depth pixels per item (plan and item kernel must agree)
+    int grp;             // tile path: registers per column group (plan and kernel must agree)
     ScoreWs ws;
     float *records;
     float *out_scores, *out_iou;
@@ -163,6 +166,10 @@ struct ScoreArgs {
     const int64_t *seg_off;     // [n_boxes + 1] word offsets
     float *out_seg;
 };
+
+}  // namespace wcr
+#include "score_tiles.cuh"
+namespace wcr {
 
 // One CTA: items per box -> exclusive prefix. n_boxes is at most a few 100 k.
 __global__ void __launch_bounds__(1024)
@@ -213,9 +220,11 @@ score_plan_kernel(const WcrImage *__restrict__ images, const WcrBox *__restrict_
 
 // k rounds of (max score, lowest index) over the CTA's SC_CHUNK candidates in smem.
 // Winner r's local index (or -1) lands in s_win[r], its score in s_wsc[r].
+template <int SC_THREADS>
 __device__ __forceinline__ void cta_topk(float *s_score, int k, float *s_red_v, int *s_red_i,
                                          int *s_win, float *s_wsc)
 {
+    constexpr int SC_T = SC_CHUNK / SC_THREADS;
     const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
     for (int r = 0; r < k; ++r) {
         float bv = -INFINITY; int bi = 0x7fffffff;
@@ -276,16 +285,20 @@ __device__ __forceinline__ void warp_merge(const float *cand, int n, int k, floa
     }
 }
 
+}  // namespace wcr
+#include "score_tiles_kernel.cuh"
+namespace wcr {
+
 // V selects the inner-loop instruction mix (same arithmetic, same results):
 //   0: FFMA2 (two proposals per packed fma) + FMNMX3 + FSET + FADD2
 //   1: scalar FFMA + FMNMX3 + FSET + FADD
 //   2: scalar FFMA + 3 x FSETP(|q| <= 1) + predicated IADD
 // (an integer-mask FSET + IADD3 pairing was tried too: ptxas lowers it to the
 //  quarter-rate FSETP + predicated IADD, 9 % slower -- profiles/variants_r1.txt)
-template <int V, int MINB>
+template <int V, int MINB, int SC_THREADS>
 __global__ void __launch_bounds__(SC_THREADS, MINB) score_items_kernel(const ScoreArgs a)
 {
-    constexpr int T = SC_T;
+    constexpr int T = SC_CHUNK / SC_THREADS;   // proposals per thread
     __shared__ __align__(16) float4 tile[SC_TILE];
     __shared__ float s_score[SC_CHUNK];
     __shared__ float s_iou[SC_CHUNK];
@@ -598,7 +611,7 @@ __global__ void __launch_bounds__(SC_THREADS, MINB) score_items_kernel(const Sco
             s_score[loc] = score; s_iou[loc] = siou; s_seg[loc] = sseg;
         }
         __syncthreads();
-        cta_topk(s_score, a.k, s_red_v, s_red_i, s_win, s_wsc);
+        cta_topk<SC_THREADS>(s_score, a.k, s_red_v, s_red_i, s_win, s_wsc);
         float *rec_base = a.n_chunks == 1
                               ? a.records + (size_t)b * a.k * WCR_RECORD_FLOATS
                               : a.ws.cand + ((size_t)b * a.n_chunks + chunk) * a.k * WCR_RECORD_FLOATS;
@@ -665,8 +678,10 @@ size_t carve(void *base, int n_boxes, int N, int k, bool need_cubes, bool need_s
     float *cand = (float *)take(nc > 1 ? (size_t)n_boxes * nc * k * WCR_RECORD_FLOATS * sizeof(float) : 0);
     float *cubes = (float *)take(need_cubes ? (size_t)n_boxes * N * 15 * sizeof(float) : 0);
     int2 *segcnt = (int2 *)take(need_seg ? (size_t)n_boxes * N * sizeof(int2) : 0);
+    wcr::PParam *params = (wcr::PParam *)take((size_t)n_boxes * N * sizeof(wcr::PParam));
+    int4 *cullbox = (int4 *)take((size_t)n_boxes * N * sizeof(int4));
     if (ws) {
-        ws->segcnt = segcnt;
+        ws->segcnt = segcnt; ws->params = params; ws->cullbox = cullbox;
         ws->queue = queue; ws->done_chunk = done_chunk; ws->done_box = done_box; ws->npts = npts;
         ws->count = count; ws->item_prefix = prefix; ws->cand = cand; ws->cubes = cubes;
     }
@@ -714,18 +729,30 @@ extern "C" int wcr_score_topk(const WcrImage *images, const WcrBox *boxes, int n
     carve(ws, n_boxes, N, k, cubes == nullptr, h_score->e_seg > 0, &a.ws, &zero_bytes);
     cudaError_t e = cudaMemsetAsync(ws, 0, zero_bytes, st);
     if (e != cudaSuccess) { wcr::set_error("cudaMemsetAsync: %s", cudaGetErrorString(e)); return WCR_ELAUNCH; }
-    // A 64-image shard has ~10^4 items of 4096 px; a single image with a handful of boxes
-    // would leave most of the 296 resident CTAs idle, so its items are cut finer.
-    {
+    static int variant = -1;
+    if (variant < 0) {  // development knob; the default is what DESIGN.md measures
+        const char *ev = getenv("WCR_SCORE_VARIANT");
+        variant = ev ? atoi(ev) : 100;
+    }
+    const bool tiles = variant >= 100;
+    if (tiles) {
+        a.grp = (variant / 10) % 10 == 1 ? 8 : 4;
+        wcr::score_plan_tiles_kernel<<<1, 1024, 0, st>>>(images, boxes, n_boxes, nc, h_score->point_stride,
+                                                         h_score->e_pts > 0, h_score->e_seg > 0, a.grp,
+                                                         a.ws.item_prefix);
+        WCR_CHECK_LAUNCH("score_plan_tiles_kernel");
+    } else {
+        // A 64-image shard has ~10^4 items of 4096 px; a single image with a handful of boxes
+        // would leave most of the 296 resident CTAs idle, so its items are cut finer.
         const long long bc = (long long)n_boxes * nc;
         long long px = wcr::SC_ITEM_PX * bc / 296;
         int item_px = wcr::SC_ITEM_PX_MIN;
         while (item_px < wcr::SC_ITEM_PX && item_px < px) item_px <<= 1;
         a.item_px = item_px;
+        wcr::score_plan_kernel<<<1, 1024, 0, st>>>(images, boxes, n_boxes, nc, h_score->point_stride,
+                                                   h_score->e_pts > 0, a.item_px, a.ws.item_prefix);
+        WCR_CHECK_LAUNCH("score_plan_kernel");
     }
-    wcr::score_plan_kernel<<<1, 1024, 0, st>>>(images, boxes, n_boxes, nc, h_score->point_stride,
-                                               h_score->e_pts > 0, a.item_px, a.ws.item_prefix);
-    WCR_CHECK_LAUNCH("score_plan_kernel");
     if (!cubes) {
         WCR_REQUIRE((N + 255) / 256 <= 65535, "wcr_score_topk: N too large");
         wcr::launch_sample_cubes(images, boxes, n_boxes, priors, normals, z0, *h_sample, N, nullptr,
@@ -738,22 +765,36 @@ extern "C" int wcr_score_topk(const WcrImage *images, const WcrBox *boxes, int n
     a.out_scores = out_scores; a.out_iou = out_iou; a.out_count = out_count;
     a.out_proj = out_proj; a.out_npts = out_npts;
     a.seg_bits = seg_bits; a.seg_off = seg_off; a.out_seg = out_seg;
-    static int variant = -1;
-    if (variant < 0) {  // development knob; the default is what DESIGN.md measures
-        const char *ev = getenv("WCR_SCORE_VARIANT");
-        variant = ev ? atoi(ev) : 4;
-    }
     const int sms = wcr::sm_count();
+    if (tiles) {
+        if (h_score->e_pts > 0) {
+            const dim3 grid(n_boxes, (N + 255) / 256);
+            wcr::score_prep_kernel<<<grid, 256, 0, st>>>(images, boxes, n_boxes, cubes ? cubes : a.ws.cubes, N,
+                                                          h_score->point_stride, 1, a.ws.params, a.ws.cullbox);
+            WCR_CHECK_LAUNCH("score_prep_kernel");
+        }
+        switch (variant) {
+        case 101: wcr::score_tiles_kernel<4, 3, 4><<<sms * 3, 128, 0, st>>>(a); break;
+        case 110: wcr::score_tiles_kernel<8, 2, 8><<<sms * 2, 256, 0, st>>>(a); break;
+        case 111: wcr::score_tiles_kernel<4, 3, 8><<<sms * 3, 128, 0, st>>>(a); break;
+        default: wcr::score_tiles_kernel<8, 2, 4><<<sms * 2, 256, 0, st>>>(a); break;
+        }
+        WCR_CHECK_LAUNCH("score_tiles_kernel");
+        return WCR_OK;
+    }
     switch (variant) {
-    case 2: wcr::score_items_kernel<2, 2><<<sms * 2, wcr::SC_THREADS, 0, st>>>(a); break;
-    case 10: wcr::score_items_kernel<0, 3><<<sms * 3, wcr::SC_THREADS, 0, st>>>(a); break;
-    case 11: wcr::score_items_kernel<1, 3><<<sms * 3, wcr::SC_THREADS, 0, st>>>(a); break;
-    case 12: wcr::score_items_kernel<2, 3><<<sms * 3, wcr::SC_THREADS, 0, st>>>(a); break;
-    case 0: wcr::score_items_kernel<0, 2><<<sms * 2, wcr::SC_THREADS, 0, st>>>(a); break;
-    case 5: wcr::score_items_kernel<5, 2><<<sms * 2, wcr::SC_THREADS, 0, st>>>(a); break;
-    case 14: wcr::score_items_kernel<4, 3><<<sms * 3, wcr::SC_THREADS, 0, st>>>(a); break;
-    case 1: wcr::score_items_kernel<1, 2><<<sms * 2, wcr::SC_THREADS, 0, st>>>(a); break;
-    default: wcr::score_items_kernel<4, 2><<<sms * 2, wcr::SC_THREADS, 0, st>>>(a); break;
+    case 2: wcr::score_items_kernel<2, 2, 256><<<sms * 2, 256, 0, st>>>(a); break;
+    case 10: wcr::score_items_kernel<0, 3, 256><<<sms * 3, 256, 0, st>>>(a); break;
+    case 11: wcr::score_items_kernel<1, 3, 256><<<sms * 3, 256, 0, st>>>(a); break;
+    case 12: wcr::score_items_kernel<2, 3, 256><<<sms * 3, 256, 0, st>>>(a); break;
+    case 0: wcr::score_items_kernel<0, 2, 256><<<sms * 2, 256, 0, st>>>(a); break;
+    case 5: wcr::score_items_kernel<5, 2, 256><<<sms * 2, 256, 0, st>>>(a); break;
+    case 14: wcr::score_items_kernel<4, 3, 256><<<sms * 3, 256, 0, st>>>(a); break;
+    case 24: wcr::score_items_kernel<4, 2, 128><<<sms * 2, 128, 0, st>>>(a); break;
+    case 34: wcr::score_items_kernel<4, 3, 128><<<sms * 3, 128, 0, st>>>(a); break;
+    case 44: wcr::score_items_kernel<4, 4, 128><<<sms * 4, 128, 0, st>>>(a); break;
+    case 1: wcr::score_items_kernel<1, 2, 256><<<sms * 2, 256, 0, st>>>(a); break;
+    default: wcr::score_items_kernel<4, 2, 256><<<sms * 2, 256, 0, st>>>(a); break;
     }
     WCR_CHECK_LAUNCH("score_items_kernel");
     return WCR_OK;

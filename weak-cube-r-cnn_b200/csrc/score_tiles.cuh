@@ -1,0 +1,204 @@
+// score_tiles.cuh -- warp-autonomous, culled form of the fused scoring kernel
+// (included by score.cu after ScoreArgs).
+//
+// Why. A point can only lie inside a cube if its pixel lies inside the cube's
+// projected box (perspective projection keeps convexity in front of the camera),
+// and on the C2 workload only ~45 % of the (proposal, ROI pixel) pairs do. The
+// thread-per-proposal layout (score_items_kernel) cannot use that: the 128
+// proposals of a warp cover the whole ROI between them. Here the roles are
+// swapped: a WARP owns a tile of depth pixels in registers (lane = image row,
+// register = column, 32 x 32 points), proposals stream past it one at a time as
+// warp-uniform parameters, and everything a proposal's projected box cannot reach
+// is skipped by uniform branches (whole tile, or 4-register column groups).
+//
+// The point test keeps the row-factored definition of score.cu bit for bit:
+//     q_k = fma(z, fma(A_k, a_u, G_k), -O_k),  G_k = fma(B_k, b_v, C_k)
+// G_k is now per (proposal, lane) -- the lane IS the row -- and a_u per register.
+// Culling is conservative (box grown by one pixel, disabled when a corner is
+// closer than 1 cm to the camera plane), so counts are identical to the unculled
+// evaluation; tests compare them with the oracle, which never culls.
+//
+// Work items, pulled by WARPS from one atomic queue (no CTA-level barrier anywhere):
+//   tile item (box, chunk, tile, half of the chunk's proposals) -> point counts
+//   seg item  (box, chunk, 32 proposals)                       -> hull fill pixel counts
+// The warp that retires the last item of a (box, chunk) runs its epilogue (corners ->
+// projection -> IoU -> score -> top-k) on its own; the warp that retires a box's last
+// chunk merges the chunk candidates.
+#pragma once
+
+namespace wcr {
+
+constexpr int TL_PS = 512;       // proposals per tile item
+constexpr int TL_SUBS = SC_CHUNK / TL_PS;
+constexpr int TL_SEGS = SC_CHUNK / 32;   // seg items per chunk
+
+
+// Tiling of a box's (sub-sampled) ROI: a tile is LR = 2^lrlog rows x (32/LR)*32
+// columns; lane = (row in tile) + LR * phase, register r = column r*(32/LR) + phase.
+struct TileGeom { int u0, v0, ncols, nrows, lrlog, n_rt, n_ct, n_tiles; };
+
+__device__ __forceinline__ TileGeom tile_geom(const WcrBox &bx, int H, int W, int s, bool use_pts, int grp)
+{
+    const Roi r = box_roi(bx, H, W, s, use_pts);
+    TileGeom g;
+    g.u0 = r.u0; g.v0 = r.v0; g.ncols = r.ncols; g.nrows = r.nrows;
+    int best = 4;
+    long long best_cost = -1;
+    const int order[3] = {4, 5, 3};   // ties go to the balanced 16-row tile
+#pragma unroll
+    for (int i = 0; i < 3; ++i) {
+        const int l = order[i], LR = 1 << l, gw = grp * (32 >> l);
+        const long long cost = (long long)((g.nrows + LR - 1) / LR) * LR * (((g.ncols + gw - 1) / gw) * gw);
+        if (best_cost < 0 || cost < best_cost) { best_cost = cost; best = l; }
+    }
+    g.lrlog = best;
+    g.n_rt = (g.nrows + (1 << best) - 1) >> best;
+    const int tw = (32 >> best) * 32;
+    g.n_ct = (g.ncols + tw - 1) / tw;
+    g.n_tiles = g.nrows > 0 ? g.n_rt * g.n_ct : 0;
+    return g;
+}
+
+// queue items of one (box, chunk); at least one so that somebody runs the epilogue
+__device__ __forceinline__ int tile_items_per_chunk(const TileGeom &g, bool use_seg)
+{
+    return max(g.n_tiles * TL_SUBS, 1) + (use_seg ? TL_SEGS : 0);
+}
+
+// Per-proposal constants of the point test, 48 B; the cull boxes live in their own
+// int4 array so that a warp reads 32 of them in one coalesced request.
+struct __align__(16) PParam {
+    float4 a;   // A_0 A_1 A_2 -O_0   (rows scaled by 2^11 / half_k, see inside_sat)
+    float4 b;   // B_0 B_1 B_2 -O_1
+    float4 c;   // C_0 C_1 C_2 -O_2
+};
+// cull box: ROI column / row index range the projected box can reach: cl ch rl rh
+// (inclusive; cl > ch: the proposal holds no point of this ROI)
+
+// One thread per proposal: test constants (same expressions as score_items_kernel's
+// prologue) and the conservative cull box.
+__global__ void __launch_bounds__(256)
+score_prep_kernel(const WcrImage *__restrict__ images, const WcrBox *__restrict__ boxes, int n_boxes,
+                  const float *__restrict__ cubes, int N, int stride, int use_pts,
+                  PParam *__restrict__ out, int4 *__restrict__ out_box)
+{
+    const int j = blockIdx.y * 256 + threadIdx.x, b = blockIdx.x;
+    if (j >= N) return;
+    const WcrBox bx = boxes[b];
+    const WcrImage im = images[bx.image];
+    const Roi roi = box_roi(bx, im.H, im.W, stride, use_pts != 0);
+    const float *src = cubes + ((size_t)b * N + j) * 15;
+    float cube[15];
+#pragma unroll
+    for (int i = 0; i < 15; ++i) cube[i] = ld_stream(src + i);
+    PParam p;
+    const bool live = roi.nrows > 0 && cube[3] > 0.f && cube[4] > 0.f && cube[5] > 0.f;
+    float A[3], B[3], C[3], NO[3];
+    if (live) {
+        const float half[3] = {cube[5] / 2.f, cube[4] / 2.f, cube[3] / 2.f};
+#pragma unroll
+        for (int k = 0; k < 3; ++k) {
+            A[k] = cube[6 + k] / half[k];
+            B[k] = cube[9 + k] / half[k];
+            C[k] = cube[12 + k] / half[k];
+            NO[k] = -fmaf(C[k], cube[2], fmaf(B[k], cube[1], A[k] * cube[0]));
+            A[k] *= 2048.f; B[k] *= 2048.f; C[k] *= 2048.f; NO[k] *= 2048.f;
+        }
+    } else {
+#pragma unroll
+        for (int k = 0; k < 3; ++k) { A[k] = B[k] = C[k] = 0.f; NO[k] = nanf_(); }
+    }
+    p.a = make_float4(A[0], A[1], A[2], NO[0]);
+    p.b = make_float4(B[0], B[1], B[2], NO[1]);
+    p.c = make_float4(C[0], C[1], C[2], NO[2]);
+    int cl = 1, ch = 0, rl = 1, rh = 0;   // dead until proven reachable
+    if (live) {
+        // unclamped projection of the 8 corners; min/max and the nearest corner depth
+        const float hx = cube[5] / 2.f, hy = cube[4] / 2.f, hz = cube[3] / 2.f;
+        const float *R = cube + 6;
+        float mnx = INFINITY, mxx = -INFINITY, mny = INFINITY, mxy = -INFINITY, mnz = INFINITY;
+        bool finite = true;
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+            float sx, sy, sz;
+            corner_signs(i, sx, sy, sz);
+            const float lx = sx * hx, ly = sy * hy, lz = sz * hz;
+            const float X = fmaf(R[2], lz, fmaf(R[1], ly, R[0] * lx)) + cube[0];
+            const float Y = fmaf(R[5], lz, fmaf(R[4], ly, R[3] * lx)) + cube[1];
+            const float Z = fmaf(R[8], lz, fmaf(R[7], ly, R[6] * lx)) + cube[2];
+            const float px = fmaf(im.cx, Z, im.fx * X) / Z, py = fmaf(im.cy, Z, im.fy * Y) / Z;
+            finite = finite && fabsf(px) <= 3.402823466e38f && fabsf(py) <= 3.402823466e38f &&
+                     fabsf(Z) <= 3.402823466e38f;
+            mnx = fminf(mnx, px); mxx = fmaxf(mxx, px);
+            mny = fminf(mny, py); mxy = fmaxf(mxy, py);
+            mnz = fminf(mnz, Z);
+        }
+        cl = 0; ch = roi.ncols - 1; rl = 0; rh = roi.nrows - 1;   // no culling
+        if (finite && mnz >= 0.01f) {
+            // pixel u = u0 + c*stride is reachable iff floor(mnx) - 1 <= u <= ceil(mxx) + 1
+            const float big = 1.0e6f;
+            const int x_lo = (int)floorf(fminf(fmaxf(mnx, -big), big)) - 1 - roi.u0;
+            const int x_hi = (int)ceilf(fminf(fmaxf(mxx, -big), big)) + 1 - roi.u0;
+            const int y_lo = (int)floorf(fminf(fmaxf(mny, -big), big)) - 1 - roi.v0;
+            const int y_hi = (int)ceilf(fminf(fmaxf(mxy, -big), big)) + 1 - roi.v0;
+            // c >= ceil(x_lo / s), c <= floor(x_hi / s)   (floor division for negatives)
+            const int s = stride;
+            cl = max(cl, x_lo <= 0 ? 0 : (x_lo + s - 1) / s);
+            ch = min(ch, x_hi < 0 ? -1 : x_hi / s);
+            rl = max(rl, y_lo <= 0 ? 0 : (y_lo + s - 1) / s);
+            rh = min(rh, y_hi < 0 ? -1 : y_hi / s);
+        }
+    }
+    if (cl > ch || rl > rh) { cl = 0x3fffffff; ch = -1; rl = 0x3fffffff; rh = -1; }   // fails every overlap test
+    out[(size_t)b * N + j] = p;
+    out_box[(size_t)b * N + j] = make_int4(cl, ch, rl, rh);
+}
+
+// One CTA: queue items per box -> exclusive prefix (tile path).
+__global__ void __launch_bounds__(1024)
+score_plan_tiles_kernel(const WcrImage *__restrict__ images, const WcrBox *__restrict__ boxes,
+                        int n_boxes, int n_chunks, int stride, int use_pts, int use_seg, int grp,
+                        int *__restrict__ prefix)
+{
+    __shared__ int s_warp[32];
+    __shared__ int s_carry;
+    const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+    if (tid == 0) s_carry = 0;
+    __syncthreads();
+    for (int base = 0; base < n_boxes; base += 1024) {
+        const int b = base + tid;
+        int n = 0;
+        if (b < n_boxes) {
+            const WcrBox bx = boxes[b];
+            const WcrImage im = images[bx.image];
+            n = tile_items_per_chunk(tile_geom(bx, im.H, im.W, stride, use_pts != 0, grp), use_seg != 0) * n_chunks;
+        }
+        int incl = n;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const int t = __shfl_up_sync(0xffffffffu, incl, o);
+            if (lane >= o) incl += t;
+        }
+        if (lane == 31) s_warp[wid] = incl;
+        __syncthreads();
+        if (wid == 0) {
+            const int t = s_warp[lane];
+            int w = t;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const int x = __shfl_up_sync(0xffffffffu, w, o);
+                if (lane >= o) w += x;
+            }
+            s_warp[lane] = w - t;
+        }
+        __syncthreads();
+        const int carry = s_carry;
+        if (b < n_boxes) prefix[b] = carry + s_warp[wid] + incl - n;
+        __syncthreads();
+        if (tid == 1023) s_carry = carry + s_warp[wid] + incl;
+        __syncthreads();
+    }
+    if (tid == 0) prefix[n_boxes] = s_carry;
+}
+
+}  // namespace wcr

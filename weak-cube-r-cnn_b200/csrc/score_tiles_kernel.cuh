@@ -1,0 +1,338 @@
+// score_tiles_kernel.cuh -- the persistent warp-autonomous scoring kernel
+// (see score_tiles.cuh for the design). Included by score.cu.
+#pragma once
+
+namespace wcr {
+
+__device__ __forceinline__ float4 ldg_f4(const float4 *p) { return __ldg(p); }
+
+// ---- tile item: one warp, 32 x 32 depth pixels in registers, proposals stream past ----
+// Pass 1 (lane = proposal): cull boxes against the tile, survivors compacted into the
+// warp's scratch list together with their column-group range. Pass 2 (lane = row):
+// survivors one at a time as warp-uniform parameters.
+template <int GRP>
+__device__ __forceinline__ void tile_item(const ScoreArgs &a, int b, const WcrImage &im,
+                                          const TileGeom &tg, int chunk, int tile, int sub,
+                                          float *wbuf, int lane)
+{
+    const int s = a.sc.point_stride;
+    const int lrlog = tg.lrlog, LR = 1 << lrlog, nph = 32 >> lrlog;
+    const int rt = tile / tg.n_ct, ct = tile - rt * tg.n_ct;
+    const int tr0 = rt << lrlog, tc0 = ct * (nph * 32);
+    const int my_row = tr0 + (lane & (LR - 1)), phase = lane >> lrlog;
+    const bool row_ok = my_row < tg.nrows;
+    const int v = tg.v0 + my_row * s;
+
+    const int chunk_n = min(SC_CHUNK, a.N - chunk * SC_CHUNK);
+    const int n = min(TL_PS, chunk_n - sub * TL_PS);
+    const size_t first = (size_t)b * a.N + (size_t)chunk * SC_CHUNK + sub * TL_PS;
+    const PParam *__restrict__ pp = a.ws.params + first;
+    unsigned *list = reinterpret_cast<unsigned *>(wbuf);   // <= TL_PS entries: j | g_lo << 16 | g_hi << 24
+    int n_keep = 0;
+    {
+        const int t_r1 = min(tr0 + LR, tg.nrows) - 1, t_c1 = min(tc0 + nph * 32, tg.ncols) - 1;
+        const int gshift = (GRP == 8 ? 3 : 2) + (5 - lrlog);   // log2(GRP * nph)
+        const int4 *__restrict__ cb = a.ws.cullbox + first;
+        for (int base = 0; base < n; base += 32) {
+            const int j = base + lane;
+            bool keep = false;
+            unsigned entry = 0;
+            if (j < n) {
+                const int4 bb = __ldg(cb + j);
+                keep = !(bb.x > t_c1 || bb.y < tc0 || bb.z > t_r1 || bb.w < tr0);
+                const int g_lo = (max(bb.x, tc0) - tc0) >> gshift, g_hi = (min(bb.y, t_c1) - tc0) >> gshift;
+                entry = (unsigned)j | (unsigned)g_lo << 16 | (unsigned)g_hi << 24;
+                if (keep) asm volatile("prefetch.global.L1 [%0];" ::"l"(pp + j));
+            }
+            const unsigned m = __ballot_sync(0xffffffffu, keep);
+            if (keep) list[n_keep + __popc(m & ((1u << lane) - 1u))] = entry;
+            n_keep += __popc(m);
+        }
+        __syncwarp();
+    }
+
+    const float *drow = im.depth + (size_t)(row_ok ? v : 0) * im.depth_pitch;
+    float z[32], av[32];
+    int valid = 0;
+#pragma unroll
+    for (int r = 0; r < 32; ++r) {
+        const int col = tc0 + r * nph + phase;
+        const int u = tg.u0 + col * s;
+        av[r] = ((float)u - im.cx) / im.fx;
+        float d = 0.f;
+        if (row_ok && col < tg.ncols) d = __ldg(drow + u);
+        const bool ok = d > 0.f && d <= 3.402823466e38f;
+        z[r] = ok ? d : nanf_();
+        valid += ok;
+    }
+    const float bv = ((float)v - im.cy) / im.fy;
+    if (sub == 0) {
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) valid += __shfl_xor_sync(0xffffffffu, valid, o);
+        if (lane == 0 && valid) atomicAdd(a.ws.npts + (size_t)b * a.n_chunks + chunk, valid);
+    }
+    int *__restrict__ cnt = a.ws.count + first;
+
+#pragma unroll 1
+    for (int i = 0; i < n_keep; ++i) {
+        // every lane reads the same word; the OR-reduction hands it back in a uniform
+        // register, which lets the group branches below compile to uniform branches
+        const unsigned e = __reduce_or_sync(0xffffffffu, list[i]);
+        const int j = e & 0xffffu;
+        const unsigned g_lo = (e >> 16) & 0xffu, g_hi = e >> 24;
+        const float4 pa = ldg_f4(&pp[j].a), pb = ldg_f4(&pp[j].b), pc = ldg_f4(&pp[j].c);
+        const float G0 = fmaf(pb.x, bv, pc.x), G1 = fmaf(pb.y, bv, pc.y), G2 = fmaf(pb.z, bv, pc.z);
+        float acc[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+        for (int g = 0; g < 32 / GRP; ++g) {
+            if (g >= g_lo && g <= g_hi) {
+#pragma unroll
+                for (int t = 0; t < GRP; ++t) {
+                    const int r = g * GRP + t;
+                    const float q0 = fmaf(z[r], fmaf(pa.x, av[r], G0), pa.w);
+                    const float q1 = fmaf(z[r], fmaf(pa.y, av[r], G1), pb.w);
+                    const float q2 = fmaf(z[r], fmaf(pa.z, av[r], G2), pc.w);
+                    acc[t & 3] += inside_sat(q0, q1, q2);
+                }
+            }
+        }
+        const float sum = (acc[0] + acc[1]) + (acc[2] + acc[3]);
+        const int c = __reduce_add_sync(0xffffffffu, (int)sum);
+        if (lane == 0 && c) atomicAdd(cnt + j, c);
+    }
+    __syncwarp();
+}
+
+// ---- seg item: hull fill pixel counts of 32 proposals (lane = proposal for the march,
+// then the warp walks the 32 hulls with lanes = pixel rows) --------------------------
+__device__ __forceinline__ void seg_item(const ScoreArgs &a, int b, const WcrBox &bx, const WcrImage &im,
+                                         int chunk, int grp, float *wbuf, int lane)
+{
+    const int chunk_n = min(SC_CHUNK, a.N - chunk * SC_CHUNK);
+    const int q = grp * 32 + lane;
+    if (grp * 32 >= chunk_n) return;
+    const float *__restrict__ cubes = a.cubes ? a.cubes : a.ws.cubes;
+    const Intr K = {im.fx, im.fy, im.cx, im.cy};
+    float lo0, hi0, lo1, hi1;
+    clamp_bounds(bx.clamp0, lo0, hi0);
+    clamp_bounds(bx.clamp1, lo1, hi1);
+    SegBox sb;
+    const Roi r1 = box_roi(bx, im.H, im.W, 1, true);
+    sb.u0 = r1.u0; sb.v0 = r1.v0; sb.ncols = r1.ncols; sb.nrows = r1.ncols > 0 ? r1.nrows : 0;
+    sb.wpr = (sb.ncols + 31) >> 5;
+    sb.bits = a.seg_bits + a.seg_off[b];
+    sb.area = 0;
+    float *scratch = wbuf + lane;
+    const Strided spx = {scratch, 32}, spy = {scratch + 8 * 32, 32};
+    const Strided shx = {scratch + 16 * 32, 32}, shy = {scratch + 24 * 32, 32};
+    const float hx2 = (float)(int)(bx.clamp0 - 1.f), hy2 = (float)(int)(bx.clamp1 - 1.f);
+    int m_own = -1;
+    if (q < chunk_n) {
+        const float *src = cubes + ((size_t)b * a.N + chunk * SC_CHUNK + q) * 15;
+        float cube[15], cxy[16];
+#pragma unroll
+        for (int i = 0; i < 15; ++i) cube[i] = ld_stream(src + i);
+        project_cube(cube, K, lo0, hi0, lo1, hi1, cxy);
+        bool finite = true;   // second clamp of the corners (roi_heads.py:950-952)
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+            finite = finite && fabsf(cxy[2 * i]) <= 3.402823466e38f && fabsf(cxy[2 * i + 1]) <= 3.402823466e38f;
+            spx(i) = fminf(fmaxf(cxy[2 * i], 0.f), hx2);
+            spy(i) = fminf(fmaxf(cxy[2 * i + 1], 0.f), hy2);
+        }
+        if (finite) {
+            m_own = jarvis_march(spx, spy, 8, shx, shy);
+            if (m_own > 0) hull_edges(shx, shy, m_own, spx, spy);   // corners are dead: reuse
+        }
+    }
+    __syncwarp();
+    int my_inter = 0, my_bube = 0;
+#pragma unroll 1
+    for (int p = 0; p < 32; ++p) {
+        const int mp = __shfl_sync(0xffffffffu, m_own, p);
+        if (mp < 1) continue;
+        const Strided exp_ = {wbuf + p, 32}, eyp = {wbuf + p + 8 * 32, 32};
+        const Strided hxp = {wbuf + p + 16 * 32, 32}, hyp = {wbuf + p + 24 * 32, 32};
+        int it, bu;
+        seg_counts_warp(hxp, hyp, exp_, eyp, mp, im.H, im.W, sb, it, bu);
+        if (lane == p) { my_inter = it; my_bube = bu; }
+    }
+    __syncwarp();
+    if (q < chunk_n) a.ws.segcnt[(size_t)b * a.N + chunk * SC_CHUNK + q] = make_int2(my_inter, my_bube);
+}
+
+// Terms of one proposal (epilogue and record writer share it).
+struct PropTerms { float score, siou, spts, sseg; int count; ProjBox pb; };
+
+__device__ __forceinline__ PropTerms prop_terms(const ScoreArgs &a, const float *cube, size_t o,
+                                                const WcrBox &bx, const Intr &K, float lo0, float hi0,
+                                                float lo1, float hi1, int npts, int area)
+{
+    PropTerms t;
+    t.count = __ldcg(a.ws.count + o);
+    t.pb = project_cube(cube, K, lo0, hi0, lo1, hi1, nullptr);
+    t.siou = iou_2d(bx.x1, bx.y1, bx.x2, bx.y2, t.pb);
+    t.spts = npts > 0 ? (float)t.count / (float)npts : 0.f;
+    t.sseg = 1.f;
+    if (a.sc.e_seg > 0) {
+        const int2 sc2 = __ldcg(a.ws.segcnt + o);
+        t.sseg = seg_ratio(sc2.x, sc2.y, area, a.sc.seg_mode);
+    }
+    t.score = (ipow(t.siou, a.sc.e_iou) * ipow(t.spts, a.sc.e_pts)) * ipow(t.sseg, a.sc.e_seg);
+    return t;
+}
+
+// ---- epilogue of (box, chunk) by ONE warp: terms -> score -> top-k -> records ----------
+__device__ __forceinline__ void chunk_epilogue_warp(const ScoreArgs &a, int b, const WcrBox &bx,
+                                                    const WcrImage &im, int chunk, float *wbuf, int lane)
+{
+    const float *__restrict__ cubes = a.cubes ? a.cubes : a.ws.cubes;
+    const Intr K = {im.fx, im.fy, im.cx, im.cy};
+    float lo0, hi0, lo1, hi1;
+    clamp_bounds(bx.clamp0, lo0, hi0);
+    clamp_bounds(bx.clamp1, lo1, hi1);
+    const int npts = __ldcg(a.ws.npts + (size_t)b * a.n_chunks + chunk);
+    if (a.out_npts && chunk == 0 && lane == 0) a.out_npts[b] = npts;
+    int area = 0;
+    if (a.sc.e_seg > 0) {
+        const Roi r1 = box_roi(bx, im.H, im.W, 1, true);
+        const int nrows = r1.ncols > 0 ? r1.nrows : 0, wpr = (r1.ncols + 31) >> 5;
+        const uint32_t *bits = a.seg_bits + a.seg_off[b];
+        for (int w = lane; w < nrows * wpr; w += 32) area += __popc(__ldg(bits + w));
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) area += __shfl_xor_sync(0xffffffffu, area, o);
+    }
+#pragma unroll 1
+    for (int i = 0; i < SC_CHUNK / 32; ++i) {
+        const int loc = i * 32 + lane, j = chunk * SC_CHUNK + loc;
+        float score = -INFINITY;
+        if (j < a.N) {
+            const size_t o = (size_t)b * a.N + j;
+            const float *src = cubes + o * 15;
+            float cube[15];
+#pragma unroll
+            for (int t = 0; t < 15; ++t) cube[t] = ld_stream(src + t);
+            const PropTerms t = prop_terms(a, cube, o, bx, K, lo0, hi0, lo1, hi1, npts, area);
+            score = t.score;
+            if (a.out_scores) a.out_scores[o] = t.score;
+            if (a.out_iou) a.out_iou[o] = t.siou;
+            if (a.out_seg) a.out_seg[o] = t.sseg;
+            if (a.out_count) a.out_count[o] = t.count;
+            if (a.out_proj) {
+                float *d = a.out_proj + o * 4;
+                d[0] = t.pb.x1; d[1] = t.pb.y1; d[2] = t.pb.x2; d[3] = t.pb.y2;
+            }
+        }
+        wbuf[loc] = score;
+    }
+    __syncwarp();
+    // k rounds of (max score, lowest index); winner r stays with lane r
+    int my_win = -1;
+    float my_wsc = 0.f;
+    for (int r = 0; r < a.k; ++r) {
+        float bvv = -INFINITY; int bi = 0x7fffffff;
+#pragma unroll 8
+        for (int i = 0; i < SC_CHUNK / 32; ++i) {
+            const int loc = i * 32 + lane;
+            const float vv = wbuf[loc];
+            if (vv > bvv) { bvv = vv; bi = loc; }   // ascending loc keeps the lowest index
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            const float ov = __shfl_xor_sync(0xffffffffu, bvv, o);
+            const int oi = __shfl_xor_sync(0xffffffffu, bi, o);
+            if (ov > bvv || (ov == bvv && oi < bi)) { bvv = ov; bi = oi; }
+        }
+        if (bvv == -INFINITY) bi = -1;
+        if (lane == r) { my_win = bi; my_wsc = bvv; }
+        if (bi >= 0 && (bi & 31) == lane) wbuf[bi] = -INFINITY;   // taken
+        __syncwarp();
+    }
+    float *rec_base = a.n_chunks == 1
+                          ? a.records + (size_t)b * a.k * WCR_RECORD_FLOATS
+                          : a.ws.cand + ((size_t)b * a.n_chunks + chunk) * a.k * WCR_RECORD_FLOATS;
+    if (lane < a.k) {
+        float *rec = rec_base + (size_t)lane * WCR_RECORD_FLOATS;
+        if (my_win < 0) {
+            rec[0] = __int_as_float(-1);
+            for (int i = 1; i < WCR_RECORD_FLOATS; ++i) rec[i] = 0.f;
+        } else {
+            const int j = chunk * SC_CHUNK + my_win;
+            const size_t o = (size_t)b * a.N + j;
+            const float *src = cubes + o * 15;
+            float cube[15];
+#pragma unroll
+            for (int t = 0; t < 15; ++t) cube[t] = __ldg(src + t);
+            const PropTerms t = prop_terms(a, cube, o, bx, K, lo0, hi0, lo1, hi1, npts, area);
+            rec[0] = __int_as_float(j);
+            rec[1] = my_wsc;
+#pragma unroll
+            for (int i = 0; i < 15; ++i) rec[2 + i] = cube[i];
+            rec[17] = t.siou; rec[18] = t.spts; rec[19] = t.sseg;
+        }
+    }
+    if (a.n_chunks > 1) {
+        __threadfence();
+        __syncwarp();
+        int last = 0;
+        if (lane == 0) last = (atomicAdd(a.ws.done_box + b, 1) == a.n_chunks - 1);
+        last = __shfl_sync(0xffffffffu, last, 0);
+        if (last) {
+            __threadfence();
+            warp_merge(a.ws.cand + (size_t)b * a.n_chunks * a.k * WCR_RECORD_FLOATS,
+                       a.n_chunks * a.k, a.k, a.records + (size_t)b * a.k * WCR_RECORD_FLOATS);
+        }
+    }
+}
+
+template <int WARPS, int MINB, int GRP>
+__global__ void __launch_bounds__(WARPS * 32, MINB) score_tiles_kernel(const ScoreArgs a)
+{
+    __shared__ __align__(16) float s_wbuf[WARPS][SC_CHUNK];   // per-warp scratch: hulls / scores
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    float *wbuf = s_wbuf[wid];
+    const int *__restrict__ prefix = a.ws.item_prefix;
+    const int total = prefix[a.n_boxes];
+    const bool use_pts = a.sc.e_pts > 0, use_seg = a.sc.e_seg > 0;
+
+    for (;;) {
+        int item = 0;
+        if (lane == 0) item = atomicAdd(a.ws.queue, 1);
+        item = __shfl_sync(0xffffffffu, item, 0);
+        if (item >= total) break;
+        int b = 0, hi = a.n_boxes;   // prefix[b] <= item < prefix[hi]
+        while (hi - b > 1) {
+            const int mid = (b + hi) >> 1;
+            if (prefix[mid] <= item) b = mid; else hi = mid;
+        }
+        const WcrBox bx = a.boxes[b];
+        const WcrImage im = a.images[bx.image];
+        const TileGeom tg = tile_geom(bx, im.H, im.W, a.sc.point_stride, use_pts, GRP);
+        const int per = tile_items_per_chunk(tg, use_seg);
+        const int local = item - prefix[b];
+        const int chunk = local / per, rem = local - chunk * per;
+        // seg items are spread evenly among the tile items of the chunk
+        const int nseg = use_seg ? TL_SEGS : 0;
+        const int seg_before = (int)(((long long)rem * nseg) / per);
+        const bool is_seg = (int)(((long long)(rem + 1) * nseg) / per) > seg_before;
+        if (is_seg) {
+            seg_item(a, b, bx, im, chunk, seg_before, wbuf, lane);
+        } else {
+            const int ti = rem - seg_before;
+            const int tile = ti / TL_SUBS, sub = ti - tile * TL_SUBS;
+            if (tile < tg.n_tiles) tile_item<GRP>(a, b, im, tg, chunk, tile, sub, wbuf, lane);
+        }
+        // ---- retire the item ------------------------------------------------------
+        __threadfence();
+        __syncwarp();
+        int last = 0;
+        if (lane == 0) last = (atomicAdd(a.ws.done_chunk + (size_t)b * a.n_chunks + chunk, 1) == per - 1);
+        last = __shfl_sync(0xffffffffu, last, 0);
+        if (!last) continue;
+        __threadfence();
+        chunk_epilogue_warp(a, b, bx, im, chunk, wbuf, lane);
+        __syncwarp();
+    }
+}
+
+}  // namespace wcr
