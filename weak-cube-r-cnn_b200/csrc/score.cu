@@ -732,11 +732,11 @@ extern "C" int wcr_score_topk(const WcrImage *images, const WcrBox *boxes, int n
     static int variant = -1;
     if (variant < 0) {  // development knob; the default is what DESIGN.md measures
         const char *ev = getenv("WCR_SCORE_VARIANT");
-        variant = ev ? atoi(ev) : 100;
+        variant = ev ? atoi(ev) : 211;
     }
     const bool tiles = variant >= 100;
     if (tiles) {
-        a.grp = (variant / 10) % 10 == 1 ? 8 : 4;
+        a.grp = 4 << ((variant / 10) % 10);   // x0y: 4, x1y: 8, x2y: 16, x3y: 32
         wcr::score_plan_tiles_kernel<<<1, 1024, 0, st>>>(images, boxes, n_boxes, nc, h_score->point_stride,
                                                          h_score->e_pts > 0, h_score->e_seg > 0, a.grp,
                                                          a.ws.item_prefix);
@@ -774,10 +774,20 @@ extern "C" int wcr_score_topk(const WcrImage *images, const WcrBox *boxes, int n
             WCR_CHECK_LAUNCH("score_prep_kernel");
         }
         switch (variant) {
-        case 101: wcr::score_tiles_kernel<4, 3, 4><<<sms * 3, 128, 0, st>>>(a); break;
-        case 110: wcr::score_tiles_kernel<8, 2, 8><<<sms * 2, 256, 0, st>>>(a); break;
-        case 111: wcr::score_tiles_kernel<4, 3, 8><<<sms * 3, 128, 0, st>>>(a); break;
-        default: wcr::score_tiles_kernel<8, 2, 4><<<sms * 2, 256, 0, st>>>(a); break;
+        case 101: wcr::score_tiles_kernel<4, 3, 4, false><<<sms * 3, 128, 0, st>>>(a); break;
+        case 110: wcr::score_tiles_kernel<8, 2, 8, false><<<sms * 2, 256, 0, st>>>(a); break;
+        case 111: wcr::score_tiles_kernel<4, 3, 8, false><<<sms * 3, 128, 0, st>>>(a); break;
+        case 210: wcr::score_tiles_kernel<8, 2, 8, true><<<sms * 2, 256, 0, st>>>(a); break;
+        case 220: wcr::score_tiles_kernel<8, 2, 16, true><<<sms * 2, 256, 0, st>>>(a); break;
+        case 230: wcr::score_tiles_kernel<8, 2, 32, true><<<sms * 2, 256, 0, st>>>(a); break;
+        case 221: wcr::score_tiles_kernel<4, 3, 16, true><<<sms * 3, 128, 0, st>>>(a); break;
+        case 211: wcr::score_tiles_kernel<4, 3, 8, true><<<sms * 3, 128, 0, st>>>(a); break;
+        case 231: wcr::score_tiles_kernel<4, 3, 32, true><<<sms * 3, 128, 0, st>>>(a); break;
+        case 121: wcr::score_tiles_kernel<4, 3, 16, false><<<sms * 3, 128, 0, st>>>(a); break;
+        case 131: wcr::score_tiles_kernel<4, 3, 32, false><<<sms * 3, 128, 0, st>>>(a); break;
+        case 120: wcr::score_tiles_kernel<8, 2, 16, false><<<sms * 2, 256, 0, st>>>(a); break;
+        case 130: wcr::score_tiles_kernel<8, 2, 32, false><<<sms * 2, 256, 0, st>>>(a); break;
+        default: wcr::score_tiles_kernel<8, 2, 4, false><<<sms * 2, 256, 0, st>>>(a); break;
         }
         WCR_CHECK_LAUNCH("score_tiles_kernel");
         return WCR_OK;

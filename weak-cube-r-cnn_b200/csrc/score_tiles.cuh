@@ -31,6 +31,7 @@ namespace wcr {
 constexpr int TL_PS = 512;       // proposals per tile item
 constexpr int TL_SUBS = SC_CHUNK / TL_PS;
 constexpr int TL_SEGS = SC_CHUNK / 32;   // seg items per chunk
+constexpr int TL_WBUF = 1024 + 3 * 32 * 4;   // per-warp scratch floats: a_u tile (also hull scratch / epilogue scores) + survivor slots
 
 
 // Tiling of a box's (sub-sampled) ROI: a tile is LR = 2^lrlog rows x (32/LR)*32

@@ -6,15 +6,19 @@ namespace wcr {
 
 __device__ __forceinline__ float4 ldg_f4(const float4 *p) { return __ldg(p); }
 
-// ---- tile item: one warp, 32 x 32 depth pixels in registers, proposals stream past ----
-// Pass 1 (lane = proposal): cull boxes against the tile, survivors compacted into the
-// warp's scratch list together with their column-group range. Pass 2 (lane = row):
-// survivors one at a time as warp-uniform parameters.
-template <int GRP>
+// ---- tile item: one warp, 32 x 32 depth pixels (z in registers, a_u in the warp's
+// shared scratch), proposals stream past in rounds of 32:
+//   lane = proposal: cull box against the tile -> ballot of survivors and of the column
+//                    groups each one reaches; survivors' constants -> shared slots
+//   lane = row:      survivors one at a time as warp-uniform parameters (broadcast LDS),
+//                    ballots and bit scans keep the control flow in uniform registers
+//   lane = proposal: one coalesced RED of the round's counts
+template <int GRP, bool F2>
 __device__ __forceinline__ void tile_item(const ScoreArgs &a, int b, const WcrImage &im,
                                           const TileGeom &tg, int chunk, int tile, int sub,
                                           float *wbuf, int lane)
 {
+    constexpr int NG = 32 / GRP;
     const int s = a.sc.point_stride;
     const int lrlog = tg.lrlog, LR = 1 << lrlog, nph = 32 >> lrlog;
     const int rt = tile / tg.n_ct, ct = tile - rt * tg.n_ct;
@@ -25,45 +29,35 @@ __device__ __forceinline__ void tile_item(const ScoreArgs &a, int b, const WcrIm
 
     const int chunk_n = min(SC_CHUNK, a.N - chunk * SC_CHUNK);
     const int n = min(TL_PS, chunk_n - sub * TL_PS);
+    if (n <= 0) return;
     const size_t first = (size_t)b * a.N + (size_t)chunk * SC_CHUNK + sub * TL_PS;
     const PParam *__restrict__ pp = a.ws.params + first;
-    unsigned *list = reinterpret_cast<unsigned *>(wbuf);   // <= TL_PS entries: j | g_lo << 16 | g_hi << 24
-    int n_keep = 0;
-    {
-        const int t_r1 = min(tr0 + LR, tg.nrows) - 1, t_c1 = min(tc0 + nph * 32, tg.ncols) - 1;
-        const int gshift = (GRP == 8 ? 3 : 2) + (5 - lrlog);   // log2(GRP * nph)
-        const int4 *__restrict__ cb = a.ws.cullbox + first;
-        for (int base = 0; base < n; base += 32) {
-            const int j = base + lane;
-            bool keep = false;
-            unsigned entry = 0;
-            if (j < n) {
-                const int4 bb = __ldg(cb + j);
-                keep = !(bb.x > t_c1 || bb.y < tc0 || bb.z > t_r1 || bb.w < tr0);
-                const int g_lo = (max(bb.x, tc0) - tc0) >> gshift, g_hi = (min(bb.y, t_c1) - tc0) >> gshift;
-                entry = (unsigned)j | (unsigned)g_lo << 16 | (unsigned)g_hi << 24;
-                if (keep) asm volatile("prefetch.global.L1 [%0];" ::"l"(pp + j));
-            }
-            const unsigned m = __ballot_sync(0xffffffffu, keep);
-            if (keep) list[n_keep + __popc(m & ((1u << lane) - 1u))] = entry;
-            n_keep += __popc(m);
-        }
-        __syncwarp();
-    }
+    const int4 *__restrict__ cbx = a.ws.cullbox + first;
+    int4 bb_next = __ldg(cbx + min(lane, n - 1));
 
     const float *drow = im.depth + (size_t)(row_ok ? v : 0) * im.depth_pitch;
-    float z[32], av[32];
+    float4 *av4 = reinterpret_cast<float4 *>(wbuf);          // [8][32]: a_u of registers 4*r4 .. 4*r4+3
+    float4 *slot = reinterpret_cast<float4 *>(wbuf + 1024);  // [3][32]: constants of the round's survivors
+    u64 z2[16];   // z of registers (2i, 2i+1) as one 64-bit pair
     int valid = 0;
 #pragma unroll
-    for (int r = 0; r < 32; ++r) {
-        const int col = tc0 + r * nph + phase;
-        const int u = tg.u0 + col * s;
-        av[r] = ((float)u - im.cx) / im.fx;
-        float d = 0.f;
-        if (row_ok && col < tg.ncols) d = __ldg(drow + u);
-        const bool ok = d > 0.f && d <= 3.402823466e38f;
-        z[r] = ok ? d : nanf_();
-        valid += ok;
+    for (int r4 = 0; r4 < 8; ++r4) {
+        float a4[4], z4[4];
+#pragma unroll
+        for (int t = 0; t < 4; ++t) {
+            const int r = r4 * 4 + t;
+            const int col = tc0 + r * nph + phase;
+            const int u = tg.u0 + col * s;
+            a4[t] = ((float)u - im.cx) / im.fx;
+            float d = 0.f;
+            if (row_ok && col < tg.ncols) d = __ldg(drow + u);
+            const bool ok = d > 0.f && d <= 3.402823466e38f;
+            z4[t] = ok ? d : nanf_();
+            valid += ok;
+        }
+        z2[r4 * 2] = pack2(z4[0], z4[1]);
+        z2[r4 * 2 + 1] = pack2(z4[2], z4[3]);
+        av4[r4 * 32 + lane] = make_float4(a4[0], a4[1], a4[2], a4[3]);
     }
     const float bv = ((float)v - im.cy) / im.fy;
     if (sub == 0) {
@@ -72,33 +66,98 @@ __device__ __forceinline__ void tile_item(const ScoreArgs &a, int b, const WcrIm
         if (lane == 0 && valid) atomicAdd(a.ws.npts + (size_t)b * a.n_chunks + chunk, valid);
     }
     int *__restrict__ cnt = a.ws.count + first;
+    const int t_r1 = min(tr0 + LR, tg.nrows) - 1, t_c1 = min(tc0 + nph * 32, tg.ncols) - 1;
+    const int gshift = (GRP == 32 ? 5 : GRP == 16 ? 4 : GRP == 8 ? 3 : 2) + (5 - lrlog);   // log2(GRP * nph)
 
 #pragma unroll 1
-    for (int i = 0; i < n_keep; ++i) {
-        // every lane reads the same word; the OR-reduction hands it back in a uniform
-        // register, which lets the group branches below compile to uniform branches
-        const unsigned e = __reduce_or_sync(0xffffffffu, list[i]);
-        const int j = e & 0xffffu;
-        const unsigned g_lo = (e >> 16) & 0xffu, g_hi = e >> 24;
-        const float4 pa = ldg_f4(&pp[j].a), pb = ldg_f4(&pp[j].b), pc = ldg_f4(&pp[j].c);
-        const float G0 = fmaf(pb.x, bv, pc.x), G1 = fmaf(pb.y, bv, pc.y), G2 = fmaf(pb.z, bv, pc.z);
-        float acc[4] = {0.f, 0.f, 0.f, 0.f};
+    for (int base = 0; base < n; base += 32) {
+        const int4 bb = bb_next;
+        const int j = base + lane;
+        bb_next = __ldg(cbx + min(j + 32, n - 1));
+        const bool keep = j < n && !(bb.x > t_c1 || bb.y < tc0 || bb.z > t_r1 || bb.w < tr0);
+        unsigned m = __ballot_sync(0xffffffffu, keep);
+        if (m == 0) continue;
+        const int g_lo = (max(bb.x, tc0) - tc0) >> gshift, g_hi = (min(bb.y, t_c1) - tc0) >> gshift;
+        unsigned mg[NG];
 #pragma unroll
-        for (int g = 0; g < 32 / GRP; ++g) {
-            if (g >= g_lo && g <= g_hi) {
-#pragma unroll
-                for (int t = 0; t < GRP; ++t) {
-                    const int r = g * GRP + t;
-                    const float q0 = fmaf(z[r], fmaf(pa.x, av[r], G0), pa.w);
-                    const float q1 = fmaf(z[r], fmaf(pa.y, av[r], G1), pb.w);
-                    const float q2 = fmaf(z[r], fmaf(pa.z, av[r], G2), pc.w);
-                    acc[t & 3] += inside_sat(q0, q1, q2);
-                }
-            }
+        for (int g = 0; g < NG; ++g) mg[g] = __ballot_sync(0xffffffffu, keep && g >= g_lo && g <= g_hi);
+        __syncwarp();   // the previous round's slot reads are done
+        if (keep) {
+            const float4 pa = ldg_f4(&pp[j].a), pb = ldg_f4(&pp[j].b), pc = ldg_f4(&pp[j].c);
+            slot[lane] = pa; slot[32 + lane] = pb; slot[64 + lane] = pc;
         }
-        const float sum = (acc[0] + acc[1]) + (acc[2] + acc[3]);
-        const int c = __reduce_add_sync(0xffffffffu, (int)sum);
-        if (lane == 0 && c) atomicAdd(cnt + j, c);
+        __syncwarp();
+        int mycnt = 0;
+        while (m) {
+            const int p = __ffs(m) - 1;
+            m &= m - 1;
+            const float4 ca = slot[p], cb4 = slot[32 + p], cc = slot[64 + p];
+            const float G0 = fmaf(cb4.x, bv, cc.x), G1 = fmaf(cb4.y, bv, cc.y), G2 = fmaf(cb4.z, bv, cc.z);
+            int c;
+            if (F2) {
+                // Blackwell packed FP32: registers (2i, 2i+1) of the tile are two points of the
+                // same row, so one fma.rn.f32x2 advances both tests (same IEEE roundings).
+                const u64 A0 = pack2(ca.x, ca.x), A1 = pack2(ca.y, ca.y), A2 = pack2(ca.z, ca.z);
+                const u64 N0 = pack2(ca.w, ca.w), N1 = pack2(cb4.w, cb4.w), N2 = pack2(cc.w, cc.w);
+                const u64 GG0 = pack2(G0, G0), GG1 = pack2(G1, G1), GG2 = pack2(G2, G2);
+                u64 acc2[4] = {pack2(0.f, 0.f), pack2(0.f, 0.f), pack2(0.f, 0.f), pack2(0.f, 0.f)};
+                // steps of 8 registers (two LDS.128), the next step's a_u loaded before this
+                // step's arithmetic so that the shared-memory latency hides behind 12
+                // independent FFMA2 chains
+                constexpr int SPG = GRP / 8;             // steps per group
+                const ulonglong2 *avq = reinterpret_cast<const ulonglong2 *>(av4) + lane;
+                ulonglong2 n0 = avq[0], n1 = avq[32];
+#pragma unroll
+                for (int st = 0; st < 4; ++st) {
+                    const ulonglong2 c0 = n0, c1 = n1;
+                    if (st < 3) { n0 = avq[(2 * st + 2) * 32]; n1 = avq[(2 * st + 3) * 32]; }
+                    if ((mg[st / SPG] >> p) & 1u) {
+                        const u64 avp[4] = {c0.x, c0.y, c1.x, c1.y};
+#pragma unroll
+                        for (int t = 0; t < 4; ++t) {
+                            const u64 zz = z2[st * 4 + t];
+                            float q0a, q0b, q1a, q1b, q2a, q2b;
+                            unpack2(ffma2(zz, ffma2(A0, avp[t], GG0), N0), q0a, q0b);
+                            unpack2(ffma2(zz, ffma2(A1, avp[t], GG1), N1), q1a, q1b);
+                            unpack2(ffma2(zz, ffma2(A2, avp[t], GG2), N2), q2a, q2b);
+                            acc2[t] = fadd2(acc2[t], pack2(inside_sat(q0a, q1a, q2a), inside_sat(q0b, q1b, q2b)));
+                        }
+                    }
+                }
+                acc2[0] = fadd2(acc2[0], acc2[2]);
+                acc2[1] = fadd2(acc2[1], acc2[3]);
+                float s0, s1, s2, s3;
+                unpack2(acc2[0], s0, s1);
+                unpack2(acc2[1], s2, s3);
+                c = (int)((s0 + s1) + (s2 + s3));
+            } else {
+                float acc[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+                for (int g = 0; g < NG; ++g) {
+                    if ((mg[g] >> p) & 1u) {
+#pragma unroll
+                        for (int h = 0; h < GRP / 4; ++h) {
+                            const float4 a4 = av4[(g * (GRP / 4) + h) * 32 + lane];
+                            const float avv[4] = {a4.x, a4.y, a4.z, a4.w};
+#pragma unroll
+                            for (int t = 0; t < 4; ++t) {
+                                float zlo, zhi;
+                                unpack2(z2[(g * GRP + h * 4 + t) / 2], zlo, zhi);
+                                const float zr = (t & 1) ? zhi : zlo;
+                                const float q0 = fmaf(zr, fmaf(ca.x, avv[t], G0), ca.w);
+                                const float q1 = fmaf(zr, fmaf(ca.y, avv[t], G1), cb4.w);
+                                const float q2 = fmaf(zr, fmaf(ca.z, avv[t], G2), cc.w);
+                                acc[t] += inside_sat(q0, q1, q2);
+                            }
+                        }
+                    }
+                }
+                c = (int)((acc[0] + acc[1]) + (acc[2] + acc[3]));
+            }
+            c = __reduce_add_sync(0xffffffffu, c);
+            if (lane == p) mycnt = c;
+        }
+        if (mycnt) atomicAdd(cnt + j, mycnt);
     }
     __syncwarp();
 }
@@ -285,10 +344,10 @@ __device__ __forceinline__ void chunk_epilogue_warp(const ScoreArgs &a, int b, c
     }
 }
 
-template <int WARPS, int MINB, int GRP>
+template <int WARPS, int MINB, int GRP, bool F2>
 __global__ void __launch_bounds__(WARPS * 32, MINB) score_tiles_kernel(const ScoreArgs a)
 {
-    __shared__ __align__(16) float s_wbuf[WARPS][SC_CHUNK];   // per-warp scratch: hulls / scores
+    __shared__ __align__(16) float s_wbuf[WARPS][TL_WBUF];   // per-warp scratch: hulls / scores
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
     float *wbuf = s_wbuf[wid];
     const int *__restrict__ prefix = a.ws.item_prefix;
@@ -320,7 +379,7 @@ __global__ void __launch_bounds__(WARPS * 32, MINB) score_tiles_kernel(const Sco
         } else {
             const int ti = rem - seg_before;
             const int tile = ti / TL_SUBS, sub = ti - tile * TL_SUBS;
-            if (tile < tg.n_tiles) tile_item<GRP>(a, b, im, tg, chunk, tile, sub, wbuf, lane);
+            if (tile < tg.n_tiles) tile_item<GRP, F2>(a, b, im, tg, chunk, tile, sub, wbuf, lane);
         }
         // ---- retire the item ------------------------------------------------------
         __threadfence();
