@@ -198,6 +198,65 @@ def test_score_edge_cases(cuda_lib):
         score_topk(shard, boxes, cubes, cfg=ScoreConfig())   # CPU tensor: no fallback
 
 
+@pytest.mark.parametrize("stride", [1, 3])
+def test_score_culling_adversarial(cuda_lib, stride):
+    """The tile path skips every (proposal, pixel) pair the proposal's projected box cannot
+    reach. The oracle never culls, so bit-exact counts on cubes chosen to break a careless
+    cull (arbitrary rotations, corners behind / on / just in front of the camera plane,
+    cubes that swallow the camera, sliver cubes, boxes of every tile shape) prove the cull
+    is conservative."""
+    from wcr.images import ImageShard
+    from wcr.proposals import BoxTable, score_topk, ScoreConfig
+    from wcr import synth
+    H, W = 300, 500
+    im = synth.make_image(11, H, W, n_boxes=1, dummy_ground=False)
+    im["depth"][::7, ::5] *= 0.1                      # a lattice of very near points
+    boxes_t = torch.tensor([[3.0, 2.0, 497.0, 41.0],      # wide and flat  -> 8-row tiles
+                            [10.5, 5.0, 27.0, 299.0],     # narrow and tall -> 32-row tiles
+                            [100.0, 60.0, 330.0, 250.0],  # large
+                            [200.2, 100.1, 233.9, 117.5],  # small
+                            [0.0, 0.0, 500.0, 300.0]])    # the whole image
+    nb = len(boxes_t)
+    shard = ImageShard([im["depth"].cuda()], None, [im["K"]])
+    boxes = BoxTable(shard, [boxes_t], [torch.zeros(nb, dtype=torch.long)])
+    g = torch.Generator().manual_seed(5)
+    N = 700
+    f = float(im["K"][0, 0])
+    cubes = torch.zeros(nb, N, 15)
+    # centres lifted from random pixels (inside and outside the box) at random depths
+    u = torch.rand(nb, N, generator=g) * 1.4 * W - 0.2 * W
+    v = torch.rand(nb, N, generator=g) * 1.4 * H - 0.2 * H
+    zc = torch.exp(torch.rand(nb, N, generator=g) * 5.0 - 2.5)            # 0.08 .. 12 m
+    cubes[:, :, 0] = zc * (u - W / 2) / f
+    cubes[:, :, 1] = zc * (v - H / 2) / f
+    cubes[:, :, 2] = zc
+    cubes[:, :, 3:6] = torch.exp(torch.rand(nb, N, 3, generator=g) * 6.0 - 4.0)   # 0.02 .. 7.4 m
+    q = torch.randn(nb, N, 4, generator=g)
+    q = q / q.norm(dim=-1, keepdim=True)
+    w_, x_, y_, z_ = q.unbind(-1)
+    R = torch.stack([1 - 2 * (y_ * y_ + z_ * z_), 2 * (x_ * y_ - z_ * w_), 2 * (x_ * z_ + y_ * w_),
+                     2 * (x_ * y_ + z_ * w_), 1 - 2 * (x_ * x_ + z_ * z_), 2 * (y_ * z_ - x_ * w_),
+                     2 * (x_ * z_ - y_ * w_), 2 * (y_ * z_ + x_ * w_), 1 - 2 * (x_ * x_ + y_ * y_)], -1)
+    cubes[:, :, 6:] = R
+    cubes[:, 0, 0:3] = torch.tensor([0.0, 0.0, 0.5])      # swallows the camera
+    cubes[:, 0, 3:6] = 3.0
+    cubes[:, 1, 2] = -1.0                                  # entirely behind the camera
+    cubes[:, 2, 2] = 0.0105                                # nearest corner within a hair of the 1 cm guard
+    cubes[:, 2, 3:6] = 0.001
+    cubes[:, 3, 3] = float("nan")
+    cubes[:, 4, 0] = float("inf")
+    res = score_topk(shard, boxes, cubes.cuda(), cfg=ScoreConfig(k=16, point_stride=stride), want_all=True)
+    total = 0
+    for b in range(nb):
+        ref = oc.score_box(im["depth"].numpy(), im["K"].numpy(), boxes_t[b].numpy(), (H, W),
+                           cubes[b].numpy(), stride)
+        assert int(res["npts"][b]) == ref["npts"]
+        assert np.array_equal(res["count"][b].cpu().numpy(), ref["count"]), b
+        assert np.array_equal(res["idx"][b].cpu().numpy(), oc.topk(ref["score"], 16))
+        total += int(ref["count"].sum())
+    assert total > 10000   # the cubes do hold points
+
+
 @pytest.mark.parametrize("N,H,W,mode,eseg", [(600, 480, 640, 0, 1), (300, 375, 1242, 1, 1),
                                              (1500, 240, 320, 0, 2)])
 def test_score_seg_term_bit_exact(cuda_lib, N, H, W, mode, eseg):
