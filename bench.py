@@ -166,11 +166,11 @@ def run_reference(args):
 
 def ncu_traffic_bytes():
     """dram__bytes_read.sum + dram__bytes_write.sum of one scoring launch, from the
-    newest committed `ncu --set full` summary (profiles/score_items_r*.txt); None when
+    newest committed `ncu --set full` summary (profiles/score_tiles_r*.txt); None when
     there is none. A profiler-derived figure, reported beside the event timing."""
     import glob
     import re
-    files = sorted(glob.glob(os.path.join(ROOT, "profiles", "score_items_r*.txt")))
+    files = sorted(glob.glob(os.path.join(ROOT, "profiles", "score_tiles_r*.txt")))
     if not files:
         return None
     unit = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
@@ -264,6 +264,7 @@ def run_wcr(args):
     full = score_topk(runner.shard, runner.boxes, None, NPROP, runner.score_cfg, priors=runner.priors,
                       normals=runner.normals, z0=z0, seed=1234, seg=runner.seg, want_all=True)
     tests_per_launch = float(full["npts"].sum().item()) * NPROP
+    executed_per_launch = float(full["workspace"].executed_tests())   # after the projected-box cull
     del full
 
     for _ in range(max(args.warmup, 3)):
@@ -353,7 +354,7 @@ def run_wcr(args):
                     "h2d_bytes_per_step": runner.h2d_bytes, "d2h_bytes_per_step": runner.d2h_bytes},
             "gpu_launches": int(launches),
             "clocks": clocks,
-            "roofline": {"bound": "fp32", "kernel": "score_topk_kernel", "achieved": achieved,
+            "roofline": {"bound": "fp32", "kernel": "score_tiles_kernel", "achieved": achieved,
                          "peak": fp32_probe_tflops, "unit": "TFLOP/s",
                          "frac": achieved / fp32_probe_tflops,
                          "peak_source": "FFMA probe kernel timed in this run (MEASURED_PEAKS.json has no FP32 figure)",
@@ -361,7 +362,8 @@ def run_wcr(args):
                          "point_tests_per_s": tests_per_launch / (score_ms * 1e-3),
                          "alg_flop_per_test": ALG_FLOP_PER_TEST,
                          "executed_flop_per_test": EXEC_FLOP_PER_TEST,
-                         "frac_executed": achieved * EXEC_FLOP_PER_TEST / ALG_FLOP_PER_TEST / fp32_probe_tflops,
+                         "tests_executed_frac": executed_per_launch / max(tests_per_launch, 1.0),
+                         "frac_executed": EXEC_FLOP_PER_TEST * executed_per_launch / (score_ms * 1e-3) / 1e12 / fp32_probe_tflops,
                          "kernel_ms": score_ms,
                          "kernel_share_of_step": score_ms * args.steps / step_ms,
                          "traffic": ncu_traffic_bytes()},

@@ -195,7 +195,10 @@ int wcr_sample_cubes(const WcrImage *images, const WcrBox *boxes, int n_boxes,
  *   optional per-proposal outputs (NULL to skip), all [n_boxes][N]:
  *     out_scores, out_iou, out_seg, out_count (int32), out_proj [n_boxes][N][4]
  *   out_npts  [n_boxes] valid depth points per ROI (P_b), optional
- *   ws        workspace, wcr_score_workspace_bytes(n_boxes, N, k) bytes */
+ *   ws        workspace, wcr_score_workspace_bytes(n_boxes, N, k) bytes, 256-byte aligned.
+ *             After the call the uint64 at byte 8 holds the number of point tests the
+ *             kernel issued (pairs the projected-box cull could not rule out; the
+ *             counts are those of the unculled evaluation) -- bench.py's frac_executed. */
 int64_t wcr_score_workspace_bytes(int n_boxes, int N, int k);
 int wcr_score_topk(const WcrImage *images, const WcrBox *boxes, int n_boxes,
                    const float *cubes, int N,

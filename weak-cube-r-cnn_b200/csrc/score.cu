@@ -133,6 +133,7 @@ struct PParam;   // score_tiles.cuh
 // Device workspace layout (caller-owned, zeroed by cudaMemsetAsync up to `zero_bytes`).
 struct ScoreWs {
     int *queue;          // [1]   next item
+    unsigned long long *executed;  // [1] at byte 8: point tests issued (tile path, after culling)
     int *item_prefix;    // [n_boxes + 1] exclusive prefix of items per box
     int *done_chunk;     // [n_boxes][n_chunks] retired items per (box, chunk)
     int *done_box;       // [n_boxes] retired chunks per box
@@ -682,7 +683,7 @@ size_t carve(void *base, int n_boxes, int N, int k, bool need_cubes, bool need_s
     int4 *cullbox = (int4 *)take((size_t)n_boxes * N * sizeof(int4));
     if (ws) {
         ws->segcnt = segcnt; ws->params = params; ws->cullbox = cullbox;
-        ws->queue = queue; ws->done_chunk = done_chunk; ws->done_box = done_box; ws->npts = npts;
+        ws->queue = queue; ws->executed = (unsigned long long *)(queue ? (char *)queue + 8 : nullptr); ws->done_chunk = done_chunk; ws->done_box = done_box; ws->npts = npts;
         ws->count = count; ws->item_prefix = prefix; ws->cand = cand; ws->cubes = cubes;
     }
     return off;
@@ -774,36 +775,19 @@ extern "C" int wcr_score_topk(const WcrImage *images, const WcrBox *boxes, int n
             WCR_CHECK_LAUNCH("score_prep_kernel");
         }
         switch (variant) {
-        case 101: wcr::score_tiles_kernel<4, 3, 4, false><<<sms * 3, 128, 0, st>>>(a); break;
-        case 110: wcr::score_tiles_kernel<8, 2, 8, false><<<sms * 2, 256, 0, st>>>(a); break;
-        case 111: wcr::score_tiles_kernel<4, 3, 8, false><<<sms * 3, 128, 0, st>>>(a); break;
-        case 210: wcr::score_tiles_kernel<8, 2, 8, true><<<sms * 2, 256, 0, st>>>(a); break;
-        case 220: wcr::score_tiles_kernel<8, 2, 16, true><<<sms * 2, 256, 0, st>>>(a); break;
-        case 230: wcr::score_tiles_kernel<8, 2, 32, true><<<sms * 2, 256, 0, st>>>(a); break;
-        case 221: wcr::score_tiles_kernel<4, 3, 16, true><<<sms * 3, 128, 0, st>>>(a); break;
-        case 211: wcr::score_tiles_kernel<4, 3, 8, true><<<sms * 3, 128, 0, st>>>(a); break;
-        case 231: wcr::score_tiles_kernel<4, 3, 32, true><<<sms * 3, 128, 0, st>>>(a); break;
-        case 121: wcr::score_tiles_kernel<4, 3, 16, false><<<sms * 3, 128, 0, st>>>(a); break;
-        case 131: wcr::score_tiles_kernel<4, 3, 32, false><<<sms * 3, 128, 0, st>>>(a); break;
+        case 100: wcr::score_tiles_kernel<8, 2, 4, false><<<sms * 2, 256, 0, st>>>(a); break;   // scalar FFMA
         case 120: wcr::score_tiles_kernel<8, 2, 16, false><<<sms * 2, 256, 0, st>>>(a); break;
-        case 130: wcr::score_tiles_kernel<8, 2, 32, false><<<sms * 2, 256, 0, st>>>(a); break;
-        default: wcr::score_tiles_kernel<8, 2, 4, false><<<sms * 2, 256, 0, st>>>(a); break;
+        case 210: wcr::score_tiles_kernel<8, 2, 8, true><<<sms * 2, 256, 0, st>>>(a); break;    // FFMA2, 16 warps/SM
+        case 221: wcr::score_tiles_kernel<4, 3, 16, true><<<sms * 3, 128, 0, st>>>(a); break;
+        case 231: wcr::score_tiles_kernel<4, 3, 32, true><<<sms * 3, 128, 0, st>>>(a); break;   // no in-tile culling
+        default: wcr::score_tiles_kernel<4, 3, 8, true><<<sms * 3, 128, 0, st>>>(a); break;     // 211
         }
         WCR_CHECK_LAUNCH("score_tiles_kernel");
         return WCR_OK;
     }
     switch (variant) {
-    case 2: wcr::score_items_kernel<2, 2, 256><<<sms * 2, 256, 0, st>>>(a); break;
-    case 10: wcr::score_items_kernel<0, 3, 256><<<sms * 3, 256, 0, st>>>(a); break;
-    case 11: wcr::score_items_kernel<1, 3, 256><<<sms * 3, 256, 0, st>>>(a); break;
-    case 12: wcr::score_items_kernel<2, 3, 256><<<sms * 3, 256, 0, st>>>(a); break;
-    case 0: wcr::score_items_kernel<0, 2, 256><<<sms * 2, 256, 0, st>>>(a); break;
-    case 5: wcr::score_items_kernel<5, 2, 256><<<sms * 2, 256, 0, st>>>(a); break;
-    case 14: wcr::score_items_kernel<4, 3, 256><<<sms * 3, 256, 0, st>>>(a); break;
-    case 24: wcr::score_items_kernel<4, 2, 128><<<sms * 2, 128, 0, st>>>(a); break;
-    case 34: wcr::score_items_kernel<4, 3, 128><<<sms * 3, 128, 0, st>>>(a); break;
-    case 44: wcr::score_items_kernel<4, 4, 128><<<sms * 4, 128, 0, st>>>(a); break;
     case 1: wcr::score_items_kernel<1, 2, 256><<<sms * 2, 256, 0, st>>>(a); break;
+    case 24: wcr::score_items_kernel<4, 2, 128><<<sms * 2, 128, 0, st>>>(a); break;
     default: wcr::score_items_kernel<4, 2, 256><<<sms * 2, 256, 0, st>>>(a); break;
     }
     WCR_CHECK_LAUNCH("score_items_kernel");

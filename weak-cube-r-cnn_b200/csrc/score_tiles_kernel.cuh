@@ -66,6 +66,7 @@ __device__ __forceinline__ void tile_item(const ScoreArgs &a, int b, const WcrIm
         if (lane == 0 && valid) atomicAdd(a.ws.npts + (size_t)b * a.n_chunks + chunk, valid);
     }
     int *__restrict__ cnt = a.ws.count + first;
+    int executed = 0;
     const int t_r1 = min(tr0 + LR, tg.nrows) - 1, t_c1 = min(tc0 + nph * 32, tg.ncols) - 1;
     const int gshift = (GRP == 32 ? 5 : GRP == 16 ? 4 : GRP == 8 ? 3 : 2) + (5 - lrlog);   // log2(GRP * nph)
 
@@ -78,6 +79,7 @@ __device__ __forceinline__ void tile_item(const ScoreArgs &a, int b, const WcrIm
         unsigned m = __ballot_sync(0xffffffffu, keep);
         if (m == 0) continue;
         const int g_lo = (max(bb.x, tc0) - tc0) >> gshift, g_hi = (min(bb.y, t_c1) - tc0) >> gshift;
+        if (keep) executed += (g_hi - g_lo + 1) * GRP;   // registers this proposal is tested on
         unsigned mg[NG];
 #pragma unroll
         for (int g = 0; g < NG; ++g) mg[g] = __ballot_sync(0xffffffffu, keep && g >= g_lo && g <= g_hi);
@@ -159,6 +161,10 @@ __device__ __forceinline__ void tile_item(const ScoreArgs &a, int b, const WcrIm
         }
         if (mycnt) atomicAdd(cnt + j, mycnt);
     }
+    // bookkeeping for the roofline report: lane-tests actually issued by this item
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) executed += __shfl_xor_sync(0xffffffffu, executed, o);
+    if (lane == 0) atomicAdd(a.ws.executed, (unsigned long long)executed * 32ull);
     __syncwarp();
 }
 

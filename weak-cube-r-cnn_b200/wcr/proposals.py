@@ -201,6 +201,12 @@ class ScoreWorkspace:
             (n_boxes, k, RECORD_FLOATS), dtype=torch.float32, device=device)
         self.n_boxes, self.N, self.k = n_boxes, N, k
 
+    def executed_tests(self) -> int:
+        """Point tests the last ``score_topk`` on this workspace actually issued (after the
+        projected-box cull; padding lanes included). The library keeps the counter at byte 8
+        of the workspace (include/wcr.h). Synchronises."""
+        return int(self.ws[8:16].view(torch.int64).item())
+
 
 def score_topk(shard: ImageShard, boxes: BoxTable, cubes: torch.Tensor | None, N: int | None = None,
                cfg: ScoreConfig | None = None, *, priors=None, normals=None, z0=None,
@@ -234,6 +240,7 @@ def score_topk(shard: ImageShard, boxes: BoxTable, cubes: torch.Tensor | None, N
     assert workspace.n_boxes >= nb and workspace.N == N and workspace.k == cfg.k
     rec = workspace.records
     outs = {}
+    outs["workspace"] = workspace
     if want_all:
         outs["scores"] = torch.empty((nb, N), dtype=torch.float32, device=dev)
         outs["iou"] = torch.empty((nb, N), dtype=torch.float32, device=dev)
