@@ -733,7 +733,7 @@ extern "C" int wcr_score_topk(const WcrImage *images, const WcrBox *boxes, int n
     static int variant = -1;
     if (variant < 0) {  // development knob; the default is what DESIGN.md measures
         const char *ev = getenv("WCR_SCORE_VARIANT");
-        variant = ev ? atoi(ev) : 211;
+        variant = ev ? atoi(ev) : 411;
     }
     const bool tiles = variant >= 100;
     if (tiles) {
@@ -779,8 +779,11 @@ extern "C" int wcr_score_topk(const WcrImage *images, const WcrBox *boxes, int n
         case 120: wcr::score_tiles_kernel<8, 2, 16, false><<<sms * 2, 256, 0, st>>>(a); break;
         case 210: wcr::score_tiles_kernel<8, 2, 8, true><<<sms * 2, 256, 0, st>>>(a); break;    // FFMA2, 16 warps/SM
         case 221: wcr::score_tiles_kernel<4, 3, 16, true><<<sms * 3, 128, 0, st>>>(a); break;
+        case 421: wcr::score_tiles_kernel<4, 3, 16, true, true><<<sms * 3, 128, 0, st>>>(a); break;
+        case 410: wcr::score_tiles_kernel<8, 2, 8, true, true><<<sms * 2, 256, 0, st>>>(a); break;
         case 231: wcr::score_tiles_kernel<4, 3, 32, true><<<sms * 3, 128, 0, st>>>(a); break;   // no in-tile culling
-        default: wcr::score_tiles_kernel<4, 3, 8, true><<<sms * 3, 128, 0, st>>>(a); break;     // 211
+        case 211: wcr::score_tiles_kernel<4, 3, 8, true><<<sms * 3, 128, 0, st>>>(a); break;    // FFMA.SAT indicator
+        default: wcr::score_tiles_kernel<4, 3, 8, true, true><<<sms * 3, 128, 0, st>>>(a); break;   // 411
         }
         WCR_CHECK_LAUNCH("score_tiles_kernel");
         return WCR_OK;

@@ -6,6 +6,20 @@ namespace wcr {
 
 __device__ __forceinline__ float4 ldg_f4(const float4 *p) { return __ldg(p); }
 
+// acc + (m > 2^11 or m is NaN ? 1 : 0) for m = max_k |q_k| >= 0 on the INTEGER pipe: non-negative
+// floats order like their bit patterns (NaN above everything), so the sign bit of
+// bits(2^11) - bits(m) is the "outside" indicator; IADD3 + LEA.HI, no FMA-pipe slot.
+__device__ __forceinline__ int add_outside(int acc, float q0, float q1, float q2)
+{
+    float m;
+    asm("max.f32 %0, %1, %2, %3;" : "=f"(m) : "f"(fabsf(q0)), "f"(fabsf(q1)), "f"(fabsf(q2)));
+    int t;
+    unsigned sgn;
+    asm("sub.s32 %0, 0x45000000, %1;" : "=r"(t) : "r"(__float_as_int(m)));
+    asm("shr.u32 %0, %1, 31;" : "=r"(sgn) : "r"(t));
+    return acc + (int)sgn;
+}
+
 // ---- tile item: one warp, 32 x 32 depth pixels (z in registers, a_u in the warp's
 // shared scratch), proposals stream past in rounds of 32:
 //   lane = proposal: cull box against the tile -> ballot of survivors and of the column
@@ -13,7 +27,7 @@ __device__ __forceinline__ float4 ldg_f4(const float4 *p) { return __ldg(p); }
 //   lane = row:      survivors one at a time as warp-uniform parameters (broadcast LDS),
 //                    ballots and bit scans keep the control flow in uniform registers
 //   lane = proposal: one coalesced RED of the round's counts
-template <int GRP, bool F2>
+template <int GRP, bool F2, bool ICNT>
 __device__ __forceinline__ void tile_item(const ScoreArgs &a, int b, const WcrImage &im,
                                           const TileGeom &tg, int chunk, int tile, int sub,
                                           float *wbuf, int lane)
@@ -102,11 +116,14 @@ __device__ __forceinline__ void tile_item(const ScoreArgs &a, int b, const WcrIm
                 const u64 A0 = pack2(ca.x, ca.x), A1 = pack2(ca.y, ca.y), A2 = pack2(ca.z, ca.z);
                 const u64 N0 = pack2(ca.w, ca.w), N1 = pack2(cb4.w, cb4.w), N2 = pack2(cc.w, cc.w);
                 const u64 GG0 = pack2(G0, G0), GG1 = pack2(G1, G1), GG2 = pack2(G2, G2);
+                // steps of 8 registers (two LDS.128 of a_u, the next step's issued before this
+                // step's arithmetic; with 168 registers ptxas hoists the whole a_u tile out of
+                // the survivor loop). ICNT: indicator and counter on the integer pipe ("outside"
+                // bits are summed and taken from the number of registers visited); otherwise
+                // FFMA.SAT indicator + FADD2 counter on the FMA pipe.
+                int oc[4] = {0, 0, 0, 0}, visited = 0;
                 u64 acc2[4] = {pack2(0.f, 0.f), pack2(0.f, 0.f), pack2(0.f, 0.f), pack2(0.f, 0.f)};
-                // steps of 8 registers (two LDS.128), the next step's a_u loaded before this
-                // step's arithmetic so that the shared-memory latency hides behind 12
-                // independent FFMA2 chains
-                constexpr int SPG = GRP / 8;             // steps per group
+                constexpr int SPG = GRP / 8;   // steps per column group
                 const ulonglong2 *avq = reinterpret_cast<const ulonglong2 *>(av4) + lane;
                 ulonglong2 n0 = avq[0], n1 = avq[32];
 #pragma unroll
@@ -114,6 +131,7 @@ __device__ __forceinline__ void tile_item(const ScoreArgs &a, int b, const WcrIm
                     const ulonglong2 c0 = n0, c1 = n1;
                     if (st < 3) { n0 = avq[(2 * st + 2) * 32]; n1 = avq[(2 * st + 3) * 32]; }
                     if ((mg[st / SPG] >> p) & 1u) {
+                        visited += 8;
                         const u64 avp[4] = {c0.x, c0.y, c1.x, c1.y};
 #pragma unroll
                         for (int t = 0; t < 4; ++t) {
@@ -122,16 +140,25 @@ __device__ __forceinline__ void tile_item(const ScoreArgs &a, int b, const WcrIm
                             unpack2(ffma2(zz, ffma2(A0, avp[t], GG0), N0), q0a, q0b);
                             unpack2(ffma2(zz, ffma2(A1, avp[t], GG1), N1), q1a, q1b);
                             unpack2(ffma2(zz, ffma2(A2, avp[t], GG2), N2), q2a, q2b);
-                            acc2[t] = fadd2(acc2[t], pack2(inside_sat(q0a, q1a, q2a), inside_sat(q0b, q1b, q2b)));
+                            if (ICNT) {
+                                oc[t] = add_outside(oc[t], q0a, q1a, q2a);
+                                oc[t] = add_outside(oc[t], q0b, q1b, q2b);
+                            } else {
+                                acc2[t] = fadd2(acc2[t], pack2(inside_sat(q0a, q1a, q2a), inside_sat(q0b, q1b, q2b)));
+                            }
                         }
                     }
                 }
-                acc2[0] = fadd2(acc2[0], acc2[2]);
-                acc2[1] = fadd2(acc2[1], acc2[3]);
-                float s0, s1, s2, s3;
-                unpack2(acc2[0], s0, s1);
-                unpack2(acc2[1], s2, s3);
-                c = (int)((s0 + s1) + (s2 + s3));
+                if (ICNT) {
+                    c = visited - ((oc[0] + oc[1]) + (oc[2] + oc[3]));
+                } else {
+                    acc2[0] = fadd2(acc2[0], acc2[2]);
+                    acc2[1] = fadd2(acc2[1], acc2[3]);
+                    float s0, s1, s2, s3;
+                    unpack2(acc2[0], s0, s1);
+                    unpack2(acc2[1], s2, s3);
+                    c = (int)((s0 + s1) + (s2 + s3));
+                }
             } else {
                 float acc[4] = {0.f, 0.f, 0.f, 0.f};
 #pragma unroll
@@ -350,15 +377,15 @@ __device__ __forceinline__ void chunk_epilogue_warp(const ScoreArgs &a, int b, c
     }
 }
 
-template <int WARPS, int MINB, int GRP, bool F2>
+template <int WARPS, int MINB, int GRP, bool F2, bool ICNT = false>
 __global__ void __launch_bounds__(WARPS * 32, MINB) score_tiles_kernel(const ScoreArgs a)
 {
     __shared__ __align__(16) float s_wbuf[WARPS][TL_WBUF];   // per-warp scratch: hulls / scores
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
     float *wbuf = s_wbuf[wid];
     const int *__restrict__ prefix = a.ws.item_prefix;
-    const int total = prefix[a.n_boxes];
     const bool use_pts = a.sc.e_pts > 0, use_seg = a.sc.e_seg > 0;
+    const int total = prefix[a.n_boxes];
 
     for (;;) {
         int item = 0;
@@ -376,7 +403,9 @@ __global__ void __launch_bounds__(WARPS * 32, MINB) score_tiles_kernel(const Sco
         const int per = tile_items_per_chunk(tg, use_seg);
         const int local = item - prefix[b];
         const int chunk = local / per, rem = local - chunk * per;
-        // seg items are spread evenly among the tile items of the chunk
+        // seg items are spread evenly among the tile items of the chunk: the two kinds of
+        // item load different pipes (integer / FMA) and overlap well on one SM (queueing
+        // all seg items first was measured 0.5 ms slower)
         const int nseg = use_seg ? TL_SEGS : 0;
         const int seg_before = (int)(((long long)rem * nseg) / per);
         const bool is_seg = (int)(((long long)(rem + 1) * nseg) / per) > seg_before;
@@ -385,7 +414,7 @@ __global__ void __launch_bounds__(WARPS * 32, MINB) score_tiles_kernel(const Sco
         } else {
             const int ti = rem - seg_before;
             const int tile = ti / TL_SUBS, sub = ti - tile * TL_SUBS;
-            if (tile < tg.n_tiles) tile_item<GRP, F2>(a, b, im, tg, chunk, tile, sub, wbuf, lane);
+            if (tile < tg.n_tiles) tile_item<GRP, F2, ICNT>(a, b, im, tg, chunk, tile, sub, wbuf, lane);
         }
         // ---- retire the item ------------------------------------------------------
         __threadfence();
