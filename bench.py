@@ -236,6 +236,9 @@ def run_wcr(args):
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
     if world > 1:
+        # NCCL logs (its version banner included) go to stdout by default: keep stdout for the
+        # one JSON line the driver parses
+        os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
         dist.init_process_group("nccl", device_id=dev)
     lib = _abi.load()                      # raises if the CUDA library is not built
     _abi.check(lib.wcr_device_check(), "wcr_device_check")
