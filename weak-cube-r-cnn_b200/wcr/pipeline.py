@@ -119,3 +119,76 @@ class ShardRunner:
         self.download()
         torch.cuda.current_stream(self.device).synchronize()
         return self.h_records
+
+
+class ShardPipeline:
+    """Double-buffered end-to-end driver: while shard i is being scored, shard i + 1 is
+    uploaded and the records of shard i - 1 are downloaded (three CUDA streams, events
+    between them; no host synchronisation inside ``submit``).
+
+        pipe = ShardPipeline([runner_a, runner_b])
+        for i, batch in enumerate(batches):
+            pipe.wait(i - 2)            # slot free again (its records were consumed)
+            fill(pipe.slot(i), batch)   # write the pinned host buffers of the slot
+            pipe.submit(i)
+        records = pipe.wait(i)          # pinned (n_boxes, k, 20) of shard i
+
+    NEW orchestration (no reference counterpart)."""
+
+    def __init__(self, runners: list[ShardRunner], after_step=None):
+        """``after_step[k]()``, if given, is called on the compute stream right after slot k's pass
+        (bench.py hangs the NCCL all-gather of the top-k records there)."""
+        self.after_step = after_step
+        assert len(runners) >= 2 and len({r.device for r in runners}) == 1
+        self.runners = runners
+        dev = runners[0].device
+        self.device = dev
+        self.s_up = torch.cuda.Stream(dev)
+        self.s_run = torch.cuda.Stream(dev)
+        self.s_down = torch.cuda.Stream(dev)
+        n = len(runners)
+        self.ev_up = [torch.cuda.Event() for _ in range(n)]
+        self.ev_run = [torch.cuda.Event() for _ in range(n)]
+        self.ev_down = [torch.cuda.Event() for _ in range(n)]
+        self.pending = [False] * n
+        # work enqueued before the pipeline existed (allocations, warm-up) is on the current stream
+        for s in (self.s_up, self.s_run, self.s_down):
+            s.wait_stream(torch.cuda.current_stream(dev))
+
+    def slot(self, i: int) -> ShardRunner:
+        return self.runners[i % len(self.runners)]
+
+    def submit(self, i: int) -> None:
+        k = i % len(self.runners)
+        r = self.runners[k]
+        with torch.cuda.stream(self.s_up):
+            if self.pending[k]:
+                self.s_up.wait_event(self.ev_run[k])    # the slot's previous pass has read its inputs
+            r.upload()
+            self.ev_up[k].record(self.s_up)
+        with torch.cuda.stream(self.s_run):
+            self.s_run.wait_event(self.ev_up[k])
+            if self.pending[k]:
+                self.s_run.wait_event(self.ev_down[k])  # the slot's previous records are on the host
+            r.step()
+            if self.after_step is not None:
+                self.after_step[k]()
+            self.ev_run[k].record(self.s_run)
+        with torch.cuda.stream(self.s_down):
+            self.s_down.wait_event(self.ev_run[k])
+            r.download()
+            self.ev_down[k].record(self.s_down)
+        self.pending[k] = True
+
+    def wait(self, i: int):
+        """Block until shard i's records are on the host; returns them (None if i < 0)."""
+        if i < 0:
+            return None
+        k = i % len(self.runners)
+        if self.pending[k]:
+            self.ev_down[k].synchronize()
+        return self.runners[k].h_records
+
+    def drain(self) -> None:
+        for s in (self.s_up, self.s_run, self.s_down):
+            s.synchronize()
