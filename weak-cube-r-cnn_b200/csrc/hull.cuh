@@ -295,7 +295,7 @@ __device__ __forceinline__ void seg_counts_warp(A hx, A hy, A ex, A ey, int m, i
     for (int i = 0; i < 8; ++i) {
         if (i < m) {
             e[i].v1x = hx(i); e[i].v1y = hy(i); e[i].ex = ex(i); e[i].ey = ey(i);
-            e[i].rcp = __frcp_rn(e[i].ey);
+            e[i].rcp = __fdividef(1.f, e[i].ey);   // approximate is enough: the cut is only a guess, proved below
             if (i == 0) { mnx = mxx = e[i].v1x; mny = mxy = e[i].v1y; }
             else {
                 mnx = fminf(mnx, e[i].v1x); mxx = fmaxf(mxx, e[i].v1x);

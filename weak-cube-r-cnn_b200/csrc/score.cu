@@ -790,7 +790,6 @@ extern "C" int wcr_score_topk(const WcrImage *images, const WcrBox *boxes, int n
     }
     switch (variant) {
     case 1: wcr::score_items_kernel<1, 2, 256><<<sms * 2, 256, 0, st>>>(a); break;
-    case 24: wcr::score_items_kernel<4, 2, 128><<<sms * 2, 128, 0, st>>>(a); break;
     default: wcr::score_items_kernel<4, 2, 256><<<sms * 2, 256, 0, st>>>(a); break;
     }
     WCR_CHECK_LAUNCH("score_items_kernel");

@@ -67,10 +67,11 @@ unproject_ground_kernel(const WcrImage *__restrict__ images, int use_nth,
     if (threadIdx.x == 0) out_count[blockIdx.x] = base < cap ? base : cap;
 }
 
-// Dense cloud, HBM bound: 4 B read + 16 B written per pixel. Each thread takes 4
-// consecutive pixels of a row -- one LDG.128 when the row is 16-byte aligned and the
-// stride is 1, four STG.128 -- so a warp reads 512 B and writes 2 KB contiguous and
-// every thread keeps 80 B in flight. grid = (ceil(Hs * ceil(Ws/4) / 256), n_images).
+// Dense cloud, HBM bound: 4 B read + 16 B written per pixel. A warp takes 128 consecutive
+// pixels of a row, lane l the pixels l, l+32, l+64, l+96: every load instruction of the warp
+// reads one full 128-byte line and every STG.128 writes 512 contiguous bytes (four full
+// lines), so no sector is ever written in two pieces; each thread keeps 80 B in flight.
+// grid = (ceil(Hs * ceil(Ws/128) / 8), n_images), 8 warps per CTA.
 __device__ __forceinline__ float4 lift_pixel(float z, int u, int v, const WcrImage &im)
 {
     if (z > 0.f && z <= 3.402823466e38f) {  // finite and positive
@@ -92,24 +93,24 @@ unproject_cloud_kernel(const WcrImage *__restrict__ images, int stride,
     const WcrImage im = images[blockIdx.y];
     const int Hs = (im.H + stride - 1) / stride;
     const int Ws = (im.W + stride - 1) / stride;
-    const int wq = (Ws + 3) >> 2;
-    const int q = blockIdx.x * blockDim.x + threadIdx.x;
-    if (q >= Hs * wq) return;
-    const int vs = q / wq, us0 = (q - vs * wq) << 2;
+    const int spans = (Ws + 127) >> 7;
+    const int w = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+    if (w >= Hs * spans) return;
+    const int vs = w / spans, us0 = ((w - vs * spans) << 7) + lane;
     const int v = vs * stride;
     const float *row = im.depth + (size_t)v * im.depth_pitch;
-    float4 *dst = out_xyz + (size_t)blockIdx.y * plane_elems + (size_t)vs * Ws + us0;
+    float4 *dst = out_xyz + (size_t)blockIdx.y * plane_elems + (size_t)vs * Ws;
     float z[4];
-    if (stride == 1 && us0 + 3 < Ws && (((uintptr_t)(row + us0)) & 15) == 0) {
-        const float4 zz = __ldcs(reinterpret_cast<const float4 *>(row + us0));
-        z[0] = zz.x; z[1] = zz.y; z[2] = zz.z; z[3] = zz.w;
-    } else {
 #pragma unroll
-        for (int k = 0; k < 4; ++k) z[k] = (us0 + k < Ws) ? __ldcs(row + (size_t)(us0 + k) * stride) : 0.f;
+    for (int k = 0; k < 4; ++k) {
+        const int us = us0 + 32 * k;
+        z[k] = us < Ws ? __ldcs(row + (size_t)us * stride) : 0.f;
     }
 #pragma unroll
-    for (int k = 0; k < 4; ++k)
-        if (us0 + k < Ws) __stcs(dst + k, lift_pixel(z[k], (us0 + k) * stride, v, im));
+    for (int k = 0; k < 4; ++k) {
+        const int us = us0 + 32 * k;
+        if (us < Ws) __stcs(dst + us, lift_pixel(z[k], us * stride, v, im));
+    }
 }
 
 }  // namespace wcr
@@ -141,9 +142,9 @@ extern "C" int wcr_unproject_cloud(const WcrImage *images, int n_images, int str
     WCR_REQUIRE(((uintptr_t)out_xyz & 15) == 0, "wcr_unproject_cloud: out_xyz not 16-byte aligned");
     WCR_REQUIRE(Hs <= 65535 && n_images <= 65535, "wcr_unproject_cloud: grid too large");
     if (n_images == 0) return WCR_OK;
-    const int64_t quads = (int64_t)Hs * ((Ws + 3) / 4);
-    WCR_REQUIRE((quads + 255) / 256 < ((int64_t)1 << 31), "wcr_unproject_cloud: image too large");
-    dim3 grid((unsigned)((quads + 255) / 256), n_images);
+    const int64_t warps = (int64_t)Hs * ((Ws + 127) / 128);
+    WCR_REQUIRE((warps + 7) / 8 < ((int64_t)1 << 31), "wcr_unproject_cloud: image too large");
+    dim3 grid((unsigned)((warps + 7) / 8), n_images);
     wcr::unproject_cloud_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(
         images, stride, (float4 *)out_xyz, plane_elems);
     WCR_CHECK_LAUNCH("unproject_cloud_kernel");
