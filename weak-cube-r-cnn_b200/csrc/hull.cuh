@@ -125,8 +125,16 @@ __device__ __forceinline__ int seg_popc_range(const SegBox &sb, int row, int a, 
     const uint32_t ma = 0xffffffffu << (a & 31);
     const uint32_t mb = 0xffffffffu >> (31 - (b & 31));
     if (wa == wb) return __popc(__ldg(w + wa) & ma & mb);
-    int c = __popc(__ldg(w + wa) & ma) + __popc(__ldg(w + wb) & mb);
-    for (int i = wa + 1; i < wb; ++i) c += __popc(__ldg(w + i));
+    // all loads issued before the first popcount (a word-by-word loop pays one L1 latency
+    // per word): the two end words + up to 6 interior words cover intervals of 256 pixels
+    const uint32_t first = __ldg(w + wa), last = __ldg(w + wb);
+    uint32_t mid[6];
+#pragma unroll
+    for (int i = 0; i < 6; ++i) mid[i] = (wa + 1 + i < wb) ? __ldg(w + wa + 1 + i) : 0u;
+    int c = __popc(first & ma) + __popc(last & mb);
+#pragma unroll
+    for (int i = 0; i < 6; ++i) c += __popc(mid[i]);
+    for (int i = wa + 7; i < wb; ++i) c += __popc(__ldg(w + i));
     return c;
 }
 
