@@ -73,8 +73,9 @@ struct __align__(16) PParam {
     float4 b;   // B_0 B_1 B_2 -O_1
     float4 c;   // C_0 C_1 C_2 -O_2
 };
-// cull box: ROI column / row index range the projected box can reach: cl ch rl rh
-// (inclusive; cl > ch: the proposal holds no point of this ROI)
+// cull record (int4): ROI column range cl | ch << 16 and row range rl | rh << 16 the projected
+// box can reach (inclusive; cl > ch: the proposal holds no point of this ROI), then the depth
+// range [zlo, zhi] (float bits) of the cube's corners
 
 // One thread per proposal: test constants (same expressions as score_items_kernel's
 // prologue) and the conservative cull box.
@@ -113,11 +114,12 @@ score_prep_kernel(const WcrImage *__restrict__ images, const WcrBox *__restrict_
     p.b = make_float4(B[0], B[1], B[2], NO[1]);
     p.c = make_float4(C[0], C[1], C[2], NO[2]);
     int cl = 1, ch = 0, rl = 1, rh = 0;   // dead until proven reachable
+    float zlo = -INFINITY, zhi = INFINITY; // depth range a point of the cube can have
     if (live) {
         // unclamped projection of the 8 corners; min/max and the nearest corner depth
         const float hx = cube[5] / 2.f, hy = cube[4] / 2.f, hz = cube[3] / 2.f;
         const float *R = cube + 6;
-        float mnx = INFINITY, mxx = -INFINITY, mny = INFINITY, mxy = -INFINITY, mnz = INFINITY;
+        float mnx = INFINITY, mxx = -INFINITY, mny = INFINITY, mxy = -INFINITY, mnz = INFINITY, mxz = -INFINITY;
         bool finite = true;
 #pragma unroll
         for (int i = 0; i < 8; ++i) {
@@ -132,7 +134,7 @@ score_prep_kernel(const WcrImage *__restrict__ images, const WcrBox *__restrict_
                      fabsf(Z) <= 3.402823466e38f;
             mnx = fminf(mnx, px); mxx = fmaxf(mxx, px);
             mny = fminf(mny, py); mxy = fmaxf(mxy, py);
-            mnz = fminf(mnz, Z);
+            mnz = fminf(mnz, Z); mxz = fmaxf(mxz, Z);
         }
         cl = 0; ch = roi.ncols - 1; rl = 0; rh = roi.nrows - 1;   // no culling
         if (finite && mnz >= 0.01f) {
@@ -148,11 +150,16 @@ score_prep_kernel(const WcrImage *__restrict__ images, const WcrBox *__restrict_
             ch = min(ch, x_hi < 0 ? -1 : x_hi / s);
             rl = max(rl, y_lo <= 0 ? 0 : (y_lo + s - 1) / s);
             rh = min(rh, y_hi < 0 ? -1 : y_hi / s);
+            // a point inside the cube has its depth between the nearest and the farthest corner;
+            // 1 mm per metre of slack covers the rounding of the test and of the corners
+            const float slack = 1.0e-3f * (fabsf(mnz) + fabsf(mxz)) + 1.0e-4f;
+            zlo = mnz - slack; zhi = mxz + slack;
         }
     }
-    if (cl > ch || rl > rh) { cl = 0x3fffffff; ch = -1; rl = 0x3fffffff; rh = -1; }   // fails every overlap test
+    if (cl > ch || rl > rh) { cl = 0xffff; ch = 0; rl = 0xffff; rh = 0; }   // fails every overlap test
     out[(size_t)b * N + j] = p;
-    out_box[(size_t)b * N + j] = make_int4(cl, ch, rl, rh);
+    // 16 bytes per proposal: ROI column range, row range (16 bits each, inclusive) and depth range
+    out_box[(size_t)b * N + j] = make_int4(cl | (ch << 16), rl | (rh << 16), __float_as_int(zlo), __float_as_int(zhi));
 }
 
 // One CTA: queue items per box -> exclusive prefix (tile path).

@@ -74,6 +74,19 @@ __device__ __forceinline__ void tile_item(const ScoreArgs &a, int b, const WcrIm
         av4[r4 * 32 + lane] = make_float4(a4[0], a4[1], a4[2], a4[3]);
     }
     const float bv = ((float)v - im.cy) / im.fy;
+    // depth range of the tile's valid points (fminf / fmaxf drop the NaN of invalid ones)
+    float t_zmin = INFINITY, t_zmax = -INFINITY;
+#pragma unroll
+    for (int i = 0; i < 16; ++i) {
+        float lo, hi;
+        unpack2(z2[i], lo, hi);
+        t_zmin = fminf(t_zmin, fminf(lo, hi)); t_zmax = fmaxf(t_zmax, fmaxf(lo, hi));
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        t_zmin = fminf(t_zmin, __shfl_xor_sync(0xffffffffu, t_zmin, o));
+        t_zmax = fmaxf(t_zmax, __shfl_xor_sync(0xffffffffu, t_zmax, o));
+    }
     if (sub == 0) {
 #pragma unroll
         for (int o = 16; o > 0; o >>= 1) valid += __shfl_xor_sync(0xffffffffu, valid, o);
@@ -89,10 +102,13 @@ __device__ __forceinline__ void tile_item(const ScoreArgs &a, int b, const WcrIm
         const int4 bb = bb_next;
         const int j = base + lane;
         bb_next = __ldg(cbx + min(j + 32, n - 1));
-        const bool keep = j < n && !(bb.x > t_c1 || bb.y < tc0 || bb.z > t_r1 || bb.w < tr0);
+        const int cl = bb.x & 0xffff, ch = (unsigned)bb.x >> 16, rl = bb.y & 0xffff, rh = (unsigned)bb.y >> 16;
+        const float zlo = __int_as_float(bb.z), zhi = __int_as_float(bb.w);
+        const bool keep = j < n && !(cl > t_c1 || ch < tc0 || rl > t_r1 || rh < tr0) &&
+                          !(zhi < t_zmin || zlo > t_zmax);
         unsigned m = __ballot_sync(0xffffffffu, keep);
         if (m == 0) continue;
-        const int g_lo = (max(bb.x, tc0) - tc0) >> gshift, g_hi = (min(bb.y, t_c1) - tc0) >> gshift;
+        const int g_lo = (max(cl, tc0) - tc0) >> gshift, g_hi = (min(ch, t_c1) - tc0) >> gshift;
         if (keep) executed += (g_hi - g_lo + 1) * GRP;   // registers this proposal is tested on
         unsigned mg[NG];
 #pragma unroll
