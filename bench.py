@@ -161,7 +161,7 @@ def run_reference(args):
                 "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
-    print(json.dumps(line), flush=True)
+    emit(line)
 
 
 def ncu_traffic_bytes():
@@ -407,12 +407,33 @@ def run_wcr(args):
                                            n_boxes=args.boxes)
             line["cpu_baseline"] = {"value": v, "unit": "proposals/s", "cores": cores,
                                     "kind": "port", "sample": sample, "seconds": dt}
-        print(json.dumps(line), flush=True)
+        emit(line)
     if world > 1:
         dist.destroy_process_group()
 
 
+_REAL_STDOUT = None
+
+
+def emit(line: dict) -> None:
+    """The ONE line of stdout. Everything else a run prints -- NCCL's version banner is a bare
+    printf to fd 1 -- has been pointed at stderr by quiet_stdout()."""
+    data = (json.dumps(line) + "\n").encode()
+    if _REAL_STDOUT is None:
+        sys.stdout.write(data.decode()); sys.stdout.flush()
+    else:
+        os.write(_REAL_STDOUT, data)
+
+
+def quiet_stdout() -> None:
+    global _REAL_STDOUT
+    sys.stdout.flush()
+    _REAL_STDOUT = os.dup(1)
+    os.dup2(2, 1)
+
+
 if __name__ == "__main__":
+    quiet_stdout()
     a = parse()
     if a.impl == "reference":
         run_reference(a)
