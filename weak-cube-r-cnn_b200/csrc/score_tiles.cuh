@@ -2,21 +2,25 @@
 // (included by score.cu after ScoreArgs).
 //
 // Why. A point can only lie inside a cube if its pixel lies inside the cube's
-// projected box (perspective projection keeps convexity in front of the camera),
-// and on the C2 workload only ~45 % of the (proposal, ROI pixel) pairs do. The
+// projected box (perspective projection keeps convexity in front of the camera)
+// and its depth lies between the cube's nearest and farthest corner; on the C2
+// workload 55 % of the (proposal, ROI pixel) pairs fail one of the two. The
 // thread-per-proposal layout (score_items_kernel) cannot use that: the 128
 // proposals of a warp cover the whole ROI between them. Here the roles are
-// swapped: a WARP owns a tile of depth pixels in registers (lane = image row,
-// register = column, 32 x 32 points), proposals stream past it one at a time as
-// warp-uniform parameters, and everything a proposal's projected box cannot reach
-// is skipped by uniform branches (whole tile, or 4-register column groups).
+// swapped: a WARP owns a tile of depth pixels (lane = image row, register =
+// column, 32 x 32 points), proposals stream past it in rounds of 32 -- culled
+// lane-parallel against the tile's rows, columns and depth range, survivors then
+// taken one at a time as warp-uniform parameters -- and inside a surviving tile
+// the 8-register column groups the projected box cannot reach are skipped by
+// uniform branches.
 //
 // The point test keeps the row-factored definition of score.cu bit for bit:
 //     q_k = fma(z, fma(A_k, a_u, G_k), -O_k),  G_k = fma(B_k, b_v, C_k)
 // G_k is now per (proposal, lane) -- the lane IS the row -- and a_u per register.
-// Culling is conservative (box grown by one pixel, disabled when a corner is
-// closer than 1 cm to the camera plane), so counts are identical to the unculled
-// evaluation; tests compare them with the oracle, which never culls.
+// Culling is conservative (box grown by one pixel, depth range by 1 mm per metre,
+// both disabled when a corner is closer than 1 cm to the camera plane), so counts
+// are identical to the unculled evaluation; tests compare them with the oracle,
+// which never culls, and at full size with score_items_kernel.
 //
 // Work items, pulled by WARPS from one atomic queue (no CTA-level barrier anywhere):
 //   tile item (box, chunk, tile, half of the chunk's proposals) -> point counts
