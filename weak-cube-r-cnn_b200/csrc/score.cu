@@ -730,11 +730,15 @@ extern "C" int wcr_score_topk(const WcrImage *images, const WcrBox *boxes, int n
     carve(ws, n_boxes, N, k, cubes == nullptr, h_score->e_seg > 0, &a.ws, &zero_bytes);
     cudaError_t e = cudaMemsetAsync(ws, 0, zero_bytes, st);
     if (e != cudaSuccess) { wcr::set_error("cudaMemsetAsync: %s", cudaGetErrorString(e)); return WCR_ELAUNCH; }
-    static int variant = -1;
-    if (variant < 0) {  // development knob; the default is what DESIGN.md measures
+    static int forced = -2;
+    if (forced == -2) {  // development knob; the default is what DESIGN.md measures
         const char *ev = getenv("WCR_SCORE_VARIANT");
-        variant = ev ? atoi(ev) : 411;
+        forced = ev ? atoi(ev) : -1;
     }
+    // inside indicator of the tile kernel: on the integer pipe (411) when the launch is point
+    // tests only; with the mask term the seg items already load the integer pipe, and the
+    // FFMA.SAT form (211) measures 1.2 % faster (profiles/variants_tiles_r1.txt)
+    const int variant = forced >= 0 ? forced : (h_score->e_seg > 0 ? 211 : 411);
     const bool tiles = variant >= 100;
     if (tiles) {
         a.grp = 4 << ((variant / 10) % 10);   // x0y: 4, x1y: 8, x2y: 16, x3y: 32
