@@ -237,8 +237,8 @@ __device__ __forceinline__ float seg_ratio(int inter, int bube, int area, int mo
 // evaluations per edge). A row whose guess cannot be proved (cut within rounding of a
 // pixel centre, ill-conditioned edge) is redone by row_interval_walk.
 template <int M, class A>
-__device__ __forceinline__ void hull_rows(const EdgeRegs (&e)[8], A hx, A hy, A ex, A ey, int r0, int r1,
-                                          int c0, int c1, const SegBox &sb, int &it, int &bu)
+__device__ __forceinline__ void hull_rows(const EdgeRegs (&e)[8], A hx, A hy, A ex, A ey, int m_real, int r0,
+                                          int r1, int c0, int c1, const SegBox &sb, int &it, int &bu)
 {
     const int lane = threadIdx.x & 31;
     const float fc0 = (float)c0, fc1 = (float)c1;
@@ -274,7 +274,7 @@ __device__ __forceinline__ void hull_rows(const EdgeRegs (&e)[8], A hx, A hy, A 
             const bool right_ok = (fR == fc1 || !pRp) && (fR < fc0 || pR);
             int lo = (int)fL, hi = (int)fR;
             if (!(left_ok && right_ok))
-                row_interval_walk(&hx(0), &hy(0), &ex(0), &ey(0), hx.stride, M, Y, c0, c1, &lo, &hi);
+                row_interval_walk(&hx(0), &hy(0), &ex(0), &ey(0), hx.stride, m_real, Y, c0, c1, &lo, &hi);
             else if (!(dacc < 0.f))
                 hi = -1;
             if (lo <= hi) {
@@ -309,18 +309,21 @@ __device__ __forceinline__ void seg_counts_warp(A hx, A hy, A ex, A ey, int m, i
                 mnx = fminf(mnx, e[i].v1x); mxx = fmaxf(mxx, e[i].v1x);
                 mny = fminf(mny, e[i].v1y); mxy = fmaxf(mxy, e[i].v1y);
             }
+        } else {
+            // padding edge: horizontal (ey = 0) with t2 = (Y + 1e30) * -1 < 0 on every row, i.e. an
+            // edge every pixel passes. It takes no part in the cuts (ey == 0) nor in the proof, so
+            // hulls with an odd vertex count run the next even instantiation: three row kernels
+            // instead of six in the instruction caches.
+            e[i].v1x = 0.f; e[i].v1y = -1.0e30f; e[i].ex = -1.f; e[i].ey = 0.f; e[i].rcp = 0.f;
         }
     }
     const int r0 = max((int)floorf(mny) - 1, 0), r1 = min((int)ceilf(mxy) + 1, H - 1);
     const int c0 = max((int)floorf(mnx) - 1, 0), c1 = min((int)ceilf(mxx) + 1, W - 1);
     int it = 0, bu = 0;
     switch (m) {
-    case 3: hull_rows<3>(e, hx, hy, ex, ey, r0, r1, c0, c1, sb, it, bu); break;
-    case 4: hull_rows<4>(e, hx, hy, ex, ey, r0, r1, c0, c1, sb, it, bu); break;
-    case 5: hull_rows<5>(e, hx, hy, ex, ey, r0, r1, c0, c1, sb, it, bu); break;
-    case 6: hull_rows<6>(e, hx, hy, ex, ey, r0, r1, c0, c1, sb, it, bu); break;
-    case 7: hull_rows<7>(e, hx, hy, ex, ey, r0, r1, c0, c1, sb, it, bu); break;
-    case 8: hull_rows<8>(e, hx, hy, ex, ey, r0, r1, c0, c1, sb, it, bu); break;
+    case 3: case 4: hull_rows<4>(e, hx, hy, ex, ey, m, r0, r1, c0, c1, sb, it, bu); break;
+    case 5: case 6: hull_rows<6>(e, hx, hy, ex, ey, m, r0, r1, c0, c1, sb, it, bu); break;
+    case 7: case 8: hull_rows<8>(e, hx, hy, ex, ey, m, r0, r1, c0, c1, sb, it, bu); break;
     default:  // m = 1, 2: no interior in exact arithmetic; evaluated the slow, literal way
         for (int Yi = r0 + lane; Yi <= r1; Yi += 32) {
             int lo, hi;
