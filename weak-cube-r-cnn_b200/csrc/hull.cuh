@@ -312,8 +312,8 @@ __device__ __forceinline__ void seg_counts_warp(A hx, A hy, A ex, A ey, int m, i
         } else {
             // padding edge: horizontal (ey = 0) with t2 = (Y + 1e30) * -1 < 0 on every row, i.e. an
             // edge every pixel passes. It takes no part in the cuts (ey == 0) nor in the proof, so
-            // hulls with an odd vertex count run the next even instantiation: three row kernels
-            // instead of six in the instruction caches.
+            // hulls with 3..5 vertices run the 6-edge row kernel and 7 the 8-edge one: two row kernels
+            // instead of six in the instruction caches (one 8-edge kernel for all was slower).
             e[i].v1x = 0.f; e[i].v1y = -1.0e30f; e[i].ex = -1.f; e[i].ey = 0.f; e[i].rcp = 0.f;
         }
     }
@@ -321,8 +321,7 @@ __device__ __forceinline__ void seg_counts_warp(A hx, A hy, A ex, A ey, int m, i
     const int c0 = max((int)floorf(mnx) - 1, 0), c1 = min((int)ceilf(mxx) + 1, W - 1);
     int it = 0, bu = 0;
     switch (m) {
-    case 3: case 4: hull_rows<4>(e, hx, hy, ex, ey, m, r0, r1, c0, c1, sb, it, bu); break;
-    case 5: case 6: hull_rows<6>(e, hx, hy, ex, ey, m, r0, r1, c0, c1, sb, it, bu); break;
+    case 3: case 4: case 5: case 6: hull_rows<6>(e, hx, hy, ex, ey, m, r0, r1, c0, c1, sb, it, bu); break;
     case 7: case 8: hull_rows<8>(e, hx, hy, ex, ey, m, r0, r1, c0, c1, sb, it, bu); break;
     default:  // m = 1, 2: no interior in exact arithmetic; evaluated the slow, literal way
         for (int Yi = r0 + lane; Yi <= r1; Yi += 32) {
