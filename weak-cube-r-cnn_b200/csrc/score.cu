@@ -157,6 +157,7 @@ struct ScoreArgs {
     int n_chunks;
     int item_px;         // depth pixels per item (plan and item kernel must agree)
     int grp;             // tile path: registers per column group (plan and kernel must agree)
+    int split_queues;    // tile path: separate queues for tile and seg items
     ScoreWs ws;
     float *records;
     float *out_scores, *out_iou;
@@ -735,15 +736,14 @@ extern "C" int wcr_score_topk(const WcrImage *images, const WcrBox *boxes, int n
         const char *ev = getenv("WCR_SCORE_VARIANT");
         forced = ev ? atoi(ev) : -1;
     }
-    // inside indicator of the tile kernel: on the integer pipe (411) when the launch is point
-    // tests only; with the mask term the seg items already load the integer pipe, and the
-    // FFMA.SAT form (211) measures 1.2 % faster (profiles/variants_tiles_r1.txt)
-    const int variant = forced >= 0 ? forced : (h_score->e_seg > 0 ? 211 : 411);
+    // 411: FFMA2 point test with the inside indicator on the integer pipe, 12 warps per SM
+    const int variant = forced >= 0 ? forced : 411;
     const bool tiles = variant >= 100;
     if (tiles) {
+        { static int sq = -1; if (sq < 0) { const char *e2 = getenv("WCR_SPLIT_QUEUES"); sq = e2 ? atoi(e2) : 1; } a.split_queues = sq; }
         a.grp = 4 << ((variant / 10) % 10);   // x0y: 4, x1y: 8, x2y: 16, x3y: 32
         wcr::score_plan_tiles_kernel<<<1, 1024, 0, st>>>(images, boxes, n_boxes, nc, h_score->point_stride,
-                                                         h_score->e_pts > 0, h_score->e_seg > 0, a.grp,
+                                                         h_score->e_pts > 0, a.split_queues ? 0 : h_score->e_seg > 0, a.grp,
                                                          a.ws.item_prefix);
         WCR_CHECK_LAUNCH("score_plan_tiles_kernel");
     } else {
