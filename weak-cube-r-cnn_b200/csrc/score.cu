@@ -158,6 +158,7 @@ struct ScoreArgs {
     int item_px;         // depth pixels per item (plan and item kernel must agree)
     int grp;             // tile path: registers per column group (plan and kernel must agree)
     int split_queues;    // tile path: separate queues for tile and seg items
+    int ps;              // tile path: proposals per tile item (power of two, 128 .. SC_CHUNK)
     ScoreWs ws;
     float *records;
     float *out_scores, *out_iou;
@@ -658,6 +659,7 @@ cudaError_t launch_sample_cubes(const WcrImage *images, const WcrBox *boxes, int
 }
 
 namespace {
+inline long long sms_resident_warps() { return (long long)wcr::sm_count() * 12; }   // 3 CTAs x 4 warps
 inline int n_chunks_for(int N) { return (N + wcr::SC_CHUNK - 1) / wcr::SC_CHUNK; }
 inline size_t align256(size_t x) { return (x + 255) & ~(size_t)255; }
 
@@ -741,9 +743,16 @@ extern "C" int wcr_score_topk(const WcrImage *images, const WcrBox *boxes, int n
     const bool tiles = variant >= 100;
     if (tiles) {
         { static int sq = -1; if (sq < 0) { const char *e2 = getenv("WCR_SPLIT_QUEUES"); sq = e2 ? atoi(e2) : 1; } a.split_queues = sq; }
+        {   // proposals per tile item: the whole chunk when the shard has enough tiles for every
+            // resident warp (a box has ~30 tiles), finer for small shards
+            const long long bc = (long long)n_boxes * nc, want = 4LL * sms_resident_warps();
+            int ps = wcr::SC_CHUNK;
+            while (ps > 128 && bc * 32 * (wcr::SC_CHUNK / ps) < want) ps >>= 1;
+            a.ps = ps;
+        }
         a.grp = 4 << ((variant / 10) % 10);   // x0y: 4, x1y: 8, x2y: 16, x3y: 32
         wcr::score_plan_tiles_kernel<<<1, 1024, 0, st>>>(images, boxes, n_boxes, nc, h_score->point_stride,
-                                                         h_score->e_pts > 0, a.split_queues ? 0 : h_score->e_seg > 0, a.grp,
+                                                         h_score->e_pts > 0, a.split_queues ? 0 : h_score->e_seg > 0, a.grp, wcr::SC_CHUNK / a.ps,
                                                          a.ws.item_prefix);
         WCR_CHECK_LAUNCH("score_plan_tiles_kernel");
     } else {

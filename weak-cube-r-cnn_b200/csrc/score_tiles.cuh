@@ -32,8 +32,9 @@
 
 namespace wcr {
 
-constexpr int TL_PS = 512;       // proposals per tile item
-constexpr int TL_SUBS = SC_CHUNK / TL_PS;
+// proposals per tile item: ScoreArgs::ps = 1024 (the whole chunk) for shards with enough tiles to
+// keep every warp busy, down to 128 for small ones (wcr_score_topk decides; 512 -> 1024 gave
+// 11.14 -> 10.95 ms on C2)
 constexpr int TL_SEGS = SC_CHUNK / 32;   // seg items per chunk
 constexpr int TL_WBUF = 1024 + 3 * 32 * 4;   // per-warp scratch floats: a_u tile (also hull scratch / epilogue scores) + survivor slots
 
@@ -65,9 +66,9 @@ __device__ __forceinline__ TileGeom tile_geom(const WcrBox &bx, int H, int W, in
 }
 
 // queue items of one (box, chunk); at least one so that somebody runs the epilogue
-__device__ __forceinline__ int tile_items_per_chunk(const TileGeom &g, bool use_seg)
+__device__ __forceinline__ int tile_items_per_chunk(const TileGeom &g, bool use_seg, int subs)
 {
-    return max(g.n_tiles * TL_SUBS, 1) + (use_seg ? TL_SEGS : 0);
+    return max(g.n_tiles * subs, 1) + (use_seg ? TL_SEGS : 0);
 }
 
 // Per-proposal constants of the point test, 48 B; the cull boxes live in their own
@@ -169,7 +170,7 @@ score_prep_kernel(const WcrImage *__restrict__ images, const WcrBox *__restrict_
 // One CTA: queue items per box -> exclusive prefix (tile path).
 __global__ void __launch_bounds__(1024)
 score_plan_tiles_kernel(const WcrImage *__restrict__ images, const WcrBox *__restrict__ boxes,
-                        int n_boxes, int n_chunks, int stride, int use_pts, int use_seg, int grp,
+                        int n_boxes, int n_chunks, int stride, int use_pts, int use_seg, int grp, int subs,
                         int *__restrict__ prefix)
 {
     __shared__ int s_warp[32];
@@ -183,7 +184,7 @@ score_plan_tiles_kernel(const WcrImage *__restrict__ images, const WcrBox *__res
         if (b < n_boxes) {
             const WcrBox bx = boxes[b];
             const WcrImage im = images[bx.image];
-            n = tile_items_per_chunk(tile_geom(bx, im.H, im.W, stride, use_pts != 0, grp), use_seg != 0) * n_chunks;
+            n = tile_items_per_chunk(tile_geom(bx, im.H, im.W, stride, use_pts != 0, grp), use_seg != 0, subs) * n_chunks;
         }
         int incl = n;
 #pragma unroll

@@ -42,9 +42,9 @@ __device__ __forceinline__ void tile_item(const ScoreArgs &a, int b, const WcrIm
     const int v = tg.v0 + my_row * s;
 
     const int chunk_n = min(SC_CHUNK, a.N - chunk * SC_CHUNK);
-    const int n = min(TL_PS, chunk_n - sub * TL_PS);
+    const int n = min(a.ps, chunk_n - sub * a.ps);
     if (n <= 0) return;
-    const size_t first = (size_t)b * a.N + (size_t)chunk * SC_CHUNK + sub * TL_PS;
+    const size_t first = (size_t)b * a.N + (size_t)chunk * SC_CHUNK + sub * a.ps;
     const PParam *__restrict__ pp = a.ws.params + first;
     const int4 *__restrict__ cbx = a.ws.cullbox + first;
     int4 bb_next = __ldg(cbx + min(lane, n - 1));
@@ -402,6 +402,7 @@ __global__ void __launch_bounds__(WARPS * 32, MINB) score_tiles_kernel(const Sco
     const int *__restrict__ prefix = a.ws.item_prefix;
     const bool use_pts = a.sc.e_pts > 0, use_seg = a.sc.e_seg > 0;
     const int total = prefix[a.n_boxes];
+    const int subs = SC_CHUNK / a.ps;   // tile items per (chunk, tile)
 
     // Queues. Default (a.split_queues = 1): tile items and seg items have their own counters; the
     // last warp of every CTA prefers seg items, the others tile items, and each falls back to
@@ -442,7 +443,7 @@ __global__ void __launch_bounds__(WARPS * 32, MINB) score_tiles_kernel(const Sco
         const WcrImage im = a.images[bx.image];
         const TileGeom tg = tile_geom(bx, im.H, im.W, a.sc.point_stride, use_pts, GRP);
         const int nseg = use_seg ? TL_SEGS : 0;
-        const int pt = tile_items_per_chunk(tg, false);
+        const int pt = tile_items_per_chunk(tg, false, subs);
         const int per = pt + nseg;   // items that retire before the chunk's epilogue
         int chunk, seg_grp = -1, ti = 0;
         if (kind == 1) {
@@ -464,7 +465,7 @@ __global__ void __launch_bounds__(WARPS * 32, MINB) score_tiles_kernel(const Sco
         if (seg_grp >= 0) {
             seg_item(a, b, bx, im, chunk, seg_grp, wbuf, lane);
         } else {
-            const int tile = ti / TL_SUBS, sub = ti - tile * TL_SUBS;
+            const int tile = ti / subs, sub = ti - tile * subs;
             if (tile < tg.n_tiles) tile_item<GRP, F2, ICNT>(a, b, im, tg, chunk, tile, sub, wbuf, lane);
         }
         // ---- retire the item ------------------------------------------------------
