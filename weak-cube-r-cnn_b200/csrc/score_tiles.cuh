@@ -22,8 +22,8 @@
 // are identical to the unculled evaluation; tests compare them with the oracle,
 // which never culls, and at full size with score_items_kernel.
 //
-// Work items, pulled by WARPS from one atomic queue (no CTA-level barrier anywhere):
-//   tile item (box, chunk, tile, half of the chunk's proposals) -> point counts
+// Work items, pulled by WARPS from two atomic queues (no CTA-level barrier anywhere):
+//   tile item (box, chunk, tile, 128..1024 proposals of the chunk) -> point counts
 //   seg item  (box, chunk, 32 proposals)                       -> hull fill pixel counts
 // The warp that retires the last item of a (box, chunk) runs its epilogue (corners ->
 // projection -> IoU -> score -> top-k) on its own; the warp that retires a box's last
