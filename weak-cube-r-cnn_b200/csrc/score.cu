@@ -59,17 +59,6 @@ __device__ __forceinline__ u64 fadd2(u64 a, u64 b)
     asm("add.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
     return r;
 }
-__device__ __forceinline__ void count_inside1(int &cnt, float q0, float q1, float q2)
-{
-    asm("{\n\t.reg .pred p;\n\t.reg .f32 a0, a1, a2;\n\t"
-        "abs.f32 a0, %1;\n\tabs.f32 a1, %2;\n\tabs.f32 a2, %3;\n\t"
-        "setp.le.f32 p, a0, 0f3F800000;\n\t"
-        "setp.le.and.f32 p, a1, 0f3F800000, p;\n\t"
-        "setp.le.and.f32 p, a2, 0f3F800000, p;\n\t"
-        "@p add.s32 %0, %0, 1;\n\t}"
-        : "+r"(cnt)
-        : "f"(q0), "f"(q1), "f"(q2));
-}
 // Read-once global data (depth pixels, cube parameters): keep it out of L1 so that the
 // box mask the hull fill re-reads stays resident.
 __device__ __forceinline__ float ld_stream(const float *p)
@@ -96,15 +85,6 @@ __device__ __forceinline__ float inside_sat(float q0, float q1, float q2)
     float m, r;
     asm("max.f32 %0, %1, %2, %3;" : "=f"(m) : "f"(fabsf(q0)), "f"(fabsf(q1)), "f"(fabsf(q2)));
     asm("fma.rn.sat.f32 %0, %1, %2, 0f4A800002;" : "=f"(r) : "f"(-m), "f"(m));
-    return r;
-}
-
-// FMA-pipe-only form: one saturated indicator per axis, multiplied into the counter
-// (3 FFMA.SAT + FMUL + FFMA; no ALU-pipe instruction at all).
-__device__ __forceinline__ float sat_axis(float q)
-{
-    float r;
-    asm("fma.rn.sat.f32 %0, %1, %2, 0f4A800002;" : "=f"(r) : "f"(-q), "f"(q));
     return r;
 }
 
@@ -292,12 +272,11 @@ __device__ __forceinline__ void warp_merge(const float *cand, int n, int k, floa
 #include "score_tiles_kernel.cuh"
 namespace wcr {
 
-// V selects the inner-loop instruction mix (same arithmetic, same results):
-//   0: FFMA2 (two proposals per packed fma) + FMNMX3 + FSET + FADD2
-//   1: scalar FFMA + FMNMX3 + FSET + FADD
-//   2: scalar FFMA + 3 x FSETP(|q| <= 1) + predicated IADD
-// (an integer-mask FSET + IADD3 pairing was tried too: ptxas lowers it to the
-//  quarter-rate FSETP + predicated IADD, 9 % slower -- profiles/variants_r1.txt)
+// The FIRST scoring kernel: thread = T proposals in registers, every ROI pixel broadcast to them
+// from shared memory, no culling. Superseded by score_tiles_kernel; kept behind
+// WCR_SCORE_VARIANT=4 (or 1) as the measured baseline and as an independent implementation
+// the tile kernel is cross-checked against at full size (tests/test_score_fullsize_gpu.py).
+// V selects the inside indicator: 1: FMNMX3 + FSET, 4: FMNMX3 + FFMA.SAT on 2^11-scaled rows.
 template <int V, int MINB, int SC_THREADS>
 __global__ void __launch_bounds__(SC_THREADS, MINB) score_items_kernel(const ScoreArgs a)
 {
@@ -342,7 +321,7 @@ __global__ void __launch_bounds__(SC_THREADS, MINB) score_items_kernel(const Sco
         // ---- prologue: proposal state -> registers, two proposals per FFMA2 lane pair
         // unit-cube form: row k of the test is scaled by 1/half_k so that
         // inside <=> max_k |q'_k| <= 1 (one FMNMX3 + one FSET instead of 3 FSETP).
-        u64 A2[T / 2][3], B2[T / 2][3], C2[T / 2][3], NO2[T / 2][3], cnt2[T / 2];
+        u64 A2[T / 2][3], B2[T / 2][3], C2[T / 2][3], NO2[T / 2][3];
 #pragma unroll
         for (int pr = 0; pr < T / 2; ++pr) {
             float Af[2][3], Bf[2][3], Cf[2][3], NOf[2][3];
@@ -365,7 +344,7 @@ __global__ void __launch_bounds__(SC_THREADS, MINB) score_items_kernel(const Sco
                         Bf[e][k] = cube[9 + k] / half[k];
                         Cf[e][k] = cube[12 + k] / half[k];
                         NOf[e][k] = -fmaf(Cf[e][k], cube[2], fmaf(Bf[e][k], cube[1], Af[e][k] * cube[0]));
-                        if (V == 4 || V == 5) {   // exact power-of-two scaling for inside_sat
+                        if (V == 4) {   // exact power-of-two scaling for inside_sat
                             Af[e][k] *= 2048.f; Bf[e][k] *= 2048.f; Cf[e][k] *= 2048.f; NOf[e][k] *= 2048.f;
                         }
                     }
@@ -379,12 +358,10 @@ __global__ void __launch_bounds__(SC_THREADS, MINB) score_items_kernel(const Sco
                 A2[pr][k] = pack2(Af[0][k], Af[1][k]); B2[pr][k] = pack2(Bf[0][k], Bf[1][k]);
                 C2[pr][k] = pack2(Cf[0][k], Cf[1][k]); NO2[pr][k] = pack2(NOf[0][k], NOf[1][k]);
             }
-            cnt2[pr] = pack2(0.f, 0.f);
         }
         float cntf[T];
-        int cnti[T];
 #pragma unroll
-        for (int t = 0; t < T; ++t) { cntf[t] = 0.f; cnti[t] = 0; }
+        for (int t = 0; t < T; ++t) cntf[t] = 0.f;
 
         // ---- main loop: this item's rows, tile by tile --------------------------
         int my_valid = 0;
@@ -409,7 +386,7 @@ __global__ void __launch_bounds__(SC_THREADS, MINB) score_items_kernel(const Sco
                         av = ((float)u - K.cx) / K.fx;
                         if (d > 0.f && d <= 3.402823466e38f) { z = d; ++my_valid; }
                     }
-                    tile[idx] = V == 0 ? make_float4(av, av, z, z) : make_float4(av, z, av, z);
+                    tile[idx] = make_float4(av, z, av, z);
                 }
                 __syncthreads();
                 for (int ss = 0; ss < nseg; ++ss) {
@@ -421,24 +398,7 @@ __global__ void __launch_bounds__(SC_THREADS, MINB) score_items_kernel(const Sco
                     for (int pr = 0; pr < T / 2; ++pr)
 #pragma unroll
                         for (int k = 0; k < 3; ++k) G2[pr][k] = ffma2(B2[pr][k], bvbv, C2[pr][k]);
-                    if (V == 0) {
-                        const ulonglong2 *src = reinterpret_cast<const ulonglong2 *>(tile + ss * segpad);
-#pragma unroll 4
-                        for (int p = 0; p < segpad; ++p) {
-                            const ulonglong2 pp = src[p];  // (a,a) , (z,z)
-#pragma unroll
-                            for (int pr = 0; pr < T / 2; ++pr) {
-                                float q[3][2];
-#pragma unroll
-                                for (int k = 0; k < 3; ++k)
-                                    unpack2(ffma2(pp.y, ffma2(A2[pr][k], pp.x, G2[pr][k]), NO2[pr][k]),
-                                            q[k][0], q[k][1]);
-                                const float r0 = inside_unit(q[0][0], q[1][0], q[2][0]);
-                                const float r1 = inside_unit(q[0][1], q[1][1], q[2][1]);
-                                cnt2[pr] = fadd2(cnt2[pr], pack2(r0, r1));
-                            }
-                        }
-                    } else {
+                    {
                         float Af[T][3], Gf[T][3], NOf[T][3];
 #pragma unroll
                         for (int pr = 0; pr < T / 2; ++pr)
@@ -457,10 +417,7 @@ __global__ void __launch_bounds__(SC_THREADS, MINB) score_items_kernel(const Sco
                                 const float q0 = fmaf(pp.y, fmaf(Af[t][0], pp.x, Gf[t][0]), NOf[t][0]);
                                 const float q1 = fmaf(pp.y, fmaf(Af[t][1], pp.x, Gf[t][1]), NOf[t][1]);
                                 const float q2 = fmaf(pp.y, fmaf(Af[t][2], pp.x, Gf[t][2]), NOf[t][2]);
-                                if (V == 1) cntf[t] += inside_unit(q0, q1, q2);
-                                else if (V == 4) cntf[t] += inside_sat(q0, q1, q2);
-                                else if (V == 5) cntf[t] = fmaf(sat_axis(q0) * sat_axis(q1), sat_axis(q2), cntf[t]);
-                                else count_inside1(cnti[t], q0, q1, q2);
+                                cntf[t] += V == 1 ? inside_unit(q0, q1, q2) : inside_sat(q0, q1, q2);
                             }
                         }
                     }
@@ -469,12 +426,7 @@ __global__ void __launch_bounds__(SC_THREADS, MINB) score_items_kernel(const Sco
         }
         int cnt[T];
 #pragma unroll
-        for (int pr = 0; pr < T / 2; ++pr) {
-            float c0, c1;
-            unpack2(cnt2[pr], c0, c1);
-            cnt[2 * pr] = (int)c0 + (int)cntf[2 * pr] + cnti[2 * pr];
-            cnt[2 * pr + 1] = (int)c1 + (int)cntf[2 * pr + 1] + cnti[2 * pr + 1];
-        }
+        for (int t = 0; t < T; ++t) cnt[t] = (int)cntf[t];
 
         // ---- mask term of this item's share of the chunk's proposals ---------------
         // The hull rasterisation does not depend on the points, so the chunk's proposals

@@ -139,7 +139,7 @@ __device__ __forceinline__ void tile_item(const ScoreArgs &a, int b, const WcrIm
                 // FFMA.SAT indicator + FADD2 counter on the FMA pipe.
                 int oc[4] = {0, 0, 0, 0}, visited = 0;
                 u64 acc2[4] = {pack2(0.f, 0.f), pack2(0.f, 0.f), pack2(0.f, 0.f), pack2(0.f, 0.f)};
-                constexpr int SPG = GRP / 8;   // steps per column group
+                constexpr int SPG = GRP >= 8 ? GRP / 8 : 1;   // steps per column group (the FFMA2 path needs GRP >= 8)
                 const ulonglong2 *avq = reinterpret_cast<const ulonglong2 *>(av4) + lane;
                 ulonglong2 n0 = avq[0], n1 = avq[32];
 #pragma unroll
