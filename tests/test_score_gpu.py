@@ -198,6 +198,30 @@ def test_score_edge_cases(cuda_lib):
         score_topk(shard, boxes, cubes, cfg=ScoreConfig())   # CPU tensor: no fallback
 
 
+@pytest.mark.parametrize("n_images,n_boxes", [(3, 20), (6, 20)])
+def test_score_mid_size_shards(cuda_lib, n_images, n_boxes):
+    """The tile kernel sizes its items per launch (128 ... 1024 proposals per tile item, from the
+    number of boxes): 60 and 120 boxes land on the two middle sizes (256, 512); the small and the
+    full-size cases are covered by the other tests. Counts and top-k bit-exact vs the oracle."""
+    from wcr.proposals import propose, score_topk, ScoreConfig
+    H, W, N = 240, 320, 700
+    ims, shard, boxes, priors, normals = _setup(n_images, H, W, n_boxes=n_boxes, first=60)
+    cubes = propose(shard, boxes, priors, normals, N, seed=9)
+    res = score_topk(shard, boxes, cubes, cfg=ScoreConfig(k=16), want_all=True)
+    executed = res["workspace"].executed_tests()
+    cubes_h = cubes.cpu().numpy()
+    gb, total = 0, 0
+    for im in ims:
+        for b in range(len(im["boxes"])):
+            ref = oc.score_box(im["depth"].numpy(), im["K"].numpy(), im["boxes"][b].numpy(), (H, W), cubes_h[gb])
+            assert np.array_equal(res["count"][gb].cpu().numpy(), ref["count"]), gb
+            assert np.array_equal(res["idx"][gb].cpu().numpy(), oc.topk(ref["score"], 16))
+            total += ref["npts"] * N
+            gb += 1
+    assert gb == n_images * n_boxes
+    assert 0 < executed < total          # the cull removed work, and the counter saw the rest
+
+
 @pytest.mark.parametrize("stride", [1, 3])
 def test_score_culling_adversarial(cuda_lib, stride):
     """The tile path skips every (proposal, pixel) pair the proposal's projected box cannot
