@@ -677,6 +677,9 @@ extern "C" int wcr_score_topk(const WcrImage *images, const WcrBox *boxes, int n
     const int nc = n_chunks_for(N);
     WCR_REQUIRE(nc <= wcr::SC_MAX_CHUNKS, "wcr_score_topk: N too large (max %d)",
                 wcr::SC_MAX_CHUNKS * wcr::SC_CHUNK);
+    // item indices are 32-bit: seg items alone are n_boxes * chunks * 32, a box has a few hundred
+    // tile items per chunk at most
+    WCR_REQUIRE((long long)n_boxes * nc * 2048 < 0x7fffffffLL, "wcr_score_topk: n_boxes * ceil(N / 1024) too large");
     if (n_boxes == 0) return WCR_OK;
     cudaStream_t st = (cudaStream_t)stream;
 
