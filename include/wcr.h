@@ -190,6 +190,8 @@ int wcr_sample_cubes(const WcrImage *images, const WcrBox *boxes, int n_boxes,
  *             (utils.py:410-454) -> pixels strictly left of every hull edge
  *             (fill_polygon > 0, utils.py:456-488) -> mask_iou / mod_mask_iou
  *             (utils.py:225-245) against the box mask
+ *   The mask term of a proposal that provably holds no depth point (score 0) is evaluated only if
+ *   the proposal reaches the top-k, unless out_seg is requested.
  *   k <= WCR_MAX_TOPK; image sides <= 65535 pixels (the cull records hold 16-bit ROI indices)
  *   out_records [n_boxes][k][20]; slots beyond N hold idx = -1
  *   optional per-proposal outputs (NULL to skip), all [n_boxes][N]:

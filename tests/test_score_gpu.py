@@ -320,6 +320,46 @@ def test_score_seg_term_bit_exact(cuda_lib, N, H, W, mode, eseg):
             gb += 1
 
 
+def test_score_seg_lazy_mask_term(cuda_lib):
+    """Without per-proposal outputs the kernel skips the hull fill of proposals that provably hold
+    no point (their score is 0 whatever the mask term is) and evaluates it lazily for those that
+    still reach the top-k. The records -- index, score, s_iou, s_pts, s_seg -- must equal the
+    oracle's, which computes every term for every proposal. Box 0: ordinary proposals; box 1:
+    half of them pushed far behind the scene (zero count, lazy); box 2: ALL of them (every
+    winner's mask term comes from the lazy path)."""
+    from wcr import synth
+    from wcr.proposals import propose, score_topk, ScoreConfig, SegMasks
+    H, W, N = 240, 320, 300
+    ims, shard, boxes, priors, normals = _setup(1, H, W, n_boxes=3, first=33)
+    masks = [m for im in ims for m in synth.seg_masks(im["boxes"], H, W)]
+    seg = SegMasks(shard, boxes, masks)
+    cubes = propose(shard, boxes, priors, normals, N, seed=13)
+    scale = torch.ones(3, N, 1, device=cubes.device)
+    scale[1, ::2] = 6.0          # same pixel footprint, six times the depth: no point inside
+    scale[2, :] = 6.0
+    cubes[:, :, 0:3] *= scale
+    cfg = ScoreConfig(e_seg=1, k=16)
+    res = score_topk(shard, boxes, cubes, cfg=cfg, seg=seg)          # want_all=False: lazy path on
+    cubes_h = cubes.cpu().numpy()
+    im = ims[0]
+    for b in range(3):
+        ref = oc.score_box(im["depth"].numpy(), im["K"].numpy(), im["boxes"][b].numpy(), (H, W),
+                           cubes_h[b], 1, 1, 1, 1, 0, masks[b].numpy())
+        want = oc.topk(ref["score"], 16)
+        assert np.array_equal(res["idx"][b].cpu().numpy(), want), b
+        rec = res["records"][b].cpu().numpy()
+        for r, j in enumerate(want):
+            assert rec[r, 1] == ref["score"][j]
+            assert rec[r, 17] == ref["iou"][j]
+            assert rec[r, 18] == (ref["count"][j] / ref["npts"] if ref["npts"] else 0.0) or \
+                abs(rec[r, 18] - ref["count"][j] / max(ref["npts"], 1)) < 1e-7
+            assert rec[r, 19] == ref["seg"][j], (b, r, j)
+        if b == 2:
+            assert (ref["count"] == 0).all() and (ref["seg"][want] > 0).any()
+        if b == 1:
+            assert (ref["count"][::2] == 0).all() and (ref["count"][1::2] > 0).any()
+
+
 def test_score_seg_degenerate(cuda_lib):
     """Empty masks, cubes behind the camera (non-finite corners), cubes entirely
     outside the image (hull collapses onto the border, duplicate corners)."""

@@ -124,6 +124,8 @@ struct ScoreWs {
     int2 *segcnt;        // [n_boxes][N] (|seg & hull|, |hull|) pixel counts of the mask term
     PParam *params;      // [n_boxes][N] point-test constants (tile path)
     int4 *cullbox;       // [n_boxes][N] cull boxes (tile path)
+    float2 *zgrid;       // [n_boxes][256] depth range of the ROI's 16 x 16 cells (tile path)
+    uint8_t *mayhit;     // [n_boxes][N] 0: the proposal provably holds no point (tile path)
 };
 
 struct ScoreArgs {
@@ -139,6 +141,7 @@ struct ScoreArgs {
     int grp;             // tile path: registers per column group (plan and kernel must agree)
     int split_queues;    // tile path: separate queues for tile and seg items
     int ps;              // tile path: proposals per tile item (power of two, 128 .. SC_CHUNK)
+    int seg_lazy;        // tile path: mask term skipped for proposals that provably hold no point
     ScoreWs ws;
     float *records;
     float *out_scores, *out_iou;
@@ -636,8 +639,10 @@ size_t carve(void *base, int n_boxes, int N, int k, bool need_cubes, bool need_s
     int2 *segcnt = (int2 *)take(need_seg ? (size_t)n_boxes * N * sizeof(int2) : 0);
     wcr::PParam *params = (wcr::PParam *)take((size_t)n_boxes * N * sizeof(wcr::PParam));
     int4 *cullbox = (int4 *)take((size_t)n_boxes * N * sizeof(int4));
+    float2 *zgrid = (float2 *)take((size_t)n_boxes * 256 * sizeof(float2));
+    uint8_t *mayhit = (uint8_t *)take((size_t)n_boxes * N);
     if (ws) {
-        ws->segcnt = segcnt; ws->params = params; ws->cullbox = cullbox;
+        ws->segcnt = segcnt; ws->params = params; ws->cullbox = cullbox; ws->zgrid = zgrid; ws->mayhit = mayhit;
         ws->queue = queue; ws->executed = (unsigned long long *)(queue ? (char *)queue + 8 : nullptr); ws->done_chunk = done_chunk; ws->done_box = done_box; ws->npts = npts;
         ws->count = count; ws->item_prefix = prefix; ws->cand = cand; ws->cubes = cubes;
     }
@@ -736,10 +741,18 @@ extern "C" int wcr_score_topk(const WcrImage *images, const WcrBox *boxes, int n
     a.seg_bits = seg_bits; a.seg_off = seg_off; a.out_seg = out_seg;
     const int sms = wcr::sm_count();
     if (tiles) {
+        // mask term lazily: only when the point term is part of the score (a zero count then
+        // forces a zero score) and the caller did not ask for the per-proposal mask ratios
+        static int lazy_knob = -1;
+        if (lazy_knob < 0) { const char *e3 = getenv("WCR_SEG_LAZY"); lazy_knob = e3 ? atoi(e3) : 1; }
+        a.seg_lazy = lazy_knob && h_score->e_seg > 0 && h_score->e_pts > 0 && out_seg == nullptr;
         if (h_score->e_pts > 0) {
+            wcr::score_zgrid_kernel<<<n_boxes, 256, 0, st>>>(images, boxes, h_score->point_stride, 1, a.ws.zgrid);
+            WCR_CHECK_LAUNCH("score_zgrid_kernel");
             const dim3 grid(n_boxes, (N + 255) / 256);
             wcr::score_prep_kernel<<<grid, 256, 0, st>>>(images, boxes, n_boxes, cubes ? cubes : a.ws.cubes, N,
-                                                          h_score->point_stride, 1, a.ws.params, a.ws.cullbox);
+                                                          h_score->point_stride, 1, a.ws.params, a.ws.cullbox,
+                                                          a.ws.zgrid, a.ws.mayhit);
             WCR_CHECK_LAUNCH("score_prep_kernel");
         }
         switch (variant) {

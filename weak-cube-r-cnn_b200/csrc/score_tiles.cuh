@@ -82,12 +82,35 @@ struct __align__(16) PParam {
 // box can reach (inclusive; cl > ch: the proposal holds no point of this ROI), then the depth
 // range [zlo, zhi] (float bits) of the cube's corners
 
+// Depth range of the valid pixels of every cell of a 16 x 16 grid over a box's (sub-sampled) ROI:
+// [n_boxes][256] (min, max); an empty cell holds (+inf, -inf). One CTA per box, thread = cell.
+__global__ void __launch_bounds__(256)
+score_zgrid_kernel(const WcrImage *__restrict__ images, const WcrBox *__restrict__ boxes, int stride,
+                   int use_pts, float2 *__restrict__ zgrid)
+{
+    const int b = blockIdx.x, cy = threadIdx.x >> 4, cx = threadIdx.x & 15;
+    const WcrBox bx = boxes[b];
+    const WcrImage im = images[bx.image];
+    const Roi roi = box_roi(bx, im.H, im.W, stride, use_pts != 0);
+    const int cw = max(1, (roi.ncols + 15) >> 4), chh = max(1, (roi.nrows + 15) >> 4);
+    float mn = INFINITY, mx = -INFINITY;
+    for (int r = cy * chh; r < min((cy + 1) * chh, roi.nrows); ++r) {
+        const float *row = im.depth + (size_t)(roi.v0 + r * stride) * im.depth_pitch + roi.u0;
+        for (int c = cx * cw; c < min((cx + 1) * cw, roi.ncols); ++c) {
+            const float d = __ldg(row + c * stride);
+            if (d > 0.f && d <= 3.402823466e38f) { mn = fminf(mn, d); mx = fmaxf(mx, d); }
+        }
+    }
+    zgrid[(size_t)b * 256 + threadIdx.x] = make_float2(mn, mx);
+}
+
 // One thread per proposal: test constants (same expressions as score_items_kernel's
 // prologue) and the conservative cull box.
 __global__ void __launch_bounds__(256)
 score_prep_kernel(const WcrImage *__restrict__ images, const WcrBox *__restrict__ boxes, int n_boxes,
                   const float *__restrict__ cubes, int N, int stride, int use_pts,
-                  PParam *__restrict__ out, int4 *__restrict__ out_box)
+                  PParam *__restrict__ out, int4 *__restrict__ out_box,
+                  const float2 *__restrict__ zgrid, uint8_t *__restrict__ out_mayhit)
 {
     const int j = blockIdx.y * 256 + threadIdx.x, b = blockIdx.x;
     if (j >= N) return;
@@ -161,7 +184,22 @@ score_prep_kernel(const WcrImage *__restrict__ images, const WcrBox *__restrict_
             zlo = mnz - slack; zhi = mxz + slack;
         }
     }
-    if (cl > ch || rl > rh) { cl = 0xffff; ch = 0; rl = 0xffff; rh = 0; }   // fails every overlap test
+    // Can the cube hold any valid pixel at all? Its corner depth range against the depth ranges of
+    // the ROI cells (16 x 16 grid, score_zgrid_kernel) its cull box overlaps. "No" is a proof that
+    // the point count is 0: such a proposal is dead for the tile items and its mask term is lazy.
+    bool mayhit = cl <= ch && rl <= rh;
+    if (mayhit && zgrid) {
+        const int cw = max(1, (roi.ncols + 15) >> 4), chh = max(1, (roi.nrows + 15) >> 4);
+        const float2 *zg = zgrid + (size_t)b * 256;
+        mayhit = false;
+        for (int cy = rl / chh; cy <= min(15, rh / chh) && !mayhit; ++cy)
+            for (int cx = cl / cw; cx <= min(15, ch / cw); ++cx) {
+                const float2 c = __ldg(zg + cy * 16 + cx);
+                if (!(zhi < c.x || zlo > c.y)) { mayhit = true; break; }
+            }
+    }
+    if (out_mayhit) out_mayhit[(size_t)b * N + j] = mayhit ? 1 : 0;
+    if (!mayhit) { cl = 0xffff; ch = 0; rl = 0xffff; rh = 0; }   // fails every overlap test
     out[(size_t)b * N + j] = p;
     // 16 bytes per proposal: ROI column range, row range (16 bits each, inclusive) and depth range
     out_box[(size_t)b * N + j] = make_int4(cl | (ch << 16), rl | (rh << 16), __float_as_int(zlo), __float_as_int(zhi));

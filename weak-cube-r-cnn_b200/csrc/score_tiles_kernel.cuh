@@ -213,13 +213,14 @@ __device__ __forceinline__ void tile_item(const ScoreArgs &a, int b, const WcrIm
 
 // ---- seg item: hull fill pixel counts of 32 proposals (lane = proposal for the march,
 // then the warp walks the 32 hulls with lanes = pixel rows) --------------------------
-__device__ __forceinline__ void seg_item(const ScoreArgs &a, int b, const WcrBox &bx, const WcrImage &im,
-                                         int chunk, int grp, float *wbuf, int lane)
+// q = the lane's proposal within the chunk, or -1 for a lane without one.
+// Out of line and fed by value: two call sites (seg items, the epilogue's lazy fill) share one
+// copy of the hull code (measured faster than inlining it into the seg items: 10.76 vs 10.87 ms),
+// and the kernel's parameter block never has to be copied to local memory.
+__device__ __noinline__ void seg_group(const float *__restrict__ cubes, int N, const uint32_t *__restrict__ seg_bits_b,
+                                       int2 *__restrict__ segcnt, int b, const WcrBox bx, const WcrImage im,
+                                       int chunk, int q, float *wbuf, int lane)
 {
-    const int chunk_n = min(SC_CHUNK, a.N - chunk * SC_CHUNK);
-    const int q = grp * 32 + lane;
-    if (grp * 32 >= chunk_n) return;
-    const float *__restrict__ cubes = a.cubes ? a.cubes : a.ws.cubes;
     const Intr K = {im.fx, im.fy, im.cx, im.cy};
     float lo0, hi0, lo1, hi1;
     clamp_bounds(bx.clamp0, lo0, hi0);
@@ -228,15 +229,15 @@ __device__ __forceinline__ void seg_item(const ScoreArgs &a, int b, const WcrBox
     const Roi r1 = box_roi(bx, im.H, im.W, 1, true);
     sb.u0 = r1.u0; sb.v0 = r1.v0; sb.ncols = r1.ncols; sb.nrows = r1.ncols > 0 ? r1.nrows : 0;
     sb.wpr = (sb.ncols + 31) >> 5;
-    sb.bits = a.seg_bits + a.seg_off[b];
+    sb.bits = seg_bits_b;
     sb.area = 0;
     float *scratch = wbuf + lane;
     const Strided spx = {scratch, 32}, spy = {scratch + 8 * 32, 32};
     const Strided shx = {scratch + 16 * 32, 32}, shy = {scratch + 24 * 32, 32};
     const float hx2 = (float)(int)(bx.clamp0 - 1.f), hy2 = (float)(int)(bx.clamp1 - 1.f);
     int m_own = -1;
-    if (q < chunk_n) {
-        const float *src = cubes + ((size_t)b * a.N + chunk * SC_CHUNK + q) * 15;
+    if (q >= 0) {
+        const float *src = cubes + ((size_t)b * N + chunk * SC_CHUNK + q) * 15;
         float cube[15], cxy[16];
 #pragma unroll
         for (int i = 0; i < 15; ++i) cube[i] = ld_stream(src + i);
@@ -266,7 +267,25 @@ __device__ __forceinline__ void seg_item(const ScoreArgs &a, int b, const WcrBox
         if (lane == p) { my_inter = it; my_bube = bu; }
     }
     __syncwarp();
-    if (q < chunk_n) a.ws.segcnt[(size_t)b * a.N + chunk * SC_CHUNK + q] = make_int2(my_inter, my_bube);
+    if (q >= 0) segcnt[(size_t)b * N + chunk * SC_CHUNK + q] = make_int2(my_inter, my_bube);
+}
+
+// seg item: proposals grp*32 .. grp*32+31 of the chunk. A proposal that provably holds no point
+// (ScoreWs::mayhit == 0, see score_prep_kernel) scores 0 whatever its mask term is: its hull is
+// not filled here -- segcnt = (-1, -1) -- but lazily by the epilogue if it reaches the top-k.
+__device__ __forceinline__ void seg_item(const ScoreArgs &a, int b, const WcrBox &bx, const WcrImage &im,
+                                         int chunk, int grp, float *wbuf, int lane)
+{
+    const int chunk_n = min(SC_CHUNK, a.N - chunk * SC_CHUNK);
+    if (grp * 32 >= chunk_n) return;
+    int q = grp * 32 + lane;
+    if (q >= chunk_n) q = -1;
+    if (q >= 0 && a.seg_lazy) {
+        const size_t o = (size_t)b * a.N + chunk * SC_CHUNK + q;
+        if (!a.ws.mayhit[o]) { a.ws.segcnt[o] = make_int2(-1, -1); q = -1; }
+    }
+    if (__any_sync(0xffffffffu, q >= 0))
+        seg_group(a.cubes ? a.cubes : a.ws.cubes, a.N, a.seg_bits + a.seg_off[b], a.ws.segcnt, b, bx, im, chunk, q, wbuf, lane);
 }
 
 // Terms of one proposal (epilogue and record writer share it).
@@ -284,7 +303,9 @@ __device__ __forceinline__ PropTerms prop_terms(const ScoreArgs &a, const float 
     t.sseg = 1.f;
     if (a.sc.e_seg > 0) {
         const int2 sc2 = __ldcg(a.ws.segcnt + o);
-        t.sseg = seg_ratio(sc2.x, sc2.y, area, a.sc.seg_mode);
+        // (-1, -1): skipped by its seg item because the point count is provably 0 -> the score is
+        // 0 for any finite mask term; the epilogue fills it in before writing a record
+        t.sseg = sc2.x < 0 ? 1.f : seg_ratio(sc2.x, sc2.y, area, a.sc.seg_mode);
     }
     t.score = (ipow(t.siou, a.sc.e_iou) * ipow(t.spts, a.sc.e_pts)) * ipow(t.sseg, a.sc.e_seg);
     return t;
@@ -354,6 +375,15 @@ __device__ __forceinline__ void chunk_epilogue_warp(const ScoreArgs &a, int b, c
         if (bvv == -INFINITY) bi = -1;
         if (lane == r) { my_win = bi; my_wsc = bvv; }
         if (bi >= 0 && (bi & 31) == lane) wbuf[bi] = -INFINITY;   // taken
+        __syncwarp();
+    }
+    if (a.seg_lazy) {   // winners whose mask term was skipped: fill it in now (the scratch is free)
+        int q = -1;
+        if (lane < a.k && my_win >= 0 &&
+            __ldcg(a.ws.segcnt + (size_t)b * a.N + chunk * SC_CHUNK + my_win).x < 0) q = my_win;
+        __syncwarp();
+        if (__any_sync(0xffffffffu, q >= 0))
+        seg_group(a.cubes ? a.cubes : a.ws.cubes, a.N, a.seg_bits + a.seg_off[b], a.ws.segcnt, b, bx, im, chunk, q, wbuf, lane);
         __syncwarp();
     }
     float *rec_base = a.n_chunks == 1
