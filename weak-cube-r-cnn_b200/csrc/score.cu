@@ -747,7 +747,7 @@ extern "C" int wcr_score_topk(const WcrImage *images, const WcrBox *boxes, int n
         if (lazy_knob < 0) { const char *e3 = getenv("WCR_SEG_LAZY"); lazy_knob = e3 ? atoi(e3) : 1; }
         a.seg_lazy = lazy_knob && h_score->e_seg > 0 && h_score->e_pts > 0 && out_seg == nullptr;
         if (h_score->e_pts > 0) {
-            wcr::score_zgrid_kernel<<<n_boxes, 256, 0, st>>>(images, boxes, h_score->point_stride, 1, a.ws.zgrid);
+            wcr::score_zgrid_kernel<<<dim3(n_boxes, 8), 1024, 0, st>>>(images, boxes, h_score->point_stride, 1, a.ws.zgrid);
             WCR_CHECK_LAUNCH("score_zgrid_kernel");
             const dim3 grid(n_boxes, (N + 255) / 256);
             wcr::score_prep_kernel<<<grid, 256, 0, st>>>(images, boxes, n_boxes, cubes ? cubes : a.ws.cubes, N,

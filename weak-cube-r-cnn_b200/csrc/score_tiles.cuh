@@ -83,25 +83,35 @@ struct __align__(16) PParam {
 // range [zlo, zhi] (float bits) of the cube's corners
 
 // Depth range of the valid pixels of every cell of a 16 x 16 grid over a box's (sub-sampled) ROI:
-// [n_boxes][256] (min, max); an empty cell holds (+inf, -inf). One CTA per box, thread = cell.
-__global__ void __launch_bounds__(256)
+// [n_boxes][256] (min, max); an empty cell holds (+inf, -inf). grid (n_boxes, 8) x 1024 threads:
+// one WARP per cell, lanes stride over the cell's pixels (a small shard has few boxes: the
+// parallelism has to come from inside the box).
+__global__ void __launch_bounds__(1024)
 score_zgrid_kernel(const WcrImage *__restrict__ images, const WcrBox *__restrict__ boxes, int stride,
                    int use_pts, float2 *__restrict__ zgrid)
 {
-    const int b = blockIdx.x, cy = threadIdx.x >> 4, cx = threadIdx.x & 15;
+    const int b = blockIdx.x, cell = blockIdx.y * 32 + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+    const int cy = cell >> 4, cx = cell & 15;
     const WcrBox bx = boxes[b];
     const WcrImage im = images[bx.image];
     const Roi roi = box_roi(bx, im.H, im.W, stride, use_pts != 0);
     const int cw = max(1, (roi.ncols + 15) >> 4), chh = max(1, (roi.nrows + 15) >> 4);
+    const int r0 = cy * chh, r1 = min(r0 + chh, roi.nrows), c0 = cx * cw, c1 = min(c0 + cw, roi.ncols);
     float mn = INFINITY, mx = -INFINITY;
-    for (int r = cy * chh; r < min((cy + 1) * chh, roi.nrows); ++r) {
-        const float *row = im.depth + (size_t)(roi.v0 + r * stride) * im.depth_pitch + roi.u0;
-        for (int c = cx * cw; c < min((cx + 1) * cw, roi.ncols); ++c) {
-            const float d = __ldg(row + c * stride);
+    if (r1 > r0 && c1 > c0) {
+        const int w = c1 - c0, n = (r1 - r0) * w;
+        for (int i = lane; i < n; i += 32) {
+            const int r = r0 + i / w, c = c0 + i % w;
+            const float d = __ldg(im.depth + (size_t)(roi.v0 + r * stride) * im.depth_pitch + roi.u0 + c * stride);
             if (d > 0.f && d <= 3.402823466e38f) { mn = fminf(mn, d); mx = fmaxf(mx, d); }
         }
     }
-    zgrid[(size_t)b * 256 + threadIdx.x] = make_float2(mn, mx);
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        mn = fminf(mn, __shfl_xor_sync(0xffffffffu, mn, o));
+        mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+    }
+    if (lane == 0) zgrid[(size_t)b * 256 + cell] = make_float2(mn, mx);
 }
 
 // One thread per proposal: test constants (same expressions as score_items_kernel's
@@ -192,11 +202,15 @@ score_prep_kernel(const WcrImage *__restrict__ images, const WcrBox *__restrict_
         const int cw = max(1, (roi.ncols + 15) >> 4), chh = max(1, (roi.nrows + 15) >> 4);
         const float2 *zg = zgrid + (size_t)b * 256;
         mayhit = false;
-        for (int cy = rl / chh; cy <= min(15, rh / chh) && !mayhit; ++cy)
-            for (int cx = cl / cw; cx <= min(15, ch / cw); ++cx) {
+        const int cx0 = cl / cw, cx1 = min(15, ch / cw);
+        for (int cy = rl / chh; cy <= min(15, rh / chh) && !mayhit; ++cy) {
+            // a whole row of cells per trip, no exit inside it: the loads are independent and overlap
+#pragma unroll 4
+            for (int cx = cx0; cx <= cx1; ++cx) {
                 const float2 c = __ldg(zg + cy * 16 + cx);
-                if (!(zhi < c.x || zlo > c.y)) { mayhit = true; break; }
+                mayhit = mayhit || !(zhi < c.x || zlo > c.y);
             }
+        }
     }
     if (out_mayhit) out_mayhit[(size_t)b * N + j] = mayhit ? 1 : 0;
     if (!mayhit) { cl = 0xffff; ch = 0; rl = 0xffff; rh = 0; }   // fails every overlap test
