@@ -101,6 +101,25 @@ int wcr_ransac_ground(const float *pts /* float4 */, const int *count, int cap,
                       float *ws_eqs /* float4 [n_images][iters] workspace */,
                       void *stream);
 
+/* Allocation-free variant of wcr_ransac_ground. NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph
+ * capture, tight serving loops, harnesses that forbid it). Same arguments and results as
+ * wcr_ransac_ground minus ws_eqs: the hypothesis workspace is a file-scope `static __device__`
+ * array of WCR_RANSAC_STATIC_MAX_HYP float4 (1 MiB) that every GPU loading the library holds
+ * until exit. The call allocates nothing (no cudaMalloc / cudaFree / allocating library routine).
+ *   n_images * iters > WCR_RANSAC_STATIC_MAX_HYP -> WCR_EINVAL with a message (split the shard
+ *   or use wcr_ransac_ground).
+ * Every call on a device shares the one array and it keeps the last call's contents (nothing in
+ * it needs to start at zero: every hypothesis slot is rewritten before it is read; out_counts is
+ * cleared by the call): two calls that OVERLAP on the same GPU (different streams, or threads
+ * without ordering) race on it -- serialise them on one stream or with events. */
+#define WCR_RANSAC_STATIC_MAX_HYP 65536
+int wcr_ransac_ground_static(const float *pts /* float4 */, const int *count, int cap,
+                             int n_images, const int32_t *sample_idx, int iters,
+                             float thresh, uint64_t seed,
+                             float *out_eq, float *out_normal, int *out_best,
+                             int *out_counts, uint8_t *out_inlier_mask, void *stream);
+
 /* ------------------------------------------------------------ steps 2+3 -- */
 
 /* One GT 2D box of the shard. 32 bytes, device memory. */

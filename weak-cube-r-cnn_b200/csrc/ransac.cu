@@ -218,3 +218,80 @@ extern "C" int wcr_ransac_ground(const float *pts, const int *count, int cap, in
     WCR_CHECK_LAUNCH("ransac_select_kernel");
     return WCR_OK;
 }
+
+// ---- allocation-free variant (no counterpart in the reference; added
+// for callers that cannot cudaMalloc: CUDA graph capture, serving loops) -------
+//
+// The hypothesis workspace (ws_eqs of wcr_ransac_ground) lives in a file-scope device array of
+// WCR_RANSAC_STATIC_MAX_HYP float4 = 1 MiB, held by every GPU that loads the library until the
+// process exits. In HOST code `g_ransac_static_eqs` is only a stand-in for the symbol, never a
+// device address: the address is resolved once per device with cudaGetSymbolAddress (that device
+// current) and that pointer is what the kernels receive.
+namespace wcr {
+
+static __device__ __align__(256) float4 g_ransac_static_eqs[WCR_RANSAC_STATIC_MAX_HYP];
+
+constexpr int MAX_DEVICES = 64;
+static float4 *g_ransac_static_ptr[MAX_DEVICES];   // per device, 0 = not resolved yet
+
+// -> device address of the scratch array on the CURRENT device, or nullptr (error set)
+static float4 *ransac_static_scratch()
+{
+    int dev = -1;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) { set_error("cudaGetDevice: %s", cudaGetErrorString(e)); return nullptr; }
+    if (dev < 0 || dev >= MAX_DEVICES) { set_error("device ordinal %d out of range", dev); return nullptr; }
+    float4 *p = __atomic_load_n(&g_ransac_static_ptr[dev], __ATOMIC_ACQUIRE);
+    if (p) return p;
+    void *sym = nullptr;
+    e = cudaGetSymbolAddress(&sym, g_ransac_static_eqs);   // no allocation: the array is part of the module image
+    if (e != cudaSuccess || sym == nullptr) {
+        set_error("cudaGetSymbolAddress(g_ransac_static_eqs) on device %d: %s", dev,
+                  cudaGetErrorString(e));
+        return nullptr;
+    }
+    // two threads racing here resolve the same address; the store is idempotent
+    __atomic_store_n(&g_ransac_static_ptr[dev], (float4 *)sym, __ATOMIC_RELEASE);
+    return (float4 *)sym;
+}
+
+}  // namespace wcr
+
+extern "C" int wcr_ransac_ground_static(const float *pts, const int *count, int cap, int n_images,
+                                        const int32_t *sample_idx, int iters, float thresh,
+                                        uint64_t seed, float *out_eq, float *out_normal,
+                                        int *out_best, int *out_counts, uint8_t *out_inlier_mask,
+                                        void *stream)
+{
+    WCR_CHECK_DEVICE();
+    WCR_REQUIRE(pts && count && out_eq && out_normal && out_best && out_counts,
+                "wcr_ransac_ground_static: null pointer");
+    WCR_REQUIRE(n_images >= 0 && iters >= 1 && cap >= 1, "wcr_ransac_ground_static: bad sizes");
+    WCR_REQUIRE(n_images <= 65535, "wcr_ransac_ground_static: too many images for one call");
+    WCR_REQUIRE((int64_t)n_images * iters <= (int64_t)WCR_RANSAC_STATIC_MAX_HYP,
+                "wcr_ransac_ground_static: n_images * iters = %lld exceeds the static scratch of %d "
+                "hypotheses (WCR_RANSAC_STATIC_MAX_HYP); split the shard or use wcr_ransac_ground",
+                (long long)n_images * iters, WCR_RANSAC_STATIC_MAX_HYP);
+    WCR_REQUIRE(((uintptr_t)pts & 15) == 0, "wcr_ransac_ground_static: pts not 16-byte aligned");
+    if (n_images == 0) return WCR_OK;
+    WCR_REQUIRE((cap + wcr::RANSAC_TILE - 1) / wcr::RANSAC_TILE <= 65535,
+                "wcr_ransac_ground_static: cap too large");
+    float4 *eqs = wcr::ransac_static_scratch();
+    if (!eqs) return WCR_ELAUNCH;
+    // Nothing in the scratch has to start at zero: tile 0 of the count kernel writes every
+    // hypothesis (NaN for images with < 3 points) before the select kernel reads it, so the
+    // previous call's contents are dead. The counts live in the caller's out_counts and are
+    // cleared here, as in wcr_ransac_ground.
+    cudaError_t me = cudaMemsetAsync(out_counts, 0, (size_t)n_images * iters * sizeof(int), (cudaStream_t)stream);
+    if (me != cudaSuccess) { wcr::set_error("cudaMemsetAsync: %s", cudaGetErrorString(me)); return WCR_ELAUNCH; }
+    dim3 grid((iters + wcr::RANSAC_HPB - 1) / wcr::RANSAC_HPB, n_images,
+              (cap + wcr::RANSAC_TILE - 1) / wcr::RANSAC_TILE);
+    wcr::ransac_count_kernel<<<grid, wcr::RANSAC_TPB, 0, (cudaStream_t)stream>>>(
+        (const float4 *)pts, count, cap, sample_idx, iters, thresh, seed, eqs, out_counts);
+    WCR_CHECK_LAUNCH("ransac_count_kernel");
+    wcr::ransac_select_kernel<<<n_images, 256, 0, (cudaStream_t)stream>>>(
+        (const float4 *)pts, count, cap, eqs, out_counts, iters, thresh,
+        out_eq, out_normal, out_best, out_inlier_mask);
+    WCR_CHECK_LAUNCH("ransac_select_kernel");
+    return WCR_OK;
+}

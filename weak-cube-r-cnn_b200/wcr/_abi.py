@@ -30,6 +30,9 @@ SIGNATURES = {
     "wcr_ransac_ground": (c_int, [c_void_p, c_void_p, c_int, c_int, c_void_p, c_int, c_float, c_u64,
                                   c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
                                   c_void_p]),
+    "wcr_ransac_ground_static": (c_int, [c_void_p, c_void_p, c_int, c_int, c_void_p, c_int, c_float,
+                                         c_u64, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
+                                         c_void_p]),
     "wcr_probe_ffma": (c_i64, [c_void_p, c_i64, c_int, c_void_p]),
     "wcr_philox_block": (c_int, [c_u64, c_u32, c_u32, c_u32, c_u32, c_void_p, c_void_p]),
     "wcr_box_center_depth": (c_int, [c_void_p, c_void_p, c_int, c_void_p, c_void_p]),
