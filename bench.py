@@ -49,6 +49,9 @@ def parse():
                          "cpu_baseline leg, 6 per step for --impl reference)")
     ap.add_argument("--no-seg", action="store_true", help="skip the mask-coverage term")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--c4-images", type=int, default=8192,
+                    help="global image count of the strong-scaling block (BASELINE configs[3]); 0 = skip")
+    ap.add_argument("--c4-passes", type=int, default=3)
     return ap.parse_args()
 
 
@@ -183,6 +186,116 @@ def ncu_traffic_bytes():
     return total if seen == 2 else None
 
 
+# ------------------------------------------------- C4: strong scaling block --
+C4_SEED = 4321
+
+
+def run_c4(args, dev, rank, world, base_ims, priors, use_seg):
+    """BASELINE.json configs[3]: `--c4-images` images (8192) over the N ranks of this run,
+    image-sharded in blocks of 64 (wcr.job), one all-gather of the top-k records per pass.
+    STRONG scaling: the global image list is the same at every N (tiled from the 64 base
+    images of the headline workload through a fixed pseudo-random map, so host generation
+    stays bounded while box counts per rank vary). Returns the `c4_strong` dict (rank 0)."""
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+    from wcr import dist as wdist
+    from wcr.job import BlockSet, ResidentBlocks, StreamedBlocks
+    from wcr.proposals import ScoreConfig
+
+    cfg = ScoreConfig(k=TOPK, e_seg=1 if use_seg else 0)
+    bs = BlockSet(base_ims, args.c4_images, block=IMAGES_PER_GPU, map_seed=0, use_seg=use_seg)
+    lo, hi = wdist.shard_range(bs.n_blocks, rank, world)
+    gather = wdist.TopkGather(bs.n_boxes_of(range(lo, hi)), TOPK, dev)
+    res = ResidentBlocks(bs, range(lo, hi), NPROP, dev, priors=priors, score_cfg=cfg, seed=C4_SEED,
+                         records=gather.send)
+
+    def sync_all():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+            torch.cuda.synchronize()
+
+    res.run_pass(); gather.gather_padded()          # warm-up pass
+    sync_all()
+    P = max(args.c4_passes, 3)
+    ev = [[torch.cuda.Event(True) for _ in range(3)] for _ in range(P)]
+    for p in range(P):
+        sync_all()
+        ev[p][0].record(); res.run_pass(); ev[p][1].record(); gather.gather_padded(); ev[p][2].record()
+    sync_all()
+    pass_ms = sum(e[0].elapsed_time(e[2]) for e in ev) / P
+    work_ms = sum(e[0].elapsed_time(e[1]) for e in ev) / P
+    gather_ms = sum(e[1].elapsed_time(e[2]) for e in ev) / P
+    resident = gather.gather().clone()               # records of every rank, global box order
+
+    # end to end: pinned host planes -> device -> records on the host, double-buffered
+    st = StreamedBlocks(bs, range(lo, hi), NPROP, dev, priors=priors, score_cfg=cfg, seed=C4_SEED,
+                        records=gather.send)
+    after = gather.gather_padded if world > 1 else None
+    st.run_pass(after)
+    e2e_s = 0.0
+    for p in range(P):
+        sync_all()
+        t0 = time.perf_counter()
+        st.run_pass(after)
+        e2e_s += time.perf_counter() - t0
+    e2e_s /= P
+    same_local = bool(torch.equal(st.h_records[:st.n_boxes].view(torch.int32),
+                                  res.records[:res.n_boxes].cpu().view(torch.int32)))
+
+    t = torch.tensor([pass_ms, e2e_s, gather_ms], dtype=torch.float64, device=dev)
+    per_rank = torch.tensor([work_ms, float(res.n_boxes), float(same_local)], dtype=torch.float64, device=dev)
+    ranks = torch.empty((world, 3), dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        dist.all_gather_into_tensor(ranks.view(-1), per_rank)
+    else:
+        ranks[0] = per_rank
+    pass_ms, e2e_s, gather_ms = (float(x) for x in t.cpu())
+    ranks = ranks.cpu().numpy()
+
+    verified, how = None, None
+    if rank == 0:
+        if world > 1:
+            # the same global list in ONE process (this GPU alone, block by block from the host planes)
+            single = StreamedBlocks(bs, range(bs.n_blocks), NPROP, dev, priors=priors, score_cfg=cfg,
+                                    seed=C4_SEED)
+            want = single.run_pass()
+            got = resident.cpu()
+            verified = bool(got.shape == want.shape and torch.equal(got.view(torch.int32), want.view(torch.int32)))
+            how = (f"TopkGather.gather() of {world} ranks == the single-process records of the same "
+                   f"{args.c4_images} images (recomputed on rank 0), compared bit for bit")
+            del single
+        else:
+            verified = bool(ranks[:, 2].all())
+            how = "N=1: records of the host-streamed pass == records of the device-resident pass, bit for bit"
+    if world > 1:
+        dist.barrier()
+    if rank != 0:
+        return None
+    total_boxes = float(ranks[:, 1].sum())
+    total_props = total_boxes * NPROP
+    return {
+        "config": f"BASELINE configs[3]: {args.c4_images} images {W}x{H} over {world} GPU(s), strong scaling, "
+                  f"blocks of {IMAGES_PER_GPU} images, {NPROP} proposals/box, mask term {'on' if use_seg else 'off'}, "
+                  f"global list tiled from the 64 base images (fixed map)",
+        "scaling": "strong", "images": args.c4_images, "boxes": int(total_boxes), "passes_timed": P,
+        "value": total_props / (pass_ms * 1e-3), "unit": "proposals/s",
+        "ms_per_pass": pass_ms, "l2": "inputs of a pass (>= 1.5 GB per rank) far exceed L2",
+        "e2e": {"value": total_props / e2e_s, "unit": "proposals/s", "s_per_pass": e2e_s,
+                "h2d_bytes_per_pass_rank0": st.h2d_bytes, "d2h_bytes_per_pass_rank0": st.d2h_bytes,
+                "api": "wcr.job.StreamedBlocks (two slots, three streams)"},
+        "allgather_ms": gather_ms, "allgather_bytes_per_rank": int(gather.send.numel() * 4),
+        "rank_boxes": {"min": int(ranks[:, 1].min()), "max": int(ranks[:, 1].max())},
+        "rank_work_ms": {"min": float(ranks[:, 0].min()), "max": float(ranks[:, 0].max()),
+                         "all": [round(float(x), 3) for x in ranks[:, 0]]},
+        "imbalance": float(ranks[:, 0].max() / max(ranks[:, 0].mean(), 1e-9)),
+        "streamed_equals_resident": bool(ranks[:, 2].all()),
+        "gather_verified": verified, "gather_check": how,
+    }
+
+
 # ------------------------------------------------------------------ GPU arm --
 class ClockSampler:
     """nvidia-smi clocks / throttle reasons DURING the timed region."""
@@ -235,6 +348,7 @@ def run_wcr(args):
     local = int(os.environ.get("LOCAL_RANK", "0"))
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
+    numa = wdist.bind_to_gpu_numa(local)   # before any pinned allocation: first touch lands on the GPU's node
     if world > 1:
         # NCCL logs (its version banner included) go to stdout by default: keep stdout for the
         # one JSON line the driver parses
@@ -360,6 +474,13 @@ def run_wcr(args):
         dist.all_reduce(props)
     total_props = float(props.item())
 
+    c4 = None
+    if args.c4_images > 0:
+        del flush
+        base = ims if (rank == 0 and args.images == IMAGES_PER_GPU and args.boxes is None) else \
+            make_images(IMAGES_PER_GPU, 0, use_seg, None, dense=False)   # the same base set on every rank
+        c4 = run_c4(args, dev, rank, world, base, priors, use_seg)
+
     if rank == 0:
         peaks = {}
         try:
@@ -382,6 +503,7 @@ def run_wcr(args):
                     "one_shard_at_a_time": total_props * args.steps / e2e_sync_s},
             "gpu_launches": int(launches),
             "clocks": clocks,
+            "numa_rank0": numa,
             "roofline": {"bound": "fp32", "kernel": "score_tiles_kernel", "achieved": achieved,
                          "peak": fp32_probe_tflops, "unit": "TFLOP/s",
                          "frac": achieved / fp32_probe_tflops,
@@ -399,6 +521,8 @@ def run_wcr(args):
                              "peak": hbm_peak, "unit": "GB/s", "frac": cloud_gbs / hbm_peak,
                              "bytes_per_launch": cloud_bytes},
         }
+        if c4 is not None:
+            line["c4_strong"] = c4
         if not args.no_cpu_baseline and world == 1:
             from oracle import clib
             clib.build()

@@ -48,3 +48,27 @@ def test_topk_allgather_world2(tmp_path):
     rec = d["rec"]
     assert rec.shape == (25, 4, 20)
     assert torch.equal(rec[:, 0, 0], torch.arange(25, dtype=torch.float32))   # global box order kept
+
+
+def test_blockset_arithmetic():
+    """wcr.job.BlockSet: blocks cut at global image positions, box offsets, ragged last block."""
+    sys.path.insert(0, os.path.join(ROOT, "weak-cube-r-cnn_b200"))
+    import numpy as np
+    from wcr import synth
+    from wcr.job import BlockSet
+    from wcr.dist import shard_range
+    base = [synth.make_image(i, 48, 64, n_boxes=1 + i) for i in range(3)]
+    bs = BlockSet(base, 11, block=4, map_seed=0, use_seg=False)
+    assert bs.n_blocks == 3 and len(bs.images_of(2)) == 3
+    per_image = np.array([1 + j for j in bs.image_map])
+    assert bs.block_boxes.tolist() == [per_image[0:4].sum(), per_image[4:8].sum(), per_image[8:].sum()]
+    assert bs.box_offset[-1] == per_image.sum()
+    img, boxes, bits, off = bs.tables(1, np.arange(4, dtype=np.uint64) * 100 + 1000, np.arange(4, dtype=np.uint64) + 7)
+    assert bits is None and off is None
+    assert img["depth"].tolist() == [1000, 1100, 1200, 1300] and len(boxes) == bs.block_boxes[1]
+    assert boxes["image"].tolist() == sum(([i] * (1 + j) for i, j in enumerate(bs.images_of(1))), [])
+    # ranks own whole blocks; with 8192 images / 64 per block that is shard_range over images
+    for world in (1, 2, 4, 8):
+        for r in range(world):
+            lo, hi = shard_range(8192 // 64, r, world)
+            assert (lo * 64, hi * 64) == shard_range(8192, r, world)

@@ -23,6 +23,42 @@ def shard_range(n_images: int, rank: int, world: int):
     return lo, lo + base + (1 if rank < rem else 0)
 
 
+def bind_to_gpu_numa(local_rank: int) -> dict:
+    """Pin this process (and so its first-touch pinned host buffers) to the CPUs of the NUMA
+    node its GPU hangs off: eight ranks that all allocate on node 0 share one socket's memory
+    controllers for their H2D copies. Reads sysfs only; a box that does
+    not expose the topology (numa_node == -1, one node, a cpuset that excludes the node) is
+    left untouched and the reason is reported."""
+    import os
+    info = {"bound": False}
+    try:
+        p = torch.cuda.get_device_properties(local_rank)
+        bdf = f"{p.pci_domain_id:04x}:{p.pci_bus_id:02x}:{p.pci_device_id:02x}.0"
+        info["pci"] = bdf
+        node = int(open(f"/sys/bus/pci/devices/{bdf}/numa_node").read())
+        info["numa_node"] = node
+        nodes = [d for d in os.listdir("/sys/devices/system/node") if d.startswith("node") and d[4:].isdigit()]
+        info["n_nodes"] = len(nodes)
+        allowed = os.sched_getaffinity(0)
+        info["cpus_allowed"] = len(allowed)
+        if node < 0 or len(nodes) < 2:
+            info["why"] = "no NUMA topology exposed for this GPU / single node"
+            return info
+        cpus = set()
+        for part in open(f"/sys/devices/system/node/node{node}/cpulist").read().strip().split(","):
+            a, _, b = part.partition("-")
+            cpus.update(range(int(a), int(b or a) + 1))
+        cpus &= allowed
+        if not cpus:
+            info["why"] = "the process cpuset holds no CPU of the GPU's node"
+            return info
+        os.sched_setaffinity(0, cpus)
+        info["bound"], info["cpus_bound"] = True, len(cpus)
+    except (OSError, ValueError, AttributeError, RuntimeError) as e:
+        info["why"] = f"{type(e).__name__}: {e}"
+    return info
+
+
 def is_dist() -> bool:
     return dist.is_available() and dist.is_initialized() and dist.get_world_size() > 1
 

@@ -57,6 +57,9 @@ class ImageShard:
         self.device = device
         self.depths, self.grounds = [], []
         rec = np.zeros(len(depths), dtype=IMAGE_DTYPE)
+        if len(depths) and all(isinstance(Ks[i], torch.Tensor) and Ks[i].is_cuda for i in range(len(depths))):
+            # the reference hands Ks_scaled_per_box on the device: one transfer, not one sync per image
+            Ks = torch.stack([Ks[i].detach().reshape(3, 3) for i in range(len(depths))]).cpu().numpy()
         for i, (d, g) in enumerate(zip(depths, grounds)):
             d = d.to(device=device, dtype=torch.float32)
             if d.stride(-1) != 1:
@@ -69,7 +72,10 @@ class ImageShard:
                     g = (g > 0).to(torch.uint8)
                 if g.stride(-1) != 1:
                     g = g.contiguous()
-                assert g.shape[0] >= d.shape[0] and g.shape[1] >= d.shape[1] or True
+                if g.shape[0] < d.shape[0] or g.shape[1] < d.shape[1]:
+                    raise _abi.WcrError(
+                        f"wcr: ground map {tuple(g.shape)} of image {i} is smaller than its depth map "
+                        f"{tuple(d.shape)} (only the (1,1) dummy may be)")
             K = Ks[i]
             K = K.detach().cpu().numpy() if isinstance(K, torch.Tensor) else np.asarray(K)
             rec[i] = (d.data_ptr(), 0 if g is None else g.data_ptr(), d.shape[0], d.shape[1],
@@ -83,6 +89,26 @@ class ImageShard:
         self.max_H = int(rec["H"].max()) if len(depths) else 0
         self.max_W = int(rec["W"].max()) if len(depths) else 0
         self.has_ground = [g is not None for g in self.grounds]
+
+    @classmethod
+    def from_host_table(cls, rec: np.ndarray, device, table: torch.Tensor | None = None):
+        """Shard over planes the CALLER keeps alive: ``rec`` is an ``IMAGE_DTYPE`` array whose
+        pointer fields already hold device addresses (wcr.job builds these for views into one
+        big resident plane). ``table``: an existing device tensor the records will be copied
+        into by the caller (a pipeline slot); None => uploaded here."""
+        self = cls.__new__(cls)
+        self.device = torch.device(device)
+        if self.device.type != "cuda":
+            raise _abi.WcrError("wcr: CUDA device required (there is no CPU fallback on this path)")
+        self.depths, self.grounds = [], []
+        self.host_table = rec
+        self.table = table if table is not None else \
+            torch.from_numpy(rec.view(np.uint8).copy()).to(self.device, non_blocking=True)
+        self.n_images = len(rec)
+        self.max_H = int(rec["H"].max()) if len(rec) else 0
+        self.max_W = int(rec["W"].max()) if len(rec) else 0
+        self.has_ground = [int(g) != 0 for g in rec["ground"]]
+        return self
 
     def __len__(self):
         return self.n_images

@@ -86,6 +86,20 @@ class BoxTable:
         self.table = torch.from_numpy(self.host.view(np.uint8).copy()).to(shard.device)
         self.num_boxes_per_image = [len(r) for r in recs]
 
+    @classmethod
+    def from_host(cls, host: np.ndarray, device, table: torch.Tensor | None = None,
+                  num_boxes_per_image=None):
+        """Table from an already built ``BOX_DTYPE`` array. ``table``: an existing device byte
+        buffer (>= 32 * len(host)) the caller uploads into (pipeline slot); None => uploaded here."""
+        self = cls.__new__(cls)
+        self.host = host
+        self.n_boxes = len(host)
+        self.device = torch.device(device)
+        self.table = table if table is not None else \
+            torch.from_numpy(host.view(np.uint8).copy()).to(self.device, non_blocking=True)
+        self.num_boxes_per_image = num_boxes_per_image
+        return self
+
     def __len__(self):
         return self.n_boxes
 
@@ -188,15 +202,37 @@ class SegMasks:
         self.n_boxes = len(rois)
 
 
+def _segmasks_from_arrays(host_bits: np.ndarray, host_off: np.ndarray, device, bits=None, off=None):
+    """SegMasks over prebuilt arrays (wcr.job); ``bits`` / ``off``: existing device buffers the
+    caller uploads into, None => uploaded here."""
+    self = SegMasks.__new__(SegMasks)
+    self.host_bits, self.host_off = host_bits, host_off
+    self.bits = bits if bits is not None else \
+        torch.from_numpy(host_bits.view(np.int32).copy()).to(device, non_blocking=True)
+    self.off = off if off is not None else torch.from_numpy(host_off.copy()).to(device, non_blocking=True)
+    self.n_boxes = len(host_off) - 1
+    return self
+
+
+SegMasks.from_arrays = staticmethod(_segmasks_from_arrays)
+
+
 class ScoreWorkspace:
     """Caller-owned buffers of ``score_topk`` so a steady-state loop allocates
     nothing (and so the top-k records can be written straight into a registered
     NCCL send buffer, see wcr.dist)."""
 
-    def __init__(self, n_boxes: int, N: int, k: int, device, records: torch.Tensor | None = None):
+    def __init__(self, n_boxes: int, N: int, k: int, device, records: torch.Tensor | None = None,
+                 ws: torch.Tensor | None = None):
+        """``ws``: share the byte buffer of another workspace (>= the size this one needs);
+        launches that share it must be ordered on one stream."""
         lib = _abi.load()
         nbytes = int(lib.wcr_score_workspace_bytes(n_boxes, N, k))
-        self.ws = torch.empty((max(nbytes, 256),), dtype=torch.uint8, device=device)  # 256-B aligned by the allocator
+        if ws is not None:
+            assert ws.numel() >= nbytes, "shared score workspace too small"
+            self.ws = ws
+        else:
+            self.ws = torch.empty((max(nbytes, 256),), dtype=torch.uint8, device=device)  # 256-B aligned by the allocator
         self.records = records if records is not None else torch.empty(
             (n_boxes, k, RECORD_FLOATS), dtype=torch.float32, device=device)
         self.n_boxes, self.N, self.k = n_boxes, N, k
