@@ -209,8 +209,6 @@ int wcr_sample_cubes(const WcrImage *images, const WcrBox *boxes, int n_boxes,
  *             (utils.py:410-454) -> pixels strictly left of every hull edge
  *             (fill_polygon > 0, utils.py:456-488) -> mask_iou / mod_mask_iou
  *             (utils.py:225-245) against the box mask
- *   The mask term of a proposal that provably holds no depth point (score 0) is evaluated only if
- *   the proposal reaches the top-k, unless out_seg is requested.
  *   k <= WCR_MAX_TOPK; image sides <= 65535 pixels (the cull records hold 16-bit ROI indices)
  *   out_records [n_boxes][k][20]; slots beyond N hold idx = -1
  *   optional per-proposal outputs (NULL to skip), all [n_boxes][N]:
@@ -219,7 +217,12 @@ int wcr_sample_cubes(const WcrImage *images, const WcrBox *boxes, int n_boxes,
  *   ws        workspace, wcr_score_workspace_bytes(n_boxes, N, k) bytes, 256-byte aligned.
  *             After the call the uint64 at byte 8 holds the number of point tests the
  *             kernel issued (pairs the projected-box cull could not rule out; the
- *             counts are those of the unculled evaluation) -- bench.py's frac_executed. */
+ *             counts are those of the unculled evaluation) -- bench.py's frac_executed -- and the
+ *             uint64 at byte 16 the number of hulls filled for the mask term.
+ *   Mask term on demand: with seg_mode 0 and out_scores == out_seg == NULL, the hull of a
+ *   proposal is filled only if its bound iou^e_iou * pts^e_pts can still reach the box's k-th
+ *   best score (the ratio is <= 1, so the bound holds in floating point too); the records are
+ *   those of the full evaluation, bit for bit. */
 int64_t wcr_score_workspace_bytes(int n_boxes, int N, int k);
 int wcr_score_topk(const WcrImage *images, const WcrBox *boxes, int n_boxes,
                    const float *cubes, int N,

@@ -360,6 +360,33 @@ def test_score_seg_lazy_mask_term(cuda_lib):
             assert (ref["count"][::2] == 0).all() and (ref["count"][1::2] > 0).any()
 
 
+@pytest.mark.parametrize("N,k,e_pts,e_seg,e_iou", [(300, 16, 1, 1, 1), (1000, 16, 1, 1, 1), (1500, 32, 1, 2, 1),
+                                                   (1000, 1, 0, 1, 1), (700, 8, 1, 1, 0), (2500, 16, 2, 1, 1)])
+def test_score_seg_on_demand_equals_full_evaluation(cuda_lib, N, k, e_pts, e_seg, e_iou):
+    """Without per-proposal outputs the mask term is evaluated only for proposals whose bound
+    iou^a * pts^b can still reach the k-th best score (chunk_epilogue_warp). The records must be
+    those of the full evaluation (want_all=True fills every hull through the seg items), bit
+    for bit, for one and several 1024-proposal chunks, k = 1 .. 32 and every exponent mix."""
+    from wcr import synth
+    from wcr.proposals import propose, score_topk, ScoreConfig, SegMasks
+    H, W = 240, 320
+    ims, shard, boxes, priors, normals = _setup(3, H, W, n_boxes=4, first=51)
+    masks = [m for im in ims for m in synth.seg_masks(im["boxes"], H, W)]
+    seg = SegMasks(shard, boxes, masks)
+    cubes = propose(shard, boxes, priors, normals, N, seed=21)
+    cubes[5, ::3, 0:3] *= 6.0                  # a box where a third of the proposals hold no point
+    cubes[7, :, 0:3] *= 6.0                    # ... and one where none does (all bounds are zero)
+    cfg = ScoreConfig(e_iou=e_iou, e_pts=e_pts, e_seg=e_seg, k=k)
+    full = score_topk(shard, boxes, cubes, cfg=cfg, seg=seg, want_all=True)
+    rec_full = full["records"].clone()
+    lazy = score_topk(shard, boxes, cubes, cfg=cfg, seg=seg)
+    assert torch.equal(lazy["records"].view(torch.int32), rec_full.view(torch.int32))
+    # the winners' scores are the full evaluation's scores
+    idx = rec_full[:, :, 0].contiguous().view(torch.int32).long()
+    assert (idx >= 0).all()
+    assert torch.equal(torch.gather(full["scores"], 1, idx), rec_full[:, :, 1])
+
+
 def test_score_seg_degenerate(cuda_lib):
     """Empty masks, cubes behind the camera (non-finite corners), cubes entirely
     outside the image (hull collapses onto the border, duplicate corners)."""

@@ -1,0 +1,38 @@
+"""Diagnostic (GPU box): scoring launch chain at C2 in three modes + hull counter."""
+import os, sys, json, time
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT); sys.path.insert(0, os.path.join(ROOT, "weak-cube-r-cnn_b200"))
+import torch
+import bench
+from wcr import synth
+from wcr.pipeline import ShardRunner
+from wcr.proposals import ScoreConfig, score_topk, box_center_depth
+
+n_img = int(sys.argv[1]) if len(sys.argv) > 1 else 64
+ims = bench.make_images(n_img, 0, True, None, dense=False)
+priors = synth.make_priors()
+r = ShardRunner(ims, 1000, "cuda", priors=priors, score_cfg=ScoreConfig(k=16, e_seg=1), seed=1234)
+r.upload(); r.step(); torch.cuda.synchronize()
+z0 = box_center_depth(r.shard, r.boxes)
+flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
+
+def timed(fn, n=5):
+    ts = []
+    for _ in range(n):
+        flush.zero_(); e0, e1 = torch.cuda.Event(True), torch.cuda.Event(True)
+        e0.record(); out = fn(); e1.record(); torch.cuda.synchronize(); ts.append(e0.elapsed_time(e1))
+    return min(ts), out
+
+def run(cfg, want_all=False, seg=True):
+    return score_topk(r.shard, r.boxes, None, 1000, cfg, priors=r.priors, normals=r.normals, z0=z0, seed=1234,
+                      seg=r.seg if seg else None, workspace=r.ws, want_all=want_all)
+
+res = {}
+t, out = timed(lambda: run(ScoreConfig(k=16, e_seg=1)))
+res["seg_on_demand_ms"] = t; res["hulls_on_demand"] = out["workspace"].hulls_filled()
+t, out = timed(lambda: run(ScoreConfig(k=16, e_seg=1), want_all=True))
+res["seg_all_ms(want_all)"] = t; res["hulls_all"] = out["workspace"].hulls_filled()
+t, out = timed(lambda: run(ScoreConfig(k=16, e_seg=0), seg=False))
+res["noseg_ms"] = t
+res["n_proposals"] = r.n_proposals
+print(json.dumps(res))

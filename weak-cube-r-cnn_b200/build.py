@@ -21,6 +21,9 @@ ROOT = os.path.dirname(HERE)
 CSRC = os.path.join(HERE, "csrc")
 OUT_DIR = os.path.join(HERE, "wcr", "_lib")
 OUT = os.path.join(OUT_DIR, "libwcr_b200.so")
+# the first, unculled scoring kernel as an independent cross-check (tests only, never the product):
+# the same sources with -DWCR_KEEP_BASELINE_KERNEL, where wcr_score_topk runs score_items_kernel
+OUT_BASELINE = os.path.join(OUT_DIR, "libwcr_b200_baseline.so")
 
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a",
@@ -46,11 +49,16 @@ def _stale() -> bool:
 
 def build(force: bool = False, verbose: bool = False) -> str:
     os.makedirs(OUT_DIR, exist_ok=True)
-    if not force and not _stale():
+    if not force and not _stale() and os.path.exists(OUT_BASELINE) and \
+            os.path.getmtime(OUT_BASELINE) >= os.path.getmtime(OUT):
         return OUT
     nvcc = os.environ.get("NVCC", "nvcc")
     objs = []
     procs = []
+    base_obj = os.path.join(OUT_DIR, "score_baseline.o")
+    procs.append(("score.cu (baseline)", subprocess.Popen(
+        [nvcc, *NVCC_FLAGS, "-DWCR_KEEP_BASELINE_KERNEL", "-c", os.path.join(CSRC, "score.cu"), "-o", base_obj],
+        stdout=subprocess.PIPE, stderr=subprocess.STDOUT)))
     for src in sources():
         obj = os.path.join(OUT_DIR, os.path.basename(src)[:-3] + ".o")
         cmd = [nvcc, *NVCC_FLAGS, "-c", src, "-o", obj]
@@ -69,6 +77,9 @@ def build(force: bool = False, verbose: bool = False) -> str:
         raise RuntimeError("nvcc failed")
     subprocess.check_call([nvcc, "-gencode", "arch=compute_100a,code=sm_100a", "-shared",
                            "-o", OUT, *objs, "-lcudart"])
+    base_objs = [base_obj if os.path.basename(o) == "score.o" else o for o in objs]
+    subprocess.check_call([nvcc, "-gencode", "arch=compute_100a,code=sm_100a", "-shared",
+                           "-o", OUT_BASELINE, *base_objs, "-lcudart"])
     return OUT
 
 

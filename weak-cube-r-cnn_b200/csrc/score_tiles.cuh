@@ -36,7 +36,8 @@ namespace wcr {
 // keep every warp busy, down to 128 for small ones (wcr_score_topk decides; 512 -> 1024 gave
 // 11.14 -> 10.95 ms on C2)
 constexpr int TL_SEGS = SC_CHUNK / 32;   // seg items per chunk
-constexpr int TL_WBUF = 1024 + 3 * 32 * 4;   // per-warp scratch floats: a_u tile (also hull scratch / epilogue scores) + survivor slots
+constexpr int TL_SCORE_OFF = 1024 + 3 * 32 * 4;   // per-warp scratch floats: a_u tile (also hull scratch) + survivor slots ...
+constexpr int TL_WBUF = TL_SCORE_OFF + SC_CHUNK;  // ... + the epilogue's scores (hulls are filled while the scores are live)
 
 
 // Tiling of a box's (sub-sampled) ROI: a tile is LR = 2^lrlog rows x (32/LR)*32

@@ -270,9 +270,9 @@ __device__ __noinline__ void seg_group(const float *__restrict__ cubes, int N, c
     if (q >= 0) segcnt[(size_t)b * N + chunk * SC_CHUNK + q] = make_int2(my_inter, my_bube);
 }
 
-// seg item: proposals grp*32 .. grp*32+31 of the chunk. A proposal that provably holds no point
-// (ScoreWs::mayhit == 0, see score_prep_kernel) scores 0 whatever its mask term is: its hull is
-// not filled here -- segcnt = (-1, -1) -- but lazily by the epilogue if it reaches the top-k.
+// seg item: proposals grp*32 .. grp*32+31 of the chunk (only when EVERY mask term is wanted:
+// per-proposal outputs, or mod_mask_iou whose ratio is not bounded by 1; otherwise the epilogue
+// evaluates the few it needs, see chunk_epilogue_warp).
 __device__ __forceinline__ void seg_item(const ScoreArgs &a, int b, const WcrBox &bx, const WcrImage &im,
                                          int chunk, int grp, float *wbuf, int lane)
 {
@@ -280,12 +280,8 @@ __device__ __forceinline__ void seg_item(const ScoreArgs &a, int b, const WcrBox
     if (grp * 32 >= chunk_n) return;
     int q = grp * 32 + lane;
     if (q >= chunk_n) q = -1;
-    if (q >= 0 && a.seg_lazy) {
-        const size_t o = (size_t)b * a.N + chunk * SC_CHUNK + q;
-        if (!a.ws.mayhit[o]) { a.ws.segcnt[o] = make_int2(-1, -1); q = -1; }
-    }
-    if (__any_sync(0xffffffffu, q >= 0))
-        seg_group(a.cubes ? a.cubes : a.ws.cubes, a.N, a.seg_bits + a.seg_off[b], a.ws.segcnt, b, bx, im, chunk, q, wbuf, lane);
+    if (lane == 0) atomicAdd(a.ws.hulls, (unsigned long long)min(32, chunk_n - grp * 32));
+    seg_group(a.cubes ? a.cubes : a.ws.cubes, a.N, a.seg_bits + a.seg_off[b], a.ws.segcnt, b, bx, im, chunk, q, wbuf, lane);
 }
 
 // Terms of one proposal (epilogue and record writer share it).
@@ -293,7 +289,8 @@ struct PropTerms { float score, siou, spts, sseg; int count; ProjBox pb; };
 
 __device__ __forceinline__ PropTerms prop_terms(const ScoreArgs &a, const float *cube, size_t o,
                                                 const WcrBox &bx, const Intr &K, float lo0, float hi0,
-                                                float lo1, float hi1, int npts, int area)
+                                                float lo1, float hi1, int npts, int area,
+                                                bool with_seg = true)
 {
     PropTerms t;
     t.count = __ldcg(a.ws.count + o);
@@ -301,27 +298,54 @@ __device__ __forceinline__ PropTerms prop_terms(const ScoreArgs &a, const float 
     t.siou = iou_2d(bx.x1, bx.y1, bx.x2, bx.y2, t.pb);
     t.spts = npts > 0 ? (float)t.count / (float)npts : 0.f;
     t.sseg = 1.f;
-    if (a.sc.e_seg > 0) {
+    if (a.sc.e_seg > 0 && with_seg) {
         const int2 sc2 = __ldcg(a.ws.segcnt + o);
-        // (-1, -1): skipped by its seg item because the point count is provably 0 -> the score is
-        // 0 for any finite mask term; the epilogue fills it in before writing a record
-        t.sseg = sc2.x < 0 ? 1.f : seg_ratio(sc2.x, sc2.y, area, a.sc.seg_mode);
+        t.sseg = seg_ratio(sc2.x, sc2.y, area, a.sc.seg_mode);
     }
     t.score = (ipow(t.siou, a.sc.e_iou) * ipow(t.spts, a.sc.e_pts)) * ipow(t.sseg, a.sc.e_seg);
     return t;
 }
 
-// ---- epilogue of (box, chunk) by ONE warp: terms -> score -> top-k -> records ----------
-__device__ __forceinline__ void chunk_epilogue_warp(const ScoreArgs &a, int b, const WcrBox &bx,
-                                                    const WcrImage &im, int chunk, float *wbuf, int lane)
-{
-    const float *__restrict__ cubes = a.cubes ? a.cubes : a.ws.cubes;
-    const Intr K = {im.fx, im.fy, im.cx, im.cy};
+// ---- epilogue of a (box, chunk): terms -> score -> top-k -> records ----------------------
+//
+// Full evaluation (a.seg_lazy == 0): the chunk's seg items have filled every hull; the warp that
+// retires the chunk's last item computes every term, takes the top-k and writes the records.
+//
+// Mask term on demand (a.seg_lazy: mask_iou mode, no per-proposal scores / ratios asked for).
+// The score is ub * sseg^e with ub = iou^a * pts^b and 0 <= sseg <= 1, every factor rounded the
+// same way whether sseg is known or not, so score <= ub in floating point too. Only proposals
+// that can still reach the top-k need their hull filled:
+//   phase A (the warp that retires the chunk's last tile item): ub of every proposal -> ws.ub;
+//           the 32 best bounds are evaluated on the spot; T = k-th best ACTUAL score among them;
+//           every other proposal with ub >= T and ub > 0 (a zero bound is a zero score whatever
+//           the mask says) goes to the chunk's candidate list, which is cut into batches of 32
+//           and PUBLISHED on a dynamic queue that every warp of the grid serves before it takes
+//           a new tile item -- a chunk's hulls are filled by many warps, not by one;
+//   batch   (any warp): hull fill of 32 candidates, actual score -> ws.ub;
+//   phase B (the warp that retires the chunk's last batch): top-k over ws.ub. An unevaluated
+//           proposal has score <= ub < T <= k-th best actual score: it cannot be in the top-k,
+//           not even through a tie; unevaluated zero bounds ARE their exact score. So the top-k
+//           over the stored values is the top-k of the full evaluation, bit for bit
+//           (tests/test_score_gpu.py: on-demand == full evaluation == oracle).
+// Winners with a zero score get their mask term filled in for the record's s_seg field.
+struct ChunkCtx {
+    Intr K;
     float lo0, hi0, lo1, hi1;
-    clamp_bounds(bx.clamp0, lo0, hi0);
-    clamp_bounds(bx.clamp1, lo1, hi1);
-    const int npts = __ldcg(a.ws.npts + (size_t)b * a.n_chunks + chunk);
-    if (a.out_npts && chunk == 0 && lane == 0) a.out_npts[b] = npts;
+    int npts, area;
+    size_t cbase;     // first proposal of the chunk in [n_boxes][N] arrays
+    int chunk_n;      // proposals in the chunk
+};
+
+__device__ __forceinline__ ChunkCtx chunk_ctx(const ScoreArgs &a, int b, const WcrBox &bx, const WcrImage &im,
+                                              int chunk, int lane)
+{
+    ChunkCtx c;
+    c.K = {im.fx, im.fy, im.cx, im.cy};
+    clamp_bounds(bx.clamp0, c.lo0, c.hi0);
+    clamp_bounds(bx.clamp1, c.lo1, c.hi1);
+    c.npts = __ldcg(a.ws.npts + (size_t)b * a.n_chunks + chunk);
+    c.cbase = (size_t)b * a.N + (size_t)chunk * SC_CHUNK;
+    c.chunk_n = min(SC_CHUNK, a.N - chunk * SC_CHUNK);
     int area = 0;
     if (a.sc.e_seg > 0) {
         const Roi r1 = box_roi(bx, im.H, im.W, 1, true);
@@ -331,17 +355,27 @@ __device__ __forceinline__ void chunk_epilogue_warp(const ScoreArgs &a, int b, c
 #pragma unroll
         for (int o = 16; o > 0; o >>= 1) area += __shfl_xor_sync(0xffffffffu, area, o);
     }
+    c.area = area;
+    return c;
+}
+
+// scores (or bounds, with_seg == false) of the whole chunk -> sc[SC_CHUNK] (+ per-proposal outputs)
+__device__ __forceinline__ void chunk_scores(const ScoreArgs &a, int b, const WcrBox &bx, const ChunkCtx &c,
+                                             int chunk, bool with_seg, float *sc, int lane)
+{
+    const float *__restrict__ cubes = a.cubes ? a.cubes : a.ws.cubes;
+    if (a.out_npts && chunk == 0 && lane == 0) a.out_npts[b] = c.npts;
 #pragma unroll 1
     for (int i = 0; i < SC_CHUNK / 32; ++i) {
-        const int loc = i * 32 + lane, j = chunk * SC_CHUNK + loc;
+        const int loc = i * 32 + lane;
         float score = -INFINITY;
-        if (j < a.N) {
-            const size_t o = (size_t)b * a.N + j;
+        if (loc < c.chunk_n) {
+            const size_t o = c.cbase + loc;
             const float *src = cubes + o * 15;
             float cube[15];
 #pragma unroll
             for (int t = 0; t < 15; ++t) cube[t] = ld_stream(src + t);
-            const PropTerms t = prop_terms(a, cube, o, bx, K, lo0, hi0, lo1, hi1, npts, area);
+            const PropTerms t = prop_terms(a, cube, o, bx, c.K, c.lo0, c.hi0, c.lo1, c.hi1, c.npts, c.area, with_seg);
             score = t.score;
             if (a.out_scores) a.out_scores[o] = t.score;
             if (a.out_iou) a.out_iou[o] = t.siou;
@@ -352,9 +386,36 @@ __device__ __forceinline__ void chunk_epilogue_warp(const ScoreArgs &a, int b, c
                 d[0] = t.pb.x1; d[1] = t.pb.y1; d[2] = t.pb.x2; d[3] = t.pb.y2;
             }
         }
-        wbuf[loc] = score;
+        sc[loc] = score;
     }
     __syncwarp();
+}
+
+// hull fill of up to 32 proposals of the chunk (q = the lane's proposal or -1) whose bound is in
+// `ub`; returns the lane's actual score (-inf without a proposal) and stores it to ws.ub
+__device__ __forceinline__ float chunk_fill(const ScoreArgs &a, int b, const WcrBox &bx, const WcrImage &im,
+                                            const ChunkCtx &c, int chunk, int q, float ub, float *wbuf, int lane)
+{
+    const float *__restrict__ cubes = a.cubes ? a.cubes : a.ws.cubes;
+    const unsigned have = __ballot_sync(0xffffffffu, q >= 0);
+    if (lane == 0) atomicAdd(a.ws.hulls, (unsigned long long)__popc(have));
+    seg_group(cubes, a.N, a.seg_bits + a.seg_off[b], a.ws.segcnt, b, bx, im, chunk, q, wbuf, lane);
+    __syncwarp();
+    float actual = -INFINITY;
+    if (q >= 0) {
+        const int2 c2 = a.ws.segcnt[c.cbase + q];          // written by this very lane
+        const float sseg = seg_ratio(c2.x, c2.y, c.area, a.sc.seg_mode);
+        actual = ub * ipow(sseg, a.sc.e_seg);              // the product prop_terms forms
+        __stcg(a.ws.ub + c.cbase + q, actual);
+    }
+    return actual;
+}
+
+// top-k of sc[] -> records (or chunk candidates); the last chunk of a box merges
+__device__ __forceinline__ void chunk_select(const ScoreArgs &a, int b, const WcrBox &bx, const WcrImage &im,
+                                             const ChunkCtx &c, int chunk, float *sc, float *wbuf, int lane)
+{
+    const float *__restrict__ cubes = a.cubes ? a.cubes : a.ws.cubes;
     // k rounds of (max score, lowest index); winner r stays with lane r
     int my_win = -1;
     float my_wsc = 0.f;
@@ -363,7 +424,7 @@ __device__ __forceinline__ void chunk_epilogue_warp(const ScoreArgs &a, int b, c
 #pragma unroll 8
         for (int i = 0; i < SC_CHUNK / 32; ++i) {
             const int loc = i * 32 + lane;
-            const float vv = wbuf[loc];
+            const float vv = sc[loc];
             if (vv > bvv) { bvv = vv; bi = loc; }   // ascending loc keeps the lowest index
         }
 #pragma unroll
@@ -374,16 +435,18 @@ __device__ __forceinline__ void chunk_epilogue_warp(const ScoreArgs &a, int b, c
         }
         if (bvv == -INFINITY) bi = -1;
         if (lane == r) { my_win = bi; my_wsc = bvv; }
-        if (bi >= 0 && (bi & 31) == lane) wbuf[bi] = -INFINITY;   // taken
+        if (bi >= 0 && (bi & 31) == lane) sc[bi] = -INFINITY;   // taken
         __syncwarp();
     }
-    if (a.seg_lazy) {   // winners whose mask term was skipped: fill it in now (the scratch is free)
-        int q = -1;
-        if (lane < a.k && my_win >= 0 &&
-            __ldcg(a.ws.segcnt + (size_t)b * a.N + chunk * SC_CHUNK + my_win).x < 0) q = my_win;
-        __syncwarp();
-        if (__any_sync(0xffffffffu, q >= 0))
-        seg_group(a.cubes ? a.cubes : a.ws.cubes, a.N, a.seg_bits + a.seg_off[b], a.ws.segcnt, b, bx, im, chunk, q, wbuf, lane);
+    if (a.seg_lazy) {
+        // a winner with a zero score may never have been evaluated (zero bound): (re)fill its
+        // hull so that the record carries its s_seg; refilling an evaluated one changes nothing
+        const int q = (lane < a.k && my_win >= 0 && my_wsc == 0.f) ? my_win : -1;
+        const unsigned need = __ballot_sync(0xffffffffu, q >= 0);
+        if (need) {
+            if (lane == 0) atomicAdd(a.ws.hulls, (unsigned long long)__popc(need));
+            seg_group(cubes, a.N, a.seg_bits + a.seg_off[b], a.ws.segcnt, b, bx, im, chunk, q, wbuf, lane);
+        }
         __syncwarp();
     }
     float *rec_base = a.n_chunks == 1
@@ -401,7 +464,7 @@ __device__ __forceinline__ void chunk_epilogue_warp(const ScoreArgs &a, int b, c
             float cube[15];
 #pragma unroll
             for (int t = 0; t < 15; ++t) cube[t] = __ldg(src + t);
-            const PropTerms t = prop_terms(a, cube, o, bx, K, lo0, hi0, lo1, hi1, npts, area);
+            const PropTerms t = prop_terms(a, cube, o, bx, c.K, c.lo0, c.hi0, c.lo1, c.hi1, c.npts, c.area);
             rec[0] = __int_as_float(j);
             rec[1] = my_wsc;
 #pragma unroll
@@ -423,6 +486,130 @@ __device__ __forceinline__ void chunk_epilogue_warp(const ScoreArgs &a, int b, c
     }
 }
 
+// phase B of the on-demand path: every batch of the chunk has retired
+__device__ __forceinline__ void chunk_finalize_lazy(const ScoreArgs &a, int b, const WcrBox &bx, const WcrImage &im,
+                                                    const ChunkCtx &c, int chunk, float *wbuf, int lane)
+{
+    float *sc = wbuf + TL_SCORE_OFF;
+#pragma unroll 8
+    for (int i = 0; i < SC_CHUNK / 32; ++i) {
+        const int loc = i * 32 + lane;
+        sc[loc] = loc < c.chunk_n ? __ldcg(a.ws.ub + c.cbase + loc) : -INFINITY;
+    }
+    __syncwarp();
+    chunk_select(a, b, bx, im, c, chunk, sc, wbuf, lane);
+}
+
+// the warp that retired the chunk's last static item
+__device__ __forceinline__ void chunk_epilogue_warp(const ScoreArgs &a, int b, const WcrBox &bx,
+                                                    const WcrImage &im, int chunk, float *wbuf, int lane)
+{
+    const ChunkCtx c = chunk_ctx(a, b, bx, im, chunk, lane);
+    float *sc = wbuf + TL_SCORE_OFF;
+    if (!a.seg_lazy) {
+        chunk_scores(a, b, bx, c, chunk, true, sc, lane);
+        chunk_select(a, b, bx, im, c, chunk, sc, wbuf, lane);
+        return;
+    }
+    // ---- phase A ---------------------------------------------------------------------------
+    chunk_scores(a, b, bx, c, chunk, false, sc, lane);
+#pragma unroll 8
+    for (int i = 0; i < SC_CHUNK / 32; ++i) {
+        const int loc = i * 32 + lane;
+        if (loc < c.chunk_n) __stcg(a.ws.ub + c.cbase + loc, sc[loc]);
+    }
+    // the 32 best positive bounds (non-destructive arg-max rounds; bit i of `taken` <-> loc i*32+lane)
+    unsigned taken = 0u;
+    int q = -1;
+    float q_ub = 0.f;
+    for (int r = 0; r < 32; ++r) {
+        float bvv = 0.f; int bi = 0x7fffffff;
+#pragma unroll 8
+        for (int i = 0; i < SC_CHUNK / 32; ++i) {
+            const float vv = sc[i * 32 + lane];
+            if (!((taken >> i) & 1u) && vv > bvv) { bvv = vv; bi = i * 32 + lane; }
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            const float ov = __shfl_xor_sync(0xffffffffu, bvv, o);
+            const int oi = __shfl_xor_sync(0xffffffffu, bi, o);
+            if (ov > bvv || (ov == bvv && oi < bi)) { bvv = ov; bi = oi; }
+        }
+        if (bi == 0x7fffffff) break;                        // uniform: no positive bound left
+        if ((bi & 31) == lane) taken |= 1u << (bi >> 5);
+        if (lane == r) { q = bi; q_ub = bvv; }
+    }
+    float T = -INFINITY;
+    if (__any_sync(0xffffffffu, q >= 0)) {
+        const float actual = chunk_fill(a, b, bx, im, c, chunk, q, q_ub, wbuf, lane);
+        // T = k-th largest actual score of the first batch (rank by counting; ties by lane)
+        int rank = 0;
+        for (int l = 0; l < 32; ++l) {
+            const float v = __shfl_sync(0xffffffffu, actual, l);
+            rank += (v > actual) || (v == actual && l < lane);
+        }
+        const unsigned kth = __ballot_sync(0xffffffffu, rank == a.k - 1 && actual > -INFINITY);
+        if (kth) T = __shfl_sync(0xffffffffu, actual, __ffs(kth) - 1);
+    }
+    // candidates: not in the first batch, positive bound, bound >= T
+    uint16_t *cl = a.ws.candlist + ((size_t)b * a.n_chunks + chunk) * SC_CHUNK;
+    int n_cand = 0;
+#pragma unroll 1
+    for (int i = 0; i < SC_CHUNK / 32; ++i) {
+        const float vv = sc[i * 32 + lane];
+        const bool cnd = !((taken >> i) & 1u) && vv > 0.f && vv >= T;
+        const unsigned bm = __ballot_sync(0xffffffffu, cnd);
+        if (cnd) cl[n_cand + __popc(bm & ((1u << lane) - 1u))] = (uint16_t)(i * 32 + lane);
+        n_cand += __popc(bm);
+    }
+    const int n_batches = (n_cand + 31) >> 5;
+    if (n_batches == 0) {
+        __threadfence();                                     // first-batch scores were stored by other lanes
+        __syncwarp();
+        chunk_finalize_lazy(a, b, bx, im, c, chunk, wbuf, lane);
+    } else {
+        const int bc = b * a.n_chunks + chunk;
+        if (lane == 0) { a.ws.ncand[bc] = n_cand; }
+        __threadfence();                                     // bounds, first-batch scores, list, count
+        __syncwarp();
+        if (lane == 0) {
+            const int start = atomicAdd(a.ws.dynq + 1, n_batches);      // reserve
+            for (int i = 0; i < n_batches; ++i)
+                *((volatile int *)a.ws.segq + start + i) = bc * 32 + i + 1;   // publish (0 = not yet)
+        }
+    }
+    __threadfence();
+    __syncwarp();
+    if (lane == 0) atomicAdd(a.ws.dynq + 2, 1);              // chunks through phase A
+}
+
+// One entry of the dynamic queue: batch `batch` of the candidates of (box, chunk).
+__device__ __forceinline__ void dyn_seg_batch(const ScoreArgs &a, int code, float *wbuf, int lane)
+{
+    const int bc = code >> 5, batch = code & 31;
+    const int b = bc / a.n_chunks, chunk = bc - b * a.n_chunks;
+    const WcrBox bx = a.boxes[b];
+    const WcrImage im = a.images[bx.image];
+    const ChunkCtx c = chunk_ctx(a, b, bx, im, chunk, lane);
+    const int n_cand = __ldcg(a.ws.ncand + bc);
+    const uint16_t *cl = a.ws.candlist + (size_t)bc * SC_CHUNK;
+    int q = -1;
+    float ub = 0.f;
+    if (batch * 32 + lane < n_cand) {
+        q = (int)__ldcg(cl + batch * 32 + lane);
+        ub = __ldcg(a.ws.ub + c.cbase + q);
+    }
+    chunk_fill(a, b, bx, im, c, chunk, q, ub, wbuf, lane);
+    __threadfence();
+    __syncwarp();
+    int last = 0;
+    if (lane == 0) last = (atomicAdd(a.ws.seg_pending + bc, 1) == ((n_cand + 31) >> 5) - 1);
+    last = __shfl_sync(0xffffffffu, last, 0);
+    if (!last) return;
+    __threadfence();
+    chunk_finalize_lazy(a, b, bx, im, c, chunk, wbuf, lane);
+}
+
 template <int WARPS, int MINB, int GRP, bool F2, bool ICNT = false>
 __global__ void __launch_bounds__(WARPS * 32, MINB) score_tiles_kernel(const ScoreArgs a)
 {
@@ -434,31 +621,64 @@ __global__ void __launch_bounds__(WARPS * 32, MINB) score_tiles_kernel(const Sco
     const int total = prefix[a.n_boxes];
     const int subs = SC_CHUNK / a.ps;   // tile items per (chunk, tile)
 
-    // Queues. Default (a.split_queues = 1): tile items and seg items have their own counters; the
-    // last warp of every CTA prefers seg items, the others tile items, and each falls back to
-    // the other queue when its own runs dry -- the two kinds of item run concurrently on an SM
-    // (integer-heavy next to FMA-heavy) but a warp rarely switches code path, which the
-    // instruction caches reward (11.37 -> 11.22 ms). split_queues = 0: ONE queue, the seg items
-    // of a chunk spread evenly among its tile items.
-    const int seg_total = (a.split_queues && use_seg) ? a.n_boxes * a.n_chunks * TL_SEGS : 0;
-    const bool pref_seg = a.split_queues && use_seg && (wid >= WARPS - a.split_queues);
+    // Queues: tile items and seg items have their own counters; the last warp of every CTA prefers
+    // seg items, the others tile items, and each falls back to the other queue when its own runs
+    // dry -- the two kinds of item run concurrently on an SM (integer-heavy next to FMA-heavy) but
+    // a warp rarely switches code path, which the instruction caches reward. Seg items exist only
+    // when every mask term is wanted (a.seg_lazy == 0); otherwise the epilogues fill the few hulls
+    // they need and every warp works on tiles.
+    const int nseg = (use_seg && !a.seg_lazy) ? TL_SEGS : 0;
+    const int seg_total = a.n_boxes * a.n_chunks * nseg;
+    const bool pref_seg = nseg > 0 && wid == WARPS - 1;
     bool seg_left = seg_total > 0, tile_left = true;
+    const int total_chunks = a.n_boxes * a.n_chunks;
+    volatile int *dynq = a.ws.dynq;   // [0] head, [1] tail (reserved), [2] chunks through phase A
     for (;;) {
-        int item = -1, kind = -1;   // kind: 0 tile queue, 1 seg queue, 2 the single mixed queue
-        if (a.split_queues) {
-            while (kind < 0 && (seg_left || tile_left)) {
-                const bool try_seg = seg_left && (pref_seg || !tile_left);
-                if (lane == 0) item = atomicAdd(a.ws.queue + (try_seg ? 1 : 0), 1);
-                item = __shfl_sync(0xffffffffu, item, 0);
-                if (try_seg) { if (item < seg_total) kind = 1; else seg_left = false; }
-                else { if (item < total) kind = 0; else tile_left = false; }
+        if (a.seg_lazy) {
+            // published hull batches first: they unblock a chunk's top-k, and the data is warm
+            int code = 0;
+            if (lane == 0) {
+                const int head = dynq[0];
+                if (head < dynq[1]) {
+                    if (atomicCAS(a.ws.dynq, head, head + 1) == head) {
+                        volatile int *e = (volatile int *)a.ws.segq + head;
+                        while ((code = *e) == 0) __nanosleep(20);   // reserved, being written
+                    } else {
+                        code = -1;                                   // lost the race: look again
+                    }
+                }
             }
-        } else {
-            if (lane == 0) item = atomicAdd(a.ws.queue, 1);
-            item = __shfl_sync(0xffffffffu, item, 0);
-            if (item < total) kind = 2;
+            code = __shfl_sync(0xffffffffu, code, 0);
+            if (code < 0) continue;
+            if (code > 0) {
+                __threadfence();
+                dyn_seg_batch(a, code - 1, wbuf, lane);
+                __syncwarp();
+                continue;
+            }
         }
-        if (kind < 0) break;
+        int item = -1, kind = -1;   // kind: 0 tile queue, 1 seg queue
+        while (kind < 0 && (seg_left || tile_left)) {
+            const bool try_seg = seg_left && (pref_seg || !tile_left);
+            if (lane == 0) item = atomicAdd(a.ws.queue + (try_seg ? 1 : 0), 1);
+            item = __shfl_sync(0xffffffffu, item, 0);
+            if (try_seg) { if (item < seg_total) kind = 1; else seg_left = false; }
+            else { if (item < total) kind = 0; else tile_left = false; }
+        }
+        if (kind < 0) {
+            if (!a.seg_lazy) break;
+            // no static item left: serve the dynamic queue until every chunk is through phase A
+            // (the tail is final then) and the queue is drained
+            int done = 0;
+            if (lane == 0) {
+                const int pa = dynq[2];
+                __threadfence();
+                done = pa == total_chunks && dynq[0] >= dynq[1];
+                if (!done) __nanosleep(100);
+            }
+            if (__shfl_sync(0xffffffffu, done, 0)) break;
+            continue;
+        }
         int b = 0;
         if (kind == 1) {
             b = item / (a.n_chunks * TL_SEGS);
@@ -472,25 +692,15 @@ __global__ void __launch_bounds__(WARPS * 32, MINB) score_tiles_kernel(const Sco
         const WcrBox bx = a.boxes[b];
         const WcrImage im = a.images[bx.image];
         const TileGeom tg = tile_geom(bx, im.H, im.W, a.sc.point_stride, use_pts, GRP);
-        const int nseg = use_seg ? TL_SEGS : 0;
         const int pt = tile_items_per_chunk(tg, false, subs);
         const int per = pt + nseg;   // items that retire before the chunk's epilogue
         int chunk, seg_grp = -1, ti = 0;
         if (kind == 1) {
             const int r = item - b * (a.n_chunks * TL_SEGS);
             chunk = r / TL_SEGS; seg_grp = r - chunk * TL_SEGS;
-        } else if (kind == 0) {
+        } else {
             const int local = item - prefix[b];
             chunk = local / pt; ti = local - chunk * pt;
-        } else {
-            // mixed queue: the two kinds of item load different pipes and overlap well on one
-            // SM (queueing ALL seg items ahead of the tile items was measured 0.5 ms slower)
-            const int local = item - prefix[b];
-            chunk = local / per;
-            const int rem = local - chunk * per;
-            const int seg_before = (int)(((long long)rem * nseg) / per);
-            if ((int)(((long long)(rem + 1) * nseg) / per) > seg_before) seg_grp = seg_before;
-            else ti = rem - seg_before;
         }
         if (seg_grp >= 0) {
             seg_item(a, b, bx, im, chunk, seg_grp, wbuf, lane);

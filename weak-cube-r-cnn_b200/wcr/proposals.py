@@ -243,6 +243,12 @@ class ScoreWorkspace:
         of the workspace (include/wcr.h). Synchronises."""
         return int(self.ws[8:16].view(torch.int64).item())
 
+    def hulls_filled(self) -> int:
+        """Hulls the last ``score_topk`` filled for the mask term (all of them with
+        ``want_all=True``; only those whose bound could still reach the top-k otherwise).
+        Synchronises."""
+        return int(self.ws[16:24].view(torch.int64).item())
+
 
 def score_topk(shard: ImageShard, boxes: BoxTable, cubes: torch.Tensor | None, N: int | None = None,
                cfg: ScoreConfig | None = None, *, priors=None, normals=None, z0=None,
