@@ -110,6 +110,15 @@ __device__ __forceinline__ Roi box_roi(const WcrBox &bx, int H, int W, int s, bo
 
 struct PParam;   // score_tiles.cuh
 
+// Where a proposal's 15 floats come from (fetch_cube, score_tiles_kernel.cuh).
+struct CubeSrc {
+    const float *cubes;                    // caller's [n_boxes][N][15], or NULL: regenerated in-kernel
+    const float *priors, *normals, *z0;    // sampler inputs (cubes == NULL)
+    WcrSampleParams sp;
+    uint64_t seed;
+    int N;
+};
+
 // Device workspace layout (caller-owned, zeroed by cudaMemsetAsync up to `zero_bytes`).
 struct ScoreWs {
     int *queue;          // [1]   next item
@@ -127,7 +136,7 @@ struct ScoreWs {
     int *npts;           // [n_boxes][n_chunks] valid depth points (P_b), one copy per chunk
     int *count;          // [n_boxes][N] inside-counts
     float *cand;         // [n_boxes][n_chunks][k][20] chunk candidates (n_chunks > 1)
-    float *cubes;        // [n_boxes][N][15] when sampled by the library
+    float *cubes;        // [n_boxes][N][15]: baseline build only (the tile path regenerates sampled cubes)
     int2 *segcnt;        // [n_boxes][N] (|seg & hull|, |hull|) pixel counts of the mask term
     PParam *params;      // [n_boxes][N] point-test constants (tile path)
     int4 *cullbox;       // [n_boxes][N] cull boxes (tile path)
@@ -140,6 +149,7 @@ struct ScoreArgs {
     const WcrBox *boxes;
     int n_boxes;
     const float *cubes;
+    CubeSrc src;
     int N;
     WcrScoreParams sc;
     int k;
@@ -256,8 +266,12 @@ size_t carve(void *base, int n_boxes, int N, int k, bool need_cubes, bool need_s
 extern "C" int64_t wcr_score_workspace_bytes(int n_boxes, int N, int k)
 {
     if (n_boxes < 0 || N < 1 || k < 1) return -1;
-    // sized for the larger case (library-side sampling needs the cube buffer)
+#ifdef WCR_KEEP_BASELINE_KERNEL
     return (int64_t)carve(nullptr, n_boxes, N, k, true, true, nullptr, nullptr);
+#else
+    // no cube buffer: a sampled proposal is regenerated from its Philox counter where it is needed
+    return (int64_t)carve(nullptr, n_boxes, N, k, false, true, nullptr, nullptr);
+#endif
 }
 
 extern "C" int wcr_score_topk(const WcrImage *images, const WcrBox *boxes, int n_boxes,
@@ -293,7 +307,11 @@ extern "C" int wcr_score_topk(const WcrImage *images, const WcrBox *boxes, int n
 
     wcr::ScoreArgs a;
     size_t zero_bytes = 0;
+#ifdef WCR_KEEP_BASELINE_KERNEL
     carve(ws, n_boxes, N, k, cubes == nullptr, h_score->e_seg > 0, &a.ws, &zero_bytes);
+#else
+    carve(ws, n_boxes, N, k, false, h_score->e_seg > 0, &a.ws, &zero_bytes);
+#endif
     cudaError_t e = cudaMemsetAsync(ws, 0, zero_bytes, st);
     if (e != cudaSuccess) { wcr::set_error("cudaMemsetAsync: %s", cudaGetErrorString(e)); return WCR_ELAUNCH; }
     a.images = images; a.boxes = boxes; a.n_boxes = n_boxes; a.cubes = cubes; a.N = N;
@@ -304,13 +322,16 @@ extern "C" int wcr_score_topk(const WcrImage *images, const WcrBox *boxes, int n
     a.seg_bits = seg_bits; a.seg_off = seg_off; a.out_seg = out_seg;
     a.item_px = 0; a.grp = 8; a.ps = wcr::SC_CHUNK; a.seg_lazy = 0;
     const int sms = wcr::sm_count();
+    WCR_REQUIRE((N + 255) / 256 <= 65535, "wcr_score_topk: N too large");
+    a.src.cubes = cubes; a.src.priors = priors; a.src.normals = normals; a.src.z0 = z0;
+    a.src.seed = seed; a.src.N = N;
+    if (h_sample) a.src.sp = *h_sample; else memset(&a.src.sp, 0, sizeof(a.src.sp));
+#ifdef WCR_KEEP_BASELINE_KERNEL
     if (!cubes) {
-        WCR_REQUIRE((N + 255) / 256 <= 65535, "wcr_score_topk: N too large");
         wcr::launch_sample_cubes(images, boxes, n_boxes, priors, normals, z0, *h_sample, N, nullptr,
                                  seed, a.ws.cubes, st);
         WCR_CHECK_LAUNCH("sample_cubes_kernel");
     }
-#ifdef WCR_KEEP_BASELINE_KERNEL
     {   // libwcr_b200_baseline.so: the first, unculled kernel (score_items_baseline.cuh)
         // A 64-image shard has ~10^4 items of 4096 px; a single image with a handful of boxes
         // would leave most of the 296 resident CTAs idle, so its items are cut finer.
@@ -345,7 +366,7 @@ extern "C" int wcr_score_topk(const WcrImage *images, const WcrBox *boxes, int n
         wcr::score_zgrid_kernel<<<dim3(n_boxes, 8), 1024, 0, st>>>(images, boxes, h_score->point_stride, 1, a.ws.zgrid);
         WCR_CHECK_LAUNCH("score_zgrid_kernel");
         const dim3 grid(n_boxes, (N + 255) / 256);
-        wcr::score_prep_kernel<<<grid, 256, 0, st>>>(images, boxes, n_boxes, cubes ? cubes : a.ws.cubes, N,
+        wcr::score_prep_kernel<<<grid, 256, 0, st>>>(images, boxes, n_boxes, a.src, N,
                                                       h_score->point_stride, 1, a.ws.params, a.ws.cullbox,
                                                       a.ws.zgrid, a.ws.mayhit);
         WCR_CHECK_LAUNCH("score_prep_kernel");

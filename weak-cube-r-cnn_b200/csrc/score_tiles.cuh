@@ -119,7 +119,7 @@ score_zgrid_kernel(const WcrImage *__restrict__ images, const WcrBox *__restrict
 // prologue) and the conservative cull box.
 __global__ void __launch_bounds__(256)
 score_prep_kernel(const WcrImage *__restrict__ images, const WcrBox *__restrict__ boxes, int n_boxes,
-                  const float *__restrict__ cubes, int N, int stride, int use_pts,
+                  const CubeSrc src, int N, int stride, int use_pts,
                   PParam *__restrict__ out, int4 *__restrict__ out_box,
                   const float2 *__restrict__ zgrid, uint8_t *__restrict__ out_mayhit)
 {
@@ -128,10 +128,15 @@ score_prep_kernel(const WcrImage *__restrict__ images, const WcrBox *__restrict_
     const WcrBox bx = boxes[b];
     const WcrImage im = images[bx.image];
     const Roi roi = box_roi(bx, im.H, im.W, stride, use_pts != 0);
-    const float *src = cubes + ((size_t)b * N + j) * 15;
     float cube[15];
+    if (src.cubes) {
+        const float *cp = src.cubes + ((size_t)b * N + j) * 15;
 #pragma unroll
-    for (int i = 0; i < 15; ++i) cube[i] = ld_stream(src + i);
+        for (int i = 0; i < 15; ++i) cube[i] = ld_stream(cp + i);
+    } else {   // sampled by the library: straight from the counter RNG, never stored
+        const BoxCtx ctx = make_box_ctx(im, bx, src.priors, src.normals, src.z0[b], src.sp);
+        sample_cube(ctx, nullptr, N, src.seed, (uint32_t)b, (uint32_t)j, cube);
+    }
     PParam p;
     const bool live = roi.nrows > 0 && cube[3] > 0.f && cube[4] > 0.f && cube[5] > 0.f;
     float A[3], B[3], C[3], NO[3];

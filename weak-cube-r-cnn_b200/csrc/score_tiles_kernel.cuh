@@ -211,13 +211,33 @@ __device__ __forceinline__ void tile_item(const ScoreArgs &a, int b, const WcrIm
     __syncwarp();
 }
 
+// The 15 floats of proposal j of box b: read from the caller's array, or -- when the library
+// samples (cubes == NULL) -- REGENERATED from the counter RNG wherever they are needed (Philox is
+// keyed by (seed; proposal, box, attribute, try): no state, so a proposal is never stored; the
+// records carry the winners' cubes). Out of line: three call sites, none in the tile loop.
+__device__ __noinline__ void fetch_cube(const CubeSrc src, const WcrImage im, const WcrBox bx, int b, int j,
+                                        float *cube)
+{
+    if (src.cubes) {
+        const float *p = src.cubes + ((size_t)b * src.N + j) * 15;
+#pragma unroll
+        for (int i = 0; i < 15; ++i) cube[i] = ld_stream(p + i);
+        return;
+    }
+    const BoxCtx ctx = make_box_ctx(im, bx, src.priors, src.normals, src.z0[b], src.sp);
+    float c[15];
+    sample_cube(ctx, nullptr, src.N, src.seed, (uint32_t)b, (uint32_t)j, c);
+#pragma unroll
+    for (int i = 0; i < 15; ++i) cube[i] = c[i];
+}
+
 // ---- seg item: hull fill pixel counts of 32 proposals (lane = proposal for the march,
 // then the warp walks the 32 hulls with lanes = pixel rows) --------------------------
 // q = the lane's proposal within the chunk, or -1 for a lane without one.
 // Out of line and fed by value: two call sites (seg items, the epilogue's lazy fill) share one
 // copy of the hull code (measured faster than inlining it into the seg items: 10.76 vs 10.87 ms),
 // and the kernel's parameter block never has to be copied to local memory.
-__device__ __noinline__ void seg_group(const float *__restrict__ cubes, int N, const uint32_t *__restrict__ seg_bits_b,
+__device__ __noinline__ void seg_group(const CubeSrc src, const uint32_t *__restrict__ seg_bits_b,
                                        int2 *__restrict__ segcnt, int b, const WcrBox bx, const WcrImage im,
                                        int chunk, int q, float *wbuf, int lane)
 {
@@ -237,10 +257,8 @@ __device__ __noinline__ void seg_group(const float *__restrict__ cubes, int N, c
     const float hx2 = (float)(int)(bx.clamp0 - 1.f), hy2 = (float)(int)(bx.clamp1 - 1.f);
     int m_own = -1;
     if (q >= 0) {
-        const float *src = cubes + ((size_t)b * N + chunk * SC_CHUNK + q) * 15;
         float cube[15], cxy[16];
-#pragma unroll
-        for (int i = 0; i < 15; ++i) cube[i] = ld_stream(src + i);
+        fetch_cube(src, im, bx, b, chunk * SC_CHUNK + q, cube);
         project_cube(cube, K, lo0, hi0, lo1, hi1, cxy);
         bool finite = true;   // second clamp of the corners (roi_heads.py:950-952)
 #pragma unroll
@@ -267,7 +285,7 @@ __device__ __noinline__ void seg_group(const float *__restrict__ cubes, int N, c
         if (lane == p) { my_inter = it; my_bube = bu; }
     }
     __syncwarp();
-    if (q >= 0) segcnt[(size_t)b * N + chunk * SC_CHUNK + q] = make_int2(my_inter, my_bube);
+    if (q >= 0) segcnt[(size_t)b * src.N + chunk * SC_CHUNK + q] = make_int2(my_inter, my_bube);
 }
 
 // seg item: proposals grp*32 .. grp*32+31 of the chunk (only when EVERY mask term is wanted:
@@ -281,7 +299,7 @@ __device__ __forceinline__ void seg_item(const ScoreArgs &a, int b, const WcrBox
     int q = grp * 32 + lane;
     if (q >= chunk_n) q = -1;
     if (lane == 0) atomicAdd(a.ws.hulls, (unsigned long long)min(32, chunk_n - grp * 32));
-    seg_group(a.cubes ? a.cubes : a.ws.cubes, a.N, a.seg_bits + a.seg_off[b], a.ws.segcnt, b, bx, im, chunk, q, wbuf, lane);
+    seg_group(a.src, a.seg_bits + a.seg_off[b], a.ws.segcnt, b, bx, im, chunk, q, wbuf, lane);
 }
 
 // Terms of one proposal (epilogue and record writer share it).
@@ -360,10 +378,9 @@ __device__ __forceinline__ ChunkCtx chunk_ctx(const ScoreArgs &a, int b, const W
 }
 
 // scores (or bounds, with_seg == false) of the whole chunk -> sc[SC_CHUNK] (+ per-proposal outputs)
-__device__ __forceinline__ void chunk_scores(const ScoreArgs &a, int b, const WcrBox &bx, const ChunkCtx &c,
-                                             int chunk, bool with_seg, float *sc, int lane)
+__device__ __forceinline__ void chunk_scores(const ScoreArgs &a, int b, const WcrBox &bx, const WcrImage &im,
+                                             const ChunkCtx &c, int chunk, bool with_seg, float *sc, int lane)
 {
-    const float *__restrict__ cubes = a.cubes ? a.cubes : a.ws.cubes;
     if (a.out_npts && chunk == 0 && lane == 0) a.out_npts[b] = c.npts;
 #pragma unroll 1
     for (int i = 0; i < SC_CHUNK / 32; ++i) {
@@ -371,10 +388,8 @@ __device__ __forceinline__ void chunk_scores(const ScoreArgs &a, int b, const Wc
         float score = -INFINITY;
         if (loc < c.chunk_n) {
             const size_t o = c.cbase + loc;
-            const float *src = cubes + o * 15;
             float cube[15];
-#pragma unroll
-            for (int t = 0; t < 15; ++t) cube[t] = ld_stream(src + t);
+            fetch_cube(a.src, im, bx, b, chunk * SC_CHUNK + loc, cube);
             const PropTerms t = prop_terms(a, cube, o, bx, c.K, c.lo0, c.hi0, c.lo1, c.hi1, c.npts, c.area, with_seg);
             score = t.score;
             if (a.out_scores) a.out_scores[o] = t.score;
@@ -396,10 +411,9 @@ __device__ __forceinline__ void chunk_scores(const ScoreArgs &a, int b, const Wc
 __device__ __forceinline__ float chunk_fill(const ScoreArgs &a, int b, const WcrBox &bx, const WcrImage &im,
                                             const ChunkCtx &c, int chunk, int q, float ub, float *wbuf, int lane)
 {
-    const float *__restrict__ cubes = a.cubes ? a.cubes : a.ws.cubes;
     const unsigned have = __ballot_sync(0xffffffffu, q >= 0);
     if (lane == 0) atomicAdd(a.ws.hulls, (unsigned long long)__popc(have));
-    seg_group(cubes, a.N, a.seg_bits + a.seg_off[b], a.ws.segcnt, b, bx, im, chunk, q, wbuf, lane);
+    seg_group(a.src, a.seg_bits + a.seg_off[b], a.ws.segcnt, b, bx, im, chunk, q, wbuf, lane);
     __syncwarp();
     float actual = -INFINITY;
     if (q >= 0) {
@@ -415,7 +429,6 @@ __device__ __forceinline__ float chunk_fill(const ScoreArgs &a, int b, const Wcr
 __device__ __forceinline__ void chunk_select(const ScoreArgs &a, int b, const WcrBox &bx, const WcrImage &im,
                                              const ChunkCtx &c, int chunk, float *sc, float *wbuf, int lane)
 {
-    const float *__restrict__ cubes = a.cubes ? a.cubes : a.ws.cubes;
     // k rounds of (max score, lowest index); winner r stays with lane r
     int my_win = -1;
     float my_wsc = 0.f;
@@ -445,7 +458,7 @@ __device__ __forceinline__ void chunk_select(const ScoreArgs &a, int b, const Wc
         const unsigned need = __ballot_sync(0xffffffffu, q >= 0);
         if (need) {
             if (lane == 0) atomicAdd(a.ws.hulls, (unsigned long long)__popc(need));
-            seg_group(cubes, a.N, a.seg_bits + a.seg_off[b], a.ws.segcnt, b, bx, im, chunk, q, wbuf, lane);
+            seg_group(a.src, a.seg_bits + a.seg_off[b], a.ws.segcnt, b, bx, im, chunk, q, wbuf, lane);
         }
         __syncwarp();
     }
@@ -460,10 +473,8 @@ __device__ __forceinline__ void chunk_select(const ScoreArgs &a, int b, const Wc
         } else {
             const int j = chunk * SC_CHUNK + my_win;
             const size_t o = (size_t)b * a.N + j;
-            const float *src = cubes + o * 15;
             float cube[15];
-#pragma unroll
-            for (int t = 0; t < 15; ++t) cube[t] = __ldg(src + t);
+            fetch_cube(a.src, im, bx, b, j, cube);
             const PropTerms t = prop_terms(a, cube, o, bx, c.K, c.lo0, c.hi0, c.lo1, c.hi1, c.npts, c.area);
             rec[0] = __int_as_float(j);
             rec[1] = my_wsc;
@@ -507,12 +518,12 @@ __device__ __forceinline__ void chunk_epilogue_warp(const ScoreArgs &a, int b, c
     const ChunkCtx c = chunk_ctx(a, b, bx, im, chunk, lane);
     float *sc = wbuf + TL_SCORE_OFF;
     if (!a.seg_lazy) {
-        chunk_scores(a, b, bx, c, chunk, true, sc, lane);
+        chunk_scores(a, b, bx, im, c, chunk, true, sc, lane);
         chunk_select(a, b, bx, im, c, chunk, sc, wbuf, lane);
         return;
     }
     // ---- phase A ---------------------------------------------------------------------------
-    chunk_scores(a, b, bx, c, chunk, false, sc, lane);
+    chunk_scores(a, b, bx, im, c, chunk, false, sc, lane);
 #pragma unroll 8
     for (int i = 0; i < SC_CHUNK / 32; ++i) {
         const int loc = i * 32 + lane;
