@@ -64,7 +64,8 @@ def workload_name(images, seg=True, boxes=None):
 
 def make_images(n, first, seg, n_boxes=None, dense=True):
     """Synthetic images first..first+n-1. With ``dense=False`` the per-box masks are
-    bit-packed per image right away (a 1024-image shard would hold 6 GB of dense masks)."""
+    bit-packed per image right away (a 1024-image shard would hold 6 GB of dense masks);
+    ``dense="both"`` keeps the dense masks beside the packed ones."""
     import numpy as np
     from wcr import synth
     from wcr.proposals import pack_box_masks
@@ -75,7 +76,7 @@ def make_images(n, first, seg, n_boxes=None, dense=True):
             m = synth.seg_masks(im["boxes"], H, W)
             if dense:
                 im["seg"] = m
-            else:
+            if dense is not True:
                 b = im["boxes"].numpy()
                 rois = np.stack([np.minimum(np.maximum(b[:, 0], 0), W).astype(np.int32),
                                  np.minimum(np.maximum(b[:, 1], 0), H).astype(np.int32),
@@ -359,7 +360,7 @@ def run_wcr(args):
 
     # weak scaling: every rank owns `images` images of the global synthetic set
     use_seg = not args.no_seg
-    ims = make_images(args.images, rank * args.images, use_seg, args.boxes, dense=False)
+    ims = make_images(args.images, rank * args.images, use_seg, args.boxes, dense="both")
     priors = synth.make_priors()
     n_local_boxes = sum(len(im["boxes"]) for im in ims)
     gather = wdist.TopkGather(n_local_boxes, TOPK, dev)
@@ -407,6 +408,7 @@ def run_wcr(args):
     if world > 1:
         dist.barrier()
     launches = _abi.launch_count()
+    hulls = runner.ws.hulls_filled() if use_seg else 0
     step_ms = sum(e[0].elapsed_time(e[1]) for e in ev)
     score_ms = sum(e[2].elapsed_time(e[3]) for e in ev) / args.steps
 
@@ -426,25 +428,52 @@ def run_wcr(args):
     e2e_sync_s = time.perf_counter() - t0
     # (b) the same work double-buffered (ShardPipeline): shard s + 1 is uploaded and the records
     # of shard s - 1 are downloaded while shard s is scored. Every step still copies all of its
-    # inputs from pinned host memory and its records back; this is the headline e2e figure.
+    # inputs from pinned host memory and its records back.
+    def pipelined(r_a, r_b, g_a, g_b):
+        pipe = ShardPipeline([r_a, r_b], after_step=[g_a.gather_padded, g_b.gather_padded] if world > 1 else None)
+        for s in range(4):
+            pipe.wait(s - 2); pipe.submit(s)
+        pipe.drain()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        for s in range(args.steps):
+            pipe.wait(s - 2)
+            pipe.submit(s)
+        pipe.wait(args.steps - 2); pipe.wait(args.steps - 1)
+        pipe.drain()
+        return time.perf_counter() - t0
+
     gather2 = wdist.TopkGather(n_local_boxes, TOPK, dev)
     runner2 = ShardRunner(ims, NPROP, dev, priors=priors, score_cfg=runner.score_cfg, seed=1234,
                           records=gather2.send)
-    pipe = ShardPipeline([runner, runner2],
-                         after_step=[gather.gather_padded, gather2.gather_padded] if world > 1 else None)
-    for s in range(4):
-        pipe.wait(s - 2); pipe.submit(s)
-    pipe.drain()
-    if world > 1:
-        dist.barrier()
-    torch.cuda.synchronize()
-    t0 = time.perf_counter()
-    for s in range(args.steps):
-        pipe.wait(s - 2)
-        pipe.submit(s)
-    pipe.wait(args.steps - 2); pipe.wait(args.steps - 1)
-    pipe.drain()
-    e2e_s = time.perf_counter() - t0
+    e2e_packed_s = pipelined(runner, runner2, gather, gather2)
+    # (c) the headline e2e: the per-box masks arrive DENSE, as the reference's object_masks()
+    # produces them (roi_heads.py:383-401): n_boxes x H x W bytes cross PCIe every step and are
+    # bit-packed on the device (wcr_pack_box_masks) inside the timed region
+    e2e_s, dense_h2d, e2e_dense_sync_s = e2e_packed_s, None, None
+    if use_seg:
+        gather3 = wdist.TopkGather(n_local_boxes, TOPK, dev)
+        rd = [ShardRunner(ims, NPROP, dev, priors=priors, score_cfg=runner.score_cfg, seed=1234,
+                          records=g.send, dense_seg=True) for g in (gather2, gather3)]
+        dense_h2d = rd[0].h2d_bytes
+        e2e_s = pipelined(rd[0], rd[1], gather2, gather3)
+        for _ in range(2):
+            rd[0].run_host()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        for s in range(args.steps):
+            rd[0].run_host()
+            if world > 1:
+                gather2.gather_padded()
+                torch.cuda.synchronize()
+        e2e_dense_sync_s = time.perf_counter() - t0
+        same = torch.equal(rd[0].h_records.view(torch.int32), runner.h_records.view(torch.int32))
+        assert same, "dense-mask path and pre-packed path disagree"
+        del rd, gather3
     del runner2, gather2
     clocks = sampler.stop() if rank == 0 else None
 
@@ -465,10 +494,11 @@ def run_wcr(args):
     cloud_bytes = args.images * H * W * (4 + 16)
     cloud_gbs = cloud_bytes / (min(cloud_ms) * 1e-3) / 1e9
 
-    t = torch.tensor([step_ms, e2e_s, score_ms, e2e_sync_s], dtype=torch.float64, device=dev)
+    t = torch.tensor([step_ms, e2e_s, score_ms, e2e_sync_s, e2e_packed_s, e2e_dense_sync_s or 0.0],
+                     dtype=torch.float64, device=dev)
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    step_ms, e2e_s, score_ms, e2e_sync_s = (float(x) for x in t.cpu())
+    step_ms, e2e_s, score_ms, e2e_sync_s, e2e_packed_s, e2e_dense_sync_s = (float(x) for x in t.cpu())
     props = torch.tensor([runner.n_proposals], dtype=torch.float64, device=dev)
     if world > 1:
         dist.all_reduce(props)
@@ -498,9 +528,17 @@ def run_wcr(args):
                        "parallelism": f"image-sharded x{world}, all-gather of top-k records",
                        "boxes_rank0": runner.n_boxes, "rng": "in-kernel Philox4x32-10"},
             "e2e": {"value": total_props * args.steps / e2e_s, "unit": "proposals/s",
-                    "h2d_bytes_per_step": runner.h2d_bytes, "d2h_bytes_per_step": runner.d2h_bytes,
+                    "h2d_bytes_per_step": dense_h2d if dense_h2d is not None else runner.h2d_bytes,
+                    "d2h_bytes_per_step": runner.d2h_bytes,
                     "api": "wcr.pipeline.ShardPipeline (double-buffered: copies of neighbouring steps overlap the pass)",
-                    "one_shard_at_a_time": total_props * args.steps / e2e_sync_s},
+                    "masks": ("dense per-box masks (n_boxes x H x W u8, as object_masks() yields them) cross PCIe "
+                              "every step and are bit-packed on the device" if dense_h2d is not None else "no mask term"),
+                    "one_shard_at_a_time": (total_props * args.steps / e2e_dense_sync_s) if e2e_dense_sync_s
+                    else total_props * args.steps / e2e_sync_s,
+                    "prepacked": {"value": total_props * args.steps / e2e_packed_s,
+                                  "h2d_bytes_per_step": runner.h2d_bytes,
+                                  "one_shard_at_a_time": total_props * args.steps / e2e_sync_s,
+                                  "masks": "bit-packed on the host before the timed region (loader-side)"}},
             "gpu_launches": int(launches),
             "clocks": clocks,
             "numa_rank0": numa,
@@ -514,6 +552,7 @@ def run_wcr(args):
                          "executed_flop_per_test": EXEC_FLOP_PER_TEST,
                          "tests_executed_frac": executed_per_launch / max(tests_per_launch, 1.0),
                          "frac_executed": EXEC_FLOP_PER_TEST * executed_per_launch / (score_ms * 1e-3) / 1e12 / fp32_probe_tflops,
+                         "hulls_filled_frac": hulls / max(runner.n_proposals, 1),
                          "kernel_ms": score_ms,
                          "kernel_share_of_step": score_ms * args.steps / step_ms,
                          "traffic": ncu_traffic_bytes()},

@@ -234,6 +234,15 @@ int wcr_score_topk(const WcrImage *images, const WcrBox *boxes, int n_boxes,
                    int32_t *out_count, float *out_proj, int32_t *out_npts,
                    void *ws, void *stream);
 
+/* Dense per-box object masks (the reference's masks_all_images, roi_heads.py:273, 383-401: one
+ * H x W map per object, non-zero == object) -> the seg_bits layout of wcr_score_topk, on the
+ * device. Box b reads mask (mask_idx ? mask_idx[b] : b), mask_stride bytes apart, rows
+ * mask_pitch bytes apart, over its integer ROI; words land at out_bits + seg_off[b] (the
+ * offsets the caller derives from the ROIs: nrows * ceil(ncols / 32) words per box). */
+int wcr_pack_box_masks(const uint8_t *masks, int64_t mask_stride, int mask_pitch,
+                       const int32_t *mask_idx, const WcrImage *images, const WcrBox *boxes,
+                       int n_boxes, const int64_t *seg_off, uint32_t *out_bits, void *stream);
+
 /* ------------------------------------------------- block-level drop-ins -- */
 /* One launch behind each helper the reference exposes by name (SURVEY A2.1-A2.5,
  * A3.2-A3.8); the fused entry points above use the same device functions. */

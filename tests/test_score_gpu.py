@@ -387,6 +387,53 @@ def test_score_seg_on_demand_equals_full_evaluation(cuda_lib, N, k, e_pts, e_seg
     assert torch.equal(torch.gather(full["scores"], 1, idx), rec_full[:, :, 1])
 
 
+def test_pack_box_masks_device_equals_host(cuda_lib):
+    """wcr_pack_box_masks (dense per-box masks -> seg_bits on the device) == the host packer, word
+    for word: boxes cut by the image border, empty ROIs, widths that are / are not multiples of
+    32, a mask_idx indirection, and a pitched (padded) mask tensor."""
+    from wcr.images import ImageShard
+    from wcr.proposals import BoxTable, SegMasks
+    from wcr import synth
+    H, W = 97, 133
+    ims = [synth.make_image(70 + i, H, W, n_boxes=1, dummy_ground=True) for i in range(2)]
+    shard = ImageShard([im["depth"].cuda() for im in ims], None, [im["K"] for im in ims])
+    bx = [torch.tensor([[-5.0, -3.0, 40.7, 50.2], [10.0, 10.0, 74.0, 30.0], [100.0, 60.0, 200.0, 120.0],
+                        [20.3, 20.3, 20.9, 40.0], [0.0, 0.0, 133.0, 97.0]]),
+          torch.tensor([[5.5, 6.5, 69.5, 80.0], [130.0, 90.0, 140.0, 99.0]])]
+    boxes = BoxTable(shard, bx, [torch.zeros(len(b), dtype=torch.int64) for b in bx])
+    g = torch.Generator().manual_seed(3)
+    n = len(boxes)
+    padded = torch.zeros((n, H + 3, W + 11), dtype=torch.uint8)
+    padded[:, :H, :W] = (torch.rand((n, H, W), generator=g) < 0.4).to(torch.uint8) * 7   # any non-zero == object
+    dense = padded[:, :H, :W]
+    host = SegMasks(shard, boxes, [dense[i] for i in range(n)])
+    dev = SegMasks.from_dense(shard, boxes, padded.cuda()[:, :H, :W])
+    assert np.array_equal(dev.host_off, host.host_off)
+    assert np.array_equal(dev.bits.cpu().numpy().view(np.uint32)[:host.host_off[-1]], host.host_bits[:host.host_off[-1]])
+    perm = torch.randperm(n, generator=g)
+    inv = torch.empty_like(perm); inv[perm] = torch.arange(n)
+    dev2 = SegMasks.from_dense(shard, boxes, dense[perm].contiguous().cuda(), mask_idx=inv)
+    assert torch.equal(dev2.bits, dev.bits)
+
+
+def test_shard_runner_dense_masks_equal_prepacked(cuda_lib):
+    from wcr import synth
+    from wcr.pipeline import ShardRunner
+    from wcr.proposals import ScoreConfig
+    H, W = 240, 320
+    ims = [synth.make_image(80 + i, H, W, n_boxes=3, dummy_ground=(i == 1)) for i in range(3)]
+    for im in ims:
+        im["seg"] = synth.seg_masks(im["boxes"], H, W)
+    kw = dict(priors=synth.make_priors(), score_cfg=ScoreConfig(k=8, e_seg=1), seed=3)
+    a = ShardRunner(ims, 400, "cuda", **kw).run_host().clone()
+    r = ShardRunner(ims, 400, "cuda", dense_seg=True, **kw)
+    assert r.h2d_bytes > 9 * H * W
+    assert torch.equal(r.run_host().view(torch.int32), a.view(torch.int32))
+    r.h_seg_dense.zero_()                   # new mask contents reach the kernel through upload()
+    b = r.run_host()
+    assert not torch.equal(b, a) and (b[:, :, 19] == 0).all()
+
+
 def test_score_seg_degenerate(cuda_lib):
     """Empty masks, cubes behind the camera (non-finite corners), cubes entirely
     outside the image (hull collapses onto the border, duplicate corners)."""

@@ -377,3 +377,49 @@ extern "C" int wcr_score_topk(const WcrImage *images, const WcrBox *boxes, int n
     return WCR_OK;
 #endif
 }
+
+// ---- dense per-box masks -> the bit-packed seg_bits layout --------------------------------
+// The reference's object masks arrive dense, one H x W map per box (roi_heads.py:383-401,
+// masks_all_images); wcr_score_topk wants them bit-packed over each box's integer ROI. One warp
+// per 32-pixel word: 32 byte loads (one 32-byte sector), one ballot, one store.
+namespace wcr {
+__global__ void __launch_bounds__(256)
+pack_box_masks_kernel(const uint8_t *__restrict__ masks, int64_t mask_stride, int mask_pitch,
+                      const int32_t *__restrict__ mask_idx, const WcrImage *__restrict__ images,
+                      const WcrBox *__restrict__ boxes, const int64_t *__restrict__ seg_off,
+                      uint32_t *__restrict__ out_bits)
+{
+    const int b = blockIdx.x, lane = threadIdx.x & 31;
+    const WcrBox bx = boxes[b];
+    const WcrImage im = images[bx.image];
+    const Roi r = box_roi(bx, im.H, im.W, 1, true);
+    const int nrows = r.ncols > 0 ? r.nrows : 0, wpr = (r.ncols + 31) >> 5;
+    const int n_words = nrows * wpr;
+    const uint8_t *m = masks + (size_t)(mask_idx ? mask_idx[b] : b) * mask_stride;
+    uint32_t *out = out_bits + seg_off[b];
+    const int warps = (blockDim.x >> 5) * gridDim.y;
+    for (int w = blockIdx.y * (blockDim.x >> 5) + (threadIdx.x >> 5); w < n_words; w += warps) {
+        const int row = w / wpr, c = (w - row * wpr) * 32 + lane;
+        bool on = false;
+        if (c < r.ncols) on = m[(size_t)(r.v0 + row) * mask_pitch + r.u0 + c] != 0;
+        const unsigned word = __ballot_sync(0xffffffffu, on);
+        if (lane == 0) out[w] = word;
+    }
+}
+}  // namespace wcr
+
+extern "C" int wcr_pack_box_masks(const uint8_t *masks, int64_t mask_stride, int mask_pitch,
+                                  const int32_t *mask_idx, const WcrImage *images, const WcrBox *boxes,
+                                  int n_boxes, const int64_t *seg_off, uint32_t *out_bits, void *stream)
+{
+    WCR_CHECK_DEVICE();
+    WCR_REQUIRE(masks && images && boxes && seg_off && out_bits, "wcr_pack_box_masks: null pointer");
+    WCR_REQUIRE(n_boxes >= 0 && mask_pitch >= 1 && mask_stride >= 0, "wcr_pack_box_masks: bad sizes");
+    if (n_boxes == 0) return WCR_OK;
+    WCR_REQUIRE(n_boxes <= 0x7fffffff / 4, "wcr_pack_box_masks: too many boxes");
+    // a 640 x 480 ROI is 9600 words: 4 CTAs x 8 warps per box keep a small shard busy too
+    wcr::pack_box_masks_kernel<<<dim3(n_boxes, 4), 256, 0, (cudaStream_t)stream>>>(
+        masks, mask_stride, mask_pitch, mask_idx, images, boxes, seg_off, out_bits);
+    WCR_CHECK_LAUNCH("pack_box_masks_kernel");
+    return WCR_OK;
+}

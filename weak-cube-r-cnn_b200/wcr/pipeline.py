@@ -20,11 +20,20 @@ from .proposals import (BoxTable, ProposalConfig, ScoreConfig, ScoreWorkspace, S
 class ShardRunner:
     def __init__(self, images: list[dict], N: int = 1000, device="cuda", *,
                  sample_cfg: ProposalConfig | None = None, score_cfg: ScoreConfig | None = None,
-                 priors: torch.Tensor, seed: int = 0, records: torch.Tensor | None = None):
+                 priors: torch.Tensor, seed: int = 0, records: torch.Tensor | None = None,
+                 dense_seg: bool = False):
         """``images``: host dicts with depth (H,W) f32, ground (H,W) u8 or (1,1),
         K (3,3), boxes (b,4), classes (b,) and -- when ``score_cfg.e_seg > 0`` -- seg
         (b,H,W) per-box masks or seg_packed (``pack_box_masks`` output). All images are uploaded into two padded device planes
-        so a step's H2D is a handful of large copies."""
+        so a step's H2D is a handful of large copies. ``dense_seg``: the per-box masks stay DENSE
+        on the host side (what the reference's ``object_masks`` produces, roi_heads.py:383-401):
+        every ``upload`` copies them (n_boxes x H x W bytes) and every ``step`` bit-packs them on the
+        device (``wcr_pack_box_masks``); default: packed once on the host at construction.
+
+        The geometry of a runner is FROZEN at construction: image sizes, intrinsics, boxes and
+        mask offsets are part of the device tables. Re-uploading (``upload``, ``ShardPipeline``)
+        may change the depth / ground / mask CONTENTS only; a batch with other boxes needs its
+        own runner (or ``wcr.job.StreamedBlocks``, which re-uploads the tables per block)."""
         self.device = torch.device(device)
         if self.device.type != "cuda":
             raise _abi.WcrError("wcr: CUDA device required (there is no CPU fallback on this path)")
@@ -56,8 +65,19 @@ class ShardRunner:
         self.boxes = BoxTable(self.shard, [im["boxes"] for im in images],
                               [im["classes"] for im in images])
         self.h_boxes = torch.from_numpy(self.boxes.host.view("uint8").copy()).pin_memory()
-        self.seg = self.h_seg = None
-        if self.score_cfg.e_seg > 0:
+        self.seg = self.h_seg = self.h_seg_dense = self.d_seg_dense = None
+        if self.score_cfg.e_seg > 0 and dense_seg:
+            nb_ = len(self.boxes)
+            self.h_seg_dense = torch.zeros((nb_, Hm, Wm), dtype=torch.uint8).pin_memory()
+            g = 0
+            for im in images:
+                h, w = im["depth"].shape
+                m = im["seg"]
+                self.h_seg_dense[g:g + len(m), :h, :w] = (torch.as_tensor(m) != 0).to(torch.uint8)
+                g += len(m)
+            self.d_seg_dense = self.h_seg_dense.to(self.device)
+            self.seg = SegMasks.from_dense(self.shard, self.boxes, self.d_seg_dense)
+        elif self.score_cfg.e_seg > 0:
             if all("seg_packed" in im for im in images):
                 self.seg = SegMasks(self.shard, self.boxes, packed=[w for im in images for w in im["seg_packed"]])
             else:
@@ -76,6 +96,8 @@ class ShardRunner:
     @property
     def h2d_bytes(self) -> int:
         seg = self.h_seg.numel() * 4 if self.h_seg is not None else 0
+        if self.h_seg_dense is not None:
+            seg = self.h_seg_dense.numel()
         return self.h_depth.numel() * 4 + self.h_ground.numel() + self.h_boxes.numel() + seg
 
     @property
@@ -88,6 +110,8 @@ class ShardRunner:
         self.boxes.table.copy_(self.h_boxes, non_blocking=True)
         if self.h_seg is not None:
             self.seg.bits.copy_(self.h_seg, non_blocking=True)
+        if self.h_seg_dense is not None:
+            self.d_seg_dense.copy_(self.h_seg_dense, non_blocking=True)
 
     def step(self, score_events=None):
         """Device-resident pass: 5 kernel launches, no host sync, no D2H.
@@ -96,6 +120,8 @@ class ShardRunner:
         self.normals = ground.normal_vector_from_maps(None, None, None, shard=self.shard,
                                                       seed=self.seed)
         z0 = box_center_depth(self.shard, self.boxes)
+        if self.d_seg_dense is not None:
+            self.seg.repack(self.d_seg_dense)       # dense masks of this step -> seg_bits, on the device
         if score_events is not None:
             score_events[0].record()
             out = self._score(z0)

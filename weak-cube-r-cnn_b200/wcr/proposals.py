@@ -202,6 +202,42 @@ class SegMasks:
         self.n_boxes = len(rois)
 
 
+def _segmasks_from_dense(shard: ImageShard, boxes: "BoxTable", masks: torch.Tensor, mask_idx=None):
+    """SegMasks packed ON THE DEVICE from dense masks (``wcr_pack_box_masks``): ``masks``
+    (n_masks, Hm, Wm) u8/bool CUDA tensor, the reference's ``masks_all_images``
+    (roi_heads.py:273); box b uses mask ``mask_idx[b]`` (default b). Only the word offsets are
+    computed on the host (from the box ROIs). ``repack(masks)`` refreshes the bits in place."""
+    self = SegMasks.__new__(SegMasks)
+    rois = box_rois(boxes, shard)
+    off = np.zeros(len(rois) + 1, dtype=np.int64)
+    if len(rois):
+        nrows = np.maximum(rois[:, 3] - rois[:, 1], 0)
+        ncols = np.maximum(rois[:, 2] - rois[:, 0], 0)
+        off[1:] = np.cumsum(np.where(ncols > 0, nrows, 0).astype(np.int64) * ((ncols + 31) // 32))
+    self.host_off, self.host_bits = off, None
+    self.bits = torch.zeros((max(int(off[-1]), 1),), dtype=torch.int32, device=shard.device)
+    self.off = torch.from_numpy(off.copy()).to(shard.device)
+    self.n_boxes = len(rois)
+    self._shard, self._boxes = shard, boxes
+    self._mask_idx = None if mask_idx is None else \
+        torch.as_tensor(mask_idx, dtype=torch.int32).to(shard.device).contiguous()
+    self.repack(masks)
+    return self
+
+
+def _segmasks_repack(self, masks: torch.Tensor):
+    _abi.require_cuda(masks)
+    if masks.dtype == torch.bool:
+        masks = masks.view(torch.uint8)
+    assert masks.dtype == torch.uint8 and masks.dim() == 3 and masks.stride(2) == 1
+    lib = _abi.load()
+    _abi.check(lib.wcr_pack_box_masks(masks.data_ptr(), masks.stride(0), masks.stride(1),
+                                      _abi.ptr(self._mask_idx), self._shard.table.data_ptr(),
+                                      self._boxes.table.data_ptr(), self.n_boxes, self.off.data_ptr(),
+                                      self.bits.data_ptr(), _abi.stream_ptr(masks.device)),
+               "wcr_pack_box_masks")
+
+
 def _segmasks_from_arrays(host_bits: np.ndarray, host_off: np.ndarray, device, bits=None, off=None):
     """SegMasks over prebuilt arrays (wcr.job); ``bits`` / ``off``: existing device buffers the
     caller uploads into, None => uploaded here."""
@@ -215,6 +251,8 @@ def _segmasks_from_arrays(host_bits: np.ndarray, host_off: np.ndarray, device, b
 
 
 SegMasks.from_arrays = staticmethod(_segmasks_from_arrays)
+SegMasks.from_dense = staticmethod(_segmasks_from_dense)
+SegMasks.repack = _segmasks_repack
 
 
 class ScoreWorkspace:
