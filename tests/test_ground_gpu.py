@@ -119,3 +119,32 @@ def test_degenerate_inputs(cuda_lib):
     assert torch.isnan(res["eq"]).all()
     with pytest.raises(Exception):
         unproject_ground(ImageShard([im["depth"]], None, [im["K"]]))  # CPU tensor: no fallback
+
+
+import glob as _glob
+import os as _os
+
+_GROUND_GOLDEN = sorted(_glob.glob(_os.path.join(_os.path.dirname(__file__), "golden", "ground_*.npz")))
+
+
+@pytest.mark.parametrize("path", _GROUND_GOLDEN)
+def test_normal_vector_from_maps_replay_matches_reference_golden(cuda_lib, path):
+    """The drop-in with the reference's own signature, in replay mode, against the output of the
+    reference's own method (roi_heads.py:466-528, generated by tests/golden/make_golden.py with
+    random.seed(100 + case)): bit for bit, through the CUDA path. ``Ks`` is handed over per BOX,
+    the way the call site does (Ks_scaled_per_box): the method zips it against images, so image i
+    uses Ks[i] and the surplus entries are never read."""
+    from wcr.ground import normal_vector_from_maps
+    z = np.load(path)
+    n = int(z["n"])
+    case = int(_os.path.basename(path).split("_")[1].split(".")[0])
+    depth = [torch.from_numpy(z[f"depth{i}"]).cuda() for i in range(n)]
+    ground = [torch.from_numpy(z[f"ground{i}"]).cuda() for i in range(n)]
+    Ks = [torch.from_numpy(z[f"K{i}"]) for i in range(n)]
+    Ks_per_box = Ks + [Ks[0] * 3.0, Ks[-1] * 0.5]            # more boxes than images
+    got = normal_vector_from_maps(ground, depth, Ks_per_box, 5, replay_rng=random.Random(100 + case))
+    assert np.array_equal(got.cpu().numpy().view(np.uint32), z["normals"].view(np.uint32))
+    # device-side Ks (one transfer for the whole list) give the same table
+    got2 = normal_vector_from_maps(ground, depth, [k.cuda() for k in Ks_per_box[:n]], 5,
+                                   replay_rng=random.Random(100 + case))
+    assert torch.equal(got2, got)
