@@ -26,7 +26,7 @@
 extern "C" {
 #endif
 
-#define WCR_ABI_VERSION 1
+#define WCR_ABI_VERSION 2   /* 2: WcrLossIO.depth_images */
 
 #define WCR_OK        0
 #define WCR_EINVAL   -1   /* bad argument */
@@ -392,7 +392,8 @@ typedef struct WcrLossIO {
     /* 'depth' and 'segmentation' (NULL otherwise): per-object masks as the reference's masks_all_images
      * (roi_heads.py:273), dense, non-zero == object. Every mask must have the shape of the
      * depth map of the image its boxes belong to (the reference's align_corners bilinear
-     * resize, :672, is the identity then); a mismatch sets stats[WCR_STAT_SHAPE_ERR]. */
+     * resize, :672, is the identity then) unless depth_images (below) is given; a mismatch sets
+     * stats[WCR_STAT_SHAPE_ERR]. */
     const uint8_t *masks;     /* [n_masks][mask_h][mask_w]                     */
     int32_t  mask_h, mask_w;
     const int32_t *mask_idx;  /* [n] at_which_mask_idx (:723-726)              */
@@ -403,6 +404,11 @@ typedef struct WcrLossIO {
     void    *select_ws;
     /* 'segmentation', backward only: [n][16] d raw_seg / d (clamped projected corners) */
     float   *seg_dcorner;
+    /* 'depth' with masks of ANOTHER shape than the depth maps (the reference's masks have the padded
+     * batch-tensor size, the depth maps are un-padded): [n_images] depth maps already resized to
+     * (mask_h, mask_w) by wcr_resize_bilinear_ac -- what F.interpolate(bilinear, align_corners=True)
+     * at roi_heads.py:672 yields. NULL: `images` is used and a shape mismatch is an error. */
+    const WcrImage *depth_images;
 } WcrLossIO;
 
 /* Workspace of the per-box order-statistic kernels (median of a depth patch, quantiles of
@@ -451,6 +457,11 @@ void wcr_pil_nearest_table(int in_size, int out_size, int32_t *table);
 int wcr_resize_nearest(const void *src, int elem_size, int in_h, int in_w, int64_t src_pitch,
                        const int32_t *xtab, const int32_t *ytab, void *dst, int out_h, int out_w,
                        int64_t dst_pitch, void *stream);
+
+/* F.interpolate(x, size=(out_h, out_w), mode='bilinear', align_corners=True) of one f32 plane, as
+ * depth_range_loss applies it to a depth map (roi_heads.py:672). Pitches in elements. */
+int wcr_resize_bilinear_ac(const float *src, int in_h, int in_w, int64_t src_pitch, float *dst,
+                           int out_h, int out_w, int64_t dst_pitch, void *stream);
 
 /* ---- 3D IoU ------------------------------------------------------------ */
 
@@ -514,6 +525,64 @@ int wcr_dim_loss_fwd(const float *prior_mean, const float *prior_std, const floa
                      float *out3n, int32_t *nan_flag, void *stream);
 int wcr_dim_loss_bwd(const float *prior_mean, const float *prior_std, const float *dims,
                      const float *grad3n, int n, float *d_dims, void *stream);
+
+/* ---- second set of block-level drop-ins ------------------------ */
+
+/* Backward of wcr_cube_corners: grad_corners [n][8][3] -> d_cubes [n][15] (centre, w h l, R).
+ * The reference differentiates through Cubes.get_all_corners (depth_range_loss, roi_heads.py:665). */
+int wcr_cube_corners_bwd(const float *cubes, const float *grad_corners, int64_t n, float *d_cubes,
+                         void *stream);
+
+/* Backward of wcr_bube_corners (get_bube_corners, spaces.py:224-245, and the min / max of
+ * cubes_to_box, conversions.py:36-42; call site inside autograd: roi_heads.py:947-960).
+ * grad_corners [n][8][2] and / or grad_boxes [n][4] (either may be NULL) -> d_cubes [n][15].
+ * torch conventions: clamp passes the gradient on the closed interval, min / max send it to the
+ * first extremum. */
+int wcr_bube_corners_bwd(const float *cubes, int64_t n, float fx, float fy, float cx, float cy,
+                         float clamp0, float clamp1, const float *grad_corners,
+                         const float *grad_boxes, float *d_cubes, void *stream);
+
+/* ProposalNetwork/utils/utils.py:207-223 custom_mapping: x <= 0 -> 0, else
+ * 1 / (1 + (x / (1 - x)) ** -beta), evaluated in double like the reference's Python floats. */
+int wcr_custom_mapping(const float *x, int64_t n, double beta, float *out, void *stream);
+
+/* utils.py:61-68 randn_orthobasis_torch: z [n][3][3] standard-normal draws (replay of the
+ * reference's torch.randn) or NULL => in-kernel Philox4x32-10 (counter (basis, "ORTH", block),
+ * key = seed) -> out [n][3][3]: rows normalised, row 0 = cross(row 1, row 2), row 1 = cross(row 2,
+ * row 0), each re-normalised. */
+int wcr_randn_orthobasis(const float *z, int64_t n, uint64_t seed, float *out, void *stream);
+
+/* utils.py:148-152 gt_in_norm_range, element-wise over n (range, gt) pairs:
+ * out = (gt - lo) / |hi - lo|. */
+int wcr_gt_in_norm_range(const float *lo, const float *hi, const float *gt, int64_t n, float *out,
+                         void *stream);
+
+/* utils.py:257-298 is_gt_included for n GT cubes at once. gt_cubes [n][15]; ranges [n][6] =
+ * x_lo x_hi y_lo y_hi z_lo z_hi; priors [n][6] = (mean, std) of w, h, l. out_bits [n]: 0 ==
+ * included, else OR of 1 x, 2 y, 4 z, 8 w-, 16 w+, 32 h-, 64 h+, 128 l-, 256 l+ (the reference's
+ * `because_of` list); out_by [n][3]: the x / y / z distances it prints. */
+int wcr_is_gt_included(const float *gt_cubes, const float *ranges, const float *priors, int64_t n,
+                       int32_t *out_bits, float *out_by, void *stream);
+
+/* ROIHeads3DScore.z_loss (roi_heads.py:530-573) on given cubes [n][15]: K4 [n][4], clamp [n][2]
+ * (im_sizes[i]), proj_boxes [n][4] -> out [n]. Value only (the reference's graph has no path to
+ * the cube either: the arg-min offset is a constant). */
+int wcr_z_loss(const float *gt_boxes, const float *cubes, const float *K4, const float *clamp,
+               const float *proj_boxes, int n, float *out, void *stream);
+
+/* ROIHeads3DScore.normal_to_rotation (roi_heads.py:686-696): normal [n][3] -> out [n][3][3] with
+ * rows [t0, t1, normal]; t0 and t1 are divided by the Frobenius norm of the WHOLE (n, 3) matrix
+ * and the y-axis fallback is taken only when every t0 is zero (reference behaviour, kept). */
+int wcr_normal_to_rotation(const float *normal, int n, float *out, void *stream);
+
+/* q90 - q10 of the depth under each object's mask (GT box patch when the mask is empty): the GT
+ * side of ROIHeads3DScore.depth_range_loss (roi_heads.py:658-684) as a stand-alone call; same
+ * argument meaning as the WcrLossIO fields of the same names. stats: WCR_LOSS_STATS floats
+ * (stats[WCR_STAT_SHAPE_ERR] != 0: a mask whose shape differs from its depth map). */
+int wcr_masked_depth_range(const WcrImage *images, const int32_t *img_off, int n_images, int n,
+                           const uint8_t *masks, int mask_h, int mask_w, const int32_t *mask_idx,
+                           const float *gt_boxes, float *out_range, float *stats, void *select_ws,
+                           void *stream);
 
 #ifdef __cplusplus
 }

@@ -251,8 +251,129 @@ def golden_tier2_seg():
         print("tier2seg", idx, {k: round(float(v), 6) for k, v in L.items()})
 
 
+def golden_blocks2():
+    """Round-2 blocks, straight from the reference: custom_mapping, randn_orthobasis_torch (the
+    torch.randn draws are stored: replay), gt_in_norm_range, is_gt_included, the AUTOGRAD gradients
+    of Cubes.get_all_corners / get_bube_corners / cubes_to_box (spaces.py:192-245,
+    conversions.py:25-48), and the stand-alone z_loss / depth_range_loss / normal_to_rotation
+    methods of ROIHeads3DScore (roi_heads.py:530-573, 658-696)."""
+    import contextlib
+    import io
+    import types
+    ns = refshim.load()
+    U = ns.utils
+    head = refshim.roi_head_instance()
+    g = torch.Generator().manual_seed(31)
+    out = {}
+    xs = [0.0, -0.2, 1e-6, 0.05, 0.3, 0.5, 0.7, 0.95, 0.999999]
+    out["cm_x"] = np.asarray(xs, dtype=np.float32)
+    out["cm_betas"] = np.asarray([1.7, 3.0, 1.01])
+    out["cm_out"] = np.asarray([U.custom_mapping([float(np.float32(v)) for v in xs], b) for b in out["cm_betas"]])
+    torch.manual_seed(5)
+    z = torch.randn(3, 7, 3, 3)
+    torch.manual_seed(5)
+    out["ro_z"], out["ro_out"] = z.numpy(), U.randn_orthobasis_torch(7, 3).numpy()
+    lo, hi, gt = torch.randn(20, generator=g), torch.randn(20, generator=g), torch.randn(20, generator=g)
+    out["gn_lo"], out["gn_hi"], out["gn_gt"] = lo.numpy(), hi.numpy(), gt.numpy()
+    out["gn_out"] = np.stack([U.gt_in_norm_range((lo[i], hi[i]), gt[i]).numpy() for i in range(20)])
+    # is_gt_included: 24 random cases around the decision boundaries
+    n = 24
+    cen, dim = torch.randn(n, 3, generator=g) * 2, 0.2 + 2 * torch.rand(n, 3, generator=g)
+    rng = torch.sort(torch.randn(n, 3, 2, generator=g) * 2, dim=-1)[0]
+    pri = torch.stack((0.2 + 2 * torch.rand(n, 3, generator=g), 0.1 + 0.5 * torch.rand(n, 3, generator=g)), -1)
+    for i in range(0, n, 2):                   # every other case near / inside the acceptance region
+        rng[i, :, 0] = cen[i] - 0.5 - torch.rand(3, generator=g)
+        rng[i, :, 1] = cen[i] + 0.5 + torch.rand(3, generator=g)
+        dim[i] = pri[i, :, 0] + pri[i, :, 1] * (torch.rand(3, generator=g) * 3.2 - 1.6) * (1.0 if i % 4 else 0.9)
+    inc = []
+    for i in range(n):
+        cube = types.SimpleNamespace(center=cen[i], dimensions=dim[i])
+        with contextlib.redirect_stdout(io.StringIO()):
+            inc.append(bool(U.is_gt_included(cube, rng[i, 0], rng[i, 1], rng[i, 2], pri[i, 0], pri[i, 1], pri[i, 2])))
+    out.update({"ig_center": cen.numpy(), "ig_dims": dim.numpy(), "ig_ranges": rng.numpy(),
+                "ig_priors": pri.numpy(), "ig_included": np.asarray(inc)})
+    # autograd through the geometry blocks
+    I, Pn = 2, 9
+    yaw = torch.rand(Pn, generator=g) * np.pi
+    R = U.orthobasis_from_normal_t(torch.nn.functional.normalize(torch.tensor([0.03, 0.99, -0.05]), dim=0), yaw)
+    cubes = torch.zeros(I, Pn, 15)
+    cubes[:, :, 0:2] = torch.randn(I, Pn, 2, generator=g) * 0.8
+    cubes[:, :, 2] = 1.0 + 4 * torch.rand(I, Pn, generator=g)
+    cubes[:, :, 3:6] = 0.2 + 1.5 * torch.rand(I, Pn, 3, generator=g)
+    cubes[:, :, 6:] = R.reshape(Pn, 9)
+    cubes[0, 0, 2] = 0.3                       # close to the camera: clamp bounds hit, no gradient there
+    K = torch.tensor([[525.0, 0, 320], [0, 525, 240], [0, 0, 1]])
+    clamp = [480, 640]
+    up3 = torch.randn(I, Pn, 8, 3, generator=g)
+    up2 = torch.randn(I, Pn, 8, 2, generator=g)
+    up4 = torch.randn(I, Pn, 4, generator=g)
+    ct = cubes.clone().requires_grad_(True)
+    (ns.spaces.Cubes(ct).get_all_corners() * up3).sum().backward()
+    out["ag_cubes"], out["ag_K"], out["ag_clamp"] = cubes.numpy(), K.numpy(), np.asarray(clamp)
+    out["ag_up3"], out["ag_up2"], out["ag_up4"] = up3.numpy(), up2.numpy(), up4.numpy()
+    out["ag_g3"] = ct.grad.numpy().copy()
+    ct = cubes.clone().requires_grad_(True)
+    (ns.spaces.Cubes(ct).get_bube_corners(K, clamp) * up2).sum().backward()
+    out["ag_g2"] = ct.grad.numpy().copy()
+    ct = cubes.clone().requires_grad_(True)
+    boxes = torch.stack([b.tensor for b in ns.conversions.cubes_to_box(ns.spaces.Cubes(ct), K, clamp)])
+    (boxes * up4).sum().backward()
+    out["ag_g4"] = ct.grad.numpy().copy()
+    # stand-alone z_loss / depth_range_loss / normal_to_rotation on the tier-2 test inputs
+    seed, nb, H, W = 2, [4, 1, 6], 96, 128
+    inp = li.add_masks(li.make_loss_inputs(seed, nb, H=H, W=W), seed, H=H, W=W)
+    dec = ol.decode(ol.LossConfig(), inp["deltas"], inp["z_raw"], inp["dims_raw"], inp["pose"], inp["src_boxes"],
+                    inp["K4"], inp["virtual_to_real"], inp["prior_mean"], inp["prior_std"])
+    nbox = inp["deltas"].shape[0]
+    box6, Rr = dec[5].detach(), dec[4].detach()
+    cubes_t = torch.cat((box6, Rr.reshape(nbox, 9)), 1).unsqueeze(1)
+    Ks = torch.zeros(nbox, 3, 3)
+    K4 = inp["K4"]
+    Ks[:, 0, 0], Ks[:, 1, 1], Ks[:, 0, 2], Ks[:, 1, 2], Ks[:, 2, 2] = K4[:, 0], K4[:, 1], K4[:, 2], K4[:, 3], 1
+    im_sizes = [[int(c[0]), int(c[1])] for c in inp["clamp"]]
+    C = ns.spaces.Cubes(cubes_t)
+    proj = torch.stack([ns.conversions.cubes_to_box(C[i], Ks[i], im_sizes[i])[0].tensor[0] for i in range(nbox)])
+    out["sa_seed"], out["sa_nb"], out["sa_H"], out["sa_W"] = seed, np.asarray(nb), H, W
+    out["sa_cubes"], out["sa_proj"] = cubes_t.numpy(), proj.numpy()
+    out["sa_z_loss"] = head.z_loss(standins.Boxes(inp["gt_boxes"]), C, Ks, im_sizes, standins.Boxes(proj)).detach().numpy()
+    for tag, pad in (("", (0, 0)), ("_pad", (11, 32))):
+        masks = [torch.nn.functional.pad(m, (0, pad[1], 0, pad[0])) for m in inp["gt_masks"]]
+        ct = cubes_t.clone().requires_grad_(True)
+        d = head.depth_range_loss(masks, inp["at_which_mask_idx"], inp["depth_maps"], ns.spaces.Cubes(ct),
+                                  standins.Boxes(inp["gt_boxes"]), nb)
+        d.sum().backward()
+        out["sa_depth" + tag], out["sa_depth_grad" + tag] = d.detach().numpy(), ct.grad.numpy().copy()
+    out["sa_pad"] = np.asarray([11, 32])
+    nrm = torch.nn.functional.normalize(torch.randn(5, 3, generator=g), dim=1)
+    out["sa_normals"], out["sa_rot"] = nrm.numpy(), head.normal_to_rotation(nrm).numpy()
+    np.savez_compressed(os.path.join(HERE, "blocks2_0.npz"), **out)
+    print("blocks2", out["cm_out"][0][:4], out["ig_included"].sum(), out["sa_z_loss"][:4], out["sa_depth_pad"][:3])
+
+
+def golden_tier2_padded():
+    """'depth' with masks at a PADDED size (ImageList batch tensor: bottom / right padding), so
+    depth_range_loss resizes every depth map with F.interpolate(bilinear, align_corners=True)
+    (roi_heads.py:672): values and autograd gradients from the reference."""
+    T2 = ("iou", "depth", "dims")
+    seed, nb, conf, H, W, pad = 3, [5, 2, 4], 1.0, 96, 128, (16, 32)
+    inp = li.add_masks(li.make_loss_inputs(seed, nb, H=H, W=W), seed, H=H, W=W)
+    inp["gt_masks"] = [torch.nn.functional.pad(m, (0, pad[1], 0, pad[0])) for m in inp["gt_masks"]]
+    cfg = ol.LossConfig(loss_functions=T2, use_confidence=conf)
+    L, pb, grads = li.run_with_grads(ref_loss.reference_weak_loss, cfg, inp)
+    out = {"seed": seed, "nb": np.asarray(nb), "H": H, "W": W, "use_confidence": conf, "pad": np.asarray(pad)}
+    out.update({"loss:" + k: v.numpy() for k, v in L.items()})
+    out.update({"grad:" + k: v.numpy() for k, v in grads.items()})
+    out["box:raw_depth"] = pb["raw_depth"].numpy()
+    np.savez_compressed(os.path.join(HERE, "tier2pad_0.npz"), **out)
+    print("tier2pad", {k: round(float(v), 5) for k, v in L.items()})
+
+
 if __name__ == "__main__":
     assert refshim.available(), "needs /root/reference"
+    if "--round2" in sys.argv:
+        golden_blocks2()
+        golden_tier2_padded()
+        sys.exit(0)
     golden_ground()
     golden_cubes()
     golden_hull()
@@ -261,3 +382,5 @@ if __name__ == "__main__":
     golden_loss()
     golden_tier2()
     golden_tier2_seg()
+    golden_blocks2()
+    golden_tier2_padded()

@@ -26,7 +26,7 @@ def test_library_exports_every_declared_symbol():
     for n in names:
         assert hasattr(lib, n), f"{n} declared in include/wcr.h but not exported"
     assert set(names) == set(_abi.SIGNATURES), (set(names) ^ set(_abi.SIGNATURES))
-    assert lib.wcr_abi_version() == 1
+    assert lib.wcr_abi_version() == 2
 
 
 def test_struct_sizes_match_header():

@@ -201,10 +201,64 @@ def test_depth_term_empty_mask_and_shape_mismatch(cuda_lib):
     Lb, pb, gb = li.run_with_grads(ol.weak_loss, ol.LossConfig(**cfg_kw), inp)
     La, pa, ga = _run_gpu(cfg_kw, inp)
     _check(La, ga, Lb, gb)
-    bad = dict(inp)
-    bad["gt_masks"] = [m[:, :-2] for m in inp["gt_masks"]]
-    with pytest.raises(_abi.WcrError):
-        _run_gpu(cfg_kw, bad)
+    # masks of another shape than the depth maps: the depth maps are resized to the mask shape
+    # (align_corners bilinear, roi_heads.py:672) instead of raising
+    other = dict(inp)
+    other["gt_masks"] = [m[:, :-2, :-6] for m in inp["gt_masks"]]
+    other["gt_boxes"] = inp["gt_boxes"].clamp(max=float(min(H - 2, W - 6)))
+    Lb, pb, gb = li.run_with_grads(ol.weak_loss, ol.LossConfig(**cfg_kw), other)
+    La, pa, ga = _run_gpu(cfg_kw, other)
+    assert torch.allclose(pa["terms"][9 - 1].cpu(), pb["raw_depth"], rtol=1e-5, atol=2e-6)
+    _check(La, ga, Lb, gb)
+
+
+def test_weak_loss_padded_masks_match_reference_golden(cuda_lib):
+    """object masks at the PADDED batch size (roi_heads.py:383-401) while the
+    depth maps are iterated un-padded -- the reference resizes each depth map to the mask shape.
+    Values and autograd gradients of the reference's own code (tests/golden/tier2pad_0.npz)."""
+    z = np.load(os.path.join(GOLDEN, "tier2pad_0.npz"), allow_pickle=False)
+    nb = [int(v) for v in z["nb"]]
+    H, W, seed, pad = int(z["H"]), int(z["W"]), int(z["seed"]), [int(v) for v in z["pad"]]
+    inp = li.add_masks(li.make_loss_inputs(seed, nb, H=H, W=W), seed, H=H, W=W)
+    inp["gt_masks"] = [torch.nn.functional.pad(m, (0, pad[1], 0, pad[0])) for m in inp["gt_masks"]]
+    cfg_kw = dict(loss_functions=("iou", "depth", "dims"), use_confidence=float(z["use_confidence"]))
+    La, pa, ga = _run_gpu(cfg_kw, inp)
+    Lb = {k[5:]: torch.tensor(z[k]) for k in z.files if k.startswith("loss:")}
+    gb = {k[5:]: torch.tensor(z[k]) for k in z.files if k.startswith("grad:")}
+    assert np.allclose(pa["terms"][9 - 1].cpu().numpy(), z["box:raw_depth"], rtol=1e-5, atol=2e-6)
+    _check(La, ga, Lb, gb)
+
+
+def test_weak_loss_without_host_sync(cuda_lib):
+    """host_sync=False: same losses and gradients, keys decided on the host, data-dependent flags
+    checked one call late (a NaN prior std, which drops the dims keys in the reference, raises
+    at the next poll)."""
+    from wcr import _abi
+    from wcr.roi_heads import WeakLossConfig, weak_loss, poll_deferred_flags
+    inp = li.make_loss_inputs(8, [5, 1, 3])
+
+    def run(i, sync):
+        leaves = {k: i[k].cuda().requires_grad_(True) for k in li.GRAD_KEYS}
+        rest = {k: (v.cuda() if isinstance(v, torch.Tensor) else v) for k, v in i.items()
+                if k not in li.GRAD_KEYS and k != "depth_maps"}
+        rest["depth_maps"] = [d.cuda() for d in i["depth_maps"]]
+        L = weak_loss(WeakLossConfig(), **leaves, **rest, host_sync=sync)
+        sum(L.values()).backward()
+        return L, {k: v.grad for k, v in leaves.items()}
+    La, ga = run(inp, True)
+    Lb, gb = run(inp, False)
+    poll_deferred_flags(block=True)
+    assert set(La) == set(Lb)
+    assert all(torch.equal(La[k], Lb[k]) for k in La) and all(torch.equal(ga[k], gb[k]) for k in ga)
+    one = li.make_loss_inputs(1, [1, 1, 1])                 # pose term absent: decided from the box counts
+    Lc, _ = run(one, False)
+    poll_deferred_flags(block=True)
+    assert "Cube/loss_pose" not in Lc
+    bad = li.make_loss_inputs(4, [3, 2])
+    bad["prior_std"][1, 2] = float("nan")
+    run(bad, False)
+    with pytest.raises(_abi.WcrError, match="host_sync=True"):
+        poll_deferred_flags(block=True)
 
 
 # ---- 'segmentation': soft convex-hull raster vs the object mask, focal loss, differentiable --------

@@ -251,3 +251,41 @@ extern "C" int wcr_resize_nearest(const void *src, int elem_size, int in_h, int 
     WCR_CHECK_LAUNCH("resize_gather_kernel");
     return WCR_OK;
 }
+
+// F.interpolate(mode='bilinear', align_corners=True) of one f32 plane (depth_range_loss resizes the
+// depth map to the mask shape with it, roi_heads.py:672). ATen's upsample_bilinear2d:
+//   scale = (in - 1) / (out - 1) (0 when out == 1), src = scale * dst, i0 = (int)src,
+//   i1 = i0 + (i0 < in - 1), l1 = src - i0, l0 = 1 - l1,
+//   out = l0y * (l0x * v00 + l1x * v01) + l1y * (l0x * v10 + l1x * v11)
+namespace wcr {
+__global__ void __launch_bounds__(256)
+resize_bilinear_ac_kernel(const float *__restrict__ src, int in_h, int in_w, int64_t src_pitch,
+                          float *__restrict__ dst, int out_h, int out_w, int64_t dst_pitch)
+{
+    const int x = blockIdx.x * blockDim.x + threadIdx.x, y = blockIdx.y;
+    if (x >= out_w) return;
+    const float sy = out_h > 1 ? (float)(in_h - 1) / (float)(out_h - 1) : 0.f;
+    const float sx = out_w > 1 ? (float)(in_w - 1) / (float)(out_w - 1) : 0.f;
+    const float fy = sy * (float)y, fx = sx * (float)x;
+    const int y0 = (int)fy, x0 = (int)fx;
+    const int y1 = y0 + (y0 < in_h - 1 ? 1 : 0), x1 = x0 + (x0 < in_w - 1 ? 1 : 0);
+    const float l1y = fy - (float)y0, l0y = 1.f - l1y, l1x = fx - (float)x0, l0x = 1.f - l1x;
+    const float v00 = __ldg(src + (size_t)y0 * src_pitch + x0), v01 = __ldg(src + (size_t)y0 * src_pitch + x1);
+    const float v10 = __ldg(src + (size_t)y1 * src_pitch + x0), v11 = __ldg(src + (size_t)y1 * src_pitch + x1);
+    dst[(size_t)y * dst_pitch + x] = l0y * (l0x * v00 + l1x * v01) + l1y * (l0x * v10 + l1x * v11);
+}
+}  // namespace wcr
+
+extern "C" int wcr_resize_bilinear_ac(const float *src, int in_h, int in_w, int64_t src_pitch, float *dst,
+                                      int out_h, int out_w, int64_t dst_pitch, void *stream)
+{
+    WCR_CHECK_DEVICE();
+    WCR_REQUIRE(src && dst, "wcr_resize_bilinear_ac: null pointer");
+    WCR_REQUIRE(in_h >= 1 && in_w >= 1 && out_h >= 1 && out_w >= 1 && out_h <= 65535,
+                "wcr_resize_bilinear_ac: bad sizes");
+    const dim3 grid((out_w + 255) / 256, out_h);
+    wcr::resize_bilinear_ac_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(src, in_h, in_w, src_pitch, dst,
+                                                                            out_h, out_w, dst_pitch);
+    WCR_CHECK_LAUNCH("resize_bilinear_ac_kernel");
+    return WCR_OK;
+}

@@ -1468,7 +1468,10 @@ extern "C" int wcr_weak_loss_fwd(const WcrLossIO *h_io, const WcrLossParams *h_p
         WCR_CHECK_LAUNCH("ground_rot_kernel");
     }
     if (h_io->n > 0 && (h_params->loss_flags & WCR_LOSS_DEPTH)) {
-        rc = wcr::launch_mask_quantile(h_io->images, h_io->img_off, h_io->n_images, h_io->n, h_io->masks,
+        // masks of another shape than their depth maps (padded batch tensors): the caller hands in
+        // the depth maps resized to the mask shape (wcr_resize_bilinear_ac, roi_heads.py:672)
+        rc = wcr::launch_mask_quantile(h_io->depth_images ? h_io->depth_images : h_io->images,
+                                       h_io->img_off, h_io->n_images, h_io->n, h_io->masks,
                                        h_io->mask_h, h_io->mask_w, h_io->mask_idx, h_io->gt_boxes,
                                        h_io->depth_gt, h_io->stats, h_io->select_ws, st);
         if (rc != WCR_OK) return rc;
@@ -1499,6 +1502,22 @@ extern "C" int wcr_weak_loss_fwd(const WcrLossIO *h_io, const WcrLossParams *h_p
     wcr::loss_reduce_kernel<<<1, 256, 0, st>>>(*h_io, *h_params);
     WCR_CHECK_LAUNCH("loss_reduce_kernel");
     return WCR_OK;
+}
+
+extern "C" int wcr_masked_depth_range(const WcrImage *images, const int32_t *img_off, int n_images, int n,
+                                      const uint8_t *masks, int mask_h, int mask_w, const int32_t *mask_idx,
+                                      const float *gt_boxes, float *out_range, float *stats, void *select_ws,
+                                      void *stream)
+{
+    WCR_CHECK_DEVICE();
+    WCR_REQUIRE(images && img_off && masks && mask_idx && gt_boxes && out_range && stats && select_ws,
+                "wcr_masked_depth_range: null pointer");
+    WCR_REQUIRE(n >= 0 && n_images >= 1 && mask_h > 0 && mask_w > 0, "wcr_masked_depth_range: bad sizes");
+    cudaError_t e = cudaMemsetAsync(stats, 0, WCR_LOSS_STATS * sizeof(float), (cudaStream_t)stream);
+    if (e != cudaSuccess) { wcr::set_error("cudaMemsetAsync: %s", cudaGetErrorString(e)); return WCR_ELAUNCH; }
+    if (n == 0) return WCR_OK;
+    return wcr::launch_mask_quantile(images, img_off, n_images, n, masks, mask_h, mask_w, mask_idx, gt_boxes,
+                                     out_range, stats, select_ws, (cudaStream_t)stream);
 }
 
 extern "C" int wcr_weak_loss_bwd(const WcrLossIO *h_io, const WcrLossParams *h_params, void *stream)

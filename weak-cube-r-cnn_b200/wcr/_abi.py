@@ -82,6 +82,18 @@ SIGNATURES = {
     "wcr_resize_nearest": (c_int, [c_void_p, c_int, c_int, c_int, c_i64, c_void_p, c_void_p, c_void_p,
                                    c_int, c_int, c_i64, c_void_p]),
     "wcr_sizeof": (c_i64, [c_int]),
+    "wcr_resize_bilinear_ac": (c_int, [c_void_p, c_int, c_int, c_i64, c_void_p, c_int, c_int, c_i64, c_void_p]),
+    "wcr_cube_corners_bwd": (c_int, [c_void_p, c_void_p, c_i64, c_void_p, c_void_p]),
+    "wcr_bube_corners_bwd": (c_int, [c_void_p, c_i64, c_float, c_float, c_float, c_float, c_float, c_float,
+                                     c_void_p, c_void_p, c_void_p, c_void_p]),
+    "wcr_custom_mapping": (c_int, [c_void_p, c_i64, ctypes.c_double, c_void_p, c_void_p]),
+    "wcr_randn_orthobasis": (c_int, [c_void_p, c_i64, c_u64, c_void_p, c_void_p]),
+    "wcr_gt_in_norm_range": (c_int, [c_void_p, c_void_p, c_void_p, c_i64, c_void_p, c_void_p]),
+    "wcr_is_gt_included": (c_int, [c_void_p, c_void_p, c_void_p, c_i64, c_void_p, c_void_p, c_void_p]),
+    "wcr_z_loss": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_void_p, c_void_p]),
+    "wcr_normal_to_rotation": (c_int, [c_void_p, c_int, c_void_p, c_void_p]),
+    "wcr_masked_depth_range": (c_int, [c_void_p, c_void_p, c_int, c_int, c_void_p, c_int, c_int, c_void_p,
+                                       c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
 }
 _lib = None
 
@@ -169,7 +181,8 @@ _LOSS_IO_PTRS = ["deltas", "z_raw", "dims_raw", "pose", "uncert", "src_boxes", "
                  "z_dec", "z_gt", "z_inside", "z_sign"]
 
 
-_LOSS_IO_PTRS2 = ["mask_idx", "depth_gt", "gt_rot", "select_ws", "seg_dcorner"]   # after the mask shape (tier-2 terms)
+_LOSS_IO_PTRS2 = ["mask_idx", "depth_gt", "gt_rot", "select_ws", "seg_dcorner",   # after the mask shape (tier-2 terms)
+                  "depth_images"]
 
 
 class LossIO(ctypes.Structure):

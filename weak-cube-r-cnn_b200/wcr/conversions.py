@@ -57,6 +57,17 @@ except Exception:  # noqa: BLE001
             return f"Boxes({self.tensor})"
 
 
+def cube_to_box(cube, K):
+    """conversions.py:5-23: ONE cube -> a ``Boxes`` of one box. The reference calls
+    ``cube.get_bube_corners(K)`` without a clamp there, which raises (spaces.py:240-243 leaves x, y
+    undefined); the same ``NameError`` surfaces here, so a caller ported from the reference behaves
+    identically. (With a clamp the box is ``cubes_to_box(cube, K, clamp)[0]``.)"""
+    bube_corners = cube.get_bube_corners(K)        # raises NameError, like the reference
+    min_x, max_x = bube_corners[..., 0].min(), bube_corners[..., 0].max()
+    min_y, max_y = bube_corners[..., 1].min(), bube_corners[..., 1].max()
+    return Boxes(torch.stack((min_x, min_y, max_x, max_y)).view(1, 4))
+
+
 def cubes_to_box(cubes, K, im_shape):
     """conversions.py:25-48: per instance, the (P, 4) boxes ``(min_x, min_y, max_x,
     max_y)`` over the 8 clamped projected corners. One kernel launch

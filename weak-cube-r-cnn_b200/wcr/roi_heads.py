@@ -64,6 +64,29 @@ def _c(t, dev, dtype=torch.float32):
     return t.detach().to(device=dev, dtype=dtype).contiguous()
 
 
+def resized_depth_shard(shard: ImageShard, mask_hw):
+    """depth_range_loss resizes every depth map to the mask shape with
+    ``F.interpolate(mode='bilinear', align_corners=True)`` (roi_heads.py:672) -- the masks have the
+    padded batch-tensor size, the depth maps are iterated un-padded. -> an ``ImageShard`` of the
+    resized maps (one ``wcr_resize_bilinear_ac`` launch per image whose shape differs), or None when
+    every depth map already has the mask shape (the resize is the identity then)."""
+    mh, mw = mask_hw
+    sizes = shard.sizes()
+    if all((h, w) == (mh, mw) for h, w in sizes):
+        return None
+    lib = _abi.load()
+    dev = shard.device
+    planes = torch.empty((len(sizes), mh, mw), dtype=torch.float32, device=dev)
+    rec = shard.host_table
+    for i, (h, w) in enumerate(sizes):
+        _abi.check(lib.wcr_resize_bilinear_ac(int(rec["depth"][i]), h, w, int(rec["depth_pitch"][i]),
+                                              planes[i].data_ptr(), mh, mw, mw, _abi.stream_ptr(dev)),
+                   "wcr_resize_bilinear_ac")
+    out = ImageShard([planes[i] for i in range(len(sizes))], None, [torch.eye(3)] * len(sizes), device=dev)
+    out._planes = planes
+    return out
+
+
 class _Ctx:
     """Everything one fwd/bwd pair shares: contiguous device inputs + saved buffers."""
 
@@ -114,6 +137,11 @@ class _Ctx:
                       "depth_gt": torch.empty(max(n, 1), device=dev)})
             assert t["mask_idx"].numel() == n
             self.mask_hw = (int(m.shape[-2]), int(m.shape[-1]))
+        if "depth" in cfg.loss_functions:
+            t["depth_images"] = None
+            self.depth_shard = resized_depth_shard(shard, self.mask_hw)
+            if self.depth_shard is not None:
+                t["depth_images"] = self.depth_shard.table
         if "pose_ground2" in cfg.loss_functions:
             t["gt_rot"] = torch.empty((B, 9), device=dev)
         if "depth" in cfg.loss_functions or "z_pseudo_gt_patch" in cfg.loss_functions:
@@ -169,7 +197,7 @@ class _WeakLossFn(torch.autograd.Function):
 def weak_loss(cfg: WeakLossConfig, deltas, z_raw, dims_raw, pose, uncert, *, src_boxes, K4,
               virtual_to_real, prior_mean, prior_std, gt_boxes, clamp, num_boxes_per_image,
               depth_maps, normals, ground_conf, gt_masks=None, at_which_mask_idx=None,
-              return_per_box: bool = False):
+              return_per_box: bool = False, host_sync: bool = True):
     """Fused weak-loss block. Per-box tensors follow the reference's torch.cat order
     (boxes of one image contiguous). ``depth_maps``: an ``ImageShard`` or anything
     ``ImageShard`` accepts (ImageList-like / list of (h,w) CUDA tensors); ``normals``
@@ -178,19 +206,29 @@ def weak_loss(cfg: WeakLossConfig, deltas, z_raw, dims_raw, pose, uncert, *, src
 
     -> dict keyed like the reference ('Cube/loss_iou', ...); keys the reference would
     not emit (pose term when every image has one box, dims when a prior std is NaN,
-    'Cube/uncert' when USE_CONFIDENCE == 0) are absent. One host sync (8 ints) to
-    build that dict -- the reference syncs many times here (.item(), :1061-1073)."""
+    'Cube/uncert' when USE_CONFIDENCE == 0) are absent.
+
+    ``host_sync=True`` (default): ONE 52-byte device -> host read decides the keys exactly as
+    the reference does (it syncs many times here: .item(), :1061-1073).
+    ``host_sync=False``: NO host synchronisation. The keys are decided on the host from what the
+    host knows (loss list, USE_CONFIDENCE, boxes per image); the two data-dependent cases -- a NaN
+    prior std (the reference drops the dims keys) and the error flags -- are copied to pinned
+    memory asynchronously and checked ONE CALL LATE (``poll_deferred_flags()``, also run at the
+    start of the next call): a violation raises then, naming the step it belongs to."""
     shard = depth_maps if isinstance(depth_maps, ImageShard) else ImageShard(
         depth_maps, None, [torch.eye(3)] * len(num_boxes_per_image), device=deltas.device)
     c = _Ctx(cfg, deltas, z_raw, dims_raw, pose, uncert, src_boxes, K4, virtual_to_real, prior_mean,
              prior_std, gt_boxes, clamp, num_boxes_per_image, shard, normals, ground_conf, gt_masks,
              at_which_mask_idx)
+    if not host_sync:
+        poll_deferred_flags()
     out = _WeakLossFn.apply(c, deltas, z_raw, dims_raw, pose, uncert)
-    present = c.t["present"].cpu().tolist()     # the one host sync: term flags + two error flags
-    if present[N_TERMS]:
-        raise ValueError("A matrix has trace outside valid range [-1-eps,3+eps].")   # pytorch3d so3_rotation_angle
-    if present[N_TERMS + 1]:
-        raise _abi.WcrError("wcr.weak_loss: 'depth' needs masks of the same shape as their depth maps")
+    if host_sync:
+        present = c.t["present"].cpu().tolist()     # the one host sync: term flags + two error flags
+        _raise_flags(present)
+    else:
+        present = _host_side_present(cfg, num_boxes_per_image, c.n)
+        _defer_flags(c.t["present"], present)
     losses = {k: out[i] for i, k in enumerate(TERM_KEYS) if present[i]}
     if return_per_box:
         t = c.t
@@ -198,6 +236,62 @@ def weak_loss(cfg: WeakLossConfig, deltas, z_raw, dims_raw, pose, uncert, *, src
                    "stats": t["stats"]}
         return losses, per_box
     return losses
+
+
+def _raise_flags(present):
+    if present[N_TERMS]:
+        raise ValueError("A matrix has trace outside valid range [-1-eps,3+eps].")   # pytorch3d so3_rotation_angle
+    if present[N_TERMS + 1]:
+        raise _abi.WcrError("wcr.weak_loss: 'depth' needs masks of the same shape as their depth maps")
+
+
+_TERM_OF = {"iou": (1,), "pose_alignment": (2,), "pose_ground": (3,), "pose_ground2": (3,),
+            "z_pseudo_gt_center": (4,), "z_pseudo_gt_patch": (4,), "dims": (5, 6, 7), "z": (8,),
+            "depth": (9,), "segmentation": (10,)}
+_deferred = []      # (step, pinned flags, event, keys assumed present)
+_step_counter = [0]
+
+
+def _host_side_present(cfg, num_boxes_per_image, n):
+    """Which keys the reference emits, from host-side knowledge only (data-dependent NaNs aside)."""
+    p = [0] * (N_TERMS + 2)
+    if n == 0:
+        return p
+    for f in cfg.loss_functions:
+        for t in _TERM_OF[f]:
+            p[t] = 1
+    if all(int(b) == 1 for b in num_boxes_per_image):
+        p[2] = 0                                    # pose_loss returns None (roi_heads.py:462-463)
+    p[0] = 1 if cfg.use_confidence > 0 else 0
+    return p
+
+
+def _defer_flags(present_dev, assumed):
+    h = torch.empty(present_dev.shape, dtype=present_dev.dtype).pin_memory()
+    h.copy_(present_dev, non_blocking=True)
+    ev = torch.cuda.Event()
+    ev.record(torch.cuda.current_stream(present_dev.device))
+    _step_counter[0] += 1
+    _deferred.append((_step_counter[0], h, ev, list(assumed)))
+
+
+def poll_deferred_flags(block: bool = False):
+    """Check the flags of earlier ``weak_loss(host_sync=False)`` calls whose copy has completed
+    (all of them with ``block=True``). Raises what the synchronous path would have raised, one
+    call late."""
+    while _deferred:
+        step, h, ev, assumed = _deferred[0]
+        if not block and not ev.query():
+            return
+        ev.synchronize()
+        _deferred.pop(0)
+        got = h.tolist()
+        _raise_flags(got)
+        wrong = [TERM_KEYS[i] for i in range(N_TERMS) if bool(got[i]) != bool(assumed[i])]
+        if wrong:
+            raise _abi.WcrError(f"wcr.weak_loss(host_sync=False), call #{step}: the keys {wrong} were decided on the "
+                                "host but the data says otherwise (a NaN prior std drops the dims terms, "
+                                "roi_heads.py:620-623); rerun that step with host_sync=True")
 
 
 # ---- drop-in helpers with the reference's names (roi_heads.py:445, 575, 612, 635, 1307) ----
@@ -358,16 +452,18 @@ class _DimLossFn(torch.autograd.Function):
         return dd.view(ctx.shape), None, None
 
 
-def dim_loss(priors, dimensions):
+def dim_loss(priors, dimensions, *, host_sync: bool = True):
     """roi_heads.py:612-633: ``priors = (prior_mean, prior_std)`` (n,3) each ->
     three (n,) hinge losses ``max(|d - mean|/std - 1, 0)``, or ``(None, None, None)``
-    when a prior std is NaN (one 4-byte host read, the reference's ``mask.all()``)."""
+    when a prior std is NaN (one 4-byte host read, the reference's ``mask.all()``).
+    ``host_sync=False`` skips that read: the priors are taken to be finite (category statistics
+    are; a NaN std then shows up as a NaN loss instead of a dropped key)."""
     prior_mean, prior_std = priors
     _abi.require_cuda(dimensions, prior_mean, prior_std)
     dev = dimensions.device
     mean, std = _c(prior_mean, dev).view(-1, 3), _c(prior_std, dev).view(-1, 3)
     out, flag = _DimLossFn.apply(dimensions, mean, std)
-    if int(flag.item()) != 0:
+    if host_sync and int(flag.item()) != 0:
         return None, None, None
     return out[0], out[1], out[2]
 
@@ -419,3 +515,84 @@ def segment_loss(gt_mask, bube_corners, at_which_mask_idx, loss: str = "focal"):
     idx = torch.as_tensor(list(at_which_mask_idx) if not isinstance(at_which_mask_idx, torch.Tensor)
                           else at_which_mask_idx, dtype=torch.int32).to(dev)
     return _SegmentLossFn.apply(bube_corners, masks, idx)
+
+
+# ---- stand-alone tier-2 helpers with the reference's method names (roi_heads.py:530, 658, 686) ----
+def _boxes_tensor(b, dev):
+    t = b.tensor if hasattr(b, "tensor") else torch.as_tensor(b)
+    return t.detach().to(device=dev, dtype=torch.float32).reshape(-1, 4).contiguous()
+
+
+def z_loss(gt_boxes, cubes, Ks, im_sizes, proj_boxes):
+    """roi_heads.py:530-573: per predicted cube, 50 offsets of 0.1 m along z, arg-min of the
+    mismatch between the GT box area and the projected area, score = |z - z_best| / 2 (2.5 when
+    the projected centre is outside the GT box grown by 50 px -- with the reference's chained
+    comparison kept). ``cubes``: a ``Cubes`` of shape (n, 1, 15); ``Ks``: n (3,3) intrinsics;
+    ``im_sizes``: n pairs handed to ``cubes_to_box``. One launch instead of n x 50 ``cubes_to_box``
+    calls; value only, like the reference's graph (the selected offset is a constant)."""
+    lib = _abi.load()
+    ct = cubes.tensor if hasattr(cubes, "tensor") else cubes
+    _abi.require_cuda(ct)
+    dev = ct.device
+    flat = ct.detach().to(torch.float32).reshape(-1, 15).contiguous()
+    n = flat.shape[0]
+    Kt = torch.stack([torch.as_tensor(k, dtype=torch.float32).reshape(3, 3) for k in Ks]) \
+        if not isinstance(Ks, torch.Tensor) else Ks.to(torch.float32).reshape(-1, 3, 3)
+    K4 = torch.stack((Kt[:, 0, 0], Kt[:, 1, 1], Kt[:, 0, 2], Kt[:, 1, 2]), dim=1).to(dev).contiguous()
+    clamp = torch.as_tensor([[float(s[0]), float(s[1])] for s in im_sizes], dtype=torch.float32).to(dev) \
+        if not isinstance(im_sizes, torch.Tensor) else im_sizes.to(device=dev, dtype=torch.float32).reshape(-1, 2)
+    gt, pj = _boxes_tensor(gt_boxes, dev), _boxes_tensor(proj_boxes, dev)
+    assert K4.shape[0] == n and clamp.shape[0] == n and gt.shape[0] == n and pj.shape[0] == n
+    out = torch.empty((n,), dtype=torch.float32, device=dev)
+    _abi.check(lib.wcr_z_loss(gt.data_ptr(), flat.data_ptr(), K4.data_ptr(), clamp.contiguous().data_ptr(),
+                              pj.data_ptr(), n, out.data_ptr(), _abi.stream_ptr(dev)), "wcr_z_loss")
+    return out
+
+
+def masked_depth_range(gt_mask, at_which_mask_idx, depth_maps, gt_boxes, num_instances):
+    """The GT side of ``depth_range_loss``: (n,) q90 - q10 of the depth under each object's mask
+    (GT box patch where the mask is empty), depth maps resized to the mask shape first where the
+    shapes differ (roi_heads.py:668-676)."""
+    lib = _abi.load()
+    gt_src = gt_boxes.tensor if hasattr(gt_boxes, "tensor") else torch.as_tensor(gt_boxes)
+    _abi.require_cuda(gt_src)
+    dev = gt_src.device
+    gt = _boxes_tensor(gt_src, dev)
+    masks = _stack_masks(gt_mask, dev)
+    shard = _as_shard(depth_maps, dev)
+    rs = resized_depth_shard(shard, (int(masks.shape[1]), int(masks.shape[2])))
+    use = rs if rs is not None else shard
+    off, n = _img_off(num_instances, dev)
+    assert n == gt.shape[0]
+    idx = torch.as_tensor(list(at_which_mask_idx) if not isinstance(at_which_mask_idx, torch.Tensor)
+                          else at_which_mask_idx, dtype=torch.int32).to(dev)
+    out = torch.empty((max(n, 1),), dtype=torch.float32, device=dev)
+    stats = torch.zeros((N_STATS,), dtype=torch.float32, device=dev)
+    ws = torch.empty(int(lib.wcr_select_ws_bytes(max(n, 1))), dtype=torch.uint8, device=dev)
+    _abi.check(lib.wcr_masked_depth_range(use.table.data_ptr(), off.data_ptr(), len(use), n, masks.data_ptr(),
+                                          int(masks.shape[1]), int(masks.shape[2]), idx.data_ptr(),
+                                          gt.data_ptr(), out.data_ptr(), stats.data_ptr(), ws.data_ptr(),
+                                          _abi.stream_ptr(dev)), "wcr_masked_depth_range")
+    return out[:n]
+
+
+def depth_range_loss(gt_mask, at_which_mask_idx, depth_maps, cubes, gt_boxes, num_instances):
+    """roi_heads.py:658-684: |(q90 - q10 of the depth under the object's mask) - (depth extent of
+    the cube's 8 corners)| per box. Differentiable in ``cubes.tensor`` through
+    ``Cubes.get_all_corners`` (first arg-max / arg-min corner, like torch.max / torch.min)."""
+    corner_depths = cubes.get_all_corners()[:, 0, :, 2]
+    pred_depth = torch.max(corner_depths, dim=1)[0] - torch.min(corner_depths, dim=1)[0]
+    gt_depths = masked_depth_range(gt_mask, at_which_mask_idx, depth_maps, gt_boxes, num_instances)
+    return torch.nn.functional.smooth_l1_loss(gt_depths, pred_depth, reduction="none", beta=0.0)
+
+
+def normal_to_rotation(normal):
+    """roi_heads.py:686-696: (n, 3) normals -> (n, 3, 3) with rows [t0, t1, normal] (quirks of the
+    reference kept: whole-matrix Frobenius norms, bool-compared fallback test; see wcr.h)."""
+    _abi.require_cuda(normal)
+    lib = _abi.load()
+    nrm = normal.detach().to(torch.float32).reshape(-1, 3).contiguous()
+    out = torch.empty((nrm.shape[0], 3, 3), dtype=torch.float32, device=nrm.device)
+    _abi.check(lib.wcr_normal_to_rotation(nrm.data_ptr(), nrm.shape[0], out.data_ptr(),
+                                          _abi.stream_ptr(nrm.device)), "wcr_normal_to_rotation")
+    return out

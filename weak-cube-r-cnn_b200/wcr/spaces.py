@@ -6,9 +6,10 @@ the geometry (``get_all_corners``, ``get_bube_corners``) runs in libwcr_b200
 torch ops. Container logic (views, indexing, cat, split) is plain tensor plumbing.
 
 Differences: tensors must live on a CUDA device for the geometry methods (no CPU
-fallback); the geometry outputs carry no autograd graph -- the differentiable use of
-these blocks in the weak loss goes through ``wcr.roi_heads.weak_loss`` (fused
-forward/backward kernels).
+fallback). The geometry methods are DIFFERENTIABLE in ``Cubes.tensor`` like the reference's
+torch ops (it calls them inside autograd: spaces.py:224-245, roi_heads.py:947-960): each is a
+``torch.autograd.Function`` over a forward and a backward kernel (wcr_cube_corners[_bwd],
+wcr_bube_corners[_bwd]); the fused ``wcr.roi_heads.weak_loss`` remains the fast path.
 """
 from __future__ import annotations
 
@@ -21,6 +22,65 @@ from . import _abi
 def _K4(K):
     K = K.detach().cpu() if isinstance(K, torch.Tensor) else torch.as_tensor(np.asarray(K))
     return float(K[0, 0]), float(K[1, 1]), float(K[0, 2]), float(K[1, 2])
+
+
+# faces of get_cuboid_verts_faces (math_util.py:220-238): vertex indices per triangle
+_FACES = [[0, 1, 2], [2, 3, 0], [1, 5, 6], [6, 2, 1], [4, 0, 3], [3, 7, 4],
+          [5, 4, 7], [7, 6, 5], [4, 5, 1], [1, 0, 4], [3, 2, 6], [6, 7, 3]]
+
+
+class _CornersFn(torch.autograd.Function):
+    """Cubes.get_all_corners: (M, 15) -> (M, 8, 3)."""
+
+    @staticmethod
+    def forward(ctx, flat):
+        lib = _abi.load()
+        f = flat.detach().contiguous()
+        out = torch.empty((f.shape[0], 8, 3), dtype=torch.float32, device=f.device)
+        _abi.check(lib.wcr_cube_corners(f.data_ptr(), f.shape[0], out.data_ptr(),
+                                        _abi.stream_ptr(f.device)), "wcr_cube_corners")
+        ctx.save_for_backward(f)
+        return out
+
+    @staticmethod
+    def backward(ctx, g):
+        lib = _abi.load()
+        (f,) = ctx.saved_tensors
+        g = g.to(torch.float32).contiguous()
+        d = torch.empty_like(f)
+        _abi.check(lib.wcr_cube_corners_bwd(f.data_ptr(), g.data_ptr(), f.shape[0], d.data_ptr(),
+                                            _abi.stream_ptr(f.device)), "wcr_cube_corners_bwd")
+        return d
+
+
+class _BubeFn(torch.autograd.Function):
+    """get_bube_corners (which == 0: (M, 8, 2)) or the cubes_to_box min / max (which == 1: (M, 4))."""
+
+    @staticmethod
+    def forward(ctx, flat, K4, clamp, which):
+        lib = _abi.load()
+        f = flat.detach().contiguous()
+        M = f.shape[0]
+        out = torch.empty((M, 8, 2) if which == 0 else (M, 4), dtype=torch.float32, device=f.device)
+        _abi.check(lib.wcr_bube_corners(f.data_ptr(), M, *K4, float(clamp[0]), float(clamp[1]),
+                                        out.data_ptr() if which == 0 else None,
+                                        out.data_ptr() if which == 1 else None,
+                                        _abi.stream_ptr(f.device)), "wcr_bube_corners")
+        ctx.save_for_backward(f)
+        ctx.K4, ctx.clamp, ctx.which = K4, (float(clamp[0]), float(clamp[1])), which
+        return out
+
+    @staticmethod
+    def backward(ctx, g):
+        lib = _abi.load()
+        (f,) = ctx.saved_tensors
+        g = g.to(torch.float32).contiguous()
+        d = torch.empty_like(f)
+        _abi.check(lib.wcr_bube_corners_bwd(f.data_ptr(), f.shape[0], *ctx.K4, *ctx.clamp,
+                                            g.data_ptr() if ctx.which == 0 else None,
+                                            g.data_ptr() if ctx.which == 1 else None,
+                                            d.data_ptr(), _abi.stream_ptr(f.device)), "wcr_bube_corners_bwd")
+        return d, None, None, None
 
 
 class Cubes:
@@ -74,42 +134,36 @@ class Cubes:
     # ---- geometry: one kernel launch each -------------------------------------
     def _flat(self):
         _abi.require_cuda(self.tensor)
-        return self.tensor.contiguous().view(-1, 15)
+        return self.tensor.contiguous().view(-1, 15)      # keeps the autograd graph of self.tensor
 
     def get_all_corners(self) -> torch.Tensor:
         """(I, P, 8, 3) camera-space vertices, ``get_cuboid_verts_faces`` order
-        (math_util.py:198-217) -- spaces.py:192-204."""
-        lib = _abi.load()
-        flat = self._flat()
-        out = torch.empty((flat.shape[0], 8, 3), dtype=torch.float32, device=flat.device)
-        _abi.check(lib.wcr_cube_corners(flat.data_ptr(), flat.shape[0], out.data_ptr(),
-                                        _abi.stream_ptr(flat.device)), "wcr_cube_corners")
+        (math_util.py:198-217) -- spaces.py:192-204. Differentiable."""
+        out = _CornersFn.apply(self._flat())
         return out.view(self.tensor.shape[0], self.tensor.shape[1], 8, 3)
+
+    def get_cuboids_verts_faces(self):
+        """spaces.py:206-222: ``(verts (I, P, 8, 3), faces (I, P, 12, 3))``; the faces are the
+        constant triangle table of math_util.py:220-238 (as floats, like the reference)."""
+        verts = self.get_all_corners()
+        faces = torch.tensor(_FACES, dtype=torch.float32, device=verts.device)
+        return verts, faces.expand(verts.shape[0], verts.shape[1], 12, 3).contiguous()
 
     def get_bube_corners(self, K, clamp: tuple = None) -> torch.Tensor:
         """(I, P, 8, 2) projected corners clamped to
         ``[int(-clamp/2+1), int(clamp-1+clamp)]`` -- spaces.py:224-245. Like the
-        reference, ``clamp=None`` is an error (there: NameError at :243)."""
+        reference, ``clamp=None`` is an error (there: NameError at :243). Differentiable
+        (clamp passes the gradient on the closed interval, like torch.clamp)."""
         if clamp is None:
             raise NameError("get_bube_corners: clamp is required (the reference leaves x, y "
                             "undefined without it, spaces.py:240-243)")
-        lib = _abi.load()
-        flat = self._flat()
-        out = torch.empty((flat.shape[0], 8, 2), dtype=torch.float32, device=flat.device)
-        _abi.check(lib.wcr_bube_corners(flat.data_ptr(), flat.shape[0], *_K4(K), float(clamp[0]),
-                                        float(clamp[1]), out.data_ptr(), None,
-                                        _abi.stream_ptr(flat.device)), "wcr_bube_corners")
+        out = _BubeFn.apply(self._flat(), _K4(K), clamp, 0)
         return out.view(self.tensor.shape[0], self.tensor.shape[1], 8, 2)
 
     def projected_boxes(self, K, clamp) -> torch.Tensor:
         """(I, P, 4) min/max of the clamped projected corners: the tensor behind
-        ``cubes_to_box`` (conversions.py:36-42)."""
-        lib = _abi.load()
-        flat = self._flat()
-        out = torch.empty((flat.shape[0], 4), dtype=torch.float32, device=flat.device)
-        _abi.check(lib.wcr_bube_corners(flat.data_ptr(), flat.shape[0], *_K4(K), float(clamp[0]),
-                                        float(clamp[1]), None, out.data_ptr(),
-                                        _abi.stream_ptr(flat.device)), "wcr_bube_corners")
+        ``cubes_to_box`` (conversions.py:36-42). Differentiable (first arg-min / arg-max)."""
+        out = _BubeFn.apply(self._flat(), _K4(K), clamp, 1)
         return out.view(self.tensor.shape[0], self.tensor.shape[1], 4)
 
     def get_volumes(self):

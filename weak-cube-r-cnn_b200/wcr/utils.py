@@ -4,6 +4,8 @@ path, each one kernel launch in libwcr_b200 (csrc/blocks.cu):
   sample_normal_in_range (:41-59)   orthobasis_from_normal_t (:119-131)
   vectorized_linspace   (:169-176)  iou_2d (:181-187)
   mask_iou (:225-234)  mod_mask_iou (:236-245)  convex_hull (:490-493)
+  randn_orthobasis_torch (:61-68)   gt_in_norm_range (:148-152)
+  custom_mapping (:207-223)         is_gt_included (:257-298)
 
 Same positional signatures and return shapes. CUDA tensors only (no CPU fallback).
 """
@@ -164,3 +166,107 @@ def iou_3d(gt_cube, proposal_cubes):
     proposal_corners = proposal_cubes.get_all_corners()[0]
     vol, iou = box3d_overlap(gt_corners, proposal_corners)
     return iou[0]
+
+
+def randn_orthobasis_torch(num_samples=1, num_instances=1, *, z: torch.Tensor | None = None,
+                           seed: int | None = None, device="cuda"):
+    """utils.py:61-68 -> (num_instances, num_samples, 3, 3) random orthonormal bases. ``z``: the
+    (num_instances, num_samples, 3, 3) ``torch.randn`` draws of the reference (replay mode, exact
+    parity); None => in-kernel Philox (``seed`` None: taken from torch's global generator)."""
+    lib = _abi.load()
+    n = int(num_instances) * int(num_samples)
+    if z is not None:
+        _abi.require_cuda(z)
+        device = z.device
+        z = _f32c(z).reshape(n, 9)
+    device = torch.device(device)
+    if device.type != "cuda":
+        raise _abi.WcrError("wcr: CUDA device required (there is no CPU fallback on this path)")
+    if seed is None:
+        seed = int(torch.randint(0, 2 ** 62, (1,)).item())
+    out = torch.empty((n, 9), dtype=torch.float32, device=device)
+    _abi.check(lib.wcr_randn_orthobasis(_abi.ptr(z), n, int(seed), out.data_ptr(), _abi.stream_ptr(device)),
+               "wcr_randn_orthobasis")
+    return out.view(int(num_instances), int(num_samples), 3, 3)
+
+
+def gt_in_norm_range(range, gt):  # noqa: A002 - the reference's parameter name
+    """utils.py:148-152: ``(gt - range[0]) / abs(range[1] - range[0])``. ``range``: a pair of
+    scalars or tensors broadcastable against ``gt``; one launch for all elements."""
+    gt_t = torch.as_tensor(gt)
+    _abi.require_cuda(gt_t)
+    lib = _abi.load()
+    dev = gt_t.device
+    g = _f32c(gt_t)
+    lo = _f32c(torch.as_tensor(range[0]), dev).expand_as(g).contiguous()
+    hi = _f32c(torch.as_tensor(range[1]), dev).expand_as(g).contiguous()
+    out = torch.empty_like(g)
+    _abi.check(lib.wcr_gt_in_norm_range(lo.data_ptr(), hi.data_ptr(), g.data_ptr(), g.numel(),
+                                        out.data_ptr(), _abi.stream_ptr(dev)), "wcr_gt_in_norm_range")
+    return out
+
+
+def custom_mapping(x, beta=1.7):
+    """utils.py:207-223: S-curve ``1 / (1 + (x / (1 - x)) ** -beta)`` (0 for x <= 0). A list in, a
+    list of Python floats out, like the reference; a CUDA tensor in, a tensor out (no sync)."""
+    lib = _abi.load()
+    as_list = not isinstance(x, torch.Tensor)
+    t = torch.as_tensor(x, dtype=torch.float32)
+    if as_list:
+        t = t.cuda()
+    _abi.require_cuda(t)
+    t = t.contiguous()
+    out = torch.empty_like(t)
+    _abi.check(lib.wcr_custom_mapping(t.data_ptr(), t.numel(), float(beta), out.data_ptr(),
+                                      _abi.stream_ptr(t.device)), "wcr_custom_mapping")
+    return [float(v) for v in out.cpu().tolist()] if as_list else out
+
+
+_REASONS = ("x", "y", "z", "w-", "w+", "h-", "h+", "l-", "l+")
+
+
+def is_gt_included_batch(gt_cubes, x_range, y_range, z_range, w_prior, h_prior, l_prior):
+    """``is_gt_included`` for n GT cubes in one launch. ``gt_cubes`` (n, 15) or a ``Cubes``;
+    ranges (n, 2) each; priors (n, 2) = (mean, std) each. -> (bits (n,) int32, by (n, 3)):
+    bits == 0 <=> included (bit order: x y z w- w+ h- h+ l- l+)."""
+    lib = _abi.load()
+    c = gt_cubes.tensor if hasattr(gt_cubes, "tensor") else gt_cubes
+    _abi.require_cuda(c)
+    dev = c.device
+    c = _f32c(c).reshape(-1, 15)
+    n = c.shape[0]
+    ranges = torch.cat([_f32c(torch.as_tensor(r), dev).reshape(-1, 2).expand(n, 2)
+                        for r in (x_range, y_range, z_range)], dim=1).contiguous()
+    priors = torch.cat([_f32c(torch.as_tensor(p), dev).reshape(-1, 2).expand(n, 2)
+                        for p in (w_prior, h_prior, l_prior)], dim=1).contiguous()
+    bits = torch.empty((n,), dtype=torch.int32, device=dev)
+    by = torch.empty((n, 3), dtype=torch.float32, device=dev)
+    _abi.check(lib.wcr_is_gt_included(c.data_ptr(), ranges.data_ptr(), priors.data_ptr(), n, bits.data_ptr(),
+                                      by.data_ptr(), _abi.stream_ptr(dev)), "wcr_is_gt_included")
+    return bits, by
+
+
+def is_gt_included(gt_cube, x_range, y_range, z_range, w_prior, h_prior, l_prior):
+    """utils.py:257-298 for ONE GT cube (an object with ``center`` / ``dimensions`` like the
+    reference's ``Cube``, a ``Cubes`` of one cube, or a (15,) tensor): True when the GT lies inside
+    the search ranges and within 1.5 std of the dimension priors, else prints the reference's
+    message and returns False. One small host read (the reference is host code throughout)."""
+    if hasattr(gt_cube, "center") and hasattr(gt_cube, "dimensions"):
+        c = torch.zeros(15)
+        c[0:3] = torch.as_tensor(gt_cube.center, dtype=torch.float32).reshape(-1)[:3]
+        c[3:6] = torch.as_tensor(gt_cube.dimensions, dtype=torch.float32).reshape(-1)[:3]
+        c = c.cuda()
+    else:
+        c = (gt_cube.tensor if hasattr(gt_cube, "tensor") else torch.as_tensor(gt_cube)).reshape(-1)[:15]
+        c = c if c.is_cuda else c.cuda()
+    dev = c.device
+    mk = lambda v: torch.as_tensor([float(v[0]), float(v[1])], dtype=torch.float32, device=dev)  # noqa: E731
+    bits, by = is_gt_included_batch(c.view(1, 15), mk(x_range), mk(y_range), mk(z_range), mk(w_prior),
+                                    mk(h_prior), mk(l_prior))
+    b, dist = int(bits.item()), by[0].cpu().tolist()
+    if b == 0:
+        return True
+    because_of = [f"{_REASONS[i]} by {dist[i]:.1f}" for i in range(3) if b >> i & 1]
+    because_of += [_REASONS[i] for i in range(3, 9) if b >> i & 1]
+    print("GT cannot be found due to", because_of)
+    return False
