@@ -368,11 +368,35 @@ def golden_tier2_padded():
     print("tier2pad", {k: round(float(v), 5) for k, v in L.items()})
 
 
+FORWARD_CUBE_CASES = [
+    dict(seed=0, nb=[3, 1, 4]),                                                         # config.py:186 default list
+    dict(seed=5, nb=[6, 2, 5, 3], use_confidence=0.0,
+         loss_functions=("iou", "z_pseudo_gt_center", "pose_alignment", "pose_ground2", "dims", "segmentation", "depth"),
+         pad=(8, 16)),
+]
+
+
+def golden_forward_cube():
+    """The reference's OWN ROIHeads3DScore._forward_cube training branch (roi_heads.py:698-1144),
+    driven through oracle/ref_forward_cube.py with a stub pooler / cube head: the Cube/loss_*
+    dict and the autograd gradients w.r.t. the five per-class head outputs."""
+    from oracle import ref_forward_cube as rf
+    for idx, kw in enumerate(FORWARD_CUBE_CASES):
+        case = rf.make_case(**kw)
+        L, grads = rf.run_reference_with_grads(case)
+        out = {"kw": np.frombuffer(repr(kw).encode(), dtype=np.uint8)}
+        out.update({"loss:" + k: v.numpy() for k, v in L.items()})
+        out.update({"grad:" + k: v.numpy() for k, v in grads.items()})
+        np.savez_compressed(os.path.join(HERE, f"forward_cube_{idx}.npz"), **out)
+        print("forward_cube", idx, {k: round(float(v), 5) for k, v in L.items()})
+
+
 if __name__ == "__main__":
     assert refshim.available(), "needs /root/reference"
     if "--round2" in sys.argv:
         golden_blocks2()
         golden_tier2_padded()
+        golden_forward_cube()
         sys.exit(0)
     golden_ground()
     golden_cubes()

@@ -111,7 +111,7 @@ def cube_losses_from_head(cfg: WeakLossConfig, cube_2d_deltas, cube_z, cube_dims
                           box_classes, *, proposal_boxes, gt_boxes, Ks, im_scales_ratio, im_current_dims,
                           num_boxes_per_image, priors_dims_per_cat, depth_maps, normals, ground_conf,
                           virtual_focal=512.0, virtual_depth=True, pose_is_6d=False, gt_masks=None,
-                          at_which_mask_idx=None):
+                          at_which_mask_idx=None, return_per_box=False, host_sync=True):
     """NEW (no reference counterpart as one call): roi_heads.py:748-1144 from the cube head's
     per-class outputs to the loss dict.
 
@@ -138,4 +138,4 @@ def cube_losses_from_head(cfg: WeakLossConfig, cube_2d_deltas, cube_z, cube_dims
                      virtual_to_real=v2r, prior_mean=pri[:, 0, :].contiguous(), prior_std=pri[:, 1, :].contiguous(),
                      gt_boxes=gt_boxes, clamp=clamp, num_boxes_per_image=num_boxes_per_image,
                      depth_maps=depth_maps, normals=normals, ground_conf=ground_conf, gt_masks=gt_masks,
-                     at_which_mask_idx=at_which_mask_idx)
+                     at_which_mask_idx=at_which_mask_idx, return_per_box=return_per_box, host_sync=host_sync)

@@ -596,3 +596,175 @@ def normal_to_rotation(normal):
     _abi.check(lib.wcr_normal_to_rotation(nrm.data_ptr(), nrm.shape[0], out.data_ptr(),
                                           _abi.stream_ptr(nrm.device)), "wcr_normal_to_rotation")
     return out
+
+
+# ---- the ROI head drop-in -------------------------------------------------
+_FUSED_LOSSES = frozenset(_FLAG)
+
+
+def make_roi_heads_b200(base):
+    """Subclass ``base`` -- the reference's ``ROIHeads3DScore`` (roi_heads.py:52) -- so that the
+    training loss block of ``_forward_cube`` (roi_heads.py:786-1144: class gather, decode, the
+    per-box Python loops, every weak-loss term, uncertainty weighting, safe reductions) is ONE
+    call into the fused kernels (``wcr.glue.cube_losses_from_head``). Everything else -- the box
+    branch, proposal sampling, the pooler, the cube head, inference -- stays the reference's code.
+
+    Configurations outside the fused path (z clusters, no dimension priors, egocentric head,
+    a loss name the kernels do not know) raise ``WcrError`` in training: there is no silent
+    fallback to the torch path. Attributes a caller may set on the instance:
+      ``wcr_replay_rng``  a ``random.Random`` / the ``random`` module: the RANSAC triples are drawn
+                          from it exactly as plane.py:95 does (parity mode); None: in-kernel Philox
+      ``wcr_seed``        seed of the in-kernel generator (default 0)
+      ``wcr_host_sync``   False: no host synchronisation in the loss block (see ``weak_loss``)"""
+    import sys
+
+    class ROIHeads3DScoreB200(base):
+        wcr_replay_rng = None
+        wcr_seed = 0
+        wcr_host_sync = True
+
+        def _wcr_check_config(self):
+            bad = []
+            if getattr(self, "cluster_bins", 1) > 1 or self.z_type == "clusters":
+                bad.append("z clusters")
+            if not self.dims_priors_enabled:
+                bad.append("DIMS_PRIORS_ENABLED = False")
+            if not self.allocentric_pose:
+                bad.append("ALLOCENTRIC_POSE = False")
+            unknown = [f for f in self.loss_functions if f not in _FUSED_LOSSES]
+            if unknown:
+                bad.append(f"loss functions {unknown}")
+            if bad:
+                raise _abi.WcrError("ROIHeads3DScoreB200: not on the fused path: " + ", ".join(bad))
+
+        def _forward_cube(self, features, instances, Ks, im_current_dims, im_scales_ratio,
+                          masks_all_images, first_occurrence_indices, ground_maps, depth_maps):
+            if not self.training:
+                return super()._forward_cube(features, instances, Ks, im_current_dims, im_scales_ratio,
+                                             masks_all_images, first_occurrence_indices, ground_maps, depth_maps)
+            self._wcr_check_config()
+            from . import glue, ground as wground
+            from .spaces import Cubes as WCubes
+            ref_mod = sys.modules[base.__module__]
+            feats = [features[f] for f in self.in_features]
+            self.normalize_factor = max(sum(i.gt_classes.numel() for i in instances), 1.0)
+            proposals, _ = ref_mod.select_foreground_proposals(instances, self.num_classes)
+            proposal_boxes = [x.proposal_boxes for x in proposals]
+            pred_boxes = [x.pred_boxes for x in proposals]
+            cube_features = self.cube_pooler(feats, self.scale_proposals(proposal_boxes)).flatten(1)
+            n = cube_features.shape[0]
+            if n == 0:
+                return instances, {}
+            nb = [len(p) for p in proposals]
+            heads = self.cube_head(cube_features)
+            dev = heads[0].device
+            if dev.type != "cuda":
+                raise _abi.WcrError("ROIHeads3DScoreB200: the cube head must run on a CUDA device")
+            box_classes = torch.cat([p.gt_classes for p in proposals]).to(dev)
+            at_which = None
+            if masks_all_images is not None:
+                ids = torch.cat([p.gt_boxes3D[:, 0] for p in proposals]).tolist()
+                at_which = [first_occurrence_indices[e] for e in ids]
+            src = torch.cat([b.tensor for b in proposal_boxes]).to(dev)
+            gt = torch.cat([p.gt_boxes.tensor for p in proposals]).to(dev)
+            # normal_vector_from_maps zips Ks_scaled_per_box (one K per BOX) against IMAGES
+            # (roi_heads.py:472, :990): image i is unprojected with the K of box i. Kept.
+            B = len(nb)
+            im_of_box = [i for i, c in enumerate(nb) for _ in range(c)]
+            Kq = []
+            for i in range(B):
+                j = im_of_box[i] if i < n else i
+                Kb = torch.as_tensor(Ks[j], dtype=torch.float32).detach().cpu().clone() / float(im_scales_ratio[j])
+                Kb[-1, -1] = 1
+                Kq.append(Kb)
+            need_normals = any(f in self.loss_functions for f in ("pose_ground", "pose_ground2"))
+            if need_normals:
+                normals = wground.normal_vector_from_maps(
+                    [g.to(dev) for g in ground_maps], [d.to(dev) for d in depth_maps], Kq,
+                    replay_rng=self.wcr_replay_rng, seed=self.wcr_seed)
+            else:
+                normals = torch.tensor([[0.0, 1.0, 0.0]], device=dev).repeat(B, 1)
+            conf = torch.tensor([0.1 if tuple(s) == (1, 1) else 1.0 for s in ground_maps.image_sizes], device=dev)
+            cfg = WeakLossConfig(
+                loss_functions=tuple(self.loss_functions), z_type=self.z_type, dims_priors_func=self.dims_priors_func,
+                use_confidence=float(self.use_confidence), loss_w_3d=self.loss_w_3d, loss_w_iou=self.loss_w_iou,
+                loss_w_pose=self.loss_w_pose, loss_w_normal_vec=self.loss_w_normal_vec, loss_w_z=self.loss_w_z,
+                loss_w_dims=self.loss_w_dims, loss_w_depth=self.loss_w_depth, loss_w_seg=self.loss_w_seg)
+            deltas_c, z_c, dims_c, pose_c, uncert_c = heads
+            losses, per_box = glue.cube_losses_from_head(
+                cfg, deltas_c, z_c, dims_c, pose_c, uncert_c if self.use_confidence else None, box_classes,
+                proposal_boxes=src, gt_boxes=gt, Ks=Ks, im_scales_ratio=im_scales_ratio,
+                im_current_dims=im_current_dims, num_boxes_per_image=nb,
+                priors_dims_per_cat=self.priors_dims_per_cat, depth_maps=[d.to(dev) for d in depth_maps],
+                normals=normals, ground_conf=conf, virtual_focal=self.virtual_focal,
+                virtual_depth=self.virtual_depth, gt_masks=masks_all_images, at_which_mask_idx=at_which,
+                return_per_box=True, host_sync=self.wcr_host_sync)
+            pred = self._wcr_pred_instances(ref_mod, heads, box_classes, src, per_box, Ks, im_current_dims,
+                                            im_scales_ratio, nb, pred_boxes, WCubes)
+            return pred, losses
+
+        @torch.no_grad()
+        def _wcr_pred_instances(self, ref_mod, heads, box_classes, src, per_box, Ks, im_dims, ratios, nb,
+                                pred_boxes, WCubes):
+            """The per-image ``Instances`` the reference returns from the training branch
+            (roi_heads.py:1153-1195): a handful of vectorised tensor ops, no gradient."""
+            dev = src.device
+            n = src.shape[0]
+            ar = torch.arange(n, device=dev)
+            deltas = heads[0][ar, box_classes]
+            z = heads[1][ar, box_classes].reshape(n)
+            dims_n = heads[2][ar, box_classes]
+            from . import glue
+            K4, v2r, _ = glue.box_constants(Ks, ratios, im_dims, nb, virtual_focal=self.virtual_focal,
+                                            virtual_depth=self.virtual_depth, device=dev)
+            w, h = src[:, 2] - src[:, 0], src[:, 3] - src[:, 1]
+            cx, cy = src[:, 0] + 0.5 * w + w * deltas[:, 0], src[:, 1] + 0.5 * h + h * deltas[:, 1]
+            pri = self.priors_dims_per_cat.detach().to(dev)[box_classes]
+            if self.dims_priors_func == "sigmoid":
+                lo, hi = (pri[:, 0] - 3 * pri[:, 1]).clip(0.0), pri[:, 0] + 3 * pri[:, 1]
+                dims = lo + (hi - lo) * torch.sigmoid(dims_n)
+            else:
+                dims = torch.exp(dims_n.clip(max=5)) * pri[:, 0]
+            if self.z_type == "sigmoid":
+                z = torch.sigmoid(z) * 100
+            elif self.z_type == "log":
+                z = torch.exp(z)
+            z = z * v2r
+            x3d, y3d = z * (cx - K4[:, 2]) / K4[:, 0], z * (cy - K4[:, 3]) / K4[:, 1]
+            ratio_pb = torch.cat([torch.full((c,), float(ratios[i])) for i, c in enumerate(nb)]).to(dev)
+            cube_3d = torch.cat((torch.stack((x3d, y3d, z)).T, dims, torch.stack((cx, cy), 1) * ratio_pb[:, None]), 1)
+            if self.use_confidence:
+                cube_3d = torch.cat((cube_3d, torch.exp(-heads[4][ar, box_classes])[:, None]), 1)
+            R = per_box["R"]
+            verts = WCubes(torch.cat((cube_3d[:, :6], R.reshape(n, 9)), 1).unsqueeze(1)).get_all_corners()[:, 0]
+            out = []
+            for i, (c3, Ri, vi, cls_i) in enumerate(zip(cube_3d.split(nb), R.split(nb), verts.split(nb),
+                                                        box_classes.split(nb))):
+                inst = ref_mod.Instances(im_dims[i])
+                inst.scores = c3[:, -1]
+                inst.pred_classes = cls_i
+                inst.pred_boxes = pred_boxes[i]
+                inst.pred_bbox3D = vi
+                inst.pred_center_cam, inst.pred_center_2D, inst.pred_dimensions = c3[:, :3], c3[:, 6:8], c3[:, 3:6]
+                inst.pred_pose = Ri
+                out.append(inst)
+            return out
+
+    ROIHeads3DScoreB200.__qualname__ = "ROIHeads3DScoreB200"
+    return ROIHeads3DScoreB200
+
+
+def register_roi_heads_b200():
+    """With detectron2 and the reference importable: build ``ROIHeads3DScoreB200`` on the
+    reference's ``ROIHeads3DScore`` and register it in ``ROI_HEADS_REGISTRY`` (select it with
+    ``MODEL.ROI_HEADS.NAME: ROIHeads3DScoreB200``, configs/Omni_combined.yaml:25-36). Returns the
+    class; raises ImportError where detectron2 is absent (then ``make_roi_heads_b200(base)``
+    builds the class on whatever ``ROIHeads3DScore`` the caller imported)."""
+    from detectron2.modeling.roi_heads import ROI_HEADS_REGISTRY          # noqa: F401 (ImportError without it)
+    from cubercnn.modeling.roi_heads.roi_heads import ROIHeads3DScore
+    cls = make_roi_heads_b200(ROIHeads3DScore)
+    try:
+        ROI_HEADS_REGISTRY.register(cls)
+    except AssertionError:
+        pass                                                               # already registered
+    return cls
