@@ -154,7 +154,10 @@ typedef struct WcrScoreParams {
     int32_t e_iou, e_pts, e_seg;
     int32_t point_stride;   /* depth ROI sub-sampling (1 == every pixel)          */
     int32_t seg_mode;       /* 0 = mask_iou (utils.py:225), 1 = mod_mask_iou (:236) */
-    int32_t reserved0, reserved1, reserved2;
+    float   map_beta;       /* > 0: every term goes through custom_mapping(x, map_beta)
+                               (utils.py:207-223, the S-curve 1 / (1 + (x / (1 - x)) ** -beta),
+                               evaluated in double) before its exponent; 0 = off (default) */
+    int32_t reserved1, reserved2;
 } WcrScoreParams;
 
 #define WCR_CUBE_FLOATS   15   /* [cx cy cz w h l R(9 row-major)], spaces.py:130-150 */
@@ -196,6 +199,8 @@ int wcr_sample_cubes(const WcrImage *images, const WcrBox *boxes, int n_boxes,
  * box (utils.py:181-187), point-in-oriented-cube count over the depth pixels of
  * the GT box ROI unprojected through K (A3.11 / A1.4), segmentation-mask
  * coverage (utils.py:225-245, 490-493), combined score, top-k.
+ *   R need not be orthonormal: the projected-box / depth-range cull (exact only for a rotation)
+ *   is switched off for a proposal whose R^T R differs from I by more than 1e-4.
  *   cubes     [n_boxes][N][15] or NULL => sampled in-kernel (same generator and
  *             arguments as wcr_sample_cubes; priors/normals/z0/h_sample/seed are
  *             only read in that case)

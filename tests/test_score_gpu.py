@@ -269,6 +269,10 @@ def test_score_culling_adversarial(cuda_lib, stride):
     cubes[:, 2, 3:6] = 0.001
     cubes[:, 3, 3] = float("nan")
     cubes[:, 4, 0] = float("inf")
+    # NON-orthonormal R (a raw head pose with drift): the accepted region {|R^T (p - c)| <= half} is
+    # no longer the box spanned by the corners, so the cull must switch itself off
+    cubes[:, 5:60, 6:] *= (0.6 + 0.8 * torch.rand(nb, 55, 9, generator=g))
+    cubes[:, 60:80, 6:] += 0.3 * torch.randn(nb, 20, 9, generator=g)
     res = score_topk(shard, boxes, cubes.cuda(), cfg=ScoreConfig(k=16, point_stride=stride), want_all=True)
     total = 0
     for b in range(nb):
@@ -385,6 +389,45 @@ def test_score_seg_on_demand_equals_full_evaluation(cuda_lib, N, k, e_pts, e_seg
     idx = rec_full[:, :, 0].contiguous().view(torch.int32).long()
     assert (idx >= 0).all()
     assert torch.equal(torch.gather(full["scores"], 1, idx), rec_full[:, :, 1])
+
+
+def test_score_custom_mapping_shaping(cuda_lib):
+    """ScoreConfig.map_beta > 0 passes every term through custom_mapping (utils.py:207-223) before
+    its exponent. Scores within 1e-5 of the composition of the oracle's terms with
+    oracle.blocks2.custom_mapping; the top-k may differ only among proposals whose scores are
+    closer than 1e-6 relative (powf in double on both sides, one float rounding apart); the
+    on-demand mask path gives the records of the full evaluation."""
+    from oracle import blocks2 as ob
+    from wcr import synth
+    from wcr.proposals import propose, score_topk, ScoreConfig, SegMasks
+    H, W, N = 240, 320, 500
+    ims, shard, boxes, priors, normals = _setup(1, H, W, n_boxes=3, first=61)
+    masks = [m for im in ims for m in synth.seg_masks(im["boxes"], H, W)]
+    seg = SegMasks(shard, boxes, masks)
+    cubes = propose(shard, boxes, priors, normals, N, seed=4)
+    cfg = ScoreConfig(e_seg=1, k=16, map_beta=1.7)
+    full = score_topk(shard, boxes, cubes, cfg=cfg, seg=seg, want_all=True)
+    rec_full = full["records"].clone()
+    lazy = score_topk(shard, boxes, cubes, cfg=cfg, seg=seg)
+    assert torch.equal(lazy["records"].view(torch.int32), rec_full.view(torch.int32))
+    ch = cubes.cpu().numpy()
+    im = ims[0]
+    for b in range(3):
+        ref = oc.score_box(im["depth"].numpy(), im["K"].numpy(), im["boxes"][b].numpy(), (H, W), ch[b],
+                           1, 1, 1, 1, 0, masks[b].numpy())
+        pts = ref["count"].astype(np.float32) / np.float32(max(ref["npts"], 1))
+
+        def cm(x):   # the reference divides by zero at x == 1 (Python floats); the limit is 1
+            return np.asarray([1.0 if v >= 1 else ob.custom_mapping([v], 1.7)[0] for v in x], dtype=np.float32)
+        want = (cm(ref["iou"]) * cm(pts)) * cm(ref["seg"])
+        got = full["scores"][b].cpu().numpy()
+        np.testing.assert_allclose(got, want, rtol=1e-5, atol=1e-12)
+        idx = rec_full[b, :, 0].contiguous().view(torch.int32).cpu().numpy()
+        order = np.argsort(-want.astype(np.float64), kind="stable")[:16]
+        for r in range(16):
+            assert idx[r] == order[r] or abs(want[idx[r]] - want[order[r]]) <= 1e-6 * abs(want[order[r]]), (b, r)
+    plain = score_topk(shard, boxes, cubes, cfg=ScoreConfig(e_seg=1, k=16), seg=seg, want_all=True)
+    assert not torch.equal(plain["scores"], full["scores"])
 
 
 def test_pack_box_masks_device_equals_host(cuda_lib):

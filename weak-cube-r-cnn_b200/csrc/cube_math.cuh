@@ -153,6 +153,16 @@ __device__ __forceinline__ float iou_2d(float gx1, float gy1, float gx2, float g
     return inter > 0.f ? inter / ((a1 + a2) - inter) : 0.f;
 }
 
+// custom_mapping (utils.py:207-223) of one score term, in double like the reference's Python
+// floats: 0 for x <= 0, 1 / (1 + (x / (1 - x)) ** -beta) else (x == 1 -> 1). beta <= 0: identity.
+__device__ __forceinline__ float shape_term(float x, float beta)
+{
+    if (!(beta > 0.f)) return x;
+    if (!(x > 0.f)) return x != x ? x : 0.f;
+    const double v = (double)x;
+    return (float)(1.0 / (1.0 + pow(v / (1.0 - v), -(double)beta)));
+}
+
 __device__ __forceinline__ float ipow(float x, int e)
 {
     float r = 1.f;

@@ -293,6 +293,7 @@ extern "C" int wcr_score_topk(const WcrImage *images, const WcrBox *boxes, int n
     WCR_REQUIRE(h_score->point_stride >= 1, "wcr_score_topk: point_stride must be >= 1");
     WCR_REQUIRE(h_score->e_iou >= 0 && h_score->e_pts >= 0 && h_score->e_seg >= 0,
                 "wcr_score_topk: negative exponent");
+    WCR_REQUIRE(h_score->map_beta >= 0.f, "wcr_score_topk: map_beta must be >= 0 (0 = no shaping)");
     WCR_REQUIRE(h_score->e_seg == 0 || (seg_bits && seg_off),
                 "wcr_score_topk: e_seg > 0 needs seg_bits and seg_off");
     WCR_REQUIRE(((uintptr_t)ws & 255) == 0, "wcr_score_topk: workspace must be 256-byte aligned");

@@ -159,6 +159,7 @@ score_prep_kernel(const WcrImage *__restrict__ images, const WcrBox *__restrict_
     p.c = make_float4(C[0], C[1], C[2], NO[2]);
     int cl = 1, ch = 0, rl = 1, rh = 0;   // dead until proven reachable
     float zlo = -INFINITY, zhi = INFINITY; // depth range a point of the cube can have
+    bool ortho = true;
     if (live) {
         // unclamped projection of the 8 corners; min/max and the nearest corner depth
         const float hx = cube[5] / 2.f, hy = cube[4] / 2.f, hz = cube[3] / 2.f;
@@ -181,7 +182,19 @@ score_prep_kernel(const WcrImage *__restrict__ images, const WcrBox *__restrict_
             mnz = fminf(mnz, Z); mxz = fmaxf(mxz, Z);
         }
         cl = 0; ch = roi.ncols - 1; rl = 0; rh = roi.nrows - 1;   // no culling
-        if (finite && mnz >= 0.01f) {
+        // The cull box and depth range come from the corners c + R (+-half); the point test accepts
+        // {|R^T (p - c)|_k <= half_k}. The two describe the same solid only for an orthonormal R
+        // (callers may hand in raw head poses): any drift beyond rounding switches culling off.
+        float dev = 0.f;
+#pragma unroll
+        for (int a = 0; a < 3; ++a)
+#pragma unroll
+            for (int c2 = a; c2 < 3; ++c2) {
+                const float d = fmaf(R[6 + a], R[6 + c2], fmaf(R[3 + a], R[3 + c2], R[a] * R[c2]));
+                dev = fmaxf(dev, fabsf(d - (a == c2 ? 1.f : 0.f)));
+            }
+        ortho = dev <= 1.0e-4f;      // NaN -> false
+        if (finite && ortho && mnz >= 0.01f) {
             // pixel u = u0 + c*stride is reachable iff floor(mnx) - 1 <= u <= ceil(mxx) + 1
             const float big = 1.0e6f;
             const int x_lo = (int)floorf(fminf(fmaxf(mnx, -big), big)) - 1 - roi.u0;
@@ -204,7 +217,7 @@ score_prep_kernel(const WcrImage *__restrict__ images, const WcrBox *__restrict_
     // the ROI cells (16 x 16 grid, score_zgrid_kernel) its cull box overlaps. "No" is a proof that
     // the point count is 0: such a proposal is dead for the tile items and its mask term is lazy.
     bool mayhit = cl <= ch && rl <= rh;
-    if (mayhit && zgrid) {
+    if (mayhit && zgrid && ortho) {
         const int cw = max(1, (roi.ncols + 15) >> 4), chh = max(1, (roi.nrows + 15) >> 4);
         const float2 *zg = zgrid + (size_t)b * 256;
         mayhit = false;

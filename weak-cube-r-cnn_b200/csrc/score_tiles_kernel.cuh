@@ -320,7 +320,9 @@ __device__ __forceinline__ PropTerms prop_terms(const ScoreArgs &a, const float 
         const int2 sc2 = __ldcg(a.ws.segcnt + o);
         t.sseg = seg_ratio(sc2.x, sc2.y, area, a.sc.seg_mode);
     }
-    t.score = (ipow(t.siou, a.sc.e_iou) * ipow(t.spts, a.sc.e_pts)) * ipow(t.sseg, a.sc.e_seg);
+    const float mb = a.sc.map_beta;
+    t.score = (ipow(shape_term(t.siou, mb), a.sc.e_iou) * ipow(shape_term(t.spts, mb), a.sc.e_pts)) *
+              ipow(shape_term(t.sseg, mb), a.sc.e_seg);
     return t;
 }
 
@@ -419,7 +421,7 @@ __device__ __forceinline__ float chunk_fill(const ScoreArgs &a, int b, const Wcr
     if (q >= 0) {
         const int2 c2 = a.ws.segcnt[c.cbase + q];          // written by this very lane
         const float sseg = seg_ratio(c2.x, c2.y, c.area, a.sc.seg_mode);
-        actual = ub * ipow(sseg, a.sc.e_seg);              // the product prop_terms forms
+        actual = ub * ipow(shape_term(sseg, a.sc.map_beta), a.sc.e_seg);   // the product prop_terms forms
         __stcg(a.ws.ub + c.cbase + q, actual);
     }
     return actual;

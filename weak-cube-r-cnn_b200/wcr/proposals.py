@@ -54,10 +54,11 @@ class ScoreConfig:
     point_stride: int = 1
     seg_mode: int = 0
     k: int = 16
+    map_beta: float = 0.0        # > 0: custom_mapping(x, beta) (utils.py:207-223) shapes every term; 0 = off
 
     def c_struct(self) -> _abi.ScoreParams:
         return _abi.ScoreParams(self.e_iou, self.e_pts, self.e_seg, self.point_stride,
-                                self.seg_mode, 0, 0, 0)
+                                self.seg_mode, float(self.map_beta), 0, 0)
 
 
 class BoxTable:
