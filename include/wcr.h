@@ -157,7 +157,10 @@ typedef struct WcrScoreParams {
     float   map_beta;       /* > 0: every term goes through custom_mapping(x, map_beta)
                                (utils.py:207-223, the S-curve 1 / (1 + (x / (1 - x)) ** -beta),
                                evaluated in double) before its exponent; 0 = off (default) */
-    int32_t reserved1, reserved2;
+    int32_t seg_eval;       /* mask term: 0 = the library decides, 1 = fill every hull, 2 = on demand
+                               (only where on demand is valid, see wcr_score_topk); results are
+                               identical, only the time differs */
+    int32_t reserved2;
 } WcrScoreParams;
 
 #define WCR_CUBE_FLOATS   15   /* [cx cy cz w h l R(9 row-major)], spaces.py:130-150 */

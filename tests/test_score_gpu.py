@@ -383,8 +383,12 @@ def test_score_seg_on_demand_equals_full_evaluation(cuda_lib, N, k, e_pts, e_seg
     cfg = ScoreConfig(e_iou=e_iou, e_pts=e_pts, e_seg=e_seg, k=k)
     full = score_topk(shard, boxes, cubes, cfg=cfg, seg=seg, want_all=True)
     rec_full = full["records"].clone()
-    lazy = score_topk(shard, boxes, cubes, cfg=cfg, seg=seg)
-    assert torch.equal(lazy["records"].view(torch.int32), rec_full.view(torch.int32))
+    for mode in (2, 1, 0):        # on demand, every hull through the seg items, the library's own choice
+        cfg_m = ScoreConfig(e_iou=e_iou, e_pts=e_pts, e_seg=e_seg, k=k, seg_eval=mode)
+        lazy = score_topk(shard, boxes, cubes, cfg=cfg_m, seg=seg)
+        assert torch.equal(lazy["records"].view(torch.int32), rec_full.view(torch.int32)), mode
+        filled = lazy["workspace"].hulls_filled()
+        assert filled >= cubes.shape[0] * N if mode == 1 else filled > 0
     # the winners' scores are the full evaluation's scores
     idx = rec_full[:, :, 0].contiguous().view(torch.int32).long()
     assert (idx >= 0).all()

@@ -34,6 +34,8 @@ def main():
     ap.add_argument("--default", action="store_true",
                     help="cfg.loss_functions of config.py:186: dims, pose_alignment, pose_ground, iou, z, "
                          "z_pseudo_gt_patch, depth (per-object masks)")
+    ap.add_argument("--no-host-sync", action="store_true",
+                    help="weak_loss(host_sync=False): keys decided on the host, flags checked one call late")
     a = ap.parse_args()
     import torch
     from oracle import loss as ol, loss_inputs as li
@@ -67,7 +69,7 @@ def main():
     def step():
         for v in leaves.values():
             v.grad = None
-        losses = weak_loss(cfg, **leaves, **rest, depth_maps=shard)
+        losses = weak_loss(cfg, **leaves, **rest, depth_maps=shard, host_sync=not a.no_host_sync)
         sum(losses.values()).backward()
         return losses
 
@@ -99,7 +101,9 @@ def main():
                                                     f"(n_i~U{{1..128}}), 480x640 {'white-noise' if a.noise_depth else 'scene-like'} depth, "
                                                     f"loss_functions={list(lf)}"},
         "gpu_launches_per_step": launches, "ms_min": min(ms), "ms_max": max(ms),
-        "includes": "Python wrapper, one 32-byte D2H read of the 'present' flags, autograd bookkeeping",
+        "includes": "Python wrapper, autograd bookkeeping, " + ("NO host synchronisation (flags checked one call late)"
+                                                                if a.no_host_sync else "one 52-byte D2H read of the 'present' flags"),
+        "host_sync": not a.no_host_sync,
         "cpu_baseline": {"value": statistics.median(cpu) if cpu else None, "unit": "ms", "cores": torch.get_num_threads(),
                          "kind": "port", "sample": "the same inputs, oracle/loss.py (torch fp32 + autograd) on the host"},
         "max_rel_diff_vs_cpu": worst,

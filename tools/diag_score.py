@@ -3,13 +3,19 @@ import os, sys, json, time
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT); sys.path.insert(0, os.path.join(ROOT, "weak-cube-r-cnn_b200"))
 import torch
+from wcr import _abi
+for a_ in sys.argv[1:]:
+    if a_.startswith("--lib="):
+        _abi.LIB_PATH = _abi.LIB_PATH.replace("libwcr_b200.so", a_[6:])
+sys.argv = [sys.argv[0]] + [a_ for a_ in sys.argv[1:] if not a_.startswith("--lib=")]
 import bench
 from wcr import synth
 from wcr.pipeline import ShardRunner
 from wcr.proposals import ScoreConfig, score_topk, box_center_depth
 
 n_img = int(sys.argv[1]) if len(sys.argv) > 1 else 64
-ims = bench.make_images(n_img, 0, True, None, dense=False)
+n_box = int(sys.argv[2]) if len(sys.argv) > 2 else None
+ims = bench.make_images(n_img, 0, True, n_box, dense=False)
 priors = synth.make_priors()
 r = ShardRunner(ims, 1000, "cuda", priors=priors, score_cfg=ScoreConfig(k=16, e_seg=1), seed=1234)
 r.upload(); r.step(); torch.cuda.synchronize()
@@ -28,11 +34,18 @@ def run(cfg, want_all=False, seg=True):
                       seg=r.seg if seg else None, workspace=r.ws, want_all=want_all)
 
 res = {}
-t, out = timed(lambda: run(ScoreConfig(k=16, e_seg=1)))
+t, out = timed(lambda: run(ScoreConfig(k=16, e_seg=1, seg_eval=2)))
 res["seg_on_demand_ms"] = t; res["hulls_on_demand"] = out["workspace"].hulls_filled()
+t, out = timed(lambda: run(ScoreConfig(k=16, e_seg=1, seg_eval=1)))
+res["seg_every_hull_ms"] = t
+t, out = timed(lambda: run(ScoreConfig(k=16, e_seg=1)))
+res["seg_auto_ms"] = t; res["hulls_auto"] = out["workspace"].hulls_filled()
 t, out = timed(lambda: run(ScoreConfig(k=16, e_seg=1), want_all=True))
 res["seg_all_ms(want_all)"] = t; res["hulls_all"] = out["workspace"].hulls_filled()
 t, out = timed(lambda: run(ScoreConfig(k=16, e_seg=0), seg=False))
 res["noseg_ms"] = t
 res["n_proposals"] = r.n_proposals
+out = run(ScoreConfig(k=16, e_seg=1))
+res["records_checksum"] = int(out["records"].view(torch.int32).to(torch.int64).sum().item())
+res["lib"] = os.path.basename(_abi.LIB_PATH)
 print(json.dumps(res))

@@ -142,6 +142,7 @@ struct ScoreWs {
     int4 *cullbox;       // [n_boxes][N] cull boxes (tile path)
     float2 *zgrid;       // [n_boxes][256] depth range of the ROI's 16 x 16 cells (tile path)
     uint8_t *mayhit;     // [n_boxes][N] 0: the proposal provably holds no point (tile path)
+    float *siou;         // [n_boxes][N] IoU term, written by score_prep_kernel
 };
 
 struct ScoreArgs {
@@ -158,6 +159,7 @@ struct ScoreArgs {
     int grp;             // tile path: registers per column group (plan and kernel must agree)
     int ps;              // tile path: proposals per tile item (power of two, 128 .. SC_CHUNK)
     int seg_lazy;        // tile path: mask term evaluated on demand by the epilogues (no seg items)
+    int siou_ready;      // tile path: ws.siou holds every proposal's IoU term (written by score_prep_kernel)
     ScoreWs ws;
     float *records;
     float *out_scores, *out_iou;
@@ -251,8 +253,9 @@ size_t carve(void *base, int n_boxes, int N, int k, bool need_cubes, bool need_s
     int4 *cullbox = (int4 *)take((size_t)n_boxes * N * sizeof(int4));
     float2 *zgrid = (float2 *)take((size_t)n_boxes * 256 * sizeof(float2));
     uint8_t *mayhit = (uint8_t *)take((size_t)n_boxes * N);
+    float *siou = (float *)take((size_t)n_boxes * N * sizeof(float));
     if (ws) {
-        ws->segcnt = segcnt; ws->params = params; ws->cullbox = cullbox; ws->zgrid = zgrid; ws->mayhit = mayhit;
+        ws->segcnt = segcnt; ws->params = params; ws->cullbox = cullbox; ws->zgrid = zgrid; ws->mayhit = mayhit; ws->siou = siou;
         ws->queue = queue; ws->executed = (unsigned long long *)(queue ? (char *)queue + 8 : nullptr);
         ws->hulls = (unsigned long long *)(queue ? (char *)queue + 16 : nullptr);
         ws->dynq = (int *)(queue ? (char *)queue + 24 : nullptr);
@@ -293,6 +296,7 @@ extern "C" int wcr_score_topk(const WcrImage *images, const WcrBox *boxes, int n
     WCR_REQUIRE(h_score->point_stride >= 1, "wcr_score_topk: point_stride must be >= 1");
     WCR_REQUIRE(h_score->e_iou >= 0 && h_score->e_pts >= 0 && h_score->e_seg >= 0,
                 "wcr_score_topk: negative exponent");
+    WCR_REQUIRE(h_score->seg_eval >= 0 && h_score->seg_eval <= 2, "wcr_score_topk: seg_eval must be 0, 1 or 2");
     WCR_REQUIRE(h_score->map_beta >= 0.f, "wcr_score_topk: map_beta must be >= 0 (0 = no shaping)");
     WCR_REQUIRE(h_score->e_seg == 0 || (seg_bits && seg_off),
                 "wcr_score_topk: e_seg > 0 needs seg_bits and seg_off");
@@ -321,7 +325,7 @@ extern "C" int wcr_score_topk(const WcrImage *images, const WcrBox *boxes, int n
     a.out_scores = out_scores; a.out_iou = out_iou; a.out_count = out_count;
     a.out_proj = out_proj; a.out_npts = out_npts;
     a.seg_bits = seg_bits; a.seg_off = seg_off; a.out_seg = out_seg;
-    a.item_px = 0; a.grp = 8; a.ps = wcr::SC_CHUNK; a.seg_lazy = 0;
+    a.item_px = 0; a.grp = 8; a.ps = wcr::SC_CHUNK; a.seg_lazy = 0; a.siou_ready = 0;
     const int sms = wcr::sm_count();
     WCR_REQUIRE((N + 255) / 256 <= 65535, "wcr_score_topk: N too large");
     a.src.cubes = cubes; a.src.priors = priors; a.src.normals = normals; a.src.z0 = z0;
@@ -363,13 +367,22 @@ extern "C" int wcr_score_topk(const WcrImage *images, const WcrBox *boxes, int n
     // Mask term on demand (chunk_epilogue_warp): valid when the ratio is bounded by 1 (mask_iou;
     // mod_mask_iou = inter^5 / union is not) and nobody asked for per-proposal scores or ratios.
     a.seg_lazy = h_score->e_seg > 0 && h_score->seg_mode == 0 && out_seg == nullptr && out_scores == nullptr;
+    // Mask term on demand needs enough (box, chunk) pairs to hide the two dependent phases of a
+    // chunk behind other chunks' work; a small shard fills every hull through the parallel seg
+    // items instead. seg_eval: 0 = decide here, 1 = every hull, 2 = on demand.
+    if (a.seg_lazy && h_score->seg_eval != 2)
+        a.seg_lazy = h_score->seg_eval == 0 && (long long)n_boxes * nc >= sms_resident_warps() / 4;   // measured: 4.23 vs 4.51 ms at 486 chunks, 1.37 vs 0.90 ms at 64
+    // per-proposal IoU term in the prep kernel unless per-proposal outputs want the projected box
+    a.siou_ready = !(out_scores || out_iou || out_seg || out_count || out_proj);
     if (h_score->e_pts > 0) {
         wcr::score_zgrid_kernel<<<dim3(n_boxes, 8), 1024, 0, st>>>(images, boxes, h_score->point_stride, 1, a.ws.zgrid);
         WCR_CHECK_LAUNCH("score_zgrid_kernel");
+    }
+    if (h_score->e_pts > 0 || a.siou_ready) {
         const dim3 grid(n_boxes, (N + 255) / 256);
         wcr::score_prep_kernel<<<grid, 256, 0, st>>>(images, boxes, n_boxes, a.src, N,
-                                                      h_score->point_stride, 1, a.ws.params, a.ws.cullbox,
-                                                      a.ws.zgrid, a.ws.mayhit);
+                                                      h_score->point_stride, h_score->e_pts > 0, a.ws.params, a.ws.cullbox,
+                                                      a.ws.zgrid, a.ws.mayhit, a.siou_ready ? a.ws.siou : nullptr);
         WCR_CHECK_LAUNCH("score_prep_kernel");
     }
     // FFMA2 point test, inside indicator on the integer pipe, 3 CTAs x 4 warps per SM

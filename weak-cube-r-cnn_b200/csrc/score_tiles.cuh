@@ -121,7 +121,8 @@ __global__ void __launch_bounds__(256)
 score_prep_kernel(const WcrImage *__restrict__ images, const WcrBox *__restrict__ boxes, int n_boxes,
                   const CubeSrc src, int N, int stride, int use_pts,
                   PParam *__restrict__ out, int4 *__restrict__ out_box,
-                  const float2 *__restrict__ zgrid, uint8_t *__restrict__ out_mayhit)
+                  const float2 *__restrict__ zgrid, uint8_t *__restrict__ out_mayhit,
+                  float *__restrict__ out_siou)
 {
     const int j = blockIdx.y * 256 + threadIdx.x, b = blockIdx.x;
     if (j >= N) return;
@@ -137,6 +138,18 @@ score_prep_kernel(const WcrImage *__restrict__ images, const WcrBox *__restrict_
         const BoxCtx ctx = make_box_ctx(im, bx, src.priors, src.normals, src.z0[b], src.sp);
         sample_cube(ctx, nullptr, N, src.seed, (uint32_t)b, (uint32_t)j, cube);
     }
+    // the IoU term of the score (corners -> K -> clamp -> min / max -> pairwise_iou), here where
+    // every proposal has a thread of its own: the chunk epilogues (ONE warp per 1024 proposals)
+    // then only combine it with the point count
+    if (out_siou) {
+        const Intr Kc = {im.fx, im.fy, im.cx, im.cy};
+        float lo0, hi0, lo1, hi1;
+        clamp_bounds(bx.clamp0, lo0, hi0);
+        clamp_bounds(bx.clamp1, lo1, hi1);
+        const ProjBox pbx = project_cube(cube, Kc, lo0, hi0, lo1, hi1, nullptr);
+        out_siou[(size_t)b * N + j] = iou_2d(bx.x1, bx.y1, bx.x2, bx.y2, pbx);
+    }
+    if (!use_pts) return;     // launched for the IoU term only
     PParam p;
     const bool live = roi.nrows > 0 && cube[3] > 0.f && cube[4] > 0.f && cube[5] > 0.f;
     float A[3], B[3], C[3], NO[3];

@@ -384,6 +384,32 @@ __device__ __forceinline__ void chunk_scores(const ScoreArgs &a, int b, const Wc
                                              const ChunkCtx &c, int chunk, bool with_seg, float *sc, int lane)
 {
     if (a.out_npts && chunk == 0 && lane == 0) a.out_npts[b] = c.npts;
+    if (a.siou_ready) {
+        // fast path: the IoU term was computed per thread by score_prep_kernel; a lane only combines
+        // it with the point count (and the mask ratio when every hull was filled)
+        const float mb = a.sc.map_beta;
+#pragma unroll 4
+        for (int i = 0; i < SC_CHUNK / 32; ++i) {
+            const int loc = i * 32 + lane;
+            float score = -INFINITY;
+            if (loc < c.chunk_n) {
+                const size_t o = c.cbase + loc;
+                const float siou = __ldcg(a.ws.siou + o);
+                const int count = __ldcg(a.ws.count + o);
+                const float spts = c.npts > 0 ? (float)count / (float)c.npts : 0.f;
+                float sseg = 1.f;
+                if (a.sc.e_seg > 0 && with_seg) {
+                    const int2 sc2 = __ldcg(a.ws.segcnt + o);
+                    sseg = seg_ratio(sc2.x, sc2.y, c.area, a.sc.seg_mode);
+                }
+                score = (ipow(shape_term(siou, mb), a.sc.e_iou) * ipow(shape_term(spts, mb), a.sc.e_pts)) *
+                        ipow(shape_term(sseg, mb), a.sc.e_seg);
+            }
+            sc[loc] = score;
+        }
+        __syncwarp();
+        return;
+    }
 #pragma unroll 1
     for (int i = 0; i < SC_CHUNK / 32; ++i) {
         const int loc = i * 32 + lane;

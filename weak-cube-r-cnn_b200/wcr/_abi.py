@@ -162,7 +162,7 @@ class ScoreParams(ctypes.Structure):
     """include/wcr.h WcrScoreParams."""
     _fields_ = [("e_iou", ctypes.c_int32), ("e_pts", ctypes.c_int32), ("e_seg", ctypes.c_int32),
                 ("point_stride", ctypes.c_int32), ("seg_mode", ctypes.c_int32),
-                ("map_beta", c_float), ("reserved1", ctypes.c_int32),
+                ("map_beta", c_float), ("seg_eval", ctypes.c_int32),
                 ("reserved2", ctypes.c_int32)]
 
 

@@ -55,10 +55,11 @@ class ScoreConfig:
     seg_mode: int = 0
     k: int = 16
     map_beta: float = 0.0        # > 0: custom_mapping(x, beta) (utils.py:207-223) shapes every term; 0 = off
+    seg_eval: int = 0            # mask term: 0 = library decides, 1 = every hull, 2 = on demand (same results)
 
     def c_struct(self) -> _abi.ScoreParams:
         return _abi.ScoreParams(self.e_iou, self.e_pts, self.e_seg, self.point_stride,
-                                self.seg_mode, float(self.map_beta), 0, 0)
+                                self.seg_mode, float(self.map_beta), int(self.seg_eval), 0)
 
 
 class BoxTable:
