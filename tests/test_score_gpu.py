@@ -149,8 +149,9 @@ def test_score_topk_bit_exact(cuda_lib, N, H, W, stride):
 
 
 def test_score_fused_sampling_equals_two_step(cuda_lib):
-    """cubes == NULL (proposals generated and held in registers) must select the
-    same top-k as sampling to HBM first."""
+    """cubes == NULL (a proposal is regenerated from its Philox counter wherever the launch needs
+    it -- prep kernel, hull fills, record writer -- and never stored) must select the same top-k,
+    with the same records, as sampling to HBM first (wcr_sample_cubes) and scoring that array."""
     from wcr.proposals import propose, score_topk, ScoreConfig
     N = 1000
     ims, shard, boxes, priors, normals = _setup(3, n_boxes=4, first=7)

@@ -94,7 +94,7 @@ __device__ __forceinline__ void cta_topk(float *s_score, int k, float *s_red_v, 
 
 // The FIRST scoring kernel: thread = T proposals in registers, every ROI pixel broadcast to them
 // from shared memory, no culling. Superseded by score_tiles_kernel; kept behind
-// WCR_SCORE_VARIANT=4 (or 1) as the measured baseline and as an independent implementation
+// -DWCR_KEEP_BASELINE_KERNEL (libwcr_b200_baseline.so) as the measured baseline and as an independent implementation
 // the tile kernel is cross-checked against at full size (tests/test_score_fullsize_gpu.py).
 // V selects the inside indicator: 1: FMNMX3 + FSET, 4: FMNMX3 + FFMA.SAT on 2^11-scaled rows.
 template <int V, int MINB, int SC_THREADS>
