@@ -450,8 +450,9 @@ def run_wcr(args):
                           records=gather2.send)
     e2e_packed_s = pipelined(runner, runner2, gather, gather2)
     # (c) the headline e2e: the per-box masks arrive DENSE, as the reference's object_masks()
-    # produces them (roi_heads.py:383-401): n_boxes x H x W bytes cross PCIe every step and are
-    # bit-packed on the device (wcr_pack_box_masks) inside the timed region
+    # produces them (roi_heads.py:383-401), in pinned host memory; inside the timed region the ROI
+    # rectangle of every box's map is copied H2D (one 2-D copy per box: only what the packer reads
+    # crosses PCIe; h2d_bytes_per_step counts those bytes) and bit-packed on the device
     e2e_s, dense_h2d, e2e_dense_sync_s = e2e_packed_s, None, None
     if use_seg:
         gather3 = wdist.TopkGather(n_local_boxes, TOPK, dev)
@@ -531,8 +532,10 @@ def run_wcr(args):
                     "h2d_bytes_per_step": dense_h2d if dense_h2d is not None else runner.h2d_bytes,
                     "d2h_bytes_per_step": runner.d2h_bytes,
                     "api": "wcr.pipeline.ShardPipeline (double-buffered: copies of neighbouring steps overlap the pass)",
-                    "masks": ("dense per-box masks (n_boxes x H x W u8, as object_masks() yields them) cross PCIe "
-                              "every step and are bit-packed on the device" if dense_h2d is not None else "no mask term"),
+                    "masks": ("dense per-box masks (n_boxes x H x W u8, as object_masks() yields them) in pinned host memory; "
+                              "every step the ROI rectangle of each box's map is copied H2D (one 2-D copy per box) and "
+                              "bit-packed on the device" if dense_h2d is not None else "no mask term"),
+                    "dense_mask_bytes_on_host": (int(runner.n_boxes) * H * W) if dense_h2d is not None else 0,
                     "one_shard_at_a_time": (total_props * args.steps / e2e_dense_sync_s) if e2e_dense_sync_s
                     else total_props * args.steps / e2e_sync_s,
                     "prepacked": {"value": total_props * args.steps / e2e_packed_s,

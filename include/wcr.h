@@ -251,6 +251,14 @@ int wcr_pack_box_masks(const uint8_t *masks, int64_t mask_stride, int mask_pitch
                        const int32_t *mask_idx, const WcrImage *images, const WcrBox *boxes,
                        int n_boxes, const int64_t *seg_off, uint32_t *out_bits, void *stream);
 
+/* Host -> device copy of just the ROI rectangle of every box's dense mask (one cudaMemcpy2DAsync
+ * per box on `stream`): what wcr_pack_box_masks reads, and nothing else, crosses PCIe. h_masks:
+ * PINNED host memory, same layout as d_masks; h_rois [n_boxes][4] = u0 v0 u1 v1, HOST array;
+ * h_mask_idx HOST array or NULL. No device check: enqueues copies only. */
+int wcr_h2d_box_mask_rois(const uint8_t *h_masks, uint8_t *d_masks, int64_t mask_stride,
+                          int mask_pitch, const int32_t *h_rois, const int32_t *h_mask_idx,
+                          int n_boxes, void *stream);
+
 /* ------------------------------------------------- block-level drop-ins -- */
 /* One launch behind each helper the reference exposes by name (SURVEY A2.1-A2.5,
  * A3.2-A3.8); the fused entry points above use the same device functions. */

@@ -474,12 +474,16 @@ def test_shard_runner_dense_masks_equal_prepacked(cuda_lib):
         im["seg"] = synth.seg_masks(im["boxes"], H, W)
     kw = dict(priors=synth.make_priors(), score_cfg=ScoreConfig(k=8, e_seg=1), seed=3)
     a = ShardRunner(ims, 400, "cuda", **kw).run_host().clone()
-    r = ShardRunner(ims, 400, "cuda", dense_seg=True, **kw)
-    assert r.h2d_bytes > 9 * H * W
-    assert torch.equal(r.run_host().view(torch.int32), a.view(torch.int32))
-    r.h_seg_dense.zero_()                   # new mask contents reach the kernel through upload()
-    b = r.run_host()
-    assert not torch.equal(b, a) and (b[:, :, 19] == 0).all()
+    for mode in (True, "copy", "mapped"):   # ROI rectangles copied / whole maps copied / ROI bytes read from host
+        r = ShardRunner(ims, 400, "cuda", dense_seg=mode, **kw)
+        if mode == "copy":
+            assert r.h2d_bytes > 9 * H * W
+        else:
+            assert 0 < r.seg.roi_bytes < 9 * H * W and (r.d_seg_dense is None) == (mode == "mapped")
+        assert torch.equal(r.run_host().view(torch.int32), a.view(torch.int32)), mode
+        r.h_seg_dense.zero_()               # new mask contents reach the kernel
+        b = r.run_host()
+        assert not torch.equal(b, a) and (b[:, :, 19] == 0).all()
 
 
 def test_score_seg_degenerate(cuda_lib):

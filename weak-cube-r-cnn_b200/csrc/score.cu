@@ -437,3 +437,30 @@ extern "C" int wcr_pack_box_masks(const uint8_t *masks, int64_t mask_stride, int
     WCR_CHECK_LAUNCH("pack_box_masks_kernel");
     return WCR_OK;
 }
+
+// Host -> device copy of just the ROI rectangle of every box's dense mask: one cudaMemcpy2DAsync
+// per box on `stream` (copy engine; overlaps kernels of other streams). The dense maps are the
+// reference's masks_all_images in PINNED host memory; the device buffer has the same layout, only
+// the rectangles wcr_pack_box_masks reads are refreshed. h_rois [n][4] = u0 v0 u1 v1 (HOST array,
+// the integer ROIs: Boxes.clip + .long(), as wcr_score_topk slices them).
+extern "C" int wcr_h2d_box_mask_rois(const uint8_t *h_masks, uint8_t *d_masks, int64_t mask_stride,
+                                     int mask_pitch, const int32_t *h_rois, const int32_t *h_mask_idx,
+                                     int n_boxes, void *stream)
+{
+    WCR_REQUIRE(h_masks && d_masks && h_rois, "wcr_h2d_box_mask_rois: null pointer");
+    WCR_REQUIRE(n_boxes >= 0 && mask_pitch >= 1 && mask_stride >= 0, "wcr_h2d_box_mask_rois: bad sizes");
+    for (int b = 0; b < n_boxes; ++b) {
+        const int u0 = h_rois[4 * b], v0 = h_rois[4 * b + 1], u1 = h_rois[4 * b + 2], v1 = h_rois[4 * b + 3];
+        if (u1 <= u0 || v1 <= v0) continue;
+        const size_t off = (size_t)(h_mask_idx ? h_mask_idx[b] : b) * (size_t)mask_stride +
+                           (size_t)v0 * (size_t)mask_pitch + (size_t)u0;
+        cudaError_t e = cudaMemcpy2DAsync(d_masks + off, (size_t)mask_pitch, h_masks + off, (size_t)mask_pitch,
+                                          (size_t)(u1 - u0), (size_t)(v1 - v0), cudaMemcpyHostToDevice,
+                                          (cudaStream_t)stream);
+        if (e != cudaSuccess) {
+            wcr::set_error("wcr_h2d_box_mask_rois: cudaMemcpy2DAsync (box %d): %s", b, cudaGetErrorString(e));
+            return WCR_ELAUNCH;
+        }
+    }
+    return WCR_OK;
+}

@@ -26,9 +26,13 @@ class ShardRunner:
         K (3,3), boxes (b,4), classes (b,) and -- when ``score_cfg.e_seg > 0`` -- seg
         (b,H,W) per-box masks or seg_packed (``pack_box_masks`` output). All images are uploaded into two padded device planes
         so a step's H2D is a handful of large copies. ``dense_seg``: the per-box masks stay DENSE
-        on the host side (what the reference's ``object_masks`` produces, roi_heads.py:383-401):
-        every ``upload`` copies them (n_boxes x H x W bytes) and every ``step`` bit-packs them on the
-        device (``wcr_pack_box_masks``); default: packed once on the host at construction.
+        on the host side (what the reference's ``object_masks`` produces, roi_heads.py:383-401), in
+        pinned memory; every ``upload`` copies the ROI rectangle of each box's map H2D (one 2-D copy
+        per box, ``wcr_h2d_box_mask_rois``: only what the packer reads crosses PCIe) and every
+        ``step`` bit-packs them on the device (``wcr_pack_box_masks``). ``dense_seg="copy"``: whole
+        maps, n_boxes x H x W bytes per step; ``dense_seg="mapped"``: no copy at all, the pack kernel
+        reads the ROI bytes from the pinned maps over PCIe (best for one shard at a time, but it
+        cannot overlap the scoring kernel). Default (False): packed once on the host.
 
         The geometry of a runner is FROZEN at construction: image sizes, intrinsics, boxes and
         mask offsets are part of the device tables. Re-uploading (``upload``, ``ShardPipeline``)
@@ -75,8 +79,15 @@ class ShardRunner:
                 m = im["seg"]
                 self.h_seg_dense[g:g + len(m), :h, :w] = (torch.as_tensor(m) != 0).to(torch.uint8)
                 g += len(m)
-            self.d_seg_dense = self.h_seg_dense.to(self.device)
-            self.seg = SegMasks.from_dense(self.shard, self.boxes, self.d_seg_dense)
+            self.dense_mode = dense_seg if isinstance(dense_seg, str) else "roi"
+            if self.dense_mode == "mapped":
+                self.seg = SegMasks.from_dense(self.shard, self.boxes, self.h_seg_dense)
+            else:
+                self.d_seg_dense = self.h_seg_dense.to(self.device)
+                self.seg = SegMasks.from_dense(self.shard, self.boxes, self.d_seg_dense)
+                from .proposals import box_rois
+                import numpy as _np
+                self._h_rois = _np.ascontiguousarray(box_rois(self.boxes, self.shard), dtype=_np.int32)
         elif self.score_cfg.e_seg > 0:
             if all("seg_packed" in im for im in images):
                 self.seg = SegMasks(self.shard, self.boxes, packed=[w for im in images for w in im["seg_packed"]])
@@ -96,8 +107,8 @@ class ShardRunner:
     @property
     def h2d_bytes(self) -> int:
         seg = self.h_seg.numel() * 4 if self.h_seg is not None else 0
-        if self.h_seg_dense is not None:
-            seg = self.h_seg_dense.numel()
+        if self.h_seg_dense is not None:      # bytes that cross PCIe for the masks
+            seg = self.h_seg_dense.numel() if self.dense_mode == "copy" else self.seg.roi_bytes
         return self.h_depth.numel() * 4 + self.h_ground.numel() + self.h_boxes.numel() + seg
 
     @property
@@ -110,8 +121,14 @@ class ShardRunner:
         self.boxes.table.copy_(self.h_boxes, non_blocking=True)
         if self.h_seg is not None:
             self.seg.bits.copy_(self.h_seg, non_blocking=True)
-        if self.h_seg_dense is not None:
+        if self.d_seg_dense is not None and self.dense_mode == "copy":
             self.d_seg_dense.copy_(self.h_seg_dense, non_blocking=True)
+        elif self.d_seg_dense is not None:
+            m = self.h_seg_dense
+            _abi.check(_abi.load().wcr_h2d_box_mask_rois(
+                m.data_ptr(), self.d_seg_dense.data_ptr(), m.stride(0), m.stride(1),
+                self._h_rois.ctypes.data, None, self.n_boxes, _abi.stream_ptr(self.device)),
+                "wcr_h2d_box_mask_rois")
 
     def step(self, score_events=None):
         """Device-resident pass: 5 kernel launches, no host sync, no D2H.
@@ -120,8 +137,8 @@ class ShardRunner:
         self.normals = ground.normal_vector_from_maps(None, None, None, shard=self.shard,
                                                       seed=self.seed)
         z0 = box_center_depth(self.shard, self.boxes)
-        if self.d_seg_dense is not None:
-            self.seg.repack(self.d_seg_dense)       # dense masks of this step -> seg_bits, on the device
+        if self.h_seg_dense is not None:         # dense masks of this step -> seg_bits, on the device
+            self.seg.repack(self.d_seg_dense if self.d_seg_dense is not None else self.h_seg_dense)
         if score_events is not None:
             score_events[0].record()
             out = self._score(z0)

@@ -217,6 +217,7 @@ def _segmasks_from_dense(shard: ImageShard, boxes: "BoxTable", masks: torch.Tens
         ncols = np.maximum(rois[:, 2] - rois[:, 0], 0)
         off[1:] = np.cumsum(np.where(ncols > 0, nrows, 0).astype(np.int64) * ((ncols + 31) // 32))
     self.host_off, self.host_bits = off, None
+    self.roi_bytes = int((np.where(ncols > 0, nrows, 0).astype(np.int64) * ncols).sum()) if len(rois) else 0
     self.bits = torch.zeros((max(int(off[-1]), 1),), dtype=torch.int32, device=shard.device)
     self.off = torch.from_numpy(off.copy()).to(shard.device)
     self.n_boxes = len(rois)
@@ -228,7 +229,11 @@ def _segmasks_from_dense(shard: ImageShard, boxes: "BoxTable", masks: torch.Tens
 
 
 def _segmasks_repack(self, masks: torch.Tensor):
-    _abi.require_cuda(masks)
+    """``masks``: a CUDA tensor, or a PINNED host tensor -- pinned memory is mapped into the
+    device's address space (unified virtual addressing), so the pack kernel then reads just the
+    ROI bytes it needs straight from host memory over PCIe and the dense maps are never copied."""
+    if not masks.is_cuda and not masks.is_pinned():
+        raise _abi.WcrError("wcr: CUDA or pinned host tensor required (there is no CPU fallback on this path)")
     if masks.dtype == torch.bool:
         masks = masks.view(torch.uint8)
     assert masks.dtype == torch.uint8 and masks.dim() == 3 and masks.stride(2) == 1
@@ -236,7 +241,7 @@ def _segmasks_repack(self, masks: torch.Tensor):
     _abi.check(lib.wcr_pack_box_masks(masks.data_ptr(), masks.stride(0), masks.stride(1),
                                       _abi.ptr(self._mask_idx), self._shard.table.data_ptr(),
                                       self._boxes.table.data_ptr(), self.n_boxes, self.off.data_ptr(),
-                                      self.bits.data_ptr(), _abi.stream_ptr(masks.device)),
+                                      self.bits.data_ptr(), _abi.stream_ptr(self.bits.device)),
                "wcr_pack_box_masks")
 
 
