@@ -30,12 +30,14 @@ def main():
     bs = BlockSet(base, 37, block=4, map_seed=3)          # 10 blocks, the last one ragged
     cfg = ScoreConfig(k=K, e_seg=1)
     priors = synth.make_priors()
-    lo, hi = wd.shard_range(bs.n_blocks, rank, world)
-    gather = wd.TopkGather(bs.n_boxes_of(range(lo, hi)), K, dev)
-    mine = ResidentBlocks(bs, range(lo, hi), N, dev, priors=priors, score_cfg=cfg, seed=77,
+    # blocks -> ranks by predicted work (not contiguous): the gathered records are put back into
+    # global box order before the comparison
+    rank_blocks = wd.balanced_assignment(bs.block_weights(N), world)
+    gather = wd.TopkGather(bs.n_boxes_of(rank_blocks[rank]), K, dev)
+    mine = ResidentBlocks(bs, rank_blocks[rank], N, dev, priors=priors, score_cfg=cfg, seed=77,
                           records=gather.send)
     mine.run_pass()
-    allrec = gather.gather()
+    allrec = gather.gather().index_select(0, torch.from_numpy(bs.global_order(rank_blocks)).to(dev))
     torch.cuda.synchronize()
     if rank == 0:
         single = ResidentBlocks(bs, range(bs.n_blocks), N, dev, priors=priors, score_cfg=cfg, seed=77)

@@ -72,3 +72,25 @@ def test_blockset_arithmetic():
         for r in range(world):
             lo, hi = shard_range(8192 // 64, r, world)
             assert (lo * 64, hi * 64) == shard_range(8192, r, world)
+
+
+def test_balanced_assignment_and_global_order():
+    sys.path.insert(0, os.path.join(ROOT, "weak-cube-r-cnn_b200"))
+    import numpy as np
+    from wcr import synth
+    from wcr.dist import balanced_assignment
+    from wcr.job import BlockSet
+    rng = np.random.default_rng(0)
+    w = rng.uniform(0.8, 1.2, 128)
+    a = balanced_assignment(w, 8)
+    assert sorted(b for r in a for b in r) == list(range(128)) and all(r == sorted(r) for r in a)
+    loads = [w[r].sum() for r in a]
+    assert max(loads) / np.mean(loads) < 1.005          # contiguous ranges: ~1.02
+    assert balanced_assignment(w, 8) == a               # deterministic
+    base = [synth.make_image(i, 48, 64, n_boxes=1 + i) for i in range(3)]
+    bs = BlockSet(base, 23, block=4, map_seed=0, use_seg=False)
+    rb = balanced_assignment(bs.block_weights(100), 2)
+    idx = bs.global_order(rb)
+    # tag every box with its global id in rank-major order, then undo
+    tags = np.concatenate([np.arange(bs.box_offset[b], bs.box_offset[b + 1]) for r in rb for b in r])
+    assert np.array_equal(tags[idx], np.arange(bs.box_offset[-1]))

@@ -59,6 +59,21 @@ def bind_to_gpu_numa(local_rank: int) -> dict:
     return info
 
 
+def balanced_assignment(weights, world: int):
+    """Blocks -> ranks by weight, longest first (LPT): rank lists of block ids, each ascending.
+    Deterministic (ties by block id), so every rank computes the same assignment. Contiguous
+    ranges (``shard_range``) leave the slowest rank ~2 % above the mean on the 8192-image job;
+    this brings it within a block's granularity of the mean."""
+    order = sorted(range(len(weights)), key=lambda b: (-float(weights[b]), b))
+    load = [0.0] * world
+    out = [[] for _ in range(world)]
+    for b in order:
+        r = min(range(world), key=lambda i: (load[i], i))
+        out[r].append(b)
+        load[r] += float(weights[b])
+    return [sorted(x) for x in out]
+
+
 def is_dist() -> bool:
     return dist.is_available() and dist.is_initialized() and dist.get_world_size() > 1
 
