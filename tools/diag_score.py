@@ -43,7 +43,7 @@ res["seg_auto_ms"] = t; res["hulls_auto"] = out["workspace"].hulls_filled()
 t, out = timed(lambda: run(ScoreConfig(k=16, e_seg=1), want_all=True))
 res["seg_all_ms(want_all)"] = t; res["hulls_all"] = out["workspace"].hulls_filled()
 t, out = timed(lambda: run(ScoreConfig(k=16, e_seg=0), seg=False))
-res["noseg_ms"] = t
+res["noseg_ms"] = t; res["executed_tests"] = out["workspace"].executed_tests()
 res["n_proposals"] = r.n_proposals
 out = run(ScoreConfig(k=16, e_seg=1))
 res["records_checksum"] = int(out["records"].view(torch.int32).to(torch.int64).sum().item())

@@ -5,6 +5,10 @@ import os, sys
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT); sys.path.insert(0, os.path.join(ROOT, "weak-cube-r-cnn_b200"))
 import torch
+from wcr import _abi
+for a_ in sys.argv[1:]:
+    if a_.startswith("--lib="):
+        _abi.LIB_PATH = _abi.LIB_PATH.replace("libwcr_b200.so", a_[6:])
 import bench
 from wcr import synth
 from wcr.pipeline import ShardRunner
