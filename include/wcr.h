@@ -246,7 +246,9 @@ int wcr_score_topk(const WcrImage *images, const WcrBox *boxes, int n_boxes,
  * H x W map per object, non-zero == object) -> the seg_bits layout of wcr_score_topk, on the
  * device. Box b reads mask (mask_idx ? mask_idx[b] : b), mask_stride bytes apart, rows
  * mask_pitch bytes apart, over its integer ROI; words land at out_bits + seg_off[b] (the
- * offsets the caller derives from the ROIs: nrows * ceil(ncols / 32) words per box). */
+ * offsets the caller derives from the ROIs: nrows * ceil(ncols / 32) words per box).
+ * `masks` may also be PINNED host memory (mapped into the device's address space under unified
+ * addressing): the kernel then reads the ROI bytes over PCIe and no copy is needed. */
 int wcr_pack_box_masks(const uint8_t *masks, int64_t mask_stride, int mask_pitch,
                        const int32_t *mask_idx, const WcrImage *images, const WcrBox *boxes,
                        int n_boxes, const int64_t *seg_off, uint32_t *out_bits, void *stream);
