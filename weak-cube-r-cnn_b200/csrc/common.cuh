@@ -80,4 +80,29 @@ __host__ __device__ inline float u01(uint32_t x) { return ((x >> 8) + 1) * (1.0f
 
 __device__ __forceinline__ float nanf_() { return __int_as_float(0x7fc00000); }
 
+// ---- packed FP32 (Blackwell FFMA2): two independent IEEE fma.rn per instruction --------------
+typedef unsigned long long u64;
+__device__ __forceinline__ u64 pack2(float lo, float hi)
+{
+    u64 r;
+    asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi));
+    return r;
+}
+__device__ __forceinline__ void unpack2(u64 v, float &lo, float &hi)
+{
+    asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v));
+}
+__device__ __forceinline__ u64 ffma2(u64 a, u64 b, u64 c)
+{
+    u64 r;
+    asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(a), "l"(b), "l"(c));
+    return r;
+}
+__device__ __forceinline__ u64 fadd2(u64 a, u64 b)
+{
+    u64 r;
+    asm("add.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
+    return r;
+}
+
 }  // namespace wcr

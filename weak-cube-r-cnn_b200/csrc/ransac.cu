@@ -19,7 +19,7 @@ namespace wcr {
 constexpr int RANSAC_TPB = 128;    // threads per CTA
 constexpr int RANSAC_HPT = 4;      // hypotheses per thread (registers)
 constexpr int RANSAC_HPB = RANSAC_TPB * RANSAC_HPT;
-constexpr int RANSAC_TILE = 1024;  // points per CTA (one 16 KB shared-memory tile)
+constexpr int RANSAC_TILE = 1024;  // points per CTA (one 24 KB shared-memory tile, coordinates doubled)
 
 __device__ __forceinline__ float cross_c(float a1, float b2, float a2, float b1)
 {
@@ -50,16 +50,23 @@ __device__ __forceinline__ void philox_triple(uint64_t seed, uint32_t image, uin
 __global__ void __launch_bounds__(RANSAC_TPB)
 ransac_count_kernel(const float4 *__restrict__ pts, const int *__restrict__ count, int cap,
                     const int32_t *__restrict__ sample_idx, int iters, float thresh,
-                    uint64_t seed, float4 *__restrict__ eqs, int *__restrict__ out_counts)
+                    uint64_t seed, float4 *__restrict__ eqs, int *__restrict__ out_counts,
+                    float k_one, float k_negzero)
 {
-    __shared__ float4 tile[RANSAC_TILE];
+    // coordinates stored twice, (x,x,y,y) and (z,z): the 64-bit operands of the packed test below
+    __shared__ float4 tile_xy[RANSAC_TILE];
+    __shared__ float2 tile_z[RANSAC_TILE];
     const int img = blockIdx.y;
     const int n = count[img];
     const int base = blockIdx.z * RANSAC_TILE;
     if (base >= n && !(blockIdx.z == 0)) return;  // tile 0 always runs: it publishes the planes
     const float4 *P = pts + (size_t)img * cap;
     const int m = max(0, min(RANSAC_TILE, n - base));
-    for (int j = threadIdx.x; j < m; j += RANSAC_TPB) tile[j] = P[base + j];
+    for (int j = threadIdx.x; j < m; j += RANSAC_TPB) {
+        const float4 p = P[base + j];
+        tile_xy[j] = make_float4(p.x, p.x, p.y, p.y);
+        tile_z[j] = make_float2(p.z, p.z);
+    }
 
     float a[RANSAC_HPT], b[RANSAC_HPT], c[RANSAC_HPT], d[RANSAC_HPT], den[RANSAC_HPT];
     bool live[RANSAC_HPT];
@@ -97,28 +104,71 @@ ransac_count_kernel(const float4 *__restrict__ pts, const int *__restrict__ coun
     float cnt[RANSAC_HPT];
 #pragma unroll
     for (int t = 0; t < RANSAC_HPT; ++t) cnt[t] = 0.f;
-    // x / 1.0f == x exactly: the IEEE division is skipped when the denominator is 1
-    // (it nearly always is, the normal was just normalised)
-    bool unit = true;
+    // The reference tests fl(|dist| / den) <= thresh with den = |normal| ~ 1 (plane.py:118-121).
+    // x -> fl(x / den) is monotone (den > 0, round to nearest), so there is a largest float T with
+    // fl(T / den) <= thresh, and |dist| <= T decides EXACTLY like the division does. T is found once
+    // per hypothesis (start at fl(thresh * den), walk a few ulps); the per-point test then costs
+    // 3 FMUL + 3 FADD + FSET + FADD instead of an IEEE division on top. A hypothesis whose walk does
+    // not settle (den infinite or not positive) keeps the division.
+    float thr[RANSAC_HPT];
+    bool fast = true;
 #pragma unroll
-    for (int t = 0; t < RANSAC_HPT; ++t) unit = unit && den[t] == 1.0f;
-    if (unit) {
+    for (int t = 0; t < RANSAC_HPT; ++t) {
+        float g = thresh * den[t];
+        bool ok = den[t] > 0.f && den[t] < 3.0e38f && g > 0.f && g < 3.0e38f;
+        if (ok) {
+            int it = 0;
+            while (it < 8 && g / den[t] > thresh) { g = __int_as_float(__float_as_int(g) - 1); ++it; }
+            while (it < 16) {
+                const float up = __int_as_float(__float_as_int(g) + 1);
+                if (!(up / den[t] <= thresh)) break;
+                g = up; ++it;
+            }
+            ok = it < 16 && g / den[t] <= thresh;
+        }
+        thr[t] = g;
+        // NaN den <=> NaN normal <=> NaN dist: never an inlier on either path
+        fast = fast && (ok || den[t] != den[t]);
+    }
+    if (fast) {
+        // Two hypotheses per FFMA2. A product is fma(a, x, -0) and a sum fma(s, 1, t): both round
+        // once, exactly like FMUL / FADD (x*1 is exact; p + -0 == p for every p incl. signed
+        // zeros), so the chain keeps the reference's roundings at 3.25 issue slots per test
+        // instead of 8. The constants arrive as kernel arguments so that ptxas cannot fold the
+        // fma back into mul/add (it expands mul.rn.f32x2 / add.rn.f32x2 to scalar code).
+        const u64 ONE = pack2(k_one, k_one), NZ = pack2(k_negzero, k_negzero);
+        u64 A[RANSAC_HPT / 2], B[RANSAC_HPT / 2], C[RANSAC_HPT / 2], D[RANSAC_HPT / 2], CNT[RANSAC_HPT / 2];
+#pragma unroll
+        for (int q = 0; q < RANSAC_HPT / 2; ++q) {
+            A[q] = pack2(a[2 * q], a[2 * q + 1]); B[q] = pack2(b[2 * q], b[2 * q + 1]);
+            C[q] = pack2(c[2 * q], c[2 * q + 1]); D[q] = pack2(d[2 * q], d[2 * q + 1]);
+            CNT[q] = pack2(0.f, 0.f);
+        }
 #pragma unroll 8
         for (int j = 0; j < m; ++j) {
-            const float4 p = tile[j];
+            const float4 xy = tile_xy[j];
+            const float2 zz = tile_z[j];
+            const u64 X = pack2(xy.x, xy.y), Y = pack2(xy.z, xy.w), Z = pack2(zz.x, zz.y);
 #pragma unroll
-            for (int t = 0; t < RANSAC_HPT; ++t) {
-                const float dist = ((a[t] * p.x + b[t] * p.y) + c[t] * p.z) + d[t];
-                cnt[t] += (fabsf(dist) <= thresh) ? 1.f : 0.f;
+            for (int q = 0; q < RANSAC_HPT / 2; ++q) {
+                const u64 m1 = ffma2(A[q], X, NZ), m2 = ffma2(B[q], Y, NZ), m3 = ffma2(C[q], Z, NZ);
+                const u64 ds = ffma2(ffma2(ffma2(m1, ONE, m2), ONE, m3), ONE, D[q]);
+                float d0, d1;
+                unpack2(ds, d0, d1);
+                const float i0 = (fabsf(d0) <= thr[2 * q]) ? 1.f : 0.f;
+                const float i1 = (fabsf(d1) <= thr[2 * q + 1]) ? 1.f : 0.f;
+                CNT[q] = ffma2(pack2(i0, i1), ONE, CNT[q]);
             }
         }
+#pragma unroll
+        for (int q = 0; q < RANSAC_HPT / 2; ++q) unpack2(CNT[q], cnt[2 * q], cnt[2 * q + 1]);
     } else {
 #pragma unroll 4
         for (int j = 0; j < m; ++j) {
-            const float4 p = tile[j];
+            const float px = tile_xy[j].x, py = tile_xy[j].z, pz = tile_z[j].x;
 #pragma unroll
             for (int t = 0; t < RANSAC_HPT; ++t) {
-                const float dist = (((a[t] * p.x + b[t] * p.y) + c[t] * p.z) + d[t]) / den[t];
+                const float dist = (((a[t] * px + b[t] * py) + c[t] * pz) + d[t]) / den[t];
                 cnt[t] += (fabsf(dist) <= thresh) ? 1.f : 0.f;
             }
         }
@@ -210,7 +260,7 @@ extern "C" int wcr_ransac_ground(const float *pts, const int *count, int cap, in
               (cap + wcr::RANSAC_TILE - 1) / wcr::RANSAC_TILE);
     wcr::ransac_count_kernel<<<grid, wcr::RANSAC_TPB, 0, (cudaStream_t)stream>>>(
         (const float4 *)pts, count, cap, sample_idx, iters, thresh, seed, (float4 *)ws_eqs,
-        out_counts);
+        out_counts, 1.0f, -0.0f);
     WCR_CHECK_LAUNCH("ransac_count_kernel");
     wcr::ransac_select_kernel<<<n_images, 256, 0, (cudaStream_t)stream>>>(
         (const float4 *)pts, count, cap, (const float4 *)ws_eqs, out_counts, iters, thresh,
@@ -287,7 +337,7 @@ extern "C" int wcr_ransac_ground_static(const float *pts, const int *count, int 
     dim3 grid((iters + wcr::RANSAC_HPB - 1) / wcr::RANSAC_HPB, n_images,
               (cap + wcr::RANSAC_TILE - 1) / wcr::RANSAC_TILE);
     wcr::ransac_count_kernel<<<grid, wcr::RANSAC_TPB, 0, (cudaStream_t)stream>>>(
-        (const float4 *)pts, count, cap, sample_idx, iters, thresh, seed, eqs, out_counts);
+        (const float4 *)pts, count, cap, sample_idx, iters, thresh, seed, eqs, out_counts, 1.0f, -0.0f);
     WCR_CHECK_LAUNCH("ransac_count_kernel");
     wcr::ransac_select_kernel<<<n_images, 256, 0, (cudaStream_t)stream>>>(
         (const float4 *)pts, count, cap, eqs, out_counts, iters, thresh,

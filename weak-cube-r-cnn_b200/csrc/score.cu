@@ -35,30 +35,6 @@ constexpr int SC_ITEM_PX = 4096;               // target depth pixels per item (
 constexpr int SC_ITEM_PX_MIN = 512;            // ... shrunk for small shards so every SM gets items
 constexpr int SC_MAX_CHUNKS = 64;
 
-typedef unsigned long long u64;
-__device__ __forceinline__ u64 pack2(float lo, float hi)
-{
-    u64 r;
-    asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi));
-    return r;
-}
-__device__ __forceinline__ void unpack2(u64 v, float &lo, float &hi)
-{
-    asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v));
-}
-// Blackwell packed FP32: two independent IEEE fma.rn per instruction (FFMA2).
-__device__ __forceinline__ u64 ffma2(u64 a, u64 b, u64 c)
-{
-    u64 r;
-    asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(a), "l"(b), "l"(c));
-    return r;
-}
-__device__ __forceinline__ u64 fadd2(u64 a, u64 b)
-{
-    u64 r;
-    asm("add.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
-    return r;
-}
 // Read-once global data (depth pixels, cube parameters): keep it out of L1 so that the
 // box mask the hull fill re-reads stays resident.
 __device__ __forceinline__ float ld_stream(const float *p)
