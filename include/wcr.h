@@ -160,7 +160,12 @@ typedef struct WcrScoreParams {
     int32_t seg_eval;       /* mask term: 0 = the library decides, 1 = fill every hull, 2 = on demand
                                (only where on demand is valid, see wcr_score_topk); results are
                                identical, only the time differs */
-    int32_t reserved2;
+    int32_t pts_eval;       /* point term: 0 = the library decides, 1 = test every proposal against the
+                               depth points, 2 = on demand: proposals whose score BOUND (IoU term x
+                               share of the ROI's points their cull box can hold) is below the k-th
+                               best score already known are never tested (only where valid, see
+                               wcr_score_topk); results are identical, only the time differs.
+                               (Was `reserved2`, which had to be 0.) */
 } WcrScoreParams;
 
 #define WCR_CUBE_FLOATS   15   /* [cx cy cz w h l R(9 row-major)], spaces.py:130-150 */

@@ -396,6 +396,50 @@ def test_score_seg_on_demand_equals_full_evaluation(cuda_lib, N, k, e_pts, e_seg
     assert torch.equal(torch.gather(full["scores"], 1, idx), rec_full[:, :, 1])
 
 
+@pytest.mark.parametrize("N,k,e_pts,e_seg,e_iou", [(300, 16, 1, 1, 1), (1000, 16, 1, 1, 1), (1000, 16, 1, 0, 1),
+                                                   (1500, 32, 1, 2, 1), (100, 4, 1, 0, 1), (700, 8, 2, 1, 0),
+                                                   (2500, 1, 2, 0, 1), (1000, 16, 1, 1, 2)])
+def test_score_pts_on_demand_equals_every_proposal(cuda_lib, N, k, e_pts, e_seg, e_iou):
+    """pts_eval=2: the tiles are walked twice; the second pass skips every proposal whose score bound
+    (IoU factor x share of the ROI's points its cull box can reach) is below the k-th best score of
+    the first pass (chunk_epilogue_first). The records must be those of pts_eval=1 (every proposal
+    tested) and of the full evaluation with per-proposal outputs, bit for bit, with and without the
+    mask term, for one and several chunks, chunks shorter than the first pass, k = 1 .. 32."""
+    from wcr import synth
+    from wcr.proposals import propose, score_topk, ScoreConfig, SegMasks
+    H, W = 240, 320
+    ims, shard, boxes, priors, normals = _setup(3, H, W, n_boxes=4, first=51)
+    seg = None
+    if e_seg:
+        masks = [m for im in ims for m in synth.seg_masks(im["boxes"], H, W)]
+        seg = SegMasks(shard, boxes, masks)
+    cubes = propose(shard, boxes, priors, normals, N, seed=21)
+    cubes[5, ::3, 0:3] *= 6.0                  # a box where a third of the proposals hold no point
+    cubes[7, :, 0:3] *= 6.0                    # ... and one where none does (T = 0: nothing may be pruned)
+    cubes[2, 5, 6:15] *= 1.01                  # a cube the cull does not apply to (bound = every point)
+    cubes[2, 7, 3] = float("nan")
+    cfg = dict(e_iou=e_iou, e_pts=e_pts, e_seg=e_seg, k=k)
+    full = score_topk(shard, boxes, cubes, cfg=ScoreConfig(**cfg), seg=seg, want_all=True)
+    rec_full = full["records"].clone()
+    every = score_topk(shard, boxes, cubes, cfg=ScoreConfig(pts_eval=1, **cfg), seg=seg)
+    assert every["workspace"].proposals_pruned() == 0
+    assert torch.equal(every["records"].view(torch.int32), rec_full.view(torch.int32))
+    lazy = score_topk(shard, boxes, cubes, cfg=ScoreConfig(pts_eval=2, seg_eval=2, **cfg), seg=seg)
+    assert torch.equal(lazy["records"].view(torch.int32), rec_full.view(torch.int32))
+    pruned = lazy["workspace"].proposals_pruned()
+    if N > 128:
+        assert 0 < pruned < cubes.shape[0] * N, pruned
+    else:
+        assert pruned == 0
+    # sampled in-kernel (no cube array): same equality, and the library's own choice of mode
+    a = score_topk(shard, boxes, None, N, ScoreConfig(pts_eval=1, **cfg), priors=priors, normals=normals, seed=9, seg=seg)
+    ra = a["records"].clone()
+    for mode in (2, 0):
+        bq = score_topk(shard, boxes, None, N, ScoreConfig(pts_eval=mode, **cfg), priors=priors, normals=normals,
+                        seed=9, seg=seg)
+        assert torch.equal(bq["records"].view(torch.int32), ra.view(torch.int32)), mode
+
+
 def test_score_custom_mapping_shaping(cuda_lib):
     """ScoreConfig.map_beta > 0 passes every term through custom_mapping (utils.py:207-223) before
     its exponent. Scores within 1e-5 of the composition of the oracle's terms with

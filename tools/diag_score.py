@@ -7,7 +7,8 @@ from wcr import _abi
 for a_ in sys.argv[1:]:
     if a_.startswith("--lib="):
         _abi.LIB_PATH = _abi.LIB_PATH.replace("libwcr_b200.so", a_[6:])
-sys.argv = [sys.argv[0]] + [a_ for a_ in sys.argv[1:] if not a_.startswith("--lib=")]
+PTS_ONLY = "--pts-only" in sys.argv
+sys.argv = [sys.argv[0]] + [a_ for a_ in sys.argv[1:] if not a_.startswith("--")]
 import bench
 from wcr import synth
 from wcr.pipeline import ShardRunner
@@ -34,6 +35,35 @@ def run(cfg, want_all=False, seg=True):
                       seg=r.seg if seg else None, workspace=r.ws, want_all=want_all)
 
 res = {}
+for pe in (1, 2):
+    t, out = timed(lambda: run(ScoreConfig(k=16, e_seg=1, pts_eval=pe)))
+    res[f"seg_pts_eval{pe}_ms"] = t; res[f"seg_pts_eval{pe}_pruned"] = out["workspace"].proposals_pruned()
+    res[f"seg_pts_eval{pe}_hulls"] = out["workspace"].hulls_filled(); res[f"seg_pts_eval{pe}_tests"] = out["workspace"].executed_tests()
+    t, out = timed(lambda: run(ScoreConfig(k=16, e_seg=0, pts_eval=pe), seg=False))
+    res[f"noseg_pts_eval{pe}_ms"] = t; res[f"noseg_pts_eval{pe}_pruned"] = out["workspace"].proposals_pruned()
+    res[f"noseg_pts_eval{pe}_tests"] = out["workspace"].executed_tests()
+a_ = run(ScoreConfig(k=16, e_seg=1, pts_eval=1))["records"].clone()
+b_ = run(ScoreConfig(k=16, e_seg=1, pts_eval=2))["records"].clone()
+res["seg_records_equal"] = bool(torch.equal(a_.view(torch.int32), b_.view(torch.int32)))
+a_ = run(ScoreConfig(k=16, e_seg=0, pts_eval=1), seg=False)["records"].clone()
+b_ = run(ScoreConfig(k=16, e_seg=0, pts_eval=2), seg=False)["records"].clone()
+res["noseg_records_equal"] = bool(torch.equal(a_.view(torch.int32), b_.view(torch.int32)))
+def phases(ws):
+    v = ws.ws[64:64 + 8 * 13].view(torch.int64).tolist()
+    d = dict(zip(["tiles_pass1", "tiles_pass2", "epilogue_first", "epilogue_final", "seg_batches", "wait_ready",
+                  "claim_decode", "retire", "tail", "lost_race"], v))
+    d = {k: round(x / (444 * 4 * 1.92e6), 3) for k, x in d.items()}   # ms per warp at 1.92 GHz, 1776 warps
+    d["kernel_ms(last exit - first start)"] = round((v[10] - v[12]) / 1e6, 3)
+    d["mean_warp_lifetime_ms"] = round(v[11] / 1776 / 1e6, 3)
+    return d
+if "prof" in _abi.LIB_PATH:
+    for pe in (1, 2):
+        out = run(ScoreConfig(k=16, e_seg=1, pts_eval=pe)); torch.cuda.synchronize()
+        res[f"seg_pts_eval{pe}_cycles"] = phases(out["workspace"])
+        out = run(ScoreConfig(k=16, e_seg=0, pts_eval=pe), seg=False); torch.cuda.synchronize()
+        res[f"noseg_pts_eval{pe}_cycles"] = phases(out["workspace"])
+if PTS_ONLY:
+    print(json.dumps(res)); sys.exit(0)
 t, out = timed(lambda: run(ScoreConfig(k=16, e_seg=1, seg_eval=2)))
 res["seg_on_demand_ms"] = t; res["hulls_on_demand"] = out["workspace"].hulls_filled()
 t, out = timed(lambda: run(ScoreConfig(k=16, e_seg=1, seg_eval=1)))

@@ -16,10 +16,11 @@ from wcr.proposals import ScoreConfig
 from wcr.ground import unproject_cloud
 
 seg = "--no-seg" not in sys.argv
+pts_eval = next((int(a_[6:]) for a_ in sys.argv[1:] if a_.startswith("--pts=")), 0)
 n_img = 1 if "--small" in sys.argv else 64
 ims = bench.make_images(n_img, 0, seg, 5 if n_img == 1 else None, dense=False)
 r = ShardRunner(ims, 1000, "cuda", priors=synth.make_priors(),
-                score_cfg=ScoreConfig(k=16, e_seg=1 if seg else 0), seed=1234)
+                score_cfg=ScoreConfig(k=16, e_seg=1 if seg else 0, pts_eval=pts_eval), seed=1234)
 r.upload()
 for _ in range(3):
     r.step()

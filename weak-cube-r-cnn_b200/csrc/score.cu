@@ -101,6 +101,8 @@ struct ScoreWs {
     unsigned long long *executed;  // [1] at byte 8: point tests issued (tile path, after culling)
     unsigned long long *hulls;     // [1] at byte 16: hulls filled for the mask term
     int *dynq;           // [3] at byte 24: dynamic hull-batch queue head, tail, chunks through phase A
+    int *queue_b;        // [1] at byte 36: next second-pass tile item (point term on demand)
+    unsigned long long *pruned;    // [1] at byte 40: proposals never tested against the depth points
     int *segq;           // [n_boxes * n_chunks * 32] published batches (code + 1; 0 = not yet written)
     int *seg_pending;    // [n_boxes][n_chunks] retired batches per chunk
     int *ncand;          // [n_boxes][n_chunks] candidates per chunk
@@ -119,6 +121,14 @@ struct ScoreWs {
     float2 *zgrid;       // [n_boxes][256] depth range of the ROI's 16 x 16 cells (tile path)
     uint8_t *mayhit;     // [n_boxes][N] 0: the proposal provably holds no point (tile path)
     float *siou;         // [n_boxes][N] IoU term, written by score_prep_kernel
+    // point term on demand (a.pts_lazy)
+    int *zcnt;           // [n_boxes][256] valid depth points of the ROI's 16 x 16 cells
+    int *ubcnt;          // [n_boxes][N] upper bound of the inside-count (points of the cells the cube can reach)
+    float *okey;         // [n_boxes][N] ordering key: IoU factor x bound factor
+    uint16_t *order;     // [n_boxes][n_chunks][SC_CHUNK] chunk proposals by descending key; the first
+                         //   pass tests [0, pa), its epilogue compacts the survivors of the rest behind them
+    int *done_b;         // [n_boxes][n_chunks] retired second-pass items
+    int *bready;         // [n_boxes][n_chunks] 0: first pass running; else 1 + survivors of the second pass
 };
 
 struct ScoreArgs {
@@ -136,6 +146,8 @@ struct ScoreArgs {
     int ps;              // tile path: proposals per tile item (power of two, 128 .. SC_CHUNK)
     int seg_lazy;        // tile path: mask term evaluated on demand by the epilogues (no seg items)
     int siou_ready;      // tile path: ws.siou holds every proposal's IoU term (written by score_prep_kernel)
+    int pts_lazy;        // tile path: point term on demand (two passes over the tiles, see chunk_epilogue_first)
+    int pa;              // ... proposals per chunk tested in the first pass (multiple of 32)
     ScoreWs ws;
     float *records;
     float *out_scores, *out_iou;
@@ -210,13 +222,15 @@ size_t carve(void *base, int n_boxes, int N, int k, bool need_cubes, bool need_s
     char *p = (char *)base;
     size_t off = 0;
     auto take = [&](size_t bytes) { char *q = p ? p + off : nullptr; off += align256(bytes); return q; };
-    int *queue = (int *)take(sizeof(int));
+    int *queue = (int *)take(256);  // header: queues and counters, see ScoreWs (+ phase cycles at byte 64, profiling build)
     int *done_chunk = (int *)take((size_t)n_boxes * nc * sizeof(int));
     int *done_box = (int *)take((size_t)n_boxes * sizeof(int));
     int *npts = (int *)take((size_t)n_boxes * nc * sizeof(int));
     int *count = (int *)take((size_t)n_boxes * N * sizeof(int));
     int *segq = (int *)take(need_seg ? (size_t)n_boxes * nc * 32 * sizeof(int) : 0);
     int *seg_pending = (int *)take(need_seg ? (size_t)n_boxes * nc * sizeof(int) : 0);
+    int *done_b = (int *)take((size_t)n_boxes * nc * sizeof(int));
+    int *bready = (int *)take((size_t)n_boxes * nc * sizeof(int));
     if (zero_bytes) *zero_bytes = off;
     int *ncand = (int *)take(need_seg ? (size_t)n_boxes * nc * sizeof(int) : 0);
     uint16_t *candlist = (uint16_t *)take(need_seg ? (size_t)n_boxes * nc * wcr::SC_CHUNK * sizeof(uint16_t) : 0);
@@ -230,7 +244,14 @@ size_t carve(void *base, int n_boxes, int N, int k, bool need_cubes, bool need_s
     float2 *zgrid = (float2 *)take((size_t)n_boxes * 256 * sizeof(float2));
     uint8_t *mayhit = (uint8_t *)take((size_t)n_boxes * N);
     float *siou = (float *)take((size_t)n_boxes * N * sizeof(float));
+    int *zcnt = (int *)take((size_t)n_boxes * 256 * sizeof(int));
+    int *ubcnt = (int *)take((size_t)n_boxes * N * sizeof(int));
+    float *okey = (float *)take((size_t)n_boxes * N * sizeof(float));
+    uint16_t *order = (uint16_t *)take((size_t)n_boxes * nc * wcr::SC_CHUNK * sizeof(uint16_t));
     if (ws) {
+        ws->zcnt = zcnt; ws->ubcnt = ubcnt; ws->okey = okey; ws->order = order; ws->done_b = done_b; ws->bready = bready;
+        ws->queue_b = (int *)(queue ? (char *)queue + 36 : nullptr);
+        ws->pruned = (unsigned long long *)(queue ? (char *)queue + 40 : nullptr);
         ws->segcnt = segcnt; ws->params = params; ws->cullbox = cullbox; ws->zgrid = zgrid; ws->mayhit = mayhit; ws->siou = siou;
         ws->queue = queue; ws->executed = (unsigned long long *)(queue ? (char *)queue + 8 : nullptr);
         ws->hulls = (unsigned long long *)(queue ? (char *)queue + 16 : nullptr);
@@ -273,6 +294,7 @@ extern "C" int wcr_score_topk(const WcrImage *images, const WcrBox *boxes, int n
     WCR_REQUIRE(h_score->e_iou >= 0 && h_score->e_pts >= 0 && h_score->e_seg >= 0,
                 "wcr_score_topk: negative exponent");
     WCR_REQUIRE(h_score->seg_eval >= 0 && h_score->seg_eval <= 2, "wcr_score_topk: seg_eval must be 0, 1 or 2");
+    WCR_REQUIRE(h_score->pts_eval >= 0 && h_score->pts_eval <= 2, "wcr_score_topk: pts_eval must be 0, 1 or 2");
     WCR_REQUIRE(h_score->map_beta >= 0.f, "wcr_score_topk: map_beta must be >= 0 (0 = no shaping)");
     WCR_REQUIRE(h_score->e_seg == 0 || (seg_bits && seg_off),
                 "wcr_score_topk: e_seg > 0 needs seg_bits and seg_off");
@@ -295,13 +317,16 @@ extern "C" int wcr_score_topk(const WcrImage *images, const WcrBox *boxes, int n
 #endif
     cudaError_t e = cudaMemsetAsync(ws, 0, zero_bytes, st);
     if (e != cudaSuccess) { wcr::set_error("cudaMemsetAsync: %s", cudaGetErrorString(e)); return WCR_ELAUNCH; }
+#ifdef WCR_PROFILE_PHASES
+    cudaMemsetAsync((char *)ws + 64 + 12 * 8, 0xff, 8, st);   // earliest start: atomicMin
+#endif
     a.images = images; a.boxes = boxes; a.n_boxes = n_boxes; a.cubes = cubes; a.N = N;
     a.sc = *h_score; a.k = k;
     a.n_chunks = nc; a.records = out_records;
     a.out_scores = out_scores; a.out_iou = out_iou; a.out_count = out_count;
     a.out_proj = out_proj; a.out_npts = out_npts;
     a.seg_bits = seg_bits; a.seg_off = seg_off; a.out_seg = out_seg;
-    a.item_px = 0; a.grp = 8; a.ps = wcr::SC_CHUNK; a.seg_lazy = 0; a.siou_ready = 0;
+    a.item_px = 0; a.grp = 8; a.ps = wcr::SC_CHUNK; a.seg_lazy = 0; a.siou_ready = 0; a.pts_lazy = 0; a.pa = 128;
     const int sms = wcr::sm_count();
     WCR_REQUIRE((N + 255) / 256 <= 65535, "wcr_score_topk: N too large");
     a.src.cubes = cubes; a.src.priors = priors; a.src.normals = normals; a.src.z0 = z0;
@@ -329,37 +354,51 @@ extern "C" int wcr_score_topk(const WcrImage *images, const WcrBox *boxes, int n
         return WCR_OK;
     }
 #else
-    {   // proposals per tile item: the whole chunk when the shard has enough tiles for every
-        // resident warp (a box has ~30 tiles), finer for small shards
-        const long long bc = (long long)n_boxes * nc, want = 4LL * sms_resident_warps();
-        int ps = wcr::SC_CHUNK;
-        while (ps > 128 && bc * 32 * (wcr::SC_CHUNK / ps) < want) ps >>= 1;
-        a.ps = ps;
-    }
-    wcr::score_plan_tiles_kernel<<<1, 1024, 0, st>>>(images, boxes, n_boxes, nc, h_score->point_stride,
-                                                     h_score->e_pts > 0, 0, a.grp, wcr::SC_CHUNK / a.ps,
-                                                     a.ws.item_prefix);
-    WCR_CHECK_LAUNCH("score_plan_tiles_kernel");
     // Mask term on demand (chunk_epilogue_warp): valid when the ratio is bounded by 1 (mask_iou;
     // mod_mask_iou = inter^5 / union is not) and nobody asked for per-proposal scores or ratios.
     a.seg_lazy = h_score->e_seg > 0 && h_score->seg_mode == 0 && out_seg == nullptr && out_scores == nullptr;
     // Mask term on demand needs enough (box, chunk) pairs to hide the two dependent phases of a
     // chunk behind other chunks' work; a small shard fills every hull through the parallel seg
     // items instead. seg_eval: 0 = decide here, 1 = every hull, 2 = on demand.
-    if (a.seg_lazy && h_score->seg_eval != 2)
-        a.seg_lazy = h_score->seg_eval == 0 && (long long)n_boxes * nc >= sms_resident_warps() / 4;   // measured: 4.23 vs 4.51 ms at 486 chunks, 1.37 vs 0.90 ms at 64
+    const bool many_chunks = (long long)n_boxes * nc >= sms_resident_warps() / 4;   // measured: 4.23 vs 4.51 ms at 486 chunks, 1.37 vs 0.90 ms at 64
+    if (a.seg_lazy && h_score->seg_eval != 2) a.seg_lazy = h_score->seg_eval == 0 && many_chunks;
     // per-proposal IoU term in the prep kernel unless per-proposal outputs want the projected box
     a.siou_ready = !(out_scores || out_iou || out_seg || out_count || out_proj);
+    // Point term on demand (chunk_epilogue_first): the score is bounded by the IoU factor times the
+    // share of the ROI's points the cube's cull box can reach, every other factor being <= 1. Valid
+    // when nobody wants per-proposal outputs, the terms are not reshaped (custom_mapping goes
+    // through pow(): monotone only up to an ulp) and the mask ratio, if any, is bounded by 1.
+    a.pts_lazy = h_score->e_pts > 0 && a.siou_ready && h_score->map_beta == 0.f &&
+                 (h_score->e_seg == 0 || a.seg_lazy) && h_score->pts_eval != 1 &&
+                 (h_score->pts_eval == 2 || many_chunks);
+    {   // proposals per tile item: the whole chunk when the shard has enough tiles for every
+        // resident warp (a box has ~30 tiles), finer for small shards
+        const long long bc = (long long)n_boxes * nc, want = 4LL * sms_resident_warps();
+        int ps = wcr::SC_CHUNK;
+        while (!a.pts_lazy && ps > 128 && bc * 32 * (wcr::SC_CHUNK / ps) < want) ps >>= 1;
+        a.ps = ps;
+    }
+    wcr::score_plan_tiles_kernel<<<1, 1024, 0, st>>>(images, boxes, n_boxes, nc, h_score->point_stride,
+                                                     h_score->e_pts > 0, 0, a.grp, wcr::SC_CHUNK / a.ps,
+                                                     a.ws.item_prefix);
+    WCR_CHECK_LAUNCH("score_plan_tiles_kernel");
     if (h_score->e_pts > 0) {
-        wcr::score_zgrid_kernel<<<dim3(n_boxes, 8), 1024, 0, st>>>(images, boxes, h_score->point_stride, 1, a.ws.zgrid);
+        wcr::score_zgrid_kernel<<<dim3(n_boxes, 8), 1024, 0, st>>>(images, boxes, h_score->point_stride, 1, a.ws.zgrid,
+                                                                   a.pts_lazy ? a.ws.zcnt : nullptr);
         WCR_CHECK_LAUNCH("score_zgrid_kernel");
     }
     if (h_score->e_pts > 0 || a.siou_ready) {
         const dim3 grid(n_boxes, (N + 255) / 256);
         wcr::score_prep_kernel<<<grid, 256, 0, st>>>(images, boxes, n_boxes, a.src, N,
                                                       h_score->point_stride, h_score->e_pts > 0, a.ws.params, a.ws.cullbox,
-                                                      a.ws.zgrid, a.ws.mayhit, a.siou_ready ? a.ws.siou : nullptr);
+                                                      a.ws.zgrid, a.ws.mayhit, a.siou_ready ? a.ws.siou : nullptr,
+                                                      a.pts_lazy ? a.ws.zcnt : nullptr, a.ws.ubcnt, a.ws.okey,
+                                                      h_score->e_iou, h_score->e_pts);
         WCR_CHECK_LAUNCH("score_prep_kernel");
+    }
+    if (a.pts_lazy) {
+        wcr::score_order_kernel<<<n_boxes * nc, 1024, 0, st>>>(a.ws.okey, N, nc, a.ws.order);
+        WCR_CHECK_LAUNCH("score_order_kernel");
     }
     // FFMA2 point test, inside indicator on the integer pipe, 3 CTAs x 4 warps per SM
     wcr::score_tiles_kernel<4, 3, 8, true, true><<<sms * 3, 128, 0, st>>>(a);

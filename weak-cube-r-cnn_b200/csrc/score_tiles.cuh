@@ -89,7 +89,7 @@ struct __align__(16) PParam {
 // parallelism has to come from inside the box).
 __global__ void __launch_bounds__(1024)
 score_zgrid_kernel(const WcrImage *__restrict__ images, const WcrBox *__restrict__ boxes, int stride,
-                   int use_pts, float2 *__restrict__ zgrid)
+                   int use_pts, float2 *__restrict__ zgrid, int *__restrict__ zcnt)
 {
     const int b = blockIdx.x, cell = blockIdx.y * 32 + (threadIdx.x >> 5), lane = threadIdx.x & 31;
     const int cy = cell >> 4, cx = cell & 15;
@@ -99,20 +99,25 @@ score_zgrid_kernel(const WcrImage *__restrict__ images, const WcrBox *__restrict
     const int cw = max(1, (roi.ncols + 15) >> 4), chh = max(1, (roi.nrows + 15) >> 4);
     const int r0 = cy * chh, r1 = min(r0 + chh, roi.nrows), c0 = cx * cw, c1 = min(c0 + cw, roi.ncols);
     float mn = INFINITY, mx = -INFINITY;
+    int nv = 0;   // valid points of the cell: the validity rule of tile_item
     if (r1 > r0 && c1 > c0) {
         const int w = c1 - c0, n = (r1 - r0) * w;
         for (int i = lane; i < n; i += 32) {
             const int r = r0 + i / w, c = c0 + i % w;
             const float d = __ldg(im.depth + (size_t)(roi.v0 + r * stride) * im.depth_pitch + roi.u0 + c * stride);
-            if (d > 0.f && d <= 3.402823466e38f) { mn = fminf(mn, d); mx = fmaxf(mx, d); }
+            if (d > 0.f && d <= 3.402823466e38f) { mn = fminf(mn, d); mx = fmaxf(mx, d); ++nv; }
         }
     }
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) {
         mn = fminf(mn, __shfl_xor_sync(0xffffffffu, mn, o));
         mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+        nv += __shfl_xor_sync(0xffffffffu, nv, o);
     }
-    if (lane == 0) zgrid[(size_t)b * 256 + cell] = make_float2(mn, mx);
+    if (lane == 0) {
+        zgrid[(size_t)b * 256 + cell] = make_float2(mn, mx);
+        if (zcnt) zcnt[(size_t)b * 256 + cell] = nv;
+    }
 }
 
 // One thread per proposal: test constants (same expressions as score_items_kernel's
@@ -122,7 +127,8 @@ score_prep_kernel(const WcrImage *__restrict__ images, const WcrBox *__restrict_
                   const CubeSrc src, int N, int stride, int use_pts,
                   PParam *__restrict__ out, int4 *__restrict__ out_box,
                   const float2 *__restrict__ zgrid, uint8_t *__restrict__ out_mayhit,
-                  float *__restrict__ out_siou)
+                  float *__restrict__ out_siou, const int *__restrict__ zcnt,
+                  int *__restrict__ out_ubcnt, float *__restrict__ out_key, int e_iou, int e_pts)
 {
     const int j = blockIdx.y * 256 + threadIdx.x, b = blockIdx.x;
     if (j >= N) return;
@@ -141,13 +147,15 @@ score_prep_kernel(const WcrImage *__restrict__ images, const WcrBox *__restrict_
     // the IoU term of the score (corners -> K -> clamp -> min / max -> pairwise_iou), here where
     // every proposal has a thread of its own: the chunk epilogues (ONE warp per 1024 proposals)
     // then only combine it with the point count
+    float siou_j = 1.f;
     if (out_siou) {
         const Intr Kc = {im.fx, im.fy, im.cx, im.cy};
         float lo0, hi0, lo1, hi1;
         clamp_bounds(bx.clamp0, lo0, hi0);
         clamp_bounds(bx.clamp1, lo1, hi1);
         const ProjBox pbx = project_cube(cube, Kc, lo0, hi0, lo1, hi1, nullptr);
-        out_siou[(size_t)b * N + j] = iou_2d(bx.x1, bx.y1, bx.x2, bx.y2, pbx);
+        siou_j = iou_2d(bx.x1, bx.y1, bx.x2, bx.y2, pbx);
+        out_siou[(size_t)b * N + j] = siou_j;
     }
     if (!use_pts) return;     // launched for the IoU term only
     PParam p;
@@ -230,7 +238,25 @@ score_prep_kernel(const WcrImage *__restrict__ images, const WcrBox *__restrict_
     // the ROI cells (16 x 16 grid, score_zgrid_kernel) its cull box overlaps. "No" is a proof that
     // the point count is 0: such a proposal is dead for the tile items and its mask term is lazy.
     bool mayhit = cl <= ch && rl <= rh;
-    if (mayhit && zgrid && ortho) {
+    // Point term on demand: an upper bound of the inside-count = the valid points of the cells the
+    // cube can reach (a point inside the cube lies inside the cull box and the depth range; the cell
+    // that holds it then overlaps both). Cubes the cull does not apply to can hold every point.
+    int ubc = mayhit ? 0x7fffffff : 0;
+    if (mayhit && zgrid && ortho && zcnt) {
+        const int cw = max(1, (roi.ncols + 15) >> 4), chh = max(1, (roi.nrows + 15) >> 4);
+        const float2 *zg = zgrid + (size_t)b * 256;
+        const int *zc = zcnt + (size_t)b * 256;
+        const int cx0 = cl / cw, cx1 = min(15, ch / cw);
+        ubc = 0;
+        for (int cy = rl / chh; cy <= min(15, rh / chh); ++cy) {
+#pragma unroll 4
+            for (int cx = cx0; cx <= cx1; ++cx) {
+                const float2 c = __ldg(zg + cy * 16 + cx);
+                if (!(zhi < c.x || zlo > c.y)) ubc += __ldg(zc + cy * 16 + cx);
+            }
+        }
+        mayhit = ubc > 0;   // an empty cell holds (+inf, -inf): same verdict as the scan below
+    } else if (mayhit && zgrid && ortho) {
         const int cw = max(1, (roi.ncols + 15) >> 4), chh = max(1, (roi.nrows + 15) >> 4);
         const float2 *zg = zgrid + (size_t)b * 256;
         mayhit = false;
@@ -245,10 +271,46 @@ score_prep_kernel(const WcrImage *__restrict__ images, const WcrBox *__restrict_
         }
     }
     if (out_mayhit) out_mayhit[(size_t)b * N + j] = mayhit ? 1 : 0;
+    if (zcnt) {
+        out_ubcnt[(size_t)b * N + j] = ubc;
+        // ordering key of the first pass (the score bound up to the common factor 1 / P_b^e_pts);
+        // only the ORDER it induces is used, the pruning test recomputes the bound exactly
+        out_key[(size_t)b * N + j] = ipow(siou_j, e_iou) * ipow((float)min(ubc, 1 << 24), e_pts);
+    }
     if (!mayhit) { cl = 0xffff; ch = 0; rl = 0xffff; rh = 0; }   // fails every overlap test
     out[(size_t)b * N + j] = p;
     // 16 bytes per proposal: ROI column range, row range (16 bits each, inclusive) and depth range
     out_box[(size_t)b * N + j] = make_int4(cl | (ch << 16), rl | (rh << 16), __float_as_int(zlo), __float_as_int(zhi));
+}
+
+// Point term on demand: the proposals of a (box, chunk) by descending key (ties: lower index
+// first; NaN keys first), one CTA of 1024 threads per chunk, bitonic sort of 64-bit composites
+// (ordered key bits << 16 | 1023 - index) in shared memory. Slots past the chunk's end sort last.
+__global__ void __launch_bounds__(1024)
+score_order_kernel(const float *__restrict__ key, int N, int n_chunks, uint16_t *__restrict__ order)
+{
+    __shared__ unsigned long long s_v[SC_CHUNK];
+    const int bc = blockIdx.x, b = bc / n_chunks, chunk = bc - b * n_chunks, t = threadIdx.x;
+    const int chunk_n = min(SC_CHUNK, N - chunk * SC_CHUNK);
+    unsigned long long v = 0ull;
+    if (t < chunk_n) {
+        unsigned u = __float_as_uint(key[(size_t)b * N + (size_t)chunk * SC_CHUNK + t]);
+        u = (u & 0x80000000u) ? ~u : (u | 0x80000000u);        // monotone map float -> unsigned
+        v = ((unsigned long long)u << 16) | (unsigned)(SC_CHUNK - 1 - t) | (1ull << 48);
+    }
+    s_v[t] = v;
+    __syncthreads();
+    for (int k = 2; k <= SC_CHUNK; k <<= 1)
+        for (int j = k >> 1; j > 0; j >>= 1) {
+            const int p = t ^ j;
+            if (p > t) {
+                const unsigned long long x = s_v[t], y = s_v[p];
+                const bool desc = (t & k) == 0;                 // descending blocks -> descending array
+                if (desc ? x < y : x > y) { s_v[t] = y; s_v[p] = x; }
+            }
+            __syncthreads();
+        }
+    order[(size_t)bc * SC_CHUNK + t] = (uint16_t)(SC_CHUNK - 1 - (int)(s_v[t] & 0xffffu));
 }
 
 // One CTA: queue items per box -> exclusive prefix (tile path).

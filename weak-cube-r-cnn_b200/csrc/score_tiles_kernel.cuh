@@ -30,7 +30,8 @@ __device__ __forceinline__ int add_outside(int acc, float q0, float q1, float q2
 template <int GRP, bool F2, bool ICNT>
 __device__ __forceinline__ void tile_item(const ScoreArgs &a, int b, const WcrImage &im,
                                           const TileGeom &tg, int chunk, int tile, int sub,
-                                          float *wbuf, int lane)
+                                          float *wbuf, int lane,
+                                          const uint16_t *list = nullptr, int n_list = 0, bool count_valid = true)
 {
     constexpr int NG = 32 / GRP;
     const int s = a.sc.point_stride;
@@ -41,13 +42,17 @@ __device__ __forceinline__ void tile_item(const ScoreArgs &a, int b, const WcrIm
     const bool row_ok = my_row < tg.nrows;
     const int v = tg.v0 + my_row * s;
 
+    // the proposals of the item: slots sub * ps .. of the chunk, or (point term on demand) the
+    // n_list chunk-relative indices of `list` (written during this launch: read through L2)
     const int chunk_n = min(SC_CHUNK, a.N - chunk * SC_CHUNK);
-    const int n = min(a.ps, chunk_n - sub * a.ps);
+    const int n = list ? n_list : min(a.ps, chunk_n - sub * a.ps);
     if (n <= 0) return;
-    const size_t first = (size_t)b * a.N + (size_t)chunk * SC_CHUNK + sub * a.ps;
+    const size_t first = (size_t)b * a.N + (size_t)chunk * SC_CHUNK + (list ? 0 : sub * a.ps);
     const PParam *__restrict__ pp = a.ws.params + first;
     const int4 *__restrict__ cbx = a.ws.cullbox + first;
-    int4 bb_next = __ldg(cbx + min(lane, n - 1));
+    int loc_next = min(lane, n - 1);
+    if (list) loc_next = (int)__ldcg(list + loc_next);
+    int4 bb_next = __ldg(cbx + loc_next);
 
     const float *drow = im.depth + (size_t)(row_ok ? v : 0) * im.depth_pitch;
     float4 *av4 = reinterpret_cast<float4 *>(wbuf);          // [8][32]: a_u of registers 4*r4 .. 4*r4+3
@@ -87,7 +92,7 @@ __device__ __forceinline__ void tile_item(const ScoreArgs &a, int b, const WcrIm
         t_zmin = fminf(t_zmin, __shfl_xor_sync(0xffffffffu, t_zmin, o));
         t_zmax = fmaxf(t_zmax, __shfl_xor_sync(0xffffffffu, t_zmax, o));
     }
-    if (sub == 0) {
+    if (sub == 0 && count_valid) {
 #pragma unroll
         for (int o = 16; o > 0; o >>= 1) valid += __shfl_xor_sync(0xffffffffu, valid, o);
         if (lane == 0 && valid) atomicAdd(a.ws.npts + (size_t)b * a.n_chunks + chunk, valid);
@@ -100,8 +105,10 @@ __device__ __forceinline__ void tile_item(const ScoreArgs &a, int b, const WcrIm
 #pragma unroll 1
     for (int base = 0; base < n; base += 32) {
         const int4 bb = bb_next;
-        const int j = base + lane;
-        bb_next = __ldg(cbx + min(j + 32, n - 1));
+        const int j = base + lane, jl = loc_next;   // slot in the item, index in the chunk
+        loc_next = min(j + 32, n - 1);
+        if (list) loc_next = (int)__ldcg(list + loc_next);
+        bb_next = __ldg(cbx + loc_next);
         const int cl = bb.x & 0xffff, ch = (unsigned)bb.x >> 16, rl = bb.y & 0xffff, rh = (unsigned)bb.y >> 16;
         const float zlo = __int_as_float(bb.z), zhi = __int_as_float(bb.w);
         const bool keep = j < n && !(cl > t_c1 || ch < tc0 || rl > t_r1 || rh < tr0) &&
@@ -115,7 +122,7 @@ __device__ __forceinline__ void tile_item(const ScoreArgs &a, int b, const WcrIm
         for (int g = 0; g < NG; ++g) mg[g] = __ballot_sync(0xffffffffu, keep && g >= g_lo && g <= g_hi);
         __syncwarp();   // the previous round's slot reads are done
         if (keep) {
-            const float4 pa = ldg_f4(&pp[j].a), pb = ldg_f4(&pp[j].b), pc = ldg_f4(&pp[j].c);
+            const float4 pa = ldg_f4(&pp[jl].a), pb = ldg_f4(&pp[jl].b), pc = ldg_f4(&pp[jl].c);
             slot[lane] = pa; slot[32 + lane] = pb; slot[64 + lane] = pc;
         }
         __syncwarp();
@@ -202,7 +209,7 @@ __device__ __forceinline__ void tile_item(const ScoreArgs &a, int b, const WcrIm
             c = __reduce_add_sync(0xffffffffu, c);
             if (lane == p) mycnt = c;
         }
-        if (mycnt) atomicAdd(cnt + j, mycnt);
+        if (mycnt) atomicAdd(cnt + jl, mycnt);
     }
     // bookkeeping for the roofline report: lane-tests actually issued by this item
 #pragma unroll
@@ -649,6 +656,140 @@ __device__ __forceinline__ void dyn_seg_batch(const ScoreArgs &a, int code, floa
     chunk_finalize_lazy(a, b, bx, im, c, chunk, wbuf, lane);
 }
 
+// ---- point term on demand (a.pts_lazy) -------------------------------------------------
+// The tiles of a box are walked TWICE. The first pass tests only the a.pa proposals of each chunk
+// with the largest score bound (ws.order, score_order_kernel); the warp that retires the chunk's
+// last first-pass item takes T = the k-th best ACTUAL score among them (mask term filled in for
+// the 32 best when there is one) and keeps, of the other proposals, those whose bound
+//     ub = iou^a * (min(ubcnt, P_b) / P_b)^b          (ubcnt: score_prep_kernel)
+// is not below T. Every factor of the score is rounded the way the bound's factors are, the
+// count is <= ubcnt and the mask factor <= 1, so score <= ub in floating point: a proposal with
+// ub < T has k scores above it and cannot enter the top-k, not even through a tie. It is never
+// tested against the depth points (its count stays 0, its stored score 0 < T). The survivors are
+// compacted behind the first a.pa entries of ws.order; the second pass (items of a second queue
+// that open once every first-pass item has been claimed) tests them, and the warp that retires the
+// chunk's last second-pass item runs the ordinary epilogue.
+__device__ __forceinline__ float bound_score(const ScoreArgs &a, float siou, int count, int npts)
+{
+    const float spts = npts > 0 ? (float)count / (float)npts : 0.f;
+    return ipow(siou, a.sc.e_iou) * ipow(spts, a.sc.e_pts);     // map_beta == 0: shape_term is the identity
+}
+
+__device__ __forceinline__ void chunk_epilogue_first(const ScoreArgs &a, int b, const WcrBox &bx,
+                                                     const WcrImage &im, int chunk, float *wbuf, int lane)
+{
+    const ChunkCtx c = chunk_ctx(a, b, bx, im, chunk, lane);
+    const int bc = b * a.n_chunks + chunk;
+    uint16_t *list = a.ws.order + (size_t)bc * SC_CHUNK;
+    const int PA = min(a.pa, c.chunk_n);
+    float *sc = wbuf + TL_SCORE_OFF;                 // [128] first-pass scores without the mask factor
+    int *sl = reinterpret_cast<int *>(sc + 128);     // [128] their chunk-relative indices
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        const int s = i * 32 + lane;
+        float v = -INFINITY; int loc = 0;
+        if (s < PA) {
+            loc = (int)__ldcg(list + s);
+            v = bound_score(a, __ldcg(a.ws.siou + c.cbase + loc), __ldcg(a.ws.count + c.cbase + loc), c.npts);
+        }
+        sc[s] = v; sl[s] = loc;
+    }
+    __syncwarp();
+    float T = -INFINITY;
+    if (a.sc.e_seg > 0) {
+        // the 32 best positive values get their hull filled; T = k-th best actual score among them
+        unsigned taken = 0u;
+        int q = -1;
+        float q_ub = 0.f;
+        for (int r = 0; r < 32; ++r) {
+            float bvv = 0.f; int bi = 0x7fffffff;
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                const float vv = sc[i * 32 + lane];
+                if (!((taken >> i) & 1u) && vv > bvv) { bvv = vv; bi = i * 32 + lane; }
+            }
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) {
+                const float ov = __shfl_xor_sync(0xffffffffu, bvv, o);
+                const int oi = __shfl_xor_sync(0xffffffffu, bi, o);
+                if (ov > bvv || (ov == bvv && oi < bi)) { bvv = ov; bi = oi; }
+            }
+            if (bi == 0x7fffffff) break;
+            if ((bi & 31) == lane) taken |= 1u << (bi >> 5);
+            if (lane == r) { q = sl[bi]; q_ub = bvv; }
+        }
+        if (__any_sync(0xffffffffu, q >= 0)) {
+            const float actual = chunk_fill(a, b, bx, im, c, chunk, q, q_ub, wbuf, lane);
+            int rank = 0;
+            for (int l = 0; l < 32; ++l) {
+                const float v = __shfl_sync(0xffffffffu, actual, l);
+                rank += (v > actual) || (v == actual && l < lane);
+            }
+            const unsigned kth = __ballot_sync(0xffffffffu, rank == a.k - 1 && actual > -INFINITY);
+            if (kth) T = __shfl_sync(0xffffffffu, actual, __ffs(kth) - 1);
+        }
+    } else {
+        // no mask factor: the values ARE the scores; T = the k-th largest of them
+        unsigned taken = 0u;
+        for (int r = 0; r < a.k; ++r) {
+            float bvv = -INFINITY; int bi = 0x7fffffff;
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                const float vv = sc[i * 32 + lane];
+                if (!((taken >> i) & 1u) && vv > bvv) { bvv = vv; bi = i * 32 + lane; }
+            }
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) {
+                const float ov = __shfl_xor_sync(0xffffffffu, bvv, o);
+                const int oi = __shfl_xor_sync(0xffffffffu, bi, o);
+                if (ov > bvv || (ov == bvv && oi < bi)) { bvv = ov; bi = oi; }
+            }
+            if (bi == 0x7fffffff) { T = -INFINITY; break; }        // fewer than k comparable scores
+            if ((bi & 31) == lane) taken |= 1u << (bi >> 5);
+            T = bvv;
+        }
+    }
+    // survivors of the rest, compacted in place behind the first pass (a round's writes stay at or
+    // below the slots it has read)
+    int nB = 0;
+#pragma unroll 1
+    for (int base = PA; base < c.chunk_n; base += 32) {
+        const int s = base + lane;
+        bool kp = false;
+        int loc = 0;
+        if (s < c.chunk_n) {
+            loc = (int)__ldcg(list + s);
+            const float siou = __ldcg(a.ws.siou + c.cbase + loc);
+            const int ubc = min(__ldcg(a.ws.ubcnt + c.cbase + loc), c.npts);
+            const float ub = bound_score(a, siou, ubc, c.npts);
+            kp = !(siou >= 0.f && ub < T);                         // NaN anywhere: kept
+        }
+        const unsigned bm = __ballot_sync(0xffffffffu, kp);
+        if (kp) list[PA + nB + __popc(bm & ((1u << lane) - 1u))] = (uint16_t)loc;
+        nB += __popc(bm);
+    }
+    if (lane == 0 && c.chunk_n - PA - nB > 0) atomicAdd(a.ws.pruned, (unsigned long long)(c.chunk_n - PA - nB));
+    __threadfence();                                               // the list, before the flag
+    __syncwarp();
+    if (lane == 0) *((volatile int *)a.ws.bready + bc) = nB + 1;
+}
+
+// Phase attribution for tools/diag_score.py (a separate build with -DWCR_PROFILE_PHASES, never the
+// product): SM cycles per phase, summed over warps, in the workspace header at byte 64 + 8 * i.
+#ifdef WCR_PROFILE_PHASES
+#define PH_T0() const long long ph_t0_ = clock64()
+#define PH_MARK(v) v = clock64()
+#define PH_ADDV(i, v) do { if (lane == 0) atomicAdd((unsigned long long *)((char *)a.ws.queue + 64) + (i), \
+                                                    (unsigned long long)(clock64() - (v))); } while (0)
+#define PH_ADD(i) do { if (lane == 0) atomicAdd((unsigned long long *)((char *)a.ws.queue + 64) + (i), \
+                                                (unsigned long long)(clock64() - ph_t0_)); } while (0)
+#else
+#define PH_T0() do { } while (0)
+#define PH_ADD(i) do { } while (0)
+#define PH_MARK(v) do { } while (0)
+#define PH_ADDV(i, v) do { } while (0)
+#endif
+
 template <int WARPS, int MINB, int GRP, bool F2, bool ICNT = false>
 __global__ void __launch_bounds__(WARPS * 32, MINB) score_tiles_kernel(const ScoreArgs a)
 {
@@ -669,40 +810,58 @@ __global__ void __launch_bounds__(WARPS * 32, MINB) score_tiles_kernel(const Sco
     const int nseg = (use_seg && !a.seg_lazy) ? TL_SEGS : 0;
     const int seg_total = a.n_boxes * a.n_chunks * nseg;
     const bool pref_seg = nseg > 0 && wid == WARPS - 1;
-    bool seg_left = seg_total > 0, tile_left = true;
+    bool seg_left = seg_total > 0, tile_left = true, pass2_left = a.pts_lazy != 0;
     const int total_chunks = a.n_boxes * a.n_chunks;
-    volatile int *dynq = a.ws.dynq;   // [0] head, [1] tail (reserved), [2] chunks through phase A
+    volatile int *dynq = a.ws.dynq;   // [0] tickets drawn, [1] tail (reserved), [2] chunks through phase A
+    const long long seg_cap_ll = (long long)total_chunks * 32;
+    const int seg_cap = seg_cap_ll > 0x7fffffffLL ? 0x7fffffff : (int)seg_cap_ll;   // entries of ws.segq
+    int my_ticket = -1;               // lane 0: queue index this warp owns (-1: none)
+    long long ph_loop = 0;
+    (void)ph_loop;
+#ifdef WCR_PROFILE_PHASES
+    unsigned long long ph_start;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(ph_start));
+    if (lane == 0) atomicMin((unsigned long long *)((char *)a.ws.queue + 64) + 12, ph_start);
+#endif
     for (;;) {
+        PH_MARK(ph_loop);
         if (a.seg_lazy) {
-            // published hull batches first: they unblock a chunk's top-k, and the data is warm
+            // Published hull batches first: they unblock a chunk's top-k. Claims are TICKETS: a warp
+            // without one draws the next queue index (one atomicAdd, never retried) and keeps it
+            // until that entry is published -- possibly later, the warp does static work meanwhile
+            // and looks again after every item. Every index below the final tail thus has exactly
+            // one owner, nobody spins on a shared word (a compare-and-swap on the head made
+            // every loser retry: 0.44 ms per warp on C2, profiles/variants_tiles_r2.txt).
             int code = 0;
             if (lane == 0) {
-                const int head = dynq[0];
-                if (head < dynq[1]) {
-                    if (atomicCAS(a.ws.dynq, head, head + 1) == head) {
-                        volatile int *e = (volatile int *)a.ws.segq + head;
-                        while ((code = *e) == 0) __nanosleep(20);   // reserved, being written
-                    } else {
-                        code = -1;                                   // lost the race: look again
-                    }
-                }
+                if (my_ticket < 0) my_ticket = atomicAdd(a.ws.dynq, 1);
+                if (my_ticket < seg_cap) code = *((volatile int *)a.ws.segq + my_ticket);
+                if (code > 0) my_ticket = -1;
             }
             code = __shfl_sync(0xffffffffu, code, 0);
-            if (code < 0) continue;
             if (code > 0) {
                 __threadfence();
+                PH_T0();
                 dyn_seg_batch(a, code - 1, wbuf, lane);
                 __syncwarp();
+                PH_ADD(4);
                 continue;
             }
         }
-        int item = -1, kind = -1;   // kind: 0 tile queue, 1 seg queue
+        int item = -1, kind = -1;   // kind: 0 tile queue, 1 seg queue, 2 second pass of the tiles
         while (kind < 0 && (seg_left || tile_left)) {
             const bool try_seg = seg_left && (pref_seg || !tile_left);
             if (lane == 0) item = atomicAdd(a.ws.queue + (try_seg ? 1 : 0), 1);
             item = __shfl_sync(0xffffffffu, item, 0);
             if (try_seg) { if (item < seg_total) kind = 1; else seg_left = false; }
             else { if (item < total) kind = 0; else tile_left = false; }
+        }
+        if (kind < 0 && pass2_left) {
+            // every first-pass item has been claimed (by warps that never wait): the second pass
+            // may wait for a chunk's first-pass epilogue without risking a deadlock
+            if (lane == 0) item = atomicAdd(a.ws.queue_b, 1);
+            item = __shfl_sync(0xffffffffu, item, 0);
+            if (item < total) kind = 2; else pass2_left = false;
         }
         if (kind < 0) {
             if (!a.seg_lazy) break;
@@ -712,10 +871,14 @@ __global__ void __launch_bounds__(WARPS * 32, MINB) score_tiles_kernel(const Sco
             if (lane == 0) {
                 const int pa = dynq[2];
                 __threadfence();
-                done = pa == total_chunks && dynq[0] >= dynq[1];
+                // the tail is final once every chunk is through phase A (a chunk reserves its
+                // entries before it reports): a ticket at or beyond it will never be published
+                done = pa == total_chunks && my_ticket >= dynq[1];
                 if (!done) __nanosleep(100);
             }
-            if (__shfl_sync(0xffffffffu, done, 0)) break;
+            const int dn = __shfl_sync(0xffffffffu, done, 0);
+            PH_ADDV(8, ph_loop);   // tail: nothing to claim, batches may still be published
+            if (dn) break;
             continue;
         }
         int b = 0;
@@ -741,23 +904,60 @@ __global__ void __launch_bounds__(WARPS * 32, MINB) score_tiles_kernel(const Sco
             const int local = item - prefix[b];
             chunk = local / pt; ti = local - chunk * pt;
         }
+        const int bc = b * a.n_chunks + chunk;
+        PH_ADDV(6, ph_loop);       // claim + decode
+        const uint16_t *list = nullptr;
+        int n_list = 0;
+        if (a.pts_lazy) {
+            list = a.ws.order + (size_t)bc * SC_CHUNK;
+            n_list = min(a.pa, min(SC_CHUNK, a.N - chunk * SC_CHUNK));
+            if (kind == 2) {
+                int v = 0;
+                PH_T0();
+                if (lane == 0) {
+                    volatile int *f = (volatile int *)a.ws.bready + bc;
+                    while ((v = *f) == 0) __nanosleep(64);
+                    __threadfence();
+                }
+                v = __shfl_sync(0xffffffffu, v, 0);
+                PH_ADD(5);
+                list += n_list; n_list = v - 1;
+            }
+        }
         if (seg_grp >= 0) {
             seg_item(a, b, bx, im, chunk, seg_grp, wbuf, lane);
         } else {
             const int tile = ti / subs, sub = ti - tile * subs;
-            if (tile < tg.n_tiles) tile_item<GRP, F2, ICNT>(a, b, im, tg, chunk, tile, sub, wbuf, lane);
+            PH_T0();
+            if (tile < tg.n_tiles)
+                tile_item<GRP, F2, ICNT>(a, b, im, tg, chunk, tile, sub, wbuf, lane, list, n_list, kind != 2);
+            PH_ADD(kind == 2 ? 1 : 0);
         }
         // ---- retire the item ------------------------------------------------------
+        PH_MARK(ph_loop);
         __threadfence();
         __syncwarp();
         int last = 0;
-        if (lane == 0) last = (atomicAdd(a.ws.done_chunk + (size_t)b * a.n_chunks + chunk, 1) == per - 1);
+        int *done = (kind == 2 ? a.ws.done_b : a.ws.done_chunk) + bc;
+        if (lane == 0) last = (atomicAdd(done, 1) == per - 1);
         last = __shfl_sync(0xffffffffu, last, 0);
+        PH_ADDV(7, ph_loop);
         if (!last) continue;
         __threadfence();
-        chunk_epilogue_warp(a, b, bx, im, chunk, wbuf, lane);
+        PH_T0();
+        if (a.pts_lazy && kind == 0) chunk_epilogue_first(a, b, bx, im, chunk, wbuf, lane);
+        else chunk_epilogue_warp(a, b, bx, im, chunk, wbuf, lane);
         __syncwarp();
+        PH_ADD((a.pts_lazy && kind == 0) ? 2 : 3);
     }
+#ifdef WCR_PROFILE_PHASES
+    unsigned long long ph_end;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(ph_end));
+    if (lane == 0) {   // [10] latest exit, [11] sum of exits (ns, absolute), [12] earliest start
+        atomicMax((unsigned long long *)((char *)a.ws.queue + 64) + 10, ph_end);
+        atomicAdd((unsigned long long *)((char *)a.ws.queue + 64) + 11, ph_end - ph_start);
+    }
+#endif
 }
 
 }  // namespace wcr

@@ -164,7 +164,7 @@ class ScoreParams(ctypes.Structure):
     _fields_ = [("e_iou", ctypes.c_int32), ("e_pts", ctypes.c_int32), ("e_seg", ctypes.c_int32),
                 ("point_stride", ctypes.c_int32), ("seg_mode", ctypes.c_int32),
                 ("map_beta", c_float), ("seg_eval", ctypes.c_int32),
-                ("reserved2", ctypes.c_int32)]
+                ("pts_eval", ctypes.c_int32)]
 
 
 class LossParams(ctypes.Structure):

@@ -56,10 +56,11 @@ class ScoreConfig:
     k: int = 16
     map_beta: float = 0.0        # > 0: custom_mapping(x, beta) (utils.py:207-223) shapes every term; 0 = off
     seg_eval: int = 0            # mask term: 0 = library decides, 1 = every hull, 2 = on demand (same results)
+    pts_eval: int = 0            # point term: 0 = library decides, 1 = every proposal, 2 = on demand (same results)
 
     def c_struct(self) -> _abi.ScoreParams:
         return _abi.ScoreParams(self.e_iou, self.e_pts, self.e_seg, self.point_stride,
-                                self.seg_mode, float(self.map_beta), int(self.seg_eval), 0)
+                                self.seg_mode, float(self.map_beta), int(self.seg_eval), int(self.pts_eval))
 
 
 class BoxTable:
@@ -293,6 +294,12 @@ class ScoreWorkspace:
         ``want_all=True``; only those whose bound could still reach the top-k otherwise).
         Synchronises."""
         return int(self.ws[16:24].view(torch.int64).item())
+
+    def proposals_pruned(self) -> int:
+        """Proposals the last ``score_topk`` on this workspace never tested against the depth
+        points (point term on demand: their score bound was below the k-th best score already
+        known). 0 when the point term was evaluated for every proposal. Synchronises."""
+        return int(self.ws[40:48].view(torch.int64).item())
 
 
 def score_topk(shard: ImageShard, boxes: BoxTable, cubes: torch.Tensor | None, N: int | None = None,
