@@ -80,6 +80,56 @@ for b in range(0, len(h), every):
     oz = (zmax[None] >= zlo[:, None]) & (zmin[None] <= zhi[:, None])                                  # (N,256)
     over = (oy[:, :, None] & ox[:, None, :]).reshape(N, 256) & oz
     ub_cell = (over.float() * ccnt[None]).sum(1)
+    # slab bound: a cell (pixel rectangle x depth range) against the cube's own three slab pairs,
+    # interval arithmetic on q_k = z * (A_k a + B_k b + C_k) - O_k, inside iff |q_k| <= 1
+    cyi, cxi = torch.arange(256, device="cuda") // 16, torch.arange(256, device="cuda") % 16
+    a_lo = ((u0 + cxi * cw).float() - cx) / fx; a_hi = ((u0 + torch.minimum((cxi + 1) * cw, torch.tensor(ncols, device="cuda")) - 1).float() - cx) / fx
+    b_lo = ((v0 + cyi * chh).float() - cy) / fy; b_hi = ((v0 + torch.minimum((cyi + 1) * chh, torch.tensor(nrows, device="cuda")) - 1).float() - cy) / fy
+    Rm = c[:, 6:15].reshape(N, 3, 3)
+    Ak, Bk, Ck = Rm[:, 0, :] / half, Rm[:, 1, :] / half, Rm[:, 2, :] / half          # (N,3)
+    Ok = (Ak * c[:, None, 0] + Bk * c[:, None, 1] + Ck * c[:, None, 2])                 # (N,3)
+    def iv(coef, lo, hi):      # (N,3) x (256,) -> (N,256,3) interval of coef * x
+        p1, p2 = coef[:, None, :] * lo[None, :, None], coef[:, None, :] * hi[None, :, None]
+        return torch.minimum(p1, p2), torch.maximum(p1, p2)
+    al, ah = iv(Ak, a_lo, a_hi); bl, bh = iv(Bk, b_lo, b_hi)
+    g_lo = al + bl + Ck[:, None, :]; g_hi = ah + bh + Ck[:, None, :]
+    zl, zh = zmin[None, :, None], zmax[None, :, None]
+    q_lo = torch.minimum(zl * g_lo, zh * g_lo) - Ok[:, None, :]
+    q_hi = torch.maximum(zl * g_hi, zh * g_hi) - Ok[:, None, :]
+    slab_ok = ((q_lo <= 1.001) & (q_hi >= -1.001)).all(2)                                 # (N,256)
+    ub_slab = ((over & slab_ok).float() * ccnt[None]).sum(1)
+    # variants: two axes only (the cube's x and z axes), and 2 x 2 blocks of cells
+    slab2_ok = ((q_lo <= 1.001) & (q_hi >= -1.001))[:, :, [0, 2]].all(2)
+    ub_slab2 = ((over & slab2_ok).float() * ccnt[None]).sum(1)
+    def blk(x, red):   # (256,) -> (64,) over 2 x 2 blocks
+        x4 = x.reshape(8, 2, 8, 2)
+        return red(red(x4, 3), 1).reshape(64)
+    mn = lambda t, d: t.min(d).values
+    mx = lambda t, d: t.max(d).values
+    zmin8, zmax8 = blk(zmin, mn), blk(zmax, mx)
+    a_lo8, a_hi8, b_lo8, b_hi8 = blk(a_lo, mn), blk(a_hi, mx), blk(b_lo, mn), blk(b_hi, mx)
+    cnt8 = blk(ccnt, lambda t, d: t.sum(d))
+    over8 = over.reshape(N, 8, 2, 8, 2).any(4).any(2).reshape(N, 64)
+    al8, ah8 = iv(Ak, a_lo8, a_hi8); bl8, bh8 = iv(Bk, b_lo8, b_hi8)
+    g_lo8 = al8 + bl8 + Ck[:, None, :]; g_hi8 = ah8 + bh8 + Ck[:, None, :]
+    zl8 = torch.maximum(zmin8[None, :, None], zlo[:, None, None]); zh8 = torch.minimum(zmax8[None, :, None], zhi[:, None, None])
+    q_lo8 = torch.minimum(zl8 * g_lo8, zh8 * g_lo8) - Ok[:, None, :]
+    q_hi8 = torch.maximum(zl8 * g_hi8, zh8 * g_hi8) - Ok[:, None, :]
+    slab8_ok = ((q_lo8 <= 1.001) & (q_hi8 >= -1.001)).all(2)
+    # block passes -> its z-overlapping cells count
+    pass8 = (over8 & slab8_ok).reshape(N, 8, 1, 8, 1).expand(N, 8, 2, 8, 2).reshape(N, 256)
+    ub_slab8 = ((over & pass8).float() * ccnt[None]).sum(1)
+    add("cost/blocks8_tested_per_proposal", over8.float().sum(), N)
+    for nm_, u_ in (("ub_slab2", ub_slab2), ("ub_slab8", ub_slab8)):
+        u_[:] = torch.where(live, torch.where(reach, u_, torch.zeros_like(u_)), torch.full_like(u_, float(valid.sum())))
+    ub_slab = torch.where(live, torch.where(reach, ub_slab, torch.zeros_like(ub_slab)), torch.full_like(ub_slab, float(valid.sum())))
+    # executed-work proxy under tile culling by cull box + depth range vs by the slab mask
+    lr = live & reach
+    add("cull/slab_over_bbox_cells", ((over & slab_ok).float().sum(1) * lr).sum(), (over.float().sum(1) * lr).sum())
+    oxy = (oy[:, :, None] & ox[:, None, :]).reshape(N, 256)
+    add("cull/slab_over_bboxonly_cells", ((over & slab_ok).float().sum(1) * lr).sum(), (oxy.float().sum(1) * lr).sum())
+    add("cull/bbox_cells_per_proposal", (oxy.float().sum(1) * lr).sum(), lr.sum())
+    add("cull/zpass_cells_per_proposal", (over.float().sum(1) * lr).sum(), lr.sum())
     npts = float(valid.sum())
     ub_cell = torch.where(live, torch.where(reach, ub_cell, torch.zeros_like(ub_cell)), torch.full_like(ub_cell, npts))
     # rect bound on a pixel subsample (every 2nd row / column) scaled back: study only
@@ -102,9 +152,10 @@ for b in range(0, len(h), every):
         cnt = o["count"][b].float()
         tag = "seg" if use_seg else "noseg"
         add(f"{tag}/viol_cell", (cnt > ub_cell + 0.5).sum(), N)
-        for name, ub in (("cell", ub_cell), ("rect", ub_rect), ("oracle1.0", cnt)):
+        add(f"{tag}/viol_slab", (cnt > ub_slab + 0.5).sum(), N)
+        for name, ub in (("cell", ub_cell), ("slab", ub_slab), ("slab2ax", ub_slab2), ("slab8", ub_slab8)):
             ubs = iou * (ub / max(npts, 1.0)).clamp(max=1)
-            for PA in (64, 128, 256):
+            for PA in (64,):
                 order = ubs.argsort(descending=True)
                 inA = torch.zeros(N, dtype=torch.bool, device="cuda"); inA[order[:PA]] = True
                 TA = sc[inA].topk(K).values[-1]

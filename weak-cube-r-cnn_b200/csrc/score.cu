@@ -123,8 +123,10 @@ struct ScoreWs {
     float *siou;         // [n_boxes][N] IoU term, written by score_prep_kernel
     // point term on demand (a.pts_lazy)
     int *zcnt;           // [n_boxes][256] valid depth points of the ROI's 16 x 16 cells
+    float *cellab;       // [n_boxes][64] pixel-ray slopes of the cell columns' / rows' first and last pixel
     int *ubcnt;          // [n_boxes][N] upper bound of the inside-count (points of the cells the cube can reach)
     float *okey;         // [n_boxes][N] ordering key: IoU factor x bound factor
+    float2 *zblk;        // [n_boxes][64] depth range of the 2 x 2 blocks of cells
     uint16_t *order;     // [n_boxes][n_chunks][SC_CHUNK] chunk proposals by descending key; the first
                          //   pass tests [0, pa), its epilogue compacts the survivors of the rest behind them
     int *done_b;         // [n_boxes][n_chunks] retired second-pass items
@@ -245,11 +247,13 @@ size_t carve(void *base, int n_boxes, int N, int k, bool need_cubes, bool need_s
     uint8_t *mayhit = (uint8_t *)take((size_t)n_boxes * N);
     float *siou = (float *)take((size_t)n_boxes * N * sizeof(float));
     int *zcnt = (int *)take((size_t)n_boxes * 256 * sizeof(int));
+    float *cellab = (float *)take((size_t)n_boxes * 64 * sizeof(float));
     int *ubcnt = (int *)take((size_t)n_boxes * N * sizeof(int));
     float *okey = (float *)take((size_t)n_boxes * N * sizeof(float));
+    float2 *zblk = (float2 *)take((size_t)n_boxes * 64 * sizeof(float2));
     uint16_t *order = (uint16_t *)take((size_t)n_boxes * nc * wcr::SC_CHUNK * sizeof(uint16_t));
     if (ws) {
-        ws->zcnt = zcnt; ws->ubcnt = ubcnt; ws->okey = okey; ws->order = order; ws->done_b = done_b; ws->bready = bready;
+        ws->zcnt = zcnt; ws->cellab = cellab; ws->ubcnt = ubcnt; ws->okey = okey; ws->zblk = zblk; ws->order = order; ws->done_b = done_b; ws->bready = bready;
         ws->queue_b = (int *)(queue ? (char *)queue + 36 : nullptr);
         ws->pruned = (unsigned long long *)(queue ? (char *)queue + 40 : nullptr);
         ws->segcnt = segcnt; ws->params = params; ws->cullbox = cullbox; ws->zgrid = zgrid; ws->mayhit = mayhit; ws->siou = siou;
@@ -326,7 +330,7 @@ extern "C" int wcr_score_topk(const WcrImage *images, const WcrBox *boxes, int n
     a.out_scores = out_scores; a.out_iou = out_iou; a.out_count = out_count;
     a.out_proj = out_proj; a.out_npts = out_npts;
     a.seg_bits = seg_bits; a.seg_off = seg_off; a.out_seg = out_seg;
-    a.item_px = 0; a.grp = 8; a.ps = wcr::SC_CHUNK; a.seg_lazy = 0; a.siou_ready = 0; a.pts_lazy = 0; a.pa = 128;
+    a.item_px = 0; a.grp = 8; a.ps = wcr::SC_CHUNK; a.seg_lazy = 0; a.siou_ready = 0; a.pts_lazy = 0; a.pa = 64;
     const int sms = wcr::sm_count();
     WCR_REQUIRE((N + 255) / 256 <= 65535, "wcr_score_topk: N too large");
     a.src.cubes = cubes; a.src.priors = priors; a.src.normals = normals; a.src.z0 = z0;
@@ -384,7 +388,8 @@ extern "C" int wcr_score_topk(const WcrImage *images, const WcrBox *boxes, int n
     WCR_CHECK_LAUNCH("score_plan_tiles_kernel");
     if (h_score->e_pts > 0) {
         wcr::score_zgrid_kernel<<<dim3(n_boxes, 8), 1024, 0, st>>>(images, boxes, h_score->point_stride, 1, a.ws.zgrid,
-                                                                   a.pts_lazy ? a.ws.zcnt : nullptr);
+                                                                   a.pts_lazy ? a.ws.zcnt : nullptr, a.pts_lazy ? a.ws.cellab : nullptr,
+                                                                   a.pts_lazy ? a.ws.zblk : nullptr);
         WCR_CHECK_LAUNCH("score_zgrid_kernel");
     }
     if (h_score->e_pts > 0 || a.siou_ready) {
@@ -392,7 +397,7 @@ extern "C" int wcr_score_topk(const WcrImage *images, const WcrBox *boxes, int n
         wcr::score_prep_kernel<<<grid, 256, 0, st>>>(images, boxes, n_boxes, a.src, N,
                                                       h_score->point_stride, h_score->e_pts > 0, a.ws.params, a.ws.cullbox,
                                                       a.ws.zgrid, a.ws.mayhit, a.siou_ready ? a.ws.siou : nullptr,
-                                                      a.pts_lazy ? a.ws.zcnt : nullptr, a.ws.ubcnt, a.ws.okey,
+                                                      a.pts_lazy ? a.ws.zcnt : nullptr, a.ws.cellab, a.ws.ubcnt, a.ws.okey, a.ws.zblk,
                                                       h_score->e_iou, h_score->e_pts);
         WCR_CHECK_LAUNCH("score_prep_kernel");
     }

@@ -87,10 +87,12 @@ struct __align__(16) PParam {
 // [n_boxes][256] (min, max); an empty cell holds (+inf, -inf). grid (n_boxes, 8) x 1024 threads:
 // one WARP per cell, lanes stride over the cell's pixels (a small shard has few boxes: the
 // parallelism has to come from inside the box).
-__global__ void __launch_bounds__(1024)
+__global__ void __launch_bounds__(1024, 2)
 score_zgrid_kernel(const WcrImage *__restrict__ images, const WcrBox *__restrict__ boxes, int stride,
-                   int use_pts, float2 *__restrict__ zgrid, int *__restrict__ zcnt)
+                   int use_pts, float2 *__restrict__ zgrid, int *__restrict__ zcnt, float *__restrict__ cellab,
+                   float2 *__restrict__ zblk)
 {
+    __shared__ float2 s_cell[32];
     const int b = blockIdx.x, cell = blockIdx.y * 32 + (threadIdx.x >> 5), lane = threadIdx.x & 31;
     const int cy = cell >> 4, cx = cell & 15;
     const WcrBox bx = boxes[b];
@@ -117,6 +119,29 @@ score_zgrid_kernel(const WcrImage *__restrict__ images, const WcrBox *__restrict
     if (lane == 0) {
         zgrid[(size_t)b * 256 + cell] = make_float2(mn, mx);
         if (zcnt) zcnt[(size_t)b * 256 + cell] = nv;
+        s_cell[threadIdx.x >> 5] = make_float2(mn, mx);
+    }
+    // depth range of the 2 x 2 blocks of cells: this CTA holds cell rows 2y and 2y + 1 = block row y
+    if (zblk) {
+        __syncthreads();
+        if (threadIdx.x < 8) {
+            const int i = threadIdx.x;
+            const float2 c0 = s_cell[2 * i], c1 = s_cell[2 * i + 1], c2 = s_cell[16 + 2 * i], c3 = s_cell[16 + 2 * i + 1];
+            zblk[(size_t)b * 64 + blockIdx.y * 8 + i] = make_float2(fminf(fminf(c0.x, c1.x), fminf(c2.x, c3.x)),
+                                                                    fmaxf(fmaxf(c0.y, c1.y), fmaxf(c2.y, c3.y)));
+        }
+    }
+    // pixel-ray slopes (the a_u, b_v of the point test) of the first and last column / row of
+    // every cell column / row: [a_lo[16] a_hi[16] b_lo[16] b_hi[16]] per box
+    if (cellab && blockIdx.y == 0 && threadIdx.x < 16) {
+        const int i = threadIdx.x;
+        const int cc0 = min(i * cw, max(roi.ncols - 1, 0)), cc1 = max(min(i * cw + cw, roi.ncols) - 1, cc0);
+        const int rr0 = min(i * chh, max(roi.nrows - 1, 0)), rr1 = max(min(i * chh + chh, roi.nrows) - 1, rr0);
+        float *ab = cellab + (size_t)b * 64;
+        ab[i] = ((float)(roi.u0 + cc0 * stride) - im.cx) / im.fx;
+        ab[16 + i] = ((float)(roi.u0 + cc1 * stride) - im.cx) / im.fx;
+        ab[32 + i] = ((float)(roi.v0 + rr0 * stride) - im.cy) / im.fy;
+        ab[48 + i] = ((float)(roi.v0 + rr1 * stride) - im.cy) / im.fy;
     }
 }
 
@@ -127,11 +152,15 @@ score_prep_kernel(const WcrImage *__restrict__ images, const WcrBox *__restrict_
                   const CubeSrc src, int N, int stride, int use_pts,
                   PParam *__restrict__ out, int4 *__restrict__ out_box,
                   const float2 *__restrict__ zgrid, uint8_t *__restrict__ out_mayhit,
-                  float *__restrict__ out_siou, const int *__restrict__ zcnt,
-                  int *__restrict__ out_ubcnt, float *__restrict__ out_key, int e_iou, int e_pts)
+                  float *__restrict__ out_siou, const int *__restrict__ zcnt, const float *__restrict__ cellab,
+                  int *__restrict__ out_ubcnt, float *__restrict__ out_key, const float2 *__restrict__ zblk,
+                  int e_iou, int e_pts)
 {
-    const int j = blockIdx.y * 256 + threadIdx.x, b = blockIdx.x;
-    if (j >= N) return;
+    // (threads past the last proposal recompute proposal N - 1 and store nothing: the bound section
+    // below is warp-cooperative)
+    const int j_raw = blockIdx.y * 256 + threadIdx.x, b = blockIdx.x;
+    const bool store = j_raw < N;
+    const int j = min(j_raw, N - 1);
     const WcrBox bx = boxes[b];
     const WcrImage im = images[bx.image];
     const Roi roi = box_roi(bx, im.H, im.W, stride, use_pts != 0);
@@ -155,7 +184,7 @@ score_prep_kernel(const WcrImage *__restrict__ images, const WcrBox *__restrict_
         clamp_bounds(bx.clamp1, lo1, hi1);
         const ProjBox pbx = project_cube(cube, Kc, lo0, hi0, lo1, hi1, nullptr);
         siou_j = iou_2d(bx.x1, bx.y1, bx.x2, bx.y2, pbx);
-        out_siou[(size_t)b * N + j] = siou_j;
+        if (store) out_siou[(size_t)b * N + j] = siou_j;
     }
     if (!use_pts) return;     // launched for the IoU term only
     PParam p;
@@ -243,16 +272,62 @@ score_prep_kernel(const WcrImage *__restrict__ images, const WcrBox *__restrict_
     // that holds it then overlaps both). Cubes the cull does not apply to can hold every point.
     int ubc = mayhit ? 0x7fffffff : 0;
     if (mayhit && zgrid && ortho && zcnt) {
+        // 2 x 2 blocks of cells that overlap the cull box and the depth range are tested against the
+        // cube itself: interval arithmetic on the very function the point test evaluates,
+        //     q_k = z (A_k a_u + B_k b_v + C_k) - O_k,   inside iff |q_k| <= 2048 for k = 0, 1, 2,
+        // over the block's pixel rectangle and the depths both the block and the cube can hold (the
+        // points of a block lie on a surface patch: its narrow depth range is what makes the test
+        // sharp). If some q_k stays outside [-2048, 2048] over the whole block -- with a margin for
+        // the rounding of both evaluations -- no point of the block is inside. (Valid for any R: it
+        // bounds the test itself.) Blocks rather than cells: 29 instead of 108 tests per proposal on
+        // C2 for 70 % of the pruning the per-cell test adds (tools/prune_study.py).
         const int cw = max(1, (roi.ncols + 15) >> 4), chh = max(1, (roi.nrows + 15) >> 4);
         const float2 *zg = zgrid + (size_t)b * 256;
+        const float2 *zb = zblk + (size_t)b * 64;
         const int *zc = zcnt + (size_t)b * 256;
-        const int cx0 = cl / cw, cx1 = min(15, ch / cw);
+        const int cx0 = cl / cw, cx1 = min(15, ch / cw), cy0 = rl / chh, cy1 = min(15, rh / chh);
+        const float Ak[3] = {p.a.x, p.a.y, p.a.z}, Bk[3] = {p.b.x, p.b.y, p.b.z}, Ck[3] = {p.c.x, p.c.y, p.c.z};
+        const float Nk[3] = {p.a.w, p.b.w, p.c.w};
+        const float *ab = cellab + (size_t)b * 64;   // a_lo[16] a_hi[16] b_lo[16] b_hi[16] (score_zgrid_kernel)
+        const float a_abs = fmaxf(fabsf(__ldg(ab)), fabsf(__ldg(ab + 31)));
+        const float b_abs = fmaxf(fabsf(__ldg(ab + 32)), fabsf(__ldg(ab + 63)));
+        float th[3];   // one margin per axis: 2.5 absolute + 1e-5 of the largest magnitude that can appear
+#pragma unroll
+        for (int k = 0; k < 3; ++k)
+            th[k] = 2050.5f + 1.0e-5f * (fabsf(zhi) * (fabsf(Ak[k]) * a_abs + fabsf(Bk[k]) * b_abs + fabsf(Ck[k])) + fabsf(Nk[k]));
         ubc = 0;
-        for (int cy = rl / chh; cy <= min(15, rh / chh); ++cy) {
-#pragma unroll 4
-            for (int cx = cx0; cx <= cx1; ++cx) {
-                const float2 c = __ldg(zg + cy * 16 + cx);
-                if (!(zhi < c.x || zlo > c.y)) ubc += __ldg(zc + cy * 16 + cx);
+        for (int by = cy0 >> 1; by <= (cy1 >> 1); ++by) {
+            const float b_lo = __ldg(ab + 32 + 2 * by), b_hi = __ldg(ab + 48 + 2 * by + 1);
+            float gl[3], gh[3];
+#pragma unroll
+            for (int k = 0; k < 3; ++k) {
+                const float t1 = Bk[k] * b_lo, t2 = Bk[k] * b_hi;
+                gl[k] = fminf(t1, t2) + Ck[k]; gh[k] = fmaxf(t1, t2) + Ck[k];
+            }
+            for (int bxi = cx0 >> 1; bxi <= (cx1 >> 1); ++bxi) {
+                const float2 c = __ldg(zb + by * 8 + bxi);
+                if (zhi < c.x || zlo > c.y) continue;              // (an empty block holds (+inf, -inf))
+                const float z0c = fmaxf(c.x, zlo), z1c = fminf(c.y, zhi);
+                const float a_lo = __ldg(ab + 2 * bxi), a_hi = __ldg(ab + 16 + 2 * bxi + 1);
+                bool hit = true;
+#ifndef WCR_EXP_NO_SLAB
+#pragma unroll
+                for (int k = 0; k < 3; ++k) {
+                    const float t1 = Ak[k] * a_lo, t2 = Ak[k] * a_hi;
+                    const float g_lo = fminf(t1, t2) + gl[k], g_hi = fmaxf(t1, t2) + gh[k];
+                    const float q_lo = fminf(z0c * g_lo, z1c * g_lo) + Nk[k], q_hi = fmaxf(z0c * g_hi, z1c * g_hi) + Nk[k];
+                    hit = hit && !(q_lo > th[k] || q_hi < -th[k]);
+                }
+#endif
+                if (!hit) continue;
+                // the block's cells inside the cull box whose depth range meets the cube's
+#pragma unroll
+                for (int q = 0; q < 4; ++q) {
+                    const int cy = 2 * by + (q >> 1), cx = 2 * bxi + (q & 1);
+                    if (cy < cy0 || cy > cy1 || cx < cx0 || cx > cx1) continue;
+                    const float2 cc = __ldg(zg + cy * 16 + cx);
+                    if (!(zhi < cc.x || zlo > cc.y)) ubc += __ldg(zc + cy * 16 + cx);
+                }
             }
         }
         mayhit = ubc > 0;   // an empty cell holds (+inf, -inf): same verdict as the scan below
@@ -270,6 +345,7 @@ score_prep_kernel(const WcrImage *__restrict__ images, const WcrBox *__restrict_
             }
         }
     }
+    if (!store) return;
     if (out_mayhit) out_mayhit[(size_t)b * N + j] = mayhit ? 1 : 0;
     if (zcnt) {
         out_ubcnt[(size_t)b * N + j] = ubc;
