@@ -388,7 +388,7 @@ def run_wcr(args):
     full = score_topk(runner.shard, runner.boxes, None, NPROP, runner.score_cfg, priors=runner.priors,
                       normals=runner.normals, z0=z0, seed=1234, seg=runner.seg, want_all=True)
     tests_per_launch = float(full["npts"].sum().item()) * NPROP
-    executed_per_launch = float(full["workspace"].executed_tests())   # after the projected-box cull
+    executed_unpruned = float(full["workspace"].executed_tests())     # after the projected-box cull, every proposal tested
     del full
 
     for _ in range(max(args.warmup, 3)):
@@ -415,6 +415,9 @@ def run_wcr(args):
         dist.barrier()
     launches = _abi.launch_count()
     hulls = runner.ws.hulls_filled() if use_seg else 0
+    # what the TIMED configuration issued (point term on demand: pruned proposals are never tested)
+    executed_per_launch = float(runner.ws.executed_tests())
+    pruned = runner.ws.proposals_pruned()
     step_ms = sum(e[0].elapsed_time(e[1]) for e in ev)
     score_ms = sum(e[2].elapsed_time(e[3]) for e in ev) / args.steps
 
@@ -560,6 +563,8 @@ def run_wcr(args):
                          "alg_flop_per_test": ALG_FLOP_PER_TEST,
                          "executed_flop_per_test": EXEC_FLOP_PER_TEST,
                          "tests_executed_frac": executed_per_launch / max(tests_per_launch, 1.0),
+                         "tests_executed_frac_every_proposal": executed_unpruned / max(tests_per_launch, 1.0),
+                         "proposals_pruned_frac": pruned / max(runner.n_proposals, 1),
                          "frac_executed": EXEC_FLOP_PER_TEST * executed_per_launch / (score_ms * 1e-3) / 1e12 / fp32_probe_tflops,
                          "hulls_filled_frac": hulls / max(runner.n_proposals, 1),
                          "kernel_ms": score_ms,

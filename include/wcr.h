@@ -235,8 +235,23 @@ int wcr_sample_cubes(const WcrImage *images, const WcrBox *boxes, int n_boxes,
  *   Mask term on demand: with seg_mode 0 and out_scores == out_seg == NULL, the hull of a
  *   proposal is filled only if its bound iou^e_iou * pts^e_pts can still reach the box's k-th
  *   best score (the ratio is <= 1, so the bound holds in floating point too); the records are
- *   those of the full evaluation, bit for bit. */
+ *   those of the full evaluation, bit for bit. With plain terms (map_beta == 0) the bound also
+ *   carries a bound of the mask ratio itself: |mask & hull| <= the pixels of the hull's bounding
+ *   box inside the ROI, |hull| >= the largest projected face minus a perimeter margin.
+ *   Point term on demand (pts_eval): with no per-proposal output and map_beta == 0 the depth
+ *   pixels of a box are walked twice. The first pass tests the 64 proposals of each 1024-proposal
+ *   chunk whose score BOUND is largest -- IoU term x (valid points of the 16 x 16 ROI cells the
+ *   cube can reach / P_b) x the mask-ratio bound -- and takes T, the k-th best actual score among
+ *   them; the second pass tests only proposals whose bound is not below T. The others cannot enter
+ *   the top-k (every factor of the score is rounded like the bound's and is <= it), their counts
+ *   are never formed; the records are those of the full evaluation, bit for bit. The uint64 at
+ *   byte 40 of the workspace holds the number of proposals skipped.
+ * wcr_score_bounds_offsets: byte offsets, inside the workspace, of the per-proposal bounds of the
+ *   last call that used them: int32 [n_boxes][N] upper bounds of the inside-counts (0x7fffffff =
+ *   none) and int32 pairs [n_boxes][N][2] (max |mask & hull|, min |hull|). No reference
+ *   counterpart; tests/test_score_bounds_gpu.py checks the bounds against the full evaluation. */
 int64_t wcr_score_workspace_bytes(int n_boxes, int N, int k);
+int wcr_score_bounds_offsets(int n_boxes, int N, int k, int64_t *off_ubcnt, int64_t *off_segb);
 int wcr_score_topk(const WcrImage *images, const WcrBox *boxes, int n_boxes,
                    const float *cubes, int N,
                    const float *priors, const float *normals, const float *z0,

@@ -145,6 +145,44 @@ for b in range(0, len(h), every):
     ub_rect = torch.where(live, torch.where(reach, ub_rect * 1.05 + 4, torch.zeros_like(ub_rect)), torch.full_like(ub_rect, npts))
     work = torch.where(live & reach, (ch - cl + 1) * (rh - rl + 1), torch.zeros_like(cl)).clamp(min=0)
     work = torch.where(live, work, torch.full_like(work, float(nrows * ncols)))
+    # mask-term bound: ratio <= B / M when the hull's bounding box holds B < M pixels (M = mask area)
+    bits = r.seg.bits[int(r.seg.off[b]):int(r.seg.off[b + 1])]
+    M = float(sum(bin(int(x) & 0xffffffff).count("1") for x in bits.cpu().tolist()))
+    pj = outs[True]["proj"][b]
+    Bpix = ((torch.floor(pj[:, 2]) - torch.ceil(pj[:, 0]) + 3).clamp(min=0) * (torch.floor(pj[:, 3]) - torch.ceil(pj[:, 1]) + 3).clamp(min=0))
+    ub_seg = torch.nan_to_num((Bpix / max(M, 1.0)).clamp(max=1.0), nan=1.0)
+    Himg, Wimg = r.shard.depths[img].shape
+    qx = px.clamp(0, Wimg - 1); qy = py.clamp(0, Himg - 1)               # (N, 8) clamped corners
+    FACES = [[0, 1, 2, 3], [4, 5, 6, 7], [0, 1, 5, 4], [1, 2, 6, 5], [2, 3, 7, 6], [3, 0, 4, 7]]
+    Af = torch.zeros(N, device="cuda")
+    for f in FACES:
+        x_, y_ = qx[:, f], qy[:, f]
+        sa = 0.5 * (x_ * y_.roll(-1, 1) - x_.roll(-1, 1) * y_).sum(1)
+        Af = torch.maximum(Af, sa.abs())
+    bw = qx.max(1).values - qx.min(1).values + 2; bh = qy.max(1).values - qy.min(1).values + 2
+    Blow = (Af - 4 * (bw + bh) - 32).clamp(min=0)
+    # inter <= pixels of (hull bbox + margin) inside the ROI
+    ix0 = torch.maximum(torch.floor(qx.min(1).values) - 1, torch.tensor(float(u0), device="cuda"))
+    ix1 = torch.minimum(torch.ceil(qx.max(1).values) + 1, torch.tensor(float(u1 - 1), device="cuda"))
+    iy0 = torch.maximum(torch.floor(qy.min(1).values) - 1, torch.tensor(float(v0), device="cuda"))
+    iy1 = torch.minimum(torch.ceil(qy.max(1).values) + 1, torch.tensor(float(v1 - 1), device="cuda"))
+    Iub = ((ix1 - ix0 + 1).clamp(min=0) * (iy1 - iy0 + 1).clamp(min=0))
+    istar = torch.minimum(Iub, torch.tensor(M, device="cuda"))
+    ub_seg2 = torch.nan_to_num(istar / (M + torch.maximum(Blow, istar) - istar).clamp(min=1), nan=1.0).clamp(max=1)
+    ub_seg2 = torch.where(live, ub_seg2, torch.ones_like(ub_seg2))
+    vio = outs[True]["seg"][b] > ub_seg2 * (1 + 1e-6)
+    if bool(vio.any()) and acc.get("dbg", [0])[0] < 6:
+        acc.setdefault("dbg", [0.0, 1.0])[0] += 1
+        k_ = int(vio.nonzero()[0])
+        print("VIOL box", b, "prop", k_, "seg", float(outs[True]["seg"][b, k_]), "ub", float(ub_seg2[k_]), "Iub", float(Iub[k_]),
+              "Blow", float(Blow[k_]), "Af", float(Af[k_]), "M", M, "bw,bh", float(bw[k_]), float(bh[k_]),
+              "roi", (u0, v0, u1, v1), "qx", [round(float(t), 1) for t in qx[k_]], "qy", [round(float(t), 1) for t in qy[k_]],
+              "clamp", float(h["clamp0"][b]), float(h["clamp1"][b]), "img", (Himg, Wimg), file=sys.stderr)
+    add("seg/viol_ubseg2", vio.sum(), N)
+    add("seg/mean_ubseg2", ub_seg2.sum(), N)
+    add("seg/mean_seg", torch.nan_to_num(outs[True]["seg"][b]).sum(), N)
+    add("seg/viol_ubseg", (outs[True]["seg"][b] > ub_seg * (1 + 1e-6)).sum(), N)
+    add("seg/mean_ubseg", ub_seg.sum(), N)
     for use_seg in (True, False):
         o = outs[use_seg]
         sc = torch.nan_to_num(o["scores"][b], nan=0.0)
@@ -153,8 +191,17 @@ for b in range(0, len(h), every):
         tag = "seg" if use_seg else "noseg"
         add(f"{tag}/viol_cell", (cnt > ub_cell + 0.5).sum(), N)
         add(f"{tag}/viol_slab", (cnt > ub_slab + 0.5).sum(), N)
-        for name, ub in (("cell", ub_cell), ("slab", ub_slab), ("slab2ax", ub_slab2), ("slab8", ub_slab8)):
+        for name, ub in (("cell", ub_cell), ("slab", ub_slab), ("slab8", ub_slab8), ("slab8+ubseg", ub_slab8), ("slab8+ubseg2", ub_slab8), ("slab8+segoracle", ub_slab8)):
             ubs = iou * (ub / max(npts, 1.0)).clamp(max=1)
+            if name.endswith("ubseg"):
+                if not use_seg: continue
+                ubs = ubs * ub_seg
+            if name.endswith("ubseg2"):
+                if not use_seg: continue
+                ubs = ubs * ub_seg2
+            if name.endswith("segoracle"):
+                if not use_seg: continue
+                ubs = ubs * torch.nan_to_num(o["seg"][b], nan=1.0)
             for PA in (64,):
                 order = ubs.argsort(descending=True)
                 inA = torch.zeros(N, dtype=torch.bool, device="cuda"); inA[order[:PA]] = True

@@ -223,6 +223,18 @@ __device__ __forceinline__ float seg_ratio(int inter, int bube, int area, int mo
     return fi / fu;
 }
 
+// Upper bound of seg_ratio(inter, bube, area, 0) from inter <= iub and bube >= max(blow, inter):
+// i / (area + h - i) grows with i and falls with h, so the bound is its value at i = min(iub, area),
+// h = max(blow, i). Integers below 2^24 and one correctly rounded division on both sides: the
+// float ratio is <= the float bound.
+__device__ __forceinline__ float seg_ratio_bound(int iub, int blow, int area)
+{
+    const int i = min(iub, area);
+    if (i <= 0) return 0.f;
+    const int h = max(blow, i);
+    return (float)i / (float)(area + h - i);
+}
+
 // Rows r0 + lane, r0 + 32 + lane, ... of one hull with M edges (compile-time, so the
 // edge loops are straight-line code with no per-edge branches).
 //

@@ -127,6 +127,7 @@ struct ScoreWs {
     int *ubcnt;          // [n_boxes][N] upper bound of the inside-count (points of the cells the cube can reach)
     float *okey;         // [n_boxes][N] ordering key: IoU factor x bound factor
     float2 *zblk;        // [n_boxes][64] depth range of the 2 x 2 blocks of cells
+    int2 *segb;          // [n_boxes][N] mask-term bounds: (max |mask & hull|, min |hull|) pixels (a.seg_tight)
     uint16_t *order;     // [n_boxes][n_chunks][SC_CHUNK] chunk proposals by descending key; the first
                          //   pass tests [0, pa), its epilogue compacts the survivors of the rest behind them
     int *done_b;         // [n_boxes][n_chunks] retired second-pass items
@@ -150,6 +151,7 @@ struct ScoreArgs {
     int siou_ready;      // tile path: ws.siou holds every proposal's IoU term (written by score_prep_kernel)
     int pts_lazy;        // tile path: point term on demand (two passes over the tiles, see chunk_epilogue_first)
     int pa;              // ... proposals per chunk tested in the first pass (multiple of 32)
+    int seg_tight;       // tile path: bounds carry the mask-term bound seg_ratio_bound (ws.segb is filled)
     ScoreWs ws;
     float *records;
     float *out_scores, *out_iou;
@@ -251,9 +253,10 @@ size_t carve(void *base, int n_boxes, int N, int k, bool need_cubes, bool need_s
     int *ubcnt = (int *)take((size_t)n_boxes * N * sizeof(int));
     float *okey = (float *)take((size_t)n_boxes * N * sizeof(float));
     float2 *zblk = (float2 *)take((size_t)n_boxes * 64 * sizeof(float2));
+    int2 *segb = (int2 *)take(need_seg ? (size_t)n_boxes * N * sizeof(int2) : 0);
     uint16_t *order = (uint16_t *)take((size_t)n_boxes * nc * wcr::SC_CHUNK * sizeof(uint16_t));
     if (ws) {
-        ws->zcnt = zcnt; ws->cellab = cellab; ws->ubcnt = ubcnt; ws->okey = okey; ws->zblk = zblk; ws->order = order; ws->done_b = done_b; ws->bready = bready;
+        ws->zcnt = zcnt; ws->cellab = cellab; ws->ubcnt = ubcnt; ws->okey = okey; ws->zblk = zblk; ws->segb = segb; ws->order = order; ws->done_b = done_b; ws->bready = bready;
         ws->queue_b = (int *)(queue ? (char *)queue + 36 : nullptr);
         ws->pruned = (unsigned long long *)(queue ? (char *)queue + 40 : nullptr);
         ws->segcnt = segcnt; ws->params = params; ws->cullbox = cullbox; ws->zgrid = zgrid; ws->mayhit = mayhit; ws->siou = siou;
@@ -276,6 +279,23 @@ extern "C" int64_t wcr_score_workspace_bytes(int n_boxes, int N, int k)
     // no cube buffer: a sampled proposal is regenerated from its Philox counter where it is needed
     return (int64_t)carve(nullptr, n_boxes, N, k, false, true, nullptr, nullptr);
 #endif
+}
+
+// Byte offsets, inside a workspace of wcr_score_workspace_bytes(n_boxes, N, k), of the per-proposal
+// bounds the on-demand paths prune with (tests check them against the full evaluation).
+extern "C" int wcr_score_bounds_offsets(int n_boxes, int N, int k, int64_t *off_ubcnt, int64_t *off_segb)
+{
+    if (n_boxes < 0 || N < 1 || k < 1 || !off_ubcnt || !off_segb) return WCR_EINVAL;
+    wcr::ScoreWs w;
+    char *base = reinterpret_cast<char *>(4096);
+#ifdef WCR_KEEP_BASELINE_KERNEL
+    carve(base, n_boxes, N, k, true, true, &w, nullptr);
+#else
+    carve(base, n_boxes, N, k, false, true, &w, nullptr);
+#endif
+    *off_ubcnt = (int64_t)((char *)w.ubcnt - base);
+    *off_segb = (int64_t)((char *)w.segb - base);
+    return WCR_OK;
 }
 
 extern "C" int wcr_score_topk(const WcrImage *images, const WcrBox *boxes, int n_boxes,
@@ -330,7 +350,7 @@ extern "C" int wcr_score_topk(const WcrImage *images, const WcrBox *boxes, int n
     a.out_scores = out_scores; a.out_iou = out_iou; a.out_count = out_count;
     a.out_proj = out_proj; a.out_npts = out_npts;
     a.seg_bits = seg_bits; a.seg_off = seg_off; a.out_seg = out_seg;
-    a.item_px = 0; a.grp = 8; a.ps = wcr::SC_CHUNK; a.seg_lazy = 0; a.siou_ready = 0; a.pts_lazy = 0; a.pa = 64;
+    a.item_px = 0; a.grp = 8; a.ps = wcr::SC_CHUNK; a.seg_lazy = 0; a.siou_ready = 0; a.pts_lazy = 0; a.pa = 64; a.seg_tight = 0;
     const int sms = wcr::sm_count();
     WCR_REQUIRE((N + 255) / 256 <= 65535, "wcr_score_topk: N too large");
     a.src.cubes = cubes; a.src.priors = priors; a.src.normals = normals; a.src.z0 = z0;
@@ -375,6 +395,9 @@ extern "C" int wcr_score_topk(const WcrImage *images, const WcrBox *boxes, int n
     a.pts_lazy = h_score->e_pts > 0 && a.siou_ready && h_score->map_beta == 0.f &&
                  (h_score->e_seg == 0 || a.seg_lazy) && h_score->pts_eval != 1 &&
                  (h_score->pts_eval == 2 || many_chunks);
+    // Bounds sharpened by a bound of the mask ratio (score_prep_kernel: hull bounding box against
+    // the ROI, largest face against the mask area): needs the per-thread IoU pass and plain terms.
+    a.seg_tight = a.seg_lazy && a.siou_ready && h_score->map_beta == 0.f;
     {   // proposals per tile item: the whole chunk when the shard has enough tiles for every
         // resident warp (a box has ~30 tiles), finer for small shards
         const long long bc = (long long)n_boxes * nc, want = 4LL * sms_resident_warps();
@@ -397,7 +420,7 @@ extern "C" int wcr_score_topk(const WcrImage *images, const WcrBox *boxes, int n
         wcr::score_prep_kernel<<<grid, 256, 0, st>>>(images, boxes, n_boxes, a.src, N,
                                                       h_score->point_stride, h_score->e_pts > 0, a.ws.params, a.ws.cullbox,
                                                       a.ws.zgrid, a.ws.mayhit, a.siou_ready ? a.ws.siou : nullptr,
-                                                      a.pts_lazy ? a.ws.zcnt : nullptr, a.ws.cellab, a.ws.ubcnt, a.ws.okey, a.ws.zblk,
+                                                      a.pts_lazy ? a.ws.zcnt : nullptr, a.ws.cellab, a.ws.ubcnt, a.ws.okey, a.ws.zblk, a.seg_tight ? a.ws.segb : nullptr,
                                                       h_score->e_iou, h_score->e_pts);
         WCR_CHECK_LAUNCH("score_prep_kernel");
     }

@@ -154,7 +154,7 @@ score_prep_kernel(const WcrImage *__restrict__ images, const WcrBox *__restrict_
                   const float2 *__restrict__ zgrid, uint8_t *__restrict__ out_mayhit,
                   float *__restrict__ out_siou, const int *__restrict__ zcnt, const float *__restrict__ cellab,
                   int *__restrict__ out_ubcnt, float *__restrict__ out_key, const float2 *__restrict__ zblk,
-                  int e_iou, int e_pts)
+                  int2 *__restrict__ out_segb, int e_iou, int e_pts)
 {
     // (threads past the last proposal recompute proposal N - 1 and store nothing: the bound section
     // below is warp-cooperative)
@@ -182,9 +182,66 @@ score_prep_kernel(const WcrImage *__restrict__ images, const WcrBox *__restrict_
         float lo0, hi0, lo1, hi1;
         clamp_bounds(bx.clamp0, lo0, hi0);
         clamp_bounds(bx.clamp1, lo1, hi1);
-        const ProjBox pbx = project_cube(cube, Kc, lo0, hi0, lo1, hi1, nullptr);
+        float cxy[16];
+        const ProjBox pbx = project_cube(cube, Kc, lo0, hi0, lo1, hi1, out_segb ? cxy : nullptr);
         siou_j = iou_2d(bx.x1, bx.y1, bx.x2, bx.y2, pbx);
         if (store) out_siou[(size_t)b * N + j] = siou_j;
+        if (out_segb) {
+            // Bounds for the mask term (seg_ratio_bound): the hull K that seg_group fills is the
+            // convex hull of the corners clamped a second time (roi_heads.py:950-952), some of them
+            // bumped by up to +7 pixels in x and y when they coincide (jarvis_march's duplicate
+            // rule) -- bumps add points, the hull only grows.
+            //   x = pixels of (K's bounding box, grown like seg_counts_warp's scan window and by
+            //       the bumps) inside the mask's ROI: an upper bound of |mask & hull|;
+            //   y = a lower bound of |hull|: K contains every face of the cube, so its area is at
+            //       least the largest |signed area| of the six clamped face quadrilaterals; a
+            //       convex region of area A and perimeter P holds at least A - 0.72 P pixel
+            //       centres deeper than 0.01 px inside (unit squares around lattice points tile
+            //       the plane; erode K by sqrt(2)/2 + 0.01), which is far more than the rounding
+            //       of the fill's edge tests (~1e-3 px), and P <= the bounding box's perimeter.
+            const float hx2 = (float)(int)(bx.clamp0 - 1.f), hy2 = (float)(int)(bx.clamp1 - 1.f);
+            float sx[8], sy[8];
+            bool fin = true;
+            float mnx = INFINITY, mxx = -INFINITY, mny = INFINITY, mxy = -INFINITY;
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+                fin = fin && fabsf(cxy[2 * i]) <= 3.402823466e38f && fabsf(cxy[2 * i + 1]) <= 3.402823466e38f;
+                sx[i] = fminf(fmaxf(cxy[2 * i], 0.f), hx2);
+                sy[i] = fminf(fmaxf(cxy[2 * i + 1], 0.f), hy2);
+                mnx = fminf(mnx, sx[i]); mxx = fmaxf(mxx, sx[i]);
+                mny = fminf(mny, sy[i]); mxy = fmaxf(mxy, sy[i]);
+            }
+            int2 sb2 = make_int2(0x7fffffff, 0);
+            if (fin && mxx < 1.0e6f && mxy < 1.0e6f) {
+                const Roi r1 = box_roi(bx, im.H, im.W, 1, true);
+                const int nr1 = r1.ncols > 0 ? r1.nrows : 0;
+                const int x0 = max((int)floorf(mnx) - 1, r1.u0), x1 = min((int)ceilf(mxx) + 9, r1.u0 + r1.ncols - 1);
+                const int y0 = max((int)floorf(mny) - 1, r1.v0), y1 = min((int)ceilf(mxy) + 9, r1.v0 + nr1 - 1);
+                sb2.x = (x1 >= x0 && y1 >= y0) ? (x1 - x0 + 1) * (y1 - y0 + 1) : 0;
+                {
+                    const int F[6][4] = {{0, 1, 2, 3}, {4, 5, 6, 7}, {0, 1, 5, 4}, {1, 2, 6, 5}, {2, 3, 7, 6}, {3, 0, 4, 7}};
+                    float amax = 0.f;
+#pragma unroll
+                    for (int f = 0; f < 6; ++f) {
+                        float acc = 0.f;
+#pragma unroll
+                        for (int e = 0; e < 4; ++e) {
+                            const int i0 = F[f][e], i1 = F[f][(e + 1) & 3];
+                            acc += (sx[i0] - mnx) * (sy[i1] - mny) - (sx[i1] - mnx) * (sy[i0] - mny);
+                        }
+                        amax = fmaxf(amax, fabsf(acc));
+                    }
+                    // the fill counts no pixel outside the image: the reference clamps x with
+                    // clamp0 and y with clamp1 (spaces.py:241-242; (H, W) in its call), so K may
+                    // reach past the last row or column -- at most the part of its bounding box there
+                    const float wbb = mxx - mnx + 1.f, hbb = mxy - mny + 1.f;
+                    const float outside = wbb * fmaxf(mxy - (float)(im.H - 1), 0.f) + hbb * fmaxf(mxx - (float)(im.W - 1), 0.f);
+                    const float lowf = 0.5f * amax * 0.999f - outside * 1.001f - 2.f * ((wbb + 16.f) + (hbb + 16.f)) - 16.f;
+                    sb2.y = lowf > 0.f ? (int)lowf : 0;
+                }
+            }
+            if (store) out_segb[(size_t)b * N + j] = sb2;
+        }
     }
     if (!use_pts) return;     // launched for the IoU term only
     PParam p;

@@ -441,6 +441,24 @@ __device__ __forceinline__ void chunk_scores(const ScoreArgs &a, int b, const Wc
     __syncwarp();
 }
 
+// factor <= 1 that bounds the mask factor of proposal o (1 without bounds)
+__device__ __forceinline__ float seg_bound_factor(const ScoreArgs &a, size_t o, int area)
+{
+    if (!a.seg_tight) return 1.f;
+    const int2 sb = __ldg(a.ws.segb + o);
+    return ipow(seg_ratio_bound(sb.x, sb.y, area), a.sc.e_seg);
+}
+
+// iou^a * pts^b of proposal q of the chunk, the product chunk_scores forms before the mask factor
+// (a.seg_tight: siou_ready and map_beta == 0, so this is chunk_scores' fast path bit for bit)
+__device__ __forceinline__ float fill_product(const ScoreArgs &a, const ChunkCtx &c, int q)
+{
+    const float siou = __ldcg(a.ws.siou + c.cbase + q);
+    const int count = __ldcg(a.ws.count + c.cbase + q);
+    const float spts = c.npts > 0 ? (float)count / (float)c.npts : 0.f;
+    return ipow(siou, a.sc.e_iou) * ipow(spts, a.sc.e_pts);
+}
+
 // hull fill of up to 32 proposals of the chunk (q = the lane's proposal or -1) whose bound is in
 // `ub`; returns the lane's actual score (-inf without a proposal) and stores it to ws.ub
 __device__ __forceinline__ float chunk_fill(const ScoreArgs &a, int b, const WcrBox &bx, const WcrImage &im,
@@ -562,8 +580,14 @@ __device__ __forceinline__ void chunk_epilogue_warp(const ScoreArgs &a, int b, c
 #pragma unroll 8
     for (int i = 0; i < SC_CHUNK / 32; ++i) {
         const int loc = i * 32 + lane;
-        if (loc < c.chunk_n) __stcg(a.ws.ub + c.cbase + loc, sc[loc]);
+        if (loc < c.chunk_n) {
+            // with mask-term bounds, ws.ub and sc[] hold product x bound of the mask factor; the
+            // fills recompute the plain product (fill_product)
+            if (a.seg_tight) sc[loc] = sc[loc] * seg_bound_factor(a, c.cbase + loc, c.area);
+            __stcg(a.ws.ub + c.cbase + loc, sc[loc]);
+        }
     }
+    __syncwarp();
     // the 32 best positive bounds (non-destructive arg-max rounds; bit i of `taken` <-> loc i*32+lane)
     unsigned taken = 0u;
     int q = -1;
@@ -587,6 +611,7 @@ __device__ __forceinline__ void chunk_epilogue_warp(const ScoreArgs &a, int b, c
     }
     float T = -INFINITY;
     if (__any_sync(0xffffffffu, q >= 0)) {
+        if (a.seg_tight && q >= 0) q_ub = fill_product(a, c, q);
         const float actual = chunk_fill(a, b, bx, im, c, chunk, q, q_ub, wbuf, lane);
         // T = k-th largest actual score of the first batch (rank by counting; ties by lane)
         int rank = 0;
@@ -643,7 +668,7 @@ __device__ __forceinline__ void dyn_seg_batch(const ScoreArgs &a, int code, floa
     float ub = 0.f;
     if (batch * 32 + lane < n_cand) {
         q = (int)__ldcg(cl + batch * 32 + lane);
-        ub = __ldcg(a.ws.ub + c.cbase + q);
+        ub = a.seg_tight ? fill_product(a, c, q) : __ldcg(a.ws.ub + c.cbase + q);
     }
     chunk_fill(a, b, bx, im, c, chunk, q, ub, wbuf, lane);
     __threadfence();
@@ -682,17 +707,19 @@ __device__ __forceinline__ void chunk_epilogue_first(const ScoreArgs &a, int b, 
     const int bc = b * a.n_chunks + chunk;
     uint16_t *list = a.ws.order + (size_t)bc * SC_CHUNK;
     const int PA = min(a.pa, c.chunk_n);
-    float *sc = wbuf + TL_SCORE_OFF;                 // [128] first-pass scores without the mask factor
+    float *sc = wbuf + TL_SCORE_OFF;                 // [128] first-pass scores with the mask factor's bound
     int *sl = reinterpret_cast<int *>(sc + 128);     // [128] their chunk-relative indices
+    float *pu = sc + 256;                            // [128] ... without any mask factor
 #pragma unroll
     for (int i = 0; i < 4; ++i) {
         const int s = i * 32 + lane;
-        float v = -INFINITY; int loc = 0;
+        float v = -INFINITY, pv = -INFINITY; int loc = 0;
         if (s < PA) {
             loc = (int)__ldcg(list + s);
-            v = bound_score(a, __ldcg(a.ws.siou + c.cbase + loc), __ldcg(a.ws.count + c.cbase + loc), c.npts);
+            pv = bound_score(a, __ldcg(a.ws.siou + c.cbase + loc), __ldcg(a.ws.count + c.cbase + loc), c.npts);
+            v = a.sc.e_seg > 0 ? pv * seg_bound_factor(a, c.cbase + loc, c.area) : pv;
         }
-        sc[s] = v; sl[s] = loc;
+        sc[s] = v; sl[s] = loc; pu[s] = pv;
     }
     __syncwarp();
     float T = -INFINITY;
@@ -716,7 +743,7 @@ __device__ __forceinline__ void chunk_epilogue_first(const ScoreArgs &a, int b, 
             }
             if (bi == 0x7fffffff) break;
             if ((bi & 31) == lane) taken |= 1u << (bi >> 5);
-            if (lane == r) { q = sl[bi]; q_ub = bvv; }
+            if (lane == r) { q = sl[bi]; q_ub = pu[bi]; }
         }
         if (__any_sync(0xffffffffu, q >= 0)) {
             const float actual = chunk_fill(a, b, bx, im, c, chunk, q, q_ub, wbuf, lane);
@@ -761,7 +788,8 @@ __device__ __forceinline__ void chunk_epilogue_first(const ScoreArgs &a, int b, 
             loc = (int)__ldcg(list + s);
             const float siou = __ldcg(a.ws.siou + c.cbase + loc);
             const int ubc = min(__ldcg(a.ws.ubcnt + c.cbase + loc), c.npts);
-            const float ub = bound_score(a, siou, ubc, c.npts);
+            float ub = bound_score(a, siou, ubc, c.npts);
+            if (a.sc.e_seg > 0) ub = ub * seg_bound_factor(a, c.cbase + loc, c.area);
             kp = !(siou >= 0.f && ub < T);                         // NaN anywhere: kept
         }
         const unsigned bm = __ballot_sync(0xffffffffu, kp);

@@ -295,6 +295,19 @@ class ScoreWorkspace:
         Synchronises."""
         return int(self.ws[16:24].view(torch.int64).item())
 
+    def bounds(self):
+        """-> (ubcnt (n_boxes, N) int32, segb (n_boxes, N, 2) int32): views of the per-proposal
+        bounds the last on-demand ``score_topk`` on this workspace pruned with (upper bound of
+        the inside-count; max |mask & hull| and min |hull| pixels). Test hook."""
+        lib = _abi.load()
+        o1, o2 = ctypes.c_int64(), ctypes.c_int64()
+        _abi.check(lib.wcr_score_bounds_offsets(self.n_boxes, self.N, self.k, ctypes.byref(o1), ctypes.byref(o2)),
+                   "wcr_score_bounds_offsets")
+        n = self.n_boxes * self.N
+        ub = self.ws[o1.value:o1.value + 4 * n].view(torch.int32).view(self.n_boxes, self.N)
+        sb = self.ws[o2.value:o2.value + 8 * n].view(torch.int32).view(self.n_boxes, self.N, 2)
+        return ub, sb
+
     def proposals_pruned(self) -> int:
         """Proposals the last ``score_topk`` on this workspace never tested against the depth
         points (point term on demand: their score bound was below the k-th best score already
