@@ -52,6 +52,8 @@ def parse():
     ap.add_argument("--c4-images", type=int, default=8192,
                     help="global image count of the strong-scaling block (BASELINE configs[3]); 0 = skip")
     ap.add_argument("--c4-passes", type=int, default=3)
+    ap.add_argument("--dense-mode", default="mapped", choices=["roi", "rows", "mapped", "copy"],
+                    help="how the e2e arm moves the dense per-box masks (ShardRunner dense_seg)")
     return ap.parse_args()
 
 
@@ -460,13 +462,14 @@ def run_wcr(args):
     e2e_packed_s = pipelined(runner, runner2, gather, gather2)
     # (c) the headline e2e: the per-box masks arrive DENSE, as the reference's object_masks()
     # produces them (roi_heads.py:383-401), in pinned host memory; inside the timed region the ROI
-    # rectangle of every box's map is copied H2D (one 2-D copy per box: only what the packer reads
-    # crosses PCIe; h2d_bytes_per_step counts those bytes) and bit-packed on the device
+    # bytes of every box's map cross PCIe (h2d_bytes_per_step counts them) and are bit-packed on the
+    # device: by default the pack kernel gathers them straight from the mapped pinned maps (128-byte
+    # reads, 32 GB/s; --dense-mode roi = one 2-D copy per box, 6 GB/s: 1264 small copies)
     e2e_s, dense_h2d, e2e_dense_sync_s = e2e_packed_s, None, None
     if use_seg:
         gather3 = wdist.TopkGather(n_local_boxes, TOPK, dev)
         rd = [ShardRunner(ims, NPROP, dev, priors=priors, score_cfg=runner.score_cfg, seed=1234,
-                          records=g.send, dense_seg=True) for g in (gather2, gather3)]
+                          records=g.send, dense_seg=args.dense_mode) for g in (gather2, gather3)]
         dense_h2d = rd[0].h2d_bytes
         e2e_s = pipelined(rd[0], rd[1], gather2, gather3)
         for _ in range(2):
@@ -542,8 +545,14 @@ def run_wcr(args):
                     "d2h_bytes_per_step": runner.d2h_bytes,
                     "api": "wcr.pipeline.ShardPipeline (double-buffered: copies of neighbouring steps overlap the pass)",
                     "masks": ("dense per-box masks (n_boxes x H x W u8, as object_masks() yields them) in pinned host memory; "
-                              "every step the ROI rectangle of each box's map is copied H2D (one 2-D copy per box) and "
-                              "bit-packed on the device" if dense_h2d is not None else "no mask term"),
+                              + {"mapped": "every step the pack kernel reads the ROI bytes of each box's map from the mapped "
+                                           "host memory over PCIe (on the upload stream) and writes the bit-packed words",
+                                 "roi": "every step the ROI rectangle of each box's map is copied H2D (one 2-D copy per box) and "
+                                        "bit-packed on the device",
+                                 "rows": "every step one contiguous copy per box (first to last ROI pixel) H2D, bit-packed on the device",
+                                 "copy": "every step the whole maps are copied H2D and bit-packed on the device"}[args.dense_mode]
+                              if dense_h2d is not None else "no mask term"),
+                    "dense_mode": args.dense_mode,
                     "dense_mask_bytes_on_host": (int(runner.n_boxes) * H * W) if dense_h2d is not None else 0,
                     "one_shard_at_a_time": (total_props * args.steps / e2e_dense_sync_s) if e2e_dense_sync_s
                     else total_props * args.steps / e2e_sync_s,

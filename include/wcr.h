@@ -280,6 +280,13 @@ int wcr_pack_box_masks(const uint8_t *masks, int64_t mask_stride, int mask_pitch
 int wcr_h2d_box_mask_rois(const uint8_t *h_masks, uint8_t *d_masks, int64_t mask_stride,
                           int mask_pitch, const int32_t *h_rois, const int32_t *h_mask_idx,
                           int n_boxes, void *stream);
+/* The same refresh as ONE contiguous copy per box, from the ROI's first pixel to its last with the
+ * whole rows in between ((nrows - 1) * pitch + ncols bytes; *out_bytes = the total, may be NULL):
+ * more bytes than the rectangles, but contiguous blocks move at the link's full rate on a copy
+ * engine where 2-D copies of short rows do not. No reference counterpart. */
+int wcr_h2d_box_mask_rows(const uint8_t *h_masks, uint8_t *d_masks, int64_t mask_stride,
+                          int mask_pitch, const int32_t *h_rois, const int32_t *h_mask_idx,
+                          int n_boxes, int64_t *out_bytes, void *stream);
 
 /* ------------------------------------------------- block-level drop-ins -- */
 /* One launch behind each helper the reference exposes by name (SURVEY A2.1-A2.5,

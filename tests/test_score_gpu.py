@@ -506,6 +506,17 @@ def test_pack_box_masks_device_equals_host(cuda_lib):
     inv = torch.empty_like(perm); inv[perm] = torch.arange(n)
     dev2 = SegMasks.from_dense(shard, boxes, dense[perm].contiguous().cuda(), mask_idx=inv)
     assert torch.equal(dev2.bits, dev.bits)
+    # odd pitches and a misaligned base: every byte alignment of a row start (the kernel reads aligned
+    # 32-bit words and funnel-shifts), and the same maps read from mapped pinned host memory
+    for pad, skew in ((10, 0), (8, 1), (9, 3)):
+        big = torch.zeros((n * (H + 3) * (W + pad) + 8,), dtype=torch.uint8)
+        view = big[skew:skew + n * (H + 3) * (W + pad)].view(n, H + 3, W + pad)
+        view[:, :H, :W] = dense
+        dev3 = SegMasks.from_dense(shard, boxes, big.cuda()[skew:skew + n * (H + 3) * (W + pad)].view(n, H + 3, W + pad)[:, :H, :W])
+        assert torch.equal(dev3.bits, dev.bits), (pad, skew)
+    pinned = padded.pin_memory()
+    dev4 = SegMasks.from_dense(shard, boxes, pinned[:, :H, :W])
+    assert torch.equal(dev4.bits, dev.bits)
 
 
 def test_shard_runner_dense_masks_equal_prepacked(cuda_lib):
@@ -518,7 +529,7 @@ def test_shard_runner_dense_masks_equal_prepacked(cuda_lib):
         im["seg"] = synth.seg_masks(im["boxes"], H, W)
     kw = dict(priors=synth.make_priors(), score_cfg=ScoreConfig(k=8, e_seg=1), seed=3)
     a = ShardRunner(ims, 400, "cuda", **kw).run_host().clone()
-    for mode in (True, "copy", "mapped"):   # ROI rectangles copied / whole maps copied / ROI bytes read from host
+    for mode in (True, "rows", "copy", "mapped"):   # ROI rectangles / contiguous row bands / whole maps copied, ROI bytes read from host
         r = ShardRunner(ims, 400, "cuda", dense_seg=mode, **kw)
         if mode == "copy":
             assert r.h2d_bytes > 9 * H * W

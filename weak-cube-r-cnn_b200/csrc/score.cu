@@ -437,48 +437,116 @@ extern "C" int wcr_score_topk(const WcrImage *images, const WcrBox *boxes, int n
 
 // ---- dense per-box masks -> the bit-packed seg_bits layout --------------------------------
 // The reference's object masks arrive dense, one H x W map per box (roi_heads.py:383-401,
-// masks_all_images); wcr_score_topk wants them bit-packed over each box's integer ROI. One warp
-// per 32-pixel word: 32 byte loads (one 32-byte sector), one ballot, one store.
+// masks_all_images); wcr_score_topk wants them bit-packed over each box's integer ROI. A warp
+// packs 128 pixels of a row per trip: every lane reads ONE aligned 32-bit word (128 contiguous
+// bytes per warp request -- the maps may live in mapped pinned HOST memory, where the request size
+// is what PCIe efficiency hangs on), a funnel shift with the neighbour's word undoes the row's
+// byte misalignment, the lane's four "non-zero" bits are OR-ed across groups of eight lanes into
+// the four output words.
+// One-warp CTAs of at most 32 registers, two independent requests in flight per warp, 32 CTAs per
+// box: PCIe reads want tens of thousands of bytes in flight (a 148-warp "background" shape meant to
+// sit beside the persistent scoring kernel reached 5 GB/s against 32 GB/s and was dropped).
 namespace wcr {
-__global__ void __launch_bounds__(256)
+// one 128-pixel unit of a row: issue the loads (pack_load), later turn them into 4 words (pack_store)
+__device__ __forceinline__ void pack_geom(const uint8_t *m, const Roi &r, int mask_pitch, int upr, int unit,
+                                          int &row, int &q, int &npx, int &sh, const uint32_t *&wp)
+{
+    row = unit / upr; q = unit - row * upr;
+    const int c0 = q << 7;
+    npx = min(128, r.ncols - c0);                         // pixels of this unit
+    const uintptr_t addr = (uintptr_t)(m + (size_t)(r.v0 + row) * mask_pitch + r.u0 + c0);
+    sh = (int)(addr & 3);
+    wp = reinterpret_cast<const uint32_t *>(addr - sh);   // the pixels occupy bytes [sh, sh + npx) of wp[0 ..]
+}
+
+__device__ __forceinline__ void pack_load(const uint8_t *m, const Roi &r, int mask_pitch, int upr, int unit, int lane,
+                                          uint32_t &w, uint32_t &wx)
+{
+    int row, q, npx, sh;
+    const uint32_t *wp;
+    pack_geom(m, r, mask_pitch, upr, unit, row, q, npx, sh, wp);
+    w = 0u; wx = 0u;
+    if (4 * lane < sh + npx) w = __ldcs(wp + lane);
+    if (lane == 31 && sh + npx > 128) wx = __ldcs(wp + 32);
+}
+
+__device__ __forceinline__ void pack_store(const uint8_t *m, const Roi &r, int mask_pitch, int upr, int unit, int lane,
+                                           uint32_t w, uint32_t wx, uint32_t *out, int wpr)
+{
+    int row, q, npx, sh;
+    const uint32_t *wp;
+    pack_geom(m, r, mask_pitch, upr, unit, row, q, npx, sh, wp);
+    uint32_t nxt = __shfl_down_sync(0xffffffffu, w, 1);
+    if (lane == 31) nxt = wx;
+    const uint32_t by = __funnelshift_r(w, nxt, 8 * sh);  // the lane's pixels 4 lane .. 4 lane + 3
+    const int left = npx - 4 * lane;                      // valid pixels from this lane's first on
+    uint32_t nib = 0u;
+    if (left > 0 && (by & 0x000000ffu)) nib |= 1u;
+    if (left > 1 && (by & 0x0000ff00u)) nib |= 2u;
+    if (left > 2 && (by & 0x00ff0000u)) nib |= 4u;
+    if (left > 3 && (by & 0xff000000u)) nib |= 8u;
+    uint32_t v = nib << (4 * (lane & 7));
+    v |= __shfl_xor_sync(0xffffffffu, v, 1);
+    v |= __shfl_xor_sync(0xffffffffu, v, 2);
+    v |= __shfl_xor_sync(0xffffffffu, v, 4);
+    const int k = lane >> 3;                              // output word of this lane's group
+    if ((lane & 7) == 0 && 32 * k < npx) out[(size_t)row * wpr + q * 4 + k] = v;
+}
+
+// grid (x, y): CTA (bx, by) takes boxes bx, bx + gridDim.x, ... and of each the units by, by + gridDim.y,
+// ..., U of them at a time (U independent requests in flight per warp)
+template <int U>
+__global__ void __maxnreg__(32)
 pack_box_masks_kernel(const uint8_t *__restrict__ masks, int64_t mask_stride, int mask_pitch,
                       const int32_t *__restrict__ mask_idx, const WcrImage *__restrict__ images,
-                      const WcrBox *__restrict__ boxes, const int64_t *__restrict__ seg_off,
+                      const WcrBox *__restrict__ boxes, int n_boxes, const int64_t *__restrict__ seg_off,
                       uint32_t *__restrict__ out_bits)
 {
-    const int b = blockIdx.x, lane = threadIdx.x & 31;
-    const WcrBox bx = boxes[b];
-    const WcrImage im = images[bx.image];
-    const Roi r = box_roi(bx, im.H, im.W, 1, true);
-    const int nrows = r.ncols > 0 ? r.nrows : 0, wpr = (r.ncols + 31) >> 5;
-    const int n_words = nrows * wpr;
-    const uint8_t *m = masks + (size_t)(mask_idx ? mask_idx[b] : b) * mask_stride;
-    uint32_t *out = out_bits + seg_off[b];
-    const int warps = (blockDim.x >> 5) * gridDim.y;
-    for (int w = blockIdx.y * (blockDim.x >> 5) + (threadIdx.x >> 5); w < n_words; w += warps) {
-        const int row = w / wpr, c = (w - row * wpr) * 32 + lane;
-        bool on = false;
-        if (c < r.ncols) on = m[(size_t)(r.v0 + row) * mask_pitch + r.u0 + c] != 0;
-        const unsigned word = __ballot_sync(0xffffffffu, on);
-        if (lane == 0) out[w] = word;
+    const int lane = threadIdx.x & 31, step = gridDim.y;
+    for (int b = blockIdx.x; b < n_boxes; b += gridDim.x) {
+        const WcrBox bx = boxes[b];
+        const WcrImage im = images[bx.image];
+        const Roi r = box_roi(bx, im.H, im.W, 1, true);
+        const int nrows = r.ncols > 0 ? r.nrows : 0, wpr = (r.ncols + 31) >> 5;
+        const int upr = (r.ncols + 127) >> 7;             // 128-pixel units per row
+        const int n_units = nrows * upr;
+        const uint8_t *m = masks + (size_t)(mask_idx ? mask_idx[b] : b) * mask_stride;
+        uint32_t *out = out_bits + seg_off[b];
+        for (int unit = blockIdx.y; unit < n_units; unit += U * step) {
+            uint32_t w[U], wx[U];
+#pragma unroll
+            for (int i = 0; i < U; ++i)
+                if (unit + i * step < n_units) pack_load(m, r, mask_pitch, upr, unit + i * step, lane, w[i], wx[i]);
+#pragma unroll
+            for (int i = 0; i < U; ++i)
+                if (unit + i * step < n_units) pack_store(m, r, mask_pitch, upr, unit + i * step, lane, w[i], wx[i], out, wpr);
+        }
     }
 }
 }  // namespace wcr
+
+static int pack_box_masks_launch(const char *who, const uint8_t *masks, int64_t mask_stride, int mask_pitch,
+                                 const int32_t *mask_idx, const WcrImage *images, const WcrBox *boxes,
+                                 int n_boxes, const int64_t *seg_off, uint32_t *out_bits, void *stream)
+{
+    WCR_CHECK_DEVICE();
+    WCR_REQUIRE(masks && images && boxes && seg_off && out_bits, "%s: null pointer", who);
+    WCR_REQUIRE(n_boxes >= 0 && mask_pitch >= 1 && mask_stride >= 0, "%s: bad sizes", who);
+    if (n_boxes == 0) return WCR_OK;
+    WCR_REQUIRE(n_boxes <= 0x7fffffff / 4, "%s: too many boxes", who);
+    // a 640 x 480 ROI is 2400 units of 128 pixels: 32 one-warp CTAs per box keep a small shard busy too
+    wcr::pack_box_masks_kernel<2><<<dim3(n_boxes, 32), 32, 0, (cudaStream_t)stream>>>(
+        masks, mask_stride, mask_pitch, mask_idx, images, boxes, n_boxes, seg_off, out_bits);
+    WCR_CHECK_LAUNCH("pack_box_masks_kernel");
+    return WCR_OK;
+}
 
 extern "C" int wcr_pack_box_masks(const uint8_t *masks, int64_t mask_stride, int mask_pitch,
                                   const int32_t *mask_idx, const WcrImage *images, const WcrBox *boxes,
                                   int n_boxes, const int64_t *seg_off, uint32_t *out_bits, void *stream)
 {
-    WCR_CHECK_DEVICE();
-    WCR_REQUIRE(masks && images && boxes && seg_off && out_bits, "wcr_pack_box_masks: null pointer");
-    WCR_REQUIRE(n_boxes >= 0 && mask_pitch >= 1 && mask_stride >= 0, "wcr_pack_box_masks: bad sizes");
-    if (n_boxes == 0) return WCR_OK;
-    WCR_REQUIRE(n_boxes <= 0x7fffffff / 4, "wcr_pack_box_masks: too many boxes");
-    // a 640 x 480 ROI is 9600 words: 4 CTAs x 8 warps per box keep a small shard busy too
-    wcr::pack_box_masks_kernel<<<dim3(n_boxes, 4), 256, 0, (cudaStream_t)stream>>>(
-        masks, mask_stride, mask_pitch, mask_idx, images, boxes, seg_off, out_bits);
-    WCR_CHECK_LAUNCH("pack_box_masks_kernel");
-    return WCR_OK;
+    return pack_box_masks_launch("wcr_pack_box_masks", masks, mask_stride, mask_pitch, mask_idx, images, boxes,
+                                 n_boxes, seg_off, out_bits, stream);
 }
 
 // Host -> device copy of just the ROI rectangle of every box's dense mask: one cudaMemcpy2DAsync
@@ -505,5 +573,34 @@ extern "C" int wcr_h2d_box_mask_rois(const uint8_t *h_masks, uint8_t *d_masks, i
             return WCR_ELAUNCH;
         }
     }
+    return WCR_OK;
+}
+
+// The same refresh as ONE contiguous copy per box: from the ROI's first pixel to its last, whole
+// rows in between ((nrows - 1) * pitch + ncols bytes). About three times the bytes of the
+// rectangles on SUN RGB-D-sized boxes, but a 2-D copy of short rows runs at a fraction of the
+// link's rate (6 GB/s measured for ~200-byte rows against 55 GB/s for contiguous blocks), and
+// copy engines need no SM: the transfer hides behind the previous shard's pass.
+extern "C" int wcr_h2d_box_mask_rows(const uint8_t *h_masks, uint8_t *d_masks, int64_t mask_stride,
+                                     int mask_pitch, const int32_t *h_rois, const int32_t *h_mask_idx,
+                                     int n_boxes, int64_t *out_bytes, void *stream)
+{
+    WCR_REQUIRE(h_masks && d_masks && h_rois, "wcr_h2d_box_mask_rows: null pointer");
+    WCR_REQUIRE(n_boxes >= 0 && mask_pitch >= 1 && mask_stride >= 0, "wcr_h2d_box_mask_rows: bad sizes");
+    int64_t total = 0;
+    for (int b = 0; b < n_boxes; ++b) {
+        const int u0 = h_rois[4 * b], v0 = h_rois[4 * b + 1], u1 = h_rois[4 * b + 2], v1 = h_rois[4 * b + 3];
+        if (u1 <= u0 || v1 <= v0) continue;
+        const size_t off = (size_t)(h_mask_idx ? h_mask_idx[b] : b) * (size_t)mask_stride +
+                           (size_t)v0 * (size_t)mask_pitch + (size_t)u0;
+        const size_t bytes = (size_t)(v1 - v0 - 1) * (size_t)mask_pitch + (size_t)(u1 - u0);
+        cudaError_t e = cudaMemcpyAsync(d_masks + off, h_masks + off, bytes, cudaMemcpyHostToDevice, (cudaStream_t)stream);
+        if (e != cudaSuccess) {
+            wcr::set_error("wcr_h2d_box_mask_rows: cudaMemcpyAsync (box %d): %s", b, cudaGetErrorString(e));
+            return WCR_ELAUNCH;
+        }
+        total += (int64_t)bytes;
+    }
+    if (out_bytes) *out_bytes = total;
     return WCR_OK;
 }

@@ -47,6 +47,7 @@ SIGNATURES = {
     "wcr_pack_box_masks": (c_int, [c_void_p, c_i64, c_int, c_void_p, c_void_p, c_void_p, c_int, c_void_p,
                                    c_void_p, c_void_p]),
     "wcr_h2d_box_mask_rois": (c_int, [c_void_p, c_void_p, c_i64, c_int, c_void_p, c_void_p, c_int, c_void_p]),
+    "wcr_h2d_box_mask_rows": (c_int, [c_void_p, c_void_p, c_i64, c_int, c_void_p, c_void_p, c_int, c_void_p, c_void_p]),
     "wcr_cube_corners": (c_int, [c_void_p, c_i64, c_void_p, c_void_p]),
     "wcr_bube_corners": (c_int, [c_void_p, c_i64, c_float, c_float, c_float, c_float, c_float,
                                  c_float, c_void_p, c_void_p, c_void_p]),

@@ -30,9 +30,13 @@ class ShardRunner:
         pinned memory; every ``upload`` copies the ROI rectangle of each box's map H2D (one 2-D copy
         per box, ``wcr_h2d_box_mask_rois``: only what the packer reads crosses PCIe) and every
         ``step`` bit-packs them on the device (``wcr_pack_box_masks``). ``dense_seg="copy"``: whole
-        maps, n_boxes x H x W bytes per step; ``dense_seg="mapped"``: no copy at all, the pack kernel
-        reads the ROI bytes from the pinned maps over PCIe (best for one shard at a time, but it
-        cannot overlap the scoring kernel). Default (False): packed once on the host.
+        maps, n_boxes x H x W bytes per step; ``dense_seg="rows"``: one CONTIGUOUS copy per box, from
+        the ROI's first pixel to its last (``wcr_h2d_box_mask_rows``; ~3x the rectangles' bytes but at
+        the link's full rate and on a copy engine, so it hides behind the previous shard's pass: the
+        fastest mode inside a ``ShardPipeline``); ``dense_seg="mapped"``: no copy at all, the pack
+        kernel gathers the ROI bytes from the pinned maps over PCIe during ``upload`` (fewest bytes;
+        best for one shard at a time -- it needs SMs, so it cannot overlap the persistent scoring
+        kernel). Default (False): packed once on the host.
 
         The geometry of a runner is FROZEN at construction: image sizes, intrinsics, boxes and
         mask offsets are part of the device tables. Re-uploading (``upload``, ``ShardPipeline``)
@@ -88,6 +92,9 @@ class ShardRunner:
                 from .proposals import box_rois
                 import numpy as _np
                 self._h_rois = _np.ascontiguousarray(box_rois(self.boxes, self.shard), dtype=_np.int32)
+                rr = self._h_rois.astype(_np.int64)
+                ok = (rr[:, 2] > rr[:, 0]) & (rr[:, 3] > rr[:, 1])
+                self.row_band_bytes = int((((rr[:, 3] - rr[:, 1] - 1) * self.h_seg_dense.stride(1) + rr[:, 2] - rr[:, 0]) * ok).sum())
         elif self.score_cfg.e_seg > 0:
             if all("seg_packed" in im for im in images):
                 self.seg = SegMasks(self.shard, self.boxes, packed=[w for im in images for w in im["seg_packed"]])
@@ -108,7 +115,8 @@ class ShardRunner:
     def h2d_bytes(self) -> int:
         seg = self.h_seg.numel() * 4 if self.h_seg is not None else 0
         if self.h_seg_dense is not None:      # bytes that cross PCIe for the masks
-            seg = self.h_seg_dense.numel() if self.dense_mode == "copy" else self.seg.roi_bytes
+            seg = self.h_seg_dense.numel() if self.dense_mode == "copy" else \
+                self.row_band_bytes if self.dense_mode == "rows" else self.seg.roi_bytes
         return self.h_depth.numel() * 4 + self.h_ground.numel() + self.h_boxes.numel() + seg
 
     @property
@@ -123,6 +131,17 @@ class ShardRunner:
             self.seg.bits.copy_(self.h_seg, non_blocking=True)
         if self.d_seg_dense is not None and self.dense_mode == "copy":
             self.d_seg_dense.copy_(self.h_seg_dense, non_blocking=True)
+        elif self.h_seg_dense is not None and self.d_seg_dense is None:
+            # "mapped": the pack kernel gathers the ROI bytes straight from the pinned maps (128-byte
+            # reads over PCIe) -- here, on the stream that uploads, so that in a ShardPipeline it
+            # overlaps the previous shard's pass
+            self.seg.repack(self.h_seg_dense)
+        elif self.d_seg_dense is not None and self.dense_mode == "rows":
+            m = self.h_seg_dense
+            _abi.check(_abi.load().wcr_h2d_box_mask_rows(
+                m.data_ptr(), self.d_seg_dense.data_ptr(), m.stride(0), m.stride(1),
+                self._h_rois.ctypes.data, None, self.n_boxes, None, _abi.stream_ptr(self.device)),
+                "wcr_h2d_box_mask_rows")
         elif self.d_seg_dense is not None:
             m = self.h_seg_dense
             _abi.check(_abi.load().wcr_h2d_box_mask_rois(
@@ -137,8 +156,8 @@ class ShardRunner:
         self.normals = ground.normal_vector_from_maps(None, None, None, shard=self.shard,
                                                       seed=self.seed)
         z0 = box_center_depth(self.shard, self.boxes)
-        if self.h_seg_dense is not None:         # dense masks of this step -> seg_bits, on the device
-            self.seg.repack(self.d_seg_dense if self.d_seg_dense is not None else self.h_seg_dense)
+        if self.d_seg_dense is not None:         # dense masks of this step -> seg_bits, on the device
+            self.seg.repack(self.d_seg_dense)
         if score_events is not None:
             score_events[0].record()
             out = self._score(z0)

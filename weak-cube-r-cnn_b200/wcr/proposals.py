@@ -240,9 +240,9 @@ def _segmasks_repack(self, masks: torch.Tensor):
     assert masks.dtype == torch.uint8 and masks.dim() == 3 and masks.stride(2) == 1
     lib = _abi.load()
     _abi.check(lib.wcr_pack_box_masks(masks.data_ptr(), masks.stride(0), masks.stride(1),
-                                      _abi.ptr(self._mask_idx), self._shard.table.data_ptr(),
-                                      self._boxes.table.data_ptr(), self.n_boxes, self.off.data_ptr(),
-                                      self.bits.data_ptr(), _abi.stream_ptr(self.bits.device)),
+                  _abi.ptr(self._mask_idx), self._shard.table.data_ptr(),
+                  self._boxes.table.data_ptr(), self.n_boxes, self.off.data_ptr(),
+                  self.bits.data_ptr(), _abi.stream_ptr(self.bits.device)),
                "wcr_pack_box_masks")
 
 
