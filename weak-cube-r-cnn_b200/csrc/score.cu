@@ -132,6 +132,7 @@ struct ScoreWs {
                          //   pass tests [0, pa), its epilogue compacts the survivors of the rest behind them
     int *done_b;         // [n_boxes][n_chunks] retired second-pass items
     int *bready;         // [n_boxes][n_chunks] 0: first pass running; else 1 + survivors of the second pass
+    unsigned *evald;     // [n_boxes][n_chunks][32] proposals whose hull the first pass's epilogue filled (ws.segcnt is valid)
 };
 
 struct ScoreArgs {
@@ -235,6 +236,7 @@ size_t carve(void *base, int n_boxes, int N, int k, bool need_cubes, bool need_s
     int *seg_pending = (int *)take(need_seg ? (size_t)n_boxes * nc * sizeof(int) : 0);
     int *done_b = (int *)take((size_t)n_boxes * nc * sizeof(int));
     int *bready = (int *)take((size_t)n_boxes * nc * sizeof(int));
+    unsigned *evald = (unsigned *)take(need_seg ? (size_t)n_boxes * nc * 32 * sizeof(unsigned) : 0);
     if (zero_bytes) *zero_bytes = off;
     int *ncand = (int *)take(need_seg ? (size_t)n_boxes * nc * sizeof(int) : 0);
     uint16_t *candlist = (uint16_t *)take(need_seg ? (size_t)n_boxes * nc * wcr::SC_CHUNK * sizeof(uint16_t) : 0);
@@ -256,7 +258,7 @@ size_t carve(void *base, int n_boxes, int N, int k, bool need_cubes, bool need_s
     int2 *segb = (int2 *)take(need_seg ? (size_t)n_boxes * N * sizeof(int2) : 0);
     uint16_t *order = (uint16_t *)take((size_t)n_boxes * nc * wcr::SC_CHUNK * sizeof(uint16_t));
     if (ws) {
-        ws->zcnt = zcnt; ws->cellab = cellab; ws->ubcnt = ubcnt; ws->okey = okey; ws->zblk = zblk; ws->segb = segb; ws->order = order; ws->done_b = done_b; ws->bready = bready;
+        ws->zcnt = zcnt; ws->cellab = cellab; ws->ubcnt = ubcnt; ws->okey = okey; ws->zblk = zblk; ws->segb = segb; ws->order = order; ws->done_b = done_b; ws->bready = bready; ws->evald = evald;
         ws->queue_b = (int *)(queue ? (char *)queue + 36 : nullptr);
         ws->pruned = (unsigned long long *)(queue ? (char *)queue + 40 : nullptr);
         ws->segcnt = segcnt; ws->params = params; ws->cullbox = cullbox; ws->zgrid = zgrid; ws->mayhit = mayhit; ws->siou = siou;
@@ -410,7 +412,7 @@ extern "C" int wcr_score_topk(const WcrImage *images, const WcrBox *boxes, int n
                                                      a.ws.item_prefix);
     WCR_CHECK_LAUNCH("score_plan_tiles_kernel");
     if (h_score->e_pts > 0) {
-        wcr::score_zgrid_kernel<<<dim3(n_boxes, 8), 1024, 0, st>>>(images, boxes, h_score->point_stride, 1, a.ws.zgrid,
+        wcr::score_zgrid_kernel<<<dim3(n_boxes, 8), 256, 0, st>>>(images, boxes, h_score->point_stride, 1, a.ws.zgrid,
                                                                    a.pts_lazy ? a.ws.zcnt : nullptr, a.pts_lazy ? a.ws.cellab : nullptr,
                                                                    a.pts_lazy ? a.ws.zblk : nullptr);
         WCR_CHECK_LAUNCH("score_zgrid_kernel");

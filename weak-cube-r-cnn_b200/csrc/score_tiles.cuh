@@ -83,58 +83,66 @@ struct __align__(16) PParam {
 // box can reach (inclusive; cl > ch: the proposal holds no point of this ROI), then the depth
 // range [zlo, zhi] (float bits) of the cube's corners
 
-// Depth range of the valid pixels of every cell of a 16 x 16 grid over a box's (sub-sampled) ROI:
-// [n_boxes][256] (min, max); an empty cell holds (+inf, -inf). grid (n_boxes, 8) x 1024 threads:
-// one WARP per cell, lanes stride over the cell's pixels (a small shard has few boxes: the
-// parallelism has to come from inside the box).
-__global__ void __launch_bounds__(1024, 2)
+// Depth range and number of the valid pixels of every cell of a 16 x 16 grid over a box's
+// (sub-sampled) ROI: zgrid [n_boxes][256] (min, max), an empty cell holds (+inf, -inf); zcnt
+// [n_boxes][256]; zblk [n_boxes][64] the ranges of the 2 x 2 blocks of cells; cellab [n_boxes][64]
+// the pixel-ray slopes (the a_u, b_v of the point test) of the first and last column / row of every
+// cell column / row: a_lo[16] a_hi[16] b_lo[16] b_hi[16]. (zcnt, zblk, cellab: only when asked for.)
+// grid (n_boxes, 8) x 256 threads: a CTA takes cell rows 2y and 2y + 1; a thread walks its COLUMN
+// down a cell row (coalesced across the CTA; valid depths are positive, so their bit patterns
+// order like the values) and merges into the cell's shared-memory slot once per cell row.
+// (The first form -- a warp per cell, lanes striding over the cell's pixels -- took 0.17 ms on C2.)
+__global__ void __launch_bounds__(256)
 score_zgrid_kernel(const WcrImage *__restrict__ images, const WcrBox *__restrict__ boxes, int stride,
                    int use_pts, float2 *__restrict__ zgrid, int *__restrict__ zcnt, float *__restrict__ cellab,
                    float2 *__restrict__ zblk)
 {
-    __shared__ float2 s_cell[32];
-    const int b = blockIdx.x, cell = blockIdx.y * 32 + (threadIdx.x >> 5), lane = threadIdx.x & 31;
-    const int cy = cell >> 4, cx = cell & 15;
+    __shared__ unsigned s_mn[32], s_mx[32];
+    __shared__ int s_n[32];
+    const int b = blockIdx.x, y = blockIdx.y, tid = threadIdx.x;
     const WcrBox bx = boxes[b];
     const WcrImage im = images[bx.image];
     const Roi roi = box_roi(bx, im.H, im.W, stride, use_pts != 0);
     const int cw = max(1, (roi.ncols + 15) >> 4), chh = max(1, (roi.nrows + 15) >> 4);
-    const int r0 = cy * chh, r1 = min(r0 + chh, roi.nrows), c0 = cx * cw, c1 = min(c0 + cw, roi.ncols);
-    float mn = INFINITY, mx = -INFINITY;
-    int nv = 0;   // valid points of the cell: the validity rule of tile_item
-    if (r1 > r0 && c1 > c0) {
-        const int w = c1 - c0, n = (r1 - r0) * w;
-        for (int i = lane; i < n; i += 32) {
-            const int r = r0 + i / w, c = c0 + i % w;
-            const float d = __ldg(im.depth + (size_t)(roi.v0 + r * stride) * im.depth_pitch + roi.u0 + c * stride);
-            if (d > 0.f && d <= 3.402823466e38f) { mn = fminf(mn, d); mx = fmaxf(mx, d); ++nv; }
-        }
-    }
+    if (tid < 32) { s_mn[tid] = 0x7f800000u; s_mx[tid] = 0u; s_n[tid] = 0; }
+    __syncthreads();
 #pragma unroll
-    for (int o = 16; o > 0; o >>= 1) {
-        mn = fminf(mn, __shfl_xor_sync(0xffffffffu, mn, o));
-        mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
-        nv += __shfl_xor_sync(0xffffffffu, nv, o);
-    }
-    if (lane == 0) {
-        zgrid[(size_t)b * 256 + cell] = make_float2(mn, mx);
-        if (zcnt) zcnt[(size_t)b * 256 + cell] = nv;
-        s_cell[threadIdx.x >> 5] = make_float2(mn, mx);
-    }
-    // depth range of the 2 x 2 blocks of cells: this CTA holds cell rows 2y and 2y + 1 = block row y
-    if (zblk) {
-        __syncthreads();
-        if (threadIdx.x < 8) {
-            const int i = threadIdx.x;
-            const float2 c0 = s_cell[2 * i], c1 = s_cell[2 * i + 1], c2 = s_cell[16 + 2 * i], c3 = s_cell[16 + 2 * i + 1];
-            zblk[(size_t)b * 64 + blockIdx.y * 8 + i] = make_float2(fminf(fminf(c0.x, c1.x), fminf(c2.x, c3.x)),
-                                                                    fmaxf(fmaxf(c0.y, c1.y), fmaxf(c2.y, c3.y)));
+    for (int h = 0; h < 2; ++h) {
+        const int cy = 2 * y + h, r0 = cy * chh, r1 = min(r0 + chh, roi.nrows);
+        for (int c = tid; c < roi.ncols && r0 < r1; c += 256) {
+            const float *col = im.depth + (size_t)(roi.v0 + r0 * stride) * im.depth_pitch + roi.u0 + c * stride;
+            unsigned mn = 0x7f800000u, mx = 0u;
+            int nv = 0;
+            for (int r = r0; r < r1; ++r, col += (size_t)stride * im.depth_pitch) {
+                const float d = __ldg(col);
+                if (d > 0.f && d <= 3.402823466e38f) {         // the validity rule of tile_item
+                    const unsigned u = __float_as_uint(d);
+                    mn = min(mn, u); mx = max(mx, u); ++nv;
+                }
+            }
+            if (nv) {
+                const int slot = h * 16 + min(15, c / cw);
+                atomicMin(&s_mn[slot], mn); atomicMax(&s_mx[slot], mx); atomicAdd(&s_n[slot], nv);
+            }
         }
     }
-    // pixel-ray slopes (the a_u, b_v of the point test) of the first and last column / row of
-    // every cell column / row: [a_lo[16] a_hi[16] b_lo[16] b_hi[16]] per box
-    if (cellab && blockIdx.y == 0 && threadIdx.x < 16) {
-        const int i = threadIdx.x;
+    __syncthreads();
+    if (tid < 32) {
+        const int cell = y * 32 + tid;                        // rows 2y (slots 0..15) and 2y + 1 (16..31)
+        const bool any = s_n[tid] > 0;
+        zgrid[(size_t)b * 256 + cell] = make_float2(any ? __uint_as_float(s_mn[tid]) : INFINITY,
+                                                    any ? __uint_as_float(s_mx[tid]) : -INFINITY);
+        if (zcnt) zcnt[(size_t)b * 256 + cell] = s_n[tid];
+    }
+    if (zblk && tid < 8) {
+        const int i = tid;
+        unsigned mn = min(min(s_mn[2 * i], s_mn[2 * i + 1]), min(s_mn[16 + 2 * i], s_mn[16 + 2 * i + 1]));
+        unsigned mx = max(max(s_mx[2 * i], s_mx[2 * i + 1]), max(s_mx[16 + 2 * i], s_mx[16 + 2 * i + 1]));
+        const bool any = (s_n[2 * i] + s_n[2 * i + 1] + s_n[16 + 2 * i] + s_n[16 + 2 * i + 1]) > 0;
+        zblk[(size_t)b * 64 + y * 8 + i] = make_float2(any ? __uint_as_float(mn) : INFINITY, any ? __uint_as_float(mx) : -INFINITY);
+    }
+    if (cellab && y == 0 && tid >= 32 && tid < 48) {
+        const int i = tid - 32;
         const int cc0 = min(i * cw, max(roi.ncols - 1, 0)), cc1 = max(min(i * cw + cw, roi.ncols) - 1, cc0);
         const int rr0 = min(i * chh, max(roi.nrows - 1, 0)), rr1 = max(min(i * chh + chh, roi.nrows) - 1, rr0);
         float *ab = cellab + (size_t)b * 64;

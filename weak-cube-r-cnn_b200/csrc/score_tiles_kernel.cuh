@@ -462,15 +462,20 @@ __device__ __forceinline__ float fill_product(const ScoreArgs &a, const ChunkCtx
 // hull fill of up to 32 proposals of the chunk (q = the lane's proposal or -1) whose bound is in
 // `ub`; returns the lane's actual score (-inf without a proposal) and stores it to ws.ub
 __device__ __forceinline__ float chunk_fill(const ScoreArgs &a, int b, const WcrBox &bx, const WcrImage &im,
-                                            const ChunkCtx &c, int chunk, int q, float ub, float *wbuf, int lane)
+                                            const ChunkCtx &c, int chunk, int q, float ub, float *wbuf, int lane,
+                                            bool known = false)
 {
-    const unsigned have = __ballot_sync(0xffffffffu, q >= 0);
-    if (lane == 0) atomicAdd(a.ws.hulls, (unsigned long long)__popc(have));
-    seg_group(a.src, a.seg_bits + a.seg_off[b], a.ws.segcnt, b, bx, im, chunk, q, wbuf, lane);
+    // known: ws.segcnt already holds this lane's proposal (filled by the first pass's epilogue)
+    const int qf = known ? -1 : q;
+    const unsigned have = __ballot_sync(0xffffffffu, qf >= 0);
+    if (have) {
+        if (lane == 0) atomicAdd(a.ws.hulls, (unsigned long long)__popc(have));
+        seg_group(a.src, a.seg_bits + a.seg_off[b], a.ws.segcnt, b, bx, im, chunk, qf, wbuf, lane);
+    }
     __syncwarp();
     float actual = -INFINITY;
     if (q >= 0) {
-        const int2 c2 = a.ws.segcnt[c.cbase + q];          // written by this very lane
+        const int2 c2 = __ldcg(a.ws.segcnt + c.cbase + q);  // written by this very lane, or earlier (known)
         const float sseg = seg_ratio(c2.x, c2.y, c.area, a.sc.seg_mode);
         actual = ub * ipow(shape_term(sseg, a.sc.map_beta), a.sc.e_seg);   // the product prop_terms forms
         __stcg(a.ws.ub + c.cbase + q, actual);
@@ -612,7 +617,9 @@ __device__ __forceinline__ void chunk_epilogue_warp(const ScoreArgs &a, int b, c
     float T = -INFINITY;
     if (__any_sync(0xffffffffu, q >= 0)) {
         if (a.seg_tight && q >= 0) q_ub = fill_product(a, c, q);
-        const float actual = chunk_fill(a, b, bx, im, c, chunk, q, q_ub, wbuf, lane);
+        const bool known = a.pts_lazy && q >= 0 &&
+                           ((__ldcg(a.ws.evald + ((size_t)b * a.n_chunks + chunk) * 32 + (q >> 5)) >> (q & 31)) & 1u);
+        const float actual = chunk_fill(a, b, bx, im, c, chunk, q, q_ub, wbuf, lane, known);
         // T = k-th largest actual score of the first batch (rank by counting; ties by lane)
         int rank = 0;
         for (int l = 0; l < 32; ++l) {
@@ -628,7 +635,16 @@ __device__ __forceinline__ void chunk_epilogue_warp(const ScoreArgs &a, int b, c
 #pragma unroll 1
     for (int i = 0; i < SC_CHUNK / 32; ++i) {
         const float vv = sc[i * 32 + lane];
-        const bool cnd = !((taken >> i) & 1u) && vv > 0.f && vv >= T;
+        bool cnd = !((taken >> i) & 1u) && vv > 0.f && vv >= T;
+        if (a.pts_lazy && cnd && a.seg_tight &&
+            ((__ldcg(a.ws.evald + ((size_t)b * a.n_chunks + chunk) * 32 + i) >> lane) & 1u)) {
+            // its hull was filled by the first pass's epilogue: the actual score, no batch
+            const int q2 = i * 32 + lane;
+            const int2 c2 = __ldcg(a.ws.segcnt + c.cbase + q2);
+            const float sseg = seg_ratio(c2.x, c2.y, c.area, a.sc.seg_mode);
+            __stcg(a.ws.ub + c.cbase + q2, fill_product(a, c, q2) * ipow(shape_term(sseg, a.sc.map_beta), a.sc.e_seg));
+            cnd = false;
+        }
         const unsigned bm = __ballot_sync(0xffffffffu, cnd);
         if (cnd) cl[n_cand + __popc(bm & ((1u << lane) - 1u))] = (uint16_t)(i * 32 + lane);
         n_cand += __popc(bm);
@@ -747,6 +763,8 @@ __device__ __forceinline__ void chunk_epilogue_first(const ScoreArgs &a, int b, 
         }
         if (__any_sync(0xffffffffu, q >= 0)) {
             const float actual = chunk_fill(a, b, bx, im, c, chunk, q, q_ub, wbuf, lane);
+            // the final epilogue will not fill these hulls again
+            if (q >= 0) atomicOr(a.ws.evald + (size_t)bc * 32 + (q >> 5), 1u << (q & 31));
             int rank = 0;
             for (int l = 0; l < 32; ++l) {
                 const float v = __shfl_sync(0xffffffffu, actual, l);
@@ -822,9 +840,16 @@ template <int WARPS, int MINB, int GRP, bool F2, bool ICNT = false>
 __global__ void __launch_bounds__(WARPS * 32, MINB) score_tiles_kernel(const ScoreArgs a)
 {
     __shared__ __align__(16) float s_wbuf[WARPS][TL_WBUF];   // per-warp scratch: hulls / scores
+    __shared__ int s_prefix[2048];                            // item prefix of up to 2047 boxes: the decode's
+                                                              // binary search then never leaves the SM
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
     float *wbuf = s_wbuf[wid];
-    const int *__restrict__ prefix = a.ws.item_prefix;
+    const int *prefix = a.ws.item_prefix;
+    if (a.n_boxes + 1 <= 2048) {
+        for (int i = threadIdx.x; i <= a.n_boxes; i += WARPS * 32) s_prefix[i] = a.ws.item_prefix[i];
+        __syncthreads();                                      // the only CTA-wide barrier, before any warp diverges
+        prefix = s_prefix;
+    }
     const bool use_pts = a.sc.e_pts > 0, use_seg = a.sc.e_seg > 0;
     const int total = prefix[a.n_boxes];
     const int subs = SC_CHUNK / a.ps;   // tile items per (chunk, tile)
