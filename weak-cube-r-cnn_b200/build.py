@@ -1,6 +1,7 @@
 """Build libwcr_b200.so (hand-written CUDA for sm_100a) in-tree with nvcc.
 
     python weak-cube-r-cnn_b200/build.py [--force]
+    python weak-cube-r-cnn_b200/build.py --prof      # + libwcr_b200_prof.so (phase cycle counters, diagnostics)
 
 Flags that matter:
   -gencode arch=compute_100a,code=sm_100a   B200 only, no PTX fallback for others
@@ -83,5 +84,23 @@ def build(force: bool = False, verbose: bool = False) -> str:
     return OUT
 
 
+def build_prof() -> str:
+    """libwcr_b200_prof.so: the product sources with -DWCR_PROFILE_PHASES (score_tiles_kernel adds up
+    the SM cycles of its phases in the workspace header). Diagnostics only
+    (tools/diag_score.py --lib=libwcr_b200_prof.so); never loaded by the package."""
+    build()
+    nvcc = os.environ.get("NVCC", "nvcc")
+    out = os.path.join(OUT_DIR, "libwcr_b200_prof.so")
+    obj = os.path.join(OUT_DIR, "score_prof.o")
+    subprocess.check_call([nvcc, *NVCC_FLAGS, "-DWCR_PROFILE_PHASES", "-c", os.path.join(CSRC, "score.cu"), "-o", obj])
+    objs = [obj if os.path.basename(s)[:-3] == "score" else os.path.join(OUT_DIR, os.path.basename(s)[:-3] + ".o")
+            for s in sources()]
+    subprocess.check_call([nvcc, "-gencode", "arch=compute_100a,code=sm_100a", "-shared", "-o", out, *objs, "-lcudart"])
+    return out
+
+
 if __name__ == "__main__":
-    print(build(force="--force" in sys.argv, verbose="-v" in sys.argv))
+    if "--prof" in sys.argv:
+        print(build_prof())
+    else:
+        print(build(force="--force" in sys.argv, verbose="-v" in sys.argv))

@@ -103,7 +103,7 @@ struct ScoreWs {
     int *dynq;           // [3] at byte 24: dynamic hull-batch queue head, tail, chunks through phase A
     int *queue_b;        // [1] at byte 36: next second-pass tile item (point term on demand)
     unsigned long long *pruned;    // [1] at byte 40: proposals never tested against the depth points
-    int *segq;           // [n_boxes * n_chunks * 32] published batches (code + 1; 0 = not yet written)
+    int *segq;           // [n_boxes * n_chunks * 128] published batches (code + 1; 0 = not yet written)
     int *seg_pending;    // [n_boxes][n_chunks] retired batches per chunk
     int *ncand;          // [n_boxes][n_chunks] candidates per chunk
     uint16_t *candlist;  // [n_boxes][n_chunks][SC_CHUNK] candidate proposals (index in the chunk)
@@ -232,7 +232,7 @@ size_t carve(void *base, int n_boxes, int N, int k, bool need_cubes, bool need_s
     int *done_box = (int *)take((size_t)n_boxes * sizeof(int));
     int *npts = (int *)take((size_t)n_boxes * nc * sizeof(int));
     int *count = (int *)take((size_t)n_boxes * N * sizeof(int));
-    int *segq = (int *)take(need_seg ? (size_t)n_boxes * nc * 32 * sizeof(int) : 0);
+    int *segq = (int *)take(need_seg ? (size_t)n_boxes * nc * 128 * sizeof(int) : 0);
     int *seg_pending = (int *)take(need_seg ? (size_t)n_boxes * nc * sizeof(int) : 0);
     int *done_b = (int *)take((size_t)n_boxes * nc * sizeof(int));
     int *bready = (int *)take((size_t)n_boxes * nc * sizeof(int));

@@ -593,8 +593,46 @@ __device__ __forceinline__ void chunk_epilogue_warp(const ScoreArgs &a, int b, c
         }
     }
     __syncwarp();
-    // the 32 best positive bounds (non-destructive arg-max rounds; bit i of `taken` <-> loc i*32+lane)
-    unsigned taken = 0u;
+    unsigned taken = 0u;   // bit i <-> loc i*32+lane: evaluated before the candidates are cut
+    float T = -INFINITY;
+    if (a.pts_lazy && a.seg_tight) {
+        // Point term on demand: the first pass's epilogue has already filled the hulls of its 32
+        // best proposals (ws.evald) -- the chunk's likeliest winners. Their actual scores give T
+        // without a single fill on this warp's critical path; everything else that can still
+        // reach T goes to the batches.
+        float *kv = wbuf;                                  // hull scratch, idle here
+        int nk = 0;
+#pragma unroll 1
+        for (int i = 0; i < SC_CHUNK / 32; ++i) {
+            const unsigned evw = __ldcg(a.ws.evald + ((size_t)b * a.n_chunks + chunk) * 32 + i);   // uniform
+            if (evw == 0u) continue;
+            const bool kn = (evw >> lane) & 1u;
+            float act = -INFINITY;
+            if (kn) {
+                const int q2 = i * 32 + lane;
+                const int2 c2 = __ldcg(a.ws.segcnt + c.cbase + q2);
+                const float sseg = seg_ratio(c2.x, c2.y, c.area, a.sc.seg_mode);
+                act = fill_product(a, c, q2) * ipow(shape_term(sseg, a.sc.map_beta), a.sc.e_seg);
+                __stcg(a.ws.ub + c.cbase + q2, act);
+                sc[q2] = act;
+                taken |= 1u << i;
+            }
+            const unsigned bm = __ballot_sync(0xffffffffu, kn);
+            if (kn) kv[nk + __popc(bm & ((1u << lane) - 1u))] = act;
+            nk += __popc(bm);
+        }
+        __syncwarp();
+        const float mine = lane < nk ? kv[lane] : -INFINITY;   // nk <= 32: one batch was filled
+        int rank = 0;
+        for (int l = 0; l < 32; ++l) {
+            const float v = __shfl_sync(0xffffffffu, mine, l);
+            rank += (v > mine) || (v == mine && l < lane);
+        }
+        const unsigned kth = __ballot_sync(0xffffffffu, rank == a.k - 1 && mine > -INFINITY);
+        if (kth) T = __shfl_sync(0xffffffffu, mine, __ffs(kth) - 1);
+        __syncwarp();
+    } else {
+    // the 32 best positive bounds (non-destructive arg-max rounds)
     int q = -1;
     float q_ub = 0.f;
     for (int r = 0; r < 32; ++r) {
@@ -614,12 +652,9 @@ __device__ __forceinline__ void chunk_epilogue_warp(const ScoreArgs &a, int b, c
         if ((bi & 31) == lane) taken |= 1u << (bi >> 5);
         if (lane == r) { q = bi; q_ub = bvv; }
     }
-    float T = -INFINITY;
     if (__any_sync(0xffffffffu, q >= 0)) {
         if (a.seg_tight && q >= 0) q_ub = fill_product(a, c, q);
-        const bool known = a.pts_lazy && q >= 0 &&
-                           ((__ldcg(a.ws.evald + ((size_t)b * a.n_chunks + chunk) * 32 + (q >> 5)) >> (q & 31)) & 1u);
-        const float actual = chunk_fill(a, b, bx, im, c, chunk, q, q_ub, wbuf, lane, known);
+        const float actual = chunk_fill(a, b, bx, im, c, chunk, q, q_ub, wbuf, lane);
         // T = k-th largest actual score of the first batch (rank by counting; ties by lane)
         int rank = 0;
         for (int l = 0; l < 32; ++l) {
@@ -629,40 +664,37 @@ __device__ __forceinline__ void chunk_epilogue_warp(const ScoreArgs &a, int b, c
         const unsigned kth = __ballot_sync(0xffffffffu, rank == a.k - 1 && actual > -INFINITY);
         if (kth) T = __shfl_sync(0xffffffffu, actual, __ffs(kth) - 1);
     }
+    }
     // candidates: not in the first batch, positive bound, bound >= T
     uint16_t *cl = a.ws.candlist + ((size_t)b * a.n_chunks + chunk) * SC_CHUNK;
     int n_cand = 0;
 #pragma unroll 1
     for (int i = 0; i < SC_CHUNK / 32; ++i) {
         const float vv = sc[i * 32 + lane];
-        bool cnd = !((taken >> i) & 1u) && vv > 0.f && vv >= T;
-        if (a.pts_lazy && cnd && a.seg_tight &&
-            ((__ldcg(a.ws.evald + ((size_t)b * a.n_chunks + chunk) * 32 + i) >> lane) & 1u)) {
-            // its hull was filled by the first pass's epilogue: the actual score, no batch
-            const int q2 = i * 32 + lane;
-            const int2 c2 = __ldcg(a.ws.segcnt + c.cbase + q2);
-            const float sseg = seg_ratio(c2.x, c2.y, c.area, a.sc.seg_mode);
-            __stcg(a.ws.ub + c.cbase + q2, fill_product(a, c, q2) * ipow(shape_term(sseg, a.sc.map_beta), a.sc.e_seg));
-            cnd = false;
-        }
+        const bool cnd = !((taken >> i) & 1u) && vv > 0.f && vv >= T;
         const unsigned bm = __ballot_sync(0xffffffffu, cnd);
         if (cnd) cl[n_cand + __popc(bm & ((1u << lane) - 1u))] = (uint16_t)(i * 32 + lane);
         n_cand += __popc(bm);
     }
-    const int n_batches = (n_cand + 31) >> 5;
+    // Batches of 32 hulls while tile items remain (a warp walks its 32 hulls one after the other,
+    // ~8 us each); once the static queues have run dry the rest of the grid is waiting for exactly
+    // these hulls, and batches of 8 put four times as many warps on them.
+    const int claimed = *((volatile int *)(a.pts_lazy ? a.ws.queue_b : a.ws.queue));
+    const int bs = claimed >= __ldg(a.ws.item_prefix + a.n_boxes) ? 8 : 32;
+    const int n_batches = (n_cand + bs - 1) / bs;            // <= 128
     if (n_batches == 0) {
         __threadfence();                                     // first-batch scores were stored by other lanes
         __syncwarp();
         chunk_finalize_lazy(a, b, bx, im, c, chunk, wbuf, lane);
     } else {
         const int bc = b * a.n_chunks + chunk;
-        if (lane == 0) { a.ws.ncand[bc] = n_cand; }
+        if (lane == 0) { a.ws.ncand[bc] = n_cand | (bs << 16); }
         __threadfence();                                     // bounds, first-batch scores, list, count
         __syncwarp();
         if (lane == 0) {
             const int start = atomicAdd(a.ws.dynq + 1, n_batches);      // reserve
             for (int i = 0; i < n_batches; ++i)
-                *((volatile int *)a.ws.segq + start + i) = bc * 32 + i + 1;   // publish (0 = not yet)
+                *((volatile int *)a.ws.segq + start + i) = bc * 128 + i + 1;  // publish (0 = not yet)
         }
     }
     __threadfence();
@@ -673,24 +705,25 @@ __device__ __forceinline__ void chunk_epilogue_warp(const ScoreArgs &a, int b, c
 // One entry of the dynamic queue: batch `batch` of the candidates of (box, chunk).
 __device__ __forceinline__ void dyn_seg_batch(const ScoreArgs &a, int code, float *wbuf, int lane)
 {
-    const int bc = code >> 5, batch = code & 31;
+    const int bc = code >> 7, batch = code & 127;
     const int b = bc / a.n_chunks, chunk = bc - b * a.n_chunks;
     const WcrBox bx = a.boxes[b];
     const WcrImage im = a.images[bx.image];
     const ChunkCtx c = chunk_ctx(a, b, bx, im, chunk, lane);
-    const int n_cand = __ldcg(a.ws.ncand + bc);
+    const int nc_bs = __ldcg(a.ws.ncand + bc);
+    const int n_cand = nc_bs & 0xffff, bs = nc_bs >> 16;     // candidates, hulls per batch (8 or 32)
     const uint16_t *cl = a.ws.candlist + (size_t)bc * SC_CHUNK;
     int q = -1;
     float ub = 0.f;
-    if (batch * 32 + lane < n_cand) {
-        q = (int)__ldcg(cl + batch * 32 + lane);
+    if (lane < bs && batch * bs + lane < n_cand) {
+        q = (int)__ldcg(cl + batch * bs + lane);
         ub = a.seg_tight ? fill_product(a, c, q) : __ldcg(a.ws.ub + c.cbase + q);
     }
     chunk_fill(a, b, bx, im, c, chunk, q, ub, wbuf, lane);
     __threadfence();
     __syncwarp();
     int last = 0;
-    if (lane == 0) last = (atomicAdd(a.ws.seg_pending + bc, 1) == ((n_cand + 31) >> 5) - 1);
+    if (lane == 0) last = (atomicAdd(a.ws.seg_pending + bc, 1) == (n_cand + bs - 1) / bs - 1);
     last = __shfl_sync(0xffffffffu, last, 0);
     if (!last) return;
     __threadfence();
@@ -866,7 +899,7 @@ __global__ void __launch_bounds__(WARPS * 32, MINB) score_tiles_kernel(const Sco
     bool seg_left = seg_total > 0, tile_left = true, pass2_left = a.pts_lazy != 0;
     const int total_chunks = a.n_boxes * a.n_chunks;
     volatile int *dynq = a.ws.dynq;   // [0] tickets drawn, [1] tail (reserved), [2] chunks through phase A
-    const long long seg_cap_ll = (long long)total_chunks * 32;
+    const long long seg_cap_ll = (long long)total_chunks * 128;
     const int seg_cap = seg_cap_ll > 0x7fffffffLL ? 0x7fffffff : (int)seg_cap_ll;   // entries of ws.segq
     int my_ticket = -1;               // lane 0: queue index this warp owns (-1: none)
     long long ph_loop = 0;
