@@ -108,7 +108,8 @@ struct ScoreWs {
     int *ncand;          // [n_boxes][n_chunks] candidates per chunk
     uint16_t *candlist;  // [n_boxes][n_chunks][SC_CHUNK] candidate proposals (index in the chunk)
     float *ub;           // [n_boxes][N] score bounds, overwritten by actual scores as hulls are filled
-    int *item_prefix;    // [n_boxes + 1] exclusive prefix of items per box
+    int *item_prefix;    // [n_boxes + 1] exclusive prefix of items per box, in serving order
+    int *box_order;      // [n_boxes] box served at each position (largest first)
     int *done_chunk;     // [n_boxes][n_chunks] retired items per (box, chunk)
     int *done_box;       // [n_boxes] retired chunks per box
     int *npts;           // [n_boxes][n_chunks] valid depth points (P_b), one copy per chunk
@@ -242,6 +243,7 @@ size_t carve(void *base, int n_boxes, int N, int k, bool need_cubes, bool need_s
     uint16_t *candlist = (uint16_t *)take(need_seg ? (size_t)n_boxes * nc * wcr::SC_CHUNK * sizeof(uint16_t) : 0);
     float *ub = (float *)take(need_seg ? (size_t)n_boxes * N * sizeof(float) : 0);
     int *prefix = (int *)take((size_t)(n_boxes + 1) * sizeof(int));
+    int *box_order = (int *)take((size_t)n_boxes * sizeof(int));
     float *cand = (float *)take(nc > 1 ? (size_t)n_boxes * nc * k * WCR_RECORD_FLOATS * sizeof(float) : 0);
     float *cubes = (float *)take(need_cubes ? (size_t)n_boxes * N * 15 * sizeof(float) : 0);
     int2 *segcnt = (int2 *)take(need_seg ? (size_t)n_boxes * N * sizeof(int2) : 0);
@@ -266,7 +268,7 @@ size_t carve(void *base, int n_boxes, int N, int k, bool need_cubes, bool need_s
         ws->hulls = (unsigned long long *)(queue ? (char *)queue + 16 : nullptr);
         ws->dynq = (int *)(queue ? (char *)queue + 24 : nullptr);
         ws->segq = segq; ws->seg_pending = seg_pending; ws->ncand = ncand; ws->candlist = candlist; ws->ub = ub; ws->done_chunk = done_chunk; ws->done_box = done_box; ws->npts = npts;
-        ws->count = count; ws->item_prefix = prefix; ws->cand = cand; ws->cubes = cubes;
+        ws->count = count; ws->item_prefix = prefix; ws->box_order = box_order; ws->cand = cand; ws->cubes = cubes;
     }
     return off;
 }
@@ -409,7 +411,7 @@ extern "C" int wcr_score_topk(const WcrImage *images, const WcrBox *boxes, int n
     }
     wcr::score_plan_tiles_kernel<<<1, 1024, 0, st>>>(images, boxes, n_boxes, nc, h_score->point_stride,
                                                      h_score->e_pts > 0, 0, a.grp, wcr::SC_CHUNK / a.ps,
-                                                     a.ws.item_prefix);
+                                                     a.ws.item_prefix, a.ws.box_order);
     WCR_CHECK_LAUNCH("score_plan_tiles_kernel");
     if (h_score->e_pts > 0) {
         wcr::score_zgrid_kernel<<<dim3(n_boxes, 8), 256, 0, st>>>(images, boxes, h_score->point_stride, 1, a.ws.zgrid,

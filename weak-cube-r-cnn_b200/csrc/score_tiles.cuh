@@ -454,21 +454,55 @@ score_order_kernel(const float *__restrict__ key, int N, int n_chunks, uint16_t 
     order[(size_t)bc * SC_CHUNK + t] = (uint16_t)(SC_CHUNK - 1 - (int)(s_v[t] & 0xffffu));
 }
 
-// One CTA: queue items per box -> exclusive prefix (tile path).
+// One CTA: queue items per box -> exclusive prefix (tile path), in the ORDER the boxes are served:
+// boxes with the most tiles first (up to 2048 boxes; beyond that, input order). The grid's last
+// items then belong to small boxes -- short tile items, small hulls -- and the warps run dry within
+// tens of microseconds of each other instead of waiting for one 2000-pixel-wide ROI claimed last.
+// box_order[pos] = box served at position pos; prefix[pos] = first item of that box.
 __global__ void __launch_bounds__(1024)
 score_plan_tiles_kernel(const WcrImage *__restrict__ images, const WcrBox *__restrict__ boxes,
                         int n_boxes, int n_chunks, int stride, int use_pts, int use_seg, int grp, int subs,
-                        int *__restrict__ prefix)
+                        int *__restrict__ prefix, int *__restrict__ box_order)
 {
     __shared__ int s_warp[32];
     __shared__ int s_carry;
+    __shared__ unsigned long long s_key[2048];
     const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+    const bool sorted = n_boxes <= 2048;
+    int K = 32;                                    // slots sorted: the next power of two
+    while (K < n_boxes) K <<= 1;
+    if (sorted) {
+        for (int i = tid; i < K; i += 1024) {
+            unsigned long long v = 0ull;
+            if (i < n_boxes) {
+                const WcrBox bx = boxes[i];
+                const WcrImage im = images[bx.image];
+                const int n = tile_items_per_chunk(tile_geom(bx, im.H, im.W, stride, use_pts != 0, grp), use_seg != 0, subs);
+                v = ((unsigned long long)(unsigned)n << 16) | (unsigned)(2047 - i) | (1ull << 48);   // ties: lower index first
+            }
+            s_key[i] = v;
+        }
+        __syncthreads();
+        for (int k = 2; k <= K; k <<= 1)
+            for (int j = k >> 1; j > 0; j >>= 1) {
+                for (int t = tid; t < K; t += 1024) {
+                    const int p = t ^ j;
+                    if (p > t) {
+                        const unsigned long long x = s_key[t], y = s_key[p];
+                        if (((t & k) == 0) ? x < y : x > y) { s_key[t] = y; s_key[p] = x; }
+                    }
+                }
+                __syncthreads();
+            }
+    }
     if (tid == 0) s_carry = 0;
     __syncthreads();
     for (int base = 0; base < n_boxes; base += 1024) {
-        const int b = base + tid;
+        const int pos = base + tid;
         int n = 0;
-        if (b < n_boxes) {
+        if (pos < n_boxes) {
+            const int b = sorted ? 2047 - (int)(s_key[pos] & 0xffffu) : pos;
+            box_order[pos] = b;
             const WcrBox bx = boxes[b];
             const WcrImage im = images[bx.image];
             n = tile_items_per_chunk(tile_geom(bx, im.H, im.W, stride, use_pts != 0, grp), use_seg != 0, subs) * n_chunks;
@@ -493,7 +527,7 @@ score_plan_tiles_kernel(const WcrImage *__restrict__ images, const WcrBox *__res
         }
         __syncthreads();
         const int carry = s_carry;
-        if (b < n_boxes) prefix[b] = carry + s_warp[wid] + incl - n;
+        if (pos < n_boxes) prefix[pos] = carry + s_warp[wid] + incl - n;
         __syncthreads();
         if (tid == 1023) s_carry = carry + s_warp[wid] + incl;
         __syncthreads();

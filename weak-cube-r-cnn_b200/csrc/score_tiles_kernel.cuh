@@ -967,15 +967,16 @@ __global__ void __launch_bounds__(WARPS * 32, MINB) score_tiles_kernel(const Sco
             if (dn) break;
             continue;
         }
-        int b = 0;
+        int b = 0, pos = 0;   // box, and its position in the serving order (tile queues)
         if (kind == 1) {
             b = item / (a.n_chunks * TL_SEGS);
         } else {
-            int hi = a.n_boxes;   // prefix[b] <= item < prefix[hi]
-            while (hi - b > 1) {
-                const int mid = (b + hi) >> 1;
-                if (prefix[mid] <= item) b = mid; else hi = mid;
+            int hi = a.n_boxes;   // prefix[pos] <= item < prefix[hi]
+            while (hi - pos > 1) {
+                const int mid = (pos + hi) >> 1;
+                if (prefix[mid] <= item) pos = mid; else hi = mid;
             }
+            b = __ldg(a.ws.box_order + pos);
         }
         const WcrBox bx = a.boxes[b];
         const WcrImage im = a.images[bx.image];
@@ -987,7 +988,7 @@ __global__ void __launch_bounds__(WARPS * 32, MINB) score_tiles_kernel(const Sco
             const int r = item - b * (a.n_chunks * TL_SEGS);
             chunk = r / TL_SEGS; seg_grp = r - chunk * TL_SEGS;
         } else {
-            const int local = item - prefix[b];
+            const int local = item - prefix[pos];
             chunk = local / pt; ti = local - chunk * pt;
         }
         const int bc = b * a.n_chunks + chunk;
