@@ -261,6 +261,19 @@ int wcr_score_topk(const WcrImage *images, const WcrBox *boxes, int n_boxes,
                    float *out_records, float *out_scores, float *out_iou, float *out_seg,
                    int32_t *out_count, float *out_proj, int32_t *out_npts,
                    void *ws, void *stream);
+/* wcr_score_topk whose scoring kernel -- the first launch of the chain that reads seg_bits -- waits
+ * for the CUDA event `seg_ready` (cudaEvent_t or NULL) on `stream`: the kernels that prepare the
+ * proposals do not need the masks and overlap a pack / upload still running on another stream
+ * (wcr.pipeline.ShardPipeline). No reference counterpart. */
+int wcr_score_topk_after(const WcrImage *images, const WcrBox *boxes, int n_boxes,
+                   const float *cubes, int N,
+                   const float *priors, const float *normals, const float *z0,
+                   const WcrSampleParams *h_sample, uint64_t seed,
+                   const uint32_t *seg_bits, const int64_t *seg_off,
+                   const WcrScoreParams *h_score, int k,
+                   float *out_records, float *out_scores, float *out_iou, float *out_seg,
+                   int32_t *out_count, float *out_proj, int32_t *out_npts,
+                   void *ws, void *seg_ready, void *stream);
 
 /* Dense per-box object masks (the reference's masks_all_images, roi_heads.py:273, 383-401: one
  * H x W map per object, non-zero == object) -> the seg_bits layout of wcr_score_topk, on the

@@ -312,6 +312,24 @@ extern "C" int wcr_score_topk(const WcrImage *images, const WcrBox *boxes, int n
                               int32_t *out_count, float *out_proj, int32_t *out_npts, void *ws,
                               void *stream)
 {
+    return wcr_score_topk_after(images, boxes, n_boxes, cubes, N, priors, normals, z0, h_sample, seed, seg_bits,
+                                seg_off, h_score, k, out_records, out_scores, out_iou, out_seg, out_count, out_proj,
+                                out_npts, ws, nullptr, stream);
+}
+
+// wcr_score_topk whose scoring kernel -- the first launch that reads seg_bits -- waits for
+// `seg_ready` (a cudaEvent_t, or NULL): the plan, depth-grid, prep and order kernels of the chain do
+// not need the masks and run while another stream is still packing them.
+extern "C" int wcr_score_topk_after(const WcrImage *images, const WcrBox *boxes, int n_boxes,
+                                    const float *cubes, int N, const float *priors,
+                                    const float *normals, const float *z0,
+                                    const WcrSampleParams *h_sample, uint64_t seed,
+                                    const uint32_t *seg_bits, const int64_t *seg_off,
+                                    const WcrScoreParams *h_score, int k, float *out_records,
+                                    float *out_scores, float *out_iou, float *out_seg,
+                                    int32_t *out_count, float *out_proj, int32_t *out_npts, void *ws,
+                                    void *seg_ready, void *stream)
+{
     WCR_CHECK_DEVICE();
     WCR_REQUIRE(images && boxes && h_score && out_records && ws, "wcr_score_topk: null pointer");
     WCR_REQUIRE(n_boxes >= 0 && N >= 1, "wcr_score_topk: bad sizes");
@@ -377,6 +395,7 @@ extern "C" int wcr_score_topk(const WcrImage *images, const WcrBox *boxes, int n
         wcr::score_plan_kernel<<<1, 1024, 0, st>>>(images, boxes, n_boxes, nc, h_score->point_stride,
                                                    h_score->e_pts > 0, a.item_px, a.ws.item_prefix);
         WCR_CHECK_LAUNCH("score_plan_kernel");
+        if (seg_ready) cudaStreamWaitEvent(st, (cudaEvent_t)seg_ready, 0);
         wcr::score_items_kernel<4, 2, 256><<<sms * 2, 256, 0, st>>>(a);
         WCR_CHECK_LAUNCH("score_items_kernel");
         return WCR_OK;
@@ -432,6 +451,10 @@ extern "C" int wcr_score_topk(const WcrImage *images, const WcrBox *boxes, int n
         wcr::score_order_kernel<<<n_boxes * nc, 1024, 0, st>>>(a.ws.okey, N, nc, a.ws.order);
         WCR_CHECK_LAUNCH("score_order_kernel");
     }
+    if (seg_ready) {
+        cudaError_t we = cudaStreamWaitEvent(st, (cudaEvent_t)seg_ready, 0);
+        if (we != cudaSuccess) { wcr::set_error("cudaStreamWaitEvent: %s", cudaGetErrorString(we)); return WCR_ELAUNCH; }
+    }
     // FFMA2 point test, inside indicator on the integer pipe, 3 CTAs x 4 warps per SM
     wcr::score_tiles_kernel<4, 3, 8, true, true><<<sms * 3, 128, 0, st>>>(a);
     WCR_CHECK_LAUNCH("score_tiles_kernel");
@@ -447,9 +470,10 @@ extern "C" int wcr_score_topk(const WcrImage *images, const WcrBox *boxes, int n
 // is what PCIe efficiency hangs on), a funnel shift with the neighbour's word undoes the row's
 // byte misalignment, the lane's four "non-zero" bits are OR-ed across groups of eight lanes into
 // the four output words.
-// One-warp CTAs of at most 32 registers, two independent requests in flight per warp, 32 CTAs per
-// box: PCIe reads want tens of thousands of bytes in flight (a 148-warp "background" shape meant to
-// sit beside the persistent scoring kernel reached 5 GB/s against 32 GB/s and was dropped).
+// At most 32 registers, two independent requests in flight per warp, 4 CTAs x 8 warps per box: PCIe
+// reads want tens of thousands of bytes in flight (a 148-warp "background" shape meant to sit beside
+// the persistent scoring kernel reached 5 GB/s against 32 GB/s and was dropped; one-warp CTAs take
+// all 32 CTA slots of an SM and lock the next shard's prep kernels out).
 namespace wcr {
 // one 128-pixel unit of a row: issue the loads (pack_load), later turn them into 4 words (pack_store)
 __device__ __forceinline__ void pack_geom(const uint8_t *m, const Roi &r, int mask_pitch, int upr, int unit,
@@ -506,7 +530,8 @@ pack_box_masks_kernel(const uint8_t *__restrict__ masks, int64_t mask_stride, in
                       const WcrBox *__restrict__ boxes, int n_boxes, const int64_t *__restrict__ seg_off,
                       uint32_t *__restrict__ out_bits)
 {
-    const int lane = threadIdx.x & 31, step = gridDim.y;
+    const int lane = threadIdx.x & 31, wpc = blockDim.x >> 5, step = gridDim.y * wpc;
+    const int first = blockIdx.y * wpc + (threadIdx.x >> 5);
     for (int b = blockIdx.x; b < n_boxes; b += gridDim.x) {
         const WcrBox bx = boxes[b];
         const WcrImage im = images[bx.image];
@@ -516,7 +541,7 @@ pack_box_masks_kernel(const uint8_t *__restrict__ masks, int64_t mask_stride, in
         const int n_units = nrows * upr;
         const uint8_t *m = masks + (size_t)(mask_idx ? mask_idx[b] : b) * mask_stride;
         uint32_t *out = out_bits + seg_off[b];
-        for (int unit = blockIdx.y; unit < n_units; unit += U * step) {
+        for (int unit = first; unit < n_units; unit += U * step) {
             uint32_t w[U], wx[U];
 #pragma unroll
             for (int i = 0; i < U; ++i)
@@ -538,8 +563,8 @@ static int pack_box_masks_launch(const char *who, const uint8_t *masks, int64_t 
     WCR_REQUIRE(n_boxes >= 0 && mask_pitch >= 1 && mask_stride >= 0, "%s: bad sizes", who);
     if (n_boxes == 0) return WCR_OK;
     WCR_REQUIRE(n_boxes <= 0x7fffffff / 4, "%s: too many boxes", who);
-    // a 640 x 480 ROI is 2400 units of 128 pixels: 32 one-warp CTAs per box keep a small shard busy too
-    wcr::pack_box_masks_kernel<2><<<dim3(n_boxes, 32), 32, 0, (cudaStream_t)stream>>>(
+    // a 640 x 480 ROI is 2400 units of 128 pixels: 4 CTAs x 8 warps per box keep a small shard busy too
+    wcr::pack_box_masks_kernel<2><<<dim3(n_boxes, 4), 256, 0, (cudaStream_t)stream>>>(
         masks, mask_stride, mask_pitch, mask_idx, images, boxes, n_boxes, seg_off, out_bits);
     WCR_CHECK_LAUNCH("pack_box_masks_kernel");
     return WCR_OK;

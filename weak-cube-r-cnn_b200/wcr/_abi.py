@@ -44,6 +44,10 @@ SIGNATURES = {
                                c_void_p, c_void_p, c_u64, c_void_p, c_void_p, c_void_p, c_int,
                                c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
                                c_void_p, c_void_p, c_void_p]),
+    "wcr_score_topk_after": (c_int, [c_void_p, c_void_p, c_int, c_void_p, c_int, c_void_p, c_void_p,
+                                     c_void_p, c_void_p, c_u64, c_void_p, c_void_p, c_void_p, c_int,
+                                     c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
+                                     c_void_p, c_void_p, c_void_p, c_void_p]),
     "wcr_pack_box_masks": (c_int, [c_void_p, c_i64, c_int, c_void_p, c_void_p, c_void_p, c_int, c_void_p,
                                    c_void_p, c_void_p]),
     "wcr_h2d_box_mask_rois": (c_int, [c_void_p, c_void_p, c_i64, c_int, c_void_p, c_void_p, c_int, c_void_p]),

@@ -124,9 +124,18 @@ class ShardRunner:
         return self.h_records.numel() * 4
 
     def upload(self):
+        self.upload_inputs()
+        self.upload_masks()
+
+    def upload_inputs(self):
+        """Depth, ground maps and boxes: everything the kernels ahead of the scoring kernel read."""
         self.d_depth.copy_(self.h_depth, non_blocking=True)
         self.d_ground.copy_(self.h_ground, non_blocking=True)
         self.boxes.table.copy_(self.h_boxes, non_blocking=True)
+
+    def upload_masks(self):
+        """The per-box masks (packed words, or dense maps packed on the device): only the scoring
+        kernel reads them (``step(seg_ready=event)``)."""
         if self.h_seg is not None:
             self.seg.bits.copy_(self.h_seg, non_blocking=True)
         if self.d_seg_dense is not None and self.dense_mode == "copy":
@@ -149,10 +158,12 @@ class ShardRunner:
                 self._h_rois.ctypes.data, None, self.n_boxes, _abi.stream_ptr(self.device)),
                 "wcr_h2d_box_mask_rois")
 
-    def step(self, score_events=None):
+    def step(self, score_events=None, seg_ready=None):
         """Device-resident pass: 5 kernel launches, no host sync, no D2H.
         ``score_events`` = (start, end) torch.cuda.Events recorded around the fused
-        scoring launch (bench.py's roofline timing)."""
+        scoring launch (bench.py's roofline timing). ``seg_ready``: event after which the masks
+        of this step are on the device (``upload_masks`` on another stream); None: already there."""
+        self._seg_ready = seg_ready
         self.normals = ground.normal_vector_from_maps(None, None, None, shard=self.shard,
                                                       seed=self.seed)
         z0 = box_center_depth(self.shard, self.boxes)
@@ -169,7 +180,7 @@ class ShardRunner:
         return score_topk(self.shard, self.boxes, None, self.N, self.score_cfg,
                           priors=self.priors, normals=self.normals, z0=z0,
                           sample_cfg=self.sample_cfg, seed=self.seed, seg=self.seg,
-                          workspace=self.ws)
+                          workspace=self.ws, seg_ready=getattr(self, "_seg_ready", None))
 
     def download(self):
         self.h_records.copy_(self.ws.records[:self.n_boxes], non_blocking=True)
@@ -209,6 +220,7 @@ class ShardPipeline:
         self.s_run = torch.cuda.Stream(dev)
         self.s_down = torch.cuda.Stream(dev)
         n = len(runners)
+        self.ev_in = [torch.cuda.Event() for _ in range(n)]
         self.ev_up = [torch.cuda.Event() for _ in range(n)]
         self.ev_run = [torch.cuda.Event() for _ in range(n)]
         self.ev_down = [torch.cuda.Event() for _ in range(n)]
@@ -226,13 +238,18 @@ class ShardPipeline:
         with torch.cuda.stream(self.s_up):
             if self.pending[k]:
                 self.s_up.wait_event(self.ev_run[k])    # the slot's previous pass has read its inputs
-            r.upload()
+            r.upload_inputs()
+            self.ev_in[k].record(self.s_up)
+            r.upload_masks()                            # only the scoring kernel waits for these
             self.ev_up[k].record(self.s_up)
         with torch.cuda.stream(self.s_run):
-            self.s_run.wait_event(self.ev_up[k])
+            self.s_run.wait_event(self.ev_in[k])
             if self.pending[k]:
                 self.s_run.wait_event(self.ev_down[k])  # the slot's previous records are on the host
-            r.step()
+            dense_on_device = r.d_seg_dense is not None # packed by step() itself on this stream: needs the maps
+            if dense_on_device:
+                self.s_run.wait_event(self.ev_up[k])
+            r.step(seg_ready=None if dense_on_device else self.ev_up[k])
             if self.after_step is not None:
                 self.after_step[k]()
             self.ev_run[k].record(self.s_run)

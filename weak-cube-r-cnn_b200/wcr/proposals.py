@@ -318,9 +318,11 @@ class ScoreWorkspace:
 def score_topk(shard: ImageShard, boxes: BoxTable, cubes: torch.Tensor | None, N: int | None = None,
                cfg: ScoreConfig | None = None, *, priors=None, normals=None, z0=None,
                sample_cfg: ProposalConfig | None = None, seed: int = 0, seg=None,
-               workspace: ScoreWorkspace | None = None, want_all: bool = False):
+               workspace: ScoreWorkspace | None = None, want_all: bool = False, seg_ready=None):
     """Fused scoring + per-box top-k. ``cubes`` (n_boxes, N, 15) or None to sample
     in-kernel (then priors/normals are required; same generator as ``propose``).
+    ``seg_ready``: a recorded ``torch.cuda.Event`` the scoring kernel waits for before it reads
+    ``seg`` (``wcr_score_topk_after``): the masks may still be on their way on another stream.
 
     -> dict(records (n_boxes,k,20) f32 [idx bits, score, cube15, s_iou, s_pts, s_seg],
             idx (n_boxes,k) i32 view, score (n_boxes,k);
@@ -361,13 +363,14 @@ def score_topk(shard: ImageShard, boxes: BoxTable, cubes: torch.Tensor | None, N
         assert seg.n_boxes == nb
     elif cfg.e_seg > 0:
         raise _abi.WcrError("score_topk: e_seg > 0 needs seg=SegMasks(...)")
-    _abi.check(lib.wcr_score_topk(
+    _abi.check(lib.wcr_score_topk_after(
         shard.table.data_ptr(), boxes.table.data_ptr(), nb, _abi.ptr(cubes), N,
         _abi.ptr(priors), _abi.ptr(normals), _abi.ptr(z0), ctypes.byref(sp), int(seed),
         _abi.ptr(seg_bits), _abi.ptr(seg_off), ctypes.byref(sc), cfg.k, rec.data_ptr(),
         _abi.ptr(outs.get("scores")), _abi.ptr(outs.get("iou")), _abi.ptr(outs.get("seg")),
         _abi.ptr(outs.get("count")),
         _abi.ptr(outs.get("proj")), _abi.ptr(outs.get("npts")), workspace.ws.data_ptr(),
+        None if seg_ready is None else ctypes.c_void_p(int(seg_ready.cuda_event)),
         _abi.stream_ptr(dev)), "wcr_score_topk")
     rec = rec[:nb]
     outs["records"] = rec
