@@ -248,10 +248,14 @@ int wcr_sample_cubes(const WcrImage *images, const WcrBox *boxes, int n_boxes,
  *   byte 40 of the workspace holds the number of proposals skipped.
  * wcr_score_bounds_offsets: byte offsets, inside the workspace, of the per-proposal bounds of the
  *   last call that used them: int32 [n_boxes][N] upper bounds of the inside-counts (0x7fffffff =
- *   none) and int32 pairs [n_boxes][N][2] (max |mask & hull|, min |hull|). No reference
+ *   none), int32 pairs [n_boxes][N][2] (max |mask & hull|, min |hull|), uint32 [n_boxes][N] cell
+ *   ranges of the hulls' scan windows in the 32 x 32 mask grid (gx0 | gx1 << 6 | gy0 << 12 |
+ *   gy1 << 18) and the grid's integral tables int32 [n_boxes][33][33] (max |mask & hull| is also
+ *   bounded by the mask pixels of those cells). No reference
  *   counterpart; tests/test_score_bounds_gpu.py checks the bounds against the full evaluation. */
 int64_t wcr_score_workspace_bytes(int n_boxes, int N, int k);
-int wcr_score_bounds_offsets(int n_boxes, int N, int k, int64_t *off_ubcnt, int64_t *off_segb);
+int wcr_score_bounds_offsets(int n_boxes, int N, int k, int64_t *off_ubcnt, int64_t *off_segb,
+                             int64_t *off_segwin, int64_t *off_mint);
 int wcr_score_topk(const WcrImage *images, const WcrBox *boxes, int n_boxes,
                    const float *cubes, int N,
                    const float *priors, const float *normals, const float *z0,

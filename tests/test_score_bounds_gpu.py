@@ -43,7 +43,7 @@ def test_bounds_hold_for_every_proposal(cuda_lib, seed, H, W, clamp):
     nb = cubes.shape[0]
     ws = ScoreWorkspace(nb, N, k, "cuda")
     lazy = score_topk(shard, boxes, cubes, cfg=ScoreConfig(e_seg=1, k=k, pts_eval=2, seg_eval=2), seg=seg, workspace=ws)
-    ub, sb = [t.clone() for t in ws.bounds()]
+    ub, sb, sw, mi = [t.clone() for t in ws.bounds()]
     assert ws.proposals_pruned() > 0
     full = score_topk(shard, boxes, cubes, cfg=ScoreConfig(e_seg=1, k=k), seg=seg, want_all=True)
     assert torch.equal(lazy["records"].view(torch.int32), full["records"].view(torch.int32))
@@ -57,6 +57,14 @@ def test_bounds_hold_for_every_proposal(cuda_lib, seed, H, W, clamp):
     area = torch.tensor([int(np.unpackbits(bits[off[b]:off[b + 1]].view(np.uint8)).sum()) for b in range(nb)],
                         dtype=torch.int64, device="cuda")[:, None]
     iub, blow = sb[..., 0].long(), sb[..., 1].long()
+    # ... |mask & hull| also bounded by the mask pixels of the grid cells the scan window touches
+    gx0, gx1, gy0, gy1 = (sw & 63).long(), ((sw >> 6) & 63).long(), ((sw >> 12) & 63).long(), ((sw >> 18) & 63).long()
+    bi = torch.arange(nb, device="cuda")[:, None].expand(nb, N)
+    mil = mi.long()
+    in_cells = (mil[bi, gy1, gx1] - mil[bi, gy0, gx1]) - (mil[bi, gy1, gx0] - mil[bi, gy0, gx0])
+    assert bool((mil[:, 32, 32] == area[:, 0]).all())            # the table's total is the mask area
+    assert int((in_cells < torch.minimum(iub, area)).sum()) > 0   # ... and it does cut
+    iub = torch.minimum(iub, in_cells)
     i = torch.minimum(iub, area)
     h = torch.maximum(blow, i)
     bound = torch.where(i > 0, i.float() / (area + h - i).clamp(min=1).float(), torch.zeros_like(i, dtype=torch.float32))

@@ -19,8 +19,8 @@ from wcr.pipeline import ShardRunner
 from wcr.proposals import ScoreConfig, score_topk, box_center_depth, propose, box_rois
 
 n_img = int(sys.argv[1]) if len(sys.argv) > 1 and sys.argv[1].isdigit() else 64
-every = 8                                       # study every 8th box
-ims = bench.make_images(n_img, 0, True, None, dense=False)
+every = 16                                      # study every 16th box
+ims = bench.make_images(n_img, 0, True, None, dense="both")
 priors = synth.make_priors()
 K, N = 16, 1000
 r = ShardRunner(ims, N, "cuda", priors=priors, score_cfg=ScoreConfig(k=K, e_seg=1), seed=1234)
@@ -33,6 +33,7 @@ for use_seg in (True, False):
                                seg=r.seg if use_seg else None, want_all=True)
 cubes = propose(r.shard, r.boxes, r.priors, r.normals, N, z0=z0, seed=1234)
 rois = box_rois(r.boxes, r.shard)
+all_masks = [m for im in ims for m in im["seg"]]
 h = r.boxes.host
 tab = r.shard.host_table
 SGN = torch.tensor([[-1, -1, -1], [1, -1, -1], [1, 1, -1], [-1, 1, -1],
@@ -152,7 +153,8 @@ for b in range(0, len(h), every):
     Bpix = ((torch.floor(pj[:, 2]) - torch.ceil(pj[:, 0]) + 3).clamp(min=0) * (torch.floor(pj[:, 3]) - torch.ceil(pj[:, 1]) + 3).clamp(min=0))
     ub_seg = torch.nan_to_num((Bpix / max(M, 1.0)).clamp(max=1.0), nan=1.0)
     Himg, Wimg = r.shard.depths[img].shape
-    qx = px.clamp(0, Wimg - 1); qy = py.clamp(0, Himg - 1)               # (N, 8) clamped corners
+    c0_, c1_ = float(h["clamp0"][b]), float(h["clamp1"][b])               # the reference clamps x with clamp0, y with clamp1
+    qx = px.clamp(0, float(int(c0_ - 1))); qy = py.clamp(0, float(int(c1_ - 1)))   # (N, 8) clamped corners
     FACES = [[0, 1, 2, 3], [4, 5, 6, 7], [0, 1, 5, 4], [1, 2, 6, 5], [2, 3, 7, 6], [3, 0, 4, 7]]
     Af = torch.zeros(N, device="cuda")
     for f in FACES:
@@ -160,7 +162,22 @@ for b in range(0, len(h), every):
         sa = 0.5 * (x_ * y_.roll(-1, 1) - x_.roll(-1, 1) * y_).sum(1)
         Af = torch.maximum(Af, sa.abs())
     bw = qx.max(1).values - qx.min(1).values + 2; bh = qy.max(1).values - qy.min(1).values + 2
-    Blow = (Af - 4 * (bw + bh) - 32).clamp(min=0)
+    outside = bw * (qy.max(1).values - (Himg - 1)).clamp(min=0) + bh * (qx.max(1).values - (Wimg - 1)).clamp(min=0)
+    Blow = (Af * 0.999 - outside * 1.001 - 2 * (bw + 16 + bh + 16) - 16).clamp(min=0)
+    # exact hull area of the clamped corners (scipy), same margins
+    from scipy.spatial import ConvexHull
+    qxc, qyc = qx.cpu().numpy(), qy.cpu().numpy()
+    Ah = np.zeros(N, dtype=np.float32)
+    for n_ in range(N):
+        try:
+            Ah[n_] = ConvexHull(np.stack([qxc[n_], qyc[n_]], 1)).volume
+        except Exception:
+            Ah[n_] = 0.0
+    Ah = torch.from_numpy(Ah).cuda()
+    Blow_h = (Ah * 0.999 - outside * 1.001 - 2 * (bw + 16 + bh + 16) - 16).clamp(min=0)
+    # mask pixels inside the hull's bounding box (integral image of the dense mask)
+    dm = torch.as_tensor(all_masks[b]).cuda().float()
+    integ = torch.zeros((Himg + 1, Wimg + 1), device="cuda"); integ[1:, 1:] = (dm[:Himg, :Wimg] != 0).float().cumsum(0).cumsum(1)
     # inter <= pixels of (hull bbox + margin) inside the ROI
     ix0 = torch.maximum(torch.floor(qx.min(1).values) - 1, torch.tensor(float(u0), device="cuda"))
     ix1 = torch.minimum(torch.ceil(qx.max(1).values) + 1, torch.tensor(float(u1 - 1), device="cuda"))
@@ -170,6 +187,54 @@ for b in range(0, len(h), every):
     istar = torch.minimum(Iub, torch.tensor(M, device="cuda"))
     ub_seg2 = torch.nan_to_num(istar / (M + torch.maximum(Blow, istar) - istar).clamp(min=1), nan=1.0).clamp(max=1)
     ub_seg2 = torch.where(live, ub_seg2, torch.ones_like(ub_seg2))
+    ub_seg3 = torch.nan_to_num(istar / (M + torch.maximum(Blow_h, istar) - istar).clamp(min=1), nan=1.0).clamp(max=1)
+    ub_seg3 = torch.where(live, ub_seg3, torch.ones_like(ub_seg3))
+    nn = lambda t: torch.nan_to_num(t, nan=0.0, posinf=0.0, neginf=0.0)
+    jx0, jx1 = nn(ix0).clamp(0, Wimg - 1).long(), (nn(ix1).clamp(-1, Wimg - 1) + 1).long()
+    jy0, jy1 = nn(iy0).clamp(0, Himg - 1).long(), (nn(iy1).clamp(-1, Himg - 1) + 1).long()
+    Imask = (integ[jy1, jx1] - integ[jy0, jx1] - integ[jy1, jx0] + integ[jy0, jx0]).clamp(min=0)
+    Imask = torch.where((ix1 >= ix0) & (iy1 >= iy0), Imask, torch.zeros_like(Imask))
+    istar4 = torch.minimum(Imask, torch.tensor(M, device="cuda"))
+    ub_seg4 = torch.nan_to_num(istar4 / (M + torch.maximum(Blow_h, istar4) - istar4).clamp(min=1), nan=0.0).clamp(max=1)
+    ub_seg4 = torch.where(live, ub_seg4, torch.ones_like(ub_seg4))
+    # cheap variants: extreme-point quadrilateral as the area bound; mask counts per cell of a 16 x 16 grid
+    ar = torch.arange(N, device="cuda")
+    iL, iR, iB, iT = qx.argmin(1), qx.argmax(1), qy.argmin(1), qy.argmax(1)
+    ex = torch.stack([qx[ar, iL], qx[ar, iB], qx[ar, iR], qx[ar, iT]], 1); ey = torch.stack([qy[ar, iL], qy[ar, iB], qy[ar, iR], qy[ar, iT]], 1)
+    Aq = (0.5 * (ex * ey.roll(-1, 1) - ex.roll(-1, 1) * ey).sum(1)).abs()
+    Blow_q = (torch.maximum(Af, Aq) * 0.999 - outside * 1.001 - 2 * (bw + 16 + bh + 16) - 16).clamp(min=0)
+    nr1, nc1 = v1 - v0, u1 - u0
+    mcw, mch = max(1, (nc1 + 15) >> 4), max(1, (nr1 + 15) >> 4)
+    roi_m = (dm[v0:v1, u0:u1] != 0).float()
+    pad = torch.zeros((16 * mch, 16 * mcw), device="cuda"); pad[:nr1, :nc1] = roi_m
+    cellm = pad.reshape(16, mch, 16, mcw).sum(3).sum(1)                      # (16,16) mask pixels per cell
+    integc = torch.zeros((17, 17), device="cuda"); integc[1:, 1:] = cellm.cumsum(0).cumsum(1)
+    cx0 = ((nn(ix0) - u0).clamp(0, nc1 - 1) // mcw).long().clamp(0, 15); cx1 = ((nn(ix1) - u0).clamp(0, nc1 - 1) // mcw).long().clamp(0, 15) + 1
+    cy0 = ((nn(iy0) - v0).clamp(0, nr1 - 1) // mch).long().clamp(0, 15); cy1 = ((nn(iy1) - v0).clamp(0, nr1 - 1) // mch).long().clamp(0, 15) + 1
+    Icell = integc[cy1, cx1] - integc[cy0, cx1] - integc[cy1, cx0] + integc[cy0, cx0]
+    Icell = torch.where((ix1 >= ix0) & (iy1 >= iy0), Icell, torch.zeros_like(Icell))
+    istar5 = torch.minimum(torch.minimum(Icell, Iub), torch.tensor(M, device="cuda"))
+    ub_seg5 = torch.nan_to_num(istar5 / (M + torch.maximum(Blow_q, istar5) - istar5).clamp(min=1), nan=0.0).clamp(max=1)
+    ub_seg5 = torch.where(live, ub_seg5, torch.ones_like(ub_seg5))
+    ub_seg6 = torch.nan_to_num(istar5 / (M + torch.maximum(Blow, istar5) - istar5).clamp(min=1), nan=0.0).clamp(max=1)
+    ub_seg6 = torch.where(live, ub_seg6, torch.ones_like(ub_seg6))
+    extra = {}
+    for G in (32, 64):
+        gw, gh = max(1, (nc1 + G - 1) // G), max(1, (nr1 + G - 1) // G)
+        padg = torch.zeros((G * gh, G * gw), device="cuda"); padg[:nr1, :nc1] = roi_m
+        cm = padg.reshape(G, gh, G, gw).sum(3).sum(1)
+        ig = torch.zeros((G + 1, G + 1), device="cuda"); ig[1:, 1:] = cm.cumsum(0).cumsum(1)
+        gx0 = ((nn(ix0) - u0).clamp(0, nc1 - 1) // gw).long().clamp(0, G - 1); gx1 = ((nn(ix1) - u0).clamp(0, nc1 - 1) // gw).long().clamp(0, G - 1) + 1
+        gy0 = ((nn(iy0) - v0).clamp(0, nr1 - 1) // gh).long().clamp(0, G - 1); gy1 = ((nn(iy1) - v0).clamp(0, nr1 - 1) // gh).long().clamp(0, G - 1) + 1
+        Ig = ig[gy1, gx1] - ig[gy0, gx1] - ig[gy1, gx0] + ig[gy0, gx0]
+        Ig = torch.where((ix1 >= ix0) & (iy1 >= iy0), Ig, torch.zeros_like(Ig))
+        ist = torch.minimum(torch.minimum(Ig, Iub), torch.tensor(M, device="cuda"))
+        u_ = torch.nan_to_num(ist / (M + torch.maximum(Blow, ist) - ist).clamp(min=1), nan=0.0).clamp(max=1)
+        extra[f"G{G}"] = torch.where(live, u_, torch.ones_like(u_))
+    u_ = torch.nan_to_num(istar4 / (M + torch.maximum(Blow, istar4) - istar4).clamp(min=1), nan=0.0).clamp(max=1)
+    extra["exactI_maxface"] = torch.where(live, u_, torch.ones_like(u_))
+    for nm_, u_ in (("3", ub_seg3), ("4", ub_seg4), ("5", ub_seg5), ("6", ub_seg6)):
+        add("seg/viol_ubseg" + nm_, (outs[True]["seg"][b] > u_ * (1 + 1e-6)).sum(), N)
     vio = outs[True]["seg"][b] > ub_seg2 * (1 + 1e-6)
     if bool(vio.any()) and acc.get("dbg", [0])[0] < 6:
         acc.setdefault("dbg", [0.0, 1.0])[0] += 1
@@ -191,7 +256,7 @@ for b in range(0, len(h), every):
         tag = "seg" if use_seg else "noseg"
         add(f"{tag}/viol_cell", (cnt > ub_cell + 0.5).sum(), N)
         add(f"{tag}/viol_slab", (cnt > ub_slab + 0.5).sum(), N)
-        for name, ub in (("cell", ub_cell), ("slab", ub_slab), ("slab8", ub_slab8), ("slab8+ubseg", ub_slab8), ("slab8+ubseg2", ub_slab8), ("slab8+segoracle", ub_slab8)):
+        for name, ub in (("cell", ub_cell), ("slab", ub_slab), ("slab8", ub_slab8), ("slab8+ubseg", ub_slab8), ("slab8+ubseg2", ub_slab8), ("slab8+ubseg3", ub_slab8), ("slab8+ubseg4", ub_slab8), ("slab8+ubseg5", ub_slab8), ("slab8+ubseg6", ub_slab8), ("slab8+segoracle", ub_slab8)):
             ubs = iou * (ub / max(npts, 1.0)).clamp(max=1)
             if name.endswith("ubseg"):
                 if not use_seg: continue
@@ -199,10 +264,26 @@ for b in range(0, len(h), every):
             if name.endswith("ubseg2"):
                 if not use_seg: continue
                 ubs = ubs * ub_seg2
+            if name.endswith("ubseg3"):
+                if not use_seg: continue
+                ubs = ubs * ub_seg3
+            if name.endswith("ubseg4"):
+                if not use_seg: continue
+                ubs = ubs * ub_seg4
+            if name.endswith("ubseg5"):
+                if not use_seg: continue
+                ubs = ubs * ub_seg5
+            if name.endswith("ubseg6"):
+                if not use_seg: continue
+                ubs = ubs * ub_seg6
             if name.endswith("segoracle"):
                 if not use_seg: continue
                 ubs = ubs * torch.nan_to_num(o["seg"][b], nan=1.0)
-            for PA in (64,):
+            variants = [(name, ubs)]
+            if name == "slab8" and use_seg:
+                variants += [(f"slab8+{k_}", ubs * v_) for k_, v_ in extra.items()]
+            for name, ubs in variants:
+              for PA in (64,):
                 order = ubs.argsort(descending=True)
                 inA = torch.zeros(N, dtype=torch.bool, device="cuda"); inA[order[:PA]] = True
                 TA = sc[inA].topk(K).values[-1]

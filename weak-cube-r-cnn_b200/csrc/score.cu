@@ -129,6 +129,8 @@ struct ScoreWs {
     float *okey;         // [n_boxes][N] ordering key: IoU factor x bound factor
     float2 *zblk;        // [n_boxes][64] depth range of the 2 x 2 blocks of cells
     int2 *segb;          // [n_boxes][N] mask-term bounds: (max |mask & hull|, min |hull|) pixels (a.seg_tight)
+    int *mint;           // [n_boxes][33 * 33] integral table of the mask pixels per cell of a 32 x 32 ROI grid
+    unsigned *segwin;    // [n_boxes][N] cell range of the hull's scan window in that grid (gx0 | gx1 << 6 | gy0 << 12 | gy1 << 18)
     uint16_t *order;     // [n_boxes][n_chunks][SC_CHUNK] chunk proposals by descending key; the first
                          //   pass tests [0, pa), its epilogue compacts the survivors of the rest behind them
     int *done_b;         // [n_boxes][n_chunks] retired second-pass items
@@ -258,9 +260,11 @@ size_t carve(void *base, int n_boxes, int N, int k, bool need_cubes, bool need_s
     float *okey = (float *)take((size_t)n_boxes * N * sizeof(float));
     float2 *zblk = (float2 *)take((size_t)n_boxes * 64 * sizeof(float2));
     int2 *segb = (int2 *)take(need_seg ? (size_t)n_boxes * N * sizeof(int2) : 0);
+    int *mint = (int *)take(need_seg ? (size_t)n_boxes * 33 * 33 * sizeof(int) : 0);
+    unsigned *segwin = (unsigned *)take(need_seg ? (size_t)n_boxes * N * sizeof(unsigned) : 0);
     uint16_t *order = (uint16_t *)take((size_t)n_boxes * nc * wcr::SC_CHUNK * sizeof(uint16_t));
     if (ws) {
-        ws->zcnt = zcnt; ws->cellab = cellab; ws->ubcnt = ubcnt; ws->okey = okey; ws->zblk = zblk; ws->segb = segb; ws->order = order; ws->done_b = done_b; ws->bready = bready; ws->evald = evald;
+        ws->zcnt = zcnt; ws->cellab = cellab; ws->ubcnt = ubcnt; ws->okey = okey; ws->zblk = zblk; ws->segb = segb; ws->mint = mint; ws->segwin = segwin; ws->order = order; ws->done_b = done_b; ws->bready = bready; ws->evald = evald;
         ws->queue_b = (int *)(queue ? (char *)queue + 36 : nullptr);
         ws->pruned = (unsigned long long *)(queue ? (char *)queue + 40 : nullptr);
         ws->segcnt = segcnt; ws->params = params; ws->cullbox = cullbox; ws->zgrid = zgrid; ws->mayhit = mayhit; ws->siou = siou;
@@ -287,9 +291,10 @@ extern "C" int64_t wcr_score_workspace_bytes(int n_boxes, int N, int k)
 
 // Byte offsets, inside a workspace of wcr_score_workspace_bytes(n_boxes, N, k), of the per-proposal
 // bounds the on-demand paths prune with (tests check them against the full evaluation).
-extern "C" int wcr_score_bounds_offsets(int n_boxes, int N, int k, int64_t *off_ubcnt, int64_t *off_segb)
+extern "C" int wcr_score_bounds_offsets(int n_boxes, int N, int k, int64_t *off_ubcnt, int64_t *off_segb,
+                                        int64_t *off_segwin, int64_t *off_mint)
 {
-    if (n_boxes < 0 || N < 1 || k < 1 || !off_ubcnt || !off_segb) return WCR_EINVAL;
+    if (n_boxes < 0 || N < 1 || k < 1 || !off_ubcnt || !off_segb || !off_segwin || !off_mint) return WCR_EINVAL;
     wcr::ScoreWs w;
     char *base = reinterpret_cast<char *>(4096);
 #ifdef WCR_KEEP_BASELINE_KERNEL
@@ -299,6 +304,8 @@ extern "C" int wcr_score_bounds_offsets(int n_boxes, int N, int k, int64_t *off_
 #endif
     *off_ubcnt = (int64_t)((char *)w.ubcnt - base);
     *off_segb = (int64_t)((char *)w.segb - base);
+    *off_segwin = (int64_t)((char *)w.segwin - base);
+    *off_mint = (int64_t)((char *)w.mint - base);
     return WCR_OK;
 }
 
@@ -444,7 +451,7 @@ extern "C" int wcr_score_topk_after(const WcrImage *images, const WcrBox *boxes,
                                                       h_score->point_stride, h_score->e_pts > 0, a.ws.params, a.ws.cullbox,
                                                       a.ws.zgrid, a.ws.mayhit, a.siou_ready ? a.ws.siou : nullptr,
                                                       a.pts_lazy ? a.ws.zcnt : nullptr, a.ws.cellab, a.ws.ubcnt, a.ws.okey, a.ws.zblk, a.seg_tight ? a.ws.segb : nullptr,
-                                                      h_score->e_iou, h_score->e_pts);
+                                                      a.ws.segwin, h_score->e_iou, h_score->e_pts);
         WCR_CHECK_LAUNCH("score_prep_kernel");
     }
     if (a.pts_lazy) {
@@ -454,6 +461,10 @@ extern "C" int wcr_score_topk_after(const WcrImage *images, const WcrBox *boxes,
     if (seg_ready) {
         cudaError_t we = cudaStreamWaitEvent(st, (cudaEvent_t)seg_ready, 0);
         if (we != cudaSuccess) { wcr::set_error("cudaStreamWaitEvent: %s", cudaGetErrorString(we)); return WCR_ELAUNCH; }
+    }
+    if (a.seg_tight) {     // mask pixels per cell of the ROI grid, for the epilogues' bound of |mask & hull|
+        wcr::score_maskgrid_kernel<<<n_boxes, wcr::MG * wcr::MG, 0, st>>>(images, boxes, seg_bits, seg_off, a.ws.mint);
+        WCR_CHECK_LAUNCH("score_maskgrid_kernel");
     }
     // FFMA2 point test, inside indicator on the integer pipe, 3 CTAs x 4 warps per SM
     wcr::score_tiles_kernel<4, 3, 8, true, true><<<sms * 3, 128, 0, st>>>(a);

@@ -153,6 +153,49 @@ score_zgrid_kernel(const WcrImage *__restrict__ images, const WcrBox *__restrict
     }
 }
 
+// Mask pixels per cell of a 32 x 32 grid over a box's mask ROI, as a 33 x 33 integral table
+// (mint[b][cy * 33 + cx] = mask pixels in cell rows < cy and cell columns < cx): the prep kernel
+// bounds |mask & hull| by the mask pixels of the cells the hull's bounding box touches -- four loads
+// per proposal. One CTA per box, one thread per cell (popcounts of the cell's bit ranges), then two
+// prefix passes in shared memory.
+constexpr int MG = 32;
+__global__ void __launch_bounds__(MG * MG)
+score_maskgrid_kernel(const WcrImage *__restrict__ images, const WcrBox *__restrict__ boxes,
+                      const uint32_t *__restrict__ seg_bits, const int64_t *__restrict__ seg_off,
+                      int *__restrict__ mint)
+{
+    __shared__ int s_c[MG][MG + 1];
+    const int b = blockIdx.x, cx = threadIdx.x & (MG - 1), cy = threadIdx.x / MG;
+    const WcrBox bx = boxes[b];
+    const WcrImage im = images[bx.image];
+    const Roi r = box_roi(bx, im.H, im.W, 1, true);
+    SegBox sb;
+    sb.u0 = r.u0; sb.v0 = r.v0; sb.ncols = r.ncols; sb.nrows = r.ncols > 0 ? r.nrows : 0;
+    sb.wpr = (sb.ncols + 31) >> 5; sb.bits = seg_bits + seg_off[b]; sb.area = 0;
+    const int gw = max(1, (sb.ncols + MG - 1) / MG), gh = max(1, (sb.nrows + MG - 1) / MG);
+    const int c0 = cx * gw, c1 = min(c0 + gw, sb.ncols) - 1, r0 = cy * gh, r1 = min(r0 + gh, sb.nrows);
+    int n = 0;
+    if (c0 <= c1)
+        for (int row = r0; row < r1; ++row) n += seg_popc_range(sb, row, c0, c1);
+    s_c[cy][cx] = n;
+    __syncthreads();
+    if (cy == 0) {          // thread cx: running sum down column cx
+        int a_ = 0;
+        for (int i = 0; i < MG; ++i) { a_ += s_c[i][cx]; s_c[i][cx] = a_; }
+    }
+    __syncthreads();
+    if (cx == 0) {          // thread cy: running sum along row cy
+        int a_ = 0;
+        for (int i = 0; i < MG; ++i) { a_ += s_c[cy][i]; s_c[cy][i] = a_; }
+    }
+    __syncthreads();
+    int *out = mint + (size_t)b * (MG + 1) * (MG + 1);
+    out[(cy + 1) * (MG + 1) + cx + 1] = s_c[cy][cx];
+    if (cy == 0) out[cx + 1] = 0;
+    if (cx == 0) out[(cy + 1) * (MG + 1)] = 0;
+    if (threadIdx.x == 0) out[0] = 0;
+}
+
 // One thread per proposal: test constants (same expressions as score_items_kernel's
 // prologue) and the conservative cull box.
 __global__ void __launch_bounds__(256)
@@ -162,7 +205,7 @@ score_prep_kernel(const WcrImage *__restrict__ images, const WcrBox *__restrict_
                   const float2 *__restrict__ zgrid, uint8_t *__restrict__ out_mayhit,
                   float *__restrict__ out_siou, const int *__restrict__ zcnt, const float *__restrict__ cellab,
                   int *__restrict__ out_ubcnt, float *__restrict__ out_key, const float2 *__restrict__ zblk,
-                  int2 *__restrict__ out_segb, int e_iou, int e_pts)
+                  int2 *__restrict__ out_segb, unsigned *__restrict__ out_segwin, int e_iou, int e_pts)
 {
     // (threads past the last proposal recompute proposal N - 1 and store nothing: the bound section
     // below is warp-cooperative)
@@ -220,12 +263,22 @@ score_prep_kernel(const WcrImage *__restrict__ images, const WcrBox *__restrict_
                 mny = fminf(mny, sy[i]); mxy = fmaxf(mxy, sy[i]);
             }
             int2 sb2 = make_int2(0x7fffffff, 0);
+            unsigned swin = 0u | (32u << 6) | (0u << 12) | (32u << 18);   // whole grid: no cut
             if (fin && mxx < 1.0e6f && mxy < 1.0e6f) {
                 const Roi r1 = box_roi(bx, im.H, im.W, 1, true);
                 const int nr1 = r1.ncols > 0 ? r1.nrows : 0;
                 const int x0 = max((int)floorf(mnx) - 1, r1.u0), x1 = min((int)ceilf(mxx) + 9, r1.u0 + r1.ncols - 1);
                 const int y0 = max((int)floorf(mny) - 1, r1.v0), y1 = min((int)ceilf(mxy) + 9, r1.v0 + nr1 - 1);
                 sb2.x = (x1 >= x0 && y1 >= y0) ? (x1 - x0 + 1) * (y1 - y0 + 1) : 0;
+                // ... and, in the epilogues (the masks may still be on their way here), by the mask
+                // pixels of the cells of a 32 x 32 grid that window touches (score_maskgrid_kernel):
+                // the window's cell range, 6 bits each
+                if (sb2.x > 0) {
+                    const int gw = max(1, (r1.ncols + MG - 1) / MG), gh = max(1, (nr1 + MG - 1) / MG);
+                    const int gx0 = min(MG - 1, (x0 - r1.u0) / gw), gx1 = min(MG - 1, (x1 - r1.u0) / gw) + 1;
+                    const int gy0 = min(MG - 1, (y0 - r1.v0) / gh), gy1 = min(MG - 1, (y1 - r1.v0) / gh) + 1;
+                    swin = (unsigned)gx0 | ((unsigned)gx1 << 6) | ((unsigned)gy0 << 12) | ((unsigned)gy1 << 18);
+                }
                 {
                     const int F[6][4] = {{0, 1, 2, 3}, {4, 5, 6, 7}, {0, 1, 5, 4}, {1, 2, 6, 5}, {2, 3, 7, 6}, {3, 0, 4, 7}};
                     float amax = 0.f;
@@ -248,7 +301,7 @@ score_prep_kernel(const WcrImage *__restrict__ images, const WcrBox *__restrict_
                     sb2.y = lowf > 0.f ? (int)lowf : 0;
                 }
             }
-            if (store) out_segb[(size_t)b * N + j] = sb2;
+            if (store) { out_segb[(size_t)b * N + j] = sb2; out_segwin[(size_t)b * N + j] = swin; }
         }
     }
     if (!use_pts) return;     // launched for the IoU term only

@@ -446,7 +446,13 @@ __device__ __forceinline__ float seg_bound_factor(const ScoreArgs &a, size_t o, 
 {
     if (!a.seg_tight) return 1.f;
     const int2 sb = __ldg(a.ws.segb + o);
-    return ipow(seg_ratio_bound(sb.x, sb.y, area), a.sc.e_seg);
+    // |mask & hull| <= the mask pixels of the grid cells the hull's scan window touches
+    const unsigned w = __ldg(a.ws.segwin + o);
+    const int gx0 = w & 63, gx1 = (w >> 6) & 63, gy0 = (w >> 12) & 63, gy1 = (w >> 18) & 63;
+    const int *mi = a.ws.mint + (o / (size_t)a.N) * (size_t)((MG + 1) * (MG + 1));
+    const int in_cells = (__ldg(mi + gy1 * (MG + 1) + gx1) - __ldg(mi + gy0 * (MG + 1) + gx1)) -
+                         (__ldg(mi + gy1 * (MG + 1) + gx0) - __ldg(mi + gy0 * (MG + 1) + gx0));
+    return ipow(seg_ratio_bound(min(sb.x, in_cells), sb.y, area), a.sc.e_seg);
 }
 
 // iou^a * pts^b of proposal q of the chunk, the product chunk_scores forms before the mask factor

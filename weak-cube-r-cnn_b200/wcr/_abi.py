@@ -39,7 +39,7 @@ SIGNATURES = {
     "wcr_sample_cubes": (c_int, [c_void_p, c_void_p, c_int, c_void_p, c_void_p, c_void_p, c_void_p,
                                  c_int, c_void_p, c_u64, c_void_p, c_void_p]),
     "wcr_score_workspace_bytes": (c_i64, [c_int, c_int, c_int]),
-    "wcr_score_bounds_offsets": (c_int, [c_int, c_int, c_int, c_void_p, c_void_p]),
+    "wcr_score_bounds_offsets": (c_int, [c_int, c_int, c_int, c_void_p, c_void_p, c_void_p, c_void_p]),
     "wcr_score_topk": (c_int, [c_void_p, c_void_p, c_int, c_void_p, c_int, c_void_p, c_void_p,
                                c_void_p, c_void_p, c_u64, c_void_p, c_void_p, c_void_p, c_int,
                                c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,

@@ -296,17 +296,21 @@ class ScoreWorkspace:
         return int(self.ws[16:24].view(torch.int64).item())
 
     def bounds(self):
-        """-> (ubcnt (n_boxes, N) int32, segb (n_boxes, N, 2) int32): views of the per-proposal
-        bounds the last on-demand ``score_topk`` on this workspace pruned with (upper bound of
-        the inside-count; max |mask & hull| and min |hull| pixels). Test hook."""
+        """-> (ubcnt (n_boxes, N) int32, segb (n_boxes, N, 2) int32, segwin (n_boxes, N) int32,
+        mint (n_boxes, 33, 33) int32): views of the per-proposal bounds the last on-demand
+        ``score_topk`` on this workspace pruned with (upper bound of the inside-count; max
+        |mask & hull| and min |hull| pixels; the scan window's cell range in the 32 x 32 mask grid
+        and that grid's integral tables). Test hook."""
         lib = _abi.load()
-        o1, o2 = ctypes.c_int64(), ctypes.c_int64()
-        _abi.check(lib.wcr_score_bounds_offsets(self.n_boxes, self.N, self.k, ctypes.byref(o1), ctypes.byref(o2)),
+        o = [ctypes.c_int64() for _ in range(4)]
+        _abi.check(lib.wcr_score_bounds_offsets(self.n_boxes, self.N, self.k, *[ctypes.byref(x) for x in o]),
                    "wcr_score_bounds_offsets")
         n = self.n_boxes * self.N
-        ub = self.ws[o1.value:o1.value + 4 * n].view(torch.int32).view(self.n_boxes, self.N)
-        sb = self.ws[o2.value:o2.value + 8 * n].view(torch.int32).view(self.n_boxes, self.N, 2)
-        return ub, sb
+        ub = self.ws[o[0].value:o[0].value + 4 * n].view(torch.int32).view(self.n_boxes, self.N)
+        sb = self.ws[o[1].value:o[1].value + 8 * n].view(torch.int32).view(self.n_boxes, self.N, 2)
+        sw = self.ws[o[2].value:o[2].value + 4 * n].view(torch.int32).view(self.n_boxes, self.N)
+        mi = self.ws[o[3].value:o[3].value + 4 * 1089 * self.n_boxes].view(torch.int32).view(self.n_boxes, 33, 33)
+        return ub, sb, sw, mi
 
     def proposals_pruned(self) -> int:
         """Proposals the last ``score_topk`` on this workspace never tested against the depth
