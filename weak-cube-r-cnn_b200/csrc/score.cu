@@ -575,7 +575,13 @@ static int pack_box_masks_launch(const char *who, const uint8_t *masks, int64_t 
     if (n_boxes == 0) return WCR_OK;
     WCR_REQUIRE(n_boxes <= 0x7fffffff / 4, "%s: too many boxes", who);
     // a 640 x 480 ROI is 2400 units of 128 pixels: 4 CTAs x 8 warps per box keep a small shard busy too
-    wcr::pack_box_masks_kernel<2><<<dim3(n_boxes, 4), 256, 0, (cudaStream_t)stream>>>(
+    // At most 3 CTAs x 8 warps per SM's worth of CTAs, each walking boxes in a grid-stride loop: plenty
+    // of requests in flight for PCIe (148 x 24 x 256 B), while two thirds of every SM's thread slots,
+    // its registers and all of its shared memory stay free for the next shard's unprojection, RANSAC
+    // and prep kernels that run beside a gather from host memory.
+    const int ctas = wcr::sm_count() * 3;
+    const int gx = n_boxes * 4 <= ctas ? n_boxes : max(1, ctas / 4);
+    wcr::pack_box_masks_kernel<2><<<dim3(gx, 4), 256, 0, (cudaStream_t)stream>>>(
         masks, mask_stride, mask_pitch, mask_idx, images, boxes, n_boxes, seg_off, out_bits);
     WCR_CHECK_LAUNCH("pack_box_masks_kernel");
     return WCR_OK;
