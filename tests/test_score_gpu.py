@@ -440,6 +440,28 @@ def test_score_pts_on_demand_equals_every_proposal(cuda_lib, N, k, e_pts, e_seg,
         assert torch.equal(bq["records"].view(torch.int32), ra.view(torch.int32)), mode
 
 
+def test_score_many_boxes_unsorted_plan(cuda_lib):
+    """More than 2048 boxes: the plan kernel keeps input order (no largest-first sort) and the
+    scoring kernel searches the item prefix in global memory instead of its shared-memory copy;
+    the library picks the on-demand paths by itself (>= 444 chunks). Records == full evaluation."""
+    from wcr import synth
+    from wcr.proposals import propose, score_topk, ScoreConfig, SegMasks
+    H, W, N = 120, 160, 96
+    ims, shard, boxes, priors, normals = _setup(3, H, W, n_boxes=700, first=91)
+    assert len(boxes) > 2048
+    masks = [m for im in ims for m in synth.seg_masks(im["boxes"], H, W)]
+    seg = SegMasks(shard, boxes, masks)
+    cubes = propose(shard, boxes, priors, normals, N, seed=5)
+    cfg = dict(e_seg=1, k=4)
+    full = score_topk(shard, boxes, cubes, cfg=ScoreConfig(**cfg), seg=seg, want_all=True)
+    rec_full = full["records"].clone()
+    auto = score_topk(shard, boxes, cubes, cfg=ScoreConfig(**cfg), seg=seg)
+    assert auto["workspace"].proposals_pruned() > 0
+    assert torch.equal(auto["records"].view(torch.int32), rec_full.view(torch.int32))
+    every = score_topk(shard, boxes, cubes, cfg=ScoreConfig(pts_eval=1, seg_eval=1, **cfg), seg=seg)
+    assert torch.equal(every["records"].view(torch.int32), rec_full.view(torch.int32))
+
+
 def test_score_custom_mapping_shaping(cuda_lib):
     """ScoreConfig.map_beta > 0 passes every term through custom_mapping (utils.py:207-223) before
     its exponent. Scores within 1e-5 of the composition of the oracle's terms with
