@@ -566,10 +566,24 @@ __device__ __forceinline__ void chunk_finalize_lazy(const ScoreArgs &a, int b, c
                                                     const ChunkCtx &c, int chunk, float *wbuf, int lane)
 {
     float *sc = wbuf + TL_SCORE_OFF;
+    if (a.pts_lazy && a.seg_tight) {
+        // only the proposals that were tested (first pass + survivors, ws.order) have a value
+        const int bc = b * a.n_chunks + chunk;
+        const uint16_t *list = a.ws.order + (size_t)bc * SC_CHUNK;
+        const int nlive = min(a.pa, c.chunk_n) + __ldcg(a.ws.bready + bc) - 1;
 #pragma unroll 8
-    for (int i = 0; i < SC_CHUNK / 32; ++i) {
-        const int loc = i * 32 + lane;
-        sc[loc] = loc < c.chunk_n ? __ldcg(a.ws.ub + c.cbase + loc) : -INFINITY;
+        for (int i = 0; i < SC_CHUNK / 32; ++i) sc[i * 32 + lane] = -INFINITY;
+        __syncwarp();
+        for (int s = lane; s < nlive; s += 32) {
+            const int loc = (int)__ldcg(list + s);
+            sc[loc] = __ldcg(a.ws.ub + c.cbase + loc);
+        }
+    } else {
+#pragma unroll 8
+        for (int i = 0; i < SC_CHUNK / 32; ++i) {
+            const int loc = i * 32 + lane;
+            sc[loc] = loc < c.chunk_n ? __ldcg(a.ws.ub + c.cbase + loc) : -INFINITY;
+        }
     }
     __syncwarp();
     chunk_select(a, b, bx, im, c, chunk, sc, wbuf, lane);
@@ -587,15 +601,34 @@ __device__ __forceinline__ void chunk_epilogue_warp(const ScoreArgs &a, int b, c
         return;
     }
     // ---- phase A ---------------------------------------------------------------------------
-    chunk_scores(a, b, bx, im, c, chunk, false, sc, lane);
+    if (a.pts_lazy && a.seg_tight) {
+        // Point term on demand: only the proposals that were tested -- the first pass and the
+        // survivors, the head of ws.order -- can be among the top-k (every other bound is below k
+        // actual scores); the rest is never looked at again (-inf in the selection)
+        if (a.out_npts && chunk == 0 && lane == 0) a.out_npts[b] = c.npts;
+        const int bc = b * a.n_chunks + chunk;
+        const uint16_t *list = a.ws.order + (size_t)bc * SC_CHUNK;
+        const int nlive = min(a.pa, c.chunk_n) + __ldcg(a.ws.bready + bc) - 1;
 #pragma unroll 8
-    for (int i = 0; i < SC_CHUNK / 32; ++i) {
-        const int loc = i * 32 + lane;
-        if (loc < c.chunk_n) {
-            // with mask-term bounds, ws.ub and sc[] hold product x bound of the mask factor; the
-            // fills recompute the plain product (fill_product)
-            if (a.seg_tight) sc[loc] = sc[loc] * seg_bound_factor(a, c.cbase + loc, c.area);
-            __stcg(a.ws.ub + c.cbase + loc, sc[loc]);
+        for (int i = 0; i < SC_CHUNK / 32; ++i) sc[i * 32 + lane] = -INFINITY;
+        __syncwarp();
+        for (int s = lane; s < nlive; s += 32) {
+            const int loc = (int)__ldcg(list + s);
+            const float tight = fill_product(a, c, loc) * seg_bound_factor(a, c.cbase + loc, c.area);
+            sc[loc] = tight;
+            __stcg(a.ws.ub + c.cbase + loc, tight);
+        }
+    } else {
+        chunk_scores(a, b, bx, im, c, chunk, false, sc, lane);
+#pragma unroll 8
+        for (int i = 0; i < SC_CHUNK / 32; ++i) {
+            const int loc = i * 32 + lane;
+            if (loc < c.chunk_n) {
+                // with mask-term bounds, ws.ub and sc[] hold product x bound of the mask factor; the
+                // fills recompute the plain product (fill_product)
+                if (a.seg_tight) sc[loc] = sc[loc] * seg_bound_factor(a, c.cbase + loc, c.area);
+                __stcg(a.ws.ub + c.cbase + loc, sc[loc]);
+            }
         }
     }
     __syncwarp();
