@@ -374,7 +374,9 @@ __device__ __forceinline__ ChunkCtx chunk_ctx(const ScoreArgs &a, int b, const W
     c.cbase = (size_t)b * a.N + (size_t)chunk * SC_CHUNK;
     c.chunk_n = min(SC_CHUNK, a.N - chunk * SC_CHUNK);
     int area = 0;
-    if (a.sc.e_seg > 0) {
+    if (a.sc.e_seg > 0 && a.seg_tight) {
+        area = __ldg(a.ws.mint + (size_t)b * ((MG + 1) * (MG + 1)) + (MG + 1) * (MG + 1) - 1);   // the mask grid's total
+    } else if (a.sc.e_seg > 0) {
         const Roi r1 = box_roi(bx, im.H, im.W, 1, true);
         const int nrows = r1.ncols > 0 ? r1.nrows : 0, wpr = (r1.ncols + 31) >> 5;
         const uint32_t *bits = a.seg_bits + a.seg_off[b];
