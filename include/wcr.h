@@ -265,6 +265,13 @@ int wcr_score_topk(const WcrImage *images, const WcrBox *boxes, int n_boxes,
                    float *out_records, float *out_scores, float *out_iou, float *out_seg,
                    int32_t *out_count, float *out_proj, int32_t *out_npts,
                    void *ws, void *stream);
+/* The persistent scoring kernel launches 3 CTAs per SM; wcr_score_set_reserved_ctas(n) makes the
+ * following wcr_score_topk calls of this process launch n fewer (at least one per SM stays), which
+ * leaves one CTA's worth of registers and shared memory free on n SMs for a kernel of another stream
+ * -- wcr.pipeline.ShardPipeline runs the next shard's mask gather there. 0 = default. Results do not
+ * depend on it. No reference counterpart. */
+int wcr_score_set_reserved_ctas(int n);
+
 /* wcr_score_topk whose scoring kernel -- the first launch of the chain that reads seg_bits -- waits
  * for the CUDA event `seg_ready` (cudaEvent_t or NULL) on `stream`: the kernels that prepare the
  * proposals do not need the masks and overlap a pack / upload still running on another stream

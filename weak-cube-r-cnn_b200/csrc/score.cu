@@ -309,6 +309,18 @@ extern "C" int wcr_score_bounds_offsets(int n_boxes, int N, int k, int64_t *off_
     return WCR_OK;
 }
 
+// CTAs the persistent scoring kernel leaves unlaunched (of its 3 per SM): the hardware then keeps
+// one CTA's worth of registers and shared memory free on that many SMs, where a kernel of ANOTHER
+// stream -- the next shard's mask gather from host memory -- runs underneath the pass instead of
+// after it (wcr_pack_box_masks then launches exactly that many 16-warp CTAs, one per freed slot). Process-wide; 0 (the default) = the whole GPU.
+static int g_reserved_ctas = 0;
+extern "C" int wcr_score_set_reserved_ctas(int n)
+{
+    if (n < 0) { wcr::set_error("wcr_score_set_reserved_ctas: n must be >= 0"); return WCR_EINVAL; }
+    g_reserved_ctas = n;
+    return WCR_OK;
+}
+
 extern "C" int wcr_score_topk(const WcrImage *images, const WcrBox *boxes, int n_boxes,
                               const float *cubes, int N, const float *priors,
                               const float *normals, const float *z0,
@@ -467,7 +479,7 @@ extern "C" int wcr_score_topk_after(const WcrImage *images, const WcrBox *boxes,
         WCR_CHECK_LAUNCH("score_maskgrid_kernel");
     }
     // FFMA2 point test, inside indicator on the integer pipe, 3 CTAs x 4 warps per SM
-    wcr::score_tiles_kernel<4, 3, 8, true, true><<<sms * 3, 128, 0, st>>>(a);
+    wcr::score_tiles_kernel<4, 3, 8, true, true><<<max(sms, sms * 3 - g_reserved_ctas), 128, 0, st>>>(a);
     WCR_CHECK_LAUNCH("score_tiles_kernel");
     return WCR_OK;
 #endif
@@ -579,10 +591,17 @@ static int pack_box_masks_launch(const char *who, const uint8_t *masks, int64_t 
     // of requests in flight for PCIe (148 x 24 x 256 B), while two thirds of every SM's thread slots,
     // its registers and all of its shared memory stay free for the next shard's unprojection, RANSAC
     // and prep kernels that run beside a gather from host memory.
-    const int ctas = wcr::sm_count() * 3;
-    const int gx = n_boxes * 4 <= ctas ? n_boxes : max(1, ctas / 4);
-    wcr::pack_box_masks_kernel<2><<<dim3(gx, 4), 256, 0, (cudaStream_t)stream>>>(
-        masks, mask_stride, mask_pitch, mask_idx, images, boxes, n_boxes, seg_off, out_bits);
+    if (g_reserved_ctas > 0) {
+        // background shape (wcr_score_set_reserved_ctas): one 16-warp CTA per slot the scoring kernel
+        // leaves free -- 16 K registers, beside two scoring CTAs -- each walking whole boxes
+        wcr::pack_box_masks_kernel<4><<<dim3(g_reserved_ctas, 1), 512, 0, (cudaStream_t)stream>>>(
+            masks, mask_stride, mask_pitch, mask_idx, images, boxes, n_boxes, seg_off, out_bits);
+    } else {
+        const int ctas = wcr::sm_count() * 3;
+        const int gx = n_boxes * 4 <= ctas ? n_boxes : max(1, ctas / 4);
+        wcr::pack_box_masks_kernel<2><<<dim3(gx, 4), 256, 0, (cudaStream_t)stream>>>(
+            masks, mask_stride, mask_pitch, mask_idx, images, boxes, n_boxes, seg_off, out_bits);
+    }
     WCR_CHECK_LAUNCH("pack_box_masks_kernel");
     return WCR_OK;
 }

@@ -44,6 +44,7 @@ SIGNATURES = {
                                c_void_p, c_void_p, c_u64, c_void_p, c_void_p, c_void_p, c_int,
                                c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
                                c_void_p, c_void_p, c_void_p]),
+    "wcr_score_set_reserved_ctas": (c_int, [c_int]),
     "wcr_score_topk_after": (c_int, [c_void_p, c_void_p, c_int, c_void_p, c_int, c_void_p, c_void_p,
                                      c_void_p, c_void_p, c_u64, c_void_p, c_void_p, c_void_p, c_int,
                                      c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,

@@ -129,8 +129,11 @@ class ShardRunner:
 
     def upload_inputs(self):
         """Depth, ground maps and boxes: everything the kernels ahead of the scoring kernel read."""
+        self.upload_boxes()
         self.d_depth.copy_(self.h_depth, non_blocking=True)
         self.d_ground.copy_(self.h_ground, non_blocking=True)
+
+    def upload_boxes(self):
         self.boxes.table.copy_(self.h_boxes, non_blocking=True)
 
     def upload_masks(self):
@@ -208,7 +211,7 @@ class ShardPipeline:
 
     NEW orchestration (no reference counterpart)."""
 
-    def __init__(self, runners: list[ShardRunner], after_step=None):
+    def __init__(self, runners: list[ShardRunner], after_step=None, reserve_ctas: int | None = None):
         """``after_step[k]()``, if given, is called on the compute stream right after slot k's pass
         (bench.py hangs the NCCL all-gather of the top-k records there)."""
         self.after_step = after_step
@@ -216,6 +219,10 @@ class ShardPipeline:
         self.runners = runners
         dev = runners[0].device
         self.device = dev
+        # mapped-memory mask gathers run beside the pass in CTA slots the scoring kernel leaves free
+        self.reserve_ctas = reserve_ctas if reserve_ctas is not None else \
+            (18 if any(r.h_seg_dense is not None and r.d_seg_dense is None for r in runners) else 0)
+        self.s_mask = torch.cuda.Stream(dev)
         self.s_up = torch.cuda.Stream(dev)
         self.s_run = torch.cuda.Stream(dev)
         self.s_down = torch.cuda.Stream(dev)
@@ -226,7 +233,7 @@ class ShardPipeline:
         self.ev_down = [torch.cuda.Event() for _ in range(n)]
         self.pending = [False] * n
         # work enqueued before the pipeline existed (allocations, warm-up) is on the current stream
-        for s in (self.s_up, self.s_run, self.s_down):
+        for s in (self.s_up, self.s_run, self.s_down, self.s_mask):
             s.wait_stream(torch.cuda.current_stream(dev))
 
     def slot(self, i: int) -> ShardRunner:
@@ -235,13 +242,26 @@ class ShardPipeline:
     def submit(self, i: int) -> None:
         k = i % len(self.runners)
         r = self.runners[k]
+        gather = r.h_seg_dense is not None and r.d_seg_dense is None   # masks gathered from mapped host memory
         with torch.cuda.stream(self.s_up):
             if self.pending[k]:
                 self.s_up.wait_event(self.ev_run[k])    # the slot's previous pass has read its inputs
             r.upload_inputs()
             self.ev_in[k].record(self.s_up)
-            r.upload_masks()                            # only the scoring kernel waits for these
-            self.ev_up[k].record(self.s_up)
+            if not gather:
+                r.upload_masks()                        # only the scoring kernel waits for these
+                self.ev_up[k].record(self.s_up)
+        if self.reserve_ctas:
+            _abi.check(_abi.load().wcr_score_set_reserved_ctas(self.reserve_ctas), "wcr_score_set_reserved_ctas")
+        if gather:
+            # The gather is a KERNEL reading host memory: it runs in the CTA slots the scoring kernel of
+            # the other slot's pass leaves free (reserve_ctas), AFTER the copies of this slot -- SM loads
+            # over PCIe beside copy-engine traffic slow the pass itself (5.6 vs 5.0 ms per step,
+            # tools/time_interference.py); one behind the other both hide inside the pass.
+            with torch.cuda.stream(self.s_mask):
+                self.s_mask.wait_event(self.ev_in[k])
+                r.upload_masks()
+                self.ev_up[k].record(self.s_mask)
         with torch.cuda.stream(self.s_run):
             self.s_run.wait_event(self.ev_in[k])
             if self.pending[k]:
@@ -249,7 +269,11 @@ class ShardPipeline:
             dense_on_device = r.d_seg_dense is not None # packed by step() itself on this stream: needs the maps
             if dense_on_device:
                 self.s_run.wait_event(self.ev_up[k])
-            r.step(seg_ready=None if dense_on_device else self.ev_up[k])
+            try:
+                r.step(seg_ready=None if dense_on_device else self.ev_up[k])
+            finally:
+                if self.reserve_ctas:
+                    _abi.load().wcr_score_set_reserved_ctas(0)
             if self.after_step is not None:
                 self.after_step[k]()
             self.ev_run[k].record(self.s_run)
@@ -269,5 +293,5 @@ class ShardPipeline:
         return self.runners[k].h_records
 
     def drain(self) -> None:
-        for s in (self.s_up, self.s_run, self.s_down):
+        for s in (self.s_up, self.s_mask, self.s_run, self.s_down):
             s.synchronize()
