@@ -52,6 +52,9 @@ def parse():
     ap.add_argument("--c4-images", type=int, default=8192,
                     help="global image count of the strong-scaling block (BASELINE configs[3]); 0 = skip")
     ap.add_argument("--c4-passes", type=int, default=3)
+    ap.add_argument("--e2e-reserve-ctas", type=int, default=None,
+                    help="CTA slots the scoring kernel leaves free for the mask gather of the other pipeline slot "
+                         "(default: ShardPipeline's, 18 with mapped dense masks; 0 = gather between the passes)")
     ap.add_argument("--dense-mode", default="mapped", choices=["roi", "rows", "mapped", "copy"],
                     help="how the e2e arm moves the dense per-box masks (ShardRunner dense_seg)")
     return ap.parse_args()
@@ -441,7 +444,9 @@ def run_wcr(args):
     # of shard s - 1 are downloaded while shard s is scored. Every step still copies all of its
     # inputs from pinned host memory and its records back.
     def pipelined(r_a, r_b, g_a, g_b):
-        pipe = ShardPipeline([r_a, r_b], after_step=[g_a.gather_padded, g_b.gather_padded] if world > 1 else None)
+        reserve = args.e2e_reserve_ctas
+        pipe = ShardPipeline([r_a, r_b], after_step=[g_a.gather_padded, g_b.gather_padded] if world > 1 else None,
+                             reserve_ctas=reserve)
         for s in range(4):
             pipe.wait(s - 2); pipe.submit(s)
         pipe.drain()
