@@ -162,7 +162,8 @@ class ShardRunner:
                 "wcr_h2d_box_mask_rois")
 
     def step(self, score_events=None, seg_ready=None):
-        """Device-resident pass: 5 kernel launches, no host sync, no D2H.
+        """Device-resident pass: 10 kernel launches (ground unprojection, RANSAC count + select, box depth,
+        plan, depth grid, prep, order, mask grid, scoring), no host sync, no D2H.
         ``score_events`` = (start, end) torch.cuda.Events recorded around the fused
         scoring launch (bench.py's roofline timing). ``seg_ready``: event after which the masks
         of this step are on the device (``upload_masks`` on another stream); None: already there."""
