@@ -398,7 +398,7 @@ def test_score_seg_on_demand_equals_full_evaluation(cuda_lib, N, k, e_pts, e_seg
 
 @pytest.mark.parametrize("N,k,e_pts,e_seg,e_iou", [(300, 16, 1, 1, 1), (1000, 16, 1, 1, 1), (1000, 16, 1, 0, 1),
                                                    (1500, 32, 1, 2, 1), (50, 4, 1, 0, 1), (100, 4, 1, 1, 1), (700, 8, 2, 1, 0),
-                                                   (2500, 1, 2, 0, 1), (1000, 16, 1, 1, 2)])
+                                                   (2500, 1, 2, 0, 1), (1000, 16, 1, 1, 2), (1025, 4, 1, 1, 1), (33, 2, 1, 0, 1)])
 def test_score_pts_on_demand_equals_every_proposal(cuda_lib, N, k, e_pts, e_seg, e_iou):
     """pts_eval=2: the tiles are walked twice; the second pass skips every proposal whose score bound
     (IoU factor x share of the ROI's points its cull box can reach) is below the k-th best score of
